@@ -1,0 +1,330 @@
+// K4: backward of the embedding side.  No per-lookup gradient tensor is ever materialised: the
+// sorted lookup list is walked in fixed chunks and the gradient of each lookup is formed on the
+// fly from dX0 (the MLP's input gradient), the saved FM sum and the head weights, accumulated in
+// registers per run of equal row ids and written once per (row, chunk).  The Adam update then
+// consumes those partials in chunk order, so the whole scatter-add is deterministic.
+#include "ctr_common.cuh"
+
+namespace {
+
+constexpr int CH = CTR_BWD_CHUNK;
+
+template <int K>
+__global__ void __launch_bounds__(256)
+embed_bwd_partials_kernel(const ctr_embed_cfg cfg, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ perm,
+                          const uint32_t* __restrict__ uidx, const int64_t n, const int32_t* __restrict__ field_of_slot,
+                          const float* __restrict__ x0, const float* __restrict__ dx0, const int64_t dx0_ld,
+                          const float* __restrict__ sum_e, const float* __restrict__ dlogit,
+                          const float* __restrict__ w_fm, const float* __restrict__ inv_cnt_emb,
+                          const float* __restrict__ inv_cnt_first, float* __restrict__ part) {
+    constexpr int G = K;       // lanes per chunk walker: lane j owns embedding coordinate j
+    constexpr int UN = 4;      // lookups in flight per walker
+    const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t c = t / G;   // chunk index
+    const int j = (int) (t % G);
+    const int64_t base = c * CH;
+    if (base >= n) return;
+    const int cnt = (int) ((n - base) < CH ? (n - base) : CH);
+    const int Fc = cfg.Fc, Fm = cfg.Fm, ids_ld = cfg.ids_ld, gs = cfg.grad_stride;
+    const bool use_fm = cfg.use_fm != 0, has_first = cfg.has_first != 0;
+    const float* __restrict__ w1 = w_fm;                         // first-order head weights, per field
+    const float w2j = use_fm ? w_fm[Fc + Fm + cfg.C + j] : 0.f;  // second-order head weight of coordinate j
+
+    uint32_t cur = CTR_PAD_KEY;
+    int64_t cur_slot = 0;
+    float acc = 0.f, accw = 0.f;
+
+    for (int i0 = 0; i0 < cnt; i0 += UN) {
+        uint32_t key[UN], u[UN];
+        float gv[UN], gw[UN];
+#pragma unroll
+        for (int q = 0; q < UN; ++q) {
+            const int i = i0 + q;
+            key[q] = CTR_PAD_KEY; u[q] = 0; gv[q] = 0.f; gw[q] = 0.f;
+            if (i < cnt) {
+                key[q] = keys[base + i];
+                if (key[q] != CTR_PAD_KEY) {
+                    u[q] = uidx[base + i];
+                    const uint32_t p = perm[base + i];
+                    const uint32_t b = p / (uint32_t) ids_ld;
+                    const int slot = (int) (p - b * (uint32_t) ids_ld);
+                    int fld = slot;
+                    float sc_e = 1.f, sc_w = 1.f;
+                    if (slot >= Fc) {
+                        const int jm = field_of_slot[slot - Fc];
+                        fld = Fc + jm;
+                        sc_e = inv_cnt_emb[(int64_t) b * Fm + jm];
+                        sc_w = inv_cnt_first[(int64_t) b * Fm + jm];
+                    }
+                    const float dl = dlogit[b];
+                    float g = dx0[(int64_t) b * dx0_ld + fld * K + j];
+                    if (use_fm) {
+                        const float s = sum_e[(int64_t) b * K + j];
+                        const float xv = x0[(int64_t) b * cfg.x0_ld + fld * K + j];
+                        g = fmaf(dl * w2j, s - xv, g);
+                        gw[q] = sc_w * dl * w1[fld];
+                    }
+                    gv[q] = sc_e * g;
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < UN; ++q) {
+            if (i0 + q < cnt) {
+                if (key[q] != cur) {
+                    if (cur != CTR_PAD_KEY) {
+                        part[cur_slot * gs + j] = acc;
+                        if (has_first && j == 0) part[cur_slot * gs + K] = accw;
+                    }
+                    cur = key[q];
+                    cur_slot = (int64_t) u[q] + c;
+                    acc = 0.f; accw = 0.f;
+                }
+                acc += gv[q];
+                accw += gw[q];
+            }
+        }
+    }
+    if (cur != CTR_PAD_KEY) {
+        part[cur_slot * gs + j] = acc;
+        if (has_first && j == 0) part[cur_slot * gs + K] = accw;
+    }
+}
+
+// sum of the partials of run u, coordinate j, in chunk order
+__device__ __forceinline__ float sum_run_partials(const float* __restrict__ part, const uint32_t* __restrict__ seg_start,
+                                                  int64_t u, int j, int gs) {
+    const uint32_t s = seg_start[u], e = seg_start[u + 1];
+    const int64_t c0 = s / CH, c1 = (e - 1) / CH;
+    const float* p = part + (u + c0) * gs + j;
+    const int64_t np = c1 - c0 + 1;
+    if (np == 1) return p[0];
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    int64_t i = 0;
+    for (; i + 4 <= np; i += 4) {
+        a0 += p[(i + 0) * gs];
+        a1 += p[(i + 1) * gs];
+        a2 += p[(i + 2) * gs];
+        a3 += p[(i + 3) * gs];
+    }
+    for (; i < np; ++i) a0 += p[i * gs];
+    return (a0 + a1) + (a2 + a3);
+}
+
+__global__ void __launch_bounds__(256)
+embed_bwd_finalize_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ n_unique, int64_t n_max,
+                          int width, int gs, const float* __restrict__ part, float* __restrict__ grads) {
+    int64_t U = *n_unique;
+    if (U > n_max) U = n_max;
+    const int64_t total = U * width;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t u = t / width;
+        const int j = (int) (t - u * width);
+        grads[u * gs + j] = sum_run_partials(part, seg_start, u, j, gs);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restrict__ n_rows, int64_t n_max, uint32_t mask,
+                 const float* __restrict__ grads, const uint32_t* __restrict__ seg_start, int gs, int width,
+                 float* __restrict__ table, float* __restrict__ m, float* __restrict__ v, int stride, int64_t table_rows,
+                 const float* __restrict__ extra_grad, int64_t extra_base, int extra_n, uint8_t* __restrict__ extra_hit,
+                 uint8_t* __restrict__ touched, const ctr_adam_hp hp) {
+    int64_t U = n_rows ? (int64_t) *n_rows : n_max;
+    if (U > n_max) U = n_max;
+    const int64_t total = U * width;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t u = t / width;
+        const int j = (int) (t - u * width);
+        const uint32_t key = row_ids[u];
+        if (key == CTR_PAD_KEY) continue;
+        const int64_t row = (int64_t) (key & mask);
+        if (row >= table_rows) continue;   // defensive: never write outside the table
+        float g = seg_start ? sum_run_partials(grads, seg_start, u, j, gs) : grads[u * gs + j];
+        if (extra_grad && row >= extra_base && row < extra_base + extra_n) {
+            g += extra_grad[(row - extra_base) * gs + j];
+            if (j == 0 && extra_hit) extra_hit[row - extra_base] = 1;
+        }
+        const int64_t o = row * stride + j;
+        const float mm = hp.beta1 * m[o] + (1.f - hp.beta1) * g;
+        const float vv = hp.beta2 * v[o] + (1.f - hp.beta2) * g * g;
+        m[o] = mm;
+        v[o] = vv;
+        table[o] -= hp.lr_t * mm / (sqrtf(vv) + hp.eps);
+        if (j == 0 && touched) touched[row] = 1;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+adam_dense_kernel(float* __restrict__ theta, float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g,
+                  int64_t n, float l2, float l1, uint8_t* __restrict__ skip, int skip_group, const ctr_adam_hp hp) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        if (skip && skip[i / skip_group]) continue;
+        const float th = theta[i];
+        float gi = g ? g[i] : 0.f;
+        if (l2 != 0.f) gi = fmaf(l2, th, gi);
+        if (l1 != 0.f) gi += l1 * (th > 0.f ? 1.f : (th < 0.f ? -1.f : 0.f));
+        const float mm = hp.beta1 * m[i] + (1.f - hp.beta1) * gi;
+        const float vv = hp.beta2 * v[i] + (1.f - hp.beta2) * gi * gi;
+        m[i] = mm;
+        v[i] = vv;
+        theta[i] = th - hp.lr_t * mm / (sqrtf(vv) + hp.eps);
+    }
+}
+
+__global__ void clear_flags_kernel(uint8_t* __restrict__ f, int64_t n) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) f[i] = 0;
+}
+
+// gradient of the continuous-field rows: pass 1 = per-block partial over a fixed slice of samples
+__global__ void __launch_bounds__(256)
+cont_bwd_pass1(const ctr_embed_cfg cfg, const float* __restrict__ cont, const float* __restrict__ cont_rows,
+               const float* __restrict__ sum_e, const float* __restrict__ dlogit, const float* __restrict__ w_fm,
+               float* __restrict__ ws) {
+    const int K = cfg.k, C = cfg.C, W = K + 1;
+    const int npairs = C * W;
+    const int64_t per = ((int64_t) cfg.B + gridDim.x - 1) / gridDim.x;
+    const int64_t lo = per * blockIdx.x, hi = (lo + per < cfg.B) ? lo + per : cfg.B;
+    const float* w1c = w_fm + cfg.Fc + cfg.Fm;
+    const float* w2 = w_fm + cfg.Fc + cfg.Fm + C;
+    for (int pr = threadIdx.x; pr < npairs; pr += blockDim.x) {
+        const int c = pr / W, j = pr - c * W;
+        float acc = 0.f;
+        if (j < K) {
+            const float th = cont_rows[(int64_t) c * cfg.table_stride + j];
+            const float w = w2[j];
+            for (int64_t b = lo; b < hi; ++b) {
+                const float x = cont[b * C + c];
+                acc = fmaf(x * dlogit[b] * w, sum_e[b * K + j] - x * th, acc);
+            }
+        } else if (cfg.has_first) {
+            const float w = w1c[c];
+            for (int64_t b = lo; b < hi; ++b) acc = fmaf(dlogit[b] * w, cont[b * C + c], acc);
+        }
+        ws[(int64_t) blockIdx.x * npairs + pr] = acc;
+    }
+}
+
+__global__ void cont_bwd_pass2(const float* __restrict__ ws, int nblk, int C, int K, int gs, float* __restrict__ out) {
+    const int W = K + 1, npairs = C * W;
+    int pr = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pr >= npairs) return;
+    float acc = 0.f;
+    for (int b = 0; b < nblk; ++b) acc += ws[(int64_t) b * npairs + pr];
+    const int c = pr / W, j = pr - c * W;
+    out[c * gs + j] = acc;
+}
+
+inline int cont_blocks(ctr_handle* h, int B) {
+    int64_t nb = ctr_cdiv(B > 0 ? B : 1, 64);
+    int64_t cap = (int64_t) h->sm_count * 8;
+    return (int) (nb < cap ? nb : cap);
+}
+
+}  // namespace
+
+int ctr_check_embed_cfg(ctr_handle* h, const ctr_embed_cfg* c);   // embed_fwd.cu
+
+extern "C" int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const uint32_t* sorted_keys,
+                                      const uint32_t* perm, const uint32_t* uidx, int64_t n, const int32_t* field_of_slot,
+                                      const float* x0, const float* dx0, int64_t dx0_ld, const float* sum_e,
+                                      const float* dlogit, const float* w_fm, const float* inv_cnt_emb,
+                                      const float* inv_cnt_first, float* part) {
+    int rc = ctr_check_embed_cfg(h, cfg);
+    if (rc) return rc;
+    CTR_REQUIRE(h, sorted_keys && perm && uidx && dx0 && part && n >= 0, "embed_bwd_partials: null pointer");
+    CTR_REQUIRE(h, cfg->grad_stride >= cfg->k + (cfg->has_first ? 1 : 0), "embed_bwd_partials: grad_stride too small");
+    CTR_REQUIRE(h, !cfg->use_fm || (x0 && sum_e && dlogit && w_fm), "embed_bwd_partials: FM inputs null");
+    CTR_REQUIRE(h, cfg->M == 0 || (field_of_slot && inv_cnt_emb && inv_cnt_first), "embed_bwd_partials: multi inputs null");
+    CTR_REQUIRE(h, dx0_ld >= (int64_t) (cfg->Fc + cfg->Fm) * cfg->k, "embed_bwd_partials: dx0_ld too small");
+    if (n == 0) return CTR_OK;
+    const int64_t chunks = ctr_cdiv(n, CH);
+    const int64_t threads = chunks * cfg->k;
+    const unsigned blocks = (unsigned) ctr_cdiv(threads, 256);
+#define LAUNCH_BP(KK)                                                                                                  \
+    embed_bwd_partials_kernel<KK><<<blocks, 256, 0, ctr_st(s)>>>(*cfg, sorted_keys, perm, uidx, n, field_of_slot, x0, dx0, \
+                                                                dx0_ld, sum_e, dlogit, w_fm, inv_cnt_emb, inv_cnt_first,   \
+                                                                part)
+    switch (cfg->k) {
+        case 4: LAUNCH_BP(4); break;
+        case 8: LAUNCH_BP(8); break;
+        case 16: LAUNCH_BP(16); break;
+        default: LAUNCH_BP(32); break;
+    }
+#undef LAUNCH_BP
+    CTR_CHECK_LAUNCH(h, "embed_bwd_partials");
+    return CTR_OK;
+}
+
+static inline unsigned grid_for(ctr_handle* h, int64_t total) {
+    int64_t blocks = ctr_cdiv(total > 0 ? total : 1, 256);
+    int64_t cap = (int64_t) h->sm_count * 16;
+    return (unsigned) (blocks < cap ? blocks : cap);
+}
+
+extern "C" int ctr_embed_bwd_finalize(ctr_handle* h, ctr_stream s, const uint32_t* seg_start, const uint32_t* n_unique,
+                                      int64_t n_max, int width, int grad_stride, const float* part, float* grads) {
+    CTR_REQUIRE(h, seg_start && n_unique && part && grads && width > 0 && grad_stride >= width && n_max >= 0,
+                "embed_bwd_finalize: bad args");
+    if (n_max == 0) return CTR_OK;
+    embed_bwd_finalize_kernel<<<grid_for(h, n_max * width), 256, 0, ctr_st(s)>>>(seg_start, n_unique, n_max, width,
+                                                                                  grad_stride, part, grads);
+    CTR_CHECK_LAUNCH(h, "embed_bwd_finalize");
+    return CTR_OK;
+}
+
+extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
+                             int local_bits, const float* grads, const uint32_t* seg_start, int grad_stride, int width,
+                             float* table, float* m, float* v, int table_stride, int64_t table_rows,
+                             const float* extra_grad, int64_t extra_base, int extra_n, uint8_t* extra_hit,
+                             uint8_t* touched, const ctr_adam_hp* hp) {
+    CTR_REQUIRE(h, row_ids && grads && table && m && v && hp, "adam_rows: null pointer");
+    CTR_REQUIRE(h, width > 0 && grad_stride >= width && table_stride >= width && n_max >= 0 && table_rows > 0,
+                "adam_rows: bad sizes");
+    if (n_max == 0) return CTR_OK;
+    uint32_t mask = (local_bits <= 0 || local_bits >= 32) ? 0xFFFFFFFFu : ((1u << local_bits) - 1u);
+    adam_rows_kernel<<<grid_for(h, n_max * width), 256, 0, ctr_st(s)>>>(row_ids, n_rows, n_max, mask, grads, seg_start,
+                                                                         grad_stride, width, table, m, v, table_stride,
+                                                                         table_rows, extra_grad, extra_base, extra_n,
+                                                                         extra_hit, touched, *hp);
+    CTR_CHECK_LAUNCH(h, "adam_rows");
+    return CTR_OK;
+}
+
+extern "C" int ctr_adam_dense(ctr_handle* h, ctr_stream s, float* theta, float* m, float* v, const float* g, int64_t n,
+                              float l2, float l1, uint8_t* skip, int skip_group, const ctr_adam_hp* hp) {
+    CTR_REQUIRE(h, theta && m && v && hp && n >= 0 && (!skip || skip_group > 0), "adam_dense: bad args");
+    if (n == 0) return CTR_OK;
+    adam_dense_kernel<<<grid_for(h, n), 256, 0, ctr_st(s)>>>(theta, m, v, g, n, l2, l1, skip, skip_group, *hp);
+    CTR_CHECK_LAUNCH(h, "adam_dense");
+    if (skip) {
+        int64_t nf = ctr_cdiv(n, skip_group);
+        clear_flags_kernel<<<grid_for(h, nf), 256, 0, ctr_st(s)>>>(skip, nf);
+        CTR_CHECK_LAUNCH(h, "clear_flags");
+    }
+    return CTR_OK;
+}
+
+extern "C" int64_t ctr_cont_bwd_ws_bytes(ctr_handle* h, const ctr_embed_cfg* cfg) {
+    if (!h || !cfg) return 0;
+    return (int64_t) cont_blocks(h, cfg->B) * cfg->C * (cfg->k + 1) * 4 + 256;
+}
+
+extern "C" int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const float* cont,
+                               const float* cont_rows, const float* sum_e, const float* dlogit, const float* w_fm,
+                               float* cont_grad, void* ws, int64_t ws_bytes) {
+    int rc = ctr_check_embed_cfg(h, cfg);
+    if (rc) return rc;
+    if (cfg->C == 0 || cfg->B == 0) return CTR_OK;
+    CTR_REQUIRE(h, cont && cont_rows && sum_e && dlogit && w_fm && cont_grad && ws, "fm_cont_bwd: null pointer");
+    CTR_REQUIRE(h, cfg->grad_stride >= cfg->k + 1, "fm_cont_bwd: grad_stride too small");
+    if (ws_bytes < ctr_cont_bwd_ws_bytes(h, cfg)) return ctr_fail(h, CTR_E_WORKSPACE, "fm_cont_bwd: ws too small");
+    const int nblk = cont_blocks(h, cfg->B);
+    cont_bwd_pass1<<<nblk, 256, 0, ctr_st(s)>>>(*cfg, cont, cont_rows, sum_e, dlogit, w_fm, (float*) ws);
+    CTR_CHECK_LAUNCH(h, "cont_bwd_pass1");
+    const int npairs = cfg->C * (cfg->k + 1);
+    cont_bwd_pass2<<<(unsigned) ctr_cdiv(npairs, 128), 128, 0, ctr_st(s)>>>((const float*) ws, nblk, cfg->C, cfg->k,
+                                                                          cfg->grad_stride, cont_grad);
+    CTR_CHECK_LAUNCH(h, "cont_bwd_pass2");
+    return CTR_OK;
+}

@@ -1,0 +1,301 @@
+// K1 / K2: field-wise embedding gather fused with the FM first/second-order terms.
+//
+// One warp per sample.  A row of k floats is fetched by k/4 lanes with one 128-bit load each, so a
+// warp-wide load instruction brings in 32/(k/4) table rows at once and the same registers feed
+//   (1) the FM accumulators  sum_f e  and  sum_f e^2,
+//   (2) the deep-tower input tile X0 (written as one contiguous, fully coalesced run per warp store),
+//   (3) the first-order output.
+// Every table row is therefore read from HBM exactly once per lookup (the reference gathers
+// feats_emb twice and feats once: models/deepfm.py:78,85,98).
+#include "ctr_common.cuh"
+
+namespace {
+
+struct f4 {
+    float x, y, z, w;
+};
+
+__device__ __forceinline__ float4 f4_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+__device__ __forceinline__ void f4_acc(float4& s, float4& q, const float4 e) {
+    s.x += e.x; s.y += e.y; s.z += e.z; s.w += e.w;
+    q.x = fmaf(e.x, e.x, q.x); q.y = fmaf(e.y, e.y, q.y); q.z = fmaf(e.z, e.z, q.z); q.w = fmaf(e.w, e.w, q.w);
+}
+__device__ __forceinline__ float4 f4_shfl_xor_add(float4 v, int o) {
+    v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+    v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+    v.z += __shfl_xor_sync(0xffffffffu, v.z, o);
+    v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
+    return v;
+}
+
+template <int K, bool USE_FM>
+__global__ void __launch_bounds__(256)
+fm_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, const void* __restrict__ ids,
+                     const int64_t id_offset, const float* __restrict__ cont, const float* __restrict__ vec,
+                     const float* __restrict__ cont_rows, const float* __restrict__ pooled_first,
+                     float* __restrict__ x0, float* __restrict__ fm, float* __restrict__ sum_e) {
+    constexpr int LPR = K / 4;       // lanes per row
+    constexpr int RPW = 32 / LPR;    // rows per warp-wide load
+    constexpr int UNR = 4;           // independent row loads in flight per lane
+    const int lane = threadIdx.x & 31;
+    const int64_t b = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (b >= cfg.B) return;
+    const int r = lane / LPR, q = lane % LPR;
+    const int Fc = cfg.Fc, Fm = cfg.Fm, C = cfg.C, V = cfg.V;
+    const int stride = cfg.table_stride;
+    const int64_t idrow = b * (int64_t) cfg.ids_ld;
+    float* __restrict__ x0row = x0 + b * (int64_t) cfg.x0_ld;
+    float* __restrict__ fmrow = USE_FM ? fm + b * (int64_t) cfg.fm_ld : nullptr;
+    const bool has_first = cfg.has_first != 0;
+    const bool zero0 = cfg.zero_row0 != 0;
+
+    float4 as = f4_zero(), aq = f4_zero();
+
+    // ---- single-valued fields: gather ------------------------------------------------
+    for (int f0 = 0; f0 < Fc; f0 += RPW * UNR) {
+        int64_t rid[UNR];
+        bool ok[UNR], live[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            int f = f0 + u * RPW + r;
+            ok[u] = f < Fc;
+            rid[u] = ok[u] ? ctr_load_id(ids, cfg.id_bytes, idrow + f) + id_offset : 0;
+            live[u] = ok[u] && !(zero0 && rid[u] == 0);
+        }
+        float4 e[UNR];
+        float w[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            const float* row = table + rid[u] * (int64_t) stride;
+            e[u] = live[u] ? ctr_ldg_f4_stream(row + q * 4) : f4_zero();
+            w[u] = (USE_FM && live[u] && has_first && q == 0) ? ctr_ldg_f1_stream(row + K) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            if (ok[u]) {
+                int f = f0 + u * RPW + r;
+                *reinterpret_cast<float4*>(x0row + f * K + q * 4) = e[u];
+                if (USE_FM) {
+                    f4_acc(as, aq, e[u]);
+                    if (q == 0) fmrow[f] = w[u];
+                }
+            }
+        }
+    }
+
+    // ---- continuous / vector values -> X0 ----------------------------------------------
+    const int cont_col = (Fc + Fm) * K;
+    for (int c = lane; c < C; c += 32) x0row[cont_col + c] = cont[b * (int64_t) C + c];
+    for (int j = lane; j < V; j += 32) x0row[cont_col + C + j] = vec[b * (int64_t) V + j];
+    for (int j = cont_col + C + V + lane; j < cfg.x0_ld; j += 32) x0row[j] = 0.f;
+
+    if (!USE_FM) return;
+
+    // ---- pooled multi-valued fields enter the FM as one field each (models/deepfm_multi.py:165-167)
+    for (int j0 = 0; j0 < Fm; j0 += RPW) {
+        int j = j0 + r;
+        if (j < Fm) {
+            float4 e = *reinterpret_cast<const float4*>(x0row + (Fc + j) * K + q * 4);
+            f4_acc(as, aq, e);
+            if (q == 0) fmrow[Fc + j] = pooled_first ? pooled_first[b * (int64_t) Fm + j] : 0.f;
+        }
+    }
+
+    // ---- continuous fields: e = x * theta_c  (models/deepfm.py:85-87) ------------------------
+    if (cfg.fm_cont) {
+        for (int c0 = 0; c0 < C; c0 += RPW) {
+            int c = c0 + r;
+            if (c < C) {
+                float x = cont[b * (int64_t) C + c];
+                const float* row = cont_rows + c * (int64_t) stride;
+                float4 t = __ldg(reinterpret_cast<const float4*>(row + q * 4));
+                float4 e = make_float4(t.x * x, t.y * x, t.z * x, t.w * x);
+                f4_acc(as, aq, e);
+                if (q == 0) fmrow[Fc + Fm + c] = (has_first ? __ldg(row + K) : 0.f) * x;
+            }
+        }
+    } else {
+        for (int c = lane; c < C; c += 32) fmrow[Fc + Fm + c] = 0.f;
+    }
+
+    // ---- reduce the row slots, finish 0.5 * ((sum e)^2 - sum e^2)  (models/deepfm.py:88-92)
+#pragma unroll
+    for (int o = LPR; o < 32; o <<= 1) {
+        as = f4_shfl_xor_add(as, o);
+        aq = f4_shfl_xor_add(aq, o);
+    }
+    if (r == 0) {
+        float* sec = fmrow + Fc + Fm + C + q * 4;
+        sec[0] = 0.5f * (as.x * as.x - aq.x);
+        sec[1] = 0.5f * (as.y * as.y - aq.y);
+        sec[2] = 0.5f * (as.z * as.z - aq.z);
+        sec[3] = 0.5f * (as.w * as.w - aq.w);
+        *reinterpret_cast<float4*>(sum_e + b * (int64_t) K + q * 4) = as;
+    }
+}
+
+// K2: one warp per (sample, multi-valued field)
+template <int K>
+__global__ void __launch_bounds__(256)
+pooled_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, const void* __restrict__ ids,
+                         const int32_t* __restrict__ multi_start, const float* __restrict__ slot_weight,
+                         float* __restrict__ x0, float* __restrict__ pooled_first, float* __restrict__ inv_cnt_emb,
+                         float* __restrict__ inv_cnt_first) {
+    constexpr int LPR = K / 4;
+    constexpr int RPW = 32 / LPR;
+    const int lane = threadIdx.x & 31;
+    const int64_t item = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int Fm = cfg.Fm;
+    if (item >= (int64_t) cfg.B * Fm) return;
+    const int64_t b = item / Fm;
+    const int j = (int) (item - b * Fm);
+    const int r = lane / LPR, q = lane % LPR;
+    const int s0 = multi_start[j], s1 = multi_start[j + 1];
+    const int stride = cfg.table_stride;
+    const bool has_first = cfg.has_first != 0, zero0 = cfg.zero_row0 != 0;
+    const int64_t idrow = b * (int64_t) cfg.ids_ld + cfg.Fc;
+
+    float4 acc = f4_zero();
+    float accw = 0.f;
+    int cnt_e = 0, cnt_w = 0;
+    for (int t0 = s0; t0 < s1; t0 += RPW) {
+        int t = t0 + r;
+        bool ok = t < s1;
+        int64_t rid = ok ? ctr_load_id(ids, cfg.id_bytes, idrow + t) : 0;
+        bool live = ok && !(zero0 && rid == 0);
+        const float* row = table + rid * (int64_t) stride;
+        float4 e = live ? ctr_ldg_f4_stream(row + q * 4) : f4_zero();
+        float w = (live && has_first && q == 0) ? ctr_ldg_f1_stream(row + K) : 0.f;
+        float sw = (ok && slot_weight) ? slot_weight[b * (int64_t) cfg.M + t] : 1.f;
+        // row sum over the k coordinates (models/deepfm_multi.py:84 axis_2_sum)
+        float rs = (e.x + e.y) + (e.z + e.w);
+#pragma unroll
+        for (int o = 1; o < LPR; o <<= 1) rs += __shfl_xor_sync(0xffffffffu, rs, o);
+        bool nz_e = cfg.count_rule == 0 ? (rs != 0.f) : live;
+        bool nz_w = cfg.count_rule == 0 ? (w != 0.f) : live;
+        cnt_e += __popc(__ballot_sync(0xffffffffu, ok && q == 0 && nz_e));
+        cnt_w += __popc(__ballot_sync(0xffffffffu, ok && q == 0 && nz_w));
+        acc.x = fmaf(e.x, sw, acc.x); acc.y = fmaf(e.y, sw, acc.y);
+        acc.z = fmaf(e.z, sw, acc.z); acc.w = fmaf(e.w, sw, acc.w);
+        accw = fmaf(w, sw, accw);
+    }
+#pragma unroll
+    for (int o = LPR; o < 32; o <<= 1) {
+        acc = f4_shfl_xor_add(acc, o);
+        accw += __shfl_xor_sync(0xffffffffu, accw, o);
+    }
+    const bool mean = cfg.combiner == 0;
+    if (r == 0) {
+        float4 p = acc;
+        if (mean) {
+            if (cnt_e > 0) {
+                float c = (float) cnt_e;
+                p = make_float4(acc.x / c, acc.y / c, acc.z / c, acc.w / c);
+            } else {
+                p = f4_zero();   // tf.div_no_nan
+            }
+        }
+        *reinterpret_cast<float4*>(x0 + b * (int64_t) cfg.x0_ld + (cfg.Fc + j) * K + q * 4) = p;
+    }
+    if (lane == 0) {
+        float pw = accw;
+        if (mean) pw = cnt_w > 0 ? accw / (float) cnt_w : 0.f;
+        pooled_first[item] = pw;
+        inv_cnt_emb[item] = mean ? (cnt_e > 0 ? 1.f / (float) cnt_e : 0.f) : 1.f;
+        inv_cnt_first[item] = mean ? (cnt_w > 0 ? 1.f / (float) cnt_w : 0.f) : 1.f;
+    }
+}
+
+__global__ void scalar_gather_sum_kernel(const float* __restrict__ table, const void* __restrict__ ids, int id_bytes,
+                                         int B, int W, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t b = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (b >= B) return;
+    float acc = 0.f;
+    for (int j = lane; j < W; j += 32) acc += ctr_ldg_f1_stream(table + ctr_load_id(ids, id_bytes, b * (int64_t) W + j));
+    acc = ctr_warp_sum(acc);
+    if (lane == 0) out[b] = acc;
+}
+
+int check_cfg(ctr_handle* h, const ctr_embed_cfg* c) {
+    CTR_REQUIRE(h, c != nullptr, "embed cfg is null");
+    CTR_REQUIRE(h, c->k == 4 || c->k == 8 || c->k == 16 || c->k == 32, "embedding_size %d unsupported (4/8/16/32)", c->k);
+    CTR_REQUIRE(h, c->id_bytes == 4 || c->id_bytes == 8, "id_bytes must be 4 or 8");
+    CTR_REQUIRE(h, c->B >= 0 && c->Fc >= 0 && c->Fm >= 0 && c->C >= 0 && c->V >= 0 && c->M >= 0, "negative sizes");
+    CTR_REQUIRE(h, c->ids_ld >= c->Fc + c->M, "ids_ld < Fc + M");
+    CTR_REQUIRE(h, c->table_stride >= c->k + (c->has_first ? 1 : 0) && c->table_stride % 4 == 0,
+                "table_stride %d too small / not a multiple of 4", c->table_stride);
+    CTR_REQUIRE(h, c->x0_ld % 4 == 0 && c->x0_ld >= (c->Fc + c->Fm) * c->k + c->C + c->V, "x0_ld %d invalid", c->x0_ld);
+    CTR_REQUIRE(h, !c->use_fm || c->fm_ld >= c->Fc + c->Fm + c->C + c->k, "fm_ld too small");
+    return CTR_OK;
+}
+
+}  // namespace
+
+int ctr_check_embed_cfg(ctr_handle* h, const ctr_embed_cfg* c) { return check_cfg(h, c); }
+
+extern "C" int ctr_fm_gather_fwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const float* table,
+                                 const void* ids, int64_t id_offset, const float* cont, const float* vec,
+                                 const float* cont_rows, const float* pooled_first, float* x0, float* fm,
+                                 float* sum_e) {
+    int rc = check_cfg(h, cfg);
+    if (rc) return rc;
+    CTR_REQUIRE(h, x0 && (cfg->Fc == 0 || (table && ids)), "fm_gather_fwd: null table/ids/x0");
+    CTR_REQUIRE(h, cfg->C == 0 || cont, "fm_gather_fwd: cont is null");
+    CTR_REQUIRE(h, cfg->V == 0 || vec, "fm_gather_fwd: vec is null");
+    CTR_REQUIRE(h, !cfg->use_fm || (fm && sum_e), "fm_gather_fwd: fm/sum_e null with use_fm");
+    CTR_REQUIRE(h, !(cfg->use_fm && cfg->fm_cont && cfg->C > 0) || cont_rows, "fm_gather_fwd: cont_rows null");
+    if (cfg->B == 0) return CTR_OK;
+    const unsigned blocks = (unsigned) ctr_cdiv((int64_t) cfg->B * 32, 256);
+#define LAUNCH_K1(KK)                                                                                              \
+    if (cfg->use_fm)                                                                                               \
+        fm_gather_fwd_kernel<KK, true><<<blocks, 256, 0, ctr_st(s)>>>(*cfg, table, ids, id_offset, cont, vec,      \
+                                                                      cont_rows, pooled_first, x0, fm, sum_e);     \
+    else                                                                                                           \
+        fm_gather_fwd_kernel<KK, false><<<blocks, 256, 0, ctr_st(s)>>>(*cfg, table, ids, id_offset, cont, vec,     \
+                                                                       cont_rows, pooled_first, x0, fm, sum_e)
+    switch (cfg->k) {
+        case 4: LAUNCH_K1(4); break;
+        case 8: LAUNCH_K1(8); break;
+        case 16: LAUNCH_K1(16); break;
+        default: LAUNCH_K1(32); break;
+    }
+#undef LAUNCH_K1
+    CTR_CHECK_LAUNCH(h, "fm_gather_fwd");
+    return CTR_OK;
+}
+
+extern "C" int ctr_pooled_gather_fwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const float* table,
+                                     const void* ids, const int32_t* multi_start, const float* slot_weight, float* x0,
+                                     float* pooled_first, float* inv_cnt_emb, float* inv_cnt_first) {
+    int rc = check_cfg(h, cfg);
+    if (rc) return rc;
+    if (cfg->Fm == 0 || cfg->B == 0) return CTR_OK;
+    CTR_REQUIRE(h, table && ids && multi_start && x0 && pooled_first && inv_cnt_emb && inv_cnt_first,
+                "pooled_gather_fwd: null pointer");
+    const int64_t items = (int64_t) cfg->B * cfg->Fm;
+    const unsigned blocks = (unsigned) ctr_cdiv(items * 32, 256);
+#define LAUNCH_K2(KK)                                                                                            \
+    pooled_gather_fwd_kernel<KK><<<blocks, 256, 0, ctr_st(s)>>>(*cfg, table, ids, multi_start, slot_weight, x0,  \
+                                                               pooled_first, inv_cnt_emb, inv_cnt_first)
+    switch (cfg->k) {
+        case 4: LAUNCH_K2(4); break;
+        case 8: LAUNCH_K2(8); break;
+        case 16: LAUNCH_K2(16); break;
+        default: LAUNCH_K2(32); break;
+    }
+#undef LAUNCH_K2
+    CTR_CHECK_LAUNCH(h, "pooled_gather_fwd");
+    return CTR_OK;
+}
+
+extern "C" int ctr_scalar_gather_sum(ctr_handle* h, ctr_stream s, const float* table, const void* ids, int id_bytes,
+                                     int B, int W, float* out) {
+    CTR_REQUIRE(h, table && ids && out && (id_bytes == 4 || id_bytes == 8) && B >= 0 && W >= 0,
+                "scalar_gather_sum: bad args");
+    if (B == 0) return CTR_OK;
+    scalar_gather_sum_kernel<<<(unsigned) ctr_cdiv((int64_t) B * 32, 256), 256, 0, ctr_st(s)>>>(table, ids, id_bytes, B,
+                                                                                               W, out);
+    CTR_CHECK_LAUNCH(h, "scalar_gather_sum");
+    return CTR_OK;
+}

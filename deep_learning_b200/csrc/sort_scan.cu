@@ -1,0 +1,387 @@
+// Stable LSD radix sort (8-bit digits), flag scans and run-length structure of sorted keys.
+// These are the integer half of K4 (the deterministic replacement of TF's unique +
+// unsorted_segment_sum) and of the AUC; all results are bit-exact and order-deterministic.
+#include "ctr_common.cuh"
+
+namespace {
+
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;                           // keys per thread
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;     // 4096 keys per block
+constexpr int SORT_WARPS = SORT_THREADS / 32;
+constexpr int WARP_SPAN = SORT_TILE / SORT_WARPS;        // 512 consecutive keys per warp
+static_assert(SORT_THREADS == RADIX, "one thread per digit is assumed");
+
+// ---- pass 1: per-block digit histogram, stored digit-major hist[d * nblk + blk] ---------------
+__global__ void __launch_bounds__(SORT_THREADS)
+radix_hist_kernel(const uint32_t* __restrict__ keys, int64_t n, int shift, uint32_t* __restrict__ hist, int nblk) {
+    __shared__ uint32_t sh[RADIX];
+    for (int i = threadIdx.x; i < RADIX; i += SORT_THREADS) sh[i] = 0;
+    __syncthreads();
+    int64_t base = (int64_t) blockIdx.x * SORT_TILE;
+#pragma unroll 4
+    for (int it = 0; it < SORT_ITEMS; ++it) {
+        int64_t i = base + it * SORT_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&sh[(keys[i] >> shift) & (RADIX - 1)], 1u);
+    }
+    __syncthreads();
+    for (int d = threadIdx.x; d < RADIX; d += SORT_THREADS) hist[(int64_t) d * nblk + blockIdx.x] = sh[d];
+}
+
+// block-wide exclusive scan of one value per thread (blockDim.x == 1024 or 256); returns exclusive
+// prefix, *total gets the block total.  smem: 33 uint32
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* sm, uint32_t* total) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) sm[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        int nw = blockDim.x >> 5;
+        uint32_t x = lane < nw ? sm[lane] : 0u;
+        uint32_t xi = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, xi, o);
+            if (lane >= o) xi += t;
+        }
+        sm[lane] = xi - x;               // exclusive warp offsets
+        if (lane == 31) sm[32] = xi;     // block total
+    }
+    __syncthreads();
+    uint32_t res = sm[w] + inc - v;
+    *total = sm[32];
+    __syncthreads();
+    return res;
+}
+
+// ---- pass 2: one block per digit scans its row of per-block counts; row totals to tot[d] --------
+__global__ void __launch_bounds__(1024)
+radix_scan_rows_kernel(uint32_t* __restrict__ hist, int nblk, uint32_t* __restrict__ tot) {
+    __shared__ uint32_t sm[33];
+    uint32_t* row = hist + (int64_t) blockIdx.x * nblk;
+    uint32_t carry = 0;
+    for (int i0 = 0; i0 < nblk; i0 += 1024) {
+        int i = i0 + threadIdx.x;
+        uint32_t v = i < nblk ? row[i] : 0u;
+        uint32_t total;
+        uint32_t ex = block_excl_scan(v, sm, &total);
+        if (i < nblk) row[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) tot[blockIdx.x] = carry;
+}
+
+// ---- pass 3: stable scatter ------------------------------------------------------------------
+// Warp w owns keys [w*512, (w+1)*512) of the tile and walks them in 16 rounds of 32 consecutive keys;
+// __match_any_sync ranks equal digits inside a round in lane (= index) order, a per-warp counter
+// table carries ranks across rounds, and a cross-warp exclusive sum finishes the tile-local rank.
+__global__ void __launch_bounds__(SORT_THREADS)
+radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                     uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift,
+                     const uint32_t* __restrict__ hist, const uint32_t* __restrict__ tot, int nblk) {
+    __shared__ uint32_t wcnt[SORT_WARPS][RADIX];   // per-warp digit counts -> per-warp bases
+    __shared__ uint32_t dbase[RADIX];              // global base of each digit for this block
+    __shared__ uint32_t sm[33];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&wcnt[0][0])[i] = 0;
+    // digit bases: exclusive scan of the 256 row totals + this block's offset inside the row
+    {
+        uint32_t t = tot[threadIdx.x];
+        uint32_t total;
+        uint32_t ex = block_excl_scan(t, sm, &total);   // includes the __syncthreads for wcnt zeroing
+        dbase[threadIdx.x] = ex + hist[(int64_t) threadIdx.x * nblk + blockIdx.x];
+    }
+    __syncthreads();
+
+    const int64_t wbase = (int64_t) blockIdx.x * SORT_TILE + (int64_t) w * WARP_SPAN;
+    uint32_t key[SORT_ITEMS];
+    uint32_t off[SORT_ITEMS];   // rank among equal digits inside this warp's span
+#pragma unroll
+    for (int it = 0; it < SORT_ITEMS; ++it) {
+        int64_t i = wbase + it * 32 + lane;
+        key[it] = i < n ? keys_in[i] : 0xFFFFFFFFu;
+    }
+#pragma unroll
+    for (int it = 0; it < SORT_ITEMS; ++it) {
+        int64_t i = wbase + it * 32 + lane;
+        bool valid = i < n;
+        uint32_t d = (key[it] >> shift) & (RADIX - 1);
+        // invalid lanes use a digit slot of their own (RADIX-1 of PAD keys still must not mix):
+        // match on (valid, d) so padding lanes never rank against real keys
+        uint32_t mkey = valid ? d : (RADIX + (uint32_t) lane);
+        uint32_t peers = __match_any_sync(0xffffffffu, mkey);
+        uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+        int leader = __ffs(peers) - 1;
+        uint32_t old = 0;
+        if (valid && lane == leader) {
+            old = wcnt[w][d];
+            wcnt[w][d] = old + __popc(peers);
+        }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        off[it] = old + rank;
+        __syncwarp();
+    }
+    __syncthreads();
+    // cross-warp exclusive sum per digit (thread d handles digit d)
+    {
+        uint32_t run = 0;
+        int d = threadIdx.x;
+#pragma unroll
+        for (int ww = 0; ww < SORT_WARPS; ++ww) {
+            uint32_t c = wcnt[ww][d];
+            wcnt[ww][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < SORT_ITEMS; ++it) {
+        int64_t i = wbase + it * 32 + lane;
+        if (i < n) {
+            uint32_t d = (key[it] >> shift) & (RADIX - 1);
+            uint32_t pos = dbase[d] + wcnt[w][d] + off[it];
+            keys_out[pos] = key[it];
+            vals_out[pos] = vals_in[i];
+        }
+    }
+}
+
+__global__ void copy_pairs_kernel(const uint32_t* __restrict__ ka, const uint32_t* __restrict__ va,
+                                  uint32_t* __restrict__ kb, uint32_t* __restrict__ vb, int64_t n) {
+    int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        kb[i] = ka[i];
+        vb[i] = va[i];
+    }
+}
+
+__global__ void build_keys_kernel(const void* __restrict__ ids, int id_bytes, int64_t rows, int64_t ld, int col0,
+                                  int ncols, int64_t id_offset, int drop_zero, int n_shards, int local_bits,
+                                  uint32_t* __restrict__ keys, uint32_t* __restrict__ perm) {
+    int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    int64_t n = rows * ncols;
+    if (i >= n) return;
+    int64_t r = i / ncols;
+    int c = (int) (i - r * ncols);
+    int64_t p = r * ld + col0 + c;
+    int64_t id = ctr_load_id(ids, id_bytes, p) + id_offset;
+    uint32_t key;
+    if (drop_zero && id == 0) key = CTR_PAD_KEY;
+    else if (n_shards > 1) key = ((uint32_t) (id % n_shards) << local_bits) | (uint32_t) (id / n_shards);
+    else key = (uint32_t) id;
+    keys[i] = key;
+    perm[i] = (uint32_t) p;
+}
+
+// ---- generic 3-phase flag scan ------------------------------------------------------------------
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;   // 2048
+
+struct HeadFlag {   // 1 where a new run of equal keys starts
+    const uint32_t* keys;
+    __device__ __forceinline__ uint32_t operator()(int64_t i) const { return (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u; }
+};
+struct PosLabel {   // 1 where the label of the i-th sorted element is positive
+    const float* labels;
+    const uint32_t* perm;
+    __device__ __forceinline__ uint32_t operator()(int64_t i) const { return labels[perm[i]] > 0.5f ? 1u : 0u; }
+};
+
+template <class F>
+__global__ void __launch_bounds__(SCAN_THREADS) scan_phase1(F f, int64_t n, uint32_t* __restrict__ blk) {
+    __shared__ uint32_t sm[33];
+    int64_t base = (int64_t) blockIdx.x * SCAN_TILE + (int64_t) threadIdx.x * SCAN_ITEMS;
+    uint32_t c = 0;
+#pragma unroll
+    for (int it = 0; it < SCAN_ITEMS; ++it)
+        if (base + it < n) c += f(base + it);
+    uint32_t total;
+    block_excl_scan(c, sm, &total);
+    if (threadIdx.x == 0) blk[blockIdx.x] = total;
+}
+
+// single block: exclusive scan of blk[0..nblk) in place, grand total to *total_out (and blk[nblk])
+__global__ void __launch_bounds__(1024) scan_phase2(uint32_t* __restrict__ blk, int nblk, uint32_t* __restrict__ total_out) {
+    __shared__ uint32_t sm[33];
+    uint32_t carry = 0;
+    for (int i0 = 0; i0 < nblk; i0 += 1024) {
+        int i = i0 + threadIdx.x;
+        uint32_t v = i < nblk ? blk[i] : 0u;
+        uint32_t total;
+        uint32_t ex = block_excl_scan(v, sm, &total);
+        if (i < nblk) blk[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) {
+        blk[nblk] = carry;
+        if (total_out) *total_out = carry;
+    }
+}
+
+struct UniqueOut {
+    const uint32_t* keys;
+    uint32_t* uniq;
+    uint32_t* seg_start;
+    uint32_t* uidx;
+    __device__ __forceinline__ void operator()(int64_t i, uint32_t incl, uint32_t flag) const {
+        uint32_t u = incl - 1u;
+        uidx[i] = u;
+        if (flag) {
+            uniq[u] = keys[i];
+            seg_start[u] = (uint32_t) i;
+        }
+    }
+};
+struct ExclOut {   // out[i] = exclusive prefix
+    uint32_t* out;
+    __device__ __forceinline__ void operator()(int64_t i, uint32_t incl, uint32_t flag) const { out[i] = incl - flag; }
+};
+
+template <class F, class O>
+__global__ void __launch_bounds__(SCAN_THREADS) scan_phase3(F f, int64_t n, const uint32_t* __restrict__ blk, O out) {
+    __shared__ uint32_t sm[33];
+    int64_t base = (int64_t) blockIdx.x * SCAN_TILE + (int64_t) threadIdx.x * SCAN_ITEMS;
+    uint32_t fl[SCAN_ITEMS];
+    uint32_t c = 0;
+#pragma unroll
+    for (int it = 0; it < SCAN_ITEMS; ++it) {
+        fl[it] = (base + it < n) ? f(base + it) : 0u;
+        c += fl[it];
+    }
+    uint32_t total;
+    uint32_t run = block_excl_scan(c, sm, &total) + blk[blockIdx.x];
+#pragma unroll
+    for (int it = 0; it < SCAN_ITEMS; ++it) {
+        if (base + it < n) {
+            run += fl[it];
+            out(base + it, run, fl[it]);
+        }
+    }
+}
+
+__global__ void seg_tail_kernel(const uint32_t* __restrict__ n_unique, uint32_t* __restrict__ seg_start, uint32_t n) {
+    seg_start[*n_unique] = n;
+}
+
+__global__ void shard_counts_kernel(const uint32_t* __restrict__ uniq, const uint32_t* __restrict__ n_unique,
+                                    int n_shards, int local_bits, uint32_t* __restrict__ counts) {
+    int o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (o >= n_shards) return;
+    uint32_t U = *n_unique;
+    auto lower = [&](uint32_t key) {
+        uint32_t lo = 0, hi = U;
+        while (lo < hi) {
+            uint32_t mid = (lo + hi) >> 1;
+            if (uniq[mid] < key) lo = mid + 1; else hi = mid;
+        }
+        return lo;
+    };
+    uint32_t a = lower((uint32_t) o << local_bits);
+    uint32_t b = (o + 1 < n_shards) ? lower((uint32_t) (o + 1) << local_bits) : lower(CTR_PAD_KEY);
+    counts[o] = b - a;
+}
+
+inline int sort_nblk(int64_t n) { return (int) ctr_cdiv(n > 0 ? n : 1, SORT_TILE); }
+
+}  // namespace
+
+extern "C" int64_t ctr_sort_ws_bytes(ctr_handle*, int64_t n) {
+    int64_t nb = sort_nblk(n);
+    return ctr_align(n * 4, 256) * 2 + ctr_align((int64_t) RADIX * nb * 4, 256) + RADIX * 4 + 256;
+}
+
+extern "C" int ctr_sort_pairs(ctr_handle* h, ctr_stream s, uint32_t* keys, uint32_t* vals, int64_t n, int key_bits,
+                              void* ws, int64_t ws_bytes) {
+    CTR_REQUIRE(h, keys && vals && ws && n >= 0 && key_bits >= 1 && key_bits <= 32, "sort_pairs: bad args");
+    CTR_REQUIRE(h, n < (int64_t) 1 << 31, "sort_pairs: n too large");
+    if (n == 0) return CTR_OK;
+    if (ws_bytes < ctr_sort_ws_bytes(h, n)) return ctr_fail(h, CTR_E_WORKSPACE, "sort_pairs: ws too small");
+    const int nblk = sort_nblk(n);
+    char* p = (char*) ws;
+    uint32_t* k2 = (uint32_t*) p; p += ctr_align(n * 4, 256);
+    uint32_t* v2 = (uint32_t*) p; p += ctr_align(n * 4, 256);
+    uint32_t* hist = (uint32_t*) p; p += ctr_align((int64_t) RADIX * nblk * 4, 256);
+    uint32_t* tot = (uint32_t*) p;
+    const int passes = (key_bits + RADIX_BITS - 1) / RADIX_BITS;
+    uint32_t *ka = keys, *va = vals, *kb = k2, *vb = v2;
+    cudaStream_t st = ctr_st(s);
+    for (int pass = 0; pass < passes; ++pass) {
+        int shift = pass * RADIX_BITS;
+        radix_hist_kernel<<<nblk, SORT_THREADS, 0, st>>>(ka, n, shift, hist, nblk);
+        radix_scan_rows_kernel<<<RADIX, 1024, 0, st>>>(hist, nblk, tot);
+        radix_scatter_kernel<<<nblk, SORT_THREADS, 0, st>>>(ka, va, kb, vb, n, shift, hist, tot, nblk);
+        uint32_t* t;
+        t = ka; ka = kb; kb = t;
+        t = va; va = vb; vb = t;
+    }
+    if (ka != keys) copy_pairs_kernel<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>(ka, va, keys, vals, n);
+    CTR_CHECK_LAUNCH(h, "sort_pairs");
+    return CTR_OK;
+}
+
+extern "C" int ctr_sort_ids(ctr_handle* h, ctr_stream s, const void* ids, int id_bytes, int64_t rows, int64_t ld,
+                            int col0, int ncols, int64_t id_offset, int drop_zero, int n_shards, int local_bits,
+                            int key_bits, uint32_t* keys_out, uint32_t* perm_out, void* ws, int64_t ws_bytes) {
+    CTR_REQUIRE(h, ids && keys_out && perm_out && (id_bytes == 4 || id_bytes == 8), "sort_ids: bad pointers");
+    CTR_REQUIRE(h, rows >= 0 && ncols >= 0 && col0 >= 0 && col0 + ncols <= ld, "sort_ids: bad shape");
+    CTR_REQUIRE(h, n_shards >= 1 && (n_shards == 1 || (local_bits > 0 && local_bits < 31)), "sort_ids: bad sharding");
+    CTR_REQUIRE(h, rows * ld < ((int64_t) 1 << 32), "sort_ids: flat positions exceed 32 bits");
+    int64_t n = rows * ncols;
+    if (n == 0) return CTR_OK;
+    build_keys_kernel<<<(unsigned) ctr_cdiv(n, 256), 256, 0, ctr_st(s)>>>(ids, id_bytes, rows, ld, col0, ncols, id_offset,
+                                                                         drop_zero, n_shards, local_bits, keys_out,
+                                                                         perm_out);
+    CTR_CHECK_LAUNCH(h, "build_keys");
+    return ctr_sort_pairs(h, s, keys_out, perm_out, n, drop_zero ? 32 : key_bits, ws, ws_bytes);
+}
+
+extern "C" int ctr_unique_segments(ctr_handle* h, ctr_stream s, const uint32_t* sorted_keys, int64_t n, uint32_t* uniq,
+                                   uint32_t* seg_start, uint32_t* uidx, uint32_t* n_unique, void* ws, int64_t ws_bytes) {
+    CTR_REQUIRE(h, sorted_keys && uniq && seg_start && uidx && n_unique && ws && n >= 0, "unique_segments: bad args");
+    cudaStream_t st = ctr_st(s);
+    if (n == 0) {
+        CTR_CUDA(h, cudaMemsetAsync(n_unique, 0, 4, st));
+        CTR_CUDA(h, cudaMemsetAsync(seg_start, 0, 4, st));
+        return CTR_OK;
+    }
+    int nblk = (int) ctr_cdiv(n, SCAN_TILE);
+    if (ws_bytes < (int64_t) (nblk + 2) * 4) return ctr_fail(h, CTR_E_WORKSPACE, "unique_segments: ws too small");
+    uint32_t* blk = (uint32_t*) ws;
+    HeadFlag f{sorted_keys};
+    scan_phase1<HeadFlag><<<nblk, SCAN_THREADS, 0, st>>>(f, n, blk);
+    scan_phase2<<<1, 1024, 0, st>>>(blk, nblk, n_unique);
+    scan_phase3<HeadFlag, UniqueOut><<<nblk, SCAN_THREADS, 0, st>>>(f, n, blk, UniqueOut{sorted_keys, uniq, seg_start, uidx});
+    seg_tail_kernel<<<1, 1, 0, st>>>(n_unique, seg_start, (uint32_t) n);
+    CTR_CHECK_LAUNCH(h, "unique_segments");
+    return CTR_OK;
+}
+
+extern "C" int ctr_shard_counts(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const uint32_t* n_unique,
+                                int n_shards, int local_bits, uint32_t* counts) {
+    CTR_REQUIRE(h, uniq && n_unique && counts && n_shards >= 1 && local_bits > 0 && local_bits < 32,
+                "shard_counts: bad args");
+    shard_counts_kernel<<<(unsigned) ctr_cdiv(n_shards, 64), 64, 0, ctr_st(s)>>>(uniq, n_unique, n_shards, local_bits,
+                                                                                 counts);
+    CTR_CHECK_LAUNCH(h, "shard_counts");
+    return CTR_OK;
+}
+
+// exclusive prefix count of positive labels in sorted order (used by ctr_auc): out[i], out[n] = total
+int ctr_scan_pos_labels(ctr_handle* h, cudaStream_t st, const float* labels, const uint32_t* perm, int64_t n,
+                        uint32_t* out, uint32_t* blk_ws) {
+    int nblk = (int) ctr_cdiv(n, SCAN_TILE);
+    PosLabel f{labels, perm};
+    scan_phase1<PosLabel><<<nblk, SCAN_THREADS, 0, st>>>(f, n, blk_ws);
+    scan_phase2<<<1, 1024, 0, st>>>(blk_ws, nblk, out + n);
+    scan_phase3<PosLabel, ExclOut><<<nblk, SCAN_THREADS, 0, st>>>(f, n, blk_ws, ExclOut{out});
+    CTR_CHECK_LAUNCH(h, "scan_pos_labels");
+    return CTR_OK;
+}

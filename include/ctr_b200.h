@@ -1,0 +1,265 @@
+/*
+ * ctr_b200.h -- C-ABI of libctr_b200.so: the B200 (sm_100a) train/predict hot path of the
+ * RodJohn/deep_learning CTR zoo (DeepFM / Wide&Deep / DNN).
+ *
+ * The reference has NO native/FFI interface: every op on its hot path is a TensorFlow-1.x
+ * Python op call inside models/<alg>.py.  Each entry point below therefore cites the reference
+ * GRAPH LINES it replaces (paths relative to the reference root).  A maintainer binds this
+ * library from the model modules with ctypes.
+ *
+ * Conventions
+ *   - plain C, extern "C"; pointers are DEVICE pointers unless named host_*; sizes are explicit.
+ *   - the caller owns every buffer, workspaces included; the library owns only the handle.
+ *   - every call takes a cudaStream_t (passed as void*), enqueues and returns: no hidden
+ *     synchronisation, no allocation, CUDA-graph capturable.
+ *   - return 0 on success; negative = CTR_E_*; ctr_last_error(h) gives the message.  Never aborts.
+ *   - one handle per device; a handle is not thread-safe.
+ *   - there is NO CPU fallback anywhere.
+ *
+ * Layouts (floats unless noted)
+ *   table row   : [ v_0 .. v_{k-1} | w | pad ]  `table_stride` floats, 32-byte multiple.  `w` (the
+ *                 FM first-order weight of the same id, reference tables feats / fm_first_order_emb)
+ *                 is present iff has_first.  Adam slots m, v use the same layout.
+ *   X0 [B,x0_ld]: deep-tower input, canonical order [ single emb Fc*k | pooled emb Fm*k | cont C |
+ *                 vector V | 0-pad ].  (The reference order is [cont|vector|emb]; the host permutes
+ *                 the rows of deep_0 once at injection time.)
+ *   fm  [B,fm_ld]: [ first single Fc | first multi Fm | first cont C | second k ].
+ *   grad row    : [ g_v0 .. g_v{k-1} | g_w | pad ]  `grad_stride` floats.
+ */
+#ifndef CTR_B200_H
+#define CTR_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CTR_ABI_VERSION 1
+
+#define CTR_OK              0
+#define CTR_E_INVALID      -1   /* bad argument / unsupported shape */
+#define CTR_E_CUDA         -2   /* CUDA runtime or launch error */
+#define CTR_E_WORKSPACE    -3   /* workspace too small */
+#define CTR_E_UNSUPPORTED  -4   /* feature not built (e.g. wrong arch) */
+
+typedef struct ctr_handle ctr_handle;
+typedef void* ctr_stream;        /* cudaStream_t */
+
+/* shape/layout of the embedding side of one model; shared by forward and backward.
+ * Mirrors the placeholders of DeepModel.__init__graph (models/deepfm.py:39-54,
+ * models/deepfm_multi.py:46-79) plus the layouts above. */
+typedef struct ctr_embed_cfg {
+    int32_t B;             /* samples in this batch (input_data_size) */
+    int32_t id_bytes;      /* 4 (models/deepfm.py:44 int32) or 8 (utils/data_loader.py:13 int64) */
+    int32_t ids_ld;        /* columns of cate_feats = Fc + M */
+    int32_t Fc;            /* single-valued categorical fields (cate_field_size) */
+    int32_t Fm;            /* multi-valued fields (multi_field_size) */
+    int32_t M;             /* total padded multi slots (multi_feats_size) */
+    int32_t C;             /* continuous fields (cont_field_size) */
+    int32_t V;             /* vector_feats width */
+    int32_t k;             /* embedding_size: 4, 8, 16 or 32 */
+    int32_t has_first;     /* rows carry the FM first-order weight at [k] */
+    int32_t use_fm;        /* compute FM first/second order (DeepFM) */
+    int32_t fm_cont;       /* continuous fields own table rows in the FM part (models/deepfm.py:63-75) */
+    int32_t zero_row0;     /* id 0 reads as zeros and gets no gradient (models/deepfm_multi.py:130-133) */
+    int32_t count_rule;    /* multi-valued mean: 0 = count rows whose sum != 0 (reference,
+                              models/deepfm_multi.py:83-88), 1 = count ids != 0 */
+    int32_t combiner;      /* 0 mean, 1 sum */
+    int32_t table_stride;  /* floats per table row */
+    int32_t x0_ld;         /* floats per X0 row (multiple of 4) */
+    int32_t fm_ld;         /* floats per fm row */
+    int32_t grad_stride;   /* floats per gradient row (multiple of 4, >= k + has_first) */
+    int32_t reserved;
+} ctr_embed_cfg;
+
+/* ---- handle ------------------------------------------------------------------------- */
+int  ctr_abi_version(void);
+int  ctr_sizeof_embed_cfg(void);
+int  ctr_create(int device, ctr_handle** out);
+int  ctr_destroy(ctr_handle* h);
+const char* ctr_last_error(ctr_handle* h);
+int  ctr_sm_count(ctr_handle* h);
+/* 1 if the tcgen05/TMA TF32 GEMM path can run on this device (sm_100) */
+int  ctr_has_tcgen05(ctr_handle* h);
+
+/* ---- table packing (host-side parameter injection / read-back) ------------------------
+ * reference variables feats_emb [R,k] + feats [R,1] (models/deepfm.py:57-60) <-> packed rows */
+int ctr_table_pack(ctr_handle* h, ctr_stream s, const float* emb /*[R,k]*/, const float* first /*[R] or NULL*/,
+                   int64_t R, int k, int table_stride, float* table);
+int ctr_table_unpack(ctr_handle* h, ctr_stream s, const float* table, int64_t R, int k, int table_stride,
+                     float* emb /*[R,k]*/, float* first /*[R] or NULL*/);
+
+/* ---- K2: multi-valued pooled gather ----------------------------------------------------
+ * replaces multi_cate_emb()/nonzero_reduce_mean (models/deepfm_multi.py:81-121,
+ * models/dnn_multi.py:83-104).  For every (sample, multi field j) pools the rows of slots
+ * [multi_start[j], multi_start[j+1]) of the multi block of `ids`; writes the pooled vector into
+ * X0[b, (Fc+j)*k ..], the pooled first-order weight into pooled_first[b,j] and the two divisors
+ * (1/count, 0 when count==0) into inv_cnt_emb / inv_cnt_first [B,Fm].  `slot_weight` ([B,M] or
+ * NULL) is the weighted form of models/dnn_multi_textline.py:94-103. */
+int ctr_pooled_gather_fwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg,
+                          const float* table, const void* ids, const int32_t* multi_start /*[Fm+1]*/,
+                          const float* slot_weight, float* x0, float* pooled_first,
+                          float* inv_cnt_emb, float* inv_cnt_first);
+
+/* ---- K1: fused field-wise gather + FM first/second order + deep-input tile --------------
+ * replaces models/deepfm.py:63-100 (index/value assembly, both embedding_lookups on feats_emb,
+ * the lookup on feats, the FM reductions and the dense_vector concat) and the same lines of
+ * models/deepfm_multi.py:137-190, models/wdl.py:132-179, models/dnn.py:54-57.
+ * Each table row is read from HBM once.  `cont_rows` points at the C table rows of the
+ * continuous fields (table + cont_base*stride on one GPU).  Outputs: X0 (single-emb block + cont +
+ * vector columns; pooled block must already be there when Fm>0), fm [B,fm_ld] and
+ * sum_e [B,k] (= sum over FM fields of e; kept for backward) when use_fm. */
+int ctr_fm_gather_fwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg,
+                      const float* table, const void* ids, int64_t id_offset,
+                      const float* cont, const float* vec, const float* cont_rows,
+                      const float* pooled_first,
+                      float* x0, float* fm, float* sum_e);
+
+/* scalar-table gather-sum: out[b] = sum_j table[ids[b,j]]   (wide part, models/wdl.py:240-246) */
+int ctr_scalar_gather_sum(ctr_handle* h, ctr_stream s, const float* table, const void* ids, int id_bytes,
+                          int B, int W, float* out);
+
+/* ---- K3: MLP tower ---------------------------------------------------------------------
+ * replaces the matmul/add/relu/dropout loop (models/deepfm.py:121-126) and what
+ * AdamOptimizer.minimize differentiates through it (models/deepfm.py:161).
+ * precision: 0 = FP32 SIMT (tight 1e-5 checks), 1 = TF32 tcgen05/TMA (2e-3).
+ * W is the reference layout [K, N] row-major (ldw = N). */
+#define CTR_PREC_FP32 0
+#define CTR_PREC_TF32 1
+/* Y[B,N] = dropout(relu(X[B,K] @ W[K,N] + bias[N])); relu/bias optional; keep==1 -> no dropout */
+int ctr_mlp_fwd(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
+                const float* X, int64_t ldx, const float* W, const float* Wt /*[N,K] or NULL*/,
+                const float* bias, int relu, float keep, uint64_t seed, float* Y, int64_t ldy);
+/* dX[B,K] = (dZ[B,N] @ W^T) * (mask[B,K] > 0 ? mask_scale : 0)   (mask = the layer's input
+ * activation, NULL for the tower input) */
+int ctr_mlp_bwd_data(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
+                     const float* dZ, int64_t lddz, const float* W,
+                     const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx);
+/* dW[K,N] = X^T @ dZ ; dbias[N] = colsum(dZ).  ws: ctr_mlp_bwd_weight_ws_bytes() */
+int64_t ctr_mlp_bwd_weight_ws_bytes(ctr_handle* h, int precision, int B, int K, int N);
+int ctr_mlp_bwd_weight(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
+                       const float* X, int64_t ldx, const float* dZ, int64_t lddz,
+                       float* dW, float* dbias, void* ws, int64_t ws_bytes);
+/* out[N,K] = in[K,N]^T (keeps the K-major copy the tcgen05 path reads) */
+int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, float* out);
+
+/* ---- K5: head + sigmoid log-loss --------------------------------------------------------
+ * replaces concat + matmul + sigmoid (models/deepfm.py:128-145; models/dnn.py:82-84; the deep half
+ * of models/wdl.py:240-247) and tf.losses.log_loss (models/deepfm.py:151-152, eps = 1e-7).
+ *   logit[b] = fm[b,:n_fm].w_fm + deep[b,:H].w_deep + (extra ? extra[b] : 0) + bias[0]
+ *   score    = sigmoid(logit)
+ *   loss     = mean_b( -y log(score+eps) - (1-y) log(1-score+eps) )        (label != NULL)
+ *   dlogit[b]= dloss/dlogit[b]                                              (label != NULL)
+ * loss_out: one float, written by a second deterministic reduction pass. ws >= 4*(ceil(B/256)+1) B */
+int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B,
+                 const float* fm, int64_t fm_ld, int n_fm, const float* w_fm,
+                 const float* deep, int64_t deep_ld, int H, const float* w_deep,
+                 const float* extra, const float* bias,
+                 const float* label, float* logit, float* score, float* dlogit, float* loss_out,
+                 void* ws, int64_t ws_bytes);
+/* dZ_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)        (through the last ReLU) */
+int ctr_head_bwd_deep(ctr_handle* h, ctr_stream s, int B, int H, const float* dlogit, const float* w_deep,
+                      const float* deep, int64_t deep_ld, float* dZ, int64_t lddz);
+/* out[j] = sum_b (w ? w[b] : 1) * X[b,j]  for j < ncols; deterministic two-pass column reduction
+ * (head-weight and bias gradients).  ws: ctr_colsum_ws_bytes() */
+int64_t ctr_colsum_ws_bytes(ctr_handle* h, int B, int ncols);
+int ctr_colsum(ctr_handle* h, ctr_stream s, const float* X, int64_t ldx, int B, int ncols,
+               const float* w, float* out, void* ws, int64_t ws_bytes);
+/* out[0] = sum_i f(x[i]);  mode 0: x, 1: x^2, 2: |x|   (regulariser terms, models/deepfm.py:155-156,
+ * models/dnn.py:90).  ws >= 4*1024 B */
+int ctr_reduce(ctr_handle* h, ctr_stream s, const float* x, int64_t n, int mode, float* out,
+               void* ws, int64_t ws_bytes);
+
+/* ---- K4: sparse backward = sort / segment-reduce / Adam ----------------------------------
+ * replaces the IndexedSlices gradient of tf.nn.embedding_lookup, TF's unique +
+ * unsorted_segment_sum de-duplication and AdamOptimizer._apply_sparse/_apply_dense
+ * (all built by `.minimize`, models/deepfm.py:161).
+ *
+ * ctr_sort_ids: key[i] = shard_key(ids[i] + id_offset) sorted ascending (stable LSD radix sort),
+ *   perm[i] = flat position (b*ids_ld + slot) of the i-th smallest.  With n_shards>1 the key is
+ *   (id % n_shards) << local_bits | (id / n_shards): owner-major, so one sort also buckets by
+ *   owner for the all-to-all.  ids == 0 become key 0xFFFFFFFF when drop_zero (padding: no grad).
+ *   ids are read as a [rows, ld] matrix restricted to columns [col0, col0+ncols). */
+int64_t ctr_sort_ws_bytes(ctr_handle* h, int64_t n);
+int ctr_sort_ids(ctr_handle* h, ctr_stream s, const void* ids, int id_bytes, int64_t rows, int64_t ld,
+                 int col0, int ncols, int64_t id_offset, int drop_zero, int n_shards, int local_bits,
+                 int key_bits, uint32_t* keys_out, uint32_t* perm_out, void* ws, int64_t ws_bytes);
+/* generic stable pair sort (also used by ctr_auc) */
+int ctr_sort_pairs(ctr_handle* h, ctr_stream s, uint32_t* keys, uint32_t* vals, int64_t n, int key_bits,
+                   void* ws, int64_t ws_bytes);
+/* run-length structure of sorted keys: uniq[u], seg_start[u] (seg_start[U] = n), uidx[i] = index of
+ * the run containing i, *n_unique = U (device).  Bit-exact against numpy.unique. ws >= 4*(n/2048+2) B*/
+int ctr_unique_segments(ctr_handle* h, ctr_stream s, const uint32_t* sorted_keys, int64_t n,
+                        uint32_t* uniq, uint32_t* seg_start, uint32_t* uidx, uint32_t* n_unique,
+                        void* ws, int64_t ws_bytes);
+/* counts[o] = number of unique keys owned by shard o (keys >> local_bits == o), o < n_shards;
+ * keys equal to 0xFFFFFFFF (dropped) are not counted. */
+int ctr_shard_counts(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const uint32_t* n_unique,
+                     int n_shards, int local_bits, uint32_t* counts);
+
+/* Per-run partial gradients.  The sorted lookup list is cut into fixed chunks of CTR_BWD_CHUNK
+ * entries; one sub-warp walks a chunk in order and writes the sum of each run it meets to
+ * part[(uidx + chunk) * grad_stride ..] (injective, a row's runs are consecutive).  The gradient of
+ * lookup (b, field) is formed on the fly:
+ *     g_v = scale_e * ( dX0[b, field*k + :] + use_fm * dlogit[b] * w_second * (sum_e[b] - X0[b, field*k + :]) )
+ *     g_w = scale_w * dlogit[b] * w_first[field]
+ * (scale = 1 for single-valued fields, the saved 1/count for multi-valued ones).
+ * part must hold (n + n/CTR_BWD_CHUNK + 2) * grad_stride floats. */
+#define CTR_BWD_CHUNK 32
+int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg,
+                           const uint32_t* sorted_keys, const uint32_t* perm, const uint32_t* uidx, int64_t n,
+                           const int32_t* field_of_slot /*[M] or NULL*/,
+                           const float* x0, const float* dx0, int64_t dx0_ld, const float* sum_e, const float* dlogit,
+                           const float* w_fm /*[Fc+Fm+C+k] internal order*/,
+                           const float* inv_cnt_emb, const float* inv_cnt_first,
+                           float* part);
+/* grads[u, :] = sum of the partials of run u, in chunk order (deterministic) */
+int ctr_embed_bwd_finalize(ctr_handle* h, ctr_stream s, const uint32_t* seg_start, const uint32_t* n_unique,
+                           int64_t n_max, int width, int grad_stride, const float* part, float* grads);
+/* gradient of the C continuous-field rows (models/deepfm.py:63-93 with value = cont):
+ *   g_v[c] = sum_b x * dlogit * w_second * (sum_e - x*theta_c),  g_w[c] = sum_b dlogit * w_first_cont[c] * x
+ * ws: ctr_cont_bwd_ws_bytes() */
+int64_t ctr_cont_bwd_ws_bytes(ctr_handle* h, const ctr_embed_cfg* cfg);
+int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const float* cont,
+                    const float* cont_rows, const float* sum_e, const float* dlogit, const float* w_fm,
+                    float* cont_grad /*[C, grad_stride]*/, void* ws, int64_t ws_bytes);
+
+/* TF1 Adam on the rows named by row_ids (unique):  g = grads[u] (+ extra_grad[row - extra_base] when
+ * the row lies in [extra_base, extra_base+extra_n), which also sets extra_hit[row - extra_base]);
+ *   m <- b1*m + (1-b1) g ; v <- b2*v + (1-b2) g^2 ; theta <- theta - lr_t * m / (sqrt(v) + eps)
+ * rows with id 0xFFFFFFFF are skipped.  `touched` ([R] bytes or NULL) is set to 1 for every updated
+ * row (used by the exact dense sweep).  row = (key & local_mask) when local_bits > 0. */
+typedef struct ctr_adam_hp { float lr_t, beta1, beta2, eps; } ctr_adam_hp;
+int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
+                  int local_bits, const float* grads, const uint32_t* seg_start /* non-NULL: `grads` is the
+                  partials buffer of ctr_embed_bwd_partials and the run sums are formed inline (fused finalize) */,
+                  int grad_stride, int width,
+                  float* table, float* m, float* v, int table_stride, int64_t table_rows,
+                  const float* extra_grad, int64_t extra_base, int extra_n, uint8_t* extra_hit,
+                  uint8_t* touched, const ctr_adam_hp* hp);
+/* dense TF1 Adam over n floats: g_eff = (g ? g[i] : 0) + l2*theta + l1*sign(theta).
+ * skip ([n/skip_group] bytes or NULL): elements whose group flag is 1 are left alone and the flag is
+ * cleared (rows already updated by ctr_adam_rows).  This is the exact `tf_dense` mode: TF1 Adam
+ * decays m,v and moves EVERY row each step. */
+int ctr_adam_dense(ctr_handle* h, ctr_stream s, float* theta, float* m, float* v, const float* g, int64_t n,
+                   float l2, float l1, uint8_t* skip, int skip_group, const ctr_adam_hp* hp);
+
+/* ---- AUC -------------------------------------------------------------------------------
+ * replaces sklearn.metrics.roc_auc_score(labels, scores) (models/deepfm.py:231,253): exact
+ * tie-aware rank statistic in integers; *auc_out is a device double (NaN if one class only). */
+int64_t ctr_auc_ws_bytes(ctr_handle* h, int64_t n);
+int ctr_auc(ctr_handle* h, ctr_stream s, const float* scores, const float* labels, int64_t n,
+            double* auc_out, void* ws, int64_t ws_bytes);
+
+/* ---- small utilities ---------------------------------------------------------------------*/
+/* dst[i, :width] = src[idx[i], :width] (row gather, e.g. owner-side rows for the all-to-all) */
+int ctr_gather_rows(ctr_handle* h, ctr_stream s, const float* src, int src_stride, const uint32_t* idx,
+                    const uint32_t* n_rows, int64_t n_max, int idx_mask_bits, int width, float* dst, int dst_stride);
+/* inv[perm[i]] = uidx[i] : lookup position -> index of its row in the unique list */
+int ctr_invert_perm(ctr_handle* h, ctr_stream s, const uint32_t* perm, const uint32_t* uidx, int64_t n, uint32_t* inv);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTR_B200_H */
