@@ -1,0 +1,250 @@
+#!/usr/bin/env python
+"""bench.py -- DeepFM train samples/sec on Criteo-shaped synthetic data (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (N=1): configs[3] on one GPU: DeepFM, 13 cont + 26 single-valued cate, k=16, MLP 400-400-400,
+batch 64K per GPU, ~1e8 table rows.  One "step" = one full train step (gather+FM, MLP fwd/bwd, log-loss,
+sort/segment-reduce scatter, Adam).  Prints ONE JSON line (see the task contract).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "deepfm_train_samples_per_sec"
+UNIT = "samples/s"
+
+
+def hparams(batch, rows):
+    from oracle.ctr_oracle import HParams   # plain dataclass of the reference's hyper-parameter names
+    return HParams(hidden_units=[400, 400, 400], batch_size=batch, embedding_size=16, cont_field_size=13,
+                   cate_field_size=26, cate_feats_size=rows, l2_reg=1e-5, learning_rate=1e-3)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured"
+    return 6650.0, 1400.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region"""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for ts, line in self.rows:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            inside = t0 <= ts <= t1 + 0.1
+            try:
+                if inside:
+                    sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            if inside:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def cpu_reference_arm(steps, warmup, batch=4096, rows=2_000_000):
+    """The reference's CPU path, restated (oracle, fp32, all host threads): one train step =
+    forward + log-loss + autodiff + TF1 dense Adam over the whole table, on a bounded sample of the
+    workload (same field shapes; batch and table rows reduced so the run ends in tens of seconds)."""
+    import torch
+    from oracle import ctr_oracle as O
+    import ctr_helpers as H
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    hp = hparams(batch, rows)
+    p = O.init_params("deepfm", hp, dtype=torch.float32)
+    st = O.adam_init(p)
+    batches = [H.oracle_batch(H.make_batch("deepfm", hp, seed=2020 + i), torch.float32) for i in range(2)]
+    for i in range(warmup):
+        _, p = O.train_step("deepfm", p, st, batches[i % 2], hp)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        _, p = O.train_step("deepfm", p, st, batches[i % 2], hp)
+    dt = time.perf_counter() - t0
+    return {"value": batch * steps / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "oracle fp32 (PyTorch-CPU restatement of models/deepfm.py; TensorFlow 1.x not installable), "
+                      "%d steps of batch %d, table %d rows, TF1 dense Adam" % (steps, batch, rows),
+            "ms_per_step": dt / steps * 1e3}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--batch", type=int, default=65536)
+    ap.add_argument("--rows", type=int, default=100_000_000)
+    ap.add_argument("--precision", default=os.environ.get("CTR_PRECISION", "fp32"))
+    ap.add_argument("--dist", default="zipf")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    W = max(a.warmup, 3)
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        cb = cpu_reference_arm(max(2, min(a.steps, 5)), 1)
+        line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus,
+                "steps": a.steps, "warmup": a.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "DeepFM Criteo-shape 13 cont + 26 cate k=16 MLP 400x3 (CPU sample: " + cb["sample"] + ")"},
+                "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+                "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    import torch
+    import torch.distributed as dist
+    import ctr_helpers as H
+    from deep_learning_b200 import data as D
+    from deep_learning_b200.engine import CtrEngine
+    from deep_learning_b200.models._base import init_weights
+    from deep_learning_b200.spec import spec_from_hparams
+
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if world > 1:
+        raise SystemExit("multi-GPU row-sharded path not wired into bench.py yet")
+
+    B, R = a.batch, a.rows
+    hp = hparams(B, R)
+    spec = spec_from_hparams("deepfm", hp)
+    eng = CtrEngine(spec, B, device=dev, learning_rate=hp.learning_rate, precision=a.precision, adam_mode="lazy")
+    eng.init_table_on_device(seed=2019)
+    eng.set_dense_weights(init_weights(spec, 2019, with_table=False))
+
+    # rotating synthetic batches, generated on the device (seed 2020+i), mirrored in pinned host memory
+    sizes = D.field_sizes(R, spec.Fc)
+    NB = 4
+    dev_batches = [D.synthetic_batch(B, spec.C, spec.Fc, sizes, seed=2020 + i, dist=a.dist, device=dev) for i in range(NB)]
+    host_batches = [{k: v.cpu().pin_memory() for k, v in b.items()} for b in dev_batches]
+    h2d = sum(v.numel() * v.element_size() for k, v in host_batches[0].items() if k != "vector_feats")
+
+    def sync():
+        torch.cuda.synchronize(dev)
+
+    # ---- device-resident timing ------------------------------------------------------------------
+    for i in range(W):
+        eng.train_step(dev_batches[i % NB])
+    sync()
+    timed = ("ctr_fm_gather_fwd", "ctr_embed_bwd_partials", "ctr_adam_rows", "ctr_sort_ids", "ctr_mlp_fwd",
+             "ctr_mlp_bwd_data", "ctr_mlp_bwd_weight")
+    eng.h.timers = {n: [] for n in timed}
+    l0 = eng.h.launches
+    clocks = ClockSampler(local)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync()
+    t0 = time.time()
+    e0.record()
+    for i in range(a.steps):
+        eng.train_step(dev_batches[i % NB])
+    e1.record()
+    sync()
+    t1 = time.time()
+    ms = e0.elapsed_time(e1)
+    launches = eng.h.launches - l0
+    kern = {n: (sum(x.elapsed_time(y) for x, y in ev) / max(len(ev), 1), len(ev)) for n, ev in eng.h.timers.items()}
+    eng.h.timers = None
+    clk = clocks.stop(t0, t1)
+    n_unique = int(eng.n_unique.item())
+    value = B * a.steps / (ms * 1e-3)
+
+    # ---- end to end through the public step API: pinned host batch in, loss scalar out, every step ----
+    for i in range(2):
+        float(eng.train_step(host_batches[i % NB]).item())
+    sync()
+    e0.record()
+    for i in range(a.steps):
+        loss = float(eng.train_step(host_batches[i % NB]).item())
+    e1.record()
+    sync()
+    e2e_ms = e0.elapsed_time(e1)
+
+    # ---- roofline of the embedding gather (K1): algorithmic bytes/sample x B / measured duration ----
+    hbm, tfl, which = peaks()
+    k1_bytes = (4 * spec.Fc + 4 * spec.C + 4 * spec.k * spec.Fc + 4 * spec.Fc + 8) * B      # 1932 B/sample
+    k1_ms = kern["ctr_fm_gather_fwd"][0]
+    k1_gbs = k1_bytes / (k1_ms * 1e-3) / 1e9
+    kernels = {}
+    step_ms = ms / a.steps
+    for n, (avg, cnt) in kern.items():
+        per_step = avg * cnt / a.steps
+        kernels[n] = {"ms_per_call": round(avg, 4), "calls_per_step": cnt / a.steps, "share_of_step": round(per_step / step_ms, 4)}
+    mlp_flops = 3 * 2 * sum(k_ * h_ for k_, h_ in eng._layer_dims()) * B
+    mlp_ms = sum(kern[n][0] * kern[n][1] for n in ("ctr_mlp_fwd", "ctr_mlp_bwd_data", "ctr_mlp_bwd_weight")) / a.steps
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": a.steps, "warmup": W,
+        "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32" if a.precision == "fp32" else "tf32", "data": "synthetic",
+        "config": {"workload": "DeepFM Criteo-shape: 13 cont + 26 single-valued cate, k=16, MLP 400-400-400, "
+                               "batch %d, table %d rows x (16+1) f32, ids %s, Adam lazy (touched rows)" % (B, R, a.dist),
+                   "batch_per_gpu": B, "table_rows": R, "unique_rows_last_step": n_unique, "mlp_precision": a.precision,
+                   "l2_flush": "working set per step (~0.9 GB activations + random rows of a %.1f GB table) >> 126 MB L2; "
+                               "%d rotating batches" % (eng.table.numel() * 4 / 1e9, NB)},
+        "clocks": clk,
+        "e2e": {"value": B * a.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+        "gpu_launches": int(launches),
+        "roofline": {"kernel": "fm_gather_fwd_kernel<16,true>", "bound": "hbm", "achieved": k1_gbs, "peak": hbm,
+                     "unit": "GB/s", "frac": k1_gbs / hbm, "traffic": None, "peak_source": which,
+                     "algorithmic_bytes_per_launch": k1_bytes},
+        "mlp": {"achieved_tflops": mlp_flops / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else None, "ms_per_step": mlp_ms},
+        "kernels": kernels,
+    }
+    if not a.no_cpu_baseline:
+        cb = cpu_reference_arm(3, 1)
+        line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

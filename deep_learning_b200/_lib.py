@@ -1,0 +1,164 @@
+"""ctypes binding of libctr_b200.so (the C-ABI declared in include/ctr_b200.h).
+
+The product path has NO CPU fallback: if the library is missing or a call fails this module
+raises; nothing is silently routed elsewhere.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libctr_b200.so")
+
+c_i32, c_i64, c_u64, c_f32, c_vp = C.c_int32, C.c_int64, C.c_uint64, C.c_float, C.c_void_p
+
+
+class EmbedCfg(C.Structure):
+    """mirror of `ctr_embed_cfg` (include/ctr_b200.h)"""
+    _fields_ = [(n, c_i32) for n in (
+        "B", "id_bytes", "ids_ld", "Fc", "Fm", "M", "C", "V", "k", "has_first", "use_fm", "fm_cont",
+        "zero_row0", "count_rule", "combiner", "table_stride", "x0_ld", "fm_ld", "grad_stride", "reserved")]
+
+
+class AdamHP(C.Structure):
+    """mirror of `ctr_adam_hp`"""
+    _fields_ = [("lr_t", c_f32), ("beta1", c_f32), ("beta2", c_f32), ("eps", c_f32)]
+
+
+_P_CFG = C.POINTER(EmbedCfg)
+_P_HP = C.POINTER(AdamHP)
+
+# name -> (restype, [argtypes]) ; the first two args (handle, stream) are added for every entry
+# except the handle-management ones.  Kept in header order.
+_PROTOS = {
+    "ctr_abi_version": (c_i32, None),
+    "ctr_sizeof_embed_cfg": (c_i32, None),
+    "ctr_create": (c_i32, [c_i32, C.POINTER(c_vp)]),
+    "ctr_destroy": (c_i32, [c_vp]),
+    "ctr_last_error": (C.c_char_p, [c_vp]),
+    "ctr_sm_count": (c_i32, [c_vp]),
+    "ctr_launch_count": (c_i64, [c_vp]),
+    "ctr_has_tcgen05": (c_i32, [c_vp]),
+    "ctr_table_pack": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp]),
+    "ctr_table_unpack": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
+    "ctr_pooled_gather_fwd": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "ctr_fm_gather_fwd": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "ctr_scalar_gather_sum": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp]),
+    "ctr_mlp_fwd": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp, c_vp, c_i32, c_f32,
+                            c_u64, c_vp, c_i64]),
+    "ctr_mlp_bwd_data": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp, c_i64, c_f32,
+                                 c_vp, c_i64]),
+    "ctr_mlp_bwd_weight_ws_bytes": (c_i64, [c_vp, c_i32, c_i32, c_i32, c_i32]),
+    "ctr_mlp_bwd_weight": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp,
+                                   c_vp, c_i64]),
+    "ctr_transpose": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp]),
+    "ctr_head_fwd": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp,
+                             c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
+    "ctr_head_bwd_deep": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64, c_vp, c_i64]),
+    "ctr_colsum_ws_bytes": (c_i64, [c_vp, c_i32, c_i32]),
+    "ctr_colsum": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64]),
+    "ctr_reduce": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64]),
+    "ctr_sort_ws_bytes": (c_i64, [c_vp, c_i64]),
+    "ctr_sort_ids": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_i32, c_i32, c_i64, c_i32, c_i64, c_i32,
+                             c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64]),
+    "ctr_sort_pairs": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_i64]),
+    "ctr_unique_segments": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
+    "ctr_shard_counts": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp]),
+    "ctr_embed_bwd_partials": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_i64, c_vp,
+                                       c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "ctr_embed_bwd_finalize": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
+    "ctr_cont_bwd_ws_bytes": (c_i64, [c_vp, _P_CFG]),
+    "ctr_fm_cont_bwd": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
+    "ctr_adam_rows": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp,
+                              c_i32, c_i64, c_vp, _P_HP]),
+    "ctr_adam_dense": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_f32, c_f32, c_vp, c_i32, _P_HP]),
+    "ctr_auc_ws_bytes": (c_i64, [c_vp, c_i64]),
+    "ctr_auc": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i64]),
+    "ctr_gather_rows": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_i32]),
+    "ctr_invert_perm": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
+}
+
+EXPORTS = tuple(_PROTOS)
+
+
+class CtrError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load(path: str = LIB_PATH) -> C.CDLL:
+    """dlopen the C-ABI library and set prototypes.  Raises if it is missing (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(path):
+        raise CtrError("libctr_b200.so not found at %s; build it with `python -m deep_learning_b200.build` "
+                       "(there is no CPU fallback)" % path)
+    lib = C.CDLL(path)
+    for name, (res, args) in _PROTOS.items():
+        fn = getattr(lib, name)          # AttributeError if the symbol is not exported
+        fn.restype = res
+        if args is not None:
+            fn.argtypes = args
+    if lib.ctr_abi_version() != 1:
+        raise CtrError("ABI version mismatch")
+    if lib.ctr_sizeof_embed_cfg() != C.sizeof(EmbedCfg):
+        raise CtrError("ctr_embed_cfg layout mismatch")
+    _lib = lib
+    return lib
+
+
+def ptr(t):
+    """device pointer of a torch tensor (None -> NULL)"""
+    return None if t is None else t.data_ptr()
+
+
+class Handle:
+    """one `ctr_handle` per device; `call` checks the status code and raises with ctr_last_error."""
+
+    def __init__(self, device_index: int):
+        self.lib = load()
+        h = c_vp()
+        rc = self.lib.ctr_create(int(device_index), C.byref(h))
+        if rc != 0 or not h.value:
+            raise CtrError("ctr_create(device=%d) failed with %d (is a CUDA device present?)" % (device_index, rc))
+        self.h = h
+        self.device_index = device_index
+        self.sm_count = self.lib.ctr_sm_count(h)
+        self.has_tcgen05 = bool(self.lib.ctr_has_tcgen05(h))
+        self.timers = None     # name -> [events] when bench.py profiles selected entry points
+
+    def call(self, name: str, stream: int, *args):
+        tm = self.timers.get(name) if self.timers is not None else None
+        if tm is not None:
+            import torch
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()          # torch's current stream == `stream` (engine passes current_stream)
+        rc = getattr(self.lib, name)(self.h, stream, *args)
+        if rc != 0:
+            raise CtrError("%s failed (%d): %s" % (name, rc, self.lib.ctr_last_error(self.h).decode()))
+        if tm is not None:
+            e1.record()
+            tm.append((e0, e1))
+
+    @property
+    def launches(self) -> int:
+        """kernels launched through this handle (counted inside the library)"""
+        return int(self.lib.ctr_launch_count(self.h))
+
+    def query(self, name: str, *args) -> int:
+        return int(getattr(self.lib, name)(self.h, *args))
+
+    def close(self):
+        if self.h is not None and self.h.value:
+            self.lib.ctr_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -17,6 +17,7 @@ extern "C" int ctr_create(int device, ctr_handle** out) {
     h->cc_major = prop.major;
     h->cc_minor = prop.minor;
     h->err[0] = 0;
+    h->launches = 0;
     *out = h;
     return CTR_OK;
 }
@@ -28,6 +29,7 @@ extern "C" int ctr_destroy(ctr_handle* h) {
 
 extern "C" const char* ctr_last_error(ctr_handle* h) { return h ? h->err : "null handle"; }
 extern "C" int ctr_sm_count(ctr_handle* h) { return h ? h->sm_count : 0; }
+extern "C" int64_t ctr_launch_count(ctr_handle* h) { return h ? (int64_t) h->launches : 0; }
 extern "C" int ctr_has_tcgen05(ctr_handle* h) { return h && h->cc_major == 10 ? 1 : 0; }
 
 // ------------------------------------------------------------------ table pack / unpack

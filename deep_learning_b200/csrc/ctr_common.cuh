@@ -11,6 +11,7 @@ struct ctr_handle {
     int device;
     int sm_count;
     int cc_major, cc_minor;
+    unsigned long long launches;   // kernels launched through this handle
     char err[512];
 };
 
@@ -37,6 +38,7 @@ static inline int ctr_fail(ctr_handle* h, int code, const char* fmt, ...) {
         cudaError_t _e = cudaGetLastError();                                             \
         if (_e != cudaSuccess)                                                           \
             return ctr_fail((h), CTR_E_CUDA, "%s: %s", (what), cudaGetErrorString(_e));  \
+        (h)->launches += 1;                                                              \
     } while (0)
 
 #define CTR_CUDA(h, call)                                                                \

@@ -16,7 +16,8 @@ embed_bwd_partials_kernel(const ctr_embed_cfg cfg, const uint32_t* __restrict__ 
                           const float* __restrict__ x0, const float* __restrict__ dx0, const int64_t dx0_ld,
                           const float* __restrict__ sum_e, const float* __restrict__ dlogit,
                           const float* __restrict__ w_fm, const float* __restrict__ inv_cnt_emb,
-                          const float* __restrict__ inv_cnt_first, float* __restrict__ part) {
+                          const float* __restrict__ inv_cnt_first, const float* __restrict__ cont_grad,
+                          float* __restrict__ part) {
     constexpr int G = K;       // lanes per chunk walker: lane j owns embedding coordinate j
     constexpr int UN = 4;      // lookups in flight per walker
     const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -29,6 +30,7 @@ embed_bwd_partials_kernel(const ctr_embed_cfg cfg, const uint32_t* __restrict__ 
     const bool use_fm = cfg.use_fm != 0, has_first = cfg.has_first != 0;
     const float* __restrict__ w1 = w_fm;                         // first-order head weights, per field
     const float w2j = use_fm ? w_fm[Fc + Fm + cfg.C + j] : 0.f;  // second-order head weight of coordinate j
+    const uint32_t n_lookup = (uint32_t) cfg.B * (uint32_t) ids_ld;
 
     uint32_t cur = CTR_PAD_KEY;
     int64_t cur_slot = 0;
@@ -46,6 +48,12 @@ embed_bwd_partials_kernel(const ctr_embed_cfg cfg, const uint32_t* __restrict__ 
                 if (key[q] != CTR_PAD_KEY) {
                     u[q] = uidx[base + i];
                     const uint32_t p = perm[base + i];
+                    if (p >= n_lookup) {   // appended continuous-field row: gradient was reduced densely
+                        const int cc = (int) (p - n_lookup);
+                        gv[q] = cont_grad[cc * gs + j];
+                        gw[q] = has_first ? cont_grad[cc * gs + K] : 0.f;
+                        continue;
+                    }
                     const uint32_t b = p / (uint32_t) ids_ld;
                     const int slot = (int) (p - b * (uint32_t) ids_ld);
                     int fld = slot;
@@ -128,7 +136,6 @@ __global__ void __launch_bounds__(256)
 adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restrict__ n_rows, int64_t n_max, uint32_t mask,
                  const float* __restrict__ grads, const uint32_t* __restrict__ seg_start, int gs, int width,
                  float* __restrict__ table, float* __restrict__ m, float* __restrict__ v, int stride, int64_t table_rows,
-                 const float* __restrict__ extra_grad, int64_t extra_base, int extra_n, uint8_t* __restrict__ extra_hit,
                  uint8_t* __restrict__ touched, const ctr_adam_hp hp) {
     int64_t U = n_rows ? (int64_t) *n_rows : n_max;
     if (U > n_max) U = n_max;
@@ -141,10 +148,6 @@ adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restric
         const int64_t row = (int64_t) (key & mask);
         if (row >= table_rows) continue;   // defensive: never write outside the table
         float g = seg_start ? sum_run_partials(grads, seg_start, u, j, gs) : grads[u * gs + j];
-        if (extra_grad && row >= extra_base && row < extra_base + extra_n) {
-            g += extra_grad[(row - extra_base) * gs + j];
-            if (j == 0 && extra_hit) extra_hit[row - extra_base] = 1;
-        }
         const int64_t o = row * stride + j;
         const float mm = hp.beta1 * m[o] + (1.f - hp.beta1) * g;
         const float vv = hp.beta2 * v[o] + (1.f - hp.beta2) * g * g;
@@ -229,7 +232,7 @@ extern "C" int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_emb
                                       const uint32_t* perm, const uint32_t* uidx, int64_t n, const int32_t* field_of_slot,
                                       const float* x0, const float* dx0, int64_t dx0_ld, const float* sum_e,
                                       const float* dlogit, const float* w_fm, const float* inv_cnt_emb,
-                                      const float* inv_cnt_first, float* part) {
+                                      const float* inv_cnt_first, const float* cont_grad, float* part) {
     int rc = ctr_check_embed_cfg(h, cfg);
     if (rc) return rc;
     CTR_REQUIRE(h, sorted_keys && perm && uidx && dx0 && part && n >= 0, "embed_bwd_partials: null pointer");
@@ -244,7 +247,7 @@ extern "C" int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_emb
 #define LAUNCH_BP(KK)                                                                                                  \
     embed_bwd_partials_kernel<KK><<<blocks, 256, 0, ctr_st(s)>>>(*cfg, sorted_keys, perm, uidx, n, field_of_slot, x0, dx0, \
                                                                 dx0_ld, sum_e, dlogit, w_fm, inv_cnt_emb, inv_cnt_first,   \
-                                                                part)
+                                                                cont_grad, part)
     switch (cfg->k) {
         case 4: LAUNCH_BP(4); break;
         case 8: LAUNCH_BP(8); break;
@@ -276,7 +279,6 @@ extern "C" int ctr_embed_bwd_finalize(ctr_handle* h, ctr_stream s, const uint32_
 extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
                              int local_bits, const float* grads, const uint32_t* seg_start, int grad_stride, int width,
                              float* table, float* m, float* v, int table_stride, int64_t table_rows,
-                             const float* extra_grad, int64_t extra_base, int extra_n, uint8_t* extra_hit,
                              uint8_t* touched, const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, row_ids && grads && table && m && v && hp, "adam_rows: null pointer");
     CTR_REQUIRE(h, width > 0 && grad_stride >= width && table_stride >= width && n_max >= 0 && table_rows > 0,
@@ -285,8 +287,7 @@ extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_id
     uint32_t mask = (local_bits <= 0 || local_bits >= 32) ? 0xFFFFFFFFu : ((1u << local_bits) - 1u);
     adam_rows_kernel<<<grid_for(h, n_max * width), 256, 0, ctr_st(s)>>>(row_ids, n_rows, n_max, mask, grads, seg_start,
                                                                          grad_stride, width, table, m, v, table_stride,
-                                                                         table_rows, extra_grad, extra_base, extra_n,
-                                                                         extra_hit, touched, *hp);
+                                                                         table_rows, touched, *hp);
     CTR_CHECK_LAUNCH(h, "adam_rows");
     return CTR_OK;
 }

@@ -1,0 +1,177 @@
+// K5: output head (concat + [.,1] projection + sigmoid), tf.losses.log_loss and its gradient,
+// plus the deterministic column reductions that give head-weight / bias gradients.
+#include "ctr_common.cuh"
+
+namespace {
+
+constexpr float LOG_LOSS_EPS = 1e-7f;   // tf.losses.log_loss default epsilon
+
+// one warp per sample
+__global__ void __launch_bounds__(256)
+head_fwd_kernel(int B, const float* __restrict__ fm, int64_t fm_ld, int n_fm, const float* __restrict__ w_fm,
+                const float* __restrict__ deep, int64_t deep_ld, int H, const float* __restrict__ w_deep,
+                const float* __restrict__ extra, const float* __restrict__ bias, const float* __restrict__ label,
+                float* __restrict__ logit, float* __restrict__ score, float* __restrict__ dlogit,
+                float* __restrict__ loss_part) {
+    __shared__ float wl[8];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t b = (int64_t) blockIdx.x * 8 + w;
+    float l = 0.f;
+    if (b < B) {
+        float acc = 0.f;
+        if (n_fm > 0) {
+            const float* r = fm + b * fm_ld;
+            for (int j = lane; j < n_fm; j += 32) acc = fmaf(r[j], w_fm[j], acc);
+        }
+        if (H > 0) {
+            const float* r = deep + b * deep_ld;
+            for (int j = lane; j < H; j += 32) acc = fmaf(r[j], w_deep[j], acc);
+        }
+        acc = ctr_warp_sum(acc);
+        float z = acc + (extra ? extra[b] : 0.f) + (bias ? bias[0] : 0.f);
+        float p = 1.f / (1.f + expf(-z));
+        if (lane == 0) {
+            if (logit) logit[b] = z;
+            if (score) score[b] = p;
+        }
+        if (label) {
+            const float y = label[b];
+            l = -y * logf(p + LOG_LOSS_EPS) - (1.f - y) * logf(1.f - p + LOG_LOSS_EPS);
+            // d/dz [ -y log(p+e) - (1-y) log(1-p+e) ] = (-y/(p+e) + (1-y)/(1-p+e)) * p(1-p), mean over B
+            if (lane == 0 && dlogit)
+                dlogit[b] = (-y / (p + LOG_LOSS_EPS) + (1.f - y) / (1.f - p + LOG_LOSS_EPS)) * p * (1.f - p) / (float) B;
+        }
+    }
+    if (label && loss_part) {
+        if (lane == 0) wl[w] = l;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float s = 0.f;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) s += wl[i];
+            loss_part[blockIdx.x] = s;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(1024) loss_final_kernel(const float* __restrict__ part, int nparts, int B, float* __restrict__ out) {
+    __shared__ float sm[32];
+    float acc = 0.f;
+    for (int i = threadIdx.x; i < nparts; i += blockDim.x) acc += part[i];
+    float r = ctr_block_sum(acc, sm);
+    if (threadIdx.x == 0) out[0] = r / (float) B;
+}
+
+__global__ void __launch_bounds__(256)
+head_bwd_deep_kernel(int B, int H, const float* __restrict__ dlogit, const float* __restrict__ w_deep,
+                     const float* __restrict__ deep, int64_t deep_ld, float* __restrict__ dZ, int64_t lddz) {
+    const int64_t total = (int64_t) B * H;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t b = t / H;
+        const int j = (int) (t - b * H);
+        const float a = deep[b * deep_ld + j];
+        dZ[b * lddz + j] = a > 0.f ? dlogit[b] * w_deep[j] : 0.f;
+    }
+}
+
+// column reduction pass 1: block (x = column tile of 128, y = row slice)
+constexpr int CS_ROWS = 256;   // rows per block slice
+__global__ void __launch_bounds__(128)
+colsum_pass1(const float* __restrict__ X, int64_t ldx, int B, int ncols, const float* __restrict__ w,
+             float* __restrict__ ws) {
+    const int col = blockIdx.x * 128 + threadIdx.x;
+    const int64_t lo = (int64_t) blockIdx.y * CS_ROWS;
+    const int64_t hi = lo + CS_ROWS < B ? lo + CS_ROWS : B;
+    if (col >= ncols) return;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    int64_t b = lo;
+    if (w) {
+        for (; b + 4 <= hi; b += 4) {
+            a0 = fmaf(w[b], X[b * ldx + col], a0);
+            a1 = fmaf(w[b + 1], X[(b + 1) * ldx + col], a1);
+            a2 = fmaf(w[b + 2], X[(b + 2) * ldx + col], a2);
+            a3 = fmaf(w[b + 3], X[(b + 3) * ldx + col], a3);
+        }
+        for (; b < hi; ++b) a0 = fmaf(w[b], X[b * ldx + col], a0);
+    } else {
+        for (; b + 4 <= hi; b += 4) {
+            a0 += X[b * ldx + col];
+            a1 += X[(b + 1) * ldx + col];
+            a2 += X[(b + 2) * ldx + col];
+            a3 += X[(b + 3) * ldx + col];
+        }
+        for (; b < hi; ++b) a0 += X[b * ldx + col];
+    }
+    ws[(int64_t) blockIdx.y * ncols + col] = (a0 + a1) + (a2 + a3);
+}
+
+__global__ void __launch_bounds__(128) colsum_pass2(const float* __restrict__ ws, int nslices, int ncols, float* __restrict__ out) {
+    const int col = blockIdx.x * 128 + threadIdx.x;
+    if (col >= ncols) return;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    int s = 0;
+    for (; s + 4 <= nslices; s += 4) {
+        a0 += ws[(int64_t) s * ncols + col];
+        a1 += ws[(int64_t) (s + 1) * ncols + col];
+        a2 += ws[(int64_t) (s + 2) * ncols + col];
+        a3 += ws[(int64_t) (s + 3) * ncols + col];
+    }
+    for (; s < nslices; ++s) a0 += ws[(int64_t) s * ncols + col];
+    out[col] = (a0 + a1) + (a2 + a3);
+}
+
+}  // namespace
+
+extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, const float* fm, int64_t fm_ld, int n_fm,
+                            const float* w_fm, const float* deep, int64_t deep_ld, int H, const float* w_deep,
+                            const float* extra, const float* bias, const float* label, float* logit, float* score,
+                            float* dlogit, float* loss_out, void* ws, int64_t ws_bytes) {
+    CTR_REQUIRE(h, B >= 0 && n_fm >= 0 && H >= 0, "head_fwd: negative sizes");
+    CTR_REQUIRE(h, n_fm == 0 || (fm && w_fm), "head_fwd: fm inputs null");
+    CTR_REQUIRE(h, H == 0 || (deep && w_deep), "head_fwd: deep inputs null");
+    if (B == 0) return CTR_OK;
+    const int nblk = (int) ctr_cdiv(B, 8);
+    float* part = nullptr;
+    if (label && loss_out) {
+        CTR_REQUIRE(h, ws != nullptr, "head_fwd: ws null");
+        if (ws_bytes < (int64_t) nblk * 4) return ctr_fail(h, CTR_E_WORKSPACE, "head_fwd: ws too small");
+        part = (float*) ws;
+    }
+    head_fwd_kernel<<<nblk, 256, 0, ctr_st(s)>>>(B, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra, bias, label,
+                                                 logit, score, dlogit, part);
+    CTR_CHECK_LAUNCH(h, "head_fwd");
+    if (part) {
+        loss_final_kernel<<<1, 1024, 0, ctr_st(s)>>>(part, nblk, B, loss_out);
+        CTR_CHECK_LAUNCH(h, "loss_final");
+    }
+    return CTR_OK;
+}
+
+extern "C" int ctr_head_bwd_deep(ctr_handle* h, ctr_stream s, int B, int H, const float* dlogit, const float* w_deep,
+                                 const float* deep, int64_t deep_ld, float* dZ, int64_t lddz) {
+    CTR_REQUIRE(h, dlogit && w_deep && deep && dZ && B >= 0 && H > 0, "head_bwd_deep: bad args");
+    if (B == 0) return CTR_OK;
+    int64_t blocks = ctr_cdiv((int64_t) B * H, 256);
+    int64_t cap = (int64_t) h->sm_count * 16;
+    if (blocks > cap) blocks = cap;
+    head_bwd_deep_kernel<<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(B, H, dlogit, w_deep, deep, deep_ld, dZ, lddz);
+    CTR_CHECK_LAUNCH(h, "head_bwd_deep");
+    return CTR_OK;
+}
+
+extern "C" int64_t ctr_colsum_ws_bytes(ctr_handle*, int B, int ncols) {
+    return ctr_cdiv(B > 0 ? B : 1, CS_ROWS) * (int64_t) ncols * 4 + 256;
+}
+
+extern "C" int ctr_colsum(ctr_handle* h, ctr_stream s, const float* X, int64_t ldx, int B, int ncols, const float* w,
+                          float* out, void* ws, int64_t ws_bytes) {
+    CTR_REQUIRE(h, X && out && ws && B >= 0 && ncols > 0 && ldx >= ncols, "colsum: bad args");
+    if (ws_bytes < ctr_colsum_ws_bytes(h, B, ncols)) return ctr_fail(h, CTR_E_WORKSPACE, "colsum: ws too small");
+    const int nsl = (int) ctr_cdiv(B > 0 ? B : 1, CS_ROWS);
+    dim3 grid((unsigned) ctr_cdiv(ncols, 128), (unsigned) nsl);
+    colsum_pass1<<<grid, 128, 0, ctr_st(s)>>>(X, ldx, B, ncols, w, (float*) ws);
+    CTR_CHECK_LAUNCH(h, "colsum_pass1");
+    colsum_pass2<<<(unsigned) ctr_cdiv(ncols, 128), 128, 0, ctr_st(s)>>>((const float*) ws, nsl, ncols, out);
+    CTR_CHECK_LAUNCH(h, "colsum_pass2");
+    return CTR_OK;
+}

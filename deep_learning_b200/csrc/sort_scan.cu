@@ -163,17 +163,26 @@ __global__ void copy_pairs_kernel(const uint32_t* __restrict__ ka, const uint32_
 }
 
 __global__ void build_keys_kernel(const void* __restrict__ ids, int id_bytes, int64_t rows, int64_t ld, int col0,
-                                  int ncols, int64_t id_offset, int drop_zero, int n_shards, int local_bits,
+                                  int ncols, int64_t id_offset, int drop_zero, int64_t extra_base, int n_extra,
+                                  int n_shards, int local_bits,
                                   uint32_t* __restrict__ keys, uint32_t* __restrict__ perm) {
     int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     int64_t n = rows * ncols;
-    if (i >= n) return;
-    int64_t r = i / ncols;
-    int c = (int) (i - r * ncols);
-    int64_t p = r * ld + col0 + c;
-    int64_t id = ctr_load_id(ids, id_bytes, p) + id_offset;
+    if (i >= n + n_extra) return;
+    int64_t p, id;
+    bool pad = false;
+    if (i < n) {
+        int64_t r = i / ncols;
+        int c = (int) (i - r * ncols);
+        p = r * ld + col0 + c;
+        id = ctr_load_id(ids, id_bytes, p) + id_offset;
+        pad = drop_zero && id == 0;
+    } else {
+        p = rows * ld + (i - n);
+        id = extra_base + (i - n);
+    }
     uint32_t key;
-    if (drop_zero && id == 0) key = CTR_PAD_KEY;
+    if (pad) key = CTR_PAD_KEY;
     else if (n_shards > 1) key = ((uint32_t) (id % n_shards) << local_bits) | (uint32_t) (id / n_shards);
     else key = (uint32_t) id;
     keys[i] = key;
@@ -322,23 +331,28 @@ extern "C" int ctr_sort_pairs(ctr_handle* h, ctr_stream s, uint32_t* keys, uint3
         t = ka; ka = kb; kb = t;
         t = va; va = vb; vb = t;
     }
-    if (ka != keys) copy_pairs_kernel<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>(ka, va, keys, vals, n);
+    h->launches += 3ull * passes - 1;
+    if (ka != keys) {
+        copy_pairs_kernel<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>(ka, va, keys, vals, n);
+        h->launches += 1;
+    }
     CTR_CHECK_LAUNCH(h, "sort_pairs");
     return CTR_OK;
 }
 
 extern "C" int ctr_sort_ids(ctr_handle* h, ctr_stream s, const void* ids, int id_bytes, int64_t rows, int64_t ld,
-                            int col0, int ncols, int64_t id_offset, int drop_zero, int n_shards, int local_bits,
+                            int col0, int ncols, int64_t id_offset, int drop_zero, int64_t extra_base, int n_extra,
+                            int n_shards, int local_bits,
                             int key_bits, uint32_t* keys_out, uint32_t* perm_out, void* ws, int64_t ws_bytes) {
     CTR_REQUIRE(h, ids && keys_out && perm_out && (id_bytes == 4 || id_bytes == 8), "sort_ids: bad pointers");
     CTR_REQUIRE(h, rows >= 0 && ncols >= 0 && col0 >= 0 && col0 + ncols <= ld, "sort_ids: bad shape");
     CTR_REQUIRE(h, n_shards >= 1 && (n_shards == 1 || (local_bits > 0 && local_bits < 31)), "sort_ids: bad sharding");
-    CTR_REQUIRE(h, rows * ld < ((int64_t) 1 << 32), "sort_ids: flat positions exceed 32 bits");
-    int64_t n = rows * ncols;
+    CTR_REQUIRE(h, n_extra >= 0 && rows * ld + n_extra < ((int64_t) 1 << 32), "sort_ids: flat positions exceed 32 bits");
+    int64_t n = rows * ncols + n_extra;
     if (n == 0) return CTR_OK;
     build_keys_kernel<<<(unsigned) ctr_cdiv(n, 256), 256, 0, ctr_st(s)>>>(ids, id_bytes, rows, ld, col0, ncols, id_offset,
-                                                                         drop_zero, n_shards, local_bits, keys_out,
-                                                                         perm_out);
+                                                                         drop_zero, extra_base, n_extra, n_shards,
+                                                                         local_bits, keys_out, perm_out);
     CTR_CHECK_LAUNCH(h, "build_keys");
     return ctr_sort_pairs(h, s, keys_out, perm_out, n, drop_zero ? 32 : key_bits, ws, ws_bytes);
 }
@@ -360,6 +374,7 @@ extern "C" int ctr_unique_segments(ctr_handle* h, ctr_stream s, const uint32_t* 
     scan_phase2<<<1, 1024, 0, st>>>(blk, nblk, n_unique);
     scan_phase3<HeadFlag, UniqueOut><<<nblk, SCAN_THREADS, 0, st>>>(f, n, blk, UniqueOut{sorted_keys, uniq, seg_start, uidx});
     seg_tail_kernel<<<1, 1, 0, st>>>(n_unique, seg_start, (uint32_t) n);
+    h->launches += 3;
     CTR_CHECK_LAUNCH(h, "unique_segments");
     return CTR_OK;
 }
@@ -382,6 +397,7 @@ int ctr_scan_pos_labels(ctr_handle* h, cudaStream_t st, const float* labels, con
     scan_phase1<PosLabel><<<nblk, SCAN_THREADS, 0, st>>>(f, n, blk_ws);
     scan_phase2<<<1, 1024, 0, st>>>(blk_ws, nblk, out + n);
     scan_phase3<PosLabel, ExclOut><<<nblk, SCAN_THREADS, 0, st>>>(f, n, blk_ws, ExclOut{out});
+    h->launches += 2;
     CTR_CHECK_LAUNCH(h, "scan_pos_labels");
     return CTR_OK;
 }

@@ -1,0 +1,423 @@
+"""CtrEngine: device state and the step schedule of one model on one GPU.
+
+PyTorch is plumbing here (device memory, streams, H2D/D2H copies); every arithmetic step of the
+hot path is a call into libctr_b200.so through `_lib.Handle.call`.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import AdamHP, EmbedCfg, ptr
+from .spec import ModelSpec
+
+ADAM_BETA1, ADAM_BETA2, ADAM_EPS = 0.9, 0.999, 1e-8   # tf.train.AdamOptimizer defaults (models/deepfm.py:161)
+PREC = {"fp32": 0, "tf32": 1}
+_ALIGN = 64   # floats; keeps every dense parameter 256-byte aligned inside the flat buffer
+
+
+def _ru(a: int, b: int) -> int:
+    return (a + b - 1) // b * b
+
+
+class CtrEngine:
+    def __init__(self, spec: ModelSpec, max_batch: int, device: Optional[torch.device] = None,
+                 learning_rate: float = 0.001, decay_steps: int = 10000000, decay_rate: float = 0.9,
+                 precision: str = "fp32", adam_mode: str = "tf_dense", train: bool = True):
+        if not torch.cuda.is_available():
+            raise _lib.CtrError("CtrEngine needs a CUDA device: the hot path has no CPU fallback")
+        assert adam_mode in ("tf_dense", "lazy") and precision in PREC
+        self.spec, self.Bmax = spec, int(max_batch)
+        self.dev = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
+        self.h = _lib.Handle(self.dev.index if self.dev.index is not None else torch.cuda.current_device())
+        self.lr0, self.decay_steps, self.decay_rate = learning_rate, decay_steps, decay_rate
+        self.prec, self.adam_mode, self.train_mode = PREC[precision], adam_mode, train
+        if self.prec == 1 and not self.h.has_tcgen05:
+            raise _lib.CtrError("precision='tf32' needs an sm_100 device")
+        self.global_step, self.beta1_power, self.beta2_power = 0, ADAM_BETA1, ADAM_BETA2
+        s, B, dev = spec, self.Bmax, self.dev
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.id_torch = torch.int64 if s.id_dtype == "int64" else torch.int32
+        self.id_bytes = 8 if s.id_dtype == "int64" else 4
+
+        # ---- parameters ---------------------------------------------------------------------
+        self.table = torch.zeros(s.table_rows, s.table_stride, **f32)
+        self.dense_shapes = s.dense_param_shapes()
+        # flat buffer ordered by regulariser group so Adam needs at most three launches
+        order = {"none": 0, "l2": 1, "l1": 2}
+        grp = lambda n: s.reg.get(n, "none") if s.l2_reg > 0 else "none"
+        names = sorted(range(len(self.dense_shapes)), key=lambda i: (order[grp(self.dense_shapes[i][0])], i))
+        self.off: Dict[str, int] = {}
+        self.groups: List[List[int]] = [[0, 0], [0, 0], [0, 0]]   # [start, end) per reg group
+        cur = 0
+        for gi in range(3):
+            self.groups[gi][0] = cur
+            for i in names:
+                n, shp = self.dense_shapes[i]
+                if order[grp(n)] != gi:
+                    continue
+                self.off[n] = cur
+                cur += _ru(int(np.prod(shp)), _ALIGN)
+            self.groups[gi][1] = cur
+        self.n_dense = cur
+        self.theta = torch.zeros(cur, **f32)
+        self.shape = dict(self.dense_shapes)
+        # K-major copies of the tower weights for the tcgen05 path
+        self.wt = [torch.zeros(h_, k_, **f32) for (k_, h_) in self._layer_dims()] if self.prec == 1 else None
+
+        # ---- batch + activations ----------------------------------------------------------------
+        self.ids = torch.zeros(B, max(s.ids_ld, 1), dtype=self.id_torch, device=dev)
+        self.cont = torch.zeros(B, max(s.C, 1), **f32)
+        self.vec = torch.zeros(B, max(s.V, 1), **f32)
+        self.label = torch.zeros(B, **f32)
+        self.x0 = torch.zeros(B, s.x0_ld, **f32)
+        self.acts = [torch.zeros(B, h_, **f32) for h_ in s.hidden]
+        self.fm = torch.zeros(B, s.fm_ld, **f32)
+        self.sum_e = torch.zeros(B, s.k, **f32)
+        self.logit, self.score, self.dlogit = (torch.zeros(B, **f32) for _ in range(3))
+        self.loss = torch.zeros(1, **f32)
+        self.reg_terms = torch.zeros(4, **f32)
+        self.pooled_first = torch.zeros(B, max(s.Fm, 1), **f32)
+        self.inv_cnt_emb = torch.zeros(B, max(s.Fm, 1), **f32)
+        self.inv_cnt_first = torch.zeros(B, max(s.Fm, 1), **f32)
+        self.multi_start = torch.from_numpy(s.multi_start()).to(dev)
+        self.field_of_slot = torch.from_numpy(s.field_of_slot()).to(dev)
+        self.wide = torch.zeros(B, max(s.wide_fields, 1), dtype=self.id_torch, device=dev) if s.head == "wdl" else None
+        self.wide_sum = torch.zeros(B, **f32) if s.head == "wdl" else None
+
+        ws_bytes = max(self.h.query("ctr_colsum_ws_bytes", B, max(s.hidden + [s.fm_ld])), 4 * (B // 8 + 8), 1 << 16)
+        if train:
+            self.m_table, self.v_table = torch.zeros_like(self.table), torch.zeros_like(self.table)
+            self.m, self.v, self.grad = (torch.zeros(cur, **f32) for _ in range(3))
+            maxh = max(s.hidden)
+            self.dz = [torch.zeros(B, maxh, **f32) for _ in range(2)]
+            self.dx0_ld = _ru(max(s.E, 4), 4)
+            self.dx0 = torch.zeros(B, self.dx0_ld, **f32)
+            self.n_extra = s.C if (s.use_fm and s.fm_cont) else 0
+            n = B * s.ids_ld + self.n_extra
+            self.n_sort = n
+            u32 = dict(dtype=torch.int32, device=dev)   # raw 32-bit storage; the library treats it as uint32
+            self.keys, self.perm, self.uidx, self.uniq = (torch.zeros(max(n, 1), **u32) for _ in range(4))
+            self.seg_start = torch.zeros(n + 2, **u32)
+            self.n_unique = torch.zeros(1, **u32)
+            self.part = torch.zeros((n + n // 32 + 2) * s.grad_stride, **f32)
+            self.cont_grad = torch.zeros(max(s.C, 1), s.grad_stride, **f32)
+            self.touched = torch.zeros(s.table_rows, dtype=torch.uint8, device=dev) if adam_mode == "tf_dense" else None
+            cfg = self._cfg(B)
+            ws_bytes = max(ws_bytes, self.h.query("ctr_sort_ws_bytes", n), self.h.query("ctr_cont_bwd_ws_bytes", cfg),
+                           4 * (n // 2048 + 8))
+            for (k_, h_) in self._layer_dims():
+                ws_bytes = max(ws_bytes, self.h.query("ctr_mlp_bwd_weight_ws_bytes", self.prec, B, k_, h_))
+        self.ws = torch.zeros(_ru(ws_bytes, 256), dtype=torch.uint8, device=dev)
+        self.last_batch = 0
+
+    # ------------------------------------------------------------------------------------------
+    def _layer_dims(self):
+        dims, prev = [], self.spec.D0
+        for h_ in self.spec.hidden:
+            dims.append((prev, h_))
+            prev = h_
+        return dims
+
+    def _cfg(self, B: int) -> EmbedCfg:
+        s = self.spec
+        return EmbedCfg(B=B, id_bytes=self.id_bytes, ids_ld=max(s.ids_ld, 1) if s.ids_ld == 0 else s.ids_ld, Fc=s.Fc,
+                        Fm=s.Fm, M=s.M, C=s.C, V=s.V, k=s.k, has_first=int(s.has_first), use_fm=int(s.use_fm),
+                        fm_cont=int(s.fm_cont), zero_row0=int(s.zero_row0), count_rule=0, combiner=0,
+                        table_stride=s.table_stride, x0_ld=s.x0_ld, fm_ld=s.fm_ld, grad_stride=s.grad_stride,
+                        reserved=0)
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.dev).cuda_stream
+
+    def view(self, name: str, buf: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """flat-buffer view of a dense parameter (internal layout)"""
+        buf = self.theta if buf is None else buf
+        shp = self.shape[name]
+        n = int(np.prod(shp))
+        return buf[self.off[name]: self.off[name] + n]
+
+    def _w(self, i: int, buf=None):
+        return self.view("deep_%d" % i, buf)
+
+    def _b(self, i: int, buf=None):
+        return self.view("deep_bias_%d" % i, buf)
+
+    def _head_parts(self, buf=None):
+        """(w_fm, w_deep, bias) views of the head parameters"""
+        s = self.spec
+        H = s.hidden[-1]
+        if s.head == "deepfm":
+            w = self.view(s.head_w_name, buf)
+            return w[:s.n_fm], w[s.n_fm:s.n_fm + H], self.view(s.head_b_name, buf)
+        if s.head == "dnn":
+            return None, self.view(s.head_w_name, buf), self.view(s.head_b_name, buf)
+        w = self.view("wdl_weights", buf)     # quirk Q4: deep weights alias rows W..W+H-1 (models/wdl.py:224-225)
+        return None, w[s.wide_fields:s.wide_fields + H], self.view("wdl_bias", buf)
+
+    # ---- parameter injection / read-back (reference names and shapes) ------------------------------
+    def set_weights(self, p: Dict[str, np.ndarray]) -> None:
+        """Load variables named and shaped as in the reference model file (e.g. feats_emb [R,k],
+        feats [R,1], deep_0 [D0,H0] in [cont|vector|emb] row order, deep_fm_weight [F+k+H,1])."""
+        s, st = self.spec, self._stream()
+        t = lambda a: torch.as_tensor(np.ascontiguousarray(np.asarray(a, dtype=np.float32))).to(self.dev)
+        emb = t(p[s.emb_name]).reshape(s.table_rows, s.k)
+        first = t(p[s.first_name]).reshape(s.table_rows) if s.has_first else None
+        self.h.call("ctr_table_pack", st, ptr(emb), ptr(first), s.table_rows, s.k, s.table_stride, ptr(self.table))
+        for name, shp in self.dense_shapes:
+            a = np.asarray(p[name], dtype=np.float32).reshape(shp)
+            if name == "deep_0":
+                a = a[s.deep0_perm(), :]
+            if s.head == "deepfm" and name == s.head_w_name:
+                perm = np.concatenate([s.head_fm_perm(), s.n_fm + np.arange(s.hidden[-1])])
+                a = a[perm, :]
+            self.view(name).copy_(t(a).reshape(-1))
+        torch.cuda.current_stream(self.dev).synchronize()
+        self._refresh_transposes()
+
+    def set_dense_weights(self, p: Dict[str, np.ndarray]) -> None:
+        """dense variables only (reference names/shapes); the table is left as is"""
+        s = self.spec
+        for name, shp in self.dense_shapes:
+            a = np.asarray(p[name], dtype=np.float32).reshape(shp)
+            if name == "deep_0":
+                a = a[s.deep0_perm(), :]
+            if s.head == "deepfm" and name == s.head_w_name:
+                a = a[np.concatenate([s.head_fm_perm(), s.n_fm + np.arange(s.hidden[-1])]), :]
+            self.view(name).copy_(torch.from_numpy(np.ascontiguousarray(a)).reshape(-1).to(self.dev))
+        self._refresh_transposes()
+
+    def init_table_on_device(self, seed: int = 2019, chunk_rows: int = 8 << 20) -> None:
+        """reference initial distributions drawn directly in HBM (tables too large to stage on the
+        host): embeddings ~ N(0, 0.01^2) (xavier-uniform for weight_mat), first-order ~ U(0,1)"""
+        s = self.spec
+        g = torch.Generator(device=self.dev); g.manual_seed(seed)
+        lim = math.sqrt(6.0 / (s.table_rows + s.k))
+        for r0 in range(0, s.table_rows, chunk_rows):
+            r1 = min(s.table_rows, r0 + chunk_rows)
+            blk = self.table[r0:r1]
+            if s.emb_name == "weight_mat":
+                blk[:, :s.k] = (torch.rand(r1 - r0, s.k, generator=g, device=self.dev) * 2 - 1) * lim
+            else:
+                blk[:, :s.k] = torch.randn(r1 - r0, s.k, generator=g, device=self.dev) * 0.01
+            if s.has_first:
+                blk[:, s.k] = torch.rand(r1 - r0, generator=g, device=self.dev)
+
+    def get_weights(self) -> Dict[str, np.ndarray]:
+        s, st = self.spec, self._stream()
+        out: Dict[str, np.ndarray] = {}
+        emb = torch.empty(s.table_rows, s.k, dtype=torch.float32, device=self.dev)
+        first = torch.empty(s.table_rows, dtype=torch.float32, device=self.dev) if s.has_first else None
+        self.h.call("ctr_table_unpack", st, ptr(self.table), s.table_rows, s.k, s.table_stride, ptr(emb), ptr(first))
+        out[s.emb_name] = emb.cpu().numpy()
+        if s.has_first:
+            out[s.first_name] = first.cpu().numpy().reshape(-1, 1)
+        for name, shp in self.dense_shapes:
+            a = self.view(name).cpu().numpy().reshape(shp).copy()
+            if name == "deep_0":
+                inv = np.empty_like(s.deep0_perm()); inv[s.deep0_perm()] = np.arange(len(inv))
+                a = a[inv, :]
+            if s.head == "deepfm" and name == s.head_w_name:
+                perm = np.concatenate([s.head_fm_perm(), s.n_fm + np.arange(s.hidden[-1])])
+                inv = np.empty_like(perm); inv[perm] = np.arange(len(perm))
+                a = a[inv, :]
+            out[name] = a
+        return out
+
+    def _refresh_transposes(self) -> None:
+        if self.wt is None:
+            return
+        st = self._stream()
+        for i, (k_, h_) in enumerate(self._layer_dims()):
+            self.h.call("ctr_transpose", st, ptr(self._w(i)), k_, h_, ptr(self.wt[i]))
+
+    # ---- batch upload ------------------------------------------------------------------------------
+    def load_batch(self, batch: Dict, non_blocking: bool = True) -> int:
+        """Copy one batch (host or device arrays/tensors, reference key names) into the device
+        buffers.  Returns B (may be < max_batch for the short last batch, models/deepfm.py:178)."""
+        s = self.spec
+
+        def as_t(x, dtype):
+            if isinstance(x, torch.Tensor):
+                return x if x.dtype == dtype else x.to(dtype)
+            return torch.as_tensor(np.asarray(x)).to(dtype)
+        cate = as_t(batch["cate_feats"], self.id_torch)
+        B = int(cate.shape[0])
+        if B > self.Bmax:
+            raise ValueError("batch of %d exceeds max_batch %d" % (B, self.Bmax))
+        if s.ids_ld:
+            if cate.shape[1] != s.ids_ld:
+                raise ValueError("cate_feats has %d columns, model expects %d" % (cate.shape[1], s.ids_ld))
+            self.ids[:B].copy_(cate, non_blocking=non_blocking)
+        cont = as_t(batch["cont_feats"], torch.float32)
+        if s.alg == "dnn" and "vector_feats" in batch and batch["vector_feats"] is not None:
+            vec = as_t(batch["vector_feats"], torch.float32)
+            if vec.shape[1] and cont.shape[1] + vec.shape[1] == s.C:
+                cont = torch.cat([cont, vec.to(cont.device)], dim=1)
+        if s.C:
+            if cont.shape[1] != s.C:
+                raise ValueError("cont_feats has %d columns, model expects %d" % (cont.shape[1], s.C))
+            self.cont[:B].copy_(cont, non_blocking=non_blocking)
+        if s.V:
+            self.vec[:B].copy_(as_t(batch["vector_feats"], torch.float32), non_blocking=non_blocking)
+        if s.head == "wdl":
+            self.wide[:B].copy_(as_t(batch["wide_feats"], self.id_torch), non_blocking=non_blocking)
+        lab = batch.get("label", batch.get("labels"))
+        if lab is not None:
+            self.label[:B].copy_(as_t(lab, torch.float32).reshape(-1), non_blocking=non_blocking)
+        self.last_batch = B
+        return B
+
+    # ---- forward -------------------------------------------------------------------------------------
+    def forward(self, B: int, with_loss: bool) -> None:
+        s, st, h = self.spec, self._stream(), self.h
+        cfg = self._cfg(B)
+        if s.Fm:
+            h.call("ctr_pooled_gather_fwd", st, cfg, ptr(self.table), ptr(self.ids), ptr(self.multi_start), None,
+                   ptr(self.x0), ptr(self.pooled_first), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first))
+        cont_rows = self.table[s.cont_base:] if (s.use_fm and s.fm_cont) else None
+        h.call("ctr_fm_gather_fwd", st, cfg, ptr(self.table), ptr(self.ids), 0, ptr(self.cont), ptr(self.vec),
+               ptr(cont_rows), ptr(self.pooled_first), ptr(self.x0), ptr(self.fm), ptr(self.sum_e))
+        x, ldx = self.x0, s.x0_ld
+        for i, (k_, h_) in enumerate(self._layer_dims()):
+            h.call("ctr_mlp_fwd", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self._w(i)),
+                   ptr(self.wt[i]) if self.wt is not None else None, ptr(self._b(i)), 1, 1.0, 0, ptr(self.acts[i]), h_)
+            x, ldx = self.acts[i], h_
+        w_fm, w_deep, bias = self._head_parts()
+        extra = None
+        if s.head == "wdl":
+            h.call("ctr_scalar_gather_sum", st, ptr(self.view("wdl_weights")), ptr(self.wide), self.id_bytes, B,
+                   s.wide_fields, ptr(self.wide_sum))
+            extra = self.wide_sum
+        lab = self.label if with_loss else None
+        h.call("ctr_head_fwd", st, B, ptr(self.fm), s.fm_ld, s.n_fm, ptr(w_fm), ptr(x), ldx, s.hidden[-1], ptr(w_deep),
+               ptr(extra), ptr(bias), ptr(lab), ptr(self.logit), ptr(self.score),
+               ptr(self.dlogit) if with_loss else None, ptr(self.loss) if with_loss else None, ptr(self.ws),
+               self.ws.numel())
+
+    def _reg_loss(self) -> torch.Tensor:
+        """regulariser terms of the reported loss (models/deepfm.py:155-156, models/wdl.py:268-275,
+        models/dnn.py:88-90): one deterministic reduction per regulariser group of the flat buffer."""
+        s, st = self.spec, self._stream()
+        total = None
+        for gi, mode, scale in ((1, 1, 0.5 * s.l2_reg), (2, 2, s.l2_reg)):
+            a, b = self.groups[gi]
+            if b > a:
+                out = self.reg_terms[gi:gi + 1]
+                self.h.call("ctr_reduce", st, ptr(self.theta[a:b]), b - a, mode, ptr(out), ptr(self.ws), self.ws.numel())
+                total = out * scale if total is None else total + out * scale
+        return total
+
+    # ---- backward + update -------------------------------------------------------------------------
+    def _adam_hp(self) -> AdamHP:
+        """TF1 Adam step size (adam.py): lr from exponential_decay(staircase) on the PRE-increment
+        global_step (models/deepfm.py:159-162), then lr_t = lr*sqrt(1-b2^t)/(1-b1^t)."""
+        lr = self.lr0 * self.decay_rate ** math.floor(self.global_step / self.decay_steps)
+        lr_t = lr * math.sqrt(1.0 - self.beta2_power) / (1.0 - self.beta1_power)
+        return AdamHP(lr_t=lr_t, beta1=ADAM_BETA1, beta2=ADAM_BETA2, eps=ADAM_EPS)
+
+    def backward_and_update(self, B: int) -> None:
+        s, st, h = self.spec, self._stream(), self.h
+        cfg = self._cfg(B)
+        L = len(s.hidden)
+        dims = self._layer_dims()
+        H = s.hidden[-1]
+        g_fm, g_deep, g_bias = self._head_parts(self.grad)
+        w_fm, w_deep, _ = self._head_parts()
+        last = self.acts[-1]
+        ws, wsn = ptr(self.ws), self.ws.numel()
+        if s.head == "wdl":
+            self.view("wdl_weights", self.grad).zero_()
+        # head gradients: d w = sum_b dlogit[b] * feats_input[b, :]  (models/deepfm.py:130,143)
+        if s.n_fm:
+            h.call("ctr_colsum", st, ptr(self.fm), s.fm_ld, B, s.n_fm, ptr(self.dlogit), ptr(g_fm), ws, wsn)
+        h.call("ctr_colsum", st, ptr(last), H, B, H, ptr(self.dlogit), ptr(g_deep), ws, wsn)
+        h.call("ctr_reduce", st, ptr(self.dlogit), B, 0, ptr(g_bias), ws, wsn)
+        if s.head == "wdl":
+            self._wdl_wide_grad(B)
+        # through the last ReLU
+        dz = self.dz[0]
+        h.call("ctr_head_bwd_deep", st, B, H, ptr(self.dlogit), ptr(w_deep), ptr(last), H, ptr(dz), H)
+        cur = 0
+        for i in range(L - 1, -1, -1):
+            k_, h_ = dims[i]
+            x, ldx = (self.acts[i - 1], s.hidden[i - 1]) if i > 0 else (self.x0, s.x0_ld)
+            h.call("ctr_mlp_bwd_weight", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self.dz[cur]), h_,
+                   ptr(self._w(i, self.grad)), ptr(self._b(i, self.grad)), ws, wsn)
+            if i > 0:
+                h.call("ctr_mlp_bwd_data", st, self.prec, B, k_, h_, ptr(self.dz[cur]), h_, ptr(self._w(i)), ptr(x),
+                       ldx, 1.0, ptr(self.dz[cur ^ 1]), k_)
+                cur ^= 1
+            elif s.E:
+                # only the embedding columns of X0 carry parameters: canonical order puts them first
+                h.call("ctr_mlp_bwd_data", st, self.prec, B, s.E, h_, ptr(self.dz[cur]), h_, ptr(self._w(0)), None, 0,
+                       1.0, ptr(self.dx0), self.dx0_ld)
+        hp = self._adam_hp()
+        # ---- sparse side: sort -> runs -> partials -> Adam on touched rows ------------------------------
+        if s.ids_ld:
+            n = B * s.ids_ld + self.n_extra
+            key_bits = max(1, int(s.table_rows - 1).bit_length())
+            h.call("ctr_sort_ids", st, ptr(self.ids), self.id_bytes, B, s.ids_ld, 0, s.ids_ld, 0, int(s.zero_row0),
+                   s.cont_base, self.n_extra, 1, 0, key_bits, ptr(self.keys), ptr(self.perm), ws, wsn)
+            h.call("ctr_unique_segments", st, ptr(self.keys), n, ptr(self.uniq), ptr(self.seg_start), ptr(self.uidx),
+                   ptr(self.n_unique), ws, wsn)
+            if self.n_extra:
+                h.call("ctr_fm_cont_bwd", st, cfg, ptr(self.cont), ptr(self.table[s.cont_base:]), ptr(self.sum_e),
+                       ptr(self.dlogit), ptr(w_fm), ptr(self.cont_grad), ws, wsn)
+            h.call("ctr_embed_bwd_partials", st, cfg, ptr(self.keys), ptr(self.perm), ptr(self.uidx), n,
+                   ptr(self.field_of_slot), ptr(self.x0), ptr(self.dx0), self.dx0_ld, ptr(self.sum_e), ptr(self.dlogit),
+                   ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.part))
+            h.call("ctr_adam_rows", st, ptr(self.uniq), ptr(self.n_unique), n, 0, ptr(self.part), ptr(self.seg_start),
+                   s.grad_stride, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
+                   s.table_rows, ptr(self.touched), hp)
+        if self.adam_mode == "tf_dense":
+            # TF1 Adam moves EVERY row each step (m, v decay; theta -= lr_t*m/(sqrt(v)+eps)) -- exact mode
+            h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
+                   self.table.numel(), 0.0, 0.0, ptr(self.touched), s.table_stride, hp)
+        # ---- dense side: one Adam launch per regulariser group ---------------------------------------------
+        for gi, (l2, l1) in enumerate(((0.0, 0.0), (s.l2_reg, 0.0), (0.0, s.l2_reg))):
+            a, b = self.groups[gi]
+            if b > a:
+                h.call("ctr_adam_dense", st, ptr(self.theta[a:b]), ptr(self.m[a:b]), ptr(self.v[a:b]),
+                       ptr(self.grad[a:b]), b - a, l2, l1, None, 1, hp)
+        self._refresh_transposes()
+        self.beta1_power *= ADAM_BETA1
+        self.beta2_power *= ADAM_BETA2
+        self.global_step += 1
+
+    def _wdl_wide_grad(self, B: int) -> None:
+        raise NotImplementedError("wdl training lands with the scalar segment-gradient kernel")
+
+    # ---- public step API -------------------------------------------------------------------------------
+    def train_step(self, batch: Optional[Dict] = None) -> torch.Tensor:
+        """One `sess.run([loss, optimizer])` (models/deepfm.py:181).  Returns the loss as a device
+        scalar tensor (log-loss + regulariser); call .item() to read it."""
+        if not self.train_mode:
+            raise _lib.CtrError("engine was created with train=False")
+        B = self.load_batch(batch) if batch is not None else self.last_batch
+        self.forward(B, with_loss=True)
+        reg = self._reg_loss()
+        total = self.loss.clone() if reg is None else self.loss + reg
+        self.backward_and_update(B)
+        return total
+
+    def predict(self, batch: Optional[Dict] = None) -> torch.Tensor:
+        """`sess.run("score:0")` (models/deepfm.py:250): scores [B] on the device."""
+        B = self.load_batch(batch) if batch is not None else self.last_batch
+        self.forward(B, with_loss=False)
+        return self.score[:B]
+
+    def auc(self, scores: torch.Tensor, labels: torch.Tensor) -> float:
+        """roc_auc_score(labels, scores) on the device (models/deepfm.py:231)."""
+        n = int(scores.numel())
+        sc = scores.reshape(-1).to(self.dev, torch.float32).contiguous()
+        lb = labels.reshape(-1).to(self.dev, torch.float32).contiguous()
+        wsn = self.h.query("ctr_auc_ws_bytes", n)
+        ws = torch.empty(wsn, dtype=torch.uint8, device=self.dev)
+        out = torch.zeros(1, dtype=torch.float64, device=self.dev)
+        self.h.call("ctr_auc", self._stream(), ptr(sc), ptr(lb), n, ptr(out), ptr(ws), wsn)
+        return float(out.item())

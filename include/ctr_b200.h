@@ -80,6 +80,8 @@ int  ctr_create(int device, ctr_handle** out);
 int  ctr_destroy(ctr_handle* h);
 const char* ctr_last_error(ctr_handle* h);
 int  ctr_sm_count(ctr_handle* h);
+/* kernels launched through this handle since ctr_create (bench.py's gpu_launches) */
+int64_t ctr_launch_count(ctr_handle* h);
 /* 1 if the tcgen05/TMA TF32 GEMM path can run on this device (sm_100) */
 int  ctr_has_tcgen05(ctr_handle* h);
 
@@ -183,7 +185,10 @@ int ctr_reduce(ctr_handle* h, ctr_stream s, const float* x, int64_t n, int mode,
  *   ids are read as a [rows, ld] matrix restricted to columns [col0, col0+ncols). */
 int64_t ctr_sort_ws_bytes(ctr_handle* h, int64_t n);
 int ctr_sort_ids(ctr_handle* h, ctr_stream s, const void* ids, int id_bytes, int64_t rows, int64_t ld,
-                 int col0, int ncols, int64_t id_offset, int drop_zero, int n_shards, int local_bits,
+                 int col0, int ncols, int64_t id_offset, int drop_zero,
+                 int64_t extra_base, int n_extra /* appends ids extra_base+c with perm = rows*ld + c: the
+                 continuous-field rows, so their gradient rides the same segment-reduce */,
+                 int n_shards, int local_bits,
                  int key_bits, uint32_t* keys_out, uint32_t* perm_out, void* ws, int64_t ws_bytes);
 /* generic stable pair sort (also used by ctr_auc) */
 int ctr_sort_pairs(ctr_handle* h, ctr_stream s, uint32_t* keys, uint32_t* vals, int64_t n, int key_bits,
@@ -213,6 +218,8 @@ int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg
                            const float* x0, const float* dx0, int64_t dx0_ld, const float* sum_e, const float* dlogit,
                            const float* w_fm /*[Fc+Fm+C+k] internal order*/,
                            const float* inv_cnt_emb, const float* inv_cnt_first,
+                           const float* cont_grad /*[C, grad_stride] or NULL: gradient of the appended
+                           continuous-field entries (perm >= B*ids_ld), from ctr_fm_cont_bwd */,
                            float* part);
 /* grads[u, :] = sum of the partials of run u, in chunk order (deterministic) */
 int ctr_embed_bwd_finalize(ctr_handle* h, ctr_stream s, const uint32_t* seg_start, const uint32_t* n_unique,
@@ -225,8 +232,7 @@ int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const
                     const float* cont_rows, const float* sum_e, const float* dlogit, const float* w_fm,
                     float* cont_grad /*[C, grad_stride]*/, void* ws, int64_t ws_bytes);
 
-/* TF1 Adam on the rows named by row_ids (unique):  g = grads[u] (+ extra_grad[row - extra_base] when
- * the row lies in [extra_base, extra_base+extra_n), which also sets extra_hit[row - extra_base]);
+/* TF1 Adam on the rows named by row_ids (unique):  g = grads[u];
  *   m <- b1*m + (1-b1) g ; v <- b2*v + (1-b2) g^2 ; theta <- theta - lr_t * m / (sqrt(v) + eps)
  * rows with id 0xFFFFFFFF are skipped.  `touched` ([R] bytes or NULL) is set to 1 for every updated
  * row (used by the exact dense sweep).  row = (key & local_mask) when local_bits > 0. */
@@ -236,7 +242,6 @@ int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const ui
                   partials buffer of ctr_embed_bwd_partials and the run sums are formed inline (fused finalize) */,
                   int grad_stride, int width,
                   float* table, float* m, float* v, int table_stride, int64_t table_rows,
-                  const float* extra_grad, int64_t extra_base, int extra_n, uint8_t* extra_hit,
                   uint8_t* touched, const ctr_adam_hp* hp);
 /* dense TF1 Adam over n floats: g_eff = (g ? g[i] : 0) + l2*theta + l1*sign(theta).
  * skip ([n/skip_group] bytes or NULL): elements whose group flag is 1 are left alone and the flag is

@@ -1,0 +1,70 @@
+"""Shared test helpers: model configurations (BASELINE.json configs at oracle-friendly sizes),
+seeded batches and the oracle<->engine glue."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from oracle import ctr_oracle as O
+from deep_learning_b200 import data as D
+
+
+def hp_c1(**kw):
+    """configs[0]: models/deepfm.py, 10 cont + 20 single-valued cate, k=8, MLP 256-128, batch 256"""
+    hp = O.HParams(hidden_units=[256, 128], batch_size=256, embedding_size=8, cont_field_size=10,
+                   cate_field_size=20, cate_feats_size=10000, l2_reg=1e-5, learning_rate=1e-3)
+    for k, v in kw.items():
+        setattr(hp, k, v)
+    return hp
+
+
+def hp_multi(B=512, **kw):
+    """configs[1] at reduced batch: models/deepfm_multi.py, 13 cont + 20 single + 6 multi (top_n 16), k=16"""
+    ranges, s = [], 0
+    for j in range(6):
+        ranges.append([s, s + 16, "m%d" % j]); s += 16
+    hp = O.HParams(hidden_units=[512, 256, 128], batch_size=B, embedding_size=16, cont_field_size=13,
+                   cate_field_size=20, cate_feats_size=20001, multi_feats_size=96, multi_field_size=6,
+                   multi_feats_range=ranges, l2_reg=1e-5)
+    for k, v in kw.items():
+        setattr(hp, k, v)
+    return hp
+
+
+def hp_criteo(B=1024, rows=50000, **kw):
+    """configs[2..4] shape at reduced batch/rows: 13 cont + 26 cate, k=16, MLP 400-400-400"""
+    hp = O.HParams(hidden_units=[400, 400, 400], batch_size=B, embedding_size=16, cont_field_size=13,
+                   cate_field_size=26, cate_feats_size=rows, cate_index_size=rows, wide_field_size=26, l2_reg=1e-5)
+    for k, v in kw.items():
+        setattr(hp, k, v)
+    return hp
+
+
+def make_batch(alg, hp, seed, B=None, dist="zipf", id_dtype=None):
+    B = B or hp.batch_size
+    multi = alg in ("deepfm_multi", "dnn_multi")
+    reserve = multi
+    n_single_rows = hp.cate_feats_size - (1 if reserve else 0)
+    if multi:
+        Fm = hp.multi_field_size
+        multi_rows = [max(2, n_single_rows // (4 * Fm))] * Fm
+        sizes = D.field_sizes(n_single_rows - sum(multi_rows), hp.cate_field_size)
+        tops = [int(r[1]) - int(r[0]) for r in hp.multi_feats_range]
+    else:
+        sizes, multi_rows, tops = D.field_sizes(n_single_rows, hp.cate_field_size), [], []
+    if id_dtype is None:
+        id_dtype = torch.int64 if multi else torch.int32
+    b = D.synthetic_batch(B, hp.cont_field_size, hp.cate_field_size, sizes, seed, V=hp.vector_feats_size,
+                          multi_top_n=tops, multi_sizes=multi_rows, wide=hp.wide_field_size if alg == "wdl" else 0,
+                          dist=dist, reserve_zero=reserve, id_dtype=id_dtype)
+    return b
+
+
+def oracle_batch(b, dtype):
+    return {k: (v.to(dtype) if v.is_floating_point() else v.long()) for k, v in b.items()}
+
+
+def rel_err(a, b):
+    """max |a-b| / max(|b|) : relative to the tensor's scale (1e-5 FP32 / 2e-3 TF32 bars, BASELINE.json)"""
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b)) / max(float(np.max(np.abs(b))), 1e-30))

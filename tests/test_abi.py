@@ -1,0 +1,75 @@
+"""CPU: the C-ABI library builds, loads and exports every symbol include/ctr_b200.h declares, with
+prototypes that match the ctypes table; the product path refuses to run without a GPU."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_protos():
+    src = open(os.path.join(ROOT, "include", "ctr_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return re.findall(r"\b(int64_t|int|const char\*)\s+(ctr_\w+)\s*\(([^;{]*?)\)\s*;", src, flags=re.S)
+
+
+def test_library_exports_every_declared_symbol(lib_built):
+    from deep_learning_b200 import _lib
+    lib = _lib.load()
+    names = [n for _, n, _ in _header_protos()]
+    assert len(names) >= 35
+    for n in names:
+        assert hasattr(lib, n), n
+    assert set(names) == set(_lib.EXPORTS)
+    assert lib.ctr_abi_version() == 1
+    assert lib.ctr_sizeof_embed_cfg() == C.sizeof(_lib.EmbedCfg) == 80
+
+
+def test_ctypes_prototypes_match_header(lib_built):
+    from deep_learning_b200 import _lib
+
+    def ctype(a):
+        a = a.strip()
+        if a in ("void", ""):
+            return None
+        if "*" in a:
+            if "ctr_embed_cfg" in a:
+                return _lib._P_CFG
+            if "ctr_adam_hp" in a:
+                return _lib._P_HP
+            if "ctr_handle**" in a.replace(" ", ""):
+                return C.POINTER(C.c_void_p)
+            return C.c_void_p
+        ty = " ".join(a.split()[:-1])
+        return {"int": C.c_int32, "int64_t": C.c_int64, "uint64_t": C.c_uint64, "float": C.c_float,
+                "ctr_stream": C.c_void_p, "int32_t": C.c_int32}[ty]
+    for ret, name, args in _header_protos():
+        want = [t for t in (ctype(x) for x in args.split(",")) if t is not None]
+        res, have = _lib._PROTOS[name]
+        assert want == (have or []), name
+        assert res == {"int": C.c_int32, "int64_t": C.c_int64, "const char*": C.c_char_p}[ret], name
+
+
+def test_no_cpu_fallback(lib_built):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from deep_learning_b200 import _lib
+    from deep_learning_b200.engine import CtrEngine
+    from deep_learning_b200.spec import spec_from_hparams
+    import ctr_helpers as H
+    with pytest.raises(_lib.CtrError):
+        CtrEngine(spec_from_hparams("deepfm", H.hp_c1()), 8)
+    with pytest.raises(_lib.CtrError):
+        _lib.Handle(0)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "deep_learning_b200")
+    for dp, _, fs in os.walk(pkg):
+        for f in fs:
+            if f.endswith(".py"):
+                txt = open(os.path.join(dp, f)).read()
+                assert "oracle" not in txt.replace("no oracle", ""), os.path.join(dp, f)

@@ -1,0 +1,138 @@
+"""-m gpu: each C-ABI entry point against numpy / the oracle on seeded inputs (bit-exact for integer
+work, stated tolerance for floating point)."""
+import numpy as np
+import pytest
+import torch
+
+import ctr_helpers as H
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def hd():
+    from deep_learning_b200 import _lib
+    assert torch.cuda.is_available()
+    return _lib.Handle(0)
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _u32(t):
+    return t.cpu().numpy().view(np.uint32)
+
+
+@pytest.mark.parametrize("n,bits", [(1, 8), (31, 32), (4096, 16), (4097, 24), (100003, 27), (1 << 20, 32)])
+def test_sort_pairs_stable_bit_exact(hd, n, bits):
+    from deep_learning_b200._lib import ptr
+    rng = np.random.RandomState(n)
+    hi = (1 << bits) - 1
+    keys = rng.randint(0, min(hi, 5000) + 1, size=n).astype(np.uint32) if n % 2 else rng.randint(0, hi + 1, size=n, dtype=np.int64).astype(np.uint32)
+    vals = np.arange(n, dtype=np.uint32)
+    k = torch.from_numpy(keys.view(np.int32)).cuda(); v = torch.from_numpy(vals.view(np.int32)).cuda()
+    wsn = hd.query("ctr_sort_ws_bytes", n)
+    ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
+    hd.call("ctr_sort_pairs", _st(), ptr(k), ptr(v), n, bits, ptr(ws), wsn)
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(_u32(k), keys[order])
+    assert np.array_equal(_u32(v), vals[order])       # stability == bit-exact permutation
+
+
+@pytest.mark.parametrize("n", [1, 2047, 2048, 2049, 70001])
+def test_unique_segments_bit_exact(hd, n):
+    from deep_learning_b200._lib import ptr
+    rng = np.random.RandomState(n)
+    keys = np.sort(rng.randint(0, max(2, n // 3), size=n).astype(np.uint32))
+    k = torch.from_numpy(keys.view(np.int32)).cuda()
+    uniq, uidx = torch.zeros(n, dtype=torch.int32, device="cuda"), torch.zeros(n, dtype=torch.int32, device="cuda")
+    seg = torch.zeros(n + 2, dtype=torch.int32, device="cuda"); nu = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ws = torch.zeros(4 * (n // 2048 + 8), dtype=torch.uint8, device="cuda")
+    hd.call("ctr_unique_segments", _st(), ptr(k), n, ptr(uniq), ptr(seg), ptr(uidx), ptr(nu), ptr(ws), ws.numel())
+    ru, rstart, rinv = np.unique(keys, return_index=True, return_inverse=True)
+    U = int(nu.item())
+    assert U == len(ru)
+    assert np.array_equal(_u32(uniq)[:U], ru)
+    assert np.array_equal(_u32(seg)[:U + 1], np.r_[rstart, n].astype(np.uint32))
+    assert np.array_equal(_u32(uidx), rinv.astype(np.uint32))
+
+
+def test_sort_ids_sharded_keys_and_counts(hd):
+    """owner-major key = (id % N) << bits | id // N; dropped zeros; shard counts (bit-exact shard map)"""
+    from deep_learning_b200._lib import ptr
+    rng = np.random.RandomState(7)
+    B, F, N, bits = 300, 7, 4, 20
+    ids = rng.randint(0, 5000, size=(B, F)).astype(np.int64)
+    ids[rng.rand(B, F) < 0.2] = 0
+    d = torch.from_numpy(ids).cuda()
+    n = B * F + 3
+    keys, perm = (torch.zeros(n, dtype=torch.int32, device="cuda") for _ in range(2))
+    wsn = hd.query("ctr_sort_ws_bytes", n); ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
+    hd.call("ctr_sort_ids", _st(), ptr(d), 8, B, F, 0, F, 0, 1, 4000, 3, N, bits, 32, ptr(keys), ptr(perm), ptr(ws), wsn)
+    flat = np.r_[ids.reshape(-1), 4000 + np.arange(3)]
+    pad = np.r_[ids.reshape(-1) == 0, np.zeros(3, bool)]
+    ref = np.where(pad, 0xFFFFFFFF, ((flat % N) << bits) | (flat // N)).astype(np.uint32)
+    order = np.argsort(ref, kind="stable")
+    assert np.array_equal(_u32(keys), ref[order])
+    assert np.array_equal(_u32(perm), np.arange(n, dtype=np.uint32)[order])
+    uniq, uidx = torch.zeros(n, dtype=torch.int32, device="cuda"), torch.zeros(n, dtype=torch.int32, device="cuda")
+    seg = torch.zeros(n + 2, dtype=torch.int32, device="cuda"); nu = torch.zeros(1, dtype=torch.int32, device="cuda")
+    hd.call("ctr_unique_segments", _st(), ptr(keys), n, ptr(uniq), ptr(seg), ptr(uidx), ptr(nu), ptr(ws), wsn)
+    cnt = torch.zeros(N, dtype=torch.int32, device="cuda")
+    hd.call("ctr_shard_counts", _st(), ptr(uniq), ptr(nu), N, bits, ptr(cnt))
+    ru = np.unique(ref); ru = ru[ru != 0xFFFFFFFF]
+    assert np.array_equal(_u32(cnt), np.bincount(ru >> bits, minlength=N).astype(np.uint32))
+
+
+@pytest.mark.parametrize("n,ties", [(2, False), (1000, True), (65536, False), (200001, True)])
+def test_auc_matches_sklearn(hd, n, ties):
+    from sklearn.metrics import roc_auc_score
+    from deep_learning_b200._lib import ptr
+    rng = np.random.RandomState(n)
+    y = (rng.rand(n) < 0.3).astype(np.float32); y[0], y[1] = 1.0, 0.0
+    s = rng.randn(n).astype(np.float32)
+    if ties:
+        s = np.round(s, 1); s[::7] = 0.0; s[3::11] = -0.0
+    wsn = hd.query("ctr_auc_ws_bytes", n); ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
+    out = torch.zeros(1, dtype=torch.float64, device="cuda")
+    hd.call("ctr_auc", _st(), ptr(torch.from_numpy(s).cuda()), ptr(torch.from_numpy(y).cuda()), n, ptr(out), ptr(ws), wsn)
+    assert abs(out.item() - roc_auc_score(y, s)) < 1e-12
+
+
+@pytest.mark.parametrize("B,K,N", [(1, 3, 5), (257, 170, 256), (1000, 429, 400), (300, 400, 1)])
+def test_mlp_fp32_gemms(hd, B, K, N):
+    """FP32 SIMT path vs fp64: forward (bias+relu), data gradient (mask) and weight gradient; 1e-5."""
+    from deep_learning_b200._lib import ptr
+    g = torch.Generator().manual_seed(B * 1000 + K)
+    X = torch.randn(B, K, generator=g); W = torch.randn(K, N, generator=g) / K ** 0.5; b = torch.randn(N, generator=g)
+    dZ = torch.randn(B, N, generator=g); mask = torch.randn(B, K, generator=g)
+    Xc, Wc, bc, dZc, mc = (t.cuda() for t in (X, W, b, dZ, mask))
+    Y = torch.zeros(B, N, device="cuda")
+    hd.call("ctr_mlp_fwd", _st(), 0, B, K, N, ptr(Xc), K, ptr(Wc), None, ptr(bc), 1, 1.0, 0, ptr(Y), N)
+    ref = torch.relu(X.double() @ W.double() + b.double())
+    assert H.rel_err(Y.cpu(), ref) < 1e-5
+    dX = torch.zeros(B, K, device="cuda")
+    hd.call("ctr_mlp_bwd_data", _st(), 0, B, K, N, ptr(dZc), N, ptr(Wc), ptr(mc), K, 1.0, ptr(dX), K)
+    ref = (dZ.double() @ W.double().T) * (mask > 0).double()
+    assert H.rel_err(dX.cpu(), ref) < 1e-5
+    wsn = hd.query("ctr_mlp_bwd_weight_ws_bytes", 0, B, K, N); ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
+    dW = torch.zeros(K, N, device="cuda"); db = torch.zeros(N, device="cuda")
+    hd.call("ctr_mlp_bwd_weight", _st(), 0, B, K, N, ptr(Xc), K, ptr(dZc), N, ptr(dW), ptr(db), ptr(ws), wsn)
+    assert H.rel_err(dW.cpu(), X.double().T @ dZ.double()) < 1e-5
+    assert H.rel_err(db.cpu(), dZ.double().sum(0)) < 1e-5
+
+
+def test_table_pack_roundtrip_and_transpose(hd):
+    from deep_learning_b200._lib import ptr
+    R, k, stride = 1000, 16, 24
+    emb = torch.randn(R, k, device="cuda"); first = torch.randn(R, device="cuda")
+    tab = torch.full((R, stride), 7.0, device="cuda")
+    hd.call("ctr_table_pack", _st(), ptr(emb), ptr(first), R, k, stride, ptr(tab))
+    assert torch.equal(tab[:, :k], emb) and torch.equal(tab[:, k], first) and float(tab[:, k + 1:].abs().max()) == 0.0
+    e2, f2 = torch.zeros_like(emb), torch.zeros_like(first)
+    hd.call("ctr_table_unpack", _st(), ptr(tab), R, k, stride, ptr(e2), ptr(f2))
+    assert torch.equal(e2, emb) and torch.equal(f2, first)
+    W = torch.randn(429, 400, device="cuda"); Wt = torch.zeros(400, 429, device="cuda")
+    hd.call("ctr_transpose", _st(), ptr(W), 429, 400, ptr(Wt))
+    assert torch.equal(Wt, W.T.contiguous())

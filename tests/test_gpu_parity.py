@@ -1,0 +1,129 @@
+"""-m gpu: model-level parity of the CUDA path against the oracle (fp64 restatement of the reference
+graph) on identical injected parameters and seeded batches.  Bars (BASELINE.json north_star): logits,
+loss and updated parameters within 1e-5 relative on the FP32 path, 2e-3 on the TF32 path."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import ctr_oracle as O
+import ctr_helpers as H
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"fp32": 1e-5, "tf32": 2e-3}
+
+
+def _engine(alg, hp, params, B, precision="fp32", adam_mode="tf_dense"):
+    from deep_learning_b200.engine import CtrEngine
+    from deep_learning_b200.spec import spec_from_hparams
+    eng = CtrEngine(spec_from_hparams(alg, hp), B, learning_rate=hp.learning_rate,
+                    decay_steps=hp.learning_rate_decay_steps, decay_rate=hp.learning_rate_decay_rate,
+                    precision=precision, adam_mode=adam_mode)
+    eng.set_weights({k: v.numpy() for k, v in params.items()})
+    return eng
+
+
+def _run_parity(alg, hp, steps, precision="fp32", adam_mode="tf_dense", B=None, dist="zipf", id_dtype=None):
+    tol = TOL[precision]
+    B = B or hp.batch_size
+    p = O.init_params(alg, hp, seed=2019, dtype=torch.float64)
+    st = O.adam_init(p)
+    eng = _engine(alg, hp, p, hp.batch_size, precision, adam_mode)
+    # weights survive the round trip through the device layouts bit-exactly
+    back = eng.get_weights()
+    for n in p:
+        assert np.array_equal(back[n].reshape(-1), p[n].float().numpy().reshape(-1)), n
+    for step in range(steps):
+        b = H.make_batch(alg, hp, seed=2020 + step, B=B, dist=dist, id_dtype=id_dtype)
+        ob = H.oracle_batch(b, torch.float64)
+        # forward / predict
+        out_ref, score_ref = O.FORWARD[alg](p, ob, hp)
+        score = eng.predict(b).cpu().numpy()
+        assert H.rel_err(eng.logit[:B].cpu().numpy(), out_ref.numpy().reshape(-1)) < tol, "logit step %d" % step
+        assert np.max(np.abs(score - score_ref.numpy().reshape(-1))) < tol, "score step %d" % step
+        # train step
+        loss_ref, p = O.train_step(alg, p, st, ob, hp, adam_mode=adam_mode)
+        loss = float(eng.train_step(b).item())
+        assert abs(loss - float(loss_ref)) < tol * max(1.0, abs(float(loss_ref))), "loss step %d" % step
+        got = eng.get_weights()
+        for n in p:
+            err = H.rel_err(got[n].reshape(-1), p[n].numpy().reshape(-1))
+            assert err < tol, "param %s step %d: rel err %.3g" % (n, step, err)
+    return eng
+
+
+def test_deepfm_c1_three_steps_tf_exact_adam():
+    """configs[0]: models/deepfm.py, B=256, 10 cont + 20 cate, k=8, MLP 256-128; TF1 dense Adam semantics"""
+    _run_parity("deepfm", H.hp_c1(), steps=3)
+
+
+def test_deepfm_c1_lazy_adam():
+    _run_parity("deepfm", H.hp_c1(), steps=3, adam_mode="lazy")
+
+
+def test_deepfm_short_last_batch_and_uniform_ids():
+    """input_data_size < batch_size (models/deepfm.py:178); uniform ids = no duplicates regime"""
+    _run_parity("deepfm", H.hp_c1(), steps=2, B=77, dist="uniform")
+
+
+def test_deepfm_int64_ids():
+    _run_parity("deepfm", H.hp_c1(), steps=1, id_dtype=torch.int64)
+
+
+def test_deepfm_criteo_shape_k16():
+    """configs[3] shape (13 cont + 26 cate, k=16, MLP 400x3) at B=1024 / 50K rows"""
+    hp = H.hp_criteo(B=1024, rows=50000)
+    _run_parity("deepfm", hp, steps=2, adam_mode="lazy")
+
+
+def test_deepfm_hot_rows_long_segments():
+    """tiny id space: every row is hit hundreds of times -> multi-chunk runs in the segment reduce"""
+    hp = H.hp_c1(cate_feats_size=64, batch_size=2048)
+    _run_parity("deepfm", hp, steps=2)
+
+
+def test_deepfm_multi_pooled_mean():
+    """configs[1] shape at B=512: zero-padded multi-valued fields, nonzero mean, row-0-zero tables"""
+    _run_parity("deepfm_multi", H.hp_multi(B=512), steps=2)
+
+
+def test_dnn_l1_reg():
+    hp = H.hp_c1(vector_feats_size=0)
+    _run_parity("dnn", hp, steps=2)
+
+
+def test_dnn_multi():
+    hp = H.hp_multi(B=256)
+    _run_parity("dnn_multi", hp, steps=2)
+
+
+def test_training_is_deterministic_run_to_run():
+    """bitwise-equal parameters from two identical runs (the sort/segment-reduce is order-fixed)"""
+    hp = H.hp_c1(cate_feats_size=500, batch_size=1024)
+    outs = []
+    for _ in range(2):
+        p = O.init_params("deepfm", hp, dtype=torch.float64)
+        eng = _engine("deepfm", hp, p, hp.batch_size, adam_mode="lazy")
+        for step in range(3):
+            eng.train_step(H.make_batch("deepfm", hp, seed=5 + step))
+        outs.append(eng.get_weights())
+    for n in outs[0]:
+        assert np.array_equal(outs[0][n], outs[1][n]), n
+
+
+def test_model_module_fit_predict_roundtrip(tmp_path, capsys):
+    """the launcher-facing surface: DeepModel(mp).fit(train, val); .predict(val) on pickled batches"""
+    from deep_learning_b200 import data as D
+    import deep_learning_b200.models.deepfm as alg_model
+    hp = H.hp_c1(batch_size=128, epochs=2)
+    hp.model_pb = str(tmp_path / "pb")
+    train = [D.to_pickled_batch(H.make_batch("deepfm", hp, seed=s)) for s in range(4)]
+    val = [D.to_pickled_batch(H.make_batch("deepfm", hp, seed=100 + s, B=50 if s else 128)) for s in range(2)]
+    m = alg_model.DeepModel(hp, adam_mode="lazy")
+    m.fit(train, val)
+    auc = m.predict(val)
+    out = capsys.readouterr().out
+    assert "valid-auc=" in out and "val of auc:" in out
+    assert 0.0 <= auc <= 1.0
+    sc = m.predict_scores(val[1])
+    assert sc.shape == (50, 1)

@@ -1,0 +1,142 @@
+"""CPU: the oracle (restatement of the reference TF graph) against hand-computed known answers,
+independent closed forms and the one reference dependency present here (scikit-learn's AUC).
+The reference ships no tests or golden vectors: parity is UNPINNED against
+TensorFlow itself; these checks pin the restatement to the published TF op semantics."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ctr_oracle as O
+import ctr_helpers as H
+
+
+def test_fm_known_answer_tiny():
+    """B=1, Fc=2, C=1, k=2, hand computed (models/deepfm.py:63-93 incl. quirk Q1 offset = Fc)"""
+    hp = O.HParams(hidden_units=[2], embedding_size=2, cont_field_size=1, cate_field_size=2, cate_feats_size=4, l2_reg=0.0)
+    p = {n: torch.zeros(s, dtype=torch.float64) for n, s in O.param_shapes("deepfm", hp).items()}
+    p["feats_emb"] = torch.tensor([[1., 2.], [3., 4.], [5., 6.], [7., 8.], [9., 10.]], dtype=torch.float64)
+    p["feats"] = torch.tensor([[.1], [.2], [.3], [.4], [.5]], dtype=torch.float64)
+    # head picks out first-order (3), second-order (2), deep (2)
+    p["deep_fm_weight"] = torch.tensor([[1.], [10.], [100.], [1000.], [10000.], [0.], [0.]], dtype=torch.float64)
+    b = {"cate_feats": torch.tensor([[0, 3]]), "cont_feats": torch.tensor([[0.5]], dtype=torch.float64),
+         "vector_feats": torch.zeros(1, 0, dtype=torch.float64), "label": torch.ones(1, 1, dtype=torch.float64)}
+    out, score = O.deepfm_forward(p, b, hp)
+    # cont row id = 0 + Fc = 2 -> e = [1,2], [7,8], 0.5*[5,6]=[2.5,3]; first = [.1, .4, .3*.5]
+    first = [0.1, 0.4, 0.15]
+    s = np.array([10.5, 13.0]); q = np.array([1 + 49 + 6.25, 4 + 64 + 9.0])
+    second = 0.5 * (s * s - q)
+    want = first[0] + 10 * first[1] + 100 * first[2] + 1000 * second[0] + 10000 * second[1]
+    assert abs(float(out) - want) < 1e-9
+    assert abs(float(score) - 1 / (1 + math.exp(-want))) < 1e-12
+
+
+def test_fm_identity_and_gradient_closed_form():
+    rng = np.random.RandomState(0)
+    e = rng.randn(5, 7, 3)
+    second = 0.5 * (e.sum(1) ** 2 - (e ** 2).sum(1))
+    assert np.allclose(second, O.fm_second_order_pairwise(e), atol=1e-12)
+    # d second / d e_f = sum_e - e_f
+    et = torch.tensor(e, requires_grad=True)
+    g = torch.tensor(rng.randn(5, 3))
+    s2 = 0.5 * (et.sum(1) ** 2 - (et ** 2).sum(1))
+    (s2 * g).sum().backward()
+    want = g.numpy()[:, None, :] * (e.sum(1)[:, None, :] - e)
+    assert np.allclose(et.grad.numpy(), want, atol=1e-12)
+
+
+def test_log_loss_matches_tf_formula():
+    y = torch.tensor([[1.], [0.], [1.]], dtype=torch.float64); p = torch.tensor([[.9], [.2], [1e-9]], dtype=torch.float64)
+    want = np.mean([-math.log(.9 + 1e-7), -math.log(.8 + 1e-7), -math.log(1e-9 + 1e-7)])
+    assert abs(float(O.log_loss(y, p)) - want) < 1e-12
+    assert abs(float(O.l2_regularizer(0.5, torch.tensor([3., 4.]))) - 0.5 * 25 / 2) < 1e-12
+    assert abs(float(O.l1_regularizer(0.5, torch.tensor([-3., 4.]))) - 3.5) < 1e-12
+    assert O.exponential_decay(0.1, 25, 10, 0.5) == 0.1 * 0.25
+
+
+def test_nonzero_reduce_mean_semantics():
+    """count rows whose SUM is non-zero (quirk Q3), div_no_nan, padding row 0 reads zero"""
+    emb = torch.tensor([[[1., -1.], [2., 2.], [0., 0.]], [[0., 0.], [0., 0.], [0., 0.]]], dtype=torch.float64)
+    r = O.nonzero_reduce_mean(emb)
+    assert torch.allclose(r[0], torch.tensor([3., 1.], dtype=torch.float64))   # only one row counts
+    assert torch.equal(r[1], torch.zeros(2, dtype=torch.float64))
+    t = torch.arange(6, dtype=torch.float64).reshape(3, 2) + 1
+    assert torch.equal(O.zero_row0(t)[0], torch.zeros(2, dtype=torch.float64)) and torch.equal(O.zero_row0(t)[1:], t[1:])
+
+
+def test_tf1_adam_first_step_closed_form_and_epsilon_placement():
+    hp = O.HParams()
+    p = {"w": torch.tensor([1.0, -2.0, 3.0], dtype=torch.float64)}
+    g = {"w": torch.tensor([1e-7, -0.5, 0.0], dtype=torch.float64)}
+    st = O.adam_init(p)
+    new = O.tf1_adam_step(p, g, st, hp)
+    lr_t = hp.learning_rate * math.sqrt(1 - 0.999) / (1 - 0.9)
+    for i in range(3):
+        gi = float(g["w"][i])
+        want = float(p["w"][i]) - lr_t * 0.1 * gi / (math.sqrt(0.001 * gi * gi) + 1e-8)
+        assert abs(float(new["w"][i]) - want) < 1e-15
+    assert st.global_step == 1 and abs(st.beta1_power - 0.81) < 1e-15
+    # second step with zero gradient still moves the parameter (TF1 Adam is not lazy)
+    new2 = O.tf1_adam_step(new, {"w": torch.zeros(3, dtype=torch.float64)}, st, hp)
+    assert float((new2["w"] - new["w"]).abs()[1]) > 1e-5
+
+
+def test_lazy_equals_dense_on_first_step_only():
+    hp = H.hp_c1(batch_size=64)
+    outs = {}
+    for mode in ("tf_dense", "lazy"):
+        p = O.init_params("deepfm", hp); st = O.adam_init(p)
+        traj = []
+        for s in range(2):
+            b = H.oracle_batch(H.make_batch("deepfm", hp, seed=s), torch.float64)
+            _, p = O.train_step("deepfm", p, st, b, hp, adam_mode=mode)
+            traj.append(p["feats_emb"].clone())
+        outs[mode] = traj
+    assert torch.equal(outs["tf_dense"][0], outs["lazy"][0])
+    assert not torch.equal(outs["tf_dense"][1], outs["lazy"][1])
+
+
+@pytest.mark.parametrize("ties", [False, True])
+def test_auc_matches_sklearn(ties):
+    from sklearn.metrics import roc_auc_score
+    rng = np.random.RandomState(3)
+    y = (rng.rand(5000) < 0.3).astype(np.float32); s = rng.randn(5000).astype(np.float32)
+    if ties:
+        s = np.round(s, 1)
+    assert abs(O.roc_auc(y, s) - roc_auc_score(y, s)) < 1e-12
+
+
+@pytest.mark.parametrize("alg", ["deepfm", "deepfm_multi", "wdl", "dnn", "dnn_multi"])
+def test_autograd_matches_finite_differences(alg):
+    hp = {"deepfm": H.hp_c1(batch_size=16, hidden_units=[8, 4]), "dnn": H.hp_c1(batch_size=16, hidden_units=[8, 4]),
+          "deepfm_multi": H.hp_multi(B=16, hidden_units=[8, 4]), "dnn_multi": H.hp_multi(B=16, hidden_units=[8, 4]),
+          "wdl": H.hp_criteo(B=16, rows=500, hidden_units=[8, 4])}[alg]
+    p = O.init_params(alg, hp)
+    b = H.oracle_batch(H.make_batch(alg, hp, seed=1), torch.float64)
+    loss, _, _, grads = O.loss_and_grads(alg, p, b, hp)
+    rng = np.random.RandomState(0)
+    for name in p:
+        flat = p[name].reshape(-1)
+        gflat = grads[name].reshape(-1)
+        nz = torch.nonzero(gflat).reshape(-1)
+        idx = int(nz[rng.randint(len(nz))]) if len(nz) else 0
+        eps = 1e-6
+        q = {k: v.clone() for k, v in p.items()}
+        q[name].reshape(-1)[idx] += eps
+        lp = float(O.LOSS[alg](q, b, hp)[0])
+        q[name].reshape(-1)[idx] -= 2 * eps
+        lm = float(O.LOSS[alg](q, b, hp)[0])
+        fd = (lp - lm) / (2 * eps)
+        assert abs(fd - float(gflat[idx])) < 1e-6 * max(1.0, abs(fd)) + 1e-9, (name, fd, float(gflat[idx]))
+
+
+def test_data_formats_roundtrip():
+    from deep_learning_b200 import data as D
+    hp = H.hp_c1(batch_size=7)
+    b = H.make_batch("deepfm", hp, seed=4)
+    d = D.from_pickled_batch(D.to_pickled_batch(b))
+    assert np.array_equal(d["cate_feats"], b["cate_feats"].numpy()) and np.allclose(d["cont_feats"], b["cont_feats"].numpy())
+    assert d["label"].shape == (7, 1)
+    sizes = D.field_sizes(10 ** 8, 26)
+    assert sum(sizes) == 10 ** 8 and min(sizes) >= 2
