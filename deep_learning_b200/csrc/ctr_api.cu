@@ -76,7 +76,7 @@ extern "C" int ctr_table_unpack(ctr_handle* h, ctr_stream s, const float* table,
 }
 
 // ------------------------------------------------------------------ transpose [K,N] -> [N,K]
-__global__ void transpose_kernel(const float* __restrict__ in, int K, int N, float* __restrict__ out) {
+__global__ void transpose_kernel(const float* __restrict__ in, int K, int N, float* __restrict__ out, int64_t ld_out) {
     __shared__ float tile[32][33];
     int n0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
@@ -86,14 +86,14 @@ __global__ void transpose_kernel(const float* __restrict__ in, int K, int N, flo
     __syncthreads();
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
         int nn = n0 + i, kk = k0 + threadIdx.x;
-        if (nn < N && kk < K) out[(int64_t) nn * K + kk] = tile[threadIdx.x][i];
+        if (nn < N && kk < K) out[(int64_t) nn * ld_out + kk] = tile[threadIdx.x][i];
     }
 }
 
-extern "C" int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, float* out) {
-    CTR_REQUIRE(h, in && out && K > 0 && N > 0, "transpose: bad args");
+extern "C" int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, float* out, int64_t ld_out) {
+    CTR_REQUIRE(h, in && out && K > 0 && N > 0 && ld_out >= K, "transpose: bad args");
     dim3 grid((unsigned) ctr_cdiv(N, 32), (unsigned) ctr_cdiv(K, 32)), block(32, 8);
-    transpose_kernel<<<grid, block, 0, ctr_st(s)>>>(in, K, N, out);
+    transpose_kernel<<<grid, block, 0, ctr_st(s)>>>(in, K, N, out, ld_out);
     CTR_CHECK_LAUNCH(h, "transpose");
     return CTR_OK;
 }

@@ -1,17 +1,486 @@
-// K3 (TF32 path): tcgen05 / TMA GEMMs.  Placeholder until the tensor-core kernels land: every
-// entry point fails loudly (there is no silent fallback to the FP32 path).
+// K3 (TF32 path): hand-written tcgen05 / TMA / TMEM GEMMs for the MLP tower (sm_100a).
+//
+//   tn kernel  C[M,N] = A[M,R] * B[N,R]^T      both operands reduction-major ("K-major"):
+//              forward  (A = X,  B = W^T copy) with bias + ReLU (+dropout) epilogue
+//              dgrad    (A = dZ, B = W)        with ReLU/dropout-mask epilogue
+//   nt kernel  C[M,N] = A[R,M]^T * B[R,N]      both operands MN-major, split over the reduction:
+//              wgrad    (A = X, B = dZ, R = batch)
+//
+// One CTA owns a 128-row output panel across the WHOLE N extent (N <= 512 fp32 accumulator columns =
+// all of TMEM), so the A panel is streamed from HBM exactly once.  Warp roles: warps 0-3 epilogue
+// (TMEM lane quarter = warp id), warp 4 = TMA producer (one elected lane), warp 5 = MMA issuer (one
+// elected lane).  Operands are staged by TMA into 128B-swizzled shared memory through a 3-stage
+// mbarrier ring; accumulators live in TMEM and are read back with tcgen05.ld for the fused epilogue.
+#include <cuda.h>
 #include "ctr_common.cuh"
 
-int ctr_tc_mlp_fwd(ctr_handle* h, cudaStream_t, int, int, int, const float*, int64_t, const float*, const float*, int,
-                   float, uint64_t, float*, int64_t) {
-    return ctr_fail(h, CTR_E_UNSUPPORTED, "TF32 tcgen05 path not built yet");
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_R = 32;            // reduction elements per stage: 32 fp32 = one 128B swizzle row
+constexpr int UMMA_K = 8;              // tf32: 32 bytes of reduction per instruction
+constexpr int MAX_N = 512;             // fp32 accumulator columns in TMEM
+constexpr int NUM_THREADS = 192;
+constexpr int SMEM_LIMIT = 227 * 1024;
+
+// ------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t) __cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
 }
-int ctr_tc_mlp_bwd_data(ctr_handle* h, cudaStream_t, int, int, int, const float*, int64_t, const float*, const float*,
-                        int64_t, float, float*, int64_t) {
-    return ctr_fail(h, CTR_E_UNSUPPORTED, "TF32 tcgen05 path not built yet");
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
-int64_t ctr_tc_bwd_weight_ws_bytes(ctr_handle*, int, int, int) { return 256; }
-int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t, int, int, int, const float*, int64_t, const float*, int64_t,
-                          float*, void*, int64_t) {
-    return ctr_fail(h, CTR_E_UNSUPPORTED, "TF32 tcgen05 path not built yet");
+// bounded wait: a protocol error traps (CUDA error) instead of hanging the GPU box
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (!done && spin > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// D[tmem] (+)= A[smem desc] * B[smem desc], kind::tf32, issued by one thread
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrive on an mbarrier once every MMA issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred = 0;
+    asm volatile(
+        "{\n\t.reg .pred P;\n\t"
+        "elect.sync _|P, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, P;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+
+// ------------------------------------------------------------------------------------ descriptors
+// shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start>>4 [0,14), LBO>>4 [16,30),
+// SBO>>4 [32,46), version=1 [46,48), layout type [61,64)
+constexpr uint64_t LAYOUT_SW128 = 2;          // K-major operands: 128B swizzle, 16B atoms
+constexpr uint64_t LAYOUT_SW128_BASE32B = 1;  // MN-major tf32 operands: 128B swizzle, 32B atoms
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint64_t layout) {
+    return (uint64_t) ((saddr & 0x3FFFF) >> 4) | ((uint64_t) ((lbo_bytes >> 4) & 0x3FFF) << 16) |
+           ((uint64_t) ((sbo_bytes >> 4) & 0x3FFF) << 32) | (1ull << 46) | (layout << 61);
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor) for kind::tf32, fp32 accumulate
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n, int a_mn_major, int b_mn_major) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t) a_mn_major << 15) | ((uint32_t) b_mn_major << 16) |
+           ((uint32_t) (n >> 3) << 17) | ((uint32_t) (m >> 4) << 24);
+}
+
+struct EpiParams {
+    const float* bias;      // [N] or null
+    int relu;
+    float keep;             // dropout keep prob, 1 = off
+    uint64_t seed;
+    const float* mask;      // [M, ldmask] or null
+    int64_t ldmask;
+    float mask_scale;
+};
+
+__device__ __forceinline__ float dropout_u01(uint64_t seed, uint64_t idx) {   // same hash as the FP32 path
+    uint64_t z = seed + idx * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z = z ^ (z >> 31);
+    return (float) (z >> 40) * (1.0f / 16777216.0f);
+}
+
+struct alignas(8) PipeBars {
+    uint64_t full[4];
+    uint64_t empty[4];
+    uint64_t tmem_full;
+    uint32_t tmem_base;
+    uint32_t pad;
+};
+
+}  // namespace
+
+namespace {
+
+// ---- epilogue shared by both kernels: TMEM -> registers -> (bias / ReLU / dropout / mask) -> global
+__device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int warp, int lane, int m0, int M, int N, float* C,
+                                              int64_t ldc, const EpiParams& ep) {
+    const int row = m0 + warp * 32 + lane;
+    const bool row_ok = row < M;
+    const bool vec_ok = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
+    const uint32_t lane_addr = tmem_base + ((uint32_t) (warp * 32) << 16);
+    for (int c0 = 0; c0 < N; c0 += 16) {
+        float v[16];
+        tmem_ld16(lane_addr + (uint32_t) c0, v);      // .sync.aligned: every lane takes part, valid row or not
+        if (!row_ok) continue;
+        const int nc = (N - c0) < 16 ? (N - c0) : 16;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            if (i < nc) {
+                const int col = c0 + i;
+                float x = v[i];
+                if (ep.bias) x += __ldg(ep.bias + col);
+                if (ep.relu) x = x > 0.f ? x : 0.f;
+                if (ep.keep < 1.f) x = dropout_u01(ep.seed, (uint64_t) row * (uint64_t) N + col) < ep.keep ? x / ep.keep : 0.f;
+                if (ep.mask) x = ep.mask[(int64_t) row * ep.ldmask + col] > 0.f ? x * ep.mask_scale : 0.f;
+                v[i] = x;
+            }
+        }
+        float* dst = C + (int64_t) row * ldc + c0;
+        if (vec_ok && nc == 16) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                reinterpret_cast<float4*>(dst)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+        } else {
+            for (int i = 0; i < nc; ++i) dst[i] = v[i];
+        }
+    }
+}
+
+__device__ __forceinline__ PipeBars* setup_cta(uint8_t* smem, int nstages, int stage_bytes, uint32_t tmem_cols, int warp) {
+    PipeBars* bars = reinterpret_cast<PipeBars*>(smem + (size_t) nstages * stage_bytes);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < nstages; ++s) {
+            mbar_init(&bars->full[s], 1);
+            mbar_init(&bars->empty[s], 1);
+        }
+        mbar_init(&bars->tmem_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 4) tmem_alloc(&bars->tmem_base, tmem_cols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    return bars;
+}
+
+// ---- C[M,N] = A[M,R] * B[N,R]^T ; A, B reduction-major, 128B-swizzled K-major tiles -------------------
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int R,
+               int n_each, int nmma, int nstages, uint32_t tmem_cols, float* __restrict__ C, int64_t ldc, EpiParams ep) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int NB = n_each * nmma;
+    const int a_bytes = BLOCK_M * BLOCK_R * 4;
+    const int stage_bytes = a_bytes + NB * BLOCK_R * 4;
+    const int m0 = blockIdx.x * BLOCK_M;
+    const int num_kb = (R + BLOCK_R - 1) / BLOCK_R;
+    PipeBars* bars = setup_cta(smem, nstages, stage_bytes, tmem_cols, warp);
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 4) {
+        if (elect_one()) {
+            prefetch_tmap(&tmA);
+            prefetch_tmap(&tmB);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % nstages;
+                const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
+                mbar_wait(&bars->empty[s], ph ^ 1u);
+                uint8_t* sa = smem + (size_t) s * stage_bytes;
+                mbar_expect_tx(&bars->full[s], (uint32_t) stage_bytes);
+                tma_load_2d(sa, &tmA, &bars->full[s], kb * BLOCK_R, m0);
+                for (int i = 0; i < nmma; ++i)
+                    tma_load_2d(sa + a_bytes + (size_t) i * n_each * BLOCK_R * 4, &tmB, &bars->full[s], kb * BLOCK_R, i * n_each);
+            }
+        }
+    } else if (warp == 5) {
+        if (elect_one()) {
+            const uint32_t idesc = make_idesc(BLOCK_M, n_each, 0, 0);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % nstages;
+                const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
+                mbar_wait(&bars->full[s], ph);
+                tc_fence_after();
+                const uint32_t a_base = smem_u32(smem + (size_t) s * stage_bytes);
+                const uint32_t b_base = a_base + a_bytes;
+#pragma unroll
+                for (int k = 0; k < BLOCK_R / UMMA_K; ++k) {
+                    const uint64_t adesc = make_desc(a_base + k * UMMA_K * 4, 16, 8 * BLOCK_R * 4, LAYOUT_SW128);
+                    for (int i = 0; i < nmma; ++i) {
+                        const uint64_t bdesc = make_desc(b_base + i * n_each * BLOCK_R * 4 + k * UMMA_K * 4, 16, 8 * BLOCK_R * 4, LAYOUT_SW128);
+                        umma_tf32(tmem_base + (uint32_t) (i * n_each), adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                }
+                umma_commit(&bars->empty[s]);     // frees the smem stage once these MMAs have read it
+            }
+            umma_commit(&bars->tmem_full);        // accumulator complete
+        }
+    } else {
+        mbar_wait(&bars->tmem_full, 0);
+        tc_fence_after();
+        epilogue_rows(tmem_base, warp, lane, m0, M, N, C, ldc, ep);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+// ---- C_split[M,N] = A[R,M]^T * B[R,N] over this CTA's slice of R ; MN-major tf32 tiles (32B-atom swizzle)
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int R,
+               int r_per_split, int n1, int n2, int nstages, uint32_t tmem_cols, float* __restrict__ Cws) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    constexpr int BOX_BYTES = 32 * BLOCK_R * 4;             // 32 MN-elements x 32 reduction rows
+    const int nbx = (n1 + n2) / 32;                          // MN blocks of the B tile
+    const int a_bytes = (BLOCK_M / 32) * BOX_BYTES;
+    const int stage_bytes = a_bytes + nbx * BOX_BYTES;
+    const int m0 = blockIdx.x * BLOCK_M;
+    const int r_lo = blockIdx.y * r_per_split;
+    const int r_hi = (r_lo + r_per_split < R) ? r_lo + r_per_split : R;
+    const int num_kb = r_hi > r_lo ? (r_hi - r_lo + BLOCK_R - 1) / BLOCK_R : 0;
+    PipeBars* bars = setup_cta(smem, nstages, stage_bytes, tmem_cols, warp);
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == 4) {
+        if (elect_one()) {
+            prefetch_tmap(&tmA);
+            prefetch_tmap(&tmB);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % nstages;
+                const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
+                mbar_wait(&bars->empty[s], ph ^ 1u);
+                uint8_t* sa = smem + (size_t) s * stage_bytes;
+                mbar_expect_tx(&bars->full[s], (uint32_t) stage_bytes);
+                const int r0 = r_lo + kb * BLOCK_R;
+                for (int j = 0; j < BLOCK_M / 32; ++j) tma_load_2d(sa + j * BOX_BYTES, &tmA, &bars->full[s], m0 + j * 32, r0);
+                for (int j = 0; j < nbx; ++j) tma_load_2d(sa + a_bytes + j * BOX_BYTES, &tmB, &bars->full[s], j * 32, r0);
+            }
+        }
+    } else if (warp == 5) {
+        if (elect_one()) {
+            const uint32_t idesc1 = make_idesc(BLOCK_M, n1, 1, 1);
+            const uint32_t idesc2 = make_idesc(BLOCK_M, n2 > 0 ? n2 : 16, 1, 1);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % nstages;
+                const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
+                mbar_wait(&bars->full[s], ph);
+                tc_fence_after();
+                const uint32_t a_base = smem_u32(smem + (size_t) s * stage_bytes);
+                const uint32_t b_base = a_base + a_bytes;
+#pragma unroll
+                for (int k = 0; k < BLOCK_R / UMMA_K; ++k) {
+                    // 8 reduction rows = two 4-row swizzle atoms (SBO = 512 B); MN blocks of 32 are LBO apart
+                    const uint32_t koff = k * UMMA_K * 128;
+                    const uint64_t adesc = make_desc(a_base + koff, BOX_BYTES, 512, LAYOUT_SW128_BASE32B);
+                    const uint64_t bdesc1 = make_desc(b_base + koff, BOX_BYTES, 512, LAYOUT_SW128_BASE32B);
+                    umma_tf32(tmem_base, adesc, bdesc1, idesc1, (kb | k) != 0 ? 1u : 0u);
+                    if (n2 > 0) {
+                        const uint64_t bdesc2 = make_desc(b_base + (n1 / 32) * BOX_BYTES + koff, BOX_BYTES, 512, LAYOUT_SW128_BASE32B);
+                        umma_tf32(tmem_base + (uint32_t) n1, adesc, bdesc2, idesc2, (kb | k) != 0 ? 1u : 0u);
+                    }
+                }
+                umma_commit(&bars->empty[s]);
+            }
+            umma_commit(&bars->tmem_full);
+        }
+    } else {
+        float* Cz = Cws + (size_t) blockIdx.y * M * N;
+        if (num_kb > 0) {
+            mbar_wait(&bars->tmem_full, 0);
+            tc_fence_after();
+            EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f};
+            epilogue_rows(tmem_base, warp, lane, m0, M, N, Cz, N, ep);
+        } else {                                   // empty slice: contribute zeros
+            const int row = m0 + warp * 32 + lane;
+            if (row < M) for (int c = 0; c < N; ++c) Cz[(size_t) row * N + c] = 0.f;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------ host side
+namespace {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 2-D fp32 tensor [rows, cols] with row pitch ld floats; box = {box_cols, box_rows}; OOB reads give zeros
+int make_map(ctr_handle* h, CUtensorMap* map, const float* base, int64_t rows, int64_t cols, int64_t ld, int box_cols,
+             int box_rows, CUtensorMapSwizzle swz) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return ctr_fail(h, CTR_E_UNSUPPORTED, "cuTensorMapEncodeTiled not available");
+    if ((reinterpret_cast<uintptr_t>(base) & 15) || (ld % 4) != 0)
+        return ctr_fail(h, CTR_E_INVALID, "TF32 path: operand must be 16-byte aligned with a row pitch multiple of 4 floats (ld=%lld)",
+                        (long long) ld);
+    cuuint64_t dims[2] = {(cuuint64_t) cols, (cuuint64_t) rows};
+    cuuint64_t strides[1] = {(cuuint64_t) ld * 4};
+    cuuint32_t box[2] = {(cuuint32_t) box_cols, (cuuint32_t) box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return ctr_fail(h, CTR_E_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int) r);
+    return CTR_OK;
+}
+
+uint32_t tmem_cols_for(int nb) {
+    uint32_t c = 32;
+    while ((int) c < nb) c <<= 1;
+    return c;
+}
+
+int pick_stages(int stage_bytes) {
+    int s = (SMEM_LIMIT - 2048) / stage_bytes;
+    return s > 4 ? 4 : s;
+}
+
+int launch_tn(ctr_handle* h, cudaStream_t st, int M, int N, int R, const float* A, int64_t lda, const float* B,
+              int64_t ldb, float* C, int64_t ldc, const EpiParams& ep) {
+    CTR_REQUIRE(h, N <= MAX_N, "TF32 path: N=%d > %d not supported", N, MAX_N);
+    const int nmma = N > 256 ? 2 : 1;
+    const int NB = nmma == 1 ? (int) ctr_align(N, 16) : (int) ctr_align(N, 32);
+    const int n_each = NB / nmma;
+    const int stage_bytes = BLOCK_M * BLOCK_R * 4 + NB * BLOCK_R * 4;
+    const int nstages = pick_stages(stage_bytes);
+    CTR_REQUIRE(h, nstages >= 2, "TF32 path: tile does not fit shared memory");
+    CUtensorMap tmA, tmB;
+    int rc = make_map(h, &tmA, A, M, R, lda, BLOCK_R, BLOCK_M, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    rc = make_map(h, &tmB, B, N, R, ldb, BLOCK_R, n_each, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    const size_t smem = (size_t) nstages * stage_bytes + sizeof(PipeBars) + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CTR_CUDA(h, cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+        attr_set = true;
+    }
+    gemm_tn_kernel<<<(unsigned) ctr_cdiv(M, BLOCK_M), NUM_THREADS, smem, st>>>(tmA, tmB, M, N, R, n_each, nmma, nstages,
+                                                                              tmem_cols_for(NB), C, ldc, ep);
+    CTR_CHECK_LAUNCH(h, "gemm_tn_kernel");
+    return CTR_OK;
+}
+
+struct NtPlan { int n1, n2, nstages, splits, r_per_split, mtiles; };
+
+NtPlan plan_nt(ctr_handle* h, int M, int N, int R) {
+    NtPlan p;
+    const int NB = (int) ctr_align(N, 32);
+    p.n1 = NB > 256 ? 256 : NB;
+    p.n2 = NB - p.n1;
+    const int stage_bytes = (BLOCK_M / 32 + NB / 32) * 32 * BLOCK_R * 4;
+    p.nstages = pick_stages(stage_bytes);
+    p.mtiles = (int) ctr_cdiv(M, BLOCK_M);
+    int want = h->sm_count / p.mtiles;
+    if (want < 1) want = 1;
+    int64_t rps = ctr_align(ctr_cdiv(R, want), BLOCK_R);
+    if (rps < 4 * BLOCK_R) rps = 4 * BLOCK_R;
+    p.r_per_split = (int) rps;
+    p.splits = (int) ctr_cdiv(R, rps);
+    return p;
+}
+
+__global__ void __launch_bounds__(256) tc_splitk_reduce(const float* __restrict__ ws, int splits, int64_t n, float* __restrict__ out) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        float a = 0.f;
+        for (int z = 0; z < splits; ++z) a += ws[(int64_t) z * n + i];
+        out[i] = a;
+    }
+}
+
+}  // namespace
+
+int ctr_tc_mlp_fwd(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* X, int64_t ldx, const float* Wt,
+                   const float* bias, int relu, float keep, uint64_t seed, float* Y, int64_t ldy) {
+    // Wt is the K-major copy [N, ldwt] with ldwt = K rounded up to 4 floats (TMA needs 16-byte row pitches)
+    EpiParams ep{bias, relu, keep, seed, nullptr, 0, 1.f};
+    return launch_tn(h, st, B, N, K, X, ldx, Wt, ctr_align(K, 4), Y, ldy, ep);
+}
+
+int ctr_tc_mlp_bwd_data(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* dZ, int64_t lddz,
+                        const float* W, const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx) {
+    // dX[B,K] = dZ[B,N] * W[K,N]^T : W is already reduction-major for this product
+    EpiParams ep{nullptr, 0, 1.f, 0, mask, ldmask, mask_scale};
+    return launch_tn(h, st, B, K, N, dZ, lddz, W, N, dX, lddx, ep);
+}
+
+int64_t ctr_tc_bwd_weight_ws_bytes(ctr_handle* h, int B, int K, int N) {
+    NtPlan p = plan_nt(h, K, N, B);
+    return ctr_align((int64_t) p.splits * K * N * 4, 256);
+}
+
+int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* X, int64_t ldx,
+                          const float* dZ, int64_t lddz, float* dW, void* ws, int64_t ws_bytes) {
+    CTR_REQUIRE(h, N <= MAX_N, "TF32 path: N=%d > %d not supported", N, MAX_N);
+    NtPlan p = plan_nt(h, K, N, B);
+    CTR_REQUIRE(h, p.nstages >= 2, "TF32 wgrad: tile does not fit shared memory");
+    if (ws_bytes < (int64_t) p.splits * K * N * 4) return ctr_fail(h, CTR_E_WORKSPACE, "TF32 wgrad: ws too small");
+    CUtensorMap tmA, tmB;
+    int rc = make_map(h, &tmA, X, B, K, ldx, 32, BLOCK_R, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+    if (rc) return rc;
+    rc = make_map(h, &tmB, dZ, B, N, lddz, 32, BLOCK_R, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+    if (rc) return rc;
+    const int stage_bytes = (BLOCK_M / 32 + (p.n1 + p.n2) / 32) * 32 * BLOCK_R * 4;
+    const size_t smem = (size_t) p.nstages * stage_bytes + sizeof(PipeBars) + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CTR_CUDA(h, cudaFuncSetAttribute(gemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+        attr_set = true;
+    }
+    dim3 grid((unsigned) p.mtiles, (unsigned) p.splits);
+    gemm_nt_kernel<<<grid, NUM_THREADS, smem, st>>>(tmA, tmB, K, N, B, p.r_per_split, p.n1, p.n2, p.nstages,
+                                                    tmem_cols_for(p.n1 + p.n2), (float*) ws);
+    CTR_CHECK_LAUNCH(h, "gemm_nt_kernel");
+    const int64_t n = (int64_t) K * N;
+    tc_splitk_reduce<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>((const float*) ws, p.splits, n, dW);
+    CTR_CHECK_LAUNCH(h, "tc_splitk_reduce");
+    return CTR_OK;
 }

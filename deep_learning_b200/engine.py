@@ -67,7 +67,7 @@ class CtrEngine:
         self.theta = torch.zeros(cur, **f32)
         self.shape = dict(self.dense_shapes)
         # K-major copies of the tower weights for the tcgen05 path
-        self.wt = [torch.zeros(h_, k_, **f32) for (k_, h_) in self._layer_dims()] if self.prec == 1 else None
+        self.wt = [torch.zeros(h_, _ru(k_, 4), **f32) for (k_, h_) in self._layer_dims()] if self.prec == 1 else None
 
         # ---- batch + activations ----------------------------------------------------------------
         self.ids = torch.zeros(B, max(s.ids_ld, 1), dtype=self.id_torch, device=dev)
@@ -233,7 +233,7 @@ class CtrEngine:
             return
         st = self._stream()
         for i, (k_, h_) in enumerate(self._layer_dims()):
-            self.h.call("ctr_transpose", st, ptr(self._w(i)), k_, h_, ptr(self.wt[i]))
+            self.h.call("ctr_transpose", st, ptr(self._w(i)), k_, h_, ptr(self.wt[i]), _ru(k_, 4))
 
     # ---- batch upload ------------------------------------------------------------------------------
     def load_batch(self, batch: Dict, non_blocking: bool = True) -> int:

@@ -131,7 +131,7 @@ int ctr_scalar_gather_sum(ctr_handle* h, ctr_stream s, const float* table, const
 #define CTR_PREC_TF32 1
 /* Y[B,N] = dropout(relu(X[B,K] @ W[K,N] + bias[N])); relu/bias optional; keep==1 -> no dropout */
 int ctr_mlp_fwd(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
-                const float* X, int64_t ldx, const float* W, const float* Wt /*[N,K] or NULL*/,
+                const float* X, int64_t ldx, const float* W, const float* Wt /*[N, roundup(K,4)] or NULL*/,
                 const float* bias, int relu, float keep, uint64_t seed, float* Y, int64_t ldy);
 /* dX[B,K] = (dZ[B,N] @ W^T) * (mask[B,K] > 0 ? mask_scale : 0)   (mask = the layer's input
  * activation, NULL for the tower input) */
@@ -143,8 +143,9 @@ int64_t ctr_mlp_bwd_weight_ws_bytes(ctr_handle* h, int precision, int B, int K, 
 int ctr_mlp_bwd_weight(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
                        const float* X, int64_t ldx, const float* dZ, int64_t lddz,
                        float* dW, float* dbias, void* ws, int64_t ws_bytes);
-/* out[N,K] = in[K,N]^T (keeps the K-major copy the tcgen05 path reads) */
-int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, float* out);
+/* out[N, ld_out] = in[K,N]^T, ld_out >= K: the K-major copy the tcgen05 path reads (TMA needs 16-byte
+ * row pitches, so ld_out = K rounded up to 4; pad columns are left untouched) */
+int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, float* out, int64_t ld_out);
 
 /* ---- K5: head + sigmoid log-loss --------------------------------------------------------
  * replaces concat + matmul + sigmoid (models/deepfm.py:128-145; models/dnn.py:82-84; the deep half

@@ -96,7 +96,8 @@ def test_auc_matches_sklearn(hd, n, ties):
         s = np.round(s, 1); s[::7] = 0.0; s[3::11] = -0.0
     wsn = hd.query("ctr_auc_ws_bytes", n); ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
     out = torch.zeros(1, dtype=torch.float64, device="cuda")
-    hd.call("ctr_auc", _st(), ptr(torch.from_numpy(s).cuda()), ptr(torch.from_numpy(y).cuda()), n, ptr(out), ptr(ws), wsn)
+    sd, yd = torch.from_numpy(s).cuda(), torch.from_numpy(y).cuda()   # keep both alive across the call
+    hd.call("ctr_auc", _st(), ptr(sd), ptr(yd), n, ptr(out), ptr(ws), wsn)
     assert abs(out.item() - roc_auc_score(y, s)) < 1e-12
 
 
@@ -134,5 +135,39 @@ def test_table_pack_roundtrip_and_transpose(hd):
     hd.call("ctr_table_unpack", _st(), ptr(tab), R, k, stride, ptr(e2), ptr(f2))
     assert torch.equal(e2, emb) and torch.equal(f2, first)
     W = torch.randn(429, 400, device="cuda"); Wt = torch.zeros(400, 429, device="cuda")
-    hd.call("ctr_transpose", _st(), ptr(W), 429, 400, ptr(Wt))
+    hd.call("ctr_transpose", _st(), ptr(W), 429, 400, ptr(Wt), 429)
     assert torch.equal(Wt, W.T.contiguous())
+
+
+@pytest.mark.parametrize("B,K,N", [(128, 32, 16), (300, 170, 256), (1000, 429, 400), (4096, 400, 400), (2500, 256, 128),
+                                   (777, 461, 512)])
+def test_mlp_tf32_tcgen05_gemms(hd, B, K, N):
+    """tcgen05/TMA TF32 path vs fp64: forward, data gradient and weight gradient within 2e-3."""
+    from deep_learning_b200._lib import ptr
+    if not hd.has_tcgen05:
+        pytest.skip("needs sm_100")
+    g = torch.Generator().manual_seed(B * 1000 + K)
+    ldx = (K + 3) // 4 * 4
+    X = torch.randn(B, K, generator=g); W = torch.randn(K, N, generator=g) / K ** 0.5; b = torch.randn(N, generator=g)
+    dZ = torch.randn(B, N, generator=g); mask = torch.randn(B, K, generator=g)
+    Xp = torch.zeros(B, ldx); Xp[:, :K] = X
+    Xc, Wc, bc, dZc = Xp.cuda(), W.cuda(), b.cuda(), dZ.cuda()
+    mp = torch.zeros(B, ldx); mp[:, :K] = mask; mc = mp.cuda()
+    Wt = torch.zeros(N, ldx, device="cuda")
+    hd.call("ctr_transpose", _st(), ptr(Wc), K, N, ptr(Wt), ldx)
+    Y = torch.zeros(B, N, device="cuda")
+    hd.call("ctr_mlp_fwd", _st(), 1, B, K, N, ptr(Xc), ldx, ptr(Wc), ptr(Wt), ptr(bc), 1, 1.0, 0, ptr(Y), N)
+    torch.cuda.synchronize()
+    ref = torch.relu(X.double() @ W.double() + b.double())
+    assert H.rel_err(Y.cpu(), ref) < 2e-3, "fwd"
+    dX = torch.zeros(B, ldx, device="cuda")
+    hd.call("ctr_mlp_bwd_data", _st(), 1, B, K, N, ptr(dZc), N, ptr(Wc), ptr(mc), ldx, 1.0, ptr(dX), ldx)
+    torch.cuda.synchronize()
+    ref = (dZ.double() @ W.double().T) * (mask > 0).double()
+    assert H.rel_err(dX.cpu()[:, :K], ref) < 2e-3, "dgrad"
+    wsn = hd.query("ctr_mlp_bwd_weight_ws_bytes", 1, B, K, N); ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
+    dW = torch.zeros(K, N, device="cuda"); db = torch.zeros(N, device="cuda")
+    hd.call("ctr_mlp_bwd_weight", _st(), 1, B, K, N, ptr(Xc), ldx, ptr(dZc), N, ptr(dW), ptr(db), ptr(ws), wsn)
+    torch.cuda.synchronize()
+    assert H.rel_err(dW.cpu(), X.double().T @ dZ.double()) < 2e-3, "wgrad"
+    assert H.rel_err(db.cpu(), dZ.double().sum(0)) < 1e-5
