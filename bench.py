@@ -119,7 +119,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--batch", type=int, default=65536)
     ap.add_argument("--rows", type=int, default=100_000_000)
-    ap.add_argument("--precision", default=os.environ.get("CTR_PRECISION", "fp32"))
+    ap.add_argument("--precision", default=os.environ.get("CTR_PRECISION", "tf32"))
     ap.add_argument("--dist", default="zipf")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     a = ap.parse_args()

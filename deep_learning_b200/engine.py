@@ -163,11 +163,15 @@ class CtrEngine:
     def set_weights(self, p: Dict[str, np.ndarray]) -> None:
         """Load variables named and shaped as in the reference model file (e.g. feats_emb [R,k],
         feats [R,1], deep_0 [D0,H0] in [cont|vector|emb] row order, deep_fm_weight [F+k+H,1])."""
+        self._load(p, self.table, self.theta)
+        self._refresh_transposes()
+
+    def _load(self, p: Dict[str, np.ndarray], table: torch.Tensor, flat: torch.Tensor) -> None:
         s, st = self.spec, self._stream()
         t = lambda a: torch.as_tensor(np.ascontiguousarray(np.asarray(a, dtype=np.float32))).to(self.dev)
         emb = t(p[s.emb_name]).reshape(s.table_rows, s.k)
         first = t(p[s.first_name]).reshape(s.table_rows) if s.has_first else None
-        self.h.call("ctr_table_pack", st, ptr(emb), ptr(first), s.table_rows, s.k, s.table_stride, ptr(self.table))
+        self.h.call("ctr_table_pack", st, ptr(emb), ptr(first), s.table_rows, s.k, s.table_stride, ptr(table))
         for name, shp in self.dense_shapes:
             a = np.asarray(p[name], dtype=np.float32).reshape(shp)
             if name == "deep_0":
@@ -175,9 +179,16 @@ class CtrEngine:
             if s.head == "deepfm" and name == s.head_w_name:
                 perm = np.concatenate([s.head_fm_perm(), s.n_fm + np.arange(s.hidden[-1])])
                 a = a[perm, :]
-            self.view(name).copy_(t(a).reshape(-1))
+            self.view(name, flat).copy_(t(a).reshape(-1))
         torch.cuda.current_stream(self.dev).synchronize()
-        self._refresh_transposes()
+
+    def set_optimizer_state(self, m: Dict[str, np.ndarray], v: Dict[str, np.ndarray], global_step: int,
+                            beta1_power: float, beta2_power: float) -> None:
+        """Adam slots named and shaped like the variables they belong to (what tf.train.Saver stores,
+        models/deepfm_multi.py:269-278,308-310), plus the step counters."""
+        self._load(m, self.m_table, self.m)
+        self._load(v, self.v_table, self.v)
+        self.global_step, self.beta1_power, self.beta2_power = int(global_step), float(beta1_power), float(beta2_power)
 
     def set_dense_weights(self, p: Dict[str, np.ndarray]) -> None:
         """dense variables only (reference names/shapes); the table is left as is"""

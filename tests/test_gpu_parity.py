@@ -62,6 +62,14 @@ def _run_parity(alg, hp, steps, precision="fp32", adam_mode="tf_dense", B=None, 
             floor = H.rel_err(p32[n].numpy().reshape(-1), ref)
             REPORT.append((alg, precision, adam_mode, step, n, err, floor))
             assert err < max(tol, 4 * floor), "param %s step %d: rel err %.3g (fp32 oracle floor %.3g)" % (n, step, err, floor)
+        # every step is checked from IDENTICAL state: re-inject the oracle's parameters and Adam slots
+        # (rounded to fp32), so a step's bar is not polluted by the previous step's rounding drift
+        eng.set_weights({k: v.numpy() for k, v in p.items()})
+        eng.set_optimizer_state({k: v.numpy() for k, v in st.m.items()}, {k: v.numpy() for k, v in st.v.items()},
+                                st.global_step, st.beta1_power, st.beta2_power)
+        p = O.to_dtype(O.to_dtype(p, torch.float32), torch.float64)
+        st.m = O.to_dtype(O.to_dtype(st.m, torch.float32), torch.float64)
+        st.v = O.to_dtype(O.to_dtype(st.v, torch.float32), torch.float64)
     return eng
 
 
@@ -126,6 +134,22 @@ def test_zz_parity_report(capsys):
     with capsys.disabled():
         for k, v in sorted(worst.items()):
             print("\nPARITY %s/%s/%s: worst param rel err %.3g (fp32-oracle floor %.3g) at %s step %d" % (k + v))
+
+
+def test_deepfm_free_running_trajectory_stays_close():
+    """10 un-resynchronised steps: the device trajectory drifts from the fp64 oracle only by rounding"""
+    hp = H.hp_c1()
+    p = O.init_params("deepfm", hp, dtype=torch.float64)
+    st = O.adam_init(p)
+    eng = _engine("deepfm", hp, p, hp.batch_size)
+    for step in range(10):
+        b = H.make_batch("deepfm", hp, seed=300 + step)
+        loss_ref, p = O.train_step("deepfm", p, st, H.oracle_batch(b, torch.float64), hp)
+        loss = float(eng.train_step(b).item())
+        assert abs(loss - float(loss_ref)) < 1e-4 * max(1.0, abs(float(loss_ref)))
+    got = eng.get_weights()
+    for n in p:
+        assert H.rel_err(got[n].reshape(-1), p[n].numpy().reshape(-1)) < 2e-3, n
 
 
 def test_training_is_deterministic_run_to_run():
