@@ -54,7 +54,7 @@ _PROTOS = {
                                    c_vp, c_i64]),
     "ctr_transpose": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_i64]),
     "ctr_head_fwd": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp,
-                             c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
+                             c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i64]),
     "ctr_head_bwd_deep": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64, c_vp, c_i64]),
     "ctr_colsum_ws_bytes": (c_i64, [c_vp, c_i32, c_i32]),
     "ctr_colsum": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64]),

@@ -208,19 +208,21 @@ cont_bwd_pass1(const ctr_embed_cfg cfg, const float* __restrict__ cont, const fl
     }
 }
 
+// one warp per (field, coordinate): lane-strided partial sums, then the fixed shuffle tree
 __global__ void cont_bwd_pass2(const float* __restrict__ ws, int nblk, int C, int K, int gs, float* __restrict__ out) {
     const int W = K + 1, npairs = C * W;
-    int pr = blockIdx.x * blockDim.x + threadIdx.x;
+    const int pr = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (pr >= npairs) return;
     float acc = 0.f;
-    for (int b = 0; b < nblk; ++b) acc += ws[(int64_t) b * npairs + pr];
+    for (int b = lane; b < nblk; b += 32) acc += ws[(int64_t) b * npairs + pr];
+    acc = ctr_warp_sum(acc);
     const int c = pr / W, j = pr - c * W;
-    out[c * gs + j] = acc;
+    if (lane == 0) out[c * gs + j] = acc;
 }
 
 inline int cont_blocks(ctr_handle* h, int B) {
-    int64_t nb = ctr_cdiv(B > 0 ? B : 1, 64);
-    int64_t cap = (int64_t) h->sm_count * 8;
+    int64_t nb = ctr_cdiv(B > 0 ? B : 1, 128);
+    int64_t cap = (int64_t) h->sm_count * 2;
     return (int) (nb < cap ? nb : cap);
 }
 
@@ -324,7 +326,7 @@ extern "C" int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg*
     cont_bwd_pass1<<<nblk, 256, 0, ctr_st(s)>>>(*cfg, cont, cont_rows, sum_e, dlogit, w_fm, (float*) ws);
     CTR_CHECK_LAUNCH(h, "cont_bwd_pass1");
     const int npairs = cfg->C * (cfg->k + 1);
-    cont_bwd_pass2<<<(unsigned) ctr_cdiv(npairs, 128), 128, 0, ctr_st(s)>>>((const float*) ws, nblk, cfg->C, cfg->k,
+    cont_bwd_pass2<<<(unsigned) ctr_cdiv((int64_t) npairs * 32, 256), 256, 0, ctr_st(s)>>>((const float*) ws, nblk, cfg->C, cfg->k,
                                                                           cfg->grad_stride, cont_grad);
     CTR_CHECK_LAUNCH(h, "cont_bwd_pass2");
     return CTR_OK;

@@ -12,7 +12,7 @@ head_fwd_kernel(int B, const float* __restrict__ fm, int64_t fm_ld, int n_fm, co
                 const float* __restrict__ deep, int64_t deep_ld, int H, const float* __restrict__ w_deep,
                 const float* __restrict__ extra, const float* __restrict__ bias, const float* __restrict__ label,
                 float* __restrict__ logit, float* __restrict__ score, float* __restrict__ dlogit,
-                float* __restrict__ loss_part) {
+                float* __restrict__ dz_last, int64_t lddz, float* __restrict__ loss_part) {
     __shared__ float wl[8];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int64_t b = (int64_t) blockIdx.x * 8 + w;
@@ -38,8 +38,15 @@ head_fwd_kernel(int B, const float* __restrict__ fm, int64_t fm_ld, int n_fm, co
             const float y = label[b];
             l = -y * logf(p + LOG_LOSS_EPS) - (1.f - y) * logf(1.f - p + LOG_LOSS_EPS);
             // d/dz [ -y log(p+e) - (1-y) log(1-p+e) ] = (-y/(p+e) + (1-y)/(1-p+e)) * p(1-p), mean over B
-            if (lane == 0 && dlogit)
-                dlogit[b] = (-y / (p + LOG_LOSS_EPS) + (1.f - y) / (1.f - p + LOG_LOSS_EPS)) * p * (1.f - p) / (float) B;
+            const float dl = (-y / (p + LOG_LOSS_EPS) + (1.f - y) / (1.f - p + LOG_LOSS_EPS)) * p * (1.f - p) / (float) B;
+            if (lane == 0 && dlogit) dlogit[b] = dl;
+            if (dz_last && H > 0) {
+                // gradient through the last ReLU, written while the row is still cache-hot:
+                // dZ_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)
+                const float* r = deep + b * deep_ld;
+                float* o = dz_last + b * lddz;
+                for (int j = lane; j < H; j += 32) o[j] = r[j] > 0.f ? dl * w_deep[j] : 0.f;
+            }
         }
     }
     if (label && loss_part) {
@@ -105,19 +112,14 @@ colsum_pass1(const float* __restrict__ X, int64_t ldx, int B, int ncols, const f
     ws[(int64_t) blockIdx.y * ncols + col] = (a0 + a1) + (a2 + a3);
 }
 
-__global__ void __launch_bounds__(128) colsum_pass2(const float* __restrict__ ws, int nslices, int ncols, float* __restrict__ out) {
-    const int col = blockIdx.x * 128 + threadIdx.x;
+// one warp per column: lane-strided sum over the slices, then the fixed shuffle tree
+__global__ void __launch_bounds__(256) colsum_pass2(const float* __restrict__ ws, int nslices, int ncols, float* __restrict__ out) {
+    const int col = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (col >= ncols) return;
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    int s = 0;
-    for (; s + 4 <= nslices; s += 4) {
-        a0 += ws[(int64_t) s * ncols + col];
-        a1 += ws[(int64_t) (s + 1) * ncols + col];
-        a2 += ws[(int64_t) (s + 2) * ncols + col];
-        a3 += ws[(int64_t) (s + 3) * ncols + col];
-    }
-    for (; s < nslices; ++s) a0 += ws[(int64_t) s * ncols + col];
-    out[col] = (a0 + a1) + (a2 + a3);
+    float a = 0.f;
+    for (int s = lane; s < nslices; s += 32) a += ws[(int64_t) s * ncols + col];
+    a = ctr_warp_sum(a);
+    if (lane == 0) out[col] = a;
 }
 
 }  // namespace
@@ -125,7 +127,7 @@ __global__ void __launch_bounds__(128) colsum_pass2(const float* __restrict__ ws
 extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, const float* fm, int64_t fm_ld, int n_fm,
                             const float* w_fm, const float* deep, int64_t deep_ld, int H, const float* w_deep,
                             const float* extra, const float* bias, const float* label, float* logit, float* score,
-                            float* dlogit, float* loss_out, void* ws, int64_t ws_bytes) {
+                            float* dlogit, float* dz_last, int64_t lddz, float* loss_out, void* ws, int64_t ws_bytes) {
     CTR_REQUIRE(h, B >= 0 && n_fm >= 0 && H >= 0, "head_fwd: negative sizes");
     CTR_REQUIRE(h, n_fm == 0 || (fm && w_fm), "head_fwd: fm inputs null");
     CTR_REQUIRE(h, H == 0 || (deep && w_deep), "head_fwd: deep inputs null");
@@ -138,7 +140,7 @@ extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, const float* fm,
         part = (float*) ws;
     }
     head_fwd_kernel<<<nblk, 256, 0, ctr_st(s)>>>(B, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra, bias, label,
-                                                 logit, score, dlogit, part);
+                                                 logit, score, dlogit, dz_last, lddz, part);
     CTR_CHECK_LAUNCH(h, "head_fwd");
     if (part) {
         loss_final_kernel<<<1, 1024, 0, ctr_st(s)>>>(part, nblk, B, loss_out);
@@ -171,7 +173,7 @@ extern "C" int ctr_colsum(ctr_handle* h, ctr_stream s, const float* X, int64_t l
     dim3 grid((unsigned) ctr_cdiv(ncols, 128), (unsigned) nsl);
     colsum_pass1<<<grid, 128, 0, ctr_st(s)>>>(X, ldx, B, ncols, w, (float*) ws);
     CTR_CHECK_LAUNCH(h, "colsum_pass1");
-    colsum_pass2<<<(unsigned) ctr_cdiv(ncols, 128), 128, 0, ctr_st(s)>>>((const float*) ws, nsl, ncols, out);
+    colsum_pass2<<<(unsigned) ctr_cdiv((int64_t) ncols * 32, 256), 256, 0, ctr_st(s)>>>((const float*) ws, nsl, ncols, out);
     CTR_CHECK_LAUNCH(h, "colsum_pass2");
     return CTR_OK;
 }

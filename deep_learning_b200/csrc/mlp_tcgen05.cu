@@ -7,9 +7,9 @@
 //              wgrad    (A = X, B = dZ, R = batch)
 //
 // One CTA owns a 128-row output panel across the WHOLE N extent (N <= 512 fp32 accumulator columns =
-// all of TMEM), so the A panel is streamed from HBM exactly once.  Warp roles: warps 0-3 epilogue
-// (TMEM lane quarter = warp id), warp 4 = TMA producer (one elected lane), warp 5 = MMA issuer (one
-// elected lane).  Operands are staged by TMA into 128B-swizzled shared memory through a 3-stage
+// all of TMEM), so the A panel is streamed from HBM exactly once.  Warp roles: warps 0-7 epilogue
+// (TMEM lane quarter = warp id & 3, alternate 32-column chunks), warp 8 = TMA producer (one elected
+// lane), warp 9 = MMA issuer (one elected lane).  Operands are staged by TMA into 128B-swizzled shared memory through a 3-stage
 // mbarrier ring; accumulators live in TMEM and are read back with tcgen05.ld for the fused epilogue.
 #include <cuda.h>
 #include "ctr_common.cuh"
@@ -20,7 +20,8 @@ constexpr int BLOCK_M = 128;
 constexpr int BLOCK_R = 32;            // reduction elements per stage: 32 fp32 = one 128B swizzle row
 constexpr int UMMA_K = 8;              // tf32: 32 bytes of reduction per instruction
 constexpr int MAX_N = 512;             // fp32 accumulator columns in TMEM
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 320;           // warps 0-7 epilogue, 8 TMA producer, 9 MMA issuer
+constexpr int TMA_WARP = 8, MMA_WARP = 9;
 constexpr int SMEM_LIMIT = 227 * 1024;
 
 // ------------------------------------------------------------------------------------ PTX wrappers
@@ -74,17 +75,6 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint6
 // arrive on an mbarrier once every MMA issued so far by this thread has completed
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
-    uint32_t r[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 __device__ __forceinline__ bool elect_one() {
     uint32_t pred = 0;
@@ -141,39 +131,102 @@ struct alignas(8) PipeBars {
 
 namespace {
 
-// ---- epilogue shared by both kernels: TMEM -> registers -> (bias / ReLU / dropout / mask) -> global
-__device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int warp, int lane, int m0, int M, int N, float* C,
+// ---- epilogue shared by both kernels: TMEM -> registers -> (bias / ReLU / dropout / mask) -> global.
+// 8 warps: warp e owns TMEM lane quarter (e & 3) and every second 32-column chunk starting at (e >> 2).
+// All per-element work stays in registers (fully unrolled, compile-time flags); the mask / bias loads
+// of a chunk are issued before the TMEM load is waited on.
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+template <bool BIAS, bool RELU, bool MASK>
+__device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
                                               int64_t ldc, const EpiParams& ep) {
-    const int row = m0 + warp * 32 + lane;
+    const int q = ewarp & 3, half = ewarp >> 2;
+    const int row = m0 + q * 32 + lane;
     const bool row_ok = row < M;
     const bool vec_ok = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
-    const uint32_t lane_addr = tmem_base + ((uint32_t) (warp * 32) << 16);
-    for (int c0 = 0; c0 < N; c0 += 16) {
-        float v[16];
-        tmem_ld16(lane_addr + (uint32_t) c0, v);      // .sync.aligned: every lane takes part, valid row or not
-        if (!row_ok) continue;
-        const int nc = (N - c0) < 16 ? (N - c0) : 16;
+    const bool mvec_ok = MASK && (ep.ldmask % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.mask) & 15) == 0);
+    const bool bvec_ok = BIAS && ((reinterpret_cast<uintptr_t>(ep.bias) & 15) == 0);
+    const bool dropout = ep.keep < 1.f;
+    const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
+    const int nchunks = (N + 31) / 32;
+    for (int c = half; c < nchunks; c += 2) {
+        const int c0 = c * 32;
+        uint32_t r[32];
+        tmem_ld32_issue(lane_addr + (uint32_t) c0, r);   // .sync.aligned: every lane takes part, valid row or not
+        const bool full = c0 + 32 <= N;
+        float mk[32];
+        if (MASK) {
+            const float* mrow = ep.mask + (int64_t) row * ep.ldmask + c0;
+            if (row_ok && full && mvec_ok) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            if (i < nc) {
-                const int col = c0 + i;
-                float x = v[i];
-                if (ep.bias) x += __ldg(ep.bias + col);
-                if (ep.relu) x = x > 0.f ? x : 0.f;
-                if (ep.keep < 1.f) x = dropout_u01(ep.seed, (uint64_t) row * (uint64_t) N + col) < ep.keep ? x / ep.keep : 0.f;
-                if (ep.mask) x = ep.mask[(int64_t) row * ep.ldmask + col] > 0.f ? x * ep.mask_scale : 0.f;
-                v[i] = x;
+                for (int i = 0; i < 8; ++i) {
+                    const float4 t = __ldg(reinterpret_cast<const float4*>(mrow) + i);
+                    mk[4 * i] = t.x; mk[4 * i + 1] = t.y; mk[4 * i + 2] = t.z; mk[4 * i + 3] = t.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) mk[i] = (row_ok && c0 + i < N) ? mrow[i] : 0.f;
             }
         }
-        float* dst = C + (int64_t) row * ldc + c0;
-        if (vec_ok && nc == 16) {
+        float bs[32];
+        if (BIAS) {
+            if (full && bvec_ok) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
+                for (int i = 0; i < 8; ++i) {
+                    const float4 t = __ldg(reinterpret_cast<const float4*>(ep.bias + c0) + i);
+                    bs[4 * i] = t.x; bs[4 * i + 1] = t.y; bs[4 * i + 2] = t.z; bs[4 * i + 3] = t.w;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 32; ++i) bs[i] = (c0 + i < N) ? __ldg(ep.bias + c0 + i) : 0.f;
+            }
+        }
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            float x = __uint_as_float(r[i]);
+            if (BIAS) x += bs[i];
+            if (RELU) x = fmaxf(x, 0.f);
+            if (MASK) x = mk[i] > 0.f ? x * ep.mask_scale : 0.f;
+            v[i] = x;
+        }
+        if (dropout) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                v[i] = dropout_u01(ep.seed, (uint64_t) row * (uint64_t) N + (c0 + i)) < ep.keep ? v[i] / ep.keep : 0.f;
+        }
+        if (!row_ok) continue;
+        float* dst = C + (int64_t) row * ldc + c0;
+        if (vec_ok && full) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
                 reinterpret_cast<float4*>(dst)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
         } else {
-            for (int i = 0; i < nc; ++i) dst[i] = v[i];
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (c0 + i < N) dst[i] = v[i];
         }
     }
+}
+
+__device__ __forceinline__ void epilogue_dispatch(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
+                                                  int64_t ldc, const EpiParams& ep) {
+    if (ep.mask) epilogue_rows<false, false, true>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep);
+    else if (ep.bias && ep.relu) epilogue_rows<true, true, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep);
+    else if (ep.bias) epilogue_rows<true, false, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep);
+    else if (ep.relu) epilogue_rows<false, true, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep);
+    else epilogue_rows<false, false, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep);
 }
 
 __device__ __forceinline__ PipeBars* setup_cta(uint8_t* smem, int nstages, int stage_bytes, uint32_t tmem_cols, int warp) {
@@ -186,7 +239,7 @@ __device__ __forceinline__ PipeBars* setup_cta(uint8_t* smem, int nstages, int s
         mbar_init(&bars->tmem_full, 1);
         fence_barrier_init();
     }
-    if (warp == 4) tmem_alloc(&bars->tmem_base, tmem_cols);
+    if (warp == TMA_WARP) tmem_alloc(&bars->tmem_base, tmem_cols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -208,7 +261,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     PipeBars* bars = setup_cta(smem, nstages, stage_bytes, tmem_cols, warp);
     const uint32_t tmem_base = bars->tmem_base;
 
-    if (warp == 4) {
+    if (warp == TMA_WARP) {
         if (elect_one()) {
             prefetch_tmap(&tmA);
             prefetch_tmap(&tmB);
@@ -223,7 +276,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     tma_load_2d(sa + a_bytes + (size_t) i * n_each * BLOCK_R * 4, &tmB, &bars->full[s], kb * BLOCK_R, i * n_each);
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == MMA_WARP) {
         if (elect_one()) {
             const uint32_t idesc = make_idesc(BLOCK_M, n_each, 0, 0);
             for (int kb = 0; kb < num_kb; ++kb) {
@@ -248,11 +301,11 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else {
         mbar_wait(&bars->tmem_full, 0);
         tc_fence_after();
-        epilogue_rows(tmem_base, warp, lane, m0, M, N, C, ldc, ep);
+        epilogue_dispatch(tmem_base, warp, lane, m0, M, N, C, ldc, ep);
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) tmem_dealloc(tmem_base, tmem_cols);
+    if (warp == TMA_WARP) tmem_dealloc(tmem_base, tmem_cols);
 }
 
 // ---- C_split[M,N] = A[R,M]^T * B[R,N] over this CTA's slice of R ; MN-major tf32 tiles (32B-atom swizzle)
@@ -273,7 +326,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     PipeBars* bars = setup_cta(smem, nstages, stage_bytes, tmem_cols, warp);
     const uint32_t tmem_base = bars->tmem_base;
 
-    if (warp == 4) {
+    if (warp == TMA_WARP) {
         if (elect_one()) {
             prefetch_tmap(&tmA);
             prefetch_tmap(&tmB);
@@ -288,7 +341,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 for (int j = 0; j < nbx; ++j) tma_load_2d(sa + a_bytes + j * BOX_BYTES, &tmB, &bars->full[s], j * 32, r0);
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == MMA_WARP) {
         if (elect_one()) {
             const uint32_t idesc1 = make_idesc(BLOCK_M, n1, 1, 1);
             const uint32_t idesc2 = make_idesc(BLOCK_M, n2 > 0 ? n2 : 16, 1, 1);
@@ -321,15 +374,15 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_wait(&bars->tmem_full, 0);
             tc_fence_after();
             EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f};
-            epilogue_rows(tmem_base, warp, lane, m0, M, N, Cz, N, ep);
+            epilogue_rows<false, false, false>(tmem_base, warp, lane, m0, M, N, Cz, N, ep);
         } else {                                   // empty slice: contribute zeros
-            const int row = m0 + warp * 32 + lane;
-            if (row < M) for (int c = 0; c < N; ++c) Cz[(size_t) row * N + c] = 0.f;
+            const int row = m0 + (warp & 3) * 32 + lane;
+            if (row < M) for (int c = (warp >> 2); c < N; c += 2) Cz[(size_t) row * N + c] = 0.f;
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) tmem_dealloc(tmem_base, tmem_cols);
+    if (warp == TMA_WARP) tmem_dealloc(tmem_base, tmem_cols);
 }
 
 }  // namespace

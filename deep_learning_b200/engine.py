@@ -307,8 +307,9 @@ class CtrEngine:
         lab = self.label if with_loss else None
         h.call("ctr_head_fwd", st, B, ptr(self.fm), s.fm_ld, s.n_fm, ptr(w_fm), ptr(x), ldx, s.hidden[-1], ptr(w_deep),
                ptr(extra), ptr(bias), ptr(lab), ptr(self.logit), ptr(self.score),
-               ptr(self.dlogit) if with_loss else None, ptr(self.loss) if with_loss else None, ptr(self.ws),
-               self.ws.numel())
+               ptr(self.dlogit) if with_loss else None,
+               ptr(self.dz[0]) if (with_loss and self.train_mode) else None, s.hidden[-1],
+               ptr(self.loss) if with_loss else None, ptr(self.ws), self.ws.numel())
 
     def _reg_loss(self) -> torch.Tensor:
         """regulariser terms of the reported loss (models/deepfm.py:155-156, models/wdl.py:268-275,
@@ -350,9 +351,7 @@ class CtrEngine:
         h.call("ctr_reduce", st, ptr(self.dlogit), B, 0, ptr(g_bias), ws, wsn)
         if s.head == "wdl":
             self._wdl_wide_grad(B)
-        # through the last ReLU
-        dz = self.dz[0]
-        h.call("ctr_head_bwd_deep", st, B, H, ptr(self.dlogit), ptr(w_deep), ptr(last), H, ptr(dz), H)
+        # dz[0] already holds the gradient through the last ReLU (written by ctr_head_fwd)
         cur = 0
         for i in range(L - 1, -1, -1):
             k_, h_ = dims[i]

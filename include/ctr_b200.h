@@ -154,13 +154,15 @@ int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, fl
  *   score    = sigmoid(logit)
  *   loss     = mean_b( -y log(score+eps) - (1-y) log(1-score+eps) )        (label != NULL)
  *   dlogit[b]= dloss/dlogit[b]                                              (label != NULL)
+ *   dz_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)   (optional: the gradient through the last ReLU,
+ *                                                            written while the row is cache-hot)
  * loss_out: one float, written by a second deterministic reduction pass. ws >= 4*(ceil(B/256)+1) B */
 int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B,
                  const float* fm, int64_t fm_ld, int n_fm, const float* w_fm,
                  const float* deep, int64_t deep_ld, int H, const float* w_deep,
                  const float* extra, const float* bias,
-                 const float* label, float* logit, float* score, float* dlogit, float* loss_out,
-                 void* ws, int64_t ws_bytes);
+                 const float* label, float* logit, float* score, float* dlogit, float* dz_last, int64_t lddz,
+                 float* loss_out, void* ws, int64_t ws_bytes);
 /* dZ_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)        (through the last ReLU) */
 int ctr_head_bwd_deep(ctr_handle* h, ctr_stream s, int B, int H, const float* dlogit, const float* w_deep,
                       const float* deep, int64_t deep_ld, float* dZ, int64_t lddz);
