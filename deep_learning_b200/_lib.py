@@ -70,8 +70,9 @@ _PROTOS = {
     "ctr_embed_bwd_finalize": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "ctr_cont_bwd_ws_bytes": (c_i64, [c_vp, _P_CFG]),
     "ctr_fm_cont_bwd": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
+    "ctr_adam_rows_ws_bytes": (c_i64, [c_vp, c_i64]),
     "ctr_adam_rows": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp,
-                              c_i32, c_i64, c_vp, _P_HP]),
+                              c_i32, c_i64, c_vp, c_vp, c_i64, _P_HP]),
     "ctr_adam_dense": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_f32, c_f32, c_vp, c_i32, _P_HP]),
     "ctr_auc_ws_bytes": (c_i64, [c_vp, c_i64]),
     "ctr_auc": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i64]),
@@ -136,12 +137,13 @@ class Handle:
         if tm is not None:
             import torch
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()          # torch's current stream == `stream` (engine passes current_stream)
+            ts = torch.cuda.ExternalStream(stream) if stream else torch.cuda.current_stream()
+            e0.record(ts)        # events go on the stream the kernel is launched on
         rc = getattr(self.lib, name)(self.h, stream, *args)
         if rc != 0:
             raise CtrError("%s failed (%d): %s" % (name, rc, self.lib.ctr_last_error(self.h).decode()))
         if tm is not None:
-            e1.record()
+            e1.record(ts)
             tm.append((e0, e1))
 
     @property

@@ -8,6 +8,7 @@
 namespace {
 
 constexpr int CH = CTR_BWD_CHUNK;
+constexpr int LONG_RUN = 8;   // runs with more partials than this take the warp-cooperative path
 
 template <int K>
 __global__ void __launch_bounds__(256)
@@ -136,7 +137,7 @@ __global__ void __launch_bounds__(256)
 adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restrict__ n_rows, int64_t n_max, uint32_t mask,
                  const float* __restrict__ grads, const uint32_t* __restrict__ seg_start, int gs, int width,
                  float* __restrict__ table, float* __restrict__ m, float* __restrict__ v, int stride, int64_t table_rows,
-                 uint8_t* __restrict__ touched, const ctr_adam_hp hp) {
+                 uint8_t* __restrict__ touched, uint32_t* __restrict__ long_list, const ctr_adam_hp hp) {
     int64_t U = n_rows ? (int64_t) *n_rows : n_max;
     if (U > n_max) U = n_max;
     const int64_t total = U * width;
@@ -147,6 +148,14 @@ adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restric
         if (key == CTR_PAD_KEY) continue;
         const int64_t row = (int64_t) (key & mask);
         if (row >= table_rows) continue;   // defensive: never write outside the table
+        if (seg_start && long_list) {
+            // runs spread over many chunks (hot rows) go to the warp-cooperative kernel
+            const int64_t np = (int64_t) ((seg_start[u + 1] - 1) / CH) - (int64_t) (seg_start[u] / CH) + 1;
+            if (np > LONG_RUN) {
+                if (j == 0) long_list[1 + atomicAdd(long_list, 1u)] = (uint32_t) u;
+                continue;
+            }
+        }
         float g = seg_start ? sum_run_partials(grads, seg_start, u, j, gs) : grads[u * gs + j];
         const int64_t o = row * stride + j;
         const float mm = hp.beta1 * m[o] + (1.f - hp.beta1) * g;
@@ -155,6 +164,66 @@ adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restric
         v[o] = vv;
         table[o] -= hp.lr_t * mm / (sqrtf(vv) + hp.eps);
         if (j == 0 && touched) touched[row] = 1;
+    }
+}
+
+// hot rows: one warp per run.  Lane l sums partial rows l, l+32, ... for ALL coordinates at once
+// (128-bit loads of the contiguous [np, gs] block), then a fixed shuffle tree: deterministic.
+constexpr int MAX_GS4 = 9;   // grad_stride / 4 for k = 32 with a first-order column
+__global__ void __launch_bounds__(256)
+adam_rows_long_kernel(const uint32_t* __restrict__ row_ids, uint32_t mask, const float* __restrict__ part,
+                      const uint32_t* __restrict__ seg_start, int gs, int width, float* __restrict__ table,
+                      float* __restrict__ m, float* __restrict__ v, int stride, int64_t table_rows,
+                      uint8_t* __restrict__ touched, const uint32_t* __restrict__ long_list, const ctr_adam_hp hp) {
+    const int lane = threadIdx.x & 31;
+    const int gs4 = gs >> 2;
+    const uint32_t nlong = long_list[0];
+    const int64_t nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
+    for (int64_t w = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < nlong; w += nwarps) {
+        const int64_t u = long_list[1 + w];
+        const uint32_t s = seg_start[u], e = seg_start[u + 1];
+        const int64_t c0 = s / CH, np = (int64_t) ((e - 1) / CH) - c0 + 1;
+        const float4* base = reinterpret_cast<const float4*>(part + (u + c0) * gs);
+        float4 acc[MAX_GS4];
+#pragma unroll
+        for (int q = 0; q < MAX_GS4; ++q) acc[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int64_t i = lane; i < np; i += 32) {
+#pragma unroll
+            for (int q = 0; q < MAX_GS4; ++q) {
+                if (q < gs4) {
+                    const float4 t = base[i * gs4 + q];
+                    acc[q].x += t.x; acc[q].y += t.y; acc[q].z += t.z; acc[q].w += t.w;
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < MAX_GS4; ++q) {
+            if (q < gs4) {
+                acc[q].x = ctr_warp_sum(acc[q].x); acc[q].y = ctr_warp_sum(acc[q].y);
+                acc[q].z = ctr_warp_sum(acc[q].z); acc[q].w = ctr_warp_sum(acc[q].w);
+            }
+        }
+        const uint32_t key = row_ids[u];
+        const int64_t row = (int64_t) (key & mask);
+        if (key == CTR_PAD_KEY || row >= table_rows) continue;
+        // lane j applies Adam to coordinate j (j + 32 for very wide rows)
+        for (int j = lane; j < width; j += 32) {
+            float g = 0.f;
+#pragma unroll
+            for (int q = 0; q < MAX_GS4; ++q) {
+                if (q == (j >> 2)) {
+                    const int r = j & 3;
+                    g = r == 0 ? acc[q].x : (r == 1 ? acc[q].y : (r == 2 ? acc[q].z : acc[q].w));
+                }
+            }
+            const int64_t o = row * stride + j;
+            const float mm = hp.beta1 * m[o] + (1.f - hp.beta1) * g;
+            const float vv = hp.beta2 * v[o] + (1.f - hp.beta2) * g * g;
+            m[o] = mm;
+            v[o] = vv;
+            table[o] -= hp.lr_t * mm / (sqrtf(vv) + hp.eps);
+        }
+        if (lane == 0 && touched) touched[row] = 1;
     }
 }
 
@@ -278,19 +347,37 @@ extern "C" int ctr_embed_bwd_finalize(ctr_handle* h, ctr_stream s, const uint32_
     return CTR_OK;
 }
 
+// a run with more than LONG_RUN partials holds more than (LONG_RUN - 1) * CH lookups
+extern "C" int64_t ctr_adam_rows_ws_bytes(ctr_handle*, int64_t n_max) {
+    return 4 * (n_max / ((LONG_RUN - 1) * CH) + 4) + 256;
+}
+
 extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
                              int local_bits, const float* grads, const uint32_t* seg_start, int grad_stride, int width,
                              float* table, float* m, float* v, int table_stride, int64_t table_rows,
-                             uint8_t* touched, const ctr_adam_hp* hp) {
+                             uint8_t* touched, void* ws, int64_t ws_bytes, const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, row_ids && grads && table && m && v && hp, "adam_rows: null pointer");
     CTR_REQUIRE(h, width > 0 && grad_stride >= width && table_stride >= width && n_max >= 0 && table_rows > 0,
                 "adam_rows: bad sizes");
     if (n_max == 0) return CTR_OK;
     uint32_t mask = (local_bits <= 0 || local_bits >= 32) ? 0xFFFFFFFFu : ((1u << local_bits) - 1u);
+    uint32_t* long_list = nullptr;
+    if (seg_start) {
+        CTR_REQUIRE(h, grad_stride % 4 == 0 && grad_stride / 4 <= MAX_GS4, "adam_rows: grad_stride must be a multiple of 4, <= 36");
+        if (!ws || ws_bytes < ctr_adam_rows_ws_bytes(h, n_max)) return ctr_fail(h, CTR_E_WORKSPACE, "adam_rows: ws too small");
+        long_list = (uint32_t*) ws;
+        CTR_CUDA(h, cudaMemsetAsync(long_list, 0, 4, ctr_st(s)));
+    }
     adam_rows_kernel<<<grid_for(h, n_max * width), 256, 0, ctr_st(s)>>>(row_ids, n_rows, n_max, mask, grads, seg_start,
                                                                          grad_stride, width, table, m, v, table_stride,
-                                                                         table_rows, touched, *hp);
+                                                                         table_rows, touched, long_list, *hp);
     CTR_CHECK_LAUNCH(h, "adam_rows");
+    if (long_list) {
+        adam_rows_long_kernel<<<(unsigned) h->sm_count * 4, 256, 0, ctr_st(s)>>>(row_ids, mask, grads, seg_start, grad_stride,
+                                                                                 width, table, m, v, table_stride, table_rows,
+                                                                                 touched, long_list, *hp);
+        CTR_CHECK_LAUNCH(h, "adam_rows_long");
+    }
     return CTR_OK;
 }
 

@@ -108,7 +108,13 @@ class CtrEngine:
             self.cont_grad = torch.zeros(max(s.C, 1), s.grad_stride, **f32)
             self.touched = torch.zeros(s.table_rows, dtype=torch.uint8, device=dev) if adam_mode == "tf_dense" else None
             cfg = self._cfg(B)
-            ws_bytes = max(ws_bytes, self.h.query("ctr_sort_ws_bytes", n), self.h.query("ctr_cont_bwd_ws_bytes", cfg),
+            # the id sort depends only on the batch: it runs on a side stream underneath the forward pass
+            self.side = torch.cuda.Stream(device=dev)
+            self.ev_batch, self.ev_sorted = torch.cuda.Event(), torch.cuda.Event()
+            self.ws_sort = torch.zeros(_ru(max(self.h.query("ctr_sort_ws_bytes", n), 4 * (n // 2048 + 8)), 256),
+                                       dtype=torch.uint8, device=dev)
+            ws_bytes = max(ws_bytes, self.h.query("ctr_cont_bwd_ws_bytes", cfg),
+                           self.h.query("ctr_adam_rows_ws_bytes", n),
                            4 * (n // 2048 + 8))
             for (k_, h_) in self._layer_dims():
                 ws_bytes = max(ws_bytes, self.h.query("ctr_mlp_bwd_weight_ws_bytes", self.prec, B, k_, h_))
@@ -219,16 +225,23 @@ class CtrEngine:
                 blk[:, s.k] = torch.rand(r1 - r0, generator=g, device=self.dev)
 
     def get_weights(self) -> Dict[str, np.ndarray]:
+        return self._dump(self.table, self.theta)
+
+    def get_optimizer_state(self):
+        """(m, v) dicts named/shaped like the variables (the Adam slots tf.train.Saver would store)"""
+        return self._dump(self.m_table, self.m), self._dump(self.v_table, self.v)
+
+    def _dump(self, table: torch.Tensor, flat: torch.Tensor) -> Dict[str, np.ndarray]:
         s, st = self.spec, self._stream()
         out: Dict[str, np.ndarray] = {}
         emb = torch.empty(s.table_rows, s.k, dtype=torch.float32, device=self.dev)
         first = torch.empty(s.table_rows, dtype=torch.float32, device=self.dev) if s.has_first else None
-        self.h.call("ctr_table_unpack", st, ptr(self.table), s.table_rows, s.k, s.table_stride, ptr(emb), ptr(first))
+        self.h.call("ctr_table_unpack", st, ptr(table), s.table_rows, s.k, s.table_stride, ptr(emb), ptr(first))
         out[s.emb_name] = emb.cpu().numpy()
         if s.has_first:
             out[s.first_name] = first.cpu().numpy().reshape(-1, 1)
         for name, shp in self.dense_shapes:
-            a = self.view(name).cpu().numpy().reshape(shp).copy()
+            a = self.view(name, flat).cpu().numpy().reshape(shp).copy()
             if name == "deep_0":
                 inv = np.empty_like(s.deep0_perm()); inv[s.deep0_perm()] = np.arange(len(inv))
                 a = a[inv, :]
@@ -370,11 +383,7 @@ class CtrEngine:
         # ---- sparse side: sort -> runs -> partials -> Adam on touched rows ------------------------------
         if s.ids_ld:
             n = B * s.ids_ld + self.n_extra
-            key_bits = max(1, int(s.table_rows - 1).bit_length())
-            h.call("ctr_sort_ids", st, ptr(self.ids), self.id_bytes, B, s.ids_ld, 0, s.ids_ld, 0, int(s.zero_row0),
-                   s.cont_base, self.n_extra, 1, 0, key_bits, ptr(self.keys), ptr(self.perm), ws, wsn)
-            h.call("ctr_unique_segments", st, ptr(self.keys), n, ptr(self.uniq), ptr(self.seg_start), ptr(self.uidx),
-                   ptr(self.n_unique), ws, wsn)
+            torch.cuda.current_stream(self.dev).wait_event(self.ev_sorted)
             if self.n_extra:
                 h.call("ctr_fm_cont_bwd", st, cfg, ptr(self.cont), ptr(self.table[s.cont_base:]), ptr(self.sum_e),
                        ptr(self.dlogit), ptr(w_fm), ptr(self.cont_grad), ws, wsn)
@@ -383,7 +392,7 @@ class CtrEngine:
                    ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.part))
             h.call("ctr_adam_rows", st, ptr(self.uniq), ptr(self.n_unique), n, 0, ptr(self.part), ptr(self.seg_start),
                    s.grad_stride, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
-                   s.table_rows, ptr(self.touched), hp)
+                   s.table_rows, ptr(self.touched), ws, wsn, hp)
         if self.adam_mode == "tf_dense":
             # TF1 Adam moves EVERY row each step (m, v decay; theta -= lr_t*m/(sqrt(v)+eps)) -- exact mode
             h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
@@ -399,6 +408,24 @@ class CtrEngine:
         self.beta2_power *= ADAM_BETA2
         self.global_step += 1
 
+    def _launch_sort(self, B: int) -> None:
+        """sort ids -> (keys, perm), run-length structure -> (uniq, seg_start, uidx, n_unique); enqueued on
+        the side stream right after the batch upload so it overlaps the forward pass"""
+        s, h = self.spec, self.h
+        if not s.ids_ld:
+            return
+        main = torch.cuda.current_stream(self.dev)
+        self.ev_batch.record(main)
+        self.side.wait_event(self.ev_batch)
+        n = B * s.ids_ld + self.n_extra
+        key_bits = max(1, int(s.table_rows - 1).bit_length())
+        st, ws, wsn = self.side.cuda_stream, ptr(self.ws_sort), self.ws_sort.numel()
+        h.call("ctr_sort_ids", st, ptr(self.ids), self.id_bytes, B, s.ids_ld, 0, s.ids_ld, 0, int(s.zero_row0),
+               s.cont_base, self.n_extra, 1, 0, key_bits, ptr(self.keys), ptr(self.perm), ws, wsn)
+        h.call("ctr_unique_segments", st, ptr(self.keys), n, ptr(self.uniq), ptr(self.seg_start), ptr(self.uidx),
+               ptr(self.n_unique), ws, wsn)
+        self.ev_sorted.record(self.side)
+
     def _wdl_wide_grad(self, B: int) -> None:
         raise NotImplementedError("wdl training lands with the scalar segment-gradient kernel")
 
@@ -409,6 +436,7 @@ class CtrEngine:
         if not self.train_mode:
             raise _lib.CtrError("engine was created with train=False")
         B = self.load_batch(batch) if batch is not None else self.last_batch
+        self._launch_sort(B)
         self.forward(B, with_loss=True)
         reg = self._reg_loss()
         total = self.loss.clone() if reg is None else self.loss + reg

@@ -240,12 +240,15 @@ int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const
  * rows with id 0xFFFFFFFF are skipped.  `touched` ([R] bytes or NULL) is set to 1 for every updated
  * row (used by the exact dense sweep).  row = (key & local_mask) when local_bits > 0. */
 typedef struct ctr_adam_hp { float lr_t, beta1, beta2, eps; } ctr_adam_hp;
+int64_t ctr_adam_rows_ws_bytes(ctr_handle* h, int64_t n_max);
 int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
                   int local_bits, const float* grads, const uint32_t* seg_start /* non-NULL: `grads` is the
                   partials buffer of ctr_embed_bwd_partials and the run sums are formed inline (fused finalize) */,
                   int grad_stride, int width,
                   float* table, float* m, float* v, int table_stride, int64_t table_rows,
-                  uint8_t* touched, const ctr_adam_hp* hp);
+                  uint8_t* touched, void* ws, int64_t ws_bytes /* ctr_adam_rows_ws_bytes(); needed when seg_start != NULL:
+                  runs spread over many chunks (hot rows) are queued and reduced by one warp each */,
+                  const ctr_adam_hp* hp);
 /* dense TF1 Adam over n floats: g_eff = (g ? g[i] : 0) + l2*theta + l1*sign(theta).
  * skip ([n/skip_group] bytes or NULL): elements whose group flag is 1 are left alone and the flag is
  * cleared (rows already updated by ctr_adam_rows).  This is the exact `tf_dense` mode: TF1 Adam

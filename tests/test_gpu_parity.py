@@ -56,11 +56,21 @@ def _run_parity(alg, hp, steps, precision="fp32", adam_mode="tf_dense", B=None, 
         loss = float(eng.train_step(b).item())
         assert abs(loss - float(loss_ref)) < tol * max(1.0, abs(float(loss_ref))), "loss step %d" % step
         got = eng.get_weights()
+        got_m, _ = eng.get_optimizer_state()
         for n in p:
             ref = p[n].numpy().reshape(-1)
             err = H.rel_err(got[n].reshape(-1), ref)
             floor = H.rel_err(p32[n].numpy().reshape(-1), ref)
             REPORT.append((alg, precision, adam_mode, step, n, err, floor))
+            if precision == "tf32":
+                # Adam's early steps move a weight by ~lr*sign(g): a TF32-level error on a near-zero gradient can
+                # flip that sign (2*lr on the element), so the max-norm bar is put on the first-moment slot
+                # m (= 0.1*g at step 1, linear in the gradient) and the parameters are bounded in bulk.
+                assert H.rel_err(got_m[n].reshape(-1), st.m[n].numpy().reshape(-1)) < tol, "m slot %s step %d" % (n, step)
+                d = np.abs(got[n].reshape(-1).astype(np.float64) - ref) / max(float(np.max(np.abs(ref))), 1e-30)
+                assert np.percentile(d, 99.9) < tol, "param %s step %d: p99.9 rel err %.3g" % (n, step, np.percentile(d, 99.9))
+                assert float(np.max(np.abs(got[n].reshape(-1) - ref))) <= 2.2 * hp.learning_rate, n
+                continue
             assert err < max(tol, 4 * floor), "param %s step %d: rel err %.3g (fp32 oracle floor %.3g)" % (n, step, err, floor)
         # every step is checked from IDENTICAL state: re-inject the oracle's parameters and Adam slots
         # (rounded to fp32), so a step's bar is not polluted by the previous step's rounding drift
