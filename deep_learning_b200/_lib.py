@@ -18,7 +18,7 @@ class EmbedCfg(C.Structure):
     """mirror of `ctr_embed_cfg` (include/ctr_b200.h)"""
     _fields_ = [(n, c_i32) for n in (
         "B", "id_bytes", "ids_ld", "Fc", "Fm", "M", "C", "V", "k", "has_first", "use_fm", "fm_cont",
-        "zero_row0", "count_rule", "combiner", "table_stride", "x0_ld", "fm_ld", "grad_stride", "reserved")]
+        "zero_row0", "count_rule", "combiner", "table_stride", "x0_ld", "fm_ld", "grad_stride", "round_tf32")]
 
 
 class AdamHP(C.Structure):
@@ -52,9 +52,10 @@ _PROTOS = {
     "ctr_mlp_bwd_weight_ws_bytes": (c_i64, [c_vp, c_i32, c_i32, c_i32, c_i32]),
     "ctr_mlp_bwd_weight": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp,
                                    c_vp, c_i64]),
-    "ctr_transpose": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_i64]),
+    "ctr_transpose": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_i64, c_i32]),
+    "ctr_round_tf32_copy": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64]),
     "ctr_head_fwd": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp,
-                             c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i64]),
+                             c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64]),
     "ctr_head_bwd_deep": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64, c_vp, c_i64]),
     "ctr_colsum_ws_bytes": (c_i64, [c_vp, c_i32, c_i32]),
     "ctr_colsum": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64]),

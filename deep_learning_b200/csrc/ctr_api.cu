@@ -76,7 +76,7 @@ extern "C" int ctr_table_unpack(ctr_handle* h, ctr_stream s, const float* table,
 }
 
 // ------------------------------------------------------------------ transpose [K,N] -> [N,K]
-__global__ void transpose_kernel(const float* __restrict__ in, int K, int N, float* __restrict__ out, int64_t ld_out) {
+__global__ void transpose_kernel(const float* __restrict__ in, int K, int N, float* __restrict__ out, int64_t ld_out, int rnd) {
     __shared__ float tile[32][33];
     int n0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
@@ -86,14 +86,30 @@ __global__ void transpose_kernel(const float* __restrict__ in, int K, int N, flo
     __syncthreads();
     for (int i = threadIdx.y; i < 32; i += blockDim.y) {
         int nn = n0 + i, kk = k0 + threadIdx.x;
-        if (nn < N && kk < K) out[(int64_t) nn * ld_out + kk] = tile[threadIdx.x][i];
+        if (nn < N && kk < K) out[(int64_t) nn * ld_out + kk] = rnd ? ctr_round_tf32(tile[threadIdx.x][i]) : tile[threadIdx.x][i];
     }
 }
 
-extern "C" int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, float* out, int64_t ld_out) {
+__global__ void round_tf32_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t n) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x)
+        out[i] = ctr_round_tf32(in[i]);
+}
+
+extern "C" int ctr_round_tf32_copy(ctr_handle* h, ctr_stream s, const float* in, float* out, int64_t n) {
+    CTR_REQUIRE(h, in && out && n >= 0, "round_tf32_copy: bad args");
+    if (n == 0) return CTR_OK;
+    int64_t blocks = ctr_cdiv(n, 256);
+    if (blocks > (int64_t) h->sm_count * 8) blocks = (int64_t) h->sm_count * 8;
+    round_tf32_kernel<<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(in, out, n);
+    CTR_CHECK_LAUNCH(h, "round_tf32_copy");
+    return CTR_OK;
+}
+
+extern "C" int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, float* out, int64_t ld_out,
+                             int round_tf32) {
     CTR_REQUIRE(h, in && out && K > 0 && N > 0 && ld_out >= K, "transpose: bad args");
     dim3 grid((unsigned) ctr_cdiv(N, 32), (unsigned) ctr_cdiv(K, 32)), block(32, 8);
-    transpose_kernel<<<grid, block, 0, ctr_st(s)>>>(in, K, N, out, ld_out);
+    transpose_kernel<<<grid, block, 0, ctr_st(s)>>>(in, K, N, out, ld_out, round_tf32);
     CTR_CHECK_LAUNCH(h, "transpose");
     return CTR_OK;
 }

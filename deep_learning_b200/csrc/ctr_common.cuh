@@ -73,6 +73,14 @@ __device__ __forceinline__ float ctr_ldg_f1_stream(const float* p) {
     return r;
 }
 
+// round-to-nearest fp32 -> tf32 (10-bit mantissa), kept in an fp32 container.  The tensor core TRUNCATES
+// fp32 operands to tf32; producers on the TF32 path pre-round so the operand error is unbiased (2^-11).
+__device__ __forceinline__ float ctr_round_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
 __device__ __forceinline__ float ctr_warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

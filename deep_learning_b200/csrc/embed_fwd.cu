@@ -48,6 +48,7 @@ fm_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, c
     float* __restrict__ fmrow = USE_FM ? fm + b * (int64_t) cfg.fm_ld : nullptr;
     const bool has_first = cfg.has_first != 0;
     const bool zero0 = cfg.zero_row0 != 0;
+    const bool rnd = cfg.round_tf32 != 0;   // TF32 tower: pre-round the tile the tensor cores will read
 
     float4 as = f4_zero(), aq = f4_zero();
 
@@ -74,7 +75,8 @@ fm_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, c
         for (int u = 0; u < UNR; ++u) {
             if (ok[u]) {
                 int f = f0 + u * RPW + r;
-                *reinterpret_cast<float4*>(x0row + f * K + q * 4) = e[u];
+                *reinterpret_cast<float4*>(x0row + f * K + q * 4) =
+                    rnd ? make_float4(ctr_round_tf32(e[u].x), ctr_round_tf32(e[u].y), ctr_round_tf32(e[u].z), ctr_round_tf32(e[u].w)) : e[u];
                 if (USE_FM) {
                     f4_acc(as, aq, e[u]);
                     if (q == 0) fmrow[f] = w[u];
@@ -85,8 +87,14 @@ fm_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, c
 
     // ---- continuous / vector values -> X0 ----------------------------------------------
     const int cont_col = (Fc + Fm) * K;
-    for (int c = lane; c < C; c += 32) x0row[cont_col + c] = cont[b * (int64_t) C + c];
-    for (int j = lane; j < V; j += 32) x0row[cont_col + C + j] = vec[b * (int64_t) V + j];
+    for (int c = lane; c < C; c += 32) {
+        const float x = cont[b * (int64_t) C + c];
+        x0row[cont_col + c] = rnd ? ctr_round_tf32(x) : x;
+    }
+    for (int j = lane; j < V; j += 32) {
+        const float x = vec[b * (int64_t) V + j];
+        x0row[cont_col + C + j] = rnd ? ctr_round_tf32(x) : x;
+    }
     for (int j = cont_col + C + V + lane; j < cfg.x0_ld; j += 32) x0row[j] = 0.f;
 
     if (!USE_FM) return;
@@ -195,6 +203,7 @@ pooled_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ tabl
                 p = f4_zero();   // tf.div_no_nan
             }
         }
+        if (cfg.round_tf32) p = make_float4(ctr_round_tf32(p.x), ctr_round_tf32(p.y), ctr_round_tf32(p.z), ctr_round_tf32(p.w));
         *reinterpret_cast<float4*>(x0 + b * (int64_t) cfg.x0_ld + (cfg.Fc + j) * K + q * 4) = p;
     }
     if (lane == 0) {

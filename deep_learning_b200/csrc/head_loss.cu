@@ -12,7 +12,7 @@ head_fwd_kernel(int B, const float* __restrict__ fm, int64_t fm_ld, int n_fm, co
                 const float* __restrict__ deep, int64_t deep_ld, int H, const float* __restrict__ w_deep,
                 const float* __restrict__ extra, const float* __restrict__ bias, const float* __restrict__ label,
                 float* __restrict__ logit, float* __restrict__ score, float* __restrict__ dlogit,
-                float* __restrict__ dz_last, int64_t lddz, float* __restrict__ loss_part) {
+                float* __restrict__ dz_last, int64_t lddz, int round_tf32, float* __restrict__ loss_part) {
     __shared__ float wl[8];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int64_t b = (int64_t) blockIdx.x * 8 + w;
@@ -45,7 +45,10 @@ head_fwd_kernel(int B, const float* __restrict__ fm, int64_t fm_ld, int n_fm, co
                 // dZ_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)
                 const float* r = deep + b * deep_ld;
                 float* o = dz_last + b * lddz;
-                for (int j = lane; j < H; j += 32) o[j] = r[j] > 0.f ? dl * w_deep[j] : 0.f;
+                for (int j = lane; j < H; j += 32) {
+                    const float g = r[j] > 0.f ? dl * w_deep[j] : 0.f;
+                    o[j] = round_tf32 ? ctr_round_tf32(g) : g;
+                }
             }
         }
     }
@@ -127,7 +130,8 @@ __global__ void __launch_bounds__(256) colsum_pass2(const float* __restrict__ ws
 extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, const float* fm, int64_t fm_ld, int n_fm,
                             const float* w_fm, const float* deep, int64_t deep_ld, int H, const float* w_deep,
                             const float* extra, const float* bias, const float* label, float* logit, float* score,
-                            float* dlogit, float* dz_last, int64_t lddz, float* loss_out, void* ws, int64_t ws_bytes) {
+                            float* dlogit, float* dz_last, int64_t lddz, int round_tf32, float* loss_out, void* ws,
+                            int64_t ws_bytes) {
     CTR_REQUIRE(h, B >= 0 && n_fm >= 0 && H >= 0, "head_fwd: negative sizes");
     CTR_REQUIRE(h, n_fm == 0 || (fm && w_fm), "head_fwd: fm inputs null");
     CTR_REQUIRE(h, H == 0 || (deep && w_deep), "head_fwd: deep inputs null");
@@ -140,7 +144,7 @@ extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, const float* fm,
         part = (float*) ws;
     }
     head_fwd_kernel<<<nblk, 256, 0, ctr_st(s)>>>(B, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra, bias, label,
-                                                 logit, score, dlogit, dz_last, lddz, part);
+                                                 logit, score, dlogit, dz_last, lddz, round_tf32, part);
     CTR_CHECK_LAUNCH(h, "head_fwd");
     if (part) {
         loss_final_kernel<<<1, 1024, 0, ctr_st(s)>>>(part, nblk, B, loss_out);

@@ -109,6 +109,7 @@ struct EpiParams {
     const float* mask;      // [M, ldmask] or null
     int64_t ldmask;
     float mask_scale;
+    int round_out;          // round outputs to tf32 (they feed the next tensor-core GEMM)
 };
 
 __device__ __forceinline__ float dropout_u01(uint64_t seed, uint64_t idx) {   // same hash as the FP32 path
@@ -200,6 +201,10 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
             if (RELU) x = fmaxf(x, 0.f);
             if (MASK) x = mk[i] > 0.f ? x * ep.mask_scale : 0.f;
             v[i] = x;
+        }
+        if (ep.round_out) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = ctr_round_tf32(v[i]);
         }
         if (dropout) {
 #pragma unroll
@@ -373,7 +378,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (num_kb > 0) {
             mbar_wait(&bars->tmem_full, 0);
             tc_fence_after();
-            EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f};
+            EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f, 0};
             epilogue_rows<false, false, false>(tmem_base, warp, lane, m0, M, N, Cz, N, ep);
         } else {                                   // empty slice: contribute zeros
             const int row = m0 + (warp & 3) * 32 + lane;
@@ -494,14 +499,14 @@ __global__ void __launch_bounds__(256) tc_splitk_reduce(const float* __restrict_
 int ctr_tc_mlp_fwd(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* X, int64_t ldx, const float* Wt,
                    const float* bias, int relu, float keep, uint64_t seed, float* Y, int64_t ldy) {
     // Wt is the K-major copy [N, ldwt] with ldwt = K rounded up to 4 floats (TMA needs 16-byte row pitches)
-    EpiParams ep{bias, relu, keep, seed, nullptr, 0, 1.f};
+    EpiParams ep{bias, relu, keep, seed, nullptr, 0, 1.f, 1};
     return launch_tn(h, st, B, N, K, X, ldx, Wt, ctr_align(K, 4), Y, ldy, ep);
 }
 
 int ctr_tc_mlp_bwd_data(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* dZ, int64_t lddz,
                         const float* W, const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx) {
     // dX[B,K] = dZ[B,N] * W[K,N]^T : W is already reduction-major for this product
-    EpiParams ep{nullptr, 0, 1.f, 0, mask, ldmask, mask_scale};
+    EpiParams ep{nullptr, 0, 1.f, 0, mask, ldmask, mask_scale, 1};
     return launch_tn(h, st, B, K, N, dZ, lddz, W, N, dX, lddx, ep);
 }
 

@@ -68,6 +68,8 @@ class CtrEngine:
         self.shape = dict(self.dense_shapes)
         # K-major copies of the tower weights for the tcgen05 path
         self.wt = [torch.zeros(h_, _ru(k_, 4), **f32) for (k_, h_) in self._layer_dims()] if self.prec == 1 else None
+        # tf32-rounded copies [K, N] the TF32 data-gradient GEMM reads
+        self.wr = [torch.zeros(k_, h_, **f32) for (k_, h_) in self._layer_dims()] if (self.prec == 1 and train) else None
 
         # ---- batch + activations ----------------------------------------------------------------
         self.ids = torch.zeros(B, max(s.ids_ld, 1), dtype=self.id_torch, device=dev)
@@ -135,7 +137,7 @@ class CtrEngine:
                         Fm=s.Fm, M=s.M, C=s.C, V=s.V, k=s.k, has_first=int(s.has_first), use_fm=int(s.use_fm),
                         fm_cont=int(s.fm_cont), zero_row0=int(s.zero_row0), count_rule=0, combiner=0,
                         table_stride=s.table_stride, x0_ld=s.x0_ld, fm_ld=s.fm_ld, grad_stride=s.grad_stride,
-                        reserved=0)
+                        round_tf32=int(self.prec == 1))
 
     def _stream(self) -> int:
         return torch.cuda.current_stream(self.dev).cuda_stream
@@ -149,6 +151,10 @@ class CtrEngine:
 
     def _w(self, i: int, buf=None):
         return self.view("deep_%d" % i, buf)
+
+    def _wd(self, i: int):
+        """weights as read by the data-gradient GEMM (tf32-rounded copy on the TF32 path)"""
+        return self.wr[i] if self.wr is not None else self._w(i)
 
     def _b(self, i: int, buf=None):
         return self.view("deep_bias_%d" % i, buf)
@@ -257,7 +263,9 @@ class CtrEngine:
             return
         st = self._stream()
         for i, (k_, h_) in enumerate(self._layer_dims()):
-            self.h.call("ctr_transpose", st, ptr(self._w(i)), k_, h_, ptr(self.wt[i]), _ru(k_, 4))
+            self.h.call("ctr_transpose", st, ptr(self._w(i)), k_, h_, ptr(self.wt[i]), _ru(k_, 4), 1)
+            if self.wr is not None:
+                self.h.call("ctr_round_tf32_copy", st, ptr(self._w(i)), ptr(self.wr[i]), k_ * h_)
 
     # ---- batch upload ------------------------------------------------------------------------------
     def load_batch(self, batch: Dict, non_blocking: bool = True) -> int:
@@ -321,7 +329,7 @@ class CtrEngine:
         h.call("ctr_head_fwd", st, B, ptr(self.fm), s.fm_ld, s.n_fm, ptr(w_fm), ptr(x), ldx, s.hidden[-1], ptr(w_deep),
                ptr(extra), ptr(bias), ptr(lab), ptr(self.logit), ptr(self.score),
                ptr(self.dlogit) if with_loss else None,
-               ptr(self.dz[0]) if (with_loss and self.train_mode) else None, s.hidden[-1],
+               ptr(self.dz[0]) if (with_loss and self.train_mode) else None, s.hidden[-1], int(self.prec == 1),
                ptr(self.loss) if with_loss else None, ptr(self.ws), self.ws.numel())
 
     def _reg_loss(self) -> torch.Tensor:
@@ -372,12 +380,12 @@ class CtrEngine:
             h.call("ctr_mlp_bwd_weight", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self.dz[cur]), h_,
                    ptr(self._w(i, self.grad)), ptr(self._b(i, self.grad)), ws, wsn)
             if i > 0:
-                h.call("ctr_mlp_bwd_data", st, self.prec, B, k_, h_, ptr(self.dz[cur]), h_, ptr(self._w(i)), ptr(x),
+                h.call("ctr_mlp_bwd_data", st, self.prec, B, k_, h_, ptr(self.dz[cur]), h_, ptr(self._wd(i)), ptr(x),
                        ldx, 1.0, ptr(self.dz[cur ^ 1]), k_)
                 cur ^= 1
             elif s.E:
                 # only the embedding columns of X0 carry parameters: canonical order puts them first
-                h.call("ctr_mlp_bwd_data", st, self.prec, B, s.E, h_, ptr(self.dz[cur]), h_, ptr(self._w(0)), None, 0,
+                h.call("ctr_mlp_bwd_data", st, self.prec, B, s.E, h_, ptr(self.dz[cur]), h_, ptr(self._wd(0)), None, 0,
                        1.0, ptr(self.dx0), self.dx0_ld)
         hp = self._adam_hp()
         # ---- sparse side: sort -> runs -> partials -> Adam on touched rows ------------------------------

@@ -70,7 +70,7 @@ typedef struct ctr_embed_cfg {
     int32_t x0_ld;         /* floats per X0 row (multiple of 4) */
     int32_t fm_ld;         /* floats per fm row */
     int32_t grad_stride;   /* floats per gradient row (multiple of 4, >= k + has_first) */
-    int32_t reserved;
+    int32_t round_tf32;    /* TF32 tower: write X0 rounded-to-nearest tf32 (tensor cores truncate fp32 operands) */
 } ctr_embed_cfg;
 
 /* ---- handle ------------------------------------------------------------------------- */
@@ -125,7 +125,8 @@ int ctr_scalar_gather_sum(ctr_handle* h, ctr_stream s, const float* table, const
 /* ---- K3: MLP tower ---------------------------------------------------------------------
  * replaces the matmul/add/relu/dropout loop (models/deepfm.py:121-126) and what
  * AdamOptimizer.minimize differentiates through it (models/deepfm.py:161).
- * precision: 0 = FP32 SIMT (tight 1e-5 checks), 1 = TF32 tcgen05/TMA (2e-3).
+ * precision: 0 = FP32 SIMT (tight 1e-5 checks), 1 = TF32 tcgen05/TMA (2e-3; outputs are written rounded to
+ * tf32 and the caller passes tf32-rounded weights, so no operand is truncated by the tensor core).
  * W is the reference layout [K, N] row-major (ldw = N). */
 #define CTR_PREC_FP32 0
 #define CTR_PREC_TF32 1
@@ -145,7 +146,10 @@ int ctr_mlp_bwd_weight(ctr_handle* h, ctr_stream s, int precision, int B, int K,
                        float* dW, float* dbias, void* ws, int64_t ws_bytes);
 /* out[N, ld_out] = in[K,N]^T, ld_out >= K: the K-major copy the tcgen05 path reads (TMA needs 16-byte
  * row pitches, so ld_out = K rounded up to 4; pad columns are left untouched) */
-int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, float* out, int64_t ld_out);
+int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, float* out, int64_t ld_out,
+                  int round_tf32);
+/* out[i] = rna_tf32(in[i]): the rounded weight copy the TF32 data-gradient GEMM reads */
+int ctr_round_tf32_copy(ctr_handle* h, ctr_stream s, const float* in, float* out, int64_t n);
 
 /* ---- K5: head + sigmoid log-loss --------------------------------------------------------
  * replaces concat + matmul + sigmoid (models/deepfm.py:128-145; models/dnn.py:82-84; the deep half
@@ -162,7 +166,7 @@ int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B,
                  const float* deep, int64_t deep_ld, int H, const float* w_deep,
                  const float* extra, const float* bias,
                  const float* label, float* logit, float* score, float* dlogit, float* dz_last, int64_t lddz,
-                 float* loss_out, void* ws, int64_t ws_bytes);
+                 int round_tf32 /* round dz_last to tf32 */, float* loss_out, void* ws, int64_t ws_bytes);
 /* dZ_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)        (through the last ReLU) */
 int ctr_head_bwd_deep(ctr_handle* h, ctr_stream s, int B, int H, const float* dlogit, const float* w_deep,
                       const float* deep, int64_t deep_ld, float* dZ, int64_t lddz);

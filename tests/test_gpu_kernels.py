@@ -135,7 +135,7 @@ def test_table_pack_roundtrip_and_transpose(hd):
     hd.call("ctr_table_unpack", _st(), ptr(tab), R, k, stride, ptr(e2), ptr(f2))
     assert torch.equal(e2, emb) and torch.equal(f2, first)
     W = torch.randn(429, 400, device="cuda"); Wt = torch.zeros(400, 429, device="cuda")
-    hd.call("ctr_transpose", _st(), ptr(W), 429, 400, ptr(Wt), 429)
+    hd.call("ctr_transpose", _st(), ptr(W), 429, 400, ptr(Wt), 429, 0)
     assert torch.equal(Wt, W.T.contiguous())
 
 
@@ -154,7 +154,7 @@ def test_mlp_tf32_tcgen05_gemms(hd, B, K, N):
     Xc, Wc, bc, dZc = Xp.cuda(), W.cuda(), b.cuda(), dZ.cuda()
     mp = torch.zeros(B, ldx); mp[:, :K] = mask; mc = mp.cuda()
     Wt = torch.zeros(N, ldx, device="cuda")
-    hd.call("ctr_transpose", _st(), ptr(Wc), K, N, ptr(Wt), ldx)
+    hd.call("ctr_transpose", _st(), ptr(Wc), K, N, ptr(Wt), ldx, 1)
     Y = torch.zeros(B, N, device="cuda")
     hd.call("ctr_mlp_fwd", _st(), 1, B, K, N, ptr(Xc), ldx, ptr(Wc), ptr(Wt), ptr(bc), 1, 1.0, 0, ptr(Y), N)
     torch.cuda.synchronize()
