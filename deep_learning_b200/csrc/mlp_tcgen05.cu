@@ -148,90 +148,110 @@ __device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t* r) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// One 32x32 sub-tile per step: TMEM -> registers (lane = row) -> this warp's padded smem tile -> registers
+// (8 lanes = one 128-byte row segment) -> bias / ReLU / mask / round / dropout -> global.  The transposition makes
+// every global access of the epilogue (the stores AND the mask loads) a fully coalesced 128-bit access: a
+// warp-wide store covers 4 complete 128-byte lines instead of 16 bytes in each of 32 different lines.
+// `stage` is pipeline shared memory, free once tmem_full has fired (every TMA write has landed and every MMA
+// that read it has completed).  Row pitch 36 floats keeps both the lane=row 128-bit writes and the 8-lanes-per-row
+// 128-bit reads bank-conflict free.
+constexpr int EPI_PITCH = 36;
+constexpr int EPI_TILE_FLOATS = 32 * EPI_PITCH;
+
 template <bool BIAS, bool RELU, bool MASK>
 __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
-                                              int64_t ldc, const EpiParams& ep) {
+                                              int64_t ldc, const EpiParams& ep, float* stage) {
     const int q = ewarp & 3, half = ewarp >> 2;
-    const int row = m0 + q * 32 + lane;
-    const bool row_ok = row < M;
+    float* tile = stage + ewarp * EPI_TILE_FLOATS;
     const bool vec_ok = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
     const bool mvec_ok = MASK && (ep.ldmask % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.mask) & 15) == 0);
-    const bool bvec_ok = BIAS && ((reinterpret_cast<uintptr_t>(ep.bias) & 15) == 0);
     const bool dropout = ep.keep < 1.f;
     const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
     const int nchunks = (N + 31) / 32;
+    const int rsub = lane >> 3;            // row inside a group of 4 rows
+    const int cc = (lane & 7) * 4;         // first of this lane's 4 columns inside the chunk
+    const int rbase = m0 + q * 32;
     for (int c = half; c < nchunks; c += 2) {
         const int c0 = c * 32;
         uint32_t r[32];
         tmem_ld32_issue(lane_addr + (uint32_t) c0, r);   // .sync.aligned: every lane takes part, valid row or not
-        const bool full = c0 + 32 <= N;
-        float mk[32];
-        if (MASK) {
-            const float* mrow = ep.mask + (int64_t) row * ep.ldmask + c0;
-            if (row_ok && full && mvec_ok) {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const float4 t = __ldg(reinterpret_cast<const float4*>(mrow) + i);
-                    mk[4 * i] = t.x; mk[4 * i + 1] = t.y; mk[4 * i + 2] = t.z; mk[4 * i + 3] = t.w;
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) mk[i] = (row_ok && c0 + i < N) ? mrow[i] : 0.f;
+        const int col = c0 + cc;
+        const bool col4 = col + 4 <= N;
+        float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (BIAS) {
+            if (col4 && ((reinterpret_cast<uintptr_t>(ep.bias) & 15) == 0)) bs = __ldg(reinterpret_cast<const float4*>(ep.bias + col));
+            else {
+                bs.x = col + 0 < N ? __ldg(ep.bias + col + 0) : 0.f;
+                bs.y = col + 1 < N ? __ldg(ep.bias + col + 1) : 0.f;
+                bs.z = col + 2 < N ? __ldg(ep.bias + col + 2) : 0.f;
+                bs.w = col + 3 < N ? __ldg(ep.bias + col + 3) : 0.f;
             }
         }
-        float bs[32];
-        if (BIAS) {
-            if (full && bvec_ok) {
+        float4 mk[8];
+        if (MASK) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    const float4 t = __ldg(reinterpret_cast<const float4*>(ep.bias + c0) + i);
-                    bs[4 * i] = t.x; bs[4 * i + 1] = t.y; bs[4 * i + 2] = t.z; bs[4 * i + 3] = t.w;
+            for (int j = 0; j < 8; ++j) {
+                const int row = rbase + rsub + 4 * j;
+                const float* mp = ep.mask + (int64_t) row * ep.ldmask + col;
+                if (row < M && col4 && mvec_ok) mk[j] = ctr_ldg_f4_stream(mp);
+                else {
+                    mk[j].x = (row < M && col + 0 < N) ? mp[0] : 0.f;
+                    mk[j].y = (row < M && col + 1 < N) ? mp[1] : 0.f;
+                    mk[j].z = (row < M && col + 2 < N) ? mp[2] : 0.f;
+                    mk[j].w = (row < M && col + 3 < N) ? mp[3] : 0.f;
                 }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 32; ++i) bs[i] = (c0 + i < N) ? __ldg(ep.bias + c0 + i) : 0.f;
             }
         }
         tmem_ld_wait();
-        float v[32];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-            float x = __uint_as_float(r[i]);
-            if (BIAS) x += bs[i];
-            if (RELU) x = fmaxf(x, 0.f);
-            if (MASK) x = mk[i] > 0.f ? x * ep.mask_scale : 0.f;
-            v[i] = x;
+        for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(tile + lane * EPI_PITCH + 4 * i) =
+                make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]), __uint_as_float(r[4 * i + 2]),
+                            __uint_as_float(r[4 * i + 3]));
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int rr = rsub + 4 * j;
+            const int row = rbase + rr;
+            float4 v = *reinterpret_cast<const float4*>(tile + rr * EPI_PITCH + cc);
+            if (BIAS) { v.x += bs.x; v.y += bs.y; v.z += bs.z; v.w += bs.w; }
+            if (RELU) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
+            if (MASK) {
+                v.x = mk[j].x > 0.f ? v.x * ep.mask_scale : 0.f;
+                v.y = mk[j].y > 0.f ? v.y * ep.mask_scale : 0.f;
+                v.z = mk[j].z > 0.f ? v.z * ep.mask_scale : 0.f;
+                v.w = mk[j].w > 0.f ? v.w * ep.mask_scale : 0.f;
+            }
+            if (ep.round_out) { v.x = ctr_round_tf32(v.x); v.y = ctr_round_tf32(v.y); v.z = ctr_round_tf32(v.z); v.w = ctr_round_tf32(v.w); }
+            if (dropout) {
+                const uint64_t e0 = (uint64_t) row * (uint64_t) N + (uint64_t) col;
+                v.x = dropout_u01(ep.seed, e0 + 0) < ep.keep ? v.x / ep.keep : 0.f;
+                v.y = dropout_u01(ep.seed, e0 + 1) < ep.keep ? v.y / ep.keep : 0.f;
+                v.z = dropout_u01(ep.seed, e0 + 2) < ep.keep ? v.z / ep.keep : 0.f;
+                v.w = dropout_u01(ep.seed, e0 + 3) < ep.keep ? v.w / ep.keep : 0.f;
+            }
+            if (row < M) {
+                float* dst = C + (int64_t) row * ldc + col;
+                if (vec_ok && col4) *reinterpret_cast<float4*>(dst) = v;
+                else {
+                    if (col + 0 < N) dst[0] = v.x;
+                    if (col + 1 < N) dst[1] = v.y;
+                    if (col + 2 < N) dst[2] = v.z;
+                    if (col + 3 < N) dst[3] = v.w;
+                }
+            }
         }
-        if (ep.round_out) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = ctr_round_tf32(v[i]);
-        }
-        if (dropout) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-                v[i] = dropout_u01(ep.seed, (uint64_t) row * (uint64_t) N + (c0 + i)) < ep.keep ? v[i] / ep.keep : 0.f;
-        }
-        if (!row_ok) continue;
-        float* dst = C + (int64_t) row * ldc + c0;
-        if (vec_ok && full) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-                reinterpret_cast<float4*>(dst)[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-        } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-                if (c0 + i < N) dst[i] = v[i];
-        }
+        __syncwarp();      // the tile is rewritten by the next chunk
     }
 }
 
 __device__ __forceinline__ void epilogue_dispatch(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
-                                                  int64_t ldc, const EpiParams& ep) {
-    if (ep.mask) epilogue_rows<false, false, true>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep);
-    else if (ep.bias && ep.relu) epilogue_rows<true, true, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep);
-    else if (ep.bias) epilogue_rows<true, false, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep);
-    else if (ep.relu) epilogue_rows<false, true, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep);
-    else epilogue_rows<false, false, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep);
+                                                  int64_t ldc, const EpiParams& ep, float* stage) {
+    if (ep.mask) epilogue_rows<false, false, true>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage);
+    else if (ep.bias && ep.relu) epilogue_rows<true, true, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage);
+    else if (ep.bias) epilogue_rows<true, false, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage);
+    else if (ep.relu) epilogue_rows<false, true, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage);
+    else epilogue_rows<false, false, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage);
 }
 
 __device__ __forceinline__ PipeBars* setup_cta(uint8_t* smem, int nstages, int stage_bytes, uint32_t tmem_cols, int warp) {
@@ -306,7 +326,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else {
         mbar_wait(&bars->tmem_full, 0);
         tc_fence_after();
-        epilogue_dispatch(tmem_base, warp, lane, m0, M, N, C, ldc, ep);
+        epilogue_dispatch(tmem_base, warp, lane, m0, M, N, C, ldc, ep, reinterpret_cast<float*>(smem));
     }
     tc_fence_before();
     __syncthreads();
@@ -379,7 +399,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_wait(&bars->tmem_full, 0);
             tc_fence_after();
             EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f, 0};
-            epilogue_rows<false, false, false>(tmem_base, warp, lane, m0, M, N, Cz, N, ep);
+            epilogue_rows<false, false, false>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem));
         } else {                                   // empty slice: contribute zeros
             const int row = m0 + (warp & 3) * 32 + lane;
             if (row < M) for (int c = (warp >> 2); c < N; c += 2) Cz[(size_t) row * N + c] = 0.f;

@@ -1,0 +1,37 @@
+"""The reference's hyper-parameter bag (`mp` / `args`): a plain attribute holder with the attribute names the
+model files read (models/deepfm.py:17-33, models/deepfm_multi.py:17-39, models/wdl.py:19-39,
+local_run_test.py:17-40, local_run_textline.py:17-67).  Launchers build one of these and hand it to
+`DeepModel(mp, ...)`; defaults are the launchers' hard-coded values."""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import List
+
+
+@dataclass
+class ModelParams:
+    hidden_units: List[int] = field(default_factory=lambda: [512, 256, 128])   # local_run.py:28-35
+    epochs: int = 1
+    batch_size: int = 256
+    learning_rate: float = 0.001
+    learning_rate_decay_steps: int = 10000000
+    learning_rate_decay_rate: float = 0.9
+    l2_reg: float = 0.00001
+    embedding_size: int = 8
+    cont_field_size: int = 0
+    vector_feats_size: int = 0
+    cate_field_size: int = 0
+    cate_feats_size: int = 0
+    cate_index_size: int = 0            # models/wdl.py:33
+    wide_field_size: int = 0            # models/wdl.py:39
+    multi_feats_size: int = 0           # sum of top_n over the multi-valued fields
+    multi_field_size: int = 0
+    multi_feats_range: List[list] = field(default_factory=list)   # [[start, end, name], ...] utils/my_utils.py:60-65
+    model_pb: str = ""
+    save_model_checkpoint: str = ""
+    restore_model_checkpoint: str = ""
+    model_restore: int = 0
+    cate_feats_conf_path: str = ""
+    alg_name: str = "deepfm"
+    action_type: str = "train"
+    num_batch_size: int = 100           # print_num_batch (local_run_test.py:79)

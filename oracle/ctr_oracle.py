@@ -85,10 +85,35 @@ def nonzero_reduce_mean(emb: Tensor) -> Tensor:
     return torch.where(nonzero == 0, torch.zeros_like(multi_sum), multi_sum / safe)
 
 
+# ReLU is continuous but its derivative is not: a pre-activation within rounding of zero can land on either
+# side in a reduced-precision (TF32) run.  Tests that check GRADIENTS of such a run pin the branch each unit
+# took (`with relu_branches(masks)`), so the comparison is same-branch and the tolerance measures rounding,
+# not the jump of d relu at 0.  Forward values (logit / score / loss) are always compared with the true relu.
+_RELU_BRANCHES: Optional[List[Tensor]] = None
+
+
+class relu_branches:
+    """context manager: masks[i] is a bool [B, H_i] tensor, True where unit (b, j) of layer i is active"""
+
+    def __init__(self, masks):
+        self.masks = masks
+
+    def __enter__(self):
+        global _RELU_BRANCHES
+        self.prev, _RELU_BRANCHES = _RELU_BRANCHES, self.masks
+        return self
+
+    def __exit__(self, *exc):
+        global _RELU_BRANCHES
+        _RELU_BRANCHES = self.prev
+        return False
+
+
 def mlp_tower(x: Tensor, p: Dict[str, Tensor], n_layers: int) -> Tensor:
     """models/deepfm.py:121-126: dropout(keep=1) is the identity; relu(x @ W_i + b_i)."""
     for i in range(n_layers):
-        x = torch.relu(x @ p['deep_%d' % i] + p['deep_bias_%d' % i])
+        z = x @ p['deep_%d' % i] + p['deep_bias_%d' % i]
+        x = torch.relu(z) if _RELU_BRANCHES is None else z * _RELU_BRANCHES[i].to(z.dtype)
     return x
 
 
