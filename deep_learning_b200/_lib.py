@@ -54,7 +54,7 @@ _PROTOS = {
                                    c_vp, c_i64]),
     "ctr_transpose": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_i64, c_i32]),
     "ctr_round_tf32_copy": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64]),
-    "ctr_head_fwd": (c_i32, [c_vp, c_vp, c_i32, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp,
+    "ctr_head_fwd": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp,
                              c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64]),
     "ctr_head_bwd_deep": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64, c_vp, c_i64]),
     "ctr_colsum_ws_bytes": (c_i64, [c_vp, c_i32, c_i32]),
@@ -71,6 +71,8 @@ _PROTOS = {
     "ctr_embed_bwd_finalize": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "ctr_cont_bwd_ws_bytes": (c_i64, [c_vp, _P_CFG]),
     "ctr_fm_cont_bwd": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
+    "ctr_scalar_segment_add": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i32, c_i64, c_vp]),
+    "ctr_segment_sum_rows": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i32, c_i32, c_vp, c_i32]),
     "ctr_adam_rows_ws_bytes": (c_i64, [c_vp, c_i64]),
     "ctr_adam_rows": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp,
                               c_i32, c_i64, c_vp, c_vp, c_i64, _P_HP]),

@@ -289,6 +289,53 @@ __global__ void cont_bwd_pass2(const float* __restrict__ ws, int nblk, int C, in
     if (lane == 0) out[c * gs + j] = acc;
 }
 
+// wide part of Wide&Deep (models/wdl.py:240-246): d wdl_weights[id] += sum over the lookups (b, j) of that id of
+// dlogit[b].  The lookups arrive sorted by id (ctr_sort_ids + ctr_unique_segments); 8 lanes walk one run with a
+// fixed stride and a fixed shuffle tree, so the sum order never changes from run to run.
+__global__ void __launch_bounds__(256)
+scalar_segment_add_kernel(const uint32_t* __restrict__ uniq, const uint32_t* __restrict__ seg_start,
+                          const uint32_t* __restrict__ n_unique, int64_t n_max, const uint32_t* __restrict__ perm,
+                          const float* __restrict__ src, uint32_t ld, int64_t dst_rows, float* __restrict__ dst) {
+    int64_t U = *n_unique;
+    if (U > n_max) U = n_max;
+    const int sub = threadIdx.x & 7;
+    const int64_t groups = ((int64_t) gridDim.x * blockDim.x) >> 3;
+    // every lane of a warp runs the same number of iterations (the shuffles below are warp-wide)
+    const int64_t g0 = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const int64_t iters = (U + groups - 1) / groups;
+    for (int64_t it = 0; it < iters; ++it) {
+        const int64_t u = g0 + it * groups;
+        float acc = 0.f;
+        uint32_t key = CTR_PAD_KEY;
+        if (u < U) {
+            key = uniq[u];
+            const uint32_t s = seg_start[u], e = seg_start[u + 1];
+            if (key != CTR_PAD_KEY)
+                for (uint32_t i = s + sub; i < e; i += 8) acc += src[perm[i] / ld];
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+        if (sub == 0 && key != CTR_PAD_KEY && (int64_t) key < dst_rows) dst[key] += acc;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+segment_sum_rows_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ n_unique, int64_t n_max,
+                        const uint32_t* __restrict__ perm, const float* __restrict__ src, int src_stride, int width,
+                        float* __restrict__ dst, int dst_stride) {
+    int64_t U = *n_unique;
+    if (U > n_max) U = n_max;
+    const int64_t total = U * width;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t u = t / width;
+        const int j = (int) (t - u * width);
+        float acc = 0.f;
+        for (uint32_t i = seg_start[u], e = seg_start[u + 1]; i < e; ++i) acc += src[(int64_t) perm[i] * src_stride + j];
+        dst[u * dst_stride + j] = acc;
+    }
+}
+
 inline int cont_blocks(ctr_handle* h, int B) {
     int64_t nb = ctr_cdiv(B > 0 ? B : 1, 128);
     int64_t cap = (int64_t) h->sm_count * 2;
@@ -416,5 +463,29 @@ extern "C" int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg*
     cont_bwd_pass2<<<(unsigned) ctr_cdiv((int64_t) npairs * 32, 256), 256, 0, ctr_st(s)>>>((const float*) ws, nblk, cfg->C, cfg->k,
                                                                           cfg->grad_stride, cont_grad);
     CTR_CHECK_LAUNCH(h, "cont_bwd_pass2");
+    return CTR_OK;
+}
+
+extern "C" int ctr_scalar_segment_add(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const uint32_t* seg_start,
+                                      const uint32_t* n_unique, int64_t n_max, const uint32_t* perm, const float* src,
+                                      int ld, int64_t dst_rows, float* dst) {
+    CTR_REQUIRE(h, uniq && seg_start && n_unique && perm && src && dst && ld > 0 && dst_rows > 0 && n_max >= 0,
+                "scalar_segment_add: bad args");
+    if (n_max == 0) return CTR_OK;
+    scalar_segment_add_kernel<<<grid_for(h, n_max * 8), 256, 0, ctr_st(s)>>>(uniq, seg_start, n_unique, n_max, perm, src,
+                                                                             (uint32_t) ld, dst_rows, dst);
+    CTR_CHECK_LAUNCH(h, "scalar_segment_add");
+    return CTR_OK;
+}
+
+extern "C" int ctr_segment_sum_rows(ctr_handle* h, ctr_stream s, const uint32_t* seg_start, const uint32_t* n_unique,
+                                    int64_t n_max, const uint32_t* perm, const float* src, int src_stride, int width,
+                                    float* dst, int dst_stride) {
+    CTR_REQUIRE(h, seg_start && n_unique && perm && src && dst && width > 0 && src_stride >= width && dst_stride >= width &&
+                       n_max >= 0, "segment_sum_rows: bad args");
+    if (n_max == 0) return CTR_OK;
+    segment_sum_rows_kernel<<<grid_for(h, n_max * width), 256, 0, ctr_st(s)>>>(seg_start, n_unique, n_max, perm, src,
+                                                                              src_stride, width, dst, dst_stride);
+    CTR_CHECK_LAUNCH(h, "segment_sum_rows");
     return CTR_OK;
 }

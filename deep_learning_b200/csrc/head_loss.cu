@@ -8,7 +8,7 @@ constexpr float LOG_LOSS_EPS = 1e-7f;   // tf.losses.log_loss default epsilon
 
 // one warp per sample
 __global__ void __launch_bounds__(256)
-head_fwd_kernel(int B, const float* __restrict__ fm, int64_t fm_ld, int n_fm, const float* __restrict__ w_fm,
+head_fwd_kernel(int B, float inv_bg, const float* __restrict__ fm, int64_t fm_ld, int n_fm, const float* __restrict__ w_fm,
                 const float* __restrict__ deep, int64_t deep_ld, int H, const float* __restrict__ w_deep,
                 const float* __restrict__ extra, const float* __restrict__ bias, const float* __restrict__ label,
                 float* __restrict__ logit, float* __restrict__ score, float* __restrict__ dlogit,
@@ -38,7 +38,7 @@ head_fwd_kernel(int B, const float* __restrict__ fm, int64_t fm_ld, int n_fm, co
             const float y = label[b];
             l = -y * logf(p + LOG_LOSS_EPS) - (1.f - y) * logf(1.f - p + LOG_LOSS_EPS);
             // d/dz [ -y log(p+e) - (1-y) log(1-p+e) ] = (-y/(p+e) + (1-y)/(1-p+e)) * p(1-p), mean over B
-            const float dl = (-y / (p + LOG_LOSS_EPS) + (1.f - y) / (1.f - p + LOG_LOSS_EPS)) * p * (1.f - p) / (float) B;
+            const float dl = (-y / (p + LOG_LOSS_EPS) + (1.f - y) / (1.f - p + LOG_LOSS_EPS)) * p * (1.f - p) * inv_bg;
             if (lane == 0 && dlogit) dlogit[b] = dl;
             if (dz_last && H > 0) {
                 // gradient through the last ReLU, written while the row is still cache-hot:
@@ -64,12 +64,12 @@ head_fwd_kernel(int B, const float* __restrict__ fm, int64_t fm_ld, int n_fm, co
     }
 }
 
-__global__ void __launch_bounds__(1024) loss_final_kernel(const float* __restrict__ part, int nparts, int B, float* __restrict__ out) {
+__global__ void __launch_bounds__(1024) loss_final_kernel(const float* __restrict__ part, int nparts, float inv_bg, float* __restrict__ out) {
     __shared__ float sm[32];
     float acc = 0.f;
     for (int i = threadIdx.x; i < nparts; i += blockDim.x) acc += part[i];
     float r = ctr_block_sum(acc, sm);
-    if (threadIdx.x == 0) out[0] = r / (float) B;
+    if (threadIdx.x == 0) out[0] = r * inv_bg;
 }
 
 __global__ void __launch_bounds__(256)
@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(256) colsum_pass2(const float* __restrict__ ws
 
 }  // namespace
 
-extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, const float* fm, int64_t fm_ld, int n_fm,
+extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, int64_t B_global, const float* fm, int64_t fm_ld, int n_fm,
                             const float* w_fm, const float* deep, int64_t deep_ld, int H, const float* w_deep,
                             const float* extra, const float* bias, const float* label, float* logit, float* score,
                             float* dlogit, float* dz_last, int64_t lddz, int round_tf32, float* loss_out, void* ws,
@@ -136,6 +136,7 @@ extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, const float* fm,
     CTR_REQUIRE(h, n_fm == 0 || (fm && w_fm), "head_fwd: fm inputs null");
     CTR_REQUIRE(h, H == 0 || (deep && w_deep), "head_fwd: deep inputs null");
     if (B == 0) return CTR_OK;
+    const float inv_bg = 1.f / (float) (B_global > 0 ? B_global : (int64_t) B);
     const int nblk = (int) ctr_cdiv(B, 8);
     float* part = nullptr;
     if (label && loss_out) {
@@ -143,11 +144,11 @@ extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, const float* fm,
         if (ws_bytes < (int64_t) nblk * 4) return ctr_fail(h, CTR_E_WORKSPACE, "head_fwd: ws too small");
         part = (float*) ws;
     }
-    head_fwd_kernel<<<nblk, 256, 0, ctr_st(s)>>>(B, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra, bias, label,
+    head_fwd_kernel<<<nblk, 256, 0, ctr_st(s)>>>(B, inv_bg, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra, bias, label,
                                                  logit, score, dlogit, dz_last, lddz, round_tf32, part);
     CTR_CHECK_LAUNCH(h, "head_fwd");
     if (part) {
-        loss_final_kernel<<<1, 1024, 0, ctr_st(s)>>>(part, nblk, B, loss_out);
+        loss_final_kernel<<<1, 1024, 0, ctr_st(s)>>>(part, nblk, inv_bg, loss_out);
         CTR_CHECK_LAUNCH(h, "loss_final");
     }
     return CTR_OK;

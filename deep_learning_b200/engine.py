@@ -27,11 +27,15 @@ def _ru(a: int, b: int) -> int:
 class CtrEngine:
     def __init__(self, spec: ModelSpec, max_batch: int, device: Optional[torch.device] = None,
                  learning_rate: float = 0.001, decay_steps: int = 10000000, decay_rate: float = 0.9,
-                 precision: str = "fp32", adam_mode: str = "tf_dense", train: bool = True):
+                 precision: str = "fp32", adam_mode: str = "tf_dense", train: bool = True,
+                 world: int = 1, rank: int = 0):
         if not torch.cuda.is_available():
             raise _lib.CtrError("CtrEngine needs a CUDA device: the hot path has no CPU fallback")
         assert adam_mode in ("tf_dense", "lazy") and precision in PREC
         self.spec, self.Bmax = spec, int(max_batch)
+        self.world, self.rank = int(world), int(rank)
+        # table rows held by this rank: row id lives on rank id % world at local row id // world
+        self.rows_local = (spec.table_rows + self.world - 1) // self.world
         self.dev = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
         self.h = _lib.Handle(self.dev.index if self.dev.index is not None else torch.cuda.current_device())
         self.lr0, self.decay_steps, self.decay_rate = learning_rate, decay_steps, decay_rate
@@ -45,7 +49,7 @@ class CtrEngine:
         self.id_bytes = 8 if s.id_dtype == "int64" else 4
 
         # ---- parameters ---------------------------------------------------------------------
-        self.table = torch.zeros(s.table_rows, s.table_stride, **f32)
+        self.table = torch.zeros(self.rows_local, s.table_stride, **f32)
         self.dense_shapes = s.dense_param_shapes()
         # flat buffer ordered by regulariser group so Adam needs at most three launches
         order = {"none": 0, "l2": 1, "l1": 2}
@@ -94,7 +98,8 @@ class CtrEngine:
         ws_bytes = max(self.h.query("ctr_colsum_ws_bytes", B, max(s.hidden + [s.fm_ld])), 4 * (B // 8 + 8), 1 << 16)
         if train:
             self.m_table, self.v_table = torch.zeros_like(self.table), torch.zeros_like(self.table)
-            self.m, self.v, self.grad = (torch.zeros(cur, **f32) for _ in range(3))
+            self.m, self.v = (torch.zeros(cur, **f32) for _ in range(2))
+            self.grad = torch.zeros(cur + _ALIGN, **f32)     # tail slot [cur] carries the loss share through the allreduce
             maxh = max(s.hidden)
             self.dz = [torch.zeros(B, maxh, **f32) for _ in range(2)]
             self.dx0_ld = _ru(max(s.E, 4), 4)
@@ -108,7 +113,7 @@ class CtrEngine:
             self.n_unique = torch.zeros(1, **u32)
             self.part = torch.zeros((n + n // 32 + 2) * s.grad_stride, **f32)
             self.cont_grad = torch.zeros(max(s.C, 1), s.grad_stride, **f32)
-            self.touched = torch.zeros(s.table_rows, dtype=torch.uint8, device=dev) if adam_mode == "tf_dense" else None
+            self.touched = torch.zeros(self.rows_local, dtype=torch.uint8, device=dev) if adam_mode == "tf_dense" else None
             cfg = self._cfg(B)
             # the id sort depends only on the batch: it runs on a side stream underneath the forward pass
             self.side = torch.cuda.Stream(device=dev)
@@ -120,6 +125,15 @@ class CtrEngine:
                            4 * (n // 2048 + 8))
             for (k_, h_) in self._layer_dims():
                 ws_bytes = max(ws_bytes, self.h.query("ctr_mlp_bwd_weight_ws_bytes", self.prec, B, k_, h_))
+            if s.head == "wdl":
+                # wide ids get their own sorted run structure (gradient of the scalar gather, models/wdl.py:240-246)
+                nw = B * s.wide_fields
+                self.w_keys, self.w_perm, self.w_uidx, self.w_uniq = (torch.zeros(max(nw, 1), **u32) for _ in range(4))
+                self.w_seg_start = torch.zeros(nw + 2, **u32)
+                self.w_n_unique = torch.zeros(1, **u32)
+                self.ws_sort_w = torch.zeros(_ru(max(self.h.query("ctr_sort_ws_bytes", nw), 4 * (nw // 2048 + 8)), 256),
+                                             dtype=torch.uint8, device=dev)
+                self.ev_sorted_w = torch.cuda.Event()
         self.ws = torch.zeros(_ru(ws_bytes, 256), dtype=torch.uint8, device=dev)
         self.last_batch = 0
 
@@ -181,9 +195,10 @@ class CtrEngine:
     def _load(self, p: Dict[str, np.ndarray], table: torch.Tensor, flat: torch.Tensor) -> None:
         s, st = self.spec, self._stream()
         t = lambda a: torch.as_tensor(np.ascontiguousarray(np.asarray(a, dtype=np.float32))).to(self.dev)
-        emb = t(p[s.emb_name]).reshape(s.table_rows, s.k)
-        first = t(p[s.first_name]).reshape(s.table_rows) if s.has_first else None
-        self.h.call("ctr_table_pack", st, ptr(emb), ptr(first), s.table_rows, s.k, s.table_stride, ptr(table))
+        emb_np = np.asarray(p[s.emb_name], dtype=np.float32).reshape(s.table_rows, s.k)[self.rank::self.world]
+        emb = t(emb_np)
+        first = t(np.asarray(p[s.first_name], dtype=np.float32).reshape(s.table_rows)[self.rank::self.world]) if s.has_first else None
+        self.h.call("ctr_table_pack", st, ptr(emb), ptr(first), emb.shape[0], s.k, s.table_stride, ptr(table))
         for name, shp in self.dense_shapes:
             a = np.asarray(p[name], dtype=np.float32).reshape(shp)
             if name == "deep_0":
@@ -220,8 +235,9 @@ class CtrEngine:
         s = self.spec
         g = torch.Generator(device=self.dev); g.manual_seed(seed)
         lim = math.sqrt(6.0 / (s.table_rows + s.k))
-        for r0 in range(0, s.table_rows, chunk_rows):
-            r1 = min(s.table_rows, r0 + chunk_rows)
+        g.manual_seed(seed + 7919 * self.rank)
+        for r0 in range(0, self.rows_local, chunk_rows):
+            r1 = min(self.rows_local, r0 + chunk_rows)
             blk = self.table[r0:r1]
             if s.emb_name == "weight_mat":
                 blk[:, :s.k] = (torch.rand(r1 - r0, s.k, generator=g, device=self.dev) * 2 - 1) * lim
@@ -240,12 +256,12 @@ class CtrEngine:
     def _dump(self, table: torch.Tensor, flat: torch.Tensor) -> Dict[str, np.ndarray]:
         s, st = self.spec, self._stream()
         out: Dict[str, np.ndarray] = {}
-        emb = torch.empty(s.table_rows, s.k, dtype=torch.float32, device=self.dev)
-        first = torch.empty(s.table_rows, dtype=torch.float32, device=self.dev) if s.has_first else None
-        self.h.call("ctr_table_unpack", st, ptr(table), s.table_rows, s.k, s.table_stride, ptr(emb), ptr(first))
-        out[s.emb_name] = emb.cpu().numpy()
+        emb = torch.empty(self.rows_local, s.k, dtype=torch.float32, device=self.dev)
+        first = torch.empty(self.rows_local, dtype=torch.float32, device=self.dev) if s.has_first else None
+        self.h.call("ctr_table_unpack", st, ptr(table), self.rows_local, s.k, s.table_stride, ptr(emb), ptr(first))
+        out[s.emb_name] = self._assemble_rows(emb)
         if s.has_first:
-            out[s.first_name] = first.cpu().numpy().reshape(-1, 1)
+            out[s.first_name] = self._assemble_rows(first.reshape(-1, 1))
         for name, shp in self.dense_shapes:
             a = self.view(name, flat).cpu().numpy().reshape(shp).copy()
             if name == "deep_0":
@@ -257,6 +273,10 @@ class CtrEngine:
                 a = a[inv, :]
             out[name] = a
         return out
+
+    def _assemble_rows(self, shard: torch.Tensor) -> np.ndarray:
+        """full [table_rows, w] host array from this rank's shard (one GPU: the shard IS the table)"""
+        return shard.cpu().numpy()
 
     def _refresh_transposes(self) -> None:
         if self.wt is None:
@@ -305,15 +325,24 @@ class CtrEngine:
         return B
 
     # ---- forward -------------------------------------------------------------------------------------
-    def forward(self, B: int, with_loss: bool) -> None:
+    def _embed_forward(self, B: int) -> None:
+        """K2 + K1: rows of the (local) table -> X0, fm, sum_e"""
         s, st, h = self.spec, self._stream(), self.h
         cfg = self._cfg(B)
         if s.Fm:
             h.call("ctr_pooled_gather_fwd", st, cfg, ptr(self.table), ptr(self.ids), ptr(self.multi_start), None,
                    ptr(self.x0), ptr(self.pooled_first), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first))
-        cont_rows = self.table[s.cont_base:] if (s.use_fm and s.fm_cont) else None
         h.call("ctr_fm_gather_fwd", st, cfg, ptr(self.table), ptr(self.ids), 0, ptr(self.cont), ptr(self.vec),
-               ptr(cont_rows), ptr(self.pooled_first), ptr(self.x0), ptr(self.fm), ptr(self.sum_e))
+               ptr(self._cont_rows()), ptr(self.pooled_first), ptr(self.x0), ptr(self.fm), ptr(self.sum_e))
+
+    def _cont_rows(self):
+        """the C table rows of the continuous fields (models/deepfm.py:63-66), contiguous"""
+        s = self.spec
+        return self.table[s.cont_base:] if (s.use_fm and s.fm_cont) else None
+
+    def forward(self, B: int, with_loss: bool) -> None:
+        s, st, h = self.spec, self._stream(), self.h
+        self._embed_forward(B)
         x, ldx = self.x0, s.x0_ld
         for i, (k_, h_) in enumerate(self._layer_dims()):
             h.call("ctr_mlp_fwd", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self._w(i)),
@@ -326,11 +355,15 @@ class CtrEngine:
                    s.wide_fields, ptr(self.wide_sum))
             extra = self.wide_sum
         lab = self.label if with_loss else None
-        h.call("ctr_head_fwd", st, B, ptr(self.fm), s.fm_ld, s.n_fm, ptr(w_fm), ptr(x), ldx, s.hidden[-1], ptr(w_deep),
+        h.call("ctr_head_fwd", st, B, self.global_batch(B), ptr(self.fm), s.fm_ld, s.n_fm, ptr(w_fm), ptr(x), ldx, s.hidden[-1], ptr(w_deep),
                ptr(extra), ptr(bias), ptr(lab), ptr(self.logit), ptr(self.score),
                ptr(self.dlogit) if with_loss else None,
                ptr(self.dz[0]) if (with_loss and self.train_mode) else None, s.hidden[-1], int(self.prec == 1),
                ptr(self.loss) if with_loss else None, ptr(self.ws), self.ws.numel())
+
+    def global_batch(self, B: int) -> int:
+        """samples the loss is a mean over (all ranks' batches when sharded)"""
+        return B
 
     def _reg_loss(self) -> torch.Tensor:
         """regulariser terms of the reported loss (models/deepfm.py:155-156, models/wdl.py:268-275,
@@ -393,14 +426,13 @@ class CtrEngine:
             n = B * s.ids_ld + self.n_extra
             torch.cuda.current_stream(self.dev).wait_event(self.ev_sorted)
             if self.n_extra:
-                h.call("ctr_fm_cont_bwd", st, cfg, ptr(self.cont), ptr(self.table[s.cont_base:]), ptr(self.sum_e),
+                h.call("ctr_fm_cont_bwd", st, cfg, ptr(self.cont), ptr(self._cont_rows()), ptr(self.sum_e),
                        ptr(self.dlogit), ptr(w_fm), ptr(self.cont_grad), ws, wsn)
             h.call("ctr_embed_bwd_partials", st, cfg, ptr(self.keys), ptr(self.perm), ptr(self.uidx), n,
                    ptr(self.field_of_slot), ptr(self.x0), ptr(self.dx0), self.dx0_ld, ptr(self.sum_e), ptr(self.dlogit),
                    ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.part))
-            h.call("ctr_adam_rows", st, ptr(self.uniq), ptr(self.n_unique), n, 0, ptr(self.part), ptr(self.seg_start),
-                   s.grad_stride, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
-                   s.table_rows, ptr(self.touched), ws, wsn, hp)
+            self._sparse_update(B, n, hp)
+        self._reduce_dense_grads()
         if self.adam_mode == "tf_dense":
             # TF1 Adam moves EVERY row each step (m, v decay; theta -= lr_t*m/(sqrt(v)+eps)) -- exact mode
             h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
@@ -415,6 +447,16 @@ class CtrEngine:
         self.beta1_power *= ADAM_BETA1
         self.beta2_power *= ADAM_BETA2
         self.global_step += 1
+
+    def _sparse_update(self, B: int, n: int, hp: AdamHP) -> None:
+        """per-run partial gradients (self.part) -> TF1 Adam on the touched rows of the local table"""
+        s, st = self.spec, self._stream()
+        self.h.call("ctr_adam_rows", st, ptr(self.uniq), ptr(self.n_unique), n, 0, ptr(self.part), ptr(self.seg_start),
+                    s.grad_stride, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
+                    self.rows_local, ptr(self.touched), ptr(self.ws), self.ws.numel(), hp)
+
+    def _reduce_dense_grads(self) -> None:
+        """data-parallel hook: sum the dense gradients over ranks (no-op on one GPU)"""
 
     def _launch_sort(self, B: int) -> None:
         """sort ids -> (keys, perm), run-length structure -> (uniq, seg_start, uidx, n_unique); enqueued on
@@ -433,9 +475,31 @@ class CtrEngine:
         h.call("ctr_unique_segments", st, ptr(self.keys), n, ptr(self.uniq), ptr(self.seg_start), ptr(self.uidx),
                ptr(self.n_unique), ws, wsn)
         self.ev_sorted.record(self.side)
+        self._sort_wide(B, st)
+
+    def _sort_wide(self, B: int, st: int) -> None:
+        """run structure of the wide ids (gradient of the scalar gather of models/wdl.py:240-246)"""
+        s, h = self.spec, self.h
+        if s.head == "wdl" and s.wide_fields and self.train_mode:
+            nw = B * s.wide_fields
+            rows = s.wide_rows + s.hidden[-1]
+            ws, wsn = ptr(self.ws_sort_w), self.ws_sort_w.numel()
+            h.call("ctr_sort_ids", st, ptr(self.wide), self.id_bytes, B, s.wide_fields, 0, s.wide_fields, 0, 0, 0, 0, 1, 0,
+                   max(1, int(rows - 1).bit_length()), ptr(self.w_keys), ptr(self.w_perm), ws, wsn)
+            h.call("ctr_unique_segments", st, ptr(self.w_keys), nw, ptr(self.w_uniq), ptr(self.w_seg_start),
+                   ptr(self.w_uidx), ptr(self.w_n_unique), ws, wsn)
+            self.ev_sorted_w.record(self.side if st == self.side.cuda_stream else torch.cuda.current_stream(self.dev))
 
     def _wdl_wide_grad(self, B: int) -> None:
-        raise NotImplementedError("wdl training lands with the scalar segment-gradient kernel")
+        """d wdl_weights[id] += sum of dlogit over the wide lookups of id (added on top of the deep-projection
+        rows W..W+H-1 that the colsum already wrote: quirk Q4 makes the two alias, models/wdl.py:224-228)"""
+        s = self.spec
+        if not s.wide_fields:
+            return
+        torch.cuda.current_stream(self.dev).wait_event(self.ev_sorted_w)
+        self.h.call("ctr_scalar_segment_add", self._stream(), ptr(self.w_uniq), ptr(self.w_seg_start), ptr(self.w_n_unique),
+                    B * s.wide_fields, ptr(self.w_perm), ptr(self.dlogit), s.wide_fields, s.wide_rows + s.hidden[-1],
+                    ptr(self.view("wdl_weights", self.grad)))
 
     # ---- public step API -------------------------------------------------------------------------------
     def train_step(self, batch: Optional[Dict] = None) -> torch.Tensor:
@@ -447,9 +511,13 @@ class CtrEngine:
         self._launch_sort(B)
         self.forward(B, with_loss=True)
         reg = self._reg_loss()
-        total = self.loss.clone() if reg is None else self.loss + reg
         self.backward_and_update(B)
-        return total
+        loss = self._global_loss()
+        return loss if reg is None else loss + reg
+
+    def _global_loss(self) -> torch.Tensor:
+        """log-loss of the global batch (sharded engines read it back from the gradient allreduce)"""
+        return self.loss.clone()
 
     def predict(self, batch: Optional[Dict] = None) -> torch.Tensor:
         """`sess.run("score:0")` (models/deepfm.py:250): scores [B] on the device."""

@@ -162,6 +162,9 @@ int ctr_round_tf32_copy(ctr_handle* h, ctr_stream s, const float* in, float* out
  *                                                            written while the row is cache-hot)
  * loss_out: one float, written by a second deterministic reduction pass. ws >= 4*(ceil(B/256)+1) B */
 int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B,
+                 int64_t B_global /* samples the loss is a mean over: B on one GPU, the sum of all ranks' batches when
+                 the batch is sharded (loss and dlogit are then this rank's SHARE, so a sum-allreduce gives the global
+                 mean and its gradient); <= 0 means B */,
                  const float* fm, int64_t fm_ld, int n_fm, const float* w_fm,
                  const float* deep, int64_t deep_ld, int H, const float* w_deep,
                  const float* extra, const float* bias,
@@ -238,6 +241,21 @@ int64_t ctr_cont_bwd_ws_bytes(ctr_handle* h, const ctr_embed_cfg* cfg);
 int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const float* cont,
                     const float* cont_rows, const float* sum_e, const float* dlogit, const float* w_fm,
                     float* cont_grad /*[C, grad_stride]*/, void* ws, int64_t ws_bytes);
+
+/* scalar-table scatter-add, the gradient of ctr_scalar_gather_sum (wide part, models/wdl.py:240-246 as
+ * differentiated by models/wdl.py:282):  dst[uniq[u]] += sum_{i in run u} src[perm[i] / ld]   (perm = flat position
+ * b*ld + j of a wide lookup, src = dlogit [B]).  Runs come from ctr_sort_ids + ctr_unique_segments; the sum order
+ * is fixed.  Keys 0xFFFFFFFF and keys >= dst_rows are skipped. */
+int ctr_scalar_segment_add(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const uint32_t* seg_start,
+                           const uint32_t* n_unique, int64_t n_max, const uint32_t* perm, const float* src,
+                           int ld, int64_t dst_rows, float* dst);
+
+/* owner-side reduction of row gradients received from several peers (multi-GPU):
+ *   dst[u, :width] = sum_{i in run u} src[perm[i], :width]   in run order.  The runs come from a STABLE sort of
+ * the received row keys, so contributions are added in fixed peer order: deterministic. */
+int ctr_segment_sum_rows(ctr_handle* h, ctr_stream s, const uint32_t* seg_start, const uint32_t* n_unique,
+                         int64_t n_max, const uint32_t* perm, const float* src, int src_stride, int width,
+                         float* dst, int dst_stride);
 
 /* TF1 Adam on the rows named by row_ids (unique):  g = grads[u];
  *   m <- b1*m + (1-b1) g ; v <- b2*v + (1-b2) g^2 ; theta <- theta - lr_t * m / (sqrt(v) + eps)

@@ -1,0 +1,113 @@
+"""Multi-GPU parity: N ranks, each on its shard of the global batch and its rows of the tables,
+against the fp64 oracle run on the CONCATENATED batch.  Launch (N = number of GPUs, 1 is a valid loopback):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        tests/mgpu_parity.py [alg] [adam_mode]
+
+Bit-exact: shard map, de-duplicated key lists, gathered rows.  1e-5 relative (FP32 path): loss, scores, updated
+parameters (same noise-floor rule as tests/test_gpu_parity.py).
+"""
+import copy
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+from oracle import ctr_oracle as O   # noqa: E402
+import ctr_helpers as H              # noqa: E402
+
+
+def main():
+    alg = sys.argv[1] if len(sys.argv) > 1 else "deepfm"
+    adam_mode = sys.argv[2] if len(sys.argv) > 2 else "lazy"
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from deep_learning_b200.sharded import ShardedCtrEngine
+    from deep_learning_b200.spec import spec_from_hparams
+
+    if alg in ("deepfm_multi", "dnn_multi"):
+        hp = H.hp_multi(B=192)
+    elif alg == "wdl":
+        hp = H.hp_c1(cate_index_size=10000, wide_field_size=20)
+    else:
+        hp = H.hp_c1()
+    Bl = 96 if alg in ("deepfm_multi", "dnn_multi") else 128          # samples per rank
+    spec = spec_from_hparams(alg, hp)
+    p = O.init_params(alg, hp, seed=2019, dtype=torch.float64)
+    st = O.adam_init(p)
+    eng = ShardedCtrEngine(spec, Bl, learning_rate=hp.learning_rate, precision="fp32", adam_mode=adam_mode)
+    eng.set_weights({k: v.numpy() for k, v in p.items()})
+    back = eng.get_weights()
+    for n in p:      # shards re-assemble to the injected tables bit-exactly
+        assert np.array_equal(back[n].reshape(-1), p[n].float().numpy().reshape(-1)), n
+    pl = eng.plan
+    tol = 1e-5
+    for step in range(3):
+        parts = [H.make_batch(alg, hp, seed=4000 + step * world + r, B=Bl) for r in range(world)]
+        glob = {k: torch.cat([b[k] for b in parts], dim=0) for k in parts[0]}
+        mine = parts[rank]
+        ob = H.oracle_batch(glob, torch.float64)
+        # ---- predict: each rank scores its own samples
+        _, score_ref = O.FORWARD[alg](p, H.oracle_batch(mine, torch.float64), hp)
+        score = eng.predict(mine).cpu().numpy()
+        assert np.max(np.abs(score - score_ref.numpy().reshape(-1))) < tol, "score step %d" % step
+        # ---- bit-exact integer side: owner-major unique keys and the rows that came back
+        ids = mine["cate_feats"].numpy().astype(np.int64)
+        if spec.use_fm and spec.fm_cont:
+            ids_all = np.concatenate([ids.reshape(-1), spec.cont_base + np.arange(spec.C)])
+        else:
+            ids_all = ids.reshape(-1)
+        if spec.zero_row0:
+            ids_all = ids_all[ids_all != 0]
+        want = np.unique(pl.key(ids_all).astype(np.uint32))
+        got_u = eng.uniq[:eng.U].cpu().numpy().view(np.uint32)
+        assert np.array_equal(got_u, want), "unique key list differs on rank %d" % rank
+        ids_u = pl.id_of_key(want.astype(np.int64))
+        rows = eng.rows_recv[:eng.U, :spec.row_width].cpu().numpy()
+        emb_ref = p[spec.emb_name].float().numpy()[ids_u]
+        assert np.array_equal(rows[:, :spec.k], emb_ref), "gathered rows differ on rank %d" % rank
+        if spec.has_first:
+            assert np.array_equal(rows[:, spec.k], p[spec.first_name].float().numpy()[ids_u, 0])
+        # ---- one train step: N ranks on N shards == oracle on the concatenated batch
+        st32 = copy.deepcopy(st)
+        st32.m = O.to_dtype(st32.m, torch.float32)
+        st32.v = O.to_dtype(st32.v, torch.float32)
+        _, p32 = O.train_step(alg, O.to_dtype(p, torch.float32), st32, H.oracle_batch(glob, torch.float32), hp, adam_mode=adam_mode)
+        loss_ref, p = O.train_step(alg, p, st, ob, hp, adam_mode=adam_mode)
+        loss = float(eng.train_step(mine).item())
+        assert abs(loss - float(loss_ref)) < tol * max(1.0, abs(float(loss_ref))), (step, loss, float(loss_ref))
+        got = eng.get_weights()
+        worst = 0.0
+        for n in p:
+            ref = p[n].numpy().reshape(-1)
+            err = H.rel_err(got[n].reshape(-1), ref)
+            floor = H.rel_err(p32[n].numpy().reshape(-1), ref)
+            worst = max(worst, err)
+            assert err < max(tol, 4 * floor), "param %s step %d: rel err %.3g (fp32 floor %.3g)" % (n, step, err, floor)
+        # resynchronise the state (fp32-rounded) so each step is checked from identical state
+        eng.set_weights({k: v.numpy() for k, v in p.items()})
+        eng.set_optimizer_state({k: v.numpy() for k, v in st.m.items()}, {k: v.numpy() for k, v in st.v.items()},
+                                st.global_step, st.beta1_power, st.beta2_power)
+        p = O.to_dtype(O.to_dtype(p, torch.float32), torch.float64)
+        st.m = O.to_dtype(O.to_dtype(st.m, torch.float32), torch.float64)
+        st.v = O.to_dtype(O.to_dtype(st.v, torch.float32), torch.float64)
+        if rank == 0:
+            print("step %d ok: loss %.6f (oracle %.6f), worst param rel err %.3g, U=%d n_req=%d" % (
+                step, loss, float(loss_ref), worst, eng.U, eng.n_req))
+    dist.barrier()
+    if rank == 0:
+        print("MGPU PARITY OK alg=%s adam=%s world=%d" % (alg, adam_mode, world))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -134,6 +134,20 @@ def test_dnn_l1_reg():
     _run_parity("dnn", hp, steps=2)
 
 
+def test_wdl_wide_and_deep_alias_quirk():
+    """models/wdl.py: wide scalar gather + deep tower sharing ONE wdl_weights table (deep rows alias wide ids
+    W..W+H-1, quirk Q4), L2 on wdl_weights and every deep_i"""
+    hp = H.hp_c1(cate_index_size=10000, wide_field_size=20, cont_field_size=10)
+    _run_parity("wdl", hp, steps=3)
+    _run_parity("wdl", hp, steps=2, adam_mode="lazy")
+
+
+def test_wdl_criteo_shape():
+    """configs[2] shape (13 cont + 26 cate, 26 wide, k=16, MLP 400x3) at B=1024 / 50K rows; wide ids < 426 hit the
+    aliased deep rows"""
+    _run_parity("wdl", H.hp_criteo(B=1024, rows=50000), steps=2, adam_mode="lazy")
+
+
 def test_dnn_multi():
     hp = H.hp_multi(B=256)
     _run_parity("dnn_multi", hp, steps=2)
