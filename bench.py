@@ -151,31 +151,44 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    if world > 1:
-        raise SystemExit("multi-GPU row-sharded path not wired into bench.py yet")
-
     B, R = a.batch, a.rows
     hp = hparams(B, R)
     spec = spec_from_hparams("deepfm", hp)
-    eng = CtrEngine(spec, B, device=dev, learning_rate=hp.learning_rate, precision=a.precision, adam_mode="lazy")
+    if world > 1:
+        os.environ["NCCL_DEBUG"] = os.environ.get("CTR_NCCL_DEBUG", "WARN")     # keep stdout to the one JSON line
+        # configs[3]: the ~1e8-row tables row-sharded over the ranks (owner = id mod N), B samples per GPU (weak scaling)
+        dist.init_process_group("nccl", device_id=dev)
+        from deep_learning_b200.sharded import ShardedCtrEngine
+        eng = ShardedCtrEngine(spec, B, device=dev, learning_rate=hp.learning_rate, precision=a.precision, adam_mode="lazy")
+    else:
+        eng = CtrEngine(spec, B, device=dev, learning_rate=hp.learning_rate, precision=a.precision, adam_mode="lazy")
     eng.init_table_on_device(seed=2019)
-    eng.set_dense_weights(init_weights(spec, 2019, with_table=False))
+    eng.set_dense_weights(init_weights(spec, 2019, with_table=False))     # same seed on every rank: replicas start equal
 
-    # rotating synthetic batches, generated on the device (seed 2020+i), mirrored in pinned host memory
+    # rotating synthetic batches, generated on the device (seed 2020 + i*world + rank), mirrored in pinned host memory
     sizes = D.field_sizes(R, spec.Fc)
     NB = 4
-    dev_batches = [D.synthetic_batch(B, spec.C, spec.Fc, sizes, seed=2020 + i, dist=a.dist, device=dev) for i in range(NB)]
+    dev_batches = [D.synthetic_batch(B, spec.C, spec.Fc, sizes, seed=2020 + i * world + rank, dist=a.dist, device=dev)
+                   for i in range(NB)]
     host_batches = [{k: v.cpu().pin_memory() for k, v in b.items()} for b in dev_batches]
     h2d = sum(v.numel() * v.element_size() for k, v in host_batches[0].items() if k != "vector_feats")
 
     def sync():
         torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
     # ---- device-resident timing ------------------------------------------------------------------
     for i in range(W):
-        eng.train_step(dev_batches[i % NB])
+        eng.train_step(dev_batches[i % NB], next_batch=dev_batches[(i + 1) % NB])
     sync()
     timed = ("ctr_fm_gather_fwd", "ctr_embed_bwd_partials", "ctr_adam_rows", "ctr_sort_ids", "ctr_mlp_fwd",
              "ctr_mlp_bwd_data", "ctr_mlp_bwd_weight")
@@ -188,29 +201,34 @@ def main():
     torch.cuda.profiler.start()      # `ncu --profile-from-start off` captures exactly the timed steps
     e0.record()
     for i in range(a.steps):
-        eng.train_step(dev_batches[i % NB])
+        eng.train_step(dev_batches[i % NB], next_batch=dev_batches[(i + 1) % NB])
     e1.record()
     sync()
     torch.cuda.profiler.stop()
     t1 = time.time()
-    ms = e0.elapsed_time(e1)
+    ms = max_over_ranks(e0.elapsed_time(e1))
     launches = eng.h.launches - l0
     kern = {n: (sum(x.elapsed_time(y) for x, y in ev) / max(len(ev), 1), len(ev)) for n, ev in eng.h.timers.items()}
     eng.h.timers = None
     clk = clocks.stop(t0, t1)
     n_unique = int(eng.n_unique.item())
-    value = B * a.steps / (ms * 1e-3)
+    value = world * B * a.steps / (ms * 1e-3)
 
     # ---- end to end through the public step API: pinned host batch in, loss scalar out, every step ----
     for i in range(2):
-        float(eng.train_step(host_batches[i % NB]).item())
+        float(eng.train_step(host_batches[i % NB], next_batch=host_batches[(i + 1) % NB]).item())
     sync()
     e0.record()
     for i in range(a.steps):
-        loss = float(eng.train_step(host_batches[i % NB]).item())
+        loss = float(eng.train_step(host_batches[i % NB], next_batch=host_batches[(i + 1) % NB]).item())
     e1.record()
     sync()
-    e2e_ms = e0.elapsed_time(e1)
+    e2e_ms = max_over_ranks(e0.elapsed_time(e1))
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
 
     # ---- roofline of the embedding gather (K1): algorithmic bytes/sample x B / measured duration ----
     hbm, tfl, which = peaks()
@@ -225,16 +243,19 @@ def main():
     mlp_flops = 3 * 2 * sum(k_ * h_ for k_, h_ in eng._layer_dims()) * B
     mlp_ms = sum(kern[n][0] * kern[n][1] for n in ("ctr_mlp_fwd", "ctr_mlp_bwd_data", "ctr_mlp_bwd_weight")) / a.steps
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": a.steps, "warmup": W,
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": W,
         "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if a.precision == "fp32" else "tf32", "data": "synthetic",
         "config": {"workload": "DeepFM Criteo-shape: 13 cont + 26 single-valued cate, k=16, MLP 400-400-400, "
-                               "batch %d, table %d rows x (16+1) f32, ids %s, Adam lazy (touched rows)" % (B, R, a.dist),
-                   "batch_per_gpu": B, "table_rows": R, "unique_rows_last_step": n_unique, "mlp_precision": a.precision,
+                               "batch %d per GPU, table %d rows x (16+1) f32%s, ids %s, Adam lazy (touched rows)"
+                               % (B, R, " row-sharded over %d GPUs (ids/vectors/grads all-to-all, dense allreduce)" % world
+                                  if world > 1 else "", a.dist),
+                   "batch_per_gpu": B, "global_batch": B * world, "parallelism": "dp%d+rowshard%d" % (world, world) if world > 1 else "single",
+                   "table_rows": R, "unique_rows_last_step": n_unique, "mlp_precision": a.precision,
                    "l2_flush": "working set per step (~0.9 GB activations + random rows of a %.1f GB table) >> 126 MB L2; "
                                "%d rotating batches" % (eng.table.numel() * 4 / 1e9, NB)},
         "clocks": clk,
-        "e2e": {"value": B * a.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4},
+        "e2e": {"value": world * B * a.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": 4 * world},
         "gpu_launches": int(launches),
         "roofline": {"kernel": "fm_gather_fwd_kernel<16,true>", "bound": "hbm", "achieved": k1_gbs, "peak": hbm,
                      "unit": "GB/s", "frac": k1_gbs / hbm, "traffic": None, "peak_source": which,
@@ -242,10 +263,16 @@ def main():
         "mlp": {"achieved_tflops": mlp_flops / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else None, "ms_per_step": mlp_ms},
         "kernels": kernels,
     }
-    if not a.no_cpu_baseline:
+    if world > 1:
+        line["exchange"] = {"unique_rows_requested_rank0": int(eng.U), "rows_served_rank0": int(eng.n_req),
+                            "wire_bytes_per_row": 4 + 2 * 4 * eng.wire}
+    if not a.no_cpu_baseline and world == 1:
         cb = cpu_reference_arm(3, 1)
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
     print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -288,7 +288,7 @@ class CtrEngine:
                 self.h.call("ctr_round_tf32_copy", st, ptr(self._w(i)), ptr(self.wr[i]), k_ * h_)
 
     # ---- batch upload ------------------------------------------------------------------------------
-    def load_batch(self, batch: Dict, non_blocking: bool = True) -> int:
+    def load_batch(self, batch: Dict, non_blocking: bool = True, skip_ids: bool = False) -> int:
         """Copy one batch (host or device arrays/tensors, reference key names) into the device
         buffers.  Returns B (may be < max_batch for the short last batch, models/deepfm.py:178)."""
         s = self.spec
@@ -304,7 +304,8 @@ class CtrEngine:
         if s.ids_ld:
             if cate.shape[1] != s.ids_ld:
                 raise ValueError("cate_feats has %d columns, model expects %d" % (cate.shape[1], s.ids_ld))
-            self.ids[:B].copy_(cate, non_blocking=non_blocking)
+            if not skip_ids:
+                self.ids[:B].copy_(cate, non_blocking=non_blocking)
         cont = as_t(batch["cont_feats"], torch.float32)
         if s.alg == "dnn" and "vector_feats" in batch and batch["vector_feats"] is not None:
             vec = as_t(batch["vector_feats"], torch.float32)
@@ -502,18 +503,29 @@ class CtrEngine:
                     ptr(self.view("wdl_weights", self.grad)))
 
     # ---- public step API -------------------------------------------------------------------------------
-    def train_step(self, batch: Optional[Dict] = None) -> torch.Tensor:
+    def train_step(self, batch: Optional[Dict] = None, next_batch: Optional[Dict] = None) -> torch.Tensor:
         """One `sess.run([loss, optimizer])` (models/deepfm.py:181).  Returns the loss as a device
-        scalar tensor (log-loss + regulariser); call .item() to read it."""
+        scalar tensor (log-loss + regulariser); call .item() to read it.  `next_batch` (optional) is the batch the
+        NEXT call will train on: the input pipeline knows it one step ahead (the reference's tf.data iterator
+        prefetches the same way, utils/data_loader.py:29-40), and the sharded engine uses it to take the id
+        de-duplication and id exchange of step i+1 off the critical path of step i."""
         if not self.train_mode:
             raise _lib.CtrError("engine was created with train=False")
         B = self.load_batch(batch) if batch is not None else self.last_batch
         self._launch_sort(B)
         self.forward(B, with_loss=True)
+        self._after_forward(next_batch)
         reg = self._reg_loss()
         self.backward_and_update(B)
         loss = self._global_loss()
+        self._end_step()
         return loss if reg is None else loss + reg
+
+    def _after_forward(self, next_batch: Optional[Dict]) -> None:
+        """hook: work for the next step that can overlap this step's backward (sharded engine)"""
+
+    def _end_step(self) -> None:
+        """hook: end-of-step bookkeeping"""
 
     def _global_loss(self) -> torch.Tensor:
         """log-loss of the global batch (sharded engines read it back from the gradient allreduce)"""

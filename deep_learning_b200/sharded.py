@@ -5,6 +5,11 @@ The arithmetic is the single-GPU engine's: the fused gather+FM kernel simply rea
 staging buffer filled by the vector all-to-all (indexed by each lookup's position in this rank's unique list)
 instead of from the table, and the Adam update runs on the owner after the gradient all-to-all.  The loss is the
 mean over the GLOBAL batch, so N ranks on N shards of a batch reproduce one GPU on the concatenated batch.
+
+Everything that depends only on the batch ids -- sort / de-dup / per-owner counts, the counts and key all-to-alls
+and the owner-side sort of the requested keys -- is an "id plan".  Given `next_batch`, the plan of step i+1 is
+built on a side stream underneath the backward pass of step i, so the critical path of a step holds only what
+depends on the parameters: owner gather -> vector all-to-all -> compute -> gradient all-to-all -> owner Adam.
 """
 from __future__ import annotations
 
@@ -20,6 +25,44 @@ from .engine import CtrEngine, _ru
 from .spec import ModelSpec
 
 
+class _IdPlan:
+    """Every id-derived structure of one batch (requester side and owner side)."""
+
+    def __init__(self, eng: "ShardedCtrEngine"):
+        s, dev, B = eng.spec, eng.dev, eng.Bmax
+        n = eng.n_max
+        u32 = dict(dtype=torch.int32, device=dev)     # raw 32-bit storage; the library reads it as uint32
+        self.ids = torch.zeros(B, max(s.ids_ld, 1), dtype=eng.id_torch, device=dev)
+        self.keys, self.perm, self.uidx, self.uniq, self.inv = (torch.zeros(max(n, 1), **u32) for _ in range(5))
+        self.seg_start = torch.zeros(n + 2, **u32)
+        self.n_unique = torch.zeros(1, **u32)
+        self.counts = torch.zeros(eng.world, **u32)
+        self.counts_host = torch.zeros(2, eng.world, dtype=torch.int64).pin_memory()
+        self.ws_sort = torch.zeros(_ru(max(eng.h.query("ctr_sort_ws_bytes", n), 4 * (n // 2048 + 8)), 256),
+                                   dtype=torch.uint8, device=dev)
+        self.ev_local, self.ev_ready, self.ev_free = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
+        self.cap = 0
+        self.B = self.U = self.n_req = 0
+        self.send_counts = self.recv_counts = None
+        self.batch_id = None
+        self.on_side = False
+        self.in_flight = False
+
+    def ensure_owner(self, eng: "ShardedCtrEngine", n_req: int) -> None:
+        if n_req <= self.cap:
+            return
+        cap = max(int(n_req * 1.25), 1024)
+        u32 = dict(dtype=torch.int32, device=eng.dev)
+        self.req = torch.zeros(cap, **u32)
+        if eng.train_mode:
+            self.o_keys, self.o_idx, self.o_uniq, self.o_uidx = (torch.zeros(cap, **u32) for _ in range(4))
+            self.o_seg = torch.zeros(cap + 2, **u32)
+            self.o_nuniq = torch.zeros(1, **u32)
+            self.o_ws = torch.zeros(_ru(max(eng.h.query("ctr_sort_ws_bytes", cap), 4 * (cap // 2048 + 8)), 256),
+                                    dtype=torch.uint8, device=eng.dev)
+        self.cap = cap
+
+
 class ShardedCtrEngine(CtrEngine):
     def __init__(self, spec: ModelSpec, max_batch: int, group=None, **kw):
         if not dist.is_initialized():
@@ -30,48 +73,31 @@ class ShardedCtrEngine(CtrEngine):
         self.wire = spec.grad_stride          # floats per row on the wire (k [+1], rounded up to 4): vectors and gradients
         super().__init__(spec, max_batch, world=world, rank=rank, **kw)
         s, B, dev = spec, self.Bmax, self.dev
-        u32 = dict(dtype=torch.int32, device=dev)
         f32 = dict(dtype=torch.float32, device=dev)
-        if not self.train_mode:      # the de-dup structure is needed by the forward exchange, training or not
-            self.n_extra = s.C if (s.use_fm and s.fm_cont) else 0
-            n = B * s.ids_ld + self.n_extra
-            self.keys, self.perm, self.uidx, self.uniq = (torch.zeros(max(n, 1), **u32) for _ in range(4))
-            self.seg_start = torch.zeros(n + 2, **u32)
-            self.n_unique = torch.zeros(1, **u32)
-            self.ws_sort = torch.zeros(_ru(max(self.h.query("ctr_sort_ws_bytes", n), 4 * (n // 2048 + 8)), 256),
-                                       dtype=torch.uint8, device=dev)
-        n = B * s.ids_ld + self.n_extra
-        self.n_max = n
-        self.inv = torch.zeros(max(n, 1), **u32)
-        self.counts = torch.zeros(world, **u32)
-        self.rows_recv = torch.zeros(n + 1, self.wire, **f32)
+        self.n_extra = s.C if (s.use_fm and s.fm_cont) else 0
+        self.n_max = B * s.ids_ld + self.n_extra
+        if not self.train_mode:
+            self.side = torch.cuda.Stream(device=dev)
+        self.plans = [_IdPlan(self), _IdPlan(self)]
+        self.cur: Optional[_IdPlan] = None
+        self.rows_recv = torch.zeros(self.n_max + 1, self.wire, **f32)
         self.cont_buf = torch.zeros(max(s.C, 1), self.wire, **f32)
-        self.grads_send = torch.zeros(max(n, 1), self.wire, **f32) if self.train_mode else None
-        self._cap = 0
-        self._ensure_owner(n)
-        self.send_counts = self.recv_counts = None
-        self.n_req = self.U = 0
-        self.exchange_rows_step = 0          # rows this rank sent+received in the last step (reported by bench.py)
+        self.grads_send = torch.zeros(max(self.n_max, 1), self.wire, **f32) if self.train_mode else None
+        self._row_cap = 0
+        self._ensure_rows(self.n_max)
+        self.U = self.n_req = 0
 
-    # ---- owner-side buffers grow with the largest request seen ------------------------------------------------
-    def _ensure_owner(self, n_req: int) -> None:
-        if n_req <= self._cap:
+    def _ensure_rows(self, n_req: int) -> None:
+        """owner-side float staging (vectors out, gradients in) grows with the largest request seen"""
+        if n_req <= self._row_cap:
             return
         cap = max(int(n_req * 1.25), 1024)
-        dev = self.dev
-        u32 = dict(dtype=torch.int32, device=dev)
-        f32 = dict(dtype=torch.float32, device=dev)
-        self.req = torch.zeros(cap, **u32)
+        f32 = dict(dtype=torch.float32, device=self.dev)
         self.rows_send = torch.zeros(cap, self.wire, **f32)
         if self.train_mode:
             self.g_recv = torch.zeros(cap, self.wire, **f32)
             self.g_own = torch.zeros(cap, self.wire, **f32)
-            self.o_keys, self.o_idx, self.o_uniq, self.o_uidx = (torch.zeros(cap, **u32) for _ in range(4))
-            self.o_seg = torch.zeros(cap + 2, **u32)
-            self.o_nuniq = torch.zeros(1, **u32)
-            self.o_ws = torch.zeros(_ru(max(self.h.query("ctr_sort_ws_bytes", cap), 4 * (cap // 2048 + 8)), 256),
-                                    dtype=torch.uint8, device=dev)
-        self._cap = cap
+        self._row_cap = cap
 
     # ---- layout hooks ------------------------------------------------------------------------------------------
     def global_batch(self, B: int) -> int:
@@ -98,62 +124,158 @@ class ShardedCtrEngine(CtrEngine):
             full[o::self.world] = t[:cnt].cpu().numpy()
         return full
 
-    # ---- forward: de-dup -> ids all-to-all -> owner gather -> vectors all-to-all -> fused gather+FM ---------------
+    # ---- id plans ----------------------------------------------------------------------------------------------
+    def _build_local(self, pl: _IdPlan, B: int, stream: torch.cuda.Stream) -> None:
+        """enqueue on `stream`: sort / de-dup / per-owner counts / inverse map, then the counts all-to-all and an
+        async copy of (send, recv) counts to pinned host memory.  No host synchronisation."""
+        s, h, sp = self.spec, self.h, self.plan
+        st = stream.cuda_stream
+        n = B * s.ids_ld + self.n_extra
+        ws, wsn = ptr(pl.ws_sort), pl.ws_sort.numel()
+        h.call("ctr_sort_ids", st, ptr(pl.ids), self.id_bytes, B, s.ids_ld, 0, s.ids_ld, 0, int(s.zero_row0),
+               s.cont_base, self.n_extra, self.world, sp.local_bits, sp.key_bits, ptr(pl.keys), ptr(pl.perm), ws, wsn)
+        h.call("ctr_unique_segments", st, ptr(pl.keys), n, ptr(pl.uniq), ptr(pl.seg_start), ptr(pl.uidx),
+               ptr(pl.n_unique), ws, wsn)
+        h.call("ctr_shard_counts", st, ptr(pl.uniq), ptr(pl.n_unique), self.world, sp.local_bits, ptr(pl.counts))
+        h.call("ctr_invert_perm", st, ptr(pl.perm), ptr(pl.uidx), n, ptr(pl.inv))
+        with torch.cuda.stream(stream):
+            send = pl.counts.to(torch.int64)
+            recv = _shard.exchange_counts(send, self.group)           # all-to-all #1a
+            pl.counts_host.copy_(torch.stack([send, recv]), non_blocking=True)
+            pl.ev_local.record(stream)
+        pl.B = B
+
+    def _build_exchange(self, pl: _IdPlan, stream: torch.cuda.Stream) -> None:
+        """host reads the split sizes (NCCL wants them on the host), then on `stream`: the key all-to-all and the
+        owner-side stable sort + run structure of the requested rows"""
+        h, sp = self.h, self.plan
+        pl.ev_local.synchronize()
+        both = pl.counts_host.tolist()
+        pl.send_counts, pl.recv_counts = [int(x) for x in both[0]], [int(x) for x in both[1]]
+        pl.U, pl.n_req = sum(pl.send_counts), sum(pl.recv_counts)
+        pl.ensure_owner(self, pl.n_req)
+        n_req, st = pl.n_req, stream.cuda_stream
+        with torch.cuda.stream(stream):
+            _shard.exchange(pl.uniq[:pl.U], pl.send_counts, pl.recv_counts, out=pl.req, group=self.group)   # #1b
+            if self.train_mode and n_req:
+                pl.o_keys[:n_req].copy_(pl.req[:n_req])
+                torch.arange(n_req, out=pl.o_idx[:n_req])
+                ws, wsn = ptr(pl.o_ws), pl.o_ws.numel()
+                # stable sort by local row: equal rows keep peer order, so the owner's sum is order-fixed
+                h.call("ctr_sort_pairs", st, ptr(pl.o_keys), ptr(pl.o_idx), n_req, sp.local_bits, ws, wsn)
+                h.call("ctr_unique_segments", st, ptr(pl.o_keys), n_req, ptr(pl.o_uniq), ptr(pl.o_seg), ptr(pl.o_uidx),
+                       ptr(pl.o_nuniq), ws, wsn)
+            pl.ev_ready.record(stream)
+
+    def _activate(self, pl: _IdPlan) -> None:
+        self.cur = pl
+        self.ids, self.keys, self.perm, self.uidx, self.uniq = pl.ids, pl.keys, pl.perm, pl.uidx, pl.uniq
+        self.seg_start, self.n_unique = pl.seg_start, pl.n_unique
+        self.U, self.n_req = pl.U, pl.n_req
+
+    def _other_plan(self) -> _IdPlan:
+        return self.plans[1] if self.cur is self.plans[0] else self.plans[0]
+
+    def load_batch(self, batch: Dict, non_blocking: bool = True, skip_ids: bool = False) -> int:
+        main = torch.cuda.current_stream(self.dev)
+        pl = next((c for c in self.plans if c.in_flight and c.batch_id == id(batch)), None)
+        if pl is not None:                         # prefetched during the previous step
+            B = super().load_batch(batch, non_blocking, skip_ids=True)
+            if self._pending_exchange is pl:       # (only if the previous step never reached its sparse update)
+                self._build_exchange(pl, self.side)
+                self._pending_exchange = None
+            pl.in_flight = False
+        else:
+            pl = self._other_plan() if self.cur is not None else self.plans[0]
+            if pl.in_flight:                       # a prefetched plan nobody claimed: let it drain, then reuse it
+                if self._pending_exchange is pl:
+                    self._build_exchange(pl, self.side)
+                    self._pending_exchange = None
+                main.wait_event(pl.ev_ready)
+                pl.in_flight = False
+            self.ids = pl.ids
+            B = super().load_batch(batch, non_blocking)
+            self._build_local(pl, B, main)
+            self._build_exchange(pl, main)
+            pl.on_side = False
+        self._activate(pl)
+        return B
+
+    _pending_exchange: Optional[_IdPlan] = None
+
+    def _after_forward(self, next_batch: Optional[Dict]) -> None:
+        """start the id plan of the next batch on the side stream (upload ids, sort, de-dup, counts all-to-all)"""
+        if next_batch is None or not self.spec.ids_ld:
+            return
+        pl = self._other_plan()
+        if pl.in_flight:
+            return
+        cate = next_batch["cate_feats"]
+        if not isinstance(cate, torch.Tensor):
+            cate = torch.as_tensor(np.asarray(cate))
+        B = int(cate.shape[0])
+        main = torch.cuda.current_stream(self.dev)
+        self.side.wait_event(pl.ev_free) if pl.batch_id is not None else None
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self.side.wait_event(ev)                  # a device-resident batch may still be in production on the main stream
+        with torch.cuda.stream(self.side):
+            pl.ids[:B].copy_(cate.to(self.id_torch) if cate.dtype != self.id_torch else cate, non_blocking=True)
+        self._build_local(pl, B, self.side)
+        pl.batch_id, pl.in_flight, pl.on_side = id(next_batch), True, True
+        self._pending_exchange = pl
+
+    def _end_step(self) -> None:
+        if self.cur is not None:
+            self.cur.ev_free.record(torch.cuda.current_stream(self.dev))
+            if self.cur.batch_id is None:
+                self.cur.batch_id = -1             # marks ev_free as recorded
+
+    # ---- forward: owner gather -> vectors all-to-all -> fused gather+FM -------------------------------------------
     def _launch_sort(self, B: int) -> None:
-        self._sort_wide(B, self._stream())      # embedding ids are sorted inside _embed_forward (predict needs it too)
+        self._sort_wide(B, self._stream())      # embedding ids are planned in load_batch / prefetched
 
     def _embed_forward(self, B: int) -> None:
-        s, st, h, pl = self.spec, self._stream(), self.h, self.plan
-        n = B * s.ids_ld + self.n_extra
-        ws, wsn = ptr(self.ws_sort), self.ws_sort.numel()
-        h.call("ctr_sort_ids", st, ptr(self.ids), self.id_bytes, B, s.ids_ld, 0, s.ids_ld, 0, int(s.zero_row0),
-               s.cont_base, self.n_extra, self.world, pl.local_bits, pl.key_bits, ptr(self.keys), ptr(self.perm), ws, wsn)
-        h.call("ctr_unique_segments", st, ptr(self.keys), n, ptr(self.uniq), ptr(self.seg_start), ptr(self.uidx),
-               ptr(self.n_unique), ws, wsn)
-        h.call("ctr_shard_counts", st, ptr(self.uniq), ptr(self.n_unique), self.world, pl.local_bits, ptr(self.counts))
-        h.call("ctr_invert_perm", st, ptr(self.perm), ptr(self.uidx), n, ptr(self.inv))
-        # all-to-all #1: counts (one host read per step: NCCL wants split sizes on the host), then unique keys
-        self.send_counts, self.recv_counts = _shard.split_sizes(self.counts, self.group)
-        U, n_req = sum(self.send_counts), sum(self.recv_counts)
-        self.U, self.n_req = U, n_req
-        self._ensure_owner(n_req)
-        _shard.exchange(self.uniq[:U], self.send_counts, self.recv_counts, out=self.req, group=self.group)
+        s, st, h, sp, pl = self.spec, self._stream(), self.h, self.plan, self.cur
+        main = torch.cuda.current_stream(self.dev)
+        if pl.on_side:
+            main.wait_event(pl.ev_ready)
+        U, n_req = pl.U, pl.n_req
+        self._ensure_rows(n_req)
         # owners gather [v | w] rows; all-to-all #2 returns them in the requester's unique-list order
         if n_req:
-            h.call("ctr_gather_rows", st, ptr(self.table), s.table_stride, ptr(self.req), None, n_req, pl.local_bits,
+            h.call("ctr_gather_rows", st, ptr(self.table), s.table_stride, ptr(pl.req), None, n_req, sp.local_bits,
                    s.row_width, ptr(self.rows_send), self.wire)
-        _shard.exchange(self.rows_send[:n_req], self.recv_counts, self.send_counts, out=self.rows_recv, group=self.group)
+        _shard.exchange(self.rows_send[:n_req], pl.recv_counts, pl.send_counts, out=self.rows_recv, group=self.group)
         self.rows_recv[U].zero_()    # the run of padding ids (key 0xFFFFFFFF), if any, is unique index U
-        self.exchange_rows_step = U + n_req
         if s.use_fm and s.fm_cont and s.C:
-            h.call("ctr_gather_rows", st, ptr(self.rows_recv), self.wire, ptr(self.inv[B * s.ids_ld:]), None, s.C, 0,
+            h.call("ctr_gather_rows", st, ptr(self.rows_recv), self.wire, ptr(pl.inv[B * s.ids_ld:]), None, s.C, 0,
                    s.row_width, ptr(self.cont_buf), self.wire)
         cfg = self._cfg(B)
         if s.Fm:
-            h.call("ctr_pooled_gather_fwd", st, cfg, ptr(self.rows_recv), ptr(self.inv), ptr(self.multi_start), None,
+            h.call("ctr_pooled_gather_fwd", st, cfg, ptr(self.rows_recv), ptr(pl.inv), ptr(self.multi_start), None,
                    ptr(self.x0), ptr(self.pooled_first), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first))
-        h.call("ctr_fm_gather_fwd", st, cfg, ptr(self.rows_recv), ptr(self.inv), 0, ptr(self.cont), ptr(self.vec),
+        h.call("ctr_fm_gather_fwd", st, cfg, ptr(self.rows_recv), ptr(pl.inv), 0, ptr(self.cont), ptr(self.vec),
                ptr(self._cont_rows()), ptr(self.pooled_first), ptr(self.x0), ptr(self.fm), ptr(self.sum_e))
 
     # ---- backward: per-unique gradients -> all-to-all #3 -> owner sum in peer order -> Adam ------------------------
     def _sparse_update(self, B: int, n: int, hp: AdamHP) -> None:
-        s, st, h, pl = self.spec, self._stream(), self.h, self.plan
-        U, n_req = self.U, self.n_req
-        h.call("ctr_embed_bwd_finalize", st, ptr(self.seg_start), ptr(self.n_unique), n, s.row_width, self.wire,
+        s, st, h, sp, pl = self.spec, self._stream(), self.h, self.plan, self.cur
+        if self._pending_exchange is not None:
+            # by now the whole forward + dense backward of THIS step is queued on the main stream, so the host read
+            # of the next plan's split sizes does not starve the GPU; its key all-to-all precedes this step's
+            # gradient all-to-all on every rank (fixed collective order)
+            self._build_exchange(self._pending_exchange, self.side)
+            self._pending_exchange = None
+        U, n_req = pl.U, pl.n_req
+        h.call("ctr_embed_bwd_finalize", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.row_width, self.wire,
                ptr(self.part), ptr(self.grads_send))
-        _shard.exchange(self.grads_send[:U], self.send_counts, self.recv_counts, out=self.g_recv, group=self.group)
+        _shard.exchange(self.grads_send[:U], pl.send_counts, pl.recv_counts, out=self.g_recv, group=self.group)
         if not n_req:
             return
-        self.o_keys[:n_req].copy_(self.req[:n_req])
-        torch.arange(n_req, out=self.o_idx[:n_req])
-        ws, wsn = ptr(self.o_ws), self.o_ws.numel()
-        # stable sort by local row: equal rows keep peer order, so the sum below is order-fixed
-        h.call("ctr_sort_pairs", st, ptr(self.o_keys), ptr(self.o_idx), n_req, pl.local_bits, ws, wsn)
-        h.call("ctr_unique_segments", st, ptr(self.o_keys), n_req, ptr(self.o_uniq), ptr(self.o_seg), ptr(self.o_uidx),
-               ptr(self.o_nuniq), ws, wsn)
-        h.call("ctr_segment_sum_rows", st, ptr(self.o_seg), ptr(self.o_nuniq), n_req, ptr(self.o_idx), ptr(self.g_recv),
+        h.call("ctr_segment_sum_rows", st, ptr(pl.o_seg), ptr(pl.o_nuniq), n_req, ptr(pl.o_idx), ptr(self.g_recv),
                self.wire, s.row_width, ptr(self.g_own), self.wire)
-        h.call("ctr_adam_rows", st, ptr(self.o_uniq), ptr(self.o_nuniq), n_req, pl.local_bits, ptr(self.g_own), None,
+        h.call("ctr_adam_rows", st, ptr(pl.o_uniq), ptr(pl.o_nuniq), n_req, sp.local_bits, ptr(self.g_own), None,
                self.wire, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
                self.rows_local, ptr(self.touched), None, 0, hp)
 
@@ -165,3 +287,8 @@ class ShardedCtrEngine(CtrEngine):
 
     def _global_loss(self) -> torch.Tensor:
         return self.grad[self.n_dense:self.n_dense + 1].clone()
+
+    def predict(self, batch: Optional[Dict] = None) -> torch.Tensor:
+        out = super().predict(batch)
+        self._end_step()
+        return out

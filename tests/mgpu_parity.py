@@ -103,6 +103,22 @@ def main():
         if rank == 0:
             print("step %d ok: loss %.6f (oracle %.6f), worst param rel err %.3g, U=%d n_req=%d" % (
                 step, loss, float(loss_ref), worst, eng.U, eng.n_req))
+    # ---- free-running, with the id plan of step i+1 prefetched under step i (next_batch): the trajectory stays
+    # on the oracle's up to rounding
+    steps = 4
+    seq = [[H.make_batch(alg, hp, seed=7000 + i * world + r, B=Bl) for r in range(world)] for i in range(steps + 1)]
+    for i in range(steps):
+        glob = {k: torch.cat([b[k] for b in seq[i]], dim=0) for k in seq[i][0]}
+        loss_ref, p = O.train_step(alg, p, st, H.oracle_batch(glob, torch.float64), hp, adam_mode=adam_mode)
+        loss = float(eng.train_step(seq[i][rank], next_batch=seq[i + 1][rank]).item())
+        assert abs(loss - float(loss_ref)) < 1e-4 * max(1.0, abs(float(loss_ref))), ("prefetch step", i, loss, float(loss_ref))
+    got = eng.get_weights()
+    for n in p:
+        ref = p[n].numpy().reshape(-1)
+        d = np.abs(got[n].reshape(-1).astype(np.float64) - ref) / max(float(np.max(np.abs(ref))), 1e-30)
+        assert np.percentile(d, 99.9) < 2e-3, (n, float(np.percentile(d, 99.9)), float(d.max()))
+    if rank == 0:
+        print("prefetched free-running steps ok")
     dist.barrier()
     if rank == 0:
         print("MGPU PARITY OK alg=%s adam=%s world=%d" % (alg, adam_mode, world))
