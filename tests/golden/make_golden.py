@@ -1,0 +1,79 @@
+"""Generates the frozen vectors in this directory from the oracle (oracle/ctr_oracle.py).
+
+    python tests/golden/make_golden.py
+
+The reference ships no golden vectors and TensorFlow 1.x cannot be imported here, so these files do
+NOT pin the oracle to the reference; they freeze the oracle's outputs on fixed inputs so that (1) any later edit of
+the oracle that changes results is caught on CPU (tests/test_golden.py) and (2) the CUDA path is checked against
+committed numbers, not only against whatever the oracle computes today (tests/test_gpu_golden.py).
+One file per model: inputs (parameters by their reference variable names, one batch), the forward outputs and the
+state after TWO train steps with TF1 dense Adam (step 2 is where lazy and dense Adam differ).
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+from oracle import ctr_oracle as O   # noqa: E402
+from deep_learning_b200 import data as D   # noqa: E402
+
+
+def tiny_hp(alg):
+    kw = dict(hidden_units=[8, 4], batch_size=16, embedding_size=4, cont_field_size=3, cate_field_size=5,
+              cate_feats_size=60, l2_reg=1e-3, learning_rate=1e-2)
+    if alg in ("deepfm_multi", "dnn_multi"):
+        kw.update(cate_feats_size=81, multi_feats_size=8, multi_field_size=2, multi_feats_range=[[0, 3, "m0"], [3, 8, "m1"]])
+    if alg == "wdl":
+        kw.update(cate_index_size=60, wide_field_size=5)
+    return O.HParams(**kw)
+
+
+def tiny_batch(alg, hp, seed):
+    multi = alg in ("deepfm_multi", "dnn_multi")
+    if multi:
+        sizes, msizes, tops = D.field_sizes(60, 5), [10, 10], [3, 5]
+    else:
+        sizes, msizes, tops = D.field_sizes(hp.cate_feats_size, 5), [], []
+    return D.synthetic_batch(hp.batch_size, hp.cont_field_size, hp.cate_field_size, sizes, seed, multi_top_n=tops,
+                             multi_sizes=msizes, wide=hp.wide_field_size if alg == "wdl" else 0, dist="uniform",
+                             reserve_zero=multi, id_dtype=torch.int64 if multi else torch.int32)
+
+
+def main():
+    for alg in ("deepfm", "deepfm_multi", "wdl", "dnn", "dnn_multi"):
+        hp = tiny_hp(alg)
+        p = O.init_params(alg, hp, seed=2019, dtype=torch.float64)
+        # golden inputs are the fp32-representable values (what gets injected into the CUDA engine)
+        p = {k: v.float().double() for k, v in p.items()}
+        st = O.adam_init(p)
+        out = {}
+        for k, v in p.items():
+            out["param/" + k] = v.numpy()
+        batches = [tiny_batch(alg, hp, seed=11), tiny_batch(alg, hp, seed=12)]
+        for i, b in enumerate(batches):
+            for k, v in b.items():
+                out["batch%d/%s" % (i, k)] = v.numpy()
+        ob = {k: (v.double() if v.is_floating_point() else v.long()) for k, v in batches[0].items()}
+        logit, score = O.FORWARD[alg](p, ob, hp)
+        out["fwd/logit"], out["fwd/score"] = logit.numpy(), score.numpy()
+        out["fwd/auc"] = np.float64(O.roc_auc(batches[0]["label"].numpy(), score.numpy()))
+        for i, b in enumerate(batches):
+            ob = {k: (v.double() if v.is_floating_point() else v.long()) for k, v in b.items()}
+            loss, p = O.train_step(alg, p, st, ob, hp, adam_mode="tf_dense")
+            out["step%d/loss" % (i + 1)] = np.float64(float(loss))
+            for k, v in p.items():
+                out["step%d/%s" % (i + 1, k)] = v.numpy()
+        path = os.path.join(HERE, "%s_tiny.npz" % alg)
+        np.savez_compressed(path, **out)
+        print(path, os.path.getsize(path), "bytes")
+
+
+if __name__ == "__main__":
+    main()
