@@ -51,11 +51,12 @@ _PROTOS = {
                                  c_vp, c_i64]),
     "ctr_mlp_bwd_weight_ws_bytes": (c_i64, [c_vp, c_i32, c_i32, c_i32, c_i32]),
     "ctr_mlp_bwd_weight": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp,
-                                   c_vp, c_i64]),
+                                   c_vp, c_i64, c_i32]),
     "ctr_transpose": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_i64, c_i32]),
     "ctr_round_tf32_copy": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64]),
+    "ctr_head_ws_bytes": (c_i64, [c_vp, c_i32, c_i32, c_i32]),
     "ctr_head_fwd": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp,
-                             c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64]),
+                             c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
     "ctr_head_bwd_deep": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64, c_vp, c_i64]),
     "ctr_colsum_ws_bytes": (c_i64, [c_vp, c_i32, c_i32]),
     "ctr_colsum": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64]),

@@ -248,32 +248,77 @@ __global__ void clear_flags_kernel(uint8_t* __restrict__ f, int64_t n) {
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) f[i] = 0;
 }
 
-// gradient of the continuous-field rows: pass 1 = per-block partial over a fixed slice of samples
+// gradient of the continuous-field rows, pass 1.  K lanes own the K coordinates of one sample slot, a warp walks
+// 32/K samples at a time (coalesced sum_e rows, broadcast cont / dlogit), every lane keeps one accumulator per
+// field; fields are taken CONT_FT at a time.  Fixed sample -> (block, warp, slot) assignment and fixed reduction
+// trees: deterministic.  Block partials go to ws[block][c*(K+1) + j] (j == K: the first-order weight).
+constexpr int CONT_FT = 16;
+template <int K>
 __global__ void __launch_bounds__(256)
 cont_bwd_pass1(const ctr_embed_cfg cfg, const float* __restrict__ cont, const float* __restrict__ cont_rows,
                const float* __restrict__ sum_e, const float* __restrict__ dlogit, const float* __restrict__ w_fm,
                float* __restrict__ ws) {
-    const int K = cfg.k, C = cfg.C, W = K + 1;
-    const int npairs = C * W;
+    constexpr int SPW = 32 / K;                 // sample slots per warp
+    constexpr int W = K + 1;
+    __shared__ float red[8][CONT_FT * (K + 1)];
+    const int C = cfg.C, npairs = C * W;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int j = lane % K, slot = lane / K;
     const int64_t per = ((int64_t) cfg.B + gridDim.x - 1) / gridDim.x;
     const int64_t lo = per * blockIdx.x, hi = (lo + per < cfg.B) ? lo + per : cfg.B;
     const float* w1c = w_fm + cfg.Fc + cfg.Fm;
-    const float* w2 = w_fm + cfg.Fc + cfg.Fm + C;
-    for (int pr = threadIdx.x; pr < npairs; pr += blockDim.x) {
-        const int c = pr / W, j = pr - c * W;
-        float acc = 0.f;
-        if (j < K) {
-            const float th = cont_rows[(int64_t) c * cfg.table_stride + j];
-            const float w = w2[j];
-            for (int64_t b = lo; b < hi; ++b) {
-                const float x = cont[b * C + c];
-                acc = fmaf(x * dlogit[b] * w, sum_e[b * K + j] - x * th, acc);
-            }
-        } else if (cfg.has_first) {
-            const float w = w1c[c];
-            for (int64_t b = lo; b < hi; ++b) acc = fmaf(dlogit[b] * w, cont[b * C + c], acc);
+    const float w2j = w_fm[cfg.Fc + cfg.Fm + C + j];
+    const bool has_first = cfg.has_first != 0;
+    for (int c0 = 0; c0 < C; c0 += CONT_FT) {
+        float th[CONT_FT], acc[CONT_FT], accw[CONT_FT];
+#pragma unroll
+        for (int t = 0; t < CONT_FT; ++t) {
+            th[t] = (c0 + t < C) ? cont_rows[(int64_t) (c0 + t) * cfg.table_stride + j] : 0.f;
+            acc[t] = 0.f;
+            accw[t] = 0.f;
         }
-        ws[(int64_t) blockIdx.x * npairs + pr] = acc;
+        for (int64_t b = lo + (int64_t) w * SPW + slot; b < hi; b += 8 * SPW) {
+            const float dl = dlogit[b];
+            const float se = sum_e[b * K + j];
+            const float* xr = cont + b * C + c0;
+#pragma unroll
+            for (int t = 0; t < CONT_FT; ++t) {
+                if (c0 + t < C) {
+                    const float x = xr[t];
+                    const float xd = x * dl;
+                    acc[t] = fmaf(xd * w2j, se - x * th[t], acc[t]);
+                    accw[t] += xd;
+                }
+            }
+        }
+        // sample slots of the warp, then the 8 warps of the block
+#pragma unroll
+        for (int t = 0; t < CONT_FT; ++t) {
+#pragma unroll
+            for (int o = K; o < 32; o <<= 1) {
+                acc[t] += __shfl_xor_sync(0xffffffffu, acc[t], o);
+                accw[t] += __shfl_xor_sync(0xffffffffu, accw[t], o);
+            }
+        }
+        if (slot == 0) {
+#pragma unroll
+            for (int t = 0; t < CONT_FT; ++t) {
+                red[w][t * W + j] = acc[t];
+                if (j == 0) red[w][t * W + K] = accw[t];
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < CONT_FT * W; i += blockDim.x) {
+            const int t = i / W, jj = i - t * W;
+            if (c0 + t < C) {
+                float a = 0.f;
+#pragma unroll
+                for (int ww = 0; ww < 8; ++ww) a += red[ww][i];
+                if (jj == K) a = has_first ? a * w1c[c0 + t] : 0.f;
+                ws[(int64_t) blockIdx.x * npairs + (c0 + t) * W + jj] = a;
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -457,7 +502,12 @@ extern "C" int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg*
     CTR_REQUIRE(h, cfg->grad_stride >= cfg->k + 1, "fm_cont_bwd: grad_stride too small");
     if (ws_bytes < ctr_cont_bwd_ws_bytes(h, cfg)) return ctr_fail(h, CTR_E_WORKSPACE, "fm_cont_bwd: ws too small");
     const int nblk = cont_blocks(h, cfg->B);
-    cont_bwd_pass1<<<nblk, 256, 0, ctr_st(s)>>>(*cfg, cont, cont_rows, sum_e, dlogit, w_fm, (float*) ws);
+    switch (cfg->k) {
+        case 4: cont_bwd_pass1<4><<<nblk, 256, 0, ctr_st(s)>>>(*cfg, cont, cont_rows, sum_e, dlogit, w_fm, (float*) ws); break;
+        case 8: cont_bwd_pass1<8><<<nblk, 256, 0, ctr_st(s)>>>(*cfg, cont, cont_rows, sum_e, dlogit, w_fm, (float*) ws); break;
+        case 16: cont_bwd_pass1<16><<<nblk, 256, 0, ctr_st(s)>>>(*cfg, cont, cont_rows, sum_e, dlogit, w_fm, (float*) ws); break;
+        default: cont_bwd_pass1<32><<<nblk, 256, 0, ctr_st(s)>>>(*cfg, cont, cont_rows, sum_e, dlogit, w_fm, (float*) ws); break;
+    }
     CTR_CHECK_LAUNCH(h, "cont_bwd_pass1");
     const int npairs = cfg->C * (cfg->k + 1);
     cont_bwd_pass2<<<(unsigned) ctr_cdiv((int64_t) npairs * 32, 256), 256, 0, ctr_st(s)>>>((const float*) ws, nblk, cfg->C, cfg->k,

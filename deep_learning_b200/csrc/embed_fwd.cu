@@ -95,7 +95,9 @@ fm_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, c
         const float x = vec[b * (int64_t) V + j];
         x0row[cont_col + C + j] = rnd ? ctr_round_tf32(x) : x;
     }
-    for (int j = cont_col + C + V + lane; j < cfg.x0_ld; j += 32) x0row[j] = 0.f;
+    // pad columns: a 1.0 at column D0 lets the layer-0 weight-gradient GEMM produce the bias gradient as an extra
+    // row (ctr_mlp_bwd_weight x_ones_col); the forward GEMM reads exactly D0 columns and never sees it
+    for (int j = cont_col + C + V + lane; j < cfg.x0_ld; j += 32) x0row[j] = (j == cont_col + C + V) ? 1.f : 0.f;
 
     if (!USE_FM) return;
 

@@ -6,61 +6,144 @@ namespace {
 
 constexpr float LOG_LOSS_EPS = 1e-7f;   // tf.losses.log_loss default epsilon
 
-// one warp per sample
+// One warp walks HEAD_SPW consecutive samples; lane l owns columns l, l+32, ... of the deep row (and of the fm row),
+// so the row stays in registers between the dot product, the ReLU-gradient write and the head-weight gradient
+//   d w_deep[j] = sum_b dlogit[b] * deep[b,j],  d w_fm[j] = sum_b dlogit[b] * fm[b,j],  d bias = sum_b dlogit[b]
+// (models/deepfm.py:130,143 differentiated), which leave the kernel as one partial row per block: no separate
+// pass over the activations.  All sums run in a fixed order (deterministic).
+constexpr int HEAD_WARPS = 8;
+constexpr int HEAD_SPW = 16;                       // samples per warp
+constexpr int HEAD_SPB = HEAD_WARPS * HEAD_SPW;    // samples per block
+constexpr int HEAD_MAXT = 16;                      // deep columns per lane  (H <= 512)
+constexpr int HEAD_MAXF = 4;                       // fm columns per lane    (n_fm <= 128)
+
 __global__ void __launch_bounds__(256)
 head_fwd_kernel(int B, float inv_bg, const float* __restrict__ fm, int64_t fm_ld, int n_fm, const float* __restrict__ w_fm,
                 const float* __restrict__ deep, int64_t deep_ld, int H, const float* __restrict__ w_deep,
                 const float* __restrict__ extra, const float* __restrict__ bias, const float* __restrict__ label,
                 float* __restrict__ logit, float* __restrict__ score, float* __restrict__ dlogit,
-                float* __restrict__ dz_last, int64_t lddz, int round_tf32, float* __restrict__ loss_part) {
-    __shared__ float wl[8];
+                float* __restrict__ dz_last, int64_t lddz, int round_tf32, float* __restrict__ loss_part,
+                float* __restrict__ colpart) {
+    extern __shared__ float sm[];                  // [HEAD_WARPS][H + n_fm + 1] when colpart, else [HEAD_WARPS]
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int64_t b = (int64_t) blockIdx.x * 8 + w;
-    float l = 0.f;
-    if (b < B) {
+    const int ncol = H + n_fm + 1;
+    float wd[HEAD_MAXT], wf[HEAD_MAXF], gd[HEAD_MAXT], gf[HEAD_MAXF];
+#pragma unroll
+    for (int t = 0; t < HEAD_MAXT; ++t) {
+        const int j = lane + 32 * t;
+        wd[t] = j < H ? w_deep[j] : 0.f;
+        gd[t] = 0.f;
+    }
+#pragma unroll
+    for (int t = 0; t < HEAD_MAXF; ++t) {
+        const int j = lane + 32 * t;
+        wf[t] = j < n_fm ? w_fm[j] : 0.f;
+        gf[t] = 0.f;
+    }
+    float gb = 0.f, lsum = 0.f;
+    const float bs = bias ? bias[0] : 0.f;
+    const int64_t b0 = (int64_t) blockIdx.x * HEAD_SPB + (int64_t) w * HEAD_SPW;
+    for (int i = 0; i < HEAD_SPW; ++i) {
+        const int64_t b = b0 + i;
+        if (b >= B) break;                         // uniform across the warp
+        float rd[HEAD_MAXT], rf[HEAD_MAXF];
         float acc = 0.f;
-        if (n_fm > 0) {
-            const float* r = fm + b * fm_ld;
-            for (int j = lane; j < n_fm; j += 32) acc = fmaf(r[j], w_fm[j], acc);
+        const float* r = deep + b * deep_ld;
+#pragma unroll
+        for (int t = 0; t < HEAD_MAXT; ++t) {
+            const int j = lane + 32 * t;
+            rd[t] = j < H ? r[j] : 0.f;
+            acc = fmaf(rd[t], wd[t], acc);
         }
-        if (H > 0) {
-            const float* r = deep + b * deep_ld;
-            for (int j = lane; j < H; j += 32) acc = fmaf(r[j], w_deep[j], acc);
+        const float* rfm = fm + b * fm_ld;
+#pragma unroll
+        for (int t = 0; t < HEAD_MAXF; ++t) {
+            const int j = lane + 32 * t;
+            rf[t] = j < n_fm ? rfm[j] : 0.f;
+            acc = fmaf(rf[t], wf[t], acc);
         }
         acc = ctr_warp_sum(acc);
-        float z = acc + (extra ? extra[b] : 0.f) + (bias ? bias[0] : 0.f);
-        float p = 1.f / (1.f + expf(-z));
+        const float z = acc + (extra ? extra[b] : 0.f) + bs;
+        const float p = 1.f / (1.f + expf(-z));
         if (lane == 0) {
             if (logit) logit[b] = z;
             if (score) score[b] = p;
         }
         if (label) {
             const float y = label[b];
-            l = -y * logf(p + LOG_LOSS_EPS) - (1.f - y) * logf(1.f - p + LOG_LOSS_EPS);
-            // d/dz [ -y log(p+e) - (1-y) log(1-p+e) ] = (-y/(p+e) + (1-y)/(1-p+e)) * p(1-p), mean over B
+            lsum += -y * logf(p + LOG_LOSS_EPS) - (1.f - y) * logf(1.f - p + LOG_LOSS_EPS);
+            // d/dz [ -y log(p+e) - (1-y) log(1-p+e) ] = (-y/(p+e) + (1-y)/(1-p+e)) * p(1-p), mean over the global batch
             const float dl = (-y / (p + LOG_LOSS_EPS) + (1.f - y) / (1.f - p + LOG_LOSS_EPS)) * p * (1.f - p) * inv_bg;
             if (lane == 0 && dlogit) dlogit[b] = dl;
-            if (dz_last && H > 0) {
-                // gradient through the last ReLU, written while the row is still cache-hot:
-                // dZ_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)
-                const float* r = deep + b * deep_ld;
+            if (dz_last) {
+                // gradient through the last ReLU: dZ_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)
                 float* o = dz_last + b * lddz;
-                for (int j = lane; j < H; j += 32) {
-                    const float g = r[j] > 0.f ? dl * w_deep[j] : 0.f;
-                    o[j] = round_tf32 ? ctr_round_tf32(g) : g;
+#pragma unroll
+                for (int t = 0; t < HEAD_MAXT; ++t) {
+                    const int j = lane + 32 * t;
+                    if (j < H) {
+                        const float g = rd[t] > 0.f ? dl * wd[t] : 0.f;
+                        o[j] = round_tf32 ? ctr_round_tf32(g) : g;
+                    }
                 }
+            }
+            if (colpart) {
+#pragma unroll
+                for (int t = 0; t < HEAD_MAXT; ++t) gd[t] = fmaf(dl, rd[t], gd[t]);
+#pragma unroll
+                for (int t = 0; t < HEAD_MAXF; ++t) gf[t] = fmaf(dl, rf[t], gf[t]);
+                gb += dl;
             }
         }
     }
+    if (label && colpart) {
+        float* mine = sm + w * ncol;
+#pragma unroll
+        for (int t = 0; t < HEAD_MAXT; ++t) {
+            const int j = lane + 32 * t;
+            if (j < H) mine[j] = gd[t];
+        }
+#pragma unroll
+        for (int t = 0; t < HEAD_MAXF; ++t) {
+            const int j = lane + 32 * t;
+            if (j < n_fm) mine[H + j] = gf[t];
+        }
+        if (lane == 0) mine[H + n_fm] = gb;
+        __syncthreads();
+        for (int c = threadIdx.x; c < ncol; c += blockDim.x) {
+            float a = 0.f;
+#pragma unroll
+            for (int ww = 0; ww < HEAD_WARPS; ++ww) a += sm[ww * ncol + c];
+            colpart[(int64_t) blockIdx.x * ncol + c] = a;
+        }
+        __syncthreads();
+    }
     if (label && loss_part) {
-        if (lane == 0) wl[w] = l;
+        if (lane == 0) sm[w] = lsum;
         __syncthreads();
         if (threadIdx.x == 0) {
-            float s = 0.f;
+            float a = 0.f;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) s += wl[i];
-            loss_part[blockIdx.x] = s;
+            for (int i = 0; i < HEAD_WARPS; ++i) a += sm[i];
+            loss_part[blockIdx.x] = a;
         }
+    }
+}
+
+// column sums of the per-block partial rows -> the three head gradients (one warp per column, fixed order)
+__global__ void __launch_bounds__(256)
+head_grad_pass2(const float* __restrict__ colpart, int nblk, int H, int n_fm, float* __restrict__ g_deep,
+                float* __restrict__ g_fm, float* __restrict__ g_bias) {
+    const int ncol = H + n_fm + 1;
+    const int col = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (col >= ncol) return;
+    float a = 0.f;
+    for (int s = lane; s < nblk; s += 32) a += colpart[(int64_t) s * ncol + col];
+    a = ctr_warp_sum(a);
+    if (lane == 0) {
+        if (col < H) { if (g_deep) g_deep[col] = a; }
+        else if (col < H + n_fm) { if (g_fm) g_fm[col - H] = a; }
+        else if (g_bias) g_bias[0] = a;
     }
 }
 
@@ -127,29 +210,46 @@ __global__ void __launch_bounds__(256) colsum_pass2(const float* __restrict__ ws
 
 }  // namespace
 
+extern "C" int64_t ctr_head_ws_bytes(ctr_handle*, int B, int n_fm, int H) {
+    const int64_t nblk = ctr_cdiv(B > 0 ? B : 1, HEAD_SPB);
+    return ctr_align(nblk * 4, 256) + ctr_align(nblk * (int64_t) (H + n_fm + 1) * 4, 256);
+}
+
 extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, int64_t B_global, const float* fm, int64_t fm_ld, int n_fm,
                             const float* w_fm, const float* deep, int64_t deep_ld, int H, const float* w_deep,
                             const float* extra, const float* bias, const float* label, float* logit, float* score,
-                            float* dlogit, float* dz_last, int64_t lddz, int round_tf32, float* loss_out, void* ws,
-                            int64_t ws_bytes) {
+                            float* dlogit, float* dz_last, int64_t lddz, int round_tf32, float* loss_out,
+                            float* g_fm, float* g_deep, float* g_bias, void* ws, int64_t ws_bytes) {
     CTR_REQUIRE(h, B >= 0 && n_fm >= 0 && H >= 0, "head_fwd: negative sizes");
     CTR_REQUIRE(h, n_fm == 0 || (fm && w_fm), "head_fwd: fm inputs null");
     CTR_REQUIRE(h, H == 0 || (deep && w_deep), "head_fwd: deep inputs null");
+    CTR_REQUIRE(h, H <= 32 * HEAD_MAXT && n_fm <= 32 * HEAD_MAXF, "head_fwd: H <= %d and n_fm <= %d supported (got %d, %d)",
+                32 * HEAD_MAXT, 32 * HEAD_MAXF, H, n_fm);
     if (B == 0) return CTR_OK;
     const float inv_bg = 1.f / (float) (B_global > 0 ? B_global : (int64_t) B);
-    const int nblk = (int) ctr_cdiv(B, 8);
-    float* part = nullptr;
-    if (label && loss_out) {
+    const int nblk = (int) ctr_cdiv(B, HEAD_SPB);
+    const bool want_grads = label && (g_fm || g_deep || g_bias);
+    float *part = nullptr, *colpart = nullptr;
+    if (label && (loss_out || want_grads)) {
         CTR_REQUIRE(h, ws != nullptr, "head_fwd: ws null");
-        if (ws_bytes < (int64_t) nblk * 4) return ctr_fail(h, CTR_E_WORKSPACE, "head_fwd: ws too small");
+        if (ws_bytes < ctr_head_ws_bytes(h, B, n_fm, H)) return ctr_fail(h, CTR_E_WORKSPACE, "head_fwd: ws too small");
         part = (float*) ws;
+        if (want_grads) colpart = (float*) ((char*) ws + ctr_align((int64_t) nblk * 4, 256));
     }
-    head_fwd_kernel<<<nblk, 256, 0, ctr_st(s)>>>(B, inv_bg, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra, bias, label,
-                                                 logit, score, dlogit, dz_last, lddz, round_tf32, part);
+    const size_t smem = (colpart ? (size_t) HEAD_WARPS * (H + n_fm + 1) : (size_t) HEAD_WARPS) * sizeof(float);
+    head_fwd_kernel<<<nblk, 256, smem, ctr_st(s)>>>(B, inv_bg, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra, bias,
+                                                    label, logit, score, dlogit, dz_last, lddz, round_tf32,
+                                                    loss_out ? part : nullptr, colpart);
     CTR_CHECK_LAUNCH(h, "head_fwd");
-    if (part) {
+    if (label && loss_out) {
         loss_final_kernel<<<1, 1024, 0, ctr_st(s)>>>(part, nblk, inv_bg, loss_out);
         CTR_CHECK_LAUNCH(h, "loss_final");
+    }
+    if (colpart) {
+        const int ncol = H + n_fm + 1;
+        head_grad_pass2<<<(unsigned) ctr_cdiv((int64_t) ncol * 32, 256), 256, 0, ctr_st(s)>>>(colpart, nblk, H, n_fm, g_deep,
+                                                                                            g_fm, g_bias);
+        CTR_CHECK_LAUNCH(h, "head_grad_pass2");
     }
     return CTR_OK;
 }

@@ -172,7 +172,7 @@ int ctr_tc_mlp_bwd_data(ctr_handle* h, cudaStream_t st, int B, int K, int N, con
                         const float* W, const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx);
 int64_t ctr_tc_bwd_weight_ws_bytes(ctr_handle* h, int B, int K, int N);
 int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* X, int64_t ldx,
-                          const float* dZ, int64_t lddz, float* dW, void* ws, int64_t ws_bytes);
+                          const float* dZ, int64_t lddz, float* dW, float* dbias, void* ws, int64_t ws_bytes);
 
 extern "C" int ctr_mlp_fwd(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N, const float* X, int64_t ldx,
                            const float* W, const float* Wt, const float* bias, int relu, float keep, uint64_t seed,
@@ -211,7 +211,7 @@ extern "C" int64_t ctr_mlp_bwd_weight_ws_bytes(ctr_handle* h, int precision, int
 
 extern "C" int ctr_mlp_bwd_weight(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N, const float* X,
                                   int64_t ldx, const float* dZ, int64_t lddz, float* dW, float* dbias, void* ws,
-                                  int64_t ws_bytes) {
+                                  int64_t ws_bytes, int x_ones_col) {
     CTR_REQUIRE(h, X && dZ && dW && ws && B > 0 && K > 0 && N > 0 && ldx >= K && lddz >= N, "mlp_bwd_weight: bad args");
     if (ws_bytes < ctr_mlp_bwd_weight_ws_bytes(h, precision, B, K, N))
         return ctr_fail(h, CTR_E_WORKSPACE, "mlp_bwd_weight: ws too small");
@@ -221,8 +221,11 @@ extern "C" int ctr_mlp_bwd_weight(ctr_handle* h, ctr_stream s, int precision, in
     int rc;
     if (precision == CTR_PREC_TF32) {
         gemm_ws = ctr_tc_bwd_weight_ws_bytes(h, B, K, N);
-        rc = ctr_tc_mlp_bwd_weight(h, st, B, K, N, X, ldx, dZ, lddz, dW, p, gemm_ws);
+        // X[:, K] == 1 (caller's promise): the bias gradient is the extra row of the same tensor-core GEMM
+        const bool fused_bias = dbias && x_ones_col && ldx > K;
+        rc = ctr_tc_mlp_bwd_weight(h, st, B, K, N, X, ldx, dZ, lddz, dW, fused_bias ? dbias : nullptr, p, gemm_ws);
         if (rc) return rc;
+        if (fused_bias) return CTR_OK;
     } else {
         CTR_REQUIRE(h, precision == CTR_PREC_FP32, "mlp_bwd_weight: bad precision");
         const int splits = wgrad_splits(h, B, K, N);

@@ -506,11 +506,20 @@ NtPlan plan_nt(ctr_handle* h, int M, int N, int R) {
     return p;
 }
 
-__global__ void __launch_bounds__(256) tc_splitk_reduce(const float* __restrict__ ws, int splits, int64_t n, float* __restrict__ out) {
+// out[i] = sum over the splits; elements past n_main (the extra row produced by a ones column of X) go to `tail`
+__global__ void __launch_bounds__(256) tc_splitk_reduce(const float* __restrict__ ws, int splits, int64_t n, int64_t n_main,
+                                                        float* __restrict__ out, float* __restrict__ tail) {
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
-        float a = 0.f;
-        for (int z = 0; z < splits; ++z) a += ws[(int64_t) z * n + i];
-        out[i] = a;
+        float a0 = 0.f, a1 = 0.f;
+        int z = 0;
+        for (; z + 2 <= splits; z += 2) {
+            a0 += ws[(int64_t) z * n + i];
+            a1 += ws[(int64_t) (z + 1) * n + i];
+        }
+        if (z < splits) a0 += ws[(int64_t) z * n + i];
+        const float a = a0 + a1;
+        if (i < n_main) out[i] = a;
+        else tail[i - n_main] = a;
     }
 }
 
@@ -531,13 +540,17 @@ int ctr_tc_mlp_bwd_data(ctr_handle* h, cudaStream_t st, int B, int K, int N, con
 }
 
 int64_t ctr_tc_bwd_weight_ws_bytes(ctr_handle* h, int B, int K, int N) {
-    NtPlan p = plan_nt(h, K, N, B);
-    return ctr_align((int64_t) p.splits * K * N * 4, 256);
+    NtPlan p = plan_nt(h, K + 1, N, B);       // + 1: room for the dbias row of the ones-column form
+    return ctr_align((int64_t) p.splits * (K + 1) * N * 4, 256);
 }
 
-int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* X, int64_t ldx,
-                          const float* dZ, int64_t lddz, float* dW, void* ws, int64_t ws_bytes) {
+// dbias != nullptr: X carries a column of ones at index K_w (ldx > K_w), so the GEMM is run with K_w + 1 rows and
+// its last row, 1^T dZ, is the bias gradient: no separate pass over dZ.
+int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K_w, int N, const float* X, int64_t ldx,
+                          const float* dZ, int64_t lddz, float* dW, float* dbias, void* ws, int64_t ws_bytes) {
     CTR_REQUIRE(h, N <= MAX_N, "TF32 path: N=%d > %d not supported", N, MAX_N);
+    const int K = K_w + (dbias ? 1 : 0);
+    CTR_REQUIRE(h, ldx >= K, "TF32 wgrad: ones-column form needs ldx > K");
     NtPlan p = plan_nt(h, K, N, B);
     CTR_REQUIRE(h, p.nstages >= 2, "TF32 wgrad: tile does not fit shared memory");
     if (ws_bytes < (int64_t) p.splits * K * N * 4) return ctr_fail(h, CTR_E_WORKSPACE, "TF32 wgrad: ws too small");
@@ -558,7 +571,7 @@ int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K, int N, c
                                                     tmem_cols_for(p.n1 + p.n2), (float*) ws);
     CTR_CHECK_LAUNCH(h, "gemm_nt_kernel");
     const int64_t n = (int64_t) K * N;
-    tc_splitk_reduce<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>((const float*) ws, p.splits, n, dW);
+    tc_splitk_reduce<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>((const float*) ws, p.splits, n, (int64_t) K_w * N, dW, dbias);
     CTR_CHECK_LAUNCH(h, "tc_splitk_reduce");
     return CTR_OK;
 }

@@ -81,7 +81,12 @@ class CtrEngine:
         self.vec = torch.zeros(B, max(s.V, 1), **f32)
         self.label = torch.zeros(B, **f32)
         self.x0 = torch.zeros(B, s.x0_ld, **f32)
-        self.acts = [torch.zeros(B, h_, **f32) for h_ in s.hidden]
+        # hidden activations carry 4 pad columns; column H holds 1.0 for good, so the weight-gradient GEMM of the next
+        # layer yields the bias gradient as an extra row (no GEMM ever reads or writes past column H-1 otherwise)
+        self.act_ld = [h_ + 4 for h_ in s.hidden]
+        self.acts = [torch.zeros(B, ld, **f32) for ld in self.act_ld]
+        for a, h_ in zip(self.acts, s.hidden):
+            a[:, h_] = 1.0
         self.fm = torch.zeros(B, s.fm_ld, **f32)
         self.sum_e = torch.zeros(B, s.k, **f32)
         self.logit, self.score, self.dlogit = (torch.zeros(B, **f32) for _ in range(3))
@@ -95,7 +100,8 @@ class CtrEngine:
         self.wide = torch.zeros(B, max(s.wide_fields, 1), dtype=self.id_torch, device=dev) if s.head == "wdl" else None
         self.wide_sum = torch.zeros(B, **f32) if s.head == "wdl" else None
 
-        ws_bytes = max(self.h.query("ctr_colsum_ws_bytes", B, max(s.hidden + [s.fm_ld])), 4 * (B // 8 + 8), 1 << 16)
+        ws_bytes = max(self.h.query("ctr_colsum_ws_bytes", B, max(s.hidden + [s.fm_ld])), 4 * (B // 8 + 8), 1 << 16,
+                       self.h.query("ctr_head_ws_bytes", B, s.n_fm, s.hidden[-1]))
         if train:
             self.m_table, self.v_table = torch.zeros_like(self.table), torch.zeros_like(self.table)
             self.m, self.v = (torch.zeros(cur, **f32) for _ in range(2))
@@ -347,8 +353,8 @@ class CtrEngine:
         x, ldx = self.x0, s.x0_ld
         for i, (k_, h_) in enumerate(self._layer_dims()):
             h.call("ctr_mlp_fwd", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self._w(i)),
-                   ptr(self.wt[i]) if self.wt is not None else None, ptr(self._b(i)), 1, 1.0, 0, ptr(self.acts[i]), h_)
-            x, ldx = self.acts[i], h_
+                   ptr(self.wt[i]) if self.wt is not None else None, ptr(self._b(i)), 1, 1.0, 0, ptr(self.acts[i]), self.act_ld[i])
+            x, ldx = self.acts[i], self.act_ld[i]
         w_fm, w_deep, bias = self._head_parts()
         extra = None
         if s.head == "wdl":
@@ -356,11 +362,19 @@ class CtrEngine:
                    s.wide_fields, ptr(self.wide_sum))
             extra = self.wide_sum
         lab = self.label if with_loss else None
+        g_fm = g_deep = g_bias = None
+        if with_loss and self.train_mode:
+            # head-weight gradients d w = sum_b dlogit[b] * feats_input[b, :] (models/deepfm.py:130,143) come out of the
+            # same kernel; for wdl the deep block aliases rows W..W+H-1 of wdl_weights (quirk Q4), zeroed first so the
+            # wide scatter can add on top
+            if s.head == "wdl":
+                self.view("wdl_weights", self.grad).zero_()
+            g_fm, g_deep, g_bias = self._head_parts(self.grad)
         h.call("ctr_head_fwd", st, B, self.global_batch(B), ptr(self.fm), s.fm_ld, s.n_fm, ptr(w_fm), ptr(x), ldx, s.hidden[-1], ptr(w_deep),
                ptr(extra), ptr(bias), ptr(lab), ptr(self.logit), ptr(self.score),
                ptr(self.dlogit) if with_loss else None,
                ptr(self.dz[0]) if (with_loss and self.train_mode) else None, s.hidden[-1], int(self.prec == 1),
-               ptr(self.loss) if with_loss else None, ptr(self.ws), self.ws.numel())
+               ptr(self.loss) if with_loss else None, ptr(g_fm), ptr(g_deep), ptr(g_bias), ptr(self.ws), self.ws.numel())
 
     def global_batch(self, B: int) -> int:
         """samples the loss is a mean over (all ranks' batches when sharded)"""
@@ -393,26 +407,18 @@ class CtrEngine:
         L = len(s.hidden)
         dims = self._layer_dims()
         H = s.hidden[-1]
-        g_fm, g_deep, g_bias = self._head_parts(self.grad)
         w_fm, w_deep, _ = self._head_parts()
-        last = self.acts[-1]
         ws, wsn = ptr(self.ws), self.ws.numel()
-        if s.head == "wdl":
-            self.view("wdl_weights", self.grad).zero_()
-        # head gradients: d w = sum_b dlogit[b] * feats_input[b, :]  (models/deepfm.py:130,143)
-        if s.n_fm:
-            h.call("ctr_colsum", st, ptr(self.fm), s.fm_ld, B, s.n_fm, ptr(self.dlogit), ptr(g_fm), ws, wsn)
-        h.call("ctr_colsum", st, ptr(last), H, B, H, ptr(self.dlogit), ptr(g_deep), ws, wsn)
-        h.call("ctr_reduce", st, ptr(self.dlogit), B, 0, ptr(g_bias), ws, wsn)
+        # head-weight gradients were written by ctr_head_fwd
         if s.head == "wdl":
             self._wdl_wide_grad(B)
         # dz[0] already holds the gradient through the last ReLU (written by ctr_head_fwd)
         cur = 0
         for i in range(L - 1, -1, -1):
             k_, h_ = dims[i]
-            x, ldx = (self.acts[i - 1], s.hidden[i - 1]) if i > 0 else (self.x0, s.x0_ld)
+            x, ldx = (self.acts[i - 1], self.act_ld[i - 1]) if i > 0 else (self.x0, s.x0_ld)
             h.call("ctr_mlp_bwd_weight", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self.dz[cur]), h_,
-                   ptr(self._w(i, self.grad)), ptr(self._b(i, self.grad)), ws, wsn)
+                   ptr(self._w(i, self.grad)), ptr(self._b(i, self.grad)), ws, wsn, 1)
             if i > 0:
                 h.call("ctr_mlp_bwd_data", st, self.prec, B, k_, h_, ptr(self.dz[cur]), h_, ptr(self._wd(i)), ptr(x),
                        ldx, 1.0, ptr(self.dz[cur ^ 1]), k_)

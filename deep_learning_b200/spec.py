@@ -64,7 +64,7 @@ class ModelSpec:
 
     @property
     def x0_ld(self) -> int:
-        return _round_up(self.D0, 4)
+        return _round_up(self.D0 + 1, 4)       # >= one pad column: it holds the 1.0 of the fused bias gradient
 
     @property
     def n_fm(self) -> int:

@@ -139,11 +139,13 @@ int ctr_mlp_fwd(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
 int ctr_mlp_bwd_data(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
                      const float* dZ, int64_t lddz, const float* W,
                      const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx);
-/* dW[K,N] = X^T @ dZ ; dbias[N] = colsum(dZ).  ws: ctr_mlp_bwd_weight_ws_bytes() */
+/* dW[K,N] = X^T @ dZ ; dbias[N] = colsum(dZ).  ws: ctr_mlp_bwd_weight_ws_bytes().
+ * x_ones_col != 0: the caller keeps X[:, K] == 1.0 (ldx > K); the TF32 path then gets dbias as row K of the same
+ * GEMM instead of a separate pass over dZ (ignored by the FP32 path). */
 int64_t ctr_mlp_bwd_weight_ws_bytes(ctr_handle* h, int precision, int B, int K, int N);
 int ctr_mlp_bwd_weight(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
                        const float* X, int64_t ldx, const float* dZ, int64_t lddz,
-                       float* dW, float* dbias, void* ws, int64_t ws_bytes);
+                       float* dW, float* dbias, void* ws, int64_t ws_bytes, int x_ones_col);
 /* out[N, ld_out] = in[K,N]^T, ld_out >= K: the K-major copy the tcgen05 path reads (TMA needs 16-byte
  * row pitches, so ld_out = K rounded up to 4; pad columns are left untouched) */
 int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, float* out, int64_t ld_out,
@@ -160,7 +162,10 @@ int ctr_round_tf32_copy(ctr_handle* h, ctr_stream s, const float* in, float* out
  *   dlogit[b]= dloss/dlogit[b]                                              (label != NULL)
  *   dz_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)   (optional: the gradient through the last ReLU,
  *                                                            written while the row is cache-hot)
- * loss_out: one float, written by a second deterministic reduction pass. ws >= 4*(ceil(B/256)+1) B */
+ *   g_fm[j] = sum_b dlogit[b]*fm[b,j], g_deep[j] = sum_b dlogit[b]*deep[b,j], g_bias = sum_b dlogit[b]   (optional, with
+ *             label: the head-weight gradients, accumulated while the rows are in registers; H <= 512, n_fm <= 128)
+ * loss_out: one float, written by a second deterministic reduction pass. ws: ctr_head_ws_bytes() */
+int64_t ctr_head_ws_bytes(ctr_handle* h, int B, int n_fm, int H);
 int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B,
                  int64_t B_global /* samples the loss is a mean over: B on one GPU, the sum of all ranks' batches when
                  the batch is sharded (loss and dlogit are then this rank's SHARE, so a sum-allreduce gives the global
@@ -169,7 +174,8 @@ int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B,
                  const float* deep, int64_t deep_ld, int H, const float* w_deep,
                  const float* extra, const float* bias,
                  const float* label, float* logit, float* score, float* dlogit, float* dz_last, int64_t lddz,
-                 int round_tf32 /* round dz_last to tf32 */, float* loss_out, void* ws, int64_t ws_bytes);
+                 int round_tf32 /* round dz_last to tf32 */, float* loss_out,
+                 float* g_fm /*[n_fm]*/, float* g_deep /*[H]*/, float* g_bias /*[1]*/, void* ws, int64_t ws_bytes);
 /* dZ_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)        (through the last ReLU) */
 int ctr_head_bwd_deep(ctr_handle* h, ctr_stream s, int B, int H, const float* dlogit, const float* w_deep,
                       const float* deep, int64_t deep_ld, float* dZ, int64_t lddz);

@@ -49,12 +49,12 @@ def study(hp, tag):
         flips = 0
         flipped_samples = np.zeros(hp.batch_size, dtype=bool)
         for i, mk in enumerate(masks):
-            dm = (eng.acts[i].cpu().numpy() > 0)
+            dm = (eng.acts[i][:, :hp.hidden_units[i]].cpu().numpy() > 0)
             diff = dm != mk
             flips += int(diff.sum())
             flipped_samples |= diff.any(axis=1)
         print("[%s/%s] relu flips: %d units, %d of %d samples" % (tag, prec, flips, int(flipped_samples.sum()), hp.batch_size))
-        dev_masks = [torch.from_numpy(eng.acts[i].cpu().numpy() > 0) for i in range(len(masks))]
+        dev_masks = [torch.from_numpy(eng.acts[i][:, :hp.hidden_units[i]].cpu().numpy() > 0) for i in range(len(masks))]
         st3 = copy.deepcopy(st)
         with O.relu_branches(dev_masks):
             O.train_step("deepfm", dict(p), st3, ob, hp, adam_mode="lazy")

@@ -119,7 +119,7 @@ def test_mlp_fp32_gemms(hd, B, K, N):
     assert H.rel_err(dX.cpu(), ref) < 1e-5
     wsn = hd.query("ctr_mlp_bwd_weight_ws_bytes", 0, B, K, N); ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
     dW = torch.zeros(K, N, device="cuda"); db = torch.zeros(N, device="cuda")
-    hd.call("ctr_mlp_bwd_weight", _st(), 0, B, K, N, ptr(Xc), K, ptr(dZc), N, ptr(dW), ptr(db), ptr(ws), wsn)
+    hd.call("ctr_mlp_bwd_weight", _st(), 0, B, K, N, ptr(Xc), K, ptr(dZc), N, ptr(dW), ptr(db), ptr(ws), wsn, 0)
     assert H.rel_err(dW.cpu(), X.double().T @ dZ.double()) < 1e-5
     assert H.rel_err(db.cpu(), dZ.double().sum(0)) < 1e-5
 
@@ -167,7 +167,7 @@ def test_mlp_tf32_tcgen05_gemms(hd, B, K, N):
     assert H.rel_err(dX.cpu()[:, :K], ref) < 2e-3, "dgrad"
     wsn = hd.query("ctr_mlp_bwd_weight_ws_bytes", 1, B, K, N); ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
     dW = torch.zeros(K, N, device="cuda"); db = torch.zeros(N, device="cuda")
-    hd.call("ctr_mlp_bwd_weight", _st(), 1, B, K, N, ptr(Xc), ldx, ptr(dZc), N, ptr(dW), ptr(db), ptr(ws), wsn)
+    hd.call("ctr_mlp_bwd_weight", _st(), 1, B, K, N, ptr(Xc), ldx, ptr(dZc), N, ptr(dW), ptr(db), ptr(ws), wsn, 0)
     torch.cuda.synchronize()
     assert H.rel_err(dW.cpu(), X.double().T @ dZ.double()) < 2e-3, "wgrad"
     assert H.rel_err(db.cpu(), dZ.double().sum(0)) < 1e-5

@@ -59,7 +59,7 @@ def _run_parity(alg, hp, steps, precision="fp32", adam_mode="tf_dense", B=None, 
             # the function is continuous there, its derivative jumps -- tests/diag_tf32.py counts these flips)
             loss_true = float(O.LOSS[alg](p, ob, hp)[0])
             assert abs(loss - loss_true) < tol * max(1.0, abs(loss_true)), "loss step %d" % step
-            masks = [a[:B].cpu() > 0 for a in eng.acts]
+            masks = [a[:B, :h_].cpu() > 0 for a, h_ in zip(eng.acts, eng.spec.hidden)]
             with O.relu_branches(masks):
                 loss_ref, p = O.train_step(alg, p, st, ob, hp, adam_mode=adam_mode)
         else:
