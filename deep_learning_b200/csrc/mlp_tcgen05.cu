@@ -12,6 +12,7 @@
 // lane), warp 9 = MMA issuer (one elected lane).  Operands are staged by TMA into 128B-swizzled shared memory through a 3-stage
 // mbarrier ring; accumulators live in TMEM and are read back with tcgen05.ld for the fused epilogue.
 #include <cuda.h>
+#include <stdlib.h>
 #include "ctr_common.cuh"
 
 namespace {
@@ -20,8 +21,9 @@ constexpr int BLOCK_M = 128;
 constexpr int BLOCK_R = 32;            // reduction elements per stage: 32 fp32 = one 128B swizzle row
 constexpr int UMMA_K = 8;              // tf32: 32 bytes of reduction per instruction
 constexpr int MAX_N = 512;             // fp32 accumulator columns in TMEM
-constexpr int NUM_THREADS = 320;           // warps 0-7 epilogue, 8 TMA producer, 9 MMA issuer
-constexpr int TMA_WARP = 8, MMA_WARP = 9;
+// warp roles: warps [0, EW) epilogue (EW = 8 or 16), warp EW = TMA producer, warp EW + 1 = MMA issuer
+constexpr int nthreads(int ew) { return (ew + 2) * 32; }
+constexpr int SBIAS_BYTES = 2048;          // bias of the CTA's columns staged in shared memory (N <= 512)
 constexpr int SMEM_LIMIT = 227 * 1024;
 
 // ------------------------------------------------------------------------------------ PTX wrappers
@@ -86,6 +88,50 @@ __device__ __forceinline__ bool elect_one() {
     return pred != 0;
 }
 
+// ---- CTA-pair (cta_group::2) variants: two CTAs of a cluster on the two SMs of a TPC run ONE M=256 MMA; each CTA
+// stages its own 128 rows of A and HALF of the B tile, so the shared-memory fill per SM per k-block drops from
+// (128 + N) to (128 + N/2) rows.  Only the leader (cluster rank 0) issues MMAs; both CTAs issue TMA, all transaction
+// bytes are counted on the leader's full barrier; commits are multicast to the same barrier offset in both CTAs.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `local_addr` (a shared::cta address) in the CTA of rank `rank`
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t local_addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint32_t leader_bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(map), "r"(leader_bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t* dst_smem, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrive (once all MMAs issued so far have completed) on the barrier at this offset in BOTH CTAs of the pair
+__device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t) 3) : "memory");
+}
+
 // ------------------------------------------------------------------------------------ descriptors
 // shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start>>4 [0,14), LBO>>4 [16,30),
 // SBO>>4 [32,46), version=1 [46,48), layout type [61,64)
@@ -110,7 +156,20 @@ struct EpiParams {
     int64_t ldmask;
     float mask_scale;
     int round_out;          // round outputs to tf32 (they feed the next tensor-core GEMM)
+    int col0;               // first global output column of this CTA's slab (dropout hash index)
+    int n_total;            // row pitch of the dropout hash index (the full N)
+    int dbg;                // timing experiments only (CTR_GEMM_DBG): 1 skip global stores, 2 skip MMAs, 4 skip TMA loads
+    unsigned long long* trace;   // CTR_GEMM_DBG & 8: per-CTA phase timestamps (8 slots per CTA)
 };
+
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// block 0 only: fine-grained slots after the per-CTA area (producer: 0.., MMA issuer: 64.., epilogue warp 0: 128..)
+#define TRACE_FINE(slot) do { if (ep.trace && blockIdx.x == 0 && (slot) < 512) ep.trace[4096 * 8 + (slot)] = gtimer(); } while (0)
+#define TRACE(slot) do { if (ep.trace && blockIdx.x < 4096) ep.trace[blockIdx.x * 8 + (slot)] = gtimer(); } while (0)
 
 __device__ __forceinline__ float dropout_u01(uint64_t seed, uint64_t idx) {   // same hash as the FP32 path
     uint64_t z = seed + idx * 0x9E3779B97F4A7C15ull;
@@ -121,8 +180,8 @@ __device__ __forceinline__ float dropout_u01(uint64_t seed, uint64_t idx) {   //
 }
 
 struct alignas(8) PipeBars {
-    uint64_t full[4];
-    uint64_t empty[4];
+    uint64_t full[6];
+    uint64_t empty[6];
     uint64_t tmem_full;
     uint32_t tmem_base;
     uint32_t pad;
@@ -158,11 +217,26 @@ __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.
 constexpr int EPI_PITCH = 36;
 constexpr int EPI_TILE_FLOATS = 32 * EPI_PITCH;
 
-template <bool BIAS, bool RELU, bool MASK>
+// explicit shared-space accesses: through a generic pointer the compiler emits LD/ST (generic), cannot tell the tile
+// from the global output, and serialises every tile read behind the previous global store
+__device__ __forceinline__ void sts_f4(uint32_t addr, float a, float b, float c, float d) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+
+// round-to-nearest (ties away) fp32 -> tf32 for finite values: what cvt.rna.tf32.f32 returns, in two integer ops
+// (ptxas expands the cvt into a longer sequence with inf/nan handling)
+__device__ __forceinline__ float round_tf32_fast(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u); }
+
+template <bool BIAS, bool RELU, bool MASK, int EW>
 __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
-                                              int64_t ldc, const EpiParams& ep, float* stage) {
-    const int q = ewarp & 3, half = ewarp >> 2;
-    float* tile = stage + ewarp * EPI_TILE_FLOATS;
+                                              int64_t ldc, const EpiParams& ep, float* stage, uint32_t sbias) {
+    const int q = ewarp & 3, half = ewarp >> 2;     // TMEM lane quarter; chunk phase (stride EW / 4)
+    const uint32_t tile = smem_u32(stage) + (uint32_t) (ewarp * EPI_TILE_FLOATS * 4);
     const bool vec_ok = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
     const bool mvec_ok = MASK && (ep.ldmask % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.mask) & 15) == 0);
     const bool dropout = ep.keep < 1.f;
@@ -171,21 +245,15 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
     const int rsub = lane >> 3;            // row inside a group of 4 rows
     const int cc = (lane & 7) * 4;         // first of this lane's 4 columns inside the chunk
     const int rbase = m0 + q * 32;
-    for (int c = half; c < nchunks; c += 2) {
+    for (int c = half; c < nchunks; c += EW / 4) {
         const int c0 = c * 32;
         uint32_t r[32];
         tmem_ld32_issue(lane_addr + (uint32_t) c0, r);   // .sync.aligned: every lane takes part, valid row or not
         const int col = c0 + cc;
         const bool col4 = col + 4 <= N;
         float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (BIAS) {
-            if (col4 && ((reinterpret_cast<uintptr_t>(ep.bias) & 15) == 0)) bs = __ldg(reinterpret_cast<const float4*>(ep.bias + col));
-            else {
-                bs.x = col + 0 < N ? __ldg(ep.bias + col + 0) : 0.f;
-                bs.y = col + 1 < N ? __ldg(ep.bias + col + 1) : 0.f;
-                bs.z = col + 2 < N ? __ldg(ep.bias + col + 2) : 0.f;
-                bs.w = col + 3 < N ? __ldg(ep.bias + col + 3) : 0.f;
-            }
+        if (BIAS) {     // staged in shared memory by the epilogue warps while the mainloop ran (zero-padded to 512)
+            bs = lds_f4(sbias + (uint32_t) (col * 4));
         }
         float4 mk[8];
         if (MASK) {
@@ -203,17 +271,20 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
             }
         }
         tmem_ld_wait();
+        if (ewarp == 0 && lane == 0) TRACE_FINE(128 + 4 * c);
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-            *reinterpret_cast<float4*>(tile + lane * EPI_PITCH + 4 * i) =
-                make_float4(__uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]), __uint_as_float(r[4 * i + 2]),
-                            __uint_as_float(r[4 * i + 3]));
+            sts_f4(tile + (uint32_t) ((lane * EPI_PITCH + 4 * i) * 4), __uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]),
+                   __uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
         __syncwarp();
+        float4 tv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) tv[j] = lds_f4(tile + (uint32_t) (((rsub + 4 * j) * EPI_PITCH + cc) * 4));
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             const int rr = rsub + 4 * j;
             const int row = rbase + rr;
-            float4 v = *reinterpret_cast<const float4*>(tile + rr * EPI_PITCH + cc);
+            float4 v = tv[j];
             if (BIAS) { v.x += bs.x; v.y += bs.y; v.z += bs.z; v.w += bs.w; }
             if (RELU) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
             if (MASK) {
@@ -222,15 +293,15 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
                 v.z = mk[j].z > 0.f ? v.z * ep.mask_scale : 0.f;
                 v.w = mk[j].w > 0.f ? v.w * ep.mask_scale : 0.f;
             }
-            if (ep.round_out) { v.x = ctr_round_tf32(v.x); v.y = ctr_round_tf32(v.y); v.z = ctr_round_tf32(v.z); v.w = ctr_round_tf32(v.w); }
+            if (ep.round_out) { v.x = round_tf32_fast(v.x); v.y = round_tf32_fast(v.y); v.z = round_tf32_fast(v.z); v.w = round_tf32_fast(v.w); }
             if (dropout) {
-                const uint64_t e0 = (uint64_t) row * (uint64_t) N + (uint64_t) col;
+                const uint64_t e0 = (uint64_t) row * (uint64_t) (ep.n_total > 0 ? ep.n_total : N) + (uint64_t) (ep.col0 + col);
                 v.x = dropout_u01(ep.seed, e0 + 0) < ep.keep ? v.x / ep.keep : 0.f;
                 v.y = dropout_u01(ep.seed, e0 + 1) < ep.keep ? v.y / ep.keep : 0.f;
                 v.z = dropout_u01(ep.seed, e0 + 2) < ep.keep ? v.z / ep.keep : 0.f;
                 v.w = dropout_u01(ep.seed, e0 + 3) < ep.keep ? v.w / ep.keep : 0.f;
             }
-            if (row < M) {
+            if (row < M && !(ep.dbg & 1)) {
                 float* dst = C + (int64_t) row * ldc + col;
                 if (vec_ok && col4) *reinterpret_cast<float4*>(dst) = v;
                 else {
@@ -241,21 +312,38 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
                 }
             }
         }
+        if (ewarp == 0 && lane == 0) TRACE_FINE(128 + 4 * c + 1);
         __syncwarp();      // the tile is rewritten by the next chunk
     }
 }
 
-__device__ __forceinline__ void epilogue_dispatch(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
-                                                  int64_t ldc, const EpiParams& ep, float* stage) {
-    if (ep.mask) epilogue_rows<false, false, true>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage);
-    else if (ep.bias && ep.relu) epilogue_rows<true, true, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage);
-    else if (ep.bias) epilogue_rows<true, false, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage);
-    else if (ep.relu) epilogue_rows<false, true, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage);
-    else epilogue_rows<false, false, false>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage);
+// shared memory: [ pipeline stages, reused as epilogue staging | PipeBars | staged bias ]
+__host__ __device__ constexpr size_t pipe_region(size_t stage_total, int ew) {
+    return stage_total > (size_t) ew * EPI_TILE_FLOATS * 4 ? stage_total : (size_t) ew * EPI_TILE_FLOATS * 4;
+}
+constexpr size_t smem_total(size_t stage_total, int ew) { return pipe_region(stage_total, ew) + sizeof(PipeBars) + SBIAS_BYTES + 1024; }
+
+// what the epilogue warps do BEFORE the accumulator is ready (they are idle during the mainloop): stage the bias of
+// this CTA's columns in shared memory (an L2 prefetch of the dgrad's mask tile was tried here: it slowed the kernel down)
+template <int EW>
+__device__ __forceinline__ void epilogue_prepare(int m0, int M, int N, const EpiParams& ep, float* sbias) {
+    const int tid = threadIdx.x;                   // epilogue warps are warps [0, EW)
+    for (int i = tid; i < SBIAS_BYTES / 4; i += EW * 32) sbias[i] = (ep.bias && i < N) ? __ldg(ep.bias + i) : 0.f;
+    asm volatile("bar.sync 1, %0;" ::"r"(EW * 32) : "memory");      // epilogue warps only
 }
 
-__device__ __forceinline__ PipeBars* setup_cta(uint8_t* smem, int nstages, int stage_bytes, uint32_t tmem_cols, int warp) {
-    PipeBars* bars = reinterpret_cast<PipeBars*>(smem + (size_t) nstages * stage_bytes);
+template <int EW>
+__device__ __forceinline__ void epilogue_dispatch(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
+                                                  int64_t ldc, const EpiParams& ep, float* stage, uint32_t sbias) {
+    if (ep.mask) epilogue_rows<false, false, true, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+    else if (ep.bias && ep.relu) epilogue_rows<true, true, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+    else if (ep.bias) epilogue_rows<true, false, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+    else if (ep.relu) epilogue_rows<false, true, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+    else epilogue_rows<false, false, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+}
+
+__device__ __forceinline__ PipeBars* setup_cta(uint8_t* smem, size_t pipe_bytes, int nstages, uint32_t tmem_cols, int warp, int tma_warp) {
+    PipeBars* bars = reinterpret_cast<PipeBars*>(smem + pipe_bytes);
     if (threadIdx.x == 0) {
         for (int s = 0; s < nstages; ++s) {
             mbar_init(&bars->full[s], 1);
@@ -264,7 +352,7 @@ __device__ __forceinline__ PipeBars* setup_cta(uint8_t* smem, int nstages, int s
         mbar_init(&bars->tmem_full, 1);
         fence_barrier_init();
     }
-    if (warp == TMA_WARP) tmem_alloc(&bars->tmem_base, tmem_cols);
+    if (warp == tma_warp) tmem_alloc(&bars->tmem_base, tmem_cols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -272,19 +360,35 @@ __device__ __forceinline__ PipeBars* setup_cta(uint8_t* smem, int nstages, int s
 }
 
 // ---- C[M,N] = A[M,R] * B[N,R]^T ; A, B reduction-major, 128B-swizzled K-major tiles -------------------
-__global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int R,
-               int n_each, int nmma, int nstages, uint32_t tmem_cols, float* __restrict__ C, int64_t ldc, EpiParams ep) {
+// MINB = 2: two CTAs share an SM (each <= 256 TMEM columns, <= ~113 KB shared memory), so one CTA's epilogue and
+// pipeline fill run under the other's MMAs; blockIdx.y selects the CTA's slab of n_each * nmma output columns.
+template <int MINB, int EW>
+__global__ void __launch_bounds__(nthreads(EW), MINB)
+gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N_total, int R,
+               int n_each, int nmma, int nslab, int nstages, uint32_t tmem_cols, float* __restrict__ C, int64_t ldc,
+               EpiParams ep) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int NB = n_each * nmma;
+    // slab index fastest: the CTAs that share a 128-row A panel launch back to back, so the second read hits L2
+    const int n0 = ((int) blockIdx.x % nslab) * NB;                   // first output column of this CTA
+    const int N = (N_total - n0) < NB ? (N_total - n0) : NB;          // columns this CTA writes
+    C += n0;
+    if (ep.bias) ep.bias += n0;
+    if (ep.mask) ep.mask += n0;
+    ep.col0 = n0;
     const int a_bytes = BLOCK_M * BLOCK_R * 4;
     const int stage_bytes = a_bytes + NB * BLOCK_R * 4;
-    const int m0 = blockIdx.x * BLOCK_M;
+    const int m0 = ((int) blockIdx.x / nslab) * BLOCK_M;
     const int num_kb = (R + BLOCK_R - 1) / BLOCK_R;
-    PipeBars* bars = setup_cta(smem, nstages, stage_bytes, tmem_cols, warp);
+    if (threadIdx.x == 0) TRACE(0);
+    constexpr int TMA_WARP = EW, MMA_WARP = EW + 1;
+    const size_t pipe_bytes = pipe_region((size_t) nstages * stage_bytes, EW);
+    PipeBars* bars = setup_cta(smem, pipe_bytes, nstages, tmem_cols, warp, TMA_WARP);
+    float* sbias = reinterpret_cast<float*>(smem + pipe_bytes + sizeof(PipeBars));
     const uint32_t tmem_base = bars->tmem_base;
+    if (threadIdx.x == 0) TRACE(1);
 
     if (warp == TMA_WARP) {
         if (elect_one()) {
@@ -294,11 +398,13 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const int s = kb % nstages;
                 const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
                 mbar_wait(&bars->empty[s], ph ^ 1u);
+                TRACE_FINE(kb);
                 uint8_t* sa = smem + (size_t) s * stage_bytes;
+                if (ep.dbg & 4) { mbar_expect_tx(&bars->full[s], 0u); continue; }
                 mbar_expect_tx(&bars->full[s], (uint32_t) stage_bytes);
                 tma_load_2d(sa, &tmA, &bars->full[s], kb * BLOCK_R, m0);
                 for (int i = 0; i < nmma; ++i)
-                    tma_load_2d(sa + a_bytes + (size_t) i * n_each * BLOCK_R * 4, &tmB, &bars->full[s], kb * BLOCK_R, i * n_each);
+                    tma_load_2d(sa + a_bytes + (size_t) i * n_each * BLOCK_R * 4, &tmB, &bars->full[s], kb * BLOCK_R, n0 + i * n_each);
             }
         }
     } else if (warp == MMA_WARP) {
@@ -309,6 +415,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
                 mbar_wait(&bars->full[s], ph);
                 tc_fence_after();
+                TRACE_FINE(64 + kb);
                 const uint32_t a_base = smem_u32(smem + (size_t) s * stage_bytes);
                 const uint32_t b_base = a_base + a_bytes;
 #pragma unroll
@@ -316,25 +423,126 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     const uint64_t adesc = make_desc(a_base + k * UMMA_K * 4, 16, 8 * BLOCK_R * 4, LAYOUT_SW128);
                     for (int i = 0; i < nmma; ++i) {
                         const uint64_t bdesc = make_desc(b_base + i * n_each * BLOCK_R * 4 + k * UMMA_K * 4, 16, 8 * BLOCK_R * 4, LAYOUT_SW128);
-                        umma_tf32(tmem_base + (uint32_t) (i * n_each), adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                        if (!(ep.dbg & 2)) umma_tf32(tmem_base + (uint32_t) (i * n_each), adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
                 }
                 umma_commit(&bars->empty[s]);     // frees the smem stage once these MMAs have read it
             }
             umma_commit(&bars->tmem_full);        // accumulator complete
+            TRACE(2);
         }
     } else {
+        epilogue_prepare<EW>(m0, M, N, ep, sbias);
         mbar_wait(&bars->tmem_full, 0);
         tc_fence_after();
-        epilogue_dispatch(tmem_base, warp, lane, m0, M, N, C, ldc, ep, reinterpret_cast<float*>(smem));
+        if (threadIdx.x == 0) TRACE(3);
+        epilogue_dispatch<EW>(tmem_base, warp, lane, m0, M, N, C, ldc, ep, reinterpret_cast<float*>(smem), smem_u32(sbias));
+        if (threadIdx.x == 0) TRACE(4);
     }
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) TRACE(5);
     if (warp == TMA_WARP) tmem_dealloc(tmem_base, tmem_cols);
+    if (threadIdx.x == TMA_WARP * 32) TRACE(6);
+}
+
+// ---- C[M,N] = A[M,R] * B[N,R]^T on CTA pairs (see the cta_group::2 notes above).  CTA rank r of pair p owns output
+// rows [(2p + r) * 128, +128) and stages rows [i*n_each + r*n_each/2, +n_each/2) of B for MMA i.
+template <int EW>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(nthreads(EW), 1)
+gemm_tn_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int R,
+                    int n_each, int nmma, int nstages, uint32_t tmem_cols, float* __restrict__ C, int64_t ldc, EpiParams ep) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int n_half = n_each / 2;
+    const int a_bytes = BLOCK_M * BLOCK_R * 4;
+    const int b_bytes = n_half * BLOCK_R * 4;                 // one MMA's B half
+    const int stage_bytes = a_bytes + nmma * b_bytes;
+    const int m0 = blockIdx.x * BLOCK_M;
+    const int num_kb = (R + BLOCK_R - 1) / BLOCK_R;
+    constexpr int TMA_WARP = EW, MMA_WARP = EW + 1;
+    const size_t pipe_bytes = pipe_region((size_t) nstages * stage_bytes, EW);
+    PipeBars* bars = reinterpret_cast<PipeBars*>(smem + pipe_bytes);
+    float* sbias = reinterpret_cast<float*>(smem + pipe_bytes + sizeof(PipeBars));
+    if (threadIdx.x == 0) TRACE(0);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < nstages; ++s) {
+            mbar_init(&bars->full[s], 1);
+            mbar_init(&bars->empty[s], 1);
+        }
+        mbar_init(&bars->tmem_full, 1);
+        fence_barrier_init();
+    }
+    cluster_sync_all();                                      // both CTAs' barriers exist before anyone signals them
+    if (warp == TMA_WARP) tmem_alloc_pair(&bars->tmem_base, tmem_cols);
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+    if (threadIdx.x == 0) TRACE(1);
+
+    if (warp == TMA_WARP) {
+        if (elect_one()) {
+            prefetch_tmap(&tmA);
+            prefetch_tmap(&tmB);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % nstages;
+                const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
+                mbar_wait(&bars->empty[s], ph ^ 1u);           // my copy of the stage is free (multicast commit)
+                TRACE_FINE(kb);
+                uint8_t* sa = smem + (size_t) s * stage_bytes;
+                if (rank == 0) mbar_expect_tx(&bars->full[s], (uint32_t) (2 * stage_bytes));   // both CTAs' bytes
+                const uint32_t lbar = mapa_shared(smem_u32(&bars->full[s]), 0);
+                tma_load_2d_pair(sa, &tmA, lbar, kb * BLOCK_R, m0);
+                for (int i = 0; i < nmma; ++i)
+                    tma_load_2d_pair(sa + a_bytes + (size_t) i * b_bytes, &tmB, lbar, kb * BLOCK_R,
+                                     i * n_each + (int) rank * n_half);
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        if (rank == 0 && elect_one()) {
+            const uint32_t idesc = make_idesc(2 * BLOCK_M, n_each, 0, 0);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % nstages;
+                const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
+                mbar_wait(&bars->full[s], ph);
+                tc_fence_after();
+                TRACE_FINE(64 + kb);
+                const uint32_t a_base = smem_u32(smem + (size_t) s * stage_bytes);
+                const uint32_t b_base = a_base + a_bytes;
+#pragma unroll
+                for (int k = 0; k < BLOCK_R / UMMA_K; ++k) {
+                    const uint64_t adesc = make_desc(a_base + k * UMMA_K * 4, 16, 8 * BLOCK_R * 4, LAYOUT_SW128);
+                    for (int i = 0; i < nmma; ++i) {
+                        const uint64_t bdesc = make_desc(b_base + i * b_bytes + k * UMMA_K * 4, 16, 8 * BLOCK_R * 4, LAYOUT_SW128);
+                        umma_tf32_pair(tmem_base + (uint32_t) (i * n_each), adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                }
+                umma_commit_pair(&bars->empty[s]);     // frees the stage in BOTH CTAs
+            }
+            umma_commit_pair(&bars->tmem_full);        // accumulators complete in both CTAs
+            TRACE(2);
+        }
+    } else {
+        epilogue_prepare<EW>(m0, M, N, ep, sbias);
+        mbar_wait(&bars->tmem_full, 0);
+        tc_fence_after();
+        if (threadIdx.x == 0) TRACE(3);
+        epilogue_dispatch<EW>(tmem_base, warp, lane, m0, M, N, C, ldc, ep, reinterpret_cast<float*>(smem), smem_u32(sbias));
+        if (threadIdx.x == 0) TRACE(4);
+    }
+    tc_fence_before();
+    cluster_sync_all();                                   // neither CTA frees TMEM / exits while its peer still runs
+    if (threadIdx.x == 0) TRACE(5);
+    if (warp == TMA_WARP) tmem_dealloc_pair(tmem_base, tmem_cols);
+    if (threadIdx.x == TMA_WARP * 32) TRACE(6);
 }
 
 // ---- C_split[M,N] = A[R,M]^T * B[R,N] over this CTA's slice of R ; MN-major tf32 tiles (32B-atom swizzle)
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+constexpr int NT_EW = 8;
+__global__ void __launch_bounds__(nthreads(NT_EW), 1)
 gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int R,
                int r_per_split, int n1, int n2, int nstages, uint32_t tmem_cols, float* __restrict__ Cws) {
     extern __shared__ uint8_t smem_raw[];
@@ -348,7 +556,9 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int r_lo = blockIdx.y * r_per_split;
     const int r_hi = (r_lo + r_per_split < R) ? r_lo + r_per_split : R;
     const int num_kb = r_hi > r_lo ? (r_hi - r_lo + BLOCK_R - 1) / BLOCK_R : 0;
-    PipeBars* bars = setup_cta(smem, nstages, stage_bytes, tmem_cols, warp);
+    constexpr int EW = NT_EW, TMA_WARP = EW, MMA_WARP = EW + 1;
+    const size_t pipe_bytes = pipe_region((size_t) nstages * stage_bytes, EW);
+    PipeBars* bars = setup_cta(smem, pipe_bytes, nstages, tmem_cols, warp, TMA_WARP);
     const uint32_t tmem_base = bars->tmem_base;
 
     if (warp == TMA_WARP) {
@@ -398,11 +608,11 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (num_kb > 0) {
             mbar_wait(&bars->tmem_full, 0);
             tc_fence_after();
-            EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f, 0};
-            epilogue_rows<false, false, false>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem));
+            EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f, 0, 0, 0, 0, nullptr};
+            epilogue_rows<false, false, false, EW>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem), 0u);
         } else {                                   // empty slice: contribute zeros
             const int row = m0 + (warp & 3) * 32 + lane;
-            if (row < M) for (int c = (warp >> 2); c < N; c += 2) Cz[(size_t) row * N + c] = 0.f;
+            if (row < M) for (int c = (warp >> 2); c < N; c += EW / 4) Cz[(size_t) row * N + c] = 0.f;
         }
     }
     tc_fence_before();
@@ -456,9 +666,41 @@ uint32_t tmem_cols_for(int nb) {
     return c;
 }
 
-int pick_stages(int stage_bytes) {
-    int s = (SMEM_LIMIT - 2048) / stage_bytes;
-    return s > 4 ? 4 : s;
+int pick_stages(int stage_bytes, int cap = 4) {
+    int s = (SMEM_LIMIT - 2048 - SBIAS_BYTES) / stage_bytes;
+    return s > cap ? cap : s;
+}
+
+unsigned long long* g_trace_buf = nullptr;
+unsigned long long* gemm_trace_buf();
+int gemm_dbg() {
+    static int d = -1;
+    if (d < 0) {
+        const char* e = getenv("CTR_GEMM_DBG");
+        d = e ? atoi(e) : 0;
+    }
+    return d;
+}
+
+unsigned long long* gemm_trace_buf() {
+    if (!(gemm_dbg() & 8)) return nullptr;
+    if (!g_trace_buf) {
+        cudaMalloc(&g_trace_buf, (4096 * 8 + 512) * sizeof(unsigned long long));
+        cudaMemset(g_trace_buf, 0, (4096 * 8 + 512) * sizeof(unsigned long long));
+    }
+    return g_trace_buf;
+}
+
+// CTR_GEMM_MODE = split2 (default: two co-resident CTAs per SM, half-N slabs) | pair (cta_group::2) | single
+int gemm_mode() {
+    static int mode = -1;
+    if (mode < 0) {
+        const char* e = getenv("CTR_GEMM_MODE");
+        mode = 0;
+        if (e && e[0] == 'p') mode = 1;
+        if (e && e[0] == 's' && e[1] == 'i') mode = 2;
+    }
+    return mode;
 }
 
 int launch_tn(ctr_handle* h, cudaStream_t st, int M, int N, int R, const float* A, int64_t lda, const float* B,
@@ -467,22 +709,60 @@ int launch_tn(ctr_handle* h, cudaStream_t st, int M, int N, int R, const float* 
     const int nmma = N > 256 ? 2 : 1;
     const int NB = nmma == 1 ? (int) ctr_align(N, 16) : (int) ctr_align(N, 32);
     const int n_each = NB / nmma;
-    const int stage_bytes = BLOCK_M * BLOCK_R * 4 + NB * BLOCK_R * 4;
-    const int nstages = pick_stages(stage_bytes);
-    CTR_REQUIRE(h, nstages >= 2, "TF32 path: tile does not fit shared memory");
+    if (gemm_mode() == 1 && M > BLOCK_M) {
+        // CTA pairs: each CTA stages 128 rows of A and half of B per k-block
+        const int n_half = n_each / 2;
+        const int stage_bytes = BLOCK_M * BLOCK_R * 4 + nmma * n_half * BLOCK_R * 4;
+        const int nstages = pick_stages(stage_bytes, 6);
+        CTR_REQUIRE(h, nstages >= 2, "TF32 path: tile does not fit shared memory");
+        CUtensorMap tmA, tmB;
+        int rc = make_map(h, &tmA, A, M, R, lda, BLOCK_R, BLOCK_M, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc) return rc;
+        rc = make_map(h, &tmB, B, N, R, ldb, BLOCK_R, n_half, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc) return rc;
+        const size_t smem = smem_total((size_t) nstages * stage_bytes, 8);
+        static bool attr_set2 = false;
+        if (!attr_set2) {
+            CTR_CUDA(h, cudaFuncSetAttribute(gemm_tn_pair_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+            attr_set2 = true;
+        }
+        const unsigned ctas = (unsigned) ctr_align(ctr_cdiv(M, BLOCK_M), 2);
+        gemm_tn_pair_kernel<8><<<ctas, nthreads(8), smem, st>>>(tmA, tmB, M, N, R, n_each, nmma, nstages, tmem_cols_for(NB), C,
+                                                             ldc, ep);
+        CTR_CHECK_LAUNCH(h, "gemm_tn_pair_kernel");
+        return CTR_OK;
+    }
     CUtensorMap tmA, tmB;
     int rc = make_map(h, &tmA, A, M, R, lda, BLOCK_R, BLOCK_M, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
     rc = make_map(h, &tmB, B, N, R, ldb, BLOCK_R, n_each, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
-    const size_t smem = (size_t) nstages * stage_bytes + sizeof(PipeBars) + 1024;
     static bool attr_set = false;
     if (!attr_set) {
-        CTR_CUDA(h, cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+        CTR_CUDA(h, cudaFuncSetAttribute(gemm_tn_kernel<1, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+        CTR_CUDA(h, cudaFuncSetAttribute(gemm_tn_kernel<2, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT / 2));
         attr_set = true;
     }
-    gemm_tn_kernel<<<(unsigned) ctr_cdiv(M, BLOCK_M), NUM_THREADS, smem, st>>>(tmA, tmB, M, N, R, n_each, nmma, nstages,
-                                                                              tmem_cols_for(NB), C, ldc, ep);
+    // split2: each CTA takes ONE MMA slab of n_each (<= 256) columns; two such CTAs fit an SM (256 TMEM columns and
+    // 2-3 pipeline stages each), which overlaps epilogue / fill / MMA of different tiles without a persistent scheduler
+    const int slab_stage = BLOCK_M * BLOCK_R * 4 + n_each * BLOCK_R * 4;
+    const int slab_budget = SMEM_LIMIT / 2 - 2048 - 1024 - SBIAS_BYTES;
+    if (gemm_mode() == 0 && slab_budget / slab_stage >= 2) {
+        int nstages = slab_budget / slab_stage;
+        if (nstages > 4) nstages = 4;
+        const size_t smem = smem_total((size_t) nstages * slab_stage, 8);
+        const unsigned grid = (unsigned) (ctr_cdiv(M, BLOCK_M) * nmma);
+        gemm_tn_kernel<2, 8><<<grid, nthreads(8), smem, st>>>(tmA, tmB, M, N, R, n_each, 1, nmma, nstages, tmem_cols_for(n_each), C,
+                                                           ldc, ep);
+        CTR_CHECK_LAUNCH(h, "gemm_tn_kernel<2>");
+        return CTR_OK;
+    }
+    const int stage_bytes = BLOCK_M * BLOCK_R * 4 + NB * BLOCK_R * 4;
+    const int nstages = pick_stages(stage_bytes);
+    CTR_REQUIRE(h, nstages >= 2, "TF32 path: tile does not fit shared memory");
+    const size_t smem = smem_total((size_t) nstages * stage_bytes, 8);
+    gemm_tn_kernel<1, 8><<<(unsigned) ctr_cdiv(M, BLOCK_M), nthreads(8), smem, st>>>(tmA, tmB, M, N, R, n_each, nmma, 1, nstages,
+                                                                                 tmem_cols_for(NB), C, ldc, ep);
     CTR_CHECK_LAUNCH(h, "gemm_tn_kernel");
     return CTR_OK;
 }
@@ -528,14 +808,14 @@ __global__ void __launch_bounds__(256) tc_splitk_reduce(const float* __restrict_
 int ctr_tc_mlp_fwd(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* X, int64_t ldx, const float* Wt,
                    const float* bias, int relu, float keep, uint64_t seed, float* Y, int64_t ldy) {
     // Wt is the K-major copy [N, ldwt] with ldwt = K rounded up to 4 floats (TMA needs 16-byte row pitches)
-    EpiParams ep{bias, relu, keep, seed, nullptr, 0, 1.f, 1};
+    EpiParams ep{bias, relu, keep, seed, nullptr, 0, 1.f, 1, 0, N, gemm_dbg(), gemm_trace_buf()};
     return launch_tn(h, st, B, N, K, X, ldx, Wt, ctr_align(K, 4), Y, ldy, ep);
 }
 
 int ctr_tc_mlp_bwd_data(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* dZ, int64_t lddz,
                         const float* W, const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx) {
     // dX[B,K] = dZ[B,N] * W[K,N]^T : W is already reduction-major for this product
-    EpiParams ep{nullptr, 0, 1.f, 0, mask, ldmask, mask_scale, 1};
+    EpiParams ep{nullptr, 0, 1.f, 0, mask, ldmask, mask_scale, 1, 0, K, gemm_dbg(), gemm_trace_buf()};
     return launch_tn(h, st, B, K, N, dZ, lddz, W, N, dX, lddx, ep);
 }
 
@@ -560,18 +840,25 @@ int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K_w, int N,
     rc = make_map(h, &tmB, dZ, B, N, lddz, 32, BLOCK_R, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
     if (rc) return rc;
     const int stage_bytes = (BLOCK_M / 32 + (p.n1 + p.n2) / 32) * 32 * BLOCK_R * 4;
-    const size_t smem = (size_t) p.nstages * stage_bytes + sizeof(PipeBars) + 1024;
+    const size_t smem = smem_total((size_t) p.nstages * stage_bytes, NT_EW);
     static bool attr_set = false;
     if (!attr_set) {
         CTR_CUDA(h, cudaFuncSetAttribute(gemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
         attr_set = true;
     }
     dim3 grid((unsigned) p.mtiles, (unsigned) p.splits);
-    gemm_nt_kernel<<<grid, NUM_THREADS, smem, st>>>(tmA, tmB, K, N, B, p.r_per_split, p.n1, p.n2, p.nstages,
+    gemm_nt_kernel<<<grid, nthreads(NT_EW), smem, st>>>(tmA, tmB, K, N, B, p.r_per_split, p.n1, p.n2, p.nstages,
                                                     tmem_cols_for(p.n1 + p.n2), (float*) ws);
     CTR_CHECK_LAUNCH(h, "gemm_nt_kernel");
     const int64_t n = (int64_t) K * N;
     tc_splitk_reduce<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>((const float*) ws, p.splits, n, (int64_t) K_w * N, dW, dbias);
     CTR_CHECK_LAUNCH(h, "tc_splitk_reduce");
     return CTR_OK;
+}
+
+// timing experiments only: copies the per-CTA phase timestamps of the last traced GEMM (CTR_GEMM_DBG & 8) to the host
+extern "C" int ctr_debug_gemm_trace(unsigned long long* host, int n_ctas) {
+    if (!g_trace_buf || !host || n_ctas <= 0 || n_ctas > 4096 + 64) return CTR_E_INVALID;
+    return cudaMemcpy(host, g_trace_buf, (size_t) n_ctas * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess
+               ? CTR_OK : CTR_E_CUDA;
 }

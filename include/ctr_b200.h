@@ -298,6 +298,12 @@ int ctr_gather_rows(ctr_handle* h, ctr_stream s, const float* src, int src_strid
 /* inv[perm[i]] = uidx[i] : lookup position -> index of its row in the unique list */
 int ctr_invert_perm(ctr_handle* h, ctr_stream s, const uint32_t* perm, const uint32_t* uidx, int64_t n, uint32_t* inv);
 
+/* ---- timing experiments (not part of the product path) -----------------------------------------------------
+ * with CTR_GEMM_DBG & 8 in the environment the TF32 forward/dgrad GEMM records %globaltimer at its phase boundaries
+ * (8 slots per CTA: start, setup done, last MMA committed, accumulator ready, epilogue done, CTA synced, TMEM freed);
+ * this copies the last launch's records to the host. */
+int ctr_debug_gemm_trace(unsigned long long* host, int n_ctas);
+
 #ifdef __cplusplus
 }
 #endif
