@@ -81,7 +81,7 @@ _PROTOS = {
     "ctr_auc_ws_bytes": (c_i64, [c_vp, c_i64]),
     "ctr_auc": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i64]),
     "ctr_gather_rows": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_i32]),
-    "ctr_debug_gemm_trace": (c_i32, None),
+    "ctr_debug_gemm_trace": (c_i32, [c_vp, c_i32]),
     "ctr_invert_perm": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
 }
 

@@ -76,10 +76,19 @@ class CtrEngine:
         self.wr = [torch.zeros(k_, h_, **f32) for (k_, h_) in self._layer_dims()] if (self.prec == 1 and train) else None
 
         # ---- batch + activations ----------------------------------------------------------------
-        self.ids = torch.zeros(B, max(s.ids_ld, 1), dtype=self.id_torch, device=dev)
-        self.cont = torch.zeros(B, max(s.C, 1), **f32)
-        self.vec = torch.zeros(B, max(s.V, 1), **f32)
-        self.label = torch.zeros(B, **f32)
+        # two sets of input buffers: the batch of step i+1 is uploaded (copy stream) while step i computes
+        self._in = []
+        for _ in range(2):
+            self._in.append(dict(ids=torch.zeros(B, max(s.ids_ld, 1), dtype=self.id_torch, device=dev),
+                                 cont=torch.zeros(B, max(s.C, 1), **f32), vec=torch.zeros(B, max(s.V, 1), **f32),
+                                 label=torch.zeros(B, **f32),
+                                 wide=torch.zeros(B, max(s.wide_fields, 1), dtype=self.id_torch, device=dev) if s.head == "wdl" else None))
+        self._in_free = [torch.cuda.Event(), torch.cuda.Event()]
+        self._in_used = [False, False]
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self._pf_event, self._pf_id, self._pf_B = torch.cuda.Event(), None, 0
+        self._ids_external = False          # sharded engine: ids live in its id plans
+        self._use_inputs(0)
         self.x0 = torch.zeros(B, s.x0_ld, **f32)
         # hidden activations carry 4 pad columns; column H holds 1.0 for good, so the weight-gradient GEMM of the next
         # layer yields the bias gradient as an extra row (no GEMM ever reads or writes past column H-1 otherwise)
@@ -97,7 +106,6 @@ class CtrEngine:
         self.inv_cnt_first = torch.zeros(B, max(s.Fm, 1), **f32)
         self.multi_start = torch.from_numpy(s.multi_start()).to(dev)
         self.field_of_slot = torch.from_numpy(s.field_of_slot()).to(dev)
-        self.wide = torch.zeros(B, max(s.wide_fields, 1), dtype=self.id_torch, device=dev) if s.head == "wdl" else None
         self.wide_sum = torch.zeros(B, **f32) if s.head == "wdl" else None
 
         ws_bytes = max(self.h.query("ctr_colsum_ws_bytes", B, max(s.hidden + [s.fm_ld])), 4 * (B // 8 + 8), 1 << 16,
@@ -294,9 +302,27 @@ class CtrEngine:
                 self.h.call("ctr_round_tf32_copy", st, ptr(self._w(i)), ptr(self.wr[i]), k_ * h_)
 
     # ---- batch upload ------------------------------------------------------------------------------
+    def _use_inputs(self, i: int) -> None:
+        self._cur_in = i
+        t = self._in[i]
+        self.ids, self.cont, self.vec, self.label, self.wide = t["ids"], t["cont"], t["vec"], t["label"], t["wide"]
+
     def load_batch(self, batch: Dict, non_blocking: bool = True, skip_ids: bool = False) -> int:
-        """Copy one batch (host or device arrays/tensors, reference key names) into the device
-        buffers.  Returns B (may be < max_batch for the short last batch, models/deepfm.py:178)."""
+        """Make `batch` (host or device arrays/tensors, reference key names) the current device batch.  Returns B
+        (may be < max_batch for the short last batch, models/deepfm.py:178).  A batch announced as `next_batch`
+        of the previous train_step is already on the device: the buffer sets just flip."""
+        if self._pf_id is not None and self._pf_id == id(batch):
+            torch.cuda.current_stream(self.dev).wait_event(self._pf_event)
+            self._use_inputs(1 - self._cur_in)
+            self._pf_id = None
+            self.last_batch = self._pf_B
+            return self._pf_B
+        self._pf_id = None
+        B = self._copy_inputs(batch, self._in[self._cur_in], non_blocking, skip_ids)
+        self.last_batch = B
+        return B
+
+    def _copy_inputs(self, batch: Dict, tgt: Dict, non_blocking: bool, skip_ids: bool) -> int:
         s = self.spec
 
         def as_t(x, dtype):
@@ -311,7 +337,7 @@ class CtrEngine:
             if cate.shape[1] != s.ids_ld:
                 raise ValueError("cate_feats has %d columns, model expects %d" % (cate.shape[1], s.ids_ld))
             if not skip_ids:
-                self.ids[:B].copy_(cate, non_blocking=non_blocking)
+                tgt["ids"][:B].copy_(cate, non_blocking=non_blocking)
         cont = as_t(batch["cont_feats"], torch.float32)
         if s.alg == "dnn" and "vector_feats" in batch and batch["vector_feats"] is not None:
             vec = as_t(batch["vector_feats"], torch.float32)
@@ -320,15 +346,14 @@ class CtrEngine:
         if s.C:
             if cont.shape[1] != s.C:
                 raise ValueError("cont_feats has %d columns, model expects %d" % (cont.shape[1], s.C))
-            self.cont[:B].copy_(cont, non_blocking=non_blocking)
+            tgt["cont"][:B].copy_(cont, non_blocking=non_blocking)
         if s.V:
-            self.vec[:B].copy_(as_t(batch["vector_feats"], torch.float32), non_blocking=non_blocking)
+            tgt["vec"][:B].copy_(as_t(batch["vector_feats"], torch.float32), non_blocking=non_blocking)
         if s.head == "wdl":
-            self.wide[:B].copy_(as_t(batch["wide_feats"], self.id_torch), non_blocking=non_blocking)
+            tgt["wide"][:B].copy_(as_t(batch["wide_feats"], self.id_torch), non_blocking=non_blocking)
         lab = batch.get("label", batch.get("labels"))
         if lab is not None:
-            self.label[:B].copy_(as_t(lab, torch.float32).reshape(-1), non_blocking=non_blocking)
-        self.last_batch = B
+            tgt["label"][:B].copy_(as_t(lab, torch.float32).reshape(-1), non_blocking=non_blocking)
         return B
 
     # ---- forward -------------------------------------------------------------------------------------
@@ -528,10 +553,24 @@ class CtrEngine:
         return loss if reg is None else loss + reg
 
     def _after_forward(self, next_batch: Optional[Dict]) -> None:
-        """hook: work for the next step that can overlap this step's backward (sharded engine)"""
+        """work for the next step that overlaps this step's backward: upload the next batch into the other input set"""
+        if next_batch is None:
+            return
+        other = 1 - self._cur_in
+        cs = self.copy_stream
+        if self._in_used[other]:
+            cs.wait_event(self._in_free[other])        # the step that last read that set has finished
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.dev))
+        cs.wait_event(ev)                              # a device-resident batch may still be in production upstream
+        with torch.cuda.stream(cs):
+            self._pf_B = self._copy_inputs(next_batch, self._in[other], True, self._ids_external)
+        self._pf_event.record(cs)
+        self._pf_id = id(next_batch)
 
     def _end_step(self) -> None:
-        """hook: end-of-step bookkeeping"""
+        self._in_free[self._cur_in].record(torch.cuda.current_stream(self.dev))
+        self._in_used[self._cur_in] = True
 
     def _global_loss(self) -> torch.Tensor:
         """log-loss of the global batch (sharded engines read it back from the gradient allreduce)"""

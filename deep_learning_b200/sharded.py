@@ -78,6 +78,7 @@ class ShardedCtrEngine(CtrEngine):
         self.n_max = B * s.ids_ld + self.n_extra
         if not self.train_mode:
             self.side = torch.cuda.Stream(device=dev)
+        self._ids_external = True
         self.plans = [_IdPlan(self), _IdPlan(self)]
         self.cur: Optional[_IdPlan] = None
         self.rows_recv = torch.zeros(self.n_max + 1, self.wire, **f32)
@@ -180,7 +181,7 @@ class ShardedCtrEngine(CtrEngine):
         main = torch.cuda.current_stream(self.dev)
         pl = next((c for c in self.plans if c.in_flight and c.batch_id == id(batch)), None)
         if pl is not None:                         # prefetched during the previous step
-            B = super().load_batch(batch, non_blocking, skip_ids=True)
+            B = super().load_batch(batch, non_blocking, skip_ids=True)     # (flips the input sets if it was uploaded too)
             if self._pending_exchange is pl:       # (only if the previous step never reached its sparse update)
                 self._build_exchange(pl, self.side)
                 self._pending_exchange = None
@@ -193,8 +194,12 @@ class ShardedCtrEngine(CtrEngine):
                     self._pending_exchange = None
                 main.wait_event(pl.ev_ready)
                 pl.in_flight = False
-            self.ids = pl.ids
-            B = super().load_batch(batch, non_blocking)
+            B = super().load_batch(batch, non_blocking, skip_ids=True)
+            cate = batch["cate_feats"]
+            if not isinstance(cate, torch.Tensor):
+                cate = torch.as_tensor(np.asarray(cate))
+            if self.spec.ids_ld:
+                pl.ids[:B].copy_(cate.to(self.id_torch) if cate.dtype != self.id_torch else cate, non_blocking=non_blocking)
             self._build_local(pl, B, main)
             self._build_exchange(pl, main)
             pl.on_side = False
@@ -205,6 +210,7 @@ class ShardedCtrEngine(CtrEngine):
 
     def _after_forward(self, next_batch: Optional[Dict]) -> None:
         """start the id plan of the next batch on the side stream (upload ids, sort, de-dup, counts all-to-all)"""
+        super()._after_forward(next_batch)         # non-id inputs: upload into the other input set
         if next_batch is None or not self.spec.ids_ld:
             return
         pl = self._other_plan()
@@ -226,6 +232,7 @@ class ShardedCtrEngine(CtrEngine):
         self._pending_exchange = pl
 
     def _end_step(self) -> None:
+        super()._end_step()
         if self.cur is not None:
             self.cur.ev_free.record(torch.cuda.current_stream(self.dev))
             if self.cur.batch_id is None:
