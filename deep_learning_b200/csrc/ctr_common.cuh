@@ -81,6 +81,12 @@ __device__ __forceinline__ float ctr_round_tf32(float x) {
     return __uint_as_float(r);
 }
 
+// the same rounding for finite values in two integer ops (ptxas expands the cvt into ~4 with inf/nan handling);
+// inf stays inf, canonical NaNs stay NaN
+__device__ __forceinline__ float ctr_round_tf32_fast(float x) {
+    return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
+
 __device__ __forceinline__ float ctr_warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

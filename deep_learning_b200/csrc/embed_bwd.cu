@@ -10,6 +10,12 @@ namespace {
 constexpr int CH = CTR_BWD_CHUNK;
 constexpr int LONG_RUN = 8;   // runs with more partials than this take the warp-cooperative path
 
+// Layout of one gradient row (grad_stride floats): [0,K) embedding coordinates, [K] first-order weight, [K+1] D.
+// For a single-valued lookup of row r by sample b the FM part of the gradient is dl_b * w2 * (s_b - e_r)
+// (models/deepfm.py:88-92 differentiated).  e_r is the same for every lookup of the run, so the walker only adds
+// dl_b * w2 * s_b and D += dl_b; the update kernel, which reads e_r anyway, subtracts w2 * e_r * D.  That removes the
+// random re-read of the X0 tile (one of three 64-byte random reads per lookup).  Multi-valued slots enter the FM
+// through their pooled vector, not the row, so they keep the direct form and add nothing to D.
 template <int K>
 __global__ void __launch_bounds__(256)
 embed_bwd_partials_kernel(const ctr_embed_cfg cfg, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ perm,
@@ -19,85 +25,102 @@ embed_bwd_partials_kernel(const ctr_embed_cfg cfg, const uint32_t* __restrict__ 
                           const float* __restrict__ w_fm, const float* __restrict__ inv_cnt_emb,
                           const float* __restrict__ inv_cnt_first, const float* __restrict__ cont_grad,
                           float* __restrict__ part) {
-    constexpr int G = K;       // lanes per chunk walker: lane j owns embedding coordinate j
+    constexpr int G = K / 4;   // lanes per chunk walker: lane q owns coordinates 4q..4q+3
     constexpr int UN = 4;      // lookups in flight per walker
     const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t c = t / G;   // chunk index
-    const int j = (int) (t % G);
+    const int q = (int) (t % G);
     const int64_t base = c * CH;
     if (base >= n) return;
     const int cnt = (int) ((n - base) < CH ? (n - base) : CH);
-    const int Fc = cfg.Fc, Fm = cfg.Fm, ids_ld = cfg.ids_ld, gs = cfg.grad_stride;
+    const int Fc = cfg.Fc, Fm = cfg.Fm, gs = cfg.grad_stride;
+    const uint32_t ids_ld = (uint32_t) cfg.ids_ld;
     const bool use_fm = cfg.use_fm != 0, has_first = cfg.has_first != 0;
     const float* __restrict__ w1 = w_fm;                         // first-order head weights, per field
-    const float w2j = use_fm ? w_fm[Fc + Fm + cfg.C + j] : 0.f;  // second-order head weight of coordinate j
-    const uint32_t n_lookup = (uint32_t) cfg.B * (uint32_t) ids_ld;
+    float4 w2 = make_float4(0.f, 0.f, 0.f, 0.f);                 // second-order head weights of this lane's coordinates
+    if (use_fm) {
+        const float* w2p = w_fm + Fc + Fm + cfg.C + q * 4;
+        w2 = make_float4(w2p[0], w2p[1], w2p[2], w2p[3]);
+    }
+    const uint32_t n_lookup = (uint32_t) cfg.B * ids_ld;
 
     uint32_t cur = CTR_PAD_KEY;
     int64_t cur_slot = 0;
-    float acc = 0.f, accw = 0.f;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    float accw = 0.f, accd = 0.f;
+
+    auto flush = [&]() {
+        float* o = part + cur_slot * gs;
+        *reinterpret_cast<float4*>(o + q * 4) = acc;
+        if (q == 0 && (has_first || use_fm)) *reinterpret_cast<float2*>(o + K) = make_float2(accw, accd);
+    };
 
     for (int i0 = 0; i0 < cnt; i0 += UN) {
         uint32_t key[UN], u[UN];
-        float gv[UN], gw[UN];
+        float4 gv[UN];
+        float gw[UN], gd[UN];
 #pragma unroll
-        for (int q = 0; q < UN; ++q) {
-            const int i = i0 + q;
-            key[q] = CTR_PAD_KEY; u[q] = 0; gv[q] = 0.f; gw[q] = 0.f;
+        for (int k = 0; k < UN; ++k) {
+            const int i = i0 + k;
+            key[k] = CTR_PAD_KEY; u[k] = 0; gv[k] = make_float4(0.f, 0.f, 0.f, 0.f); gw[k] = 0.f; gd[k] = 0.f;
             if (i < cnt) {
-                key[q] = keys[base + i];
-                if (key[q] != CTR_PAD_KEY) {
-                    u[q] = uidx[base + i];
-                    const uint32_t p = perm[base + i];
+                key[k] = __ldg(keys + base + i);
+                if (key[k] != CTR_PAD_KEY) {
+                    u[k] = __ldg(uidx + base + i);
+                    const uint32_t p = __ldg(perm + base + i);
                     if (p >= n_lookup) {   // appended continuous-field row: gradient was reduced densely
                         const int cc = (int) (p - n_lookup);
-                        gv[q] = cont_grad[cc * gs + j];
-                        gw[q] = has_first ? cont_grad[cc * gs + K] : 0.f;
+                        gv[k] = *reinterpret_cast<const float4*>(cont_grad + cc * gs + q * 4);
+                        gw[k] = has_first ? cont_grad[cc * gs + K] : 0.f;
                         continue;
                     }
-                    const uint32_t b = p / (uint32_t) ids_ld;
-                    const int slot = (int) (p - b * (uint32_t) ids_ld);
-                    int fld = slot;
-                    float sc_e = 1.f, sc_w = 1.f;
-                    if (slot >= Fc) {
+                    const uint32_t b = p / ids_ld;
+                    const int slot = (int) (p - b * ids_ld);
+                    if (slot < Fc) {
+                        float4 g = __ldg(reinterpret_cast<const float4*>(dx0 + (int64_t) b * dx0_ld + slot * K + q * 4));
+                        if (use_fm) {
+                            const float dl = __ldg(dlogit + b);
+                            const float4 sv = __ldg(reinterpret_cast<const float4*>(sum_e + (int64_t) b * K + q * 4));
+                            g.x = fmaf(dl * w2.x, sv.x, g.x); g.y = fmaf(dl * w2.y, sv.y, g.y);
+                            g.z = fmaf(dl * w2.z, sv.z, g.z); g.w = fmaf(dl * w2.w, sv.w, g.w);
+                            gw[k] = dl * __ldg(w1 + slot);
+                            gd[k] = dl;
+                        }
+                        gv[k] = g;
+                    } else {
                         const int jm = field_of_slot[slot - Fc];
-                        fld = Fc + jm;
-                        sc_e = inv_cnt_emb[(int64_t) b * Fm + jm];
-                        sc_w = inv_cnt_first[(int64_t) b * Fm + jm];
+                        const int fld = Fc + jm;
+                        const float sc_e = inv_cnt_emb[(int64_t) b * Fm + jm], sc_w = inv_cnt_first[(int64_t) b * Fm + jm];
+                        float4 g = __ldg(reinterpret_cast<const float4*>(dx0 + (int64_t) b * dx0_ld + fld * K + q * 4));
+                        if (use_fm) {
+                            const float dl = __ldg(dlogit + b);
+                            const float4 sv = __ldg(reinterpret_cast<const float4*>(sum_e + (int64_t) b * K + q * 4));
+                            const float4 xv = __ldg(reinterpret_cast<const float4*>(x0 + (int64_t) b * cfg.x0_ld + fld * K + q * 4));
+                            g.x = fmaf(dl * w2.x, sv.x - xv.x, g.x); g.y = fmaf(dl * w2.y, sv.y - xv.y, g.y);
+                            g.z = fmaf(dl * w2.z, sv.z - xv.z, g.z); g.w = fmaf(dl * w2.w, sv.w - xv.w, g.w);
+                            gw[k] = sc_w * dl * __ldg(w1 + fld);
+                        }
+                        gv[k] = make_float4(sc_e * g.x, sc_e * g.y, sc_e * g.z, sc_e * g.w);
                     }
-                    const float dl = dlogit[b];
-                    float g = dx0[(int64_t) b * dx0_ld + fld * K + j];
-                    if (use_fm) {
-                        const float s = sum_e[(int64_t) b * K + j];
-                        const float xv = x0[(int64_t) b * cfg.x0_ld + fld * K + j];
-                        g = fmaf(dl * w2j, s - xv, g);
-                        gw[q] = sc_w * dl * w1[fld];
-                    }
-                    gv[q] = sc_e * g;
                 }
             }
         }
 #pragma unroll
-        for (int q = 0; q < UN; ++q) {
-            if (i0 + q < cnt) {
-                if (key[q] != cur) {
-                    if (cur != CTR_PAD_KEY) {
-                        part[cur_slot * gs + j] = acc;
-                        if (has_first && j == 0) part[cur_slot * gs + K] = accw;
-                    }
-                    cur = key[q];
-                    cur_slot = (int64_t) u[q] + c;
-                    acc = 0.f; accw = 0.f;
+        for (int k = 0; k < UN; ++k) {
+            if (i0 + k < cnt) {
+                if (key[k] != cur) {
+                    if (cur != CTR_PAD_KEY) flush();
+                    cur = key[k];
+                    cur_slot = (int64_t) u[k] + c;
+                    acc = make_float4(0.f, 0.f, 0.f, 0.f); accw = 0.f; accd = 0.f;
                 }
-                acc += gv[q];
-                accw += gw[q];
+                acc.x += gv[k].x; acc.y += gv[k].y; acc.z += gv[k].z; acc.w += gv[k].w;
+                accw += gw[k];
+                accd += gd[k];
             }
         }
     }
-    if (cur != CTR_PAD_KEY) {
-        part[cur_slot * gs + j] = acc;
-        if (has_first && j == 0) part[cur_slot * gs + K] = accw;
-    }
+    if (cur != CTR_PAD_KEY) flush();
 }
 
 // sum of the partials of run u, coordinate j, in chunk order
@@ -133,11 +156,13 @@ embed_bwd_finalize_kernel(const uint32_t* __restrict__ seg_start, const uint32_t
     }
 }
 
+// generic width (any table): one thread per (row, coordinate)
 __global__ void __launch_bounds__(256)
 adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restrict__ n_rows, int64_t n_max, uint32_t mask,
                  const float* __restrict__ grads, const uint32_t* __restrict__ seg_start, int gs, int width,
                  float* __restrict__ table, float* __restrict__ m, float* __restrict__ v, int stride, int64_t table_rows,
-                 uint8_t* __restrict__ touched, uint32_t* __restrict__ long_list, const ctr_adam_hp hp) {
+                 uint8_t* __restrict__ touched, uint32_t* __restrict__ long_list, const float* __restrict__ fm_w2, int emb_k,
+                 const ctr_adam_hp hp) {
     int64_t U = n_rows ? (int64_t) *n_rows : n_max;
     if (U > n_max) U = n_max;
     const int64_t total = U * width;
@@ -158,12 +183,93 @@ adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restric
         }
         float g = seg_start ? sum_run_partials(grads, seg_start, u, j, gs) : grads[u * gs + j];
         const int64_t o = row * stride + j;
+        if (fm_w2 && j < emb_k) {          // the e-term of the FM gradient (see embed_bwd_partials_kernel)
+            const float D = seg_start ? sum_run_partials(grads, seg_start, u, emb_k + 1, gs) : grads[u * gs + emb_k + 1];
+            g = fmaf(-fm_w2[j] * table[o], D, g);
+        }
         const float mm = hp.beta1 * m[o] + (1.f - hp.beta1) * g;
         const float vv = hp.beta2 * v[o] + (1.f - hp.beta2) * g * g;
         m[o] = mm;
         v[o] = vv;
         table[o] -= hp.lr_t * mm / (sqrtf(vv) + hp.eps);
         if (j == 0 && touched) touched[row] = 1;
+    }
+}
+
+__device__ __forceinline__ void adam4(float4& th, float4& mm, float4& vv, const float4 g, const ctr_adam_hp& hp) {
+    const float b1 = hp.beta1, b2 = hp.beta2, c1 = 1.f - hp.beta1, c2 = 1.f - hp.beta2;
+    mm.x = b1 * mm.x + c1 * g.x; mm.y = b1 * mm.y + c1 * g.y; mm.z = b1 * mm.z + c1 * g.z; mm.w = b1 * mm.w + c1 * g.w;
+    vv.x = b2 * vv.x + c2 * g.x * g.x; vv.y = b2 * vv.y + c2 * g.y * g.y;
+    vv.z = b2 * vv.z + c2 * g.z * g.z; vv.w = b2 * vv.w + c2 * g.w * g.w;
+    th.x -= hp.lr_t * mm.x / (sqrtf(vv.x) + hp.eps); th.y -= hp.lr_t * mm.y / (sqrtf(vv.y) + hp.eps);
+    th.z -= hp.lr_t * mm.z / (sqrtf(vv.z) + hp.eps); th.w -= hp.lr_t * mm.w / (sqrtf(vv.w) + hp.eps);
+}
+
+// embedding tables (row = K coordinates [+ first-order weight]): K/4 lanes per row, 128-bit accesses, every load of a
+// row independent of the others.  The arithmetic per element is the generic kernel's, in the same order.
+template <int K>
+__global__ void __launch_bounds__(256)
+adam_rows_vec_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restrict__ n_rows, int64_t n_max, uint32_t mask,
+                     const float* __restrict__ grads, const uint32_t* __restrict__ seg_start, int gs, int has_first,
+                     float* __restrict__ table, float* __restrict__ m, float* __restrict__ v, int stride, int64_t table_rows,
+                     uint8_t* __restrict__ touched, uint32_t* __restrict__ long_list, const float* __restrict__ fm_w2,
+                     const ctr_adam_hp hp) {
+    constexpr int G = K / 4;
+    int64_t U = n_rows ? (int64_t) *n_rows : n_max;
+    if (U > n_max) U = n_max;
+    const int64_t total = U * G;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t u = t / G;
+        const int q = (int) (t - u * G);
+        const uint32_t key = __ldg(row_ids + u);
+        if (key == CTR_PAD_KEY) continue;
+        const int64_t row = (int64_t) (key & mask);
+        if (row >= table_rows) continue;
+        const float* p = grads + u * gs;
+        int np = 1;
+        if (seg_start) {
+            const uint32_t s0 = __ldg(seg_start + u), s1 = __ldg(seg_start + u + 1);
+            const int64_t c0 = s0 / CH;
+            const int64_t npl = (int64_t) ((s1 - 1) / CH) - c0 + 1;
+            if (long_list && npl > LONG_RUN) {
+                if (q == 0) long_list[1 + atomicAdd(long_list, 1u)] = (uint32_t) u;
+                continue;
+            }
+            np = (int) npl;
+            p = grads + (u + c0) * gs;
+        }
+        const int64_t o = row * stride + q * 4;
+        float4 th = *reinterpret_cast<const float4*>(table + o);
+        float4 mm = *reinterpret_cast<const float4*>(m + o);
+        float4 vv = *reinterpret_cast<const float4*>(v + o);
+        float th1 = 0.f, m1 = 0.f, v1 = 0.f;
+        const bool first = has_first && q == 0;
+        if (first) { th1 = table[row * stride + K]; m1 = m[row * stride + K]; v1 = v[row * stride + K]; }
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+        float g1 = 0.f, D = 0.f;
+        for (int i = 0; i < np; ++i) {       // partials in chunk order
+            const float4 a = __ldg(reinterpret_cast<const float4*>(p + (int64_t) i * gs + q * 4));
+            g.x += a.x; g.y += a.y; g.z += a.z; g.w += a.w;
+            if (first) g1 += __ldg(p + (int64_t) i * gs + K);
+            if (fm_w2) D += __ldg(p + (int64_t) i * gs + K + 1);
+        }
+        if (fm_w2) {
+            const float4 w2 = make_float4(__ldg(fm_w2 + q * 4), __ldg(fm_w2 + q * 4 + 1), __ldg(fm_w2 + q * 4 + 2), __ldg(fm_w2 + q * 4 + 3));
+            g.x = fmaf(-w2.x * th.x, D, g.x); g.y = fmaf(-w2.y * th.y, D, g.y);
+            g.z = fmaf(-w2.z * th.z, D, g.z); g.w = fmaf(-w2.w * th.w, D, g.w);
+        }
+        adam4(th, mm, vv, g, hp);
+        *reinterpret_cast<float4*>(m + o) = mm;
+        *reinterpret_cast<float4*>(v + o) = vv;
+        *reinterpret_cast<float4*>(table + o) = th;
+        if (first) {
+            m1 = hp.beta1 * m1 + (1.f - hp.beta1) * g1;
+            v1 = hp.beta2 * v1 + (1.f - hp.beta2) * g1 * g1;
+            m[row * stride + K] = m1;
+            v[row * stride + K] = v1;
+            table[row * stride + K] = th1 - hp.lr_t * m1 / (sqrtf(v1) + hp.eps);
+        }
+        if (q == 0 && touched) touched[row] = 1;
     }
 }
 
@@ -174,7 +280,8 @@ __global__ void __launch_bounds__(256)
 adam_rows_long_kernel(const uint32_t* __restrict__ row_ids, uint32_t mask, const float* __restrict__ part,
                       const uint32_t* __restrict__ seg_start, int gs, int width, float* __restrict__ table,
                       float* __restrict__ m, float* __restrict__ v, int stride, int64_t table_rows,
-                      uint8_t* __restrict__ touched, const uint32_t* __restrict__ long_list, const ctr_adam_hp hp) {
+                      uint8_t* __restrict__ touched, const uint32_t* __restrict__ long_list,
+                      const float* __restrict__ fm_w2, int emb_k, const ctr_adam_hp hp) {
     const int lane = threadIdx.x & 31;
     const int gs4 = gs >> 2;
     const uint32_t nlong = long_list[0];
@@ -206,8 +313,7 @@ adam_rows_long_kernel(const uint32_t* __restrict__ row_ids, uint32_t mask, const
         const uint32_t key = row_ids[u];
         const int64_t row = (int64_t) (key & mask);
         if (key == CTR_PAD_KEY || row >= table_rows) continue;
-        // lane j applies Adam to coordinate j (j + 32 for very wide rows)
-        for (int j = lane; j < width; j += 32) {
+        auto pick = [&](int j) {
             float g = 0.f;
 #pragma unroll
             for (int q = 0; q < MAX_GS4; ++q) {
@@ -216,7 +322,14 @@ adam_rows_long_kernel(const uint32_t* __restrict__ row_ids, uint32_t mask, const
                     g = r == 0 ? acc[q].x : (r == 1 ? acc[q].y : (r == 2 ? acc[q].z : acc[q].w));
                 }
             }
+            return g;
+        };
+        const float D = fm_w2 ? pick(emb_k + 1) : 0.f;
+        // lane j applies Adam to coordinate j (j + 32 for very wide rows)
+        for (int j = lane; j < width; j += 32) {
+            float g = pick(j);
             const int64_t o = row * stride + j;
+            if (fm_w2 && j < emb_k) g = fmaf(-fm_w2[j] * table[o], D, g);
             const float mm = hp.beta1 * m[o] + (1.f - hp.beta1) * g;
             const float vv = hp.beta2 * v[o] + (1.f - hp.beta2) * g * g;
             m[o] = mm;
@@ -399,13 +512,17 @@ extern "C" int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_emb
     int rc = ctr_check_embed_cfg(h, cfg);
     if (rc) return rc;
     CTR_REQUIRE(h, sorted_keys && perm && uidx && dx0 && part && n >= 0, "embed_bwd_partials: null pointer");
-    CTR_REQUIRE(h, cfg->grad_stride >= cfg->k + (cfg->has_first ? 1 : 0), "embed_bwd_partials: grad_stride too small");
+    CTR_REQUIRE(h, cfg->grad_stride >= cfg->k + ((cfg->has_first || cfg->use_fm) ? 2 : 0) && cfg->grad_stride % 4 == 0,
+                "embed_bwd_partials: grad_stride must be a multiple of 4, >= k + 2 with first-order / FM columns");
+    CTR_REQUIRE(h, dx0_ld % 4 == 0 && cfg->x0_ld % 4 == 0 && ((reinterpret_cast<uintptr_t>(dx0) | reinterpret_cast<uintptr_t>(part) |
+                       reinterpret_cast<uintptr_t>(sum_e) | reinterpret_cast<uintptr_t>(x0) | reinterpret_cast<uintptr_t>(cont_grad)) & 15) == 0,
+                "embed_bwd_partials: dx0 / x0 / sum_e / part / cont_grad must be 16-byte aligned with leading dimensions % 4 == 0");
     CTR_REQUIRE(h, !cfg->use_fm || (x0 && sum_e && dlogit && w_fm), "embed_bwd_partials: FM inputs null");
     CTR_REQUIRE(h, cfg->M == 0 || (field_of_slot && inv_cnt_emb && inv_cnt_first), "embed_bwd_partials: multi inputs null");
     CTR_REQUIRE(h, dx0_ld >= (int64_t) (cfg->Fc + cfg->Fm) * cfg->k, "embed_bwd_partials: dx0_ld too small");
     if (n == 0) return CTR_OK;
     const int64_t chunks = ctr_cdiv(n, CH);
-    const int64_t threads = chunks * cfg->k;
+    const int64_t threads = chunks * (cfg->k / 4);
     const unsigned blocks = (unsigned) ctr_cdiv(threads, 256);
 #define LAUNCH_BP(KK)                                                                                                  \
     embed_bwd_partials_kernel<KK><<<blocks, 256, 0, ctr_st(s)>>>(*cfg, sorted_keys, perm, uidx, n, field_of_slot, x0, dx0, \
@@ -447,10 +564,12 @@ extern "C" int64_t ctr_adam_rows_ws_bytes(ctr_handle*, int64_t n_max) {
 extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
                              int local_bits, const float* grads, const uint32_t* seg_start, int grad_stride, int width,
                              float* table, float* m, float* v, int table_stride, int64_t table_rows,
-                             uint8_t* touched, void* ws, int64_t ws_bytes, const ctr_adam_hp* hp) {
+                             uint8_t* touched, void* ws, int64_t ws_bytes, const float* fm_w2, int emb_k,
+                             const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, row_ids && grads && table && m && v && hp, "adam_rows: null pointer");
     CTR_REQUIRE(h, width > 0 && grad_stride >= width && table_stride >= width && n_max >= 0 && table_rows > 0,
                 "adam_rows: bad sizes");
+    CTR_REQUIRE(h, !fm_w2 || (emb_k > 0 && emb_k <= width && grad_stride >= emb_k + 2), "adam_rows: fm_w2 needs grad_stride >= emb_k + 2");
     if (n_max == 0) return CTR_OK;
     uint32_t mask = (local_bits <= 0 || local_bits >= 32) ? 0xFFFFFFFFu : ((1u << local_bits) - 1u);
     uint32_t* long_list = nullptr;
@@ -460,14 +579,34 @@ extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_id
         long_list = (uint32_t*) ws;
         CTR_CUDA(h, cudaMemsetAsync(long_list, 0, 4, ctr_st(s)));
     }
-    adam_rows_kernel<<<grid_for(h, n_max * width), 256, 0, ctr_st(s)>>>(row_ids, n_rows, n_max, mask, grads, seg_start,
-                                                                         grad_stride, width, table, m, v, table_stride,
-                                                                         table_rows, touched, long_list, *hp);
+    // embedding-table shape: vectorised kernel
+    const bool aligned = ((reinterpret_cast<uintptr_t>(table) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v) |
+                           reinterpret_cast<uintptr_t>(grads)) & 15) == 0;
+    const bool vec = emb_k > 0 && (emb_k == 4 || emb_k == 8 || emb_k == 16 || emb_k == 32) && (width == emb_k || width == emb_k + 1) &&
+                     table_stride % 4 == 0 && grad_stride % 4 == 0 && aligned && (width == emb_k || grad_stride >= emb_k + 1);
+    if (vec) {
+        const int has_first = width == emb_k + 1;
+        const unsigned grid = grid_for(h, n_max * (emb_k / 4));
+#define LAUNCH_AV(KK)                                                                                                         \
+    adam_rows_vec_kernel<KK><<<grid, 256, 0, ctr_st(s)>>>(row_ids, n_rows, n_max, mask, grads, seg_start, grad_stride, has_first, \
+                                                          table, m, v, table_stride, table_rows, touched, long_list, fm_w2, *hp)
+        switch (emb_k) {
+            case 4: LAUNCH_AV(4); break;
+            case 8: LAUNCH_AV(8); break;
+            case 16: LAUNCH_AV(16); break;
+            default: LAUNCH_AV(32); break;
+        }
+#undef LAUNCH_AV
+    } else {
+        adam_rows_kernel<<<grid_for(h, n_max * width), 256, 0, ctr_st(s)>>>(row_ids, n_rows, n_max, mask, grads, seg_start,
+                                                                             grad_stride, width, table, m, v, table_stride,
+                                                                             table_rows, touched, long_list, fm_w2, emb_k, *hp);
+    }
     CTR_CHECK_LAUNCH(h, "adam_rows");
     if (long_list) {
         adam_rows_long_kernel<<<(unsigned) h->sm_count * 4, 256, 0, ctr_st(s)>>>(row_ids, mask, grads, seg_start, grad_stride,
                                                                                  width, table, m, v, table_stride, table_rows,
-                                                                                 touched, long_list, *hp);
+                                                                                 touched, long_list, fm_w2, emb_k, *hp);
         CTR_CHECK_LAUNCH(h, "adam_rows_long");
     }
     return CTR_OK;

@@ -8,6 +8,8 @@
 // Every table row is therefore read from HBM exactly once per lookup (the reference gathers
 // feats_emb twice and feats once: models/deepfm.py:78,85,98).
 #include "ctr_common.cuh"
+#include <cstdlib>
+#include <type_traits>
 
 namespace {
 
@@ -68,8 +70,8 @@ fm_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, c
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
             const float* row = table + rid[u] * (int64_t) stride;
-            e[u] = live[u] ? ctr_ldg_f4_stream(row + q * 4) : f4_zero();
-            w[u] = (USE_FM && live[u] && has_first && q == 0) ? ctr_ldg_f1_stream(row + K) : 0.f;
+            e[u] = live[u] ? __ldg(reinterpret_cast<const float4*>(row + q * 4)) : f4_zero();
+            w[u] = (USE_FM && live[u] && has_first && q == 0) ? __ldg(row + K) : 0.f;
         }
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
@@ -144,6 +146,148 @@ fm_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, c
     }
 }
 
+// K1, fast path (no pooled fields, no vector block, C <= 2 warp-loads of rows): the same lane mapping as above,
+// restated so that a sample costs ~200 warp instructions instead of ~660 -- the general kernel is issue-bound, not
+// HBM-bound (profiles/r01a: sm__inst_executed 55 % of peak at 45 % occupancy, DRAM 24 %).
+//   * warps are persistent over a grid-stride sequence of samples, so everything that is per-model rather than
+//     per-sample (flags, strides, the C continuous-field rows, which stay in registers) is set up once;
+//   * the ids and continuous values of the NEXT sample are fetched (one coalesced load each) before the current
+//     sample's rows are requested, which takes the id -> row dependent-load chain off the critical path;
+//   * lane l owns id l: it fetches that row's first-order weight itself, so the first-order run is one coalesced
+//     store; the row-gather lanes receive their ids by shuffle;
+//   * the (sum e, sum e^2) reduction over the row slots is a halving exchange (7 shuffles instead of 24).
+template <int K, bool USE_FM, bool ID64>
+__global__ void __launch_bounds__(256, 4)
+fm_gather_fast_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, const void* __restrict__ ids,
+                      const int64_t id_offset, const float* __restrict__ cont, const float* __restrict__ cont_rows,
+                      float* __restrict__ x0, float* __restrict__ fm, float* __restrict__ sum_e) {
+    constexpr int LPR = K / 4;                                   // lanes per row
+    constexpr int RPW = 32 / LPR;                                // rows per warp-wide load
+    constexpr int UNR = LPR;                                     // warp-wide loads per 32 fields
+    constexpr int CS = 2;                                        // continuous-row slots per lane
+    constexpr int H = RPW >= 8 ? 3 : 2;                          // halving levels (offsets 16, 8[, 4])
+    constexpr int NV = 8 >> H;                                   // values left per lane after them
+    constexpr int BF_MASK = LPR < 4 ? (3 & ~(LPR - 1)) : 0;      // lane bits reduced by plain butterflies
+    typedef typename std::conditional<ID64, int64_t, int32_t>::type id_t;
+    const int lane = threadIdx.x & 31;
+    const int r = lane / LPR, q = lane % LPR;
+    const int Fc = cfg.Fc, C = cfg.C, B = cfg.B;
+    const int stride = cfg.table_stride;
+    const bool has_first = cfg.has_first != 0, zero0 = cfg.zero_row0 != 0, rnd = cfg.round_tf32 != 0;
+    const bool fm_cont = USE_FM && cfg.fm_cont != 0;
+    const int cont_col = Fc * K;
+    const int tail = cfg.x0_ld - cont_col;      // continuous values + pad columns (<= 32, checked by the launcher)
+    const int nw = (int) ((gridDim.x * blockDim.x) >> 5);
+    int b = (int) ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (b >= B) return;
+
+    float4 crow[CS];
+    float cw = 0.f;
+#pragma unroll
+    for (int s = 0; s < CS; ++s) {
+        const int c = s * RPW + r;
+        crow[s] = (fm_cont && c < C) ? __ldg(reinterpret_cast<const float4*>(cont_rows + c * (int64_t) stride + q * 4)) : f4_zero();
+    }
+    if (fm_cont && has_first && lane < C) cw = __ldg(cont_rows + lane * (int64_t) stride + K);
+
+    const id_t* __restrict__ idp = reinterpret_cast<const id_t*>(ids);
+    const char* __restrict__ tbytes = reinterpret_cast<const char*>(table);
+    const uint32_t stride_b = (uint32_t) stride * 4u;
+    id_t my_id = lane < Fc ? idp[b * (int64_t) cfg.ids_ld + lane] : (id_t) 0;
+    float my_x = lane < C ? cont[b * (int64_t) C + lane] : 0.f;
+
+    for (; b < B; b += nw) {
+        const int bn = b + nw;
+        id_t nx_id = 0;
+        float nx_x = 0.f;
+        if (bn < B) {
+            if (lane < Fc) nx_id = idp[bn * (int64_t) cfg.ids_ld + lane];
+            if (lane < C) nx_x = cont[bn * (int64_t) C + lane];
+        }
+        float* __restrict__ x0row = x0 + b * (int64_t) cfg.x0_ld;
+        float* __restrict__ fmrow = USE_FM ? fm + b * (int64_t) cfg.fm_ld : nullptr;
+        float4 as = f4_zero(), aq = f4_zero();
+
+        for (int f0 = 0; f0 < Fc; f0 += 32) {
+            id_t id_l = my_id;
+            if (f0 > 0) id_l = f0 + lane < Fc ? idp[b * (int64_t) cfg.ids_ld + f0 + lane] : (id_t) 0;
+            // row index as u32 (tables have < 2^32 rows); lanes past Fc carry id 0 -> a valid row that is never used
+            const uint32_t row_l = (uint32_t) ((int64_t) id_l + id_offset);
+            float4 e[UNR];
+            uint32_t row[UNR];
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                row[u] = __shfl_sync(0xffffffffu, row_l, u * RPW + r);
+                // L1-allocating loads on purpose: the hot rows of a skewed id distribution are served from L1; sent
+                // to L2 every time (ld.global.nc.L1::no_allocate) they queue on a few L2 slices and the kernel is 1.5x slower
+                e[u] = __ldg(reinterpret_cast<const float4*>(tbytes + (uint64_t) row[u] * stride_b) + q);
+            }
+            if (USE_FM) {      // first-order run: lane l owns field f0 + l
+                float w = 0.f;
+                if (has_first) w = __ldg(reinterpret_cast<const float*>(tbytes + (uint64_t) row_l * stride_b) + K);
+                if (zero0 && row_l == 0) w = 0.f;
+                if (f0 + lane < Fc) fmrow[f0 + lane] = w;
+            }
+            if (zero0) {
+#pragma unroll
+                for (int u = 0; u < UNR; ++u)
+                    if (row[u] == 0) e[u] = f4_zero();
+            }
+#pragma unroll
+            for (int u = 0; u < UNR; ++u) {
+                if (f0 + u * RPW + r < Fc) {
+                    float4 o = e[u];
+                    if (rnd) o = make_float4(ctr_round_tf32_fast(o.x), ctr_round_tf32_fast(o.y), ctr_round_tf32_fast(o.z), ctr_round_tf32_fast(o.w));
+                    *reinterpret_cast<float4*>(x0row + (f0 + u * RPW) * K + lane * 4) = o;
+                    if (USE_FM) f4_acc(as, aq, e[u]);
+                }
+            }
+        }
+        // continuous values, then the pad columns: the 1.0 at column D0 is the bias row of the layer-0 weight-gradient GEMM
+        if (lane < tail) x0row[cont_col + lane] = lane < C ? (rnd ? ctr_round_tf32_fast(my_x) : my_x) : (lane == C ? 1.f : 0.f);
+
+        if (USE_FM) {
+            if (lane < C) fmrow[Fc + lane] = cw * my_x;          // cw is 0 without fm_cont / first-order weights
+            if (fm_cont) {
+#pragma unroll
+                for (int s = 0; s < CS; ++s) {
+                    const float x = __shfl_sync(0xffffffffu, my_x, (s * RPW + r) & 31);     // slots c >= C hold zero rows
+                    f4_acc(as, aq, make_float4(crow[s].x * x, crow[s].y * x, crow[s].z * x, crow[s].w * x));
+                }
+            }
+            float v[8] = {as.x, as.y, as.z, as.w, aq.x, aq.y, aq.z, aq.w};
+#pragma unroll
+            for (int j = 0; j < H; ++j) {        // halving exchange: each level keeps half of the values, summed over the pair
+                const int o = 16 >> j, n = 4 >> j;
+                const bool hi = (lane & o) != 0;
+#pragma unroll
+                for (int i = 0; i < n; ++i) {
+                    const float keep = hi ? v[i + n] : v[i], send = hi ? v[i] : v[i + n];
+                    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+                }
+            }
+#pragma unroll
+            for (int o = 16 >> H; o >= LPR; o >>= 1) {
+#pragma unroll
+                for (int i = 0; i < NV; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+            }
+            // lanes with bit 16 clear hold sum e, their partners sum e^2, of coordinate q*4 + comp
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                const float sq = __shfl_xor_sync(0xffffffffu, v[i], 16);
+                if ((lane & (16 | BF_MASK)) == 0) {
+                    const int comp = (((lane & 8) ? 2 : 0) | ((H >= 3 && (lane & 4)) ? 1 : 0)) + i;
+                    const int j = q * 4 + comp;
+                    fmrow[Fc + C + j] = 0.5f * (v[i] * v[i] - sq);      // models/deepfm.py:88-92
+                    sum_e[b * (int64_t) K + j] = v[i];
+                }
+            }
+        }
+        my_id = nx_id;
+        my_x = nx_x;
+    }
+}
+
 // K2: one warp per (sample, multi-valued field)
 template <int K>
 __global__ void __launch_bounds__(256)
@@ -174,8 +318,8 @@ pooled_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ tabl
         int64_t rid = ok ? ctr_load_id(ids, cfg.id_bytes, idrow + t) : 0;
         bool live = ok && !(zero0 && rid == 0);
         const float* row = table + rid * (int64_t) stride;
-        float4 e = live ? ctr_ldg_f4_stream(row + q * 4) : f4_zero();
-        float w = (live && has_first && q == 0) ? ctr_ldg_f1_stream(row + K) : 0.f;
+        float4 e = live ? __ldg(reinterpret_cast<const float4*>(row + q * 4)) : f4_zero();
+        float w = (live && has_first && q == 0) ? __ldg(row + K) : 0.f;
         float sw = (ok && slot_weight) ? slot_weight[b * (int64_t) cfg.M + t] : 1.f;
         // row sum over the k coordinates (models/deepfm_multi.py:84 axis_2_sum)
         float rs = (e.x + e.y) + (e.z + e.w);
@@ -223,7 +367,7 @@ __global__ void scalar_gather_sum_kernel(const float* __restrict__ table, const 
     const int64_t b = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (b >= B) return;
     float acc = 0.f;
-    for (int j = lane; j < W; j += 32) acc += ctr_ldg_f1_stream(table + ctr_load_id(ids, id_bytes, b * (int64_t) W + j));
+    for (int j = lane; j < W; j += 32) acc += __ldg(table + ctr_load_id(ids, id_bytes, b * (int64_t) W + j));
     acc = ctr_warp_sum(acc);
     if (lane == 0) out[b] = acc;
 }
@@ -257,6 +401,50 @@ extern "C" int ctr_fm_gather_fwd(ctr_handle* h, ctr_stream s, const ctr_embed_cf
     CTR_REQUIRE(h, !cfg->use_fm || (fm && sum_e), "fm_gather_fwd: fm/sum_e null with use_fm");
     CTR_REQUIRE(h, !(cfg->use_fm && cfg->fm_cont && cfg->C > 0) || cont_rows, "fm_gather_fwd: cont_rows null");
     if (cfg->B == 0) return CTR_OK;
+    // fast path: the headline shapes (DeepFM / DNN / WDL with single-valued fields only)
+    {
+        const int lpr = cfg->k / 4, rpw = 32 / lpr;
+        const bool fast = cfg->Fm == 0 && cfg->V == 0 && cfg->C <= 2 * rpw && cfg->C <= 32 &&
+                          cfg->x0_ld - cfg->Fc * cfg->k <= 32 && cfg->k <= 32 && getenv("CTR_K1_GENERAL") == nullptr;
+        if (fast) {
+            static int occ[4][2][2];         // resident CTAs per SM of each instantiation, queried once
+            static int sms = 0;
+            if (!sms) {
+                int dev = 0;
+                cudaGetDevice(&dev);
+                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+            }
+            const int ki = cfg->k == 4 ? 0 : cfg->k == 8 ? 1 : cfg->k == 16 ? 2 : 3, fi = cfg->use_fm ? 1 : 0, ii = cfg->id_bytes == 8;
+#define LAUNCH_FAST(KK, FM_, I64)                                                                                      \
+    {                                                                                                                  \
+        auto kern = fm_gather_fast_kernel<KK, FM_, I64>;                                                               \
+        if (!occ[ki][fi][ii]) {                                                                                        \
+            int o = 0;                                                                                                 \
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kern, 256, 0);                                           \
+            occ[ki][fi][ii] = o > 0 ? o : 1;                                                                           \
+        }                                                                                                              \
+        const int64_t want = ctr_cdiv((int64_t) cfg->B, 8), cap = (int64_t) sms * occ[ki][fi][ii];                     \
+        kern<<<(unsigned) (want < cap ? want : cap), 256, 0, ctr_st(s)>>>(*cfg, table, ids, id_offset, cont, cont_rows, \
+                                                                         x0, fm, sum_e);                               \
+    }
+#define LAUNCH_FAST_K(KK)                                                    \
+    if (cfg->use_fm) {                                                       \
+        if (ii) LAUNCH_FAST(KK, true, true) else LAUNCH_FAST(KK, true, false)    \
+    } else {                                                                 \
+        if (ii) LAUNCH_FAST(KK, false, true) else LAUNCH_FAST(KK, false, false)  \
+    }
+            switch (cfg->k) {
+                case 4: LAUNCH_FAST_K(4) break;
+                case 8: LAUNCH_FAST_K(8) break;
+                case 16: LAUNCH_FAST_K(16) break;
+                default: LAUNCH_FAST_K(32) break;
+            }
+#undef LAUNCH_FAST_K
+#undef LAUNCH_FAST
+            CTR_CHECK_LAUNCH(h, "fm_gather_fwd(fast)");
+            return CTR_OK;
+        }
+    }
     const unsigned blocks = (unsigned) ctr_cdiv((int64_t) cfg->B * 32, 256);
 #define LAUNCH_K1(KK)                                                                                              \
     if (cfg->use_fm)                                                                                               \

@@ -485,7 +485,15 @@ class CtrEngine:
         s, st = self.spec, self._stream()
         self.h.call("ctr_adam_rows", st, ptr(self.uniq), ptr(self.n_unique), n, 0, ptr(self.part), ptr(self.seg_start),
                     s.grad_stride, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
-                    self.rows_local, ptr(self.touched), ptr(self.ws), self.ws.numel(), hp)
+                    self.rows_local, ptr(self.touched), ptr(self.ws), self.ws.numel(), self._fm_w2(), s.k, hp)
+
+    def _fm_w2(self):
+        """device pointer of the k second-order head weights (the e-term of the FM gradient is applied in ctr_adam_rows)"""
+        s = self.spec
+        if not s.use_fm:
+            return None
+        w_fm = self._head_parts()[0]
+        return w_fm.data_ptr() + 4 * (s.Fc + s.Fm + s.C)
 
     def _reduce_dense_grads(self) -> None:
         """data-parallel hook: sum the dense gradients over ranks (no-op on one GPU)"""

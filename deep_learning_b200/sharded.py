@@ -275,16 +275,16 @@ class ShardedCtrEngine(CtrEngine):
             self._build_exchange(self._pending_exchange, self.side)
             self._pending_exchange = None
         U, n_req = pl.U, pl.n_req
-        h.call("ctr_embed_bwd_finalize", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.row_width, self.wire,
+        h.call("ctr_embed_bwd_finalize", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
                ptr(self.part), ptr(self.grads_send))
         _shard.exchange(self.grads_send[:U], pl.send_counts, pl.recv_counts, out=self.g_recv, group=self.group)
         if not n_req:
             return
         h.call("ctr_segment_sum_rows", st, ptr(pl.o_seg), ptr(pl.o_nuniq), n_req, ptr(pl.o_idx), ptr(self.g_recv),
-               self.wire, s.row_width, ptr(self.g_own), self.wire)
+               self.wire, s.grad_width, ptr(self.g_own), self.wire)
         h.call("ctr_adam_rows", st, ptr(pl.o_uniq), ptr(pl.o_nuniq), n_req, sp.local_bits, ptr(self.g_own), None,
                self.wire, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
-               self.rows_local, ptr(self.touched), None, 0, hp)
+               self.rows_local, ptr(self.touched), None, 0, self._fm_w2(), s.k, hp)
 
     def _reduce_dense_grads(self) -> None:
         # dlogit already carries 1/B_global, so a plain SUM over ranks is the global-batch gradient; the loss

@@ -86,6 +86,12 @@ class ModelSpec:
     def row_width(self) -> int:
         return self.k + (1 if self.has_first else 0)
 
+    @property
+    def grad_width(self) -> int:
+        """columns of a gradient row that carry data: [0,k) embedding, [k] first-order, [k+1] D = sum of dlogit over the
+        row's single-valued FM lookups (include/ctr_b200.h, ctr_embed_bwd_partials)"""
+        return self.k + 2 if self.use_fm else self.row_width
+
     # ---- reference <-> canonical permutations -------------------------------------------------
     def deep0_perm(self) -> np.ndarray:
         """canonical X0 column i  ->  row of the reference deep_0 ([cont | vector | emb] order,

@@ -221,12 +221,15 @@ int ctr_shard_counts(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const ui
 
 /* Per-run partial gradients.  The sorted lookup list is cut into fixed chunks of CTR_BWD_CHUNK
  * entries; one sub-warp walks a chunk in order and writes the sum of each run it meets to
- * part[(uidx + chunk) * grad_stride ..] (injective, a row's runs are consecutive).  The gradient of
- * lookup (b, field) is formed on the fly:
- *     g_v = scale_e * ( dX0[b, field*k + :] + use_fm * dlogit[b] * w_second * (sum_e[b] - X0[b, field*k + :]) )
- *     g_w = scale_w * dlogit[b] * w_first[field]
- * (scale = 1 for single-valued fields, the saved 1/count for multi-valued ones).
- * part must hold (n + n/CTR_BWD_CHUNK + 2) * grad_stride floats. */
+ * part[(uidx + chunk) * grad_stride ..] (injective, a row's runs are consecutive).  A gradient row is
+ *     [0,k) embedding coordinates | [k] first-order weight | [k+1] D
+ * and the gradient of lookup (b, field) is formed on the fly (models/deepfm.py:78-98 differentiated):
+ *   single-valued field:  g_v = dX0[b, field*k + :] + use_fm * dlogit[b] * w_second * sum_e[b]        D += dlogit[b]
+ *   multi-valued slot:    g_v = scale_e * ( dX0[..] + use_fm * dlogit[b] * w_second * (sum_e[b] - X0[b, field*k + :]) )
+ *                         g_w = scale_w * dlogit[b] * w_first[field]       (scale = the saved 1/count; 1 for single-valued)
+ * The remaining FM term of a single-valued row, -w_second * e_row * D, is the same for every lookup of the row and is
+ * applied by ctr_adam_rows (fm_w2), which reads e_row anyway: the X0 tile is not re-read for single-valued fields.
+ * grad_stride: a multiple of 4, >= k + 2.  part must hold (n + n/CTR_BWD_CHUNK + 2) * grad_stride floats. */
 #define CTR_BWD_CHUNK 32
 int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg,
                            const uint32_t* sorted_keys, const uint32_t* perm, const uint32_t* uidx, int64_t n,
@@ -266,7 +269,10 @@ int ctr_segment_sum_rows(ctr_handle* h, ctr_stream s, const uint32_t* seg_start,
 /* TF1 Adam on the rows named by row_ids (unique):  g = grads[u];
  *   m <- b1*m + (1-b1) g ; v <- b2*v + (1-b2) g^2 ; theta <- theta - lr_t * m / (sqrt(v) + eps)
  * rows with id 0xFFFFFFFF are skipped.  `touched` ([R] bytes or NULL) is set to 1 for every updated
- * row (used by the exact dense sweep).  row = (key & local_mask) when local_bits > 0. */
+ * row (used by the exact dense sweep).  row = (key & local_mask) when local_bits > 0.
+ * fm_w2 ([emb_k] second-order head weights, or NULL): g[j] -= fm_w2[j] * theta[j] * grads[u, emb_k + 1] for j < emb_k
+ * before the update (the e-term ctr_embed_bwd_partials leaves out).  emb_k > 0 with width == emb_k (+1) selects the
+ * 128-bit row kernel; emb_k = 0: generic width. */
 typedef struct ctr_adam_hp { float lr_t, beta1, beta2, eps; } ctr_adam_hp;
 int64_t ctr_adam_rows_ws_bytes(ctr_handle* h, int64_t n_max);
 int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
@@ -276,7 +282,7 @@ int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const ui
                   float* table, float* m, float* v, int table_stride, int64_t table_rows,
                   uint8_t* touched, void* ws, int64_t ws_bytes /* ctr_adam_rows_ws_bytes(); needed when seg_start != NULL:
                   runs spread over many chunks (hot rows) are queued and reduced by one warp each */,
-                  const ctr_adam_hp* hp);
+                  const float* fm_w2, int emb_k, const ctr_adam_hp* hp);
 /* dense TF1 Adam over n floats: g_eff = (g ? g[i] : 0) + l2*theta + l1*sign(theta).
  * skip ([n/skip_group] bytes or NULL): elements whose group flag is 1 are left alone and the flag is
  * cleared (rows already updated by ctr_adam_rows).  This is the exact `tf_dense` mode: TF1 Adam
