@@ -160,6 +160,8 @@ struct EpiParams {
     int n_total;            // row pitch of the dropout hash index (the full N)
     int dbg;                // timing experiments only (CTR_GEMM_DBG): 1 skip global stores, 2 skip MMAs, 4 skip TMA loads
     unsigned long long* trace;   // CTR_GEMM_DBG & 8: per-CTA phase timestamps (8 slots per CTA)
+    unsigned* sm_slots;     // split2 stagger: per-SM arrival counters (zeroed before the launch), or null
+    unsigned stagger_ns;    // the second CTA to arrive on an SM starts this much later (first wave only)
 };
 
 __device__ __forceinline__ unsigned long long gtimer() {
@@ -232,6 +234,18 @@ __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
 // (ptxas expands the cvt into a longer sequence with inf/nan handling)
 __device__ __forceinline__ float round_tf32_fast(float x) { return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u); }
 
+// fp32 -> tf32 (round to nearest even) in ONE instruction (F2FP.TF32), optionally with the ReLU folded in
+__device__ __forceinline__ float cvt_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rn.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+__device__ __forceinline__ float cvt_tf32_relu(float x) {
+    uint32_t r;
+    asm("cvt.rn.relu.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+
 template <bool BIAS, bool RELU, bool MASK, int EW>
 __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
                                               int64_t ldc, const EpiParams& ep, float* stage, uint32_t sbias) {
@@ -293,7 +307,7 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
                 v.z = mk[j].z > 0.f ? v.z * ep.mask_scale : 0.f;
                 v.w = mk[j].w > 0.f ? v.w * ep.mask_scale : 0.f;
             }
-            if (ep.round_out) { v.x = round_tf32_fast(v.x); v.y = round_tf32_fast(v.y); v.z = round_tf32_fast(v.z); v.w = round_tf32_fast(v.w); }
+            if (ep.round_out) { v.x = cvt_tf32(v.x); v.y = cvt_tf32(v.y); v.z = cvt_tf32(v.z); v.w = cvt_tf32(v.w); }
             if (dropout) {
                 const uint64_t e0 = (uint64_t) row * (uint64_t) (ep.n_total > 0 ? ep.n_total : N) + (uint64_t) (ep.col0 + col);
                 v.x = dropout_u01(ep.seed, e0 + 0) < ep.keep ? v.x / ep.keep : 0.f;
@@ -317,6 +331,79 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
     }
 }
 
+// The same epilogue for the common case -- every row of the tile valid, 16-byte aligned vector accesses, N % 4 == 0,
+// rounded outputs, no dropout: ~115 instructions per 32x32 sub-tile instead of ~330.  The epilogue is issue-bound (two
+// warps per scheduler, each a dependent chain), so its duration is its instruction count: bounds checks, per-row
+// 64-bit address arithmetic and the 3-instruction ReLU + round were two thirds of it.  The ReLU mask of the data-gradient
+// GEMM is fetched one sub-tile ahead (its DRAM latency was the whole epilogue: 16 us per tile against 5.7 without it).
+// Tried and dropped: a transposition-free epilogue on tcgen05.ld.16x256b fragments (32-byte runs per thread quad, 64-bit
+// stores / mask loads) -- it frees the shared-memory port but the 8-sectors-per-instruction accesses made the
+// epilogue 1.5x (stores) to 2x (mask loads) slower.
+template <bool BIAS, bool RELU, bool MASK, int EW>
+__device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp, int lane, int m0, int N, float* C,
+                                                   int64_t ldc, const EpiParams& ep, float* stage, uint32_t sbias) {
+    const int q = ewarp & 3, half = ewarp >> 2;
+    const uint32_t tile = smem_u32(stage) + (uint32_t) (ewarp * EPI_TILE_FLOATS * 4);
+    const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
+    const int nchunks = (N + 31) / 32;
+    const int rsub = lane >> 3, cc = (lane & 7) * 4;
+    const int row0 = m0 + q * 32 + rsub;
+    const uint32_t st_addr = tile + (uint32_t) (lane * EPI_PITCH * 4);
+    const uint32_t ld_addr = tile + (uint32_t) ((rsub * EPI_PITCH + cc) * 4);
+    char* dst_row = reinterpret_cast<char*>(C + (int64_t) row0 * ldc + cc);
+    const char* msk_row = MASK ? reinterpret_cast<const char*>(ep.mask + (int64_t) row0 * ep.ldmask + cc) : nullptr;
+    const int64_t dstep = 4 * ldc * 4, mstep = 4 * ep.ldmask * 4;         // 4 rows down, in bytes
+    const float scale = ep.mask_scale;
+    float4 mk[8], mkn[8];
+    auto load_mask = [&](int c, float4* m) {
+        const bool ok = c < nchunks && c * 32 + cc < N;
+        const char* mp = msk_row + (int64_t) c * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            m[j] = ok ? ctr_ldg_f4_stream(reinterpret_cast<const float*>(mp)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            mp += mstep;
+        }
+    };
+    if (MASK) load_mask(half, mkn);
+    for (int c = half; c < nchunks; c += EW / 4) {
+        const int c0 = c * 32;
+        uint32_t r[32];
+        tmem_ld32_issue(lane_addr + (uint32_t) c0, r);
+        const bool col_ok = c0 + cc < N;                  // N % 4 == 0: a lane's four columns are valid together
+        float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (BIAS) bs = lds_f4(sbias + (uint32_t) ((c0 + cc) * 4));
+        if (MASK) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) mk[j] = mkn[j];
+            load_mask(c + EW / 4, mkn);                   // the next sub-tile's mask, in flight under this one
+        }
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            sts_f4(st_addr + (uint32_t) (16 * i), __uint_as_float(r[4 * i]), __uint_as_float(r[4 * i + 1]),
+                   __uint_as_float(r[4 * i + 2]), __uint_as_float(r[4 * i + 3]));
+        __syncwarp();
+        float4 tv[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) tv[j] = lds_f4(ld_addr + (uint32_t) (4 * j * EPI_PITCH * 4));
+        char* dp = dst_row + (int64_t) c0 * 4;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float4 v = tv[j];
+            if (BIAS) { v.x += bs.x; v.y += bs.y; v.z += bs.z; v.w += bs.w; }
+            if (MASK) {
+                v.x = mk[j].x > 0.f ? v.x * scale : 0.f; v.y = mk[j].y > 0.f ? v.y * scale : 0.f;
+                v.z = mk[j].z > 0.f ? v.z * scale : 0.f; v.w = mk[j].w > 0.f ? v.w * scale : 0.f;
+            }
+            if (RELU) { v.x = cvt_tf32_relu(v.x); v.y = cvt_tf32_relu(v.y); v.z = cvt_tf32_relu(v.z); v.w = cvt_tf32_relu(v.w); }
+            else { v.x = cvt_tf32(v.x); v.y = cvt_tf32(v.y); v.z = cvt_tf32(v.z); v.w = cvt_tf32(v.w); }
+            if (col_ok) *reinterpret_cast<float4*>(dp) = v;
+            dp += dstep;
+        }
+        __syncwarp();      // the tile is rewritten by the next chunk
+    }
+}
+
 // shared memory: [ pipeline stages, reused as epilogue staging | PipeBars | staged bias ]
 __host__ __device__ constexpr size_t pipe_region(size_t stage_total, int ew) {
     return stage_total > (size_t) ew * EPI_TILE_FLOATS * 4 ? stage_total : (size_t) ew * EPI_TILE_FLOATS * 4;
@@ -335,6 +422,17 @@ __device__ __forceinline__ void epilogue_prepare(int m0, int M, int N, const Epi
 template <int EW>
 __device__ __forceinline__ void epilogue_dispatch(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
                                                   int64_t ldc, const EpiParams& ep, float* stage, uint32_t sbias) {
+    const bool fast = m0 + BLOCK_M <= M && (N & 3) == 0 && (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
+                      ep.round_out && !(ep.keep < 1.f) && !(ep.dbg & 7) &&
+                      (!ep.mask || ((ep.ldmask & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.mask) & 15) == 0));
+    if (fast) {
+        if (ep.mask) epilogue_rows_fast<false, false, true, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        else if (ep.bias && ep.relu) epilogue_rows_fast<true, true, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        else if (ep.bias) epilogue_rows_fast<true, false, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        else if (ep.relu) epilogue_rows_fast<false, true, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        else epilogue_rows_fast<false, false, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        return;
+    }
     if (ep.mask) epilogue_rows<false, false, true, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
     else if (ep.bias && ep.relu) epilogue_rows<true, true, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
     else if (ep.bias) epilogue_rows<true, false, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
@@ -383,6 +481,20 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int m0 = ((int) blockIdx.x / nslab) * BLOCK_M;
     const int num_kb = (R + BLOCK_R - 1) / BLOCK_R;
     if (threadIdx.x == 0) TRACE(0);
+    if (MINB == 2 && ep.sm_slots) {
+        // de-phase the two CTAs that share an SM: left alone they run in lockstep (both in the TMA-bound main loop, then
+        // both in the store-bound epilogue); started half a tile apart, one's epilogue runs under the other's main loop,
+        // and since a CTA's successor starts when it exits the offset persists for the rest of the grid
+        if (threadIdx.x == 0) {
+            unsigned smid;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+            if (atomicAdd(ep.sm_slots + smid, 1u) == 1u) {
+                const unsigned long long t0 = gtimer();
+                while (gtimer() - t0 < ep.stagger_ns) __nanosleep(256);
+            }
+        }
+        __syncthreads();
+    }
     constexpr int TMA_WARP = EW, MMA_WARP = EW + 1;
     const size_t pipe_bytes = pipe_region((size_t) nstages * stage_bytes, EW);
     PipeBars* bars = setup_cta(smem, pipe_bytes, nstages, tmem_cols, warp, TMA_WARP);
@@ -540,6 +652,160 @@ gemm_tn_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (threadIdx.x == TMA_WARP * 32) TRACE(6);
 }
 
+// ---- persistent CTA pairs with a double-buffered accumulator.  A cluster walks pair tiles (256 rows) cid, cid + n_clusters,
+// ...; each tile is nmma work units of n_each (<= 256) output columns, and unit u accumulates in TMEM columns
+// [(u & 1) * 256, +n_each), so the epilogue of unit u (8 warps per CTA: TMEM -> registers -> bias / ReLU / mask / round
+// -> coalesced stores) runs under the MMAs of unit u + 1.  Barriers, TMEM and the staged bias live for the whole
+// launch; the stage ring runs on across units, so the TMA warps are always a few k-blocks ahead of the MMA issuer.
+// Per k-block a CTA stages its 128 rows of A (16 KB) and n_each / 2 rows of B (the peer CTA holds the other half): A is
+// streamed once per unit, the second time from L2.  Why this shape: the one-tile-per-CTA kernels above run main loop
+// and epilogue back to back (tests/trace_gemm.py: 12 + 7.4 us per tile, in lockstep across the GPU), and an N = 400
+// fp32 accumulator fills 400 of the 512 TMEM columns, so only half-N units leave room for a second buffer.
+struct alignas(16) PairBars {      // sizeof % 16 == 0: the staged bias behind it is read with 128-bit loads
+    uint64_t full[6];
+    uint64_t empty[6];
+    uint64_t tmem_full[2];
+    uint64_t tmem_empty[2];
+    uint32_t tmem_base;
+    uint32_t pad[3];
+};
+static_assert(sizeof(PairBars) % 16 == 0, "PairBars must keep the bias 16-byte aligned");
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+constexpr size_t pair_persistent_smem(size_t stage_total, int ew) {
+    return stage_total + (size_t) ew * EPI_TILE_FLOATS * 4 + sizeof(PairBars) + SBIAS_BYTES + 1024;
+}
+
+// 128 registers per thread (not the 204 a lone 320-thread CTA could have): the CTA owns its SM for the whole launch, and
+// the side stream's id sort (radix scatter: 256 threads x 96 registers, 10 KB of shared memory) must still fit next to it,
+// or that work only runs in the gaps between GEMMs and lands on the step's critical path
+template <int EW>
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
+gemm_tn_pair_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N,
+                               int R, int n_each, int nmma, int nstages, float* __restrict__ C, int64_t ldc, EpiParams ep) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int cid = (int) blockIdx.x >> 1, ncl = (int) gridDim.x >> 1;
+    const int n_tiles = (M + 2 * BLOCK_M - 1) / (2 * BLOCK_M);
+    const int my_tiles = cid < n_tiles ? (n_tiles - cid + ncl - 1) / ncl : 0;
+    const uint32_t n_units = (uint32_t) (my_tiles * nmma);
+    const int n_half = n_each / 2;
+    const int a_bytes = BLOCK_M * BLOCK_R * 4;
+    const int b_bytes = n_half * BLOCK_R * 4;
+    const int stage_bytes = a_bytes + b_bytes;
+    const int num_kb = (R + BLOCK_R - 1) / BLOCK_R;
+    constexpr int TMA_WARP = EW, MMA_WARP = EW + 1;
+    constexpr uint32_t TMEM_COLS = 512, BUF_COLS = 256;
+    const size_t pipe_bytes = (size_t) nstages * stage_bytes;
+    float* estage = reinterpret_cast<float*>(smem + pipe_bytes);
+    PairBars* bars = reinterpret_cast<PairBars*>(smem + pipe_bytes + (size_t) EW * EPI_TILE_FLOATS * 4);
+    float* sbias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + sizeof(PairBars));
+    if (threadIdx.x == 0) TRACE(0);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < nstages; ++s) {
+            mbar_init(&bars->full[s], 1);
+            mbar_init(&bars->empty[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&bars->tmem_full[b], 1);
+            mbar_init(&bars->tmem_empty[b], 2 * EW);       // every epilogue warp of both CTAs
+        }
+        fence_barrier_init();
+    }
+    cluster_sync_all();                                      // both CTAs' barriers exist before anyone signals them
+    if (warp == TMA_WARP) tmem_alloc_pair(&bars->tmem_base, TMEM_COLS);
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+    if (threadIdx.x == 0) TRACE(1);
+
+    if (warp == TMA_WARP) {
+        if (elect_one()) {
+            prefetch_tmap(&tmA);
+            prefetch_tmap(&tmB);
+            uint32_t it = 0;
+            for (uint32_t u = 0; u < n_units; ++u) {
+                const int tile = cid + (int) (u / (uint32_t) nmma) * ncl, hh = (int) (u % (uint32_t) nmma);
+                const int m0 = (tile * 2 + (int) rank) * BLOCK_M;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = (int) (it % (uint32_t) nstages);
+                    const uint32_t ph = (it / (uint32_t) nstages) & 1u;
+                    mbar_wait(&bars->empty[s], ph ^ 1u);       // my copy of the stage is free (multicast commit)
+                    uint8_t* sa = smem + (size_t) s * stage_bytes;
+                    if (rank == 0) mbar_expect_tx(&bars->full[s], (uint32_t) (2 * stage_bytes));   // both CTAs' bytes
+                    const uint32_t lbar = mapa_shared(smem_u32(&bars->full[s]), 0);
+                    tma_load_2d_pair(sa, &tmA, lbar, kb * BLOCK_R, m0);
+                    tma_load_2d_pair(sa + a_bytes, &tmB, lbar, kb * BLOCK_R, hh * n_each + (int) rank * n_half);
+                }
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        if (rank == 0 && elect_one()) {
+            const uint32_t idesc = make_idesc(2 * BLOCK_M, n_each, 0, 0);
+            uint32_t it = 0;
+            for (uint32_t u = 0; u < n_units; ++u) {
+                const uint32_t buf = u & 1u, use = u >> 1;
+                mbar_wait(&bars->tmem_empty[buf], (use & 1u) ^ 1u);     // the unit that used this buffer has been read out
+                tc_fence_after();
+                TRACE_FINE(256 + 4 * (int) u);
+                const uint32_t acc = tmem_base + buf * BUF_COLS;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = (int) (it % (uint32_t) nstages);
+                    const uint32_t ph = (it / (uint32_t) nstages) & 1u;
+                    mbar_wait(&bars->full[s], ph);
+                    tc_fence_after();
+                    const uint32_t a_base = smem_u32(smem + (size_t) s * stage_bytes);
+                    const uint32_t b_base = a_base + a_bytes;
+#pragma unroll
+                    for (int k = 0; k < BLOCK_R / UMMA_K; ++k) {
+                        const uint64_t adesc = make_desc(a_base + k * UMMA_K * 4, 16, 8 * BLOCK_R * 4, LAYOUT_SW128);
+                        const uint64_t bdesc = make_desc(b_base + k * UMMA_K * 4, 16, 8 * BLOCK_R * 4, LAYOUT_SW128);
+                        umma_tf32_pair(acc, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                    }
+                    umma_commit_pair(&bars->empty[s]);     // frees the stage in BOTH CTAs
+                }
+                umma_commit_pair(&bars->tmem_full[buf]);   // this unit's accumulator is complete in both CTAs
+                TRACE_FINE(256 + 4 * (int) u + 1);
+            }
+            TRACE(2);
+        }
+    } else {
+        epilogue_prepare<EW>(0, M, N, ep, sbias);
+        const uint32_t empty0 = mapa_shared(smem_u32(&bars->tmem_empty[0]), 0);
+        const uint32_t empty1 = mapa_shared(smem_u32(&bars->tmem_empty[1]), 0);
+        for (uint32_t u = 0; u < n_units; ++u) {
+            const int tile = cid + (int) (u / (uint32_t) nmma) * ncl, hh = (int) (u % (uint32_t) nmma);
+            const int m0 = (tile * 2 + (int) rank) * BLOCK_M;
+            const uint32_t buf = u & 1u, use = u >> 1;
+            const int n0 = hh * n_each;
+            const int Nu = (N - n0) < n_each ? (N - n0) : n_each;       // columns of this unit
+            EpiParams epu = ep;
+            if (epu.mask) epu.mask += n0;
+            epu.col0 = n0;
+            mbar_wait(&bars->tmem_full[buf], use & 1u);
+            tc_fence_after();
+            if (threadIdx.x == 0) TRACE_FINE(256 + 4 * (int) u + 2);
+            if (Nu > 0)
+                epilogue_dispatch<EW>(tmem_base + buf * BUF_COLS, warp, lane, m0, M, Nu, C + n0, ldc, epu, estage,
+                                      smem_u32(sbias) + (uint32_t) (n0 * 4));
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(buf ? empty1 : empty0);
+            if (threadIdx.x == 0) TRACE_FINE(256 + 4 * (int) u + 3);
+        }
+        if (threadIdx.x == 0) TRACE(4);
+    }
+    tc_fence_before();
+    cluster_sync_all();                                   // neither CTA frees TMEM / exits while its peer still runs
+    if (threadIdx.x == 0) TRACE(5);
+    if (warp == TMA_WARP) tmem_dealloc_pair(tmem_base, TMEM_COLS);
+    if (threadIdx.x == TMA_WARP * 32) TRACE(6);
+}
+
 // ---- C_split[M,N] = A[R,M]^T * B[R,N] over this CTA's slice of R ; MN-major tf32 tiles (32B-atom swizzle)
 constexpr int NT_EW = 8;
 __global__ void __launch_bounds__(nthreads(NT_EW), 1)
@@ -608,7 +874,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (num_kb > 0) {
             mbar_wait(&bars->tmem_full, 0);
             tc_fence_after();
-            EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f, 0, 0, 0, 0, nullptr};
+            EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f, 0, 0, 0, 0, nullptr, nullptr, 0};
             epilogue_rows<false, false, false, EW>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem), 0u);
         } else {                                   // empty slice: contribute zeros
             const int row = m0 + (warp & 3) * 32 + lane;
@@ -691,13 +957,15 @@ unsigned long long* gemm_trace_buf() {
     return g_trace_buf;
 }
 
-// CTR_GEMM_MODE = split2 (default: two co-resident CTAs per SM, half-N slabs) | pair (cta_group::2) | single
+// CTR_GEMM_MODE = pp (default: persistent CTA pairs, double-buffered accumulator) | split2 (two co-resident half-N CTAs
+// per SM) | pair (one cta_group::2 tile per cluster) | single (one 128-row tile per CTA)
 int gemm_mode() {
     static int mode = -1;
     if (mode < 0) {
         const char* e = getenv("CTR_GEMM_MODE");
-        mode = 0;
-        if (e && e[0] == 'p') mode = 1;
+        mode = 3;
+        if (e && e[0] == 's' && e[1] == 'p') mode = 0;
+        if (e && e[0] == 'p' && e[1] == 'a') mode = 1;
         if (e && e[0] == 's' && e[1] == 'i') mode = 2;
     }
     return mode;
@@ -709,6 +977,35 @@ int launch_tn(ctr_handle* h, cudaStream_t st, int M, int N, int R, const float* 
     const int nmma = N > 256 ? 2 : 1;
     const int NB = nmma == 1 ? (int) ctr_align(N, 16) : (int) ctr_align(N, 32);
     const int n_each = NB / nmma;
+    // output columns [N, align4(N)) exist in C when ldc allows (pad columns of the activations / dX0): storing the zeros
+    // the accumulator holds there keeps every store a full 128-bit one (fast epilogue).  Not with a bias / mask, whose
+    // vectors end at N.
+    const int Ne = ((N & 3) && ldc >= ctr_align(N, 4) && !ep.bias && !ep.mask) ? (int) ctr_align(N, 4) : N;
+    if (gemm_mode() == 3 && M > BLOCK_M) {
+        // persistent CTA pairs, double-buffered accumulator (see gemm_tn_pair_persistent_kernel)
+        const int n_half = n_each / 2;
+        const int stage_bytes = BLOCK_M * BLOCK_R * 4 + n_half * BLOCK_R * 4;
+        int nstages = (int) ((SMEM_LIMIT - 1024 - SBIAS_BYTES - sizeof(PairBars) - 8 * EPI_TILE_FLOATS * 4) / stage_bytes);
+        if (nstages > 6) nstages = 6;
+        CTR_REQUIRE(h, nstages >= 2, "TF32 path: tile does not fit shared memory");
+        CUtensorMap tmA, tmB;
+        int rc = make_map(h, &tmA, A, M, R, lda, BLOCK_R, BLOCK_M, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc) return rc;
+        rc = make_map(h, &tmB, B, N, R, ldb, BLOCK_R, n_half, CU_TENSOR_MAP_SWIZZLE_128B);
+        if (rc) return rc;
+        const size_t smem = pair_persistent_smem((size_t) nstages * stage_bytes, 8);
+        static bool attr_set3 = false;
+        if (!attr_set3) {
+            CTR_CUDA(h, cudaFuncSetAttribute(gemm_tn_pair_persistent_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+            attr_set3 = true;
+        }
+        const int n_tiles = (int) ctr_cdiv(M, 2 * BLOCK_M);
+        const int max_cl = h->sm_count / 2;
+        const unsigned ctas = 2u * (unsigned) (n_tiles < max_cl ? n_tiles : max_cl);
+        gemm_tn_pair_persistent_kernel<8><<<ctas, nthreads(8), smem, st>>>(tmA, tmB, M, Ne, R, n_each, nmma, nstages, C, ldc, ep);
+        CTR_CHECK_LAUNCH(h, "gemm_tn_pair_persistent_kernel");
+        return CTR_OK;
+    }
     if (gemm_mode() == 1 && M > BLOCK_M) {
         // CTA pairs: each CTA stages 128 rows of A and half of B per k-block
         const int n_half = n_each / 2;
@@ -727,7 +1024,7 @@ int launch_tn(ctr_handle* h, cudaStream_t st, int M, int N, int R, const float* 
             attr_set2 = true;
         }
         const unsigned ctas = (unsigned) ctr_align(ctr_cdiv(M, BLOCK_M), 2);
-        gemm_tn_pair_kernel<8><<<ctas, nthreads(8), smem, st>>>(tmA, tmB, M, N, R, n_each, nmma, nstages, tmem_cols_for(NB), C,
+        gemm_tn_pair_kernel<8><<<ctas, nthreads(8), smem, st>>>(tmA, tmB, M, Ne, R, n_each, nmma, nstages, tmem_cols_for(NB), C,
                                                              ldc, ep);
         CTR_CHECK_LAUNCH(h, "gemm_tn_pair_kernel");
         return CTR_OK;
@@ -752,8 +1049,21 @@ int launch_tn(ctr_handle* h, cudaStream_t st, int M, int N, int R, const float* 
         if (nstages > 4) nstages = 4;
         const size_t smem = smem_total((size_t) nstages * slab_stage, 8);
         const unsigned grid = (unsigned) (ctr_cdiv(M, BLOCK_M) * nmma);
-        gemm_tn_kernel<2, 8><<<grid, nthreads(8), smem, st>>>(tmA, tmB, M, N, R, n_each, 1, nmma, nstages, tmem_cols_for(n_each), C,
-                                                           ldc, ep);
+        static int stagger = -1;
+        static unsigned* slots = nullptr;
+        if (stagger < 0) {
+            const char* e = getenv("CTR_GEMM_STAGGER_NS");
+            stagger = e ? atoi(e) : 0;
+            if (stagger > 0) CTR_CUDA(h, cudaMalloc(&slots, 1024 * sizeof(unsigned)));
+        }
+        EpiParams ep2 = ep;
+        if (stagger > 0) {
+            CTR_CUDA(h, cudaMemsetAsync(slots, 0, 1024 * sizeof(unsigned), st));
+            ep2.sm_slots = slots;
+            ep2.stagger_ns = (unsigned) stagger;
+        }
+        gemm_tn_kernel<2, 8><<<grid, nthreads(8), smem, st>>>(tmA, tmB, M, Ne, R, n_each, 1, nmma, nstages, tmem_cols_for(n_each), C,
+                                                           ldc, ep2);
         CTR_CHECK_LAUNCH(h, "gemm_tn_kernel<2>");
         return CTR_OK;
     }
@@ -761,7 +1071,7 @@ int launch_tn(ctr_handle* h, cudaStream_t st, int M, int N, int R, const float* 
     const int nstages = pick_stages(stage_bytes);
     CTR_REQUIRE(h, nstages >= 2, "TF32 path: tile does not fit shared memory");
     const size_t smem = smem_total((size_t) nstages * stage_bytes, 8);
-    gemm_tn_kernel<1, 8><<<(unsigned) ctr_cdiv(M, BLOCK_M), nthreads(8), smem, st>>>(tmA, tmB, M, N, R, n_each, nmma, 1, nstages,
+    gemm_tn_kernel<1, 8><<<(unsigned) ctr_cdiv(M, BLOCK_M), nthreads(8), smem, st>>>(tmA, tmB, M, Ne, R, n_each, nmma, 1, nstages,
                                                                                  tmem_cols_for(NB), C, ldc, ep);
     CTR_CHECK_LAUNCH(h, "gemm_tn_kernel");
     return CTR_OK;
@@ -808,14 +1118,14 @@ __global__ void __launch_bounds__(256) tc_splitk_reduce(const float* __restrict_
 int ctr_tc_mlp_fwd(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* X, int64_t ldx, const float* Wt,
                    const float* bias, int relu, float keep, uint64_t seed, float* Y, int64_t ldy) {
     // Wt is the K-major copy [N, ldwt] with ldwt = K rounded up to 4 floats (TMA needs 16-byte row pitches)
-    EpiParams ep{bias, relu, keep, seed, nullptr, 0, 1.f, 1, 0, N, gemm_dbg(), gemm_trace_buf()};
+    EpiParams ep{bias, relu, keep, seed, nullptr, 0, 1.f, 1, 0, N, gemm_dbg(), gemm_trace_buf(), nullptr, 0};
     return launch_tn(h, st, B, N, K, X, ldx, Wt, ctr_align(K, 4), Y, ldy, ep);
 }
 
 int ctr_tc_mlp_bwd_data(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* dZ, int64_t lddz,
                         const float* W, const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx) {
     // dX[B,K] = dZ[B,N] * W[K,N]^T : W is already reduction-major for this product
-    EpiParams ep{nullptr, 0, 1.f, 0, mask, ldmask, mask_scale, 1, 0, K, gemm_dbg(), gemm_trace_buf()};
+    EpiParams ep{nullptr, 0, 1.f, 0, mask, ldmask, mask_scale, 1, 0, K, gemm_dbg(), gemm_trace_buf(), nullptr, 0};
     return launch_tn(h, st, B, K, N, dZ, lddz, W, N, dX, lddx, ep);
 }
 

@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_phase1(F f, int64_t n, uint
 }
 
 // single block: exclusive scan of blk[0..nblk) in place, grand total to *total_out (and blk[nblk])
-__global__ void __launch_bounds__(1024) scan_phase2(uint32_t* __restrict__ blk, int nblk, uint32_t* __restrict__ total_out) {
+__global__ void __maxnreg__(24) scan_phase2(uint32_t* __restrict__ blk, int nblk, uint32_t* __restrict__ total_out) {
     __shared__ uint32_t sm[33];
     uint32_t carry = 0;
     for (int i0 = 0; i0 < nblk; i0 += 1024) {

@@ -46,3 +46,9 @@ print("block 0 MMA issuer saw a full stage at (us):", np.round(mma, 2))
 ep0 = fine[128:128 + 64].reshape(-1, 4)[:, :2]
 ep0 = ep0[ep0[:, 0] > 0]
 print("block 0 epilogue warp 0, per chunk [ldtm done, chunk done] (us):", np.round((ep0 - base) / 1e3, 2).tolist())
+# global phase picture: how many CTAs are in the main loop / in the epilogue at each instant
+T = (t[:, 6].max() - t0) / 1e3
+grid_t = np.linspace(0, T, 41)
+ml = [(int(np.sum((t[:, 1] - t0 <= x * 1e3) & (t[:, 2] - t0 > x * 1e3))), int(np.sum((t[:, 3] - t0 <= x * 1e3) & (t[:, 4] - t0 > x * 1e3)))) for x in grid_t]
+print("time(us): CTAs in main loop / in epilogue")
+print("  ".join("%.0f:%d/%d" % (x, a, b) for x, (a, b) in zip(grid_t, ml)))
