@@ -155,7 +155,10 @@ def main():
     hp = hparams(B, R)
     spec = spec_from_hparams("deepfm", hp)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = os.environ.get("CTR_NCCL_DEBUG", "WARN")     # keep stdout to the one JSON line
+        # keep stdout to the one JSON line: NCCL prints its version banner there at VERSION level and above
+        os.environ.pop("NCCL_DEBUG", None)
+        if os.environ.get("CTR_NCCL_DEBUG"):
+            os.environ["NCCL_DEBUG"] = os.environ["CTR_NCCL_DEBUG"]
         # configs[3]: the ~1e8-row tables row-sharded over the ranks (owner = id mod N), B samples per GPU (weak scaling)
         dist.init_process_group("nccl", device_id=dev)
         from deep_learning_b200.sharded import ShardedCtrEngine

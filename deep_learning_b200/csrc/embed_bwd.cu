@@ -143,16 +143,56 @@ __device__ __forceinline__ float sum_run_partials(const float* __restrict__ part
     return (a0 + a1) + (a2 + a3);
 }
 
+// grads[u, :width] = sum of the partial rows of run u, in chunk order.  One thread per (run, 4 columns) with 128-bit
+// accesses; a run spread over more than LONG_RUN chunks (a hot row: thousands of lookups) is summed by the whole warp
+// -- lane l takes partial rows l, l + 32, ..., then a fixed shuffle tree -- so one thread never walks hundreds of rows.
 __global__ void __launch_bounds__(256)
 embed_bwd_finalize_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ n_unique, int64_t n_max,
                           int width, int gs, const float* __restrict__ part, float* __restrict__ grads) {
     int64_t U = *n_unique;
     if (U > n_max) U = n_max;
-    const int64_t total = U * width;
-    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
-        const int64_t u = t / width;
-        const int j = (int) (t - u * width);
-        grads[u * gs + j] = sum_run_partials(part, seg_start, u, j, gs);
+    const int nq = (width + 3) >> 2;                 // column quads per row
+    const int64_t total = U * nq;
+    const int lane = threadIdx.x & 31;
+    const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+    for (int64_t t0 = (int64_t) blockIdx.x * blockDim.x + (threadIdx.x & ~31); t0 < total; t0 += stride) {   // warp-uniform
+        const int64_t t = t0 + lane;
+        const bool valid = t < total;
+        const int64_t u = valid ? t / nq : 0;
+        const int q = valid ? (int) (t - u * nq) : 0;
+        int64_t c0 = 0, np = 0;
+        if (valid) {
+            const uint32_t s0 = __ldg(seg_start + u), s1 = __ldg(seg_start + u + 1);
+            c0 = s0 / CH;
+            np = (int64_t) ((s1 - 1) / CH) - c0 + 1;
+        }
+        const bool lng = valid && np > LONG_RUN;
+        if (valid && !lng) {
+            const float* p = part + (u + c0) * gs + q * 4;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int64_t i = 0; i < np; ++i) {
+                const float4 x = __ldg(reinterpret_cast<const float4*>(p + i * gs));
+                a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+            }
+            *reinterpret_cast<float4*>(grads + u * gs + q * 4) = a;
+        }
+        unsigned todo = __ballot_sync(0xffffffffu, lng && q == 0);     // the run's first quad leads
+        while (todo) {
+            const int l = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const int64_t uu = __shfl_sync(0xffffffffu, u, l), cc = __shfl_sync(0xffffffffu, c0, l), nn = __shfl_sync(0xffffffffu, np, l);
+            const float4* base = reinterpret_cast<const float4*>(part + (uu + cc) * gs);
+            const int gs4 = gs >> 2;
+            for (int qq = 0; qq < nq; ++qq) {
+                float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int64_t i = lane; i < nn; i += 32) {
+                    const float4 x = __ldg(base + i * gs4 + qq);
+                    a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+                }
+                a.x = ctr_warp_sum(a.x); a.y = ctr_warp_sum(a.y); a.z = ctr_warp_sum(a.z); a.w = ctr_warp_sum(a.w);
+                if (lane == 0) *reinterpret_cast<float4*>(grads + uu * gs + qq * 4) = a;
+            }
+        }
     }
 }
 
@@ -550,8 +590,10 @@ extern "C" int ctr_embed_bwd_finalize(ctr_handle* h, ctr_stream s, const uint32_
     CTR_REQUIRE(h, seg_start && n_unique && part && grads && width > 0 && grad_stride >= width && n_max >= 0,
                 "embed_bwd_finalize: bad args");
     if (n_max == 0) return CTR_OK;
-    embed_bwd_finalize_kernel<<<grid_for(h, n_max * width), 256, 0, ctr_st(s)>>>(seg_start, n_unique, n_max, width,
-                                                                                  grad_stride, part, grads);
+    CTR_REQUIRE(h, grad_stride % 4 == 0 && ((reinterpret_cast<uintptr_t>(part) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0,
+                "embed_bwd_finalize: grad_stride must be a multiple of 4 and part / grads 16-byte aligned");
+    embed_bwd_finalize_kernel<<<grid_for(h, n_max * ((width + 3) / 4)), 256, 0, ctr_st(s)>>>(seg_start, n_unique, n_max, width,
+                                                                                              grad_stride, part, grads);
     CTR_CHECK_LAUNCH(h, "embed_bwd_finalize");
     return CTR_OK;
 }

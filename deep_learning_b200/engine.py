@@ -170,6 +170,14 @@ class CtrEngine:
     def _stream(self) -> int:
         return torch.cuda.current_stream(self.dev).cuda_stream
 
+    phase_marks = None     # list of (name, event) when a timing script asks for the main-stream phase picture
+
+    def _mark(self, name: str) -> None:
+        if self.phase_marks is not None:
+            ev = torch.cuda.Event(enable_timing=True)
+            ev.record(torch.cuda.current_stream(self.dev))
+            self.phase_marks.append((name, ev))
+
     def view(self, name: str, buf: Optional[torch.Tensor] = None) -> torch.Tensor:
         """flat-buffer view of a dense parameter (internal layout)"""
         buf = self.theta if buf is None else buf
@@ -375,12 +383,14 @@ class CtrEngine:
     def forward(self, B: int, with_loss: bool) -> None:
         s, st, h = self.spec, self._stream(), self.h
         self._embed_forward(B)
+        self._mark("embed")
         x, ldx = self.x0, s.x0_ld
         for i, (k_, h_) in enumerate(self._layer_dims()):
             h.call("ctr_mlp_fwd", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self._w(i)),
                    ptr(self.wt[i]) if self.wt is not None else None, ptr(self._b(i)), 1, 1.0, 0, ptr(self.acts[i]), self.act_ld[i])
             x, ldx = self.acts[i], self.act_ld[i]
         w_fm, w_deep, bias = self._head_parts()
+        self._mark("mlp_fwd")
         extra = None
         if s.head == "wdl":
             h.call("ctr_scalar_gather_sum", st, ptr(self.view("wdl_weights")), ptr(self.wide), self.id_bytes, B,
@@ -453,18 +463,23 @@ class CtrEngine:
                 h.call("ctr_mlp_bwd_data", st, self.prec, B, s.E, h_, ptr(self.dz[cur]), h_, ptr(self._wd(0)), None, 0,
                        1.0, ptr(self.dx0), self.dx0_ld)
         hp = self._adam_hp()
+        self._mark("mlp_bwd")
         # ---- sparse side: sort -> runs -> partials -> Adam on touched rows ------------------------------
         if s.ids_ld:
             n = B * s.ids_ld + self.n_extra
             torch.cuda.current_stream(self.dev).wait_event(self.ev_sorted)
+            self._mark("wait_sort")
             if self.n_extra:
                 h.call("ctr_fm_cont_bwd", st, cfg, ptr(self.cont), ptr(self._cont_rows()), ptr(self.sum_e),
                        ptr(self.dlogit), ptr(w_fm), ptr(self.cont_grad), ws, wsn)
             h.call("ctr_embed_bwd_partials", st, cfg, ptr(self.keys), ptr(self.perm), ptr(self.uidx), n,
                    ptr(self.field_of_slot), ptr(self.x0), ptr(self.dx0), self.dx0_ld, ptr(self.sum_e), ptr(self.dlogit),
                    ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.part))
+            self._mark("partials")
             self._sparse_update(B, n, hp)
+            self._mark("sparse_update")
         self._reduce_dense_grads()
+        self._mark("dense_reduce")
         if self.adam_mode == "tf_dense":
             # TF1 Adam moves EVERY row each step (m, v decay; theta -= lr_t*m/(sqrt(v)+eps)) -- exact mode
             h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
@@ -550,27 +565,38 @@ class CtrEngine:
         de-duplication and id exchange of step i+1 off the critical path of step i."""
         if not self.train_mode:
             raise _lib.CtrError("engine was created with train=False")
+        self._mark("start")
+        ev_call = None
+        if next_batch is not None:
+            # whatever produced `next_batch` was enqueued before this call: work on other streams that reads it waits
+            # for this point of the main stream and no later one
+            ev_call = torch.cuda.Event()
+            ev_call.record(torch.cuda.current_stream(self.dev))
         B = self.load_batch(batch) if batch is not None else self.last_batch
         self._launch_sort(B)
+        self._mark("load")
         self.forward(B, with_loss=True)
-        self._after_forward(next_batch)
+        self._mark("head")
+        # queued from the host only now, with the whole forward already in the main stream's queue (the launches of the
+        # prefetch would otherwise sit between this step's upload and its first kernel); it still STARTS early, since
+        # it waits for ev_call and not for the forward
+        self._prefetch_next(next_batch, ev_call)
         reg = self._reg_loss()
         self.backward_and_update(B)
         loss = self._global_loss()
         self._end_step()
+        self._mark("update")
         return loss if reg is None else loss + reg
 
-    def _after_forward(self, next_batch: Optional[Dict]) -> None:
-        """work for the next step that overlaps this step's backward: upload the next batch into the other input set"""
+    def _prefetch_next(self, next_batch: Optional[Dict], ev_call) -> None:
+        """work for the next step that runs under this one: upload the next batch into the other input set"""
         if next_batch is None:
             return
         other = 1 - self._cur_in
         cs = self.copy_stream
         if self._in_used[other]:
             cs.wait_event(self._in_free[other])        # the step that last read that set has finished
-        ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream(self.dev))
-        cs.wait_event(ev)                              # a device-resident batch may still be in production upstream
+        cs.wait_event(ev_call)                         # a device-resident batch may still be in production upstream
         with torch.cuda.stream(cs):
             self._pf_B = self._copy_inputs(next_batch, self._in[other], True, self._ids_external)
         self._pf_event.record(cs)

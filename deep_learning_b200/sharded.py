@@ -69,6 +69,10 @@ class ShardedCtrEngine(CtrEngine):
             raise RuntimeError("ShardedCtrEngine needs an initialised torch.distributed process group")
         self.group = group
         world, rank = dist.get_world_size(group), dist.get_rank(group)
+        # the id plans of step i+1 are built under step i on a side stream: their collectives get a communicator of their
+        # own, or they would queue in front of step i's vector / gradient exchanges (one communicator = one FIFO)
+        ranks = dist.get_process_group_ranks(group) if group is not None else list(range(dist.get_world_size()))
+        self.group_plan = dist.new_group(ranks=ranks) if world > 1 else group
         self.plan = _shard.ShardPlan(spec.table_rows, world)
         self.wire = spec.grad_stride          # floats per row on the wire (k [+1], rounded up to 4): vectors and gradients
         super().__init__(spec, max_batch, world=world, rank=rank, **kw)
@@ -141,7 +145,7 @@ class ShardedCtrEngine(CtrEngine):
         h.call("ctr_invert_perm", st, ptr(pl.perm), ptr(pl.uidx), n, ptr(pl.inv))
         with torch.cuda.stream(stream):
             send = pl.counts.to(torch.int64)
-            recv = _shard.exchange_counts(send, self.group)           # all-to-all #1a
+            recv = _shard.exchange_counts(send, self.group_plan)      # all-to-all #1a
             pl.counts_host.copy_(torch.stack([send, recv]), non_blocking=True)
             pl.ev_local.record(stream)
         pl.B = B
@@ -157,7 +161,7 @@ class ShardedCtrEngine(CtrEngine):
         pl.ensure_owner(self, pl.n_req)
         n_req, st = pl.n_req, stream.cuda_stream
         with torch.cuda.stream(stream):
-            _shard.exchange(pl.uniq[:pl.U], pl.send_counts, pl.recv_counts, out=pl.req, group=self.group)   # #1b
+            _shard.exchange(pl.uniq[:pl.U], pl.send_counts, pl.recv_counts, out=pl.req, group=self.group_plan)   # #1b
             if self.train_mode and n_req:
                 pl.o_keys[:n_req].copy_(pl.req[:n_req])
                 torch.arange(n_req, out=pl.o_idx[:n_req])
@@ -208,9 +212,9 @@ class ShardedCtrEngine(CtrEngine):
 
     _pending_exchange: Optional[_IdPlan] = None
 
-    def _after_forward(self, next_batch: Optional[Dict]) -> None:
+    def _prefetch_next(self, next_batch: Optional[Dict], ev_call) -> None:
         """start the id plan of the next batch on the side stream (upload ids, sort, de-dup, counts all-to-all)"""
-        super()._after_forward(next_batch)         # non-id inputs: upload into the other input set
+        super()._prefetch_next(next_batch, ev_call)         # non-id inputs: upload into the other input set
         if next_batch is None or not self.spec.ids_ld:
             return
         pl = self._other_plan()
@@ -220,11 +224,8 @@ class ShardedCtrEngine(CtrEngine):
         if not isinstance(cate, torch.Tensor):
             cate = torch.as_tensor(np.asarray(cate))
         B = int(cate.shape[0])
-        main = torch.cuda.current_stream(self.dev)
         self.side.wait_event(pl.ev_free) if pl.batch_id is not None else None
-        ev = torch.cuda.Event()
-        ev.record(main)
-        self.side.wait_event(ev)                  # a device-resident batch may still be in production on the main stream
+        self.side.wait_event(ev_call)             # a device-resident batch may still be in production on the main stream
         with torch.cuda.stream(self.side):
             pl.ids[:B].copy_(cate.to(self.id_torch) if cate.dtype != self.id_torch else cate, non_blocking=True)
         self._build_local(pl, B, self.side)
@@ -248,12 +249,15 @@ class ShardedCtrEngine(CtrEngine):
         if pl.on_side:
             main.wait_event(pl.ev_ready)
         U, n_req = pl.U, pl.n_req
+        self._mark("wait_plan")
         self._ensure_rows(n_req)
         # owners gather [v | w] rows; all-to-all #2 returns them in the requester's unique-list order
         if n_req:
             h.call("ctr_gather_rows", st, ptr(self.table), s.table_stride, ptr(pl.req), None, n_req, sp.local_bits,
                    s.row_width, ptr(self.rows_send), self.wire)
+        self._mark("owner_gather")
         _shard.exchange(self.rows_send[:n_req], pl.recv_counts, pl.send_counts, out=self.rows_recv, group=self.group)
+        self._mark("a2a_vectors")
         self.rows_recv[U].zero_()    # the run of padding ids (key 0xFFFFFFFF), if any, is unique index U
         if s.use_fm and s.fm_cont and s.C:
             h.call("ctr_gather_rows", st, ptr(self.rows_recv), self.wire, ptr(pl.inv[B * s.ids_ld:]), None, s.C, 0,
@@ -268,16 +272,20 @@ class ShardedCtrEngine(CtrEngine):
     # ---- backward: per-unique gradients -> all-to-all #3 -> owner sum in peer order -> Adam ------------------------
     def _sparse_update(self, B: int, n: int, hp: AdamHP) -> None:
         s, st, h, sp, pl = self.spec, self._stream(), self.h, self.plan, self.cur
+        # The second half of the next batch's id plan (key all-to-all, owner-side sort) needs its split sizes on the
+        # host.  By now the whole forward + dense backward of THIS step is queued on the main stream, so the host wait
+        # does not starve the GPU.  The position is fixed on purpose: the plan collectives run on their own
+        # communicator, and two communicators are only safe if every rank issues all collectives in one global order
+        # (polling for "sizes ready" made that order rank-dependent and deadlocked).
         if self._pending_exchange is not None:
-            # by now the whole forward + dense backward of THIS step is queued on the main stream, so the host read
-            # of the next plan's split sizes does not starve the GPU; its key all-to-all precedes this step's
-            # gradient all-to-all on every rank (fixed collective order)
             self._build_exchange(self._pending_exchange, self.side)
             self._pending_exchange = None
         U, n_req = pl.U, pl.n_req
         h.call("ctr_embed_bwd_finalize", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
                ptr(self.part), ptr(self.grads_send))
+        self._mark("finalize")
         _shard.exchange(self.grads_send[:U], pl.send_counts, pl.recv_counts, out=self.g_recv, group=self.group)
+        self._mark("a2a_grads")
         if not n_req:
             return
         h.call("ctr_segment_sum_rows", st, ptr(pl.o_seg), ptr(pl.o_nuniq), n_req, ptr(pl.o_idx), ptr(self.g_recv),
