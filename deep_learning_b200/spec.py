@@ -183,6 +183,22 @@ def spec_from_hparams(alg: str, hp) -> ModelSpec:
                          k=k, hidden=H, table_rows=int(hp.cate_feats_size), emb_name="feats_emb", first_name=None,
                          zero_row0=True, multi_ranges=_ranges(hp), head="dnn", l2_reg=l2,
                          reg={"deep_res": "l2"}, id_dtype="int64")
+    # ---- the variants local_run_test.py dispatches: the same kernels, other field mixes
+    if alg in ("deepfm_cate", "deepfm_multi_cate"):
+        # models/deepfm_cate.py:72-171, models/deepfm_multi_cate.py:113-223: no continuous block, row-0-zero tables
+        return ModelSpec(alg, C=0, V=int(hp.vector_feats_size), Fc=int(hp.cate_field_size), k=k, hidden=H,
+                         table_rows=int(hp.cate_feats_size), emb_name="feats_emb", first_name="fm_first_order_emb",
+                         use_fm=True, fm_cont=False, zero_row0=True, cont_base=int(hp.cate_feats_size),
+                         multi_ranges=_ranges(hp) if alg == "deepfm_multi_cate" else [], head="deepfm",
+                         head_w_name="deep_fm_weight", head_b_name="deep_fm_bias", first_order_ref="cont_single_multi",
+                         l2_reg=l2, reg={"deep_fm_weight": "l2"}, id_dtype="int64")
+    if alg in ("dnn_pipeline", "dnn_cate", "dnn_multi_cate"):
+        # models/dnn_pipeline.py:68-122, models/dnn_cate.py:62-115, models/dnn_multi_cate.py:64-147
+        C = int(hp.cont_field_size) if alg == "dnn_pipeline" else 0
+        return ModelSpec(alg, C=C, V=int(hp.vector_feats_size), Fc=int(hp.cate_field_size), k=k, hidden=H,
+                         table_rows=int(hp.cate_feats_size), emb_name="feats_emb", first_name=None, zero_row0=True,
+                         multi_ranges=_ranges(hp) if alg == "dnn_multi_cate" else [], head="dnn", l2_reg=l2,
+                         reg={"deep_res": "l2"}, id_dtype="int64")
     if alg == "wdl":
         reg = {"deep_%d" % i: "l2" for i in range(len(H))}
         reg["wdl_weights"] = "l2"

@@ -314,10 +314,110 @@ def dnn_multi_loss(p, batch, hp: HParams):
     return loss, out, score
 
 
+# ---- the variants local_run_test.py dispatches: restated from their own files, not derived from
+# the functions above, so that the "same math, different field mix" claim is itself checked by the parity tests
+def deepfm_cate_forward(p, batch, hp: HParams):
+    """models/deepfm_cate.py:72-171: categorical fields only (value 1), row-0-zero tables, deep input [vector | emb]."""
+    Fc, k = hp.cate_field_size, hp.embedding_size
+    cate, vec = batch['cate_feats'].long()[:, :Fc], batch['vector_feats']
+    B = cate.shape[0]
+    feats_emb = zero_row0(p['feats_emb'])                                    # :79-80
+    fm_first = zero_row0(p['fm_first_order_emb'])                            # :81-82
+    first = embedding_lookup(fm_first, cate).reshape(B, Fc)                  # :90-92 (times ones)
+    e = embedding_lookup(feats_emb, cate)                                    # :97-99
+    sum_e = e.sum(1)
+    second = 0.5 * (sum_e * sum_e - (e * e).sum(1))                          # :100-104
+    fm_res = torch.cat([first, second], dim=1)                               # :109
+    cat_emb = embedding_lookup(feats_emb, cate).reshape(B, Fc * k)           # :115-116
+    dense_vector = torch.cat([vec, cat_emb], dim=1)                          # :118
+    deep = mlp_tower(dense_vector, p, len(hp.hidden_units))                  # :143-148
+    feats_input = torch.cat([fm_res, deep], dim=1)                           # :152-153
+    out = feats_input @ p['deep_fm_weight'] + p['deep_fm_bias']              # :166
+    return out, torch.sigmoid(out)
+
+
+def deepfm_multi_cate_forward(p, batch, hp: HParams):
+    """models/deepfm_multi_cate.py:113-223: single + pooled multi-valued categorical fields, no continuous block."""
+    Fc, k, Fm = hp.cate_field_size, hp.embedding_size, hp.multi_field_size
+    cate, vec = batch['cate_feats'].long(), batch['vector_feats']
+    B = cate.shape[0]
+    single, multi = cate[:, :Fc], cate[:, Fc:]
+    feats_emb = zero_row0(p['feats_emb'])
+    fm_first = zero_row0(p['fm_first_order_emb'])
+    all_first_multi, all_multi = _multi_cate_emb(fm_first, feats_emb, multi, hp.multi_feats_range)   # :71-111
+    first = torch.cat([embedding_lookup(fm_first, single).reshape(B, Fc), all_first_multi], dim=1)
+    e = torch.cat([embedding_lookup(feats_emb, single), all_multi.reshape(B, Fm, k)], dim=1)
+    sum_e = e.sum(1)
+    second = 0.5 * (sum_e * sum_e - (e * e).sum(1))
+    fm_res = torch.cat([first, second], dim=1)
+    single_emb = embedding_lookup(feats_emb, single).reshape(B, Fc * k)
+    dense_vector = torch.cat([vec, single_emb, all_multi], dim=1)            # :169
+    deep = mlp_tower(dense_vector, p, len(hp.hidden_units))
+    out = torch.cat([fm_res, deep], dim=1) @ p['deep_fm_weight'] + p['deep_fm_bias']
+    return out, torch.sigmoid(out)
+
+
+def _deepfm_variant_loss(fwd):
+    def loss_fn(p, batch, hp: HParams):
+        """log-loss + l2 on deep_fm_weight (models/deepfm_cate.py:174-180, models/deepfm_multi_cate.py:226-232)"""
+        out, score = fwd(p, batch, hp)
+        loss = log_loss(batch['label'], score)
+        if hp.l2_reg > 0:
+            loss = loss + l2_regularizer(hp.l2_reg, p['deep_fm_weight'])
+        return loss, out, score
+    return loss_fn
+
+
+def dnn_pipeline_forward(p, batch, hp: HParams):
+    """models/dnn_pipeline.py:68-122 (with cont_field_size = 0: models/dnn_cate.py:62-115)."""
+    Fc, k = hp.cate_field_size, hp.embedding_size
+    cate, cont, vec = batch['cate_feats'].long()[:, :Fc], batch['cont_feats'], batch['vector_feats']
+    B = cate.shape[0]
+    feats_emb = zero_row0(p['feats_emb'])                                    # dnn_pipeline.py:72-73
+    cat_emb = embedding_lookup(feats_emb, cate).reshape(B, Fc * k)           # :78-79
+    dense_vector = torch.cat([cont, vec, cat_emb], dim=1)                    # :82 ([vector | emb] in dnn_cate.py:75)
+    deep = mlp_tower(dense_vector, p, len(hp.hidden_units))
+    out = deep @ p['deep_res'] + p['deep_res_bias']                          # :119
+    return out, torch.sigmoid(out)
+
+
+def dnn_multi_cate_forward(p, batch, hp: HParams):
+    """models/dnn_multi_cate.py:64-147."""
+    Fc, k = hp.cate_field_size, hp.embedding_size
+    cate, vec = batch['cate_feats'].long(), batch['vector_feats']
+    B = cate.shape[0]
+    feats_emb = zero_row0(p['feats_emb'])
+    cate_emb = embedding_lookup(feats_emb, cate[:, :Fc]).reshape(B, Fc * k)
+    _, all_multi = _multi_cate_emb(None, feats_emb, cate[:, Fc:], hp.multi_feats_range)
+    dense_vector = torch.cat([vec, cate_emb, all_multi], dim=1)              # :103
+    deep = mlp_tower(dense_vector, p, len(hp.hidden_units))
+    out = deep @ p['deep_res'] + p['deep_res_bias']                          # :144
+    return out, torch.sigmoid(out)
+
+
+def _dnn_variant_loss(fwd):
+    def loss_fn(p, batch, hp: HParams):
+        """log-loss + l2 on deep_res (models/dnn_pipeline.py:125-131, dnn_cate.py:118-124, dnn_multi_cate.py:150-156)"""
+        out, score = fwd(p, batch, hp)
+        loss = log_loss(batch['label'], score)
+        if hp.l2_reg > 0:
+            loss = loss + l2_regularizer(hp.l2_reg, p['deep_res'])
+        return loss, out, score
+    return loss_fn
+
+
 FORWARD = {'deepfm': deepfm_forward, 'deepfm_multi': deepfm_multi_forward, 'wdl': wdl_forward,
-           'dnn': dnn_forward, 'dnn_multi': dnn_multi_forward}
+           'dnn': dnn_forward, 'dnn_multi': dnn_multi_forward,
+           'deepfm_cate': deepfm_cate_forward, 'deepfm_multi_cate': deepfm_multi_cate_forward,
+           'dnn_pipeline': dnn_pipeline_forward, 'dnn_cate': dnn_pipeline_forward, 'dnn_multi_cate': dnn_multi_cate_forward}
 LOSS = {'deepfm': deepfm_loss, 'deepfm_multi': deepfm_multi_loss, 'wdl': wdl_loss,
-        'dnn': dnn_loss, 'dnn_multi': dnn_multi_loss}
+        'dnn': dnn_loss, 'dnn_multi': dnn_multi_loss,
+        'deepfm_cate': _deepfm_variant_loss(deepfm_cate_forward),
+        'deepfm_multi_cate': _deepfm_variant_loss(deepfm_multi_cate_forward),
+        'dnn_pipeline': _dnn_variant_loss(dnn_pipeline_forward), 'dnn_cate': _dnn_variant_loss(dnn_pipeline_forward),
+        'dnn_multi_cate': _dnn_variant_loss(dnn_multi_cate_forward)}
+# variants without a continuous block read cont_field_size as 0 (their model files never define it)
+NO_CONT = ('deepfm_cate', 'deepfm_multi_cate', 'dnn_cate', 'dnn_multi_cate')
 
 
 # --------------------------------------------------------------------------------------
@@ -331,6 +431,12 @@ def deep_input_size(alg: str, hp: HParams) -> int:
         return hp.cont_field_size + hp.vector_feats_size + hp.cate_field_size * k
     if alg in ('deepfm_multi', 'dnn_multi'):
         return hp.cont_field_size + hp.vector_feats_size + (hp.cate_field_size + hp.multi_field_size) * k
+    if alg in ('deepfm_multi_cate', 'dnn_multi_cate'):
+        return hp.vector_feats_size + (hp.cate_field_size + hp.multi_field_size) * k
+    if alg in ('deepfm_cate', 'dnn_cate'):
+        return hp.vector_feats_size + hp.cate_field_size * k
+    if alg == 'dnn_pipeline':
+        return hp.cont_field_size + hp.vector_feats_size + hp.cate_field_size * k
     if alg == 'wdl':
         return hp.cont_field_size + hp.cate_field_size * k
     if alg == 'dnn':
@@ -353,15 +459,20 @@ def param_shapes(alg: str, hp: HParams) -> Dict[str, Tuple[int, ...]]:
         s['wdl_weights'] = (hp.cate_index_size + H[-1], 1); s['wdl_bias'] = (1,)
     elif alg == 'dnn':                                    # models/dnn.py:49-52
         s['weight_mat'] = (hp.cate_feats_size, k)
-    elif alg == 'dnn_multi':                              # models/dnn_multi.py:71-73
+    elif alg in ('dnn_multi', 'dnn_pipeline', 'dnn_cate', 'dnn_multi_cate'):   # models/dnn_multi.py:71-73, dnn_pipeline.py:69-71
         s['feats_emb'] = (hp.cate_feats_size, k)
+    elif alg in ('deepfm_cate', 'deepfm_multi_cate'):     # models/deepfm_cate.py:73-77
+        s['feats_emb'] = (hp.cate_feats_size, k); s['fm_first_order_emb'] = (hp.cate_feats_size, 1)
     prev = d0
     for i, h in enumerate(H):
         s['deep_%d' % i] = (prev, h); s['deep_bias_%d' % i] = (1, h); prev = h
     if alg in ('deepfm', 'deepfm_multi'):
         F = hp.cont_field_size + hp.cate_field_size + (hp.multi_field_size if alg == 'deepfm_multi' else 0)
         s['deep_fm_weight'] = (F + k + H[-1], 1); s['deep_fm_bias'] = (1,)
-    if alg in ('dnn', 'dnn_multi'):
+    if alg in ('deepfm_cate', 'deepfm_multi_cate'):
+        F = hp.cate_field_size + (hp.multi_field_size if alg == 'deepfm_multi_cate' else 0)
+        s['deep_fm_weight'] = (F + k + H[-1], 1); s['deep_fm_bias'] = (1,)
+    if alg in ('dnn', 'dnn_multi', 'dnn_pipeline', 'dnn_cate', 'dnn_multi_cate'):
         s['deep_res'] = (H[-1], 1); s['deep_res_bias'] = (1, 1)
     return s
 
@@ -485,8 +596,11 @@ def touched_rows(alg: str, batch, hp: HParams) -> Dict[str, Tensor]:
         out['weight_mat'] = mask(shapes['weight_mat'][0], cate)
     elif alg == 'dnn':
         out['weight_mat'] = mask(shapes['weight_mat'][0], cate)
-    elif alg == 'dnn_multi':
+    elif alg in ('dnn_multi', 'dnn_pipeline', 'dnn_cate', 'dnn_multi_cate'):
         out['feats_emb'] = mask(shapes['feats_emb'][0], cate, drop0=True)
+    elif alg in ('deepfm_cate', 'deepfm_multi_cate'):
+        mk = mask(shapes['feats_emb'][0], cate, drop0=True)
+        out['feats_emb'] = mk; out['fm_first_order_emb'] = mk
     return out
 
 

@@ -31,6 +31,15 @@ def hp_multi(B=512, **kw):
     return hp
 
 
+def hp_variant(alg, **kw):
+    """the variants local_run_test.py dispatches, at oracle-friendly sizes.  `*_cate` models have no
+    continuous block; a small vector block exercises the [vector | emb] deep input."""
+    if alg in ("deepfm_multi_cate", "dnn_multi_cate"):
+        return hp_multi(B=256, cont_field_size=0, vector_feats_size=5, **kw)
+    cont = 7 if alg == "dnn_pipeline" else 0
+    return hp_c1(cont_field_size=cont, vector_feats_size=5, embedding_size=16, **kw)
+
+
 def hp_criteo(B=1024, rows=50000, **kw):
     """configs[2..4] shape at reduced batch/rows: 13 cont + 26 cate, k=16, MLP 400-400-400"""
     hp = O.HParams(hidden_units=[400, 400, 400], batch_size=B, embedding_size=16, cont_field_size=13,
@@ -42,8 +51,8 @@ def hp_criteo(B=1024, rows=50000, **kw):
 
 def make_batch(alg, hp, seed, B=None, dist="zipf", id_dtype=None):
     B = B or hp.batch_size
-    multi = alg in ("deepfm_multi", "dnn_multi")
-    reserve = multi
+    multi = alg in ("deepfm_multi", "dnn_multi", "deepfm_multi_cate", "dnn_multi_cate")
+    reserve = multi or alg in ("deepfm_cate", "dnn_cate", "dnn_pipeline")      # row-0-zero models: id 0 is padding
     n_single_rows = hp.cate_feats_size - (1 if reserve else 0)
     if multi:
         Fm = hp.multi_field_size
@@ -53,7 +62,7 @@ def make_batch(alg, hp, seed, B=None, dist="zipf", id_dtype=None):
     else:
         sizes, multi_rows, tops = D.field_sizes(n_single_rows, hp.cate_field_size), [], []
     if id_dtype is None:
-        id_dtype = torch.int64 if multi else torch.int32
+        id_dtype = torch.int64 if reserve else torch.int32          # the tf.data generation parses int64 ids
     b = D.synthetic_batch(B, hp.cont_field_size, hp.cate_field_size, sizes, seed, V=hp.vector_feats_size,
                           multi_top_n=tops, multi_sizes=multi_rows, wide=hp.wide_field_size if alg == "wdl" else 0,
                           dist=dist, reserve_zero=reserve, id_dtype=id_dtype)

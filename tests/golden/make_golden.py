@@ -25,29 +25,40 @@ from oracle import ctr_oracle as O   # noqa: E402
 from deep_learning_b200 import data as D   # noqa: E402
 
 
+BASE = ("deepfm", "deepfm_multi", "wdl", "dnn", "dnn_multi")
+VARIANTS = ("deepfm_cate", "deepfm_multi_cate", "dnn_pipeline", "dnn_cate", "dnn_multi_cate")
+MULTI = ("deepfm_multi", "dnn_multi", "deepfm_multi_cate", "dnn_multi_cate")
+ROW0 = MULTI + ("deepfm_cate", "dnn_cate", "dnn_pipeline")          # row-0-zero tables: id 0 is padding
+
+
 def tiny_hp(alg):
     kw = dict(hidden_units=[8, 4], batch_size=16, embedding_size=4, cont_field_size=3, cate_field_size=5,
               cate_feats_size=60, l2_reg=1e-3, learning_rate=1e-2)
-    if alg in ("deepfm_multi", "dnn_multi"):
+    if alg in MULTI:
         kw.update(cate_feats_size=81, multi_feats_size=8, multi_field_size=2, multi_feats_range=[[0, 3, "m0"], [3, 8, "m1"]])
+    if alg in O.NO_CONT:
+        kw.update(cont_field_size=0)
+    if alg in VARIANTS:
+        kw.update(vector_feats_size=2)
     if alg == "wdl":
         kw.update(cate_index_size=60, wide_field_size=5)
     return O.HParams(**kw)
 
 
 def tiny_batch(alg, hp, seed):
-    multi = alg in ("deepfm_multi", "dnn_multi")
+    multi, row0 = alg in MULTI, alg in ROW0
     if multi:
         sizes, msizes, tops = D.field_sizes(60, 5), [10, 10], [3, 5]
     else:
-        sizes, msizes, tops = D.field_sizes(hp.cate_feats_size, 5), [], []
-    return D.synthetic_batch(hp.batch_size, hp.cont_field_size, hp.cate_field_size, sizes, seed, multi_top_n=tops,
-                             multi_sizes=msizes, wide=hp.wide_field_size if alg == "wdl" else 0, dist="uniform",
-                             reserve_zero=multi, id_dtype=torch.int64 if multi else torch.int32)
+        sizes, msizes, tops = D.field_sizes(hp.cate_feats_size - (1 if row0 else 0), 5), [], []
+    return D.synthetic_batch(hp.batch_size, hp.cont_field_size, hp.cate_field_size, sizes, seed, V=hp.vector_feats_size,
+                             multi_top_n=tops, multi_sizes=msizes, wide=hp.wide_field_size if alg == "wdl" else 0,
+                             dist="uniform", reserve_zero=row0, id_dtype=torch.int64 if row0 else torch.int32)
 
 
 def main():
-    for alg in ("deepfm", "deepfm_multi", "wdl", "dnn", "dnn_multi"):
+    only = sys.argv[1:]      # optional: regenerate just these models (the committed files of the others stay byte-identical)
+    for alg in (only or BASE + VARIANTS):
         hp = tiny_hp(alg)
         p = O.init_params(alg, hp, seed=2019, dtype=torch.float64)
         # golden inputs are the fp32-representable values (what gets injected into the CUDA engine)

@@ -153,6 +153,15 @@ def test_dnn_multi():
     _run_parity("dnn_multi", hp, steps=2)
 
 
+@pytest.mark.parametrize("alg", ["deepfm_cate", "deepfm_multi_cate", "dnn_pipeline", "dnn_cate", "dnn_multi_cate"])
+def test_variants_behind_the_same_kernels(alg):
+    """models/deepfm_cate.py, deepfm_multi_cate.py, dnn_pipeline.py, dnn_cate.py, dnn_multi_cate.py --
+    row-0-zero tables, [vector | emb] deep input, no continuous block (except dnn_pipeline)"""
+    hp = H.hp_variant(alg)
+    _run_parity(alg, hp, steps=2, B=256)
+    _run_parity(alg, hp, steps=2, B=256, adam_mode="lazy")
+
+
 def test_deepfm_tf32_tensor_core_path():
     """tcgen05 TF32 MLP inside the full step: logits/loss/params within 2e-3"""
     _run_parity("deepfm", H.hp_c1(), steps=2, precision="tf32", adam_mode="lazy")
@@ -221,3 +230,33 @@ def test_model_module_fit_predict_roundtrip(tmp_path, capsys):
     assert 0.0 <= auc <= 1.0
     sc = m.predict_scores(val[1])
     assert sc.shape == (50, 1)
+
+
+def test_variant_module_gen_b_fit_checkpoint_resume(tmp_path, capsys):
+    """generation-B surface on a variant (models/deepfm_cate.py): DeepModel(mp, train_iter).fit(n, val_iter) trains to
+    the end of the iterator, writes the Saver-style checkpoint (weights + Adam slots + step counters); a second model
+    restored from it (model_restore = 1, models/deepfm_cate.py:191-199) continues bit-identically to an uninterrupted one"""
+    import deep_learning_b200.models.deepfm_cate as alg_model
+    hp = H.hp_variant("deepfm_cate", batch_size=128)
+    batches = [H.make_batch("deepfm_cate", hp, seed=300 + s, B=128) for s in range(6)]
+    val = [H.make_batch("deepfm_cate", hp, seed=400, B=128)]
+    # uninterrupted: 6 steps
+    hp_a = H.hp_variant("deepfm_cate", batch_size=128)
+    ma = alg_model.DeepModel(hp_a, iter(batches), adam_mode="lazy")
+    ma.fit(2, iter(val))
+    # interrupted after 3 steps, checkpointed, restored into a fresh model, 3 more steps
+    hp.save_model_checkpoint = str(tmp_path / "ckpt")
+    mb = alg_model.DeepModel(hp, iter(batches[:3]), adam_mode="lazy")
+    mb.fit(2, iter(val))
+    hp_c = H.hp_variant("deepfm_cate", batch_size=128)
+    hp_c.model_restore, hp_c.restore_model_checkpoint = 1, str(tmp_path / "ckpt")
+    mc = alg_model.DeepModel(hp_c, iter(batches[3:]), adam_mode="lazy")
+    mc.fit(2, iter(val))
+    out = capsys.readouterr().out
+    assert "Old Model Restored Successfully" in out and "val_auc:" in out and "End of dataset" in out
+    wa, wc = ma.engine.get_weights(), mc.engine.get_weights()
+    for n in wa:
+        assert np.array_equal(wa[n], wc[n]), n
+    assert mc.engine.global_step == 6 and ma.engine.global_step == 6
+    auc = alg_model.predict(iter(val), str(tmp_path / "ckpt"), args=hp_c)
+    assert 0.0 <= auc <= 1.0

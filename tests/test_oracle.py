@@ -131,6 +131,42 @@ def test_autograd_matches_finite_differences(alg):
         assert abs(fd - float(gflat[idx])) < 1e-6 * max(1.0, abs(fd)) + 1e-9, (name, fd, float(gflat[idx]))
 
 
+VARIANTS = ["deepfm_cate", "deepfm_multi_cate", "dnn_pipeline", "dnn_cate", "dnn_multi_cate"]
+
+
+@pytest.mark.parametrize("alg", VARIANTS)
+def test_variants_autograd_matches_finite_differences(alg):
+    """the variants of SURVEY.md 8f N2, restated from their own files: gradient of every parameter block by central
+    differences"""
+    hp = H.hp_variant(alg, hidden_units=[8, 4])
+    p = O.init_params(alg, hp)
+    b = H.oracle_batch(H.make_batch(alg, hp, seed=1, B=16), torch.float64)
+    loss, _, _, grads = O.loss_and_grads(alg, p, b, hp)
+    rng = np.random.RandomState(0)
+    for name in p:
+        gflat = grads[name].reshape(-1)
+        nz = torch.nonzero(gflat).reshape(-1)
+        idx = int(nz[rng.randint(len(nz))]) if len(nz) else 0
+        eps = 1e-6
+        q = {k: v.clone() for k, v in p.items()}
+        q[name].reshape(-1)[idx] += eps
+        lp = float(O.LOSS[alg](q, b, hp)[0])
+        q[name].reshape(-1)[idx] -= 2 * eps
+        lm = float(O.LOSS[alg](q, b, hp)[0])
+        fd = (lp - lm) / (2 * eps)
+        assert abs(fd - float(gflat[idx])) < 1e-6 * max(1.0, abs(fd)) + 1e-9, (name, fd, float(gflat[idx]))
+
+
+def test_variants_reduce_to_their_parents():
+    """independent restatements agree where the graphs coincide: *_multi_cate == *_multi with no continuous block"""
+    hp = H.hp_variant("deepfm_multi_cate", hidden_units=[8, 4])
+    b = H.oracle_batch(H.make_batch("deepfm_multi_cate", hp, seed=3, B=32), torch.float64)
+    for child, parent in (("deepfm_multi_cate", "deepfm_multi"), ("dnn_multi_cate", "dnn_multi")):
+        p = O.init_params(child, hp)
+        assert O.param_shapes(child, hp) == O.param_shapes(parent, hp)
+        assert torch.equal(O.FORWARD[child](p, b, hp)[0], O.FORWARD[parent](p, b, hp)[0])
+
+
 def test_data_formats_roundtrip():
     from deep_learning_b200 import data as D
     hp = H.hp_c1(batch_size=7)
