@@ -26,7 +26,18 @@ class AdamHP(C.Structure):
     _fields_ = [("lr_t", c_f32), ("beta1", c_f32), ("beta2", c_f32), ("eps", c_f32)]
 
 
+MAX_PEERS = 16
+IPC_HANDLE_BYTES = 64
+
+
+class PeerRoute(C.Structure):
+    """mirror of `ctr_peer_route`"""
+    _fields_ = [("world", c_i32), ("rank", c_i32), ("slab", c_vp * MAX_PEERS), ("seg_end", C.c_uint32 * MAX_PEERS),
+                ("dst_row", C.c_uint32 * MAX_PEERS), ("dst_off", c_i64)]
+
+
 _P_CFG = C.POINTER(EmbedCfg)
+_P_RT = C.POINTER(PeerRoute)
 _P_HP = C.POINTER(AdamHP)
 
 # name -> (restype, [argtypes]) ; the first two args (handle, stream) are added for every entry
@@ -81,6 +92,13 @@ _PROTOS = {
     "ctr_auc_ws_bytes": (c_i64, [c_vp, c_i64]),
     "ctr_auc": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i64]),
     "ctr_gather_rows": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_i32]),
+    "ctr_peer_alloc": (c_i32, [c_vp, c_i64, C.POINTER(c_vp), c_vp]),
+    "ctr_peer_open": (c_i32, [c_vp, c_vp, C.POINTER(c_vp)]),
+    "ctr_peer_close": (c_i32, [c_vp, c_vp]),
+    "ctr_peer_free": (c_i32, [c_vp, c_vp]),
+    "ctr_peer_barrier": (c_i32, [c_vp, c_vp, _P_RT, c_i64, C.c_uint32, c_vp, c_i32]),
+    "ctr_gather_rows_push": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_i64, c_i32, c_i32, c_i32, _P_RT]),
+    "ctr_embed_bwd_finalize_push": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, _P_RT]),
     "ctr_debug_gemm_trace": (c_i32, [c_vp, c_i32]),
     "ctr_invert_perm": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
 }
@@ -155,6 +173,12 @@ class Handle:
     def launches(self) -> int:
         """kernels launched through this handle (counted inside the library)"""
         return int(self.lib.ctr_launch_count(self.h))
+
+    def invoke(self, name: str, *args) -> None:
+        """a status-returning entry point without a stream argument (set-up calls)"""
+        rc = getattr(self.lib, name)(self.h, *args)
+        if rc != 0:
+            raise CtrError("%s failed (%d): %s" % (name, rc, self.lib.ctr_last_error(self.h).decode()))
 
     def query(self, name: str, *args) -> int:
         return int(getattr(self.lib, name)(self.h, *args))

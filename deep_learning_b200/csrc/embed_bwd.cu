@@ -4,6 +4,7 @@
 // registers per run of equal row ids and written once per (row, chunk).  The Adam update then
 // consumes those partials in chunk order, so the whole scatter-add is deterministic.
 #include "ctr_common.cuh"
+#include "peer_route.cuh"
 
 namespace {
 
@@ -146,11 +147,16 @@ __device__ __forceinline__ float sum_run_partials(const float* __restrict__ part
 // grads[u, :width] = sum of the partial rows of run u, in chunk order.  One thread per (run, 4 columns) with 128-bit
 // accesses; a run spread over more than LONG_RUN chunks (a hot row: thousands of lookups) is summed by the whole warp
 // -- lane l takes partial rows l, l + 32, ..., then a fixed shuffle tree -- so one thread never walks hundreds of rows.
+// PUSH: the summed row goes straight into the owner's receive buffer over NVLink (the gradient all-to-all, fused);
+// runs past the routed list (the padding key) are dropped.
+template <bool PUSH>
 __global__ void __launch_bounds__(256)
 embed_bwd_finalize_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ n_unique, int64_t n_max,
-                          int width, int gs, const float* __restrict__ part, float* __restrict__ grads) {
+                          int width, int gs, const float* __restrict__ part, float* __restrict__ grads, const PeerRoute rt) {
     int64_t U = *n_unique;
     if (U > n_max) U = n_max;
+    if (PUSH && U > (int64_t) rt.seg_end[rt.world - 1]) U = rt.seg_end[rt.world - 1];
+    auto out_row = [&](int64_t u) -> float* { return PUSH ? route_row(rt, (uint32_t) u, gs) : grads + u * gs; };
     const int nq = (width + 3) >> 2;                 // column quads per row
     const int64_t total = U * nq;
     const int lane = threadIdx.x & 31;
@@ -174,7 +180,7 @@ embed_bwd_finalize_kernel(const uint32_t* __restrict__ seg_start, const uint32_t
                 const float4 x = __ldg(reinterpret_cast<const float4*>(p + i * gs));
                 a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
             }
-            *reinterpret_cast<float4*>(grads + u * gs + q * 4) = a;
+            *reinterpret_cast<float4*>(out_row(u) + q * 4) = a;
         }
         unsigned todo = __ballot_sync(0xffffffffu, lng && q == 0);     // the run's first quad leads
         while (todo) {
@@ -190,7 +196,7 @@ embed_bwd_finalize_kernel(const uint32_t* __restrict__ seg_start, const uint32_t
                     a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
                 }
                 a.x = ctr_warp_sum(a.x); a.y = ctr_warp_sum(a.y); a.z = ctr_warp_sum(a.z); a.w = ctr_warp_sum(a.w);
-                if (lane == 0) *reinterpret_cast<float4*>(grads + uu * gs + qq * 4) = a;
+                if (lane == 0) *reinterpret_cast<float4*>(out_row(uu) + qq * 4) = a;
             }
         }
     }
@@ -592,9 +598,26 @@ extern "C" int ctr_embed_bwd_finalize(ctr_handle* h, ctr_stream s, const uint32_
     if (n_max == 0) return CTR_OK;
     CTR_REQUIRE(h, grad_stride % 4 == 0 && ((reinterpret_cast<uintptr_t>(part) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0,
                 "embed_bwd_finalize: grad_stride must be a multiple of 4 and part / grads 16-byte aligned");
-    embed_bwd_finalize_kernel<<<grid_for(h, n_max * ((width + 3) / 4)), 256, 0, ctr_st(s)>>>(seg_start, n_unique, n_max, width,
-                                                                                              grad_stride, part, grads);
+    embed_bwd_finalize_kernel<false><<<grid_for(h, n_max * ((width + 3) / 4)), 256, 0, ctr_st(s)>>>(
+        seg_start, n_unique, n_max, width, grad_stride, part, grads, PeerRoute());
     CTR_CHECK_LAUNCH(h, "embed_bwd_finalize");
+    return CTR_OK;
+}
+
+extern "C" int ctr_embed_bwd_finalize_push(ctr_handle* h, ctr_stream s, const uint32_t* seg_start, const uint32_t* n_unique,
+                                           int64_t n_max, int width, int grad_stride, const float* part,
+                                           const ctr_peer_route* rt) {
+    CTR_REQUIRE(h, seg_start && n_unique && part && rt && width > 0 && grad_stride >= width && n_max >= 0,
+                "embed_bwd_finalize_push: bad args");
+    CTR_REQUIRE(h, rt->world >= 1 && rt->world <= CTR_MAX_PEERS && grad_stride % 4 == 0 && rt->dst_off % 16 == 0 &&
+                       (reinterpret_cast<uintptr_t>(part) & 15) == 0,
+                "embed_bwd_finalize_push: grad_stride must be a multiple of 4, buffers 16-byte aligned");
+    const int64_t U = rt->seg_end[rt->world - 1];
+    if (n_max == 0 || U == 0) return CTR_OK;
+    if (U < n_max) n_max = U;
+    embed_bwd_finalize_kernel<true><<<grid_for(h, n_max * ((width + 3) / 4)), 256, 0, ctr_st(s)>>>(
+        seg_start, n_unique, n_max, width, grad_stride, part, nullptr, make_route(rt));
+    CTR_CHECK_LAUNCH(h, "embed_bwd_finalize_push");
     return CTR_OK;
 }
 

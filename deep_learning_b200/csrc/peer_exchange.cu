@@ -1,0 +1,145 @@
+// Peer-memory exchange over NVLink 5 / NVSwitch: slab export/import (CUDA IPC), the all-ranks barrier and the fused
+// owner-gather-and-push kernel (include/ctr_b200.h, "peer memory").  The fused gradient push lives in embed_bwd.cu
+// next to the finalize kernel it extends.
+#include "ctr_common.cuh"
+#include "peer_route.cuh"
+
+extern "C" int ctr_peer_alloc(ctr_handle* h, int64_t bytes, void** slab, void* ipc_handle) {
+    CTR_REQUIRE(h, bytes > 0 && slab && ipc_handle, "peer_alloc: bad args");
+    static_assert(sizeof(cudaIpcMemHandle_t) == CTR_IPC_HANDLE_BYTES, "IPC handle size");
+    void* p = nullptr;
+    CTR_CUDA(h, cudaMalloc(&p, (size_t) bytes));
+    cudaError_t e = cudaMemset(p, 0, (size_t) bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    cudaIpcMemHandle_t hd;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&hd, p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        return ctr_fail(h, CTR_E_CUDA, "peer_alloc: %s", cudaGetErrorString(e));
+    }
+    memcpy(ipc_handle, &hd, sizeof(hd));
+    *slab = p;
+    return CTR_OK;
+}
+
+extern "C" int ctr_peer_open(ctr_handle* h, const void* ipc_handle, void** slab) {
+    CTR_REQUIRE(h, ipc_handle && slab, "peer_open: bad args");
+    cudaIpcMemHandle_t hd;
+    memcpy(&hd, ipc_handle, sizeof(hd));
+    void* p = nullptr;
+    CTR_CUDA(h, cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess));
+    *slab = p;
+    return CTR_OK;
+}
+
+extern "C" int ctr_peer_close(ctr_handle* h, void* slab) {
+    if (slab) CTR_CUDA(h, cudaIpcCloseMemHandle(slab));
+    return CTR_OK;
+}
+
+extern "C" int ctr_peer_free(ctr_handle* h, void* slab) {
+    if (slab) CTR_CUDA(h, cudaFree(slab));
+    return CTR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ barrier
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// lane p: tell peer p "rank arrived at `epoch`" (word [rank] of p's flags), then wait for p's word in the own flags.
+// Stores of earlier kernels on this stream are complete at this kernel's start; the system-scope fence + release
+// store order them before the arrival word as seen from the peer.
+__global__ void __launch_bounds__(32) peer_barrier_kernel(const PeerRoute rt, int64_t flags_off, uint32_t epoch,
+                                                          uint32_t* __restrict__ status, unsigned long long timeout_ns) {
+    const int p = threadIdx.x;
+    __threadfence_system();
+    if (p < rt.world) {
+        uint32_t* theirs = reinterpret_cast<uint32_t*>(static_cast<char*>(rt.slab[p]) + flags_off) + rt.rank;
+        st_release_sys(theirs, epoch);
+        const uint32_t* mine = reinterpret_cast<const uint32_t*>(static_cast<const char*>(rt.slab[rt.rank]) + flags_off) + p;
+        const unsigned long long t0 = global_ns();
+        unsigned spins = 0;
+        while ((int32_t) (ld_acquire_sys(mine) - epoch) < 0) {
+            if ((++spins & 1023u) == 0 && global_ns() - t0 > timeout_ns) {
+                if (status) *status = 1u + (uint32_t) p;
+                break;
+            }
+        }
+    }
+    __syncwarp();
+    __threadfence_system();
+}
+
+extern "C" int ctr_peer_barrier(ctr_handle* h, ctr_stream s, const ctr_peer_route* rt, int64_t flags_off, uint32_t epoch,
+                                uint32_t* status, int timeout_ms) {
+    CTR_REQUIRE(h, rt && rt->world >= 1 && rt->world <= CTR_MAX_PEERS && rt->rank >= 0 && rt->rank < rt->world &&
+                       flags_off >= 0 && flags_off % 4 == 0, "peer_barrier: bad args");
+    if (timeout_ms <= 0) timeout_ms = 10000;
+    peer_barrier_kernel<<<1, 32, 0, ctr_st(s)>>>(make_route(rt), flags_off, epoch, status,
+                                                 (unsigned long long) timeout_ms * 1000000ull);
+    CTR_CHECK_LAUNCH(h, "peer_barrier");
+    return CTR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ gather + push
+// one thread per (row, 4 columns): 128-bit table load (L1-bypassing: every row is wanted once), 128-bit store into the
+// requester's staging buffer -- consecutive rows of a segment are consecutive at the destination, so the NVLink
+// stores of a warp are contiguous
+__global__ void __launch_bounds__(256)
+gather_rows_push_kernel(const float* __restrict__ table, int table_stride, const uint32_t* __restrict__ idx, int64_t n,
+                        uint32_t mask, int width, int ds, const PeerRoute rt) {
+    const int nq = ds >> 2;
+    const int64_t total = n * nq;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t i = t / nq;
+        const int q = (int) (t - i * nq);
+        const uint32_t key = __ldg(idx + i);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int c = q * 4;
+        if (key != CTR_PAD_KEY && c < width) {
+            const float* src = table + (int64_t) (key & mask) * table_stride + c;
+            if (c + 4 <= table_stride) {
+                v = ctr_ldg_f4_stream(src);
+            } else {
+                v.x = src[0];
+                if (c + 1 < table_stride) v.y = src[1];
+                if (c + 2 < table_stride) v.z = src[2];
+            }
+            if (c + 1 >= width) v.y = 0.f;
+            if (c + 2 >= width) v.z = 0.f;
+            if (c + 3 >= width) v.w = 0.f;
+        }
+        float* dst = route_row(rt, (uint32_t) i, ds);
+        *reinterpret_cast<float4*>(dst + c) = v;
+    }
+}
+
+extern "C" int ctr_gather_rows_push(ctr_handle* h, ctr_stream s, const float* table, int table_stride, const uint32_t* idx,
+                                    int64_t n_rows, int idx_mask_bits, int width, int dst_stride, const ctr_peer_route* rt) {
+    CTR_REQUIRE(h, table && idx && rt && width > 0 && dst_stride >= width && n_rows >= 0 && n_rows < (1ll << 32),
+                "gather_rows_push: bad args");
+    CTR_REQUIRE(h, rt->world >= 1 && rt->world <= CTR_MAX_PEERS && dst_stride % 4 == 0 && table_stride % 4 == 0 &&
+                       rt->dst_off % 16 == 0 && (reinterpret_cast<uintptr_t>(table) & 15) == 0,
+                "gather_rows_push: strides must be multiples of 4 floats, buffers 16-byte aligned");
+    CTR_REQUIRE(h, (int64_t) rt->seg_end[rt->world - 1] == n_rows, "gather_rows_push: route does not cover the request list");
+    if (n_rows == 0) return CTR_OK;
+    uint32_t mask = (idx_mask_bits <= 0 || idx_mask_bits >= 32) ? 0xFFFFFFFFu : ((1u << idx_mask_bits) - 1u);
+    int64_t blocks = ctr_cdiv(n_rows * (dst_stride / 4), 256);
+    int64_t cap = (int64_t) h->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    gather_rows_push_kernel<<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(table, table_stride, idx, n_rows, mask, width,
+                                                                      dst_stride, make_route(rt));
+    CTR_CHECK_LAUNCH(h, "gather_rows_push");
+    return CTR_OK;
+}

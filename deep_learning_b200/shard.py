@@ -88,3 +88,36 @@ def split_sizes(counts_dev: torch.Tensor, group=None) -> Tuple[List[int], List[i
     recv = exchange_counts(send, group)
     both = torch.stack([send, recv]).cpu().tolist()
     return [int(x) for x in both[0]], [int(x) for x in both[1]]
+
+
+# ---- peer-memory exchange (NVLink stores instead of all-to-all #2 / #3) ----------------------------------------------
+def gather_counts(send_counts: torch.Tensor, group=None) -> torch.Tensor:
+    """all-gather of every rank's per-owner counts: mat[p, o] = unique rows rank p requests from owner o.  With the
+    whole matrix on every rank, each rank can place its rows inside a PEER's buffer without asking (peer_routes)."""
+    world = dist.get_world_size(group)
+    mat = torch.empty(world * send_counts.numel(), dtype=send_counts.dtype, device=send_counts.device)
+    dist.all_gather_into_tensor(mat, send_counts.contiguous(), group=group)
+    return mat.view(world, send_counts.numel())
+
+
+def peer_routes(mat: Sequence[Sequence[int]], rank: int):
+    """From the count matrix, the two placements of rank `rank` (each a pair (seg_end[p], dst_row[p])):
+
+    vectors   -- source = the rows peers requested of me, peer-major (recv_counts = column `rank`); the rows of peer p
+                 land at p's unique-list offset of owner `rank`:  sum_{o < rank} mat[p][o]
+    gradients -- source = my unique list, owner-major (send_counts = row `rank`); my rows land in owner o's receive
+                 buffer behind those of the ranks before me:       sum_{p < rank} mat[p][o]
+    Both reproduce exactly the layout `exchange` (all_to_all_single, peer-major) produces."""
+    world = len(mat)
+    send = [int(mat[rank][o]) for o in range(world)]
+    recv = [int(mat[p][rank]) for p in range(world)]
+
+    def ends(c):
+        out, acc = [], 0
+        for x in c:
+            acc += x
+            out.append(acc)
+        return out
+    vec = (ends(recv), [sum(int(mat[p][o]) for o in range(rank)) for p in range(world)])
+    grad = (ends(send), [sum(int(mat[p][o]) for p in range(rank)) for o in range(world)])
+    return send, recv, vec, grad

@@ -15,12 +15,16 @@ from __future__ import annotations
 
 from typing import Dict, Optional
 
+import ctypes as C
+import os
+
 import numpy as np
 import torch
 import torch.distributed as dist
 
 from . import shard as _shard
 from ._lib import AdamHP, EmbedCfg, ptr
+from .peer import PeerSlab
 from .engine import CtrEngine, _ru
 from .spec import ModelSpec
 
@@ -37,7 +41,8 @@ class _IdPlan:
         self.seg_start = torch.zeros(n + 2, **u32)
         self.n_unique = torch.zeros(1, **u32)
         self.counts = torch.zeros(eng.world, **u32)
-        self.counts_host = torch.zeros(2, eng.world, dtype=torch.int64).pin_memory()
+        self.counts_host = torch.zeros(eng.world * eng.world + 1, dtype=torch.int64).pin_memory()   # matrix + peer status
+        self.route_v = self.route_g = None
         self.ws_sort = torch.zeros(_ru(max(eng.h.query("ctr_sort_ws_bytes", n), 4 * (n // 2048 + 8)), 256),
                                    dtype=torch.uint8, device=dev)
         self.ev_local, self.ev_ready, self.ev_free = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
@@ -85,9 +90,26 @@ class ShardedCtrEngine(CtrEngine):
         self._ids_external = True
         self.plans = [_IdPlan(self), _IdPlan(self)]
         self.cur: Optional[_IdPlan] = None
-        self.rows_recv = torch.zeros(self.n_max + 1, self.wire, **f32)
+        # "peer": owners / requesters store rows straight into the peer's staging buffer over NVLink (fused kernels);
+        # "nccl": gather -> all_to_all_single -> consume
+        self.exchange_mode = os.environ.get("CTR_EXCHANGE", "peer" if world > 1 else "nccl")
+        if self.exchange_mode not in ("peer", "nccl"):
+            raise ValueError("CTR_EXCHANGE must be peer or nccl")
+        self.peer_status = torch.zeros(1, dtype=torch.int32, device=dev)
+        self._epoch, self._rows_dirty = 0, False
+        if self.exchange_mode == "peer":
+            row_bytes = self.wire * 4
+            self._flags_off, self._rows_off = 0, 256
+            self._g_off = self._rows_off + _ru((self.n_max + 1) * row_bytes, 256)
+            self._g_cap = self.n_max if self.train_mode else 0
+            self.slab = PeerSlab(self.h, self._g_off + _ru(max(self._g_cap, 1) * row_bytes, 256), group, dev)
+            self.rows_recv = self.slab.tensor(self._rows_off, (self.n_max + 1, self.wire))
+            self.g_recv = self.slab.tensor(self._g_off, (max(self._g_cap, 1), self.wire)) if self.train_mode else None
+        else:
+            self.rows_recv = torch.zeros(self.n_max + 1, self.wire, **f32)
         self.cont_buf = torch.zeros(max(s.C, 1), self.wire, **f32)
-        self.grads_send = torch.zeros(max(self.n_max, 1), self.wire, **f32) if self.train_mode else None
+        self.grads_send = (torch.zeros(max(self.n_max, 1), self.wire, **f32)
+                           if self.train_mode and self.exchange_mode == "nccl" else None)
         self._row_cap = 0
         self._ensure_rows(self.n_max)
         self.U = self.n_req = 0
@@ -98,9 +120,12 @@ class ShardedCtrEngine(CtrEngine):
             return
         cap = max(int(n_req * 1.25), 1024)
         f32 = dict(dtype=torch.float32, device=self.dev)
-        self.rows_send = torch.zeros(cap, self.wire, **f32)
+        peer = self.exchange_mode == "peer"
+        if not peer:
+            self.rows_send = torch.zeros(cap, self.wire, **f32)
         if self.train_mode:
-            self.g_recv = torch.zeros(cap, self.wire, **f32)
+            if not peer:
+                self.g_recv = torch.zeros(cap, self.wire, **f32)
             self.g_own = torch.zeros(cap, self.wire, **f32)
         self._row_cap = cap
 
@@ -145,8 +170,8 @@ class ShardedCtrEngine(CtrEngine):
         h.call("ctr_invert_perm", st, ptr(pl.perm), ptr(pl.uidx), n, ptr(pl.inv))
         with torch.cuda.stream(stream):
             send = pl.counts.to(torch.int64)
-            recv = _shard.exchange_counts(send, self.group_plan)      # all-to-all #1a
-            pl.counts_host.copy_(torch.stack([send, recv]), non_blocking=True)
+            mat = _shard.gather_counts(send, self.group_plan)         # exchange #1a: every rank learns every split
+            pl.counts_host.copy_(torch.cat([mat.reshape(-1), self.peer_status.to(torch.int64)]), non_blocking=True)
             pl.ev_local.record(stream)
         pl.B = B
 
@@ -155,10 +180,19 @@ class ShardedCtrEngine(CtrEngine):
         owner-side stable sort + run structure of the requested rows"""
         h, sp = self.h, self.plan
         pl.ev_local.synchronize()
-        both = pl.counts_host.tolist()
-        pl.send_counts, pl.recv_counts = [int(x) for x in both[0]], [int(x) for x in both[1]]
+        flat, W = pl.counts_host.tolist(), self.world
+        if flat[-1]:
+            raise RuntimeError("peer barrier timed out waiting for rank %d" % (flat[-1] - 1))
+        mat = [flat[p * W:(p + 1) * W] for p in range(W)]
+        pl.send_counts, pl.recv_counts, vec, grad = _shard.peer_routes(mat, self.rank)
         pl.U, pl.n_req = sum(pl.send_counts), sum(pl.recv_counts)
         pl.ensure_owner(self, pl.n_req)
+        if self.exchange_mode == "peer":
+            worst = max(sum(mat[p][o] for p in range(W)) for o in range(W))
+            if self.train_mode and worst > self._g_cap:      # the same verdict on every rank (all hold the matrix)
+                raise RuntimeError("peer exchange: %d rows requested of one owner, receive buffer holds %d" % (worst, self._g_cap))
+            pl.route_v = self.slab.route(vec[0], vec[1], self._rows_off)
+            pl.route_g = self.slab.route(grad[0], grad[1], self._g_off)
         n_req, st = pl.n_req, stream.cuda_stream
         with torch.cuda.stream(stream):
             _shard.exchange(pl.uniq[:pl.U], pl.send_counts, pl.recv_counts, out=pl.req, group=self.group_plan)   # #1b
@@ -251,12 +285,24 @@ class ShardedCtrEngine(CtrEngine):
         U, n_req = pl.U, pl.n_req
         self._mark("wait_plan")
         self._ensure_rows(n_req)
-        # owners gather [v | w] rows; all-to-all #2 returns them in the requester's unique-list order
-        if n_req:
-            h.call("ctr_gather_rows", st, ptr(self.table), s.table_stride, ptr(pl.req), None, n_req, sp.local_bits,
-                   s.row_width, ptr(self.rows_send), self.wire)
-        self._mark("owner_gather")
-        _shard.exchange(self.rows_send[:n_req], pl.recv_counts, pl.send_counts, out=self.rows_recv, group=self.group)
+        if self.exchange_mode == "peer":
+            # owners read their [v | w] rows and store them straight into the requester's staging buffer, in the
+            # requester's unique-list order; the barrier is the only other launch of exchange #2
+            if self._rows_dirty:                 # no gradient barrier since the last forward (predict): peers may still read
+                self._barrier(st)
+            if n_req:
+                h.call("ctr_gather_rows_push", st, ptr(self.table), s.table_stride, ptr(pl.req), n_req, sp.local_bits,
+                       s.row_width, self.wire, C.byref(pl.route_v))
+            self._mark("owner_gather")
+            self._barrier(st)
+            self._rows_dirty = True
+        else:
+            # owners gather [v | w] rows; all-to-all #2 returns them in the requester's unique-list order
+            if n_req:
+                h.call("ctr_gather_rows", st, ptr(self.table), s.table_stride, ptr(pl.req), None, n_req, sp.local_bits,
+                       s.row_width, ptr(self.rows_send), self.wire)
+            self._mark("owner_gather")
+            _shard.exchange(self.rows_send[:n_req], pl.recv_counts, pl.send_counts, out=self.rows_recv, group=self.group)
         self._mark("a2a_vectors")
         self.rows_recv[U].zero_()    # the run of padding ids (key 0xFFFFFFFF), if any, is unique index U
         if s.use_fm and s.fm_cont and s.C:
@@ -281,10 +327,18 @@ class ShardedCtrEngine(CtrEngine):
             self._build_exchange(self._pending_exchange, self.side)
             self._pending_exchange = None
         U, n_req = pl.U, pl.n_req
-        h.call("ctr_embed_bwd_finalize", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
-               ptr(self.part), ptr(self.grads_send))
-        self._mark("finalize")
-        _shard.exchange(self.grads_send[:U], pl.send_counts, pl.recv_counts, out=self.g_recv, group=self.group)
+        if self.exchange_mode == "peer":
+            # one gradient row per unique key, summed and stored straight into its owner's receive buffer (exchange #3)
+            h.call("ctr_embed_bwd_finalize_push", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
+                   ptr(self.part), C.byref(pl.route_g))
+            self._mark("finalize")
+            self._barrier(st)
+            self._rows_dirty = False
+        else:
+            h.call("ctr_embed_bwd_finalize", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
+                   ptr(self.part), ptr(self.grads_send))
+            self._mark("finalize")
+            _shard.exchange(self.grads_send[:U], pl.send_counts, pl.recv_counts, out=self.g_recv, group=self.group)
         self._mark("a2a_grads")
         if not n_req:
             return
@@ -293,6 +347,12 @@ class ShardedCtrEngine(CtrEngine):
         h.call("ctr_adam_rows", st, ptr(pl.o_uniq), ptr(pl.o_nuniq), n_req, sp.local_bits, ptr(self.g_own), None,
                self.wire, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
                self.rows_local, ptr(self.touched), None, 0, self._fm_w2(), s.k, hp)
+
+    def _barrier(self, st: int) -> None:
+        """all ranks: everything stored into peer slabs so far is visible, and every peer is at the same point"""
+        self._epoch += 1
+        self.h.call("ctr_peer_barrier", st, C.byref(self.cur.route_v), self._flags_off, self._epoch, ptr(self.peer_status),
+                    int(os.environ.get("CTR_PEER_TIMEOUT_MS", 10000)))
 
     def _reduce_dense_grads(self) -> None:
         # dlogit already carries 1/B_global, so a plain SUM over ranks is the global-batch gradient; the loss

@@ -304,6 +304,49 @@ int ctr_gather_rows(ctr_handle* h, ctr_stream s, const float* src, int src_strid
 /* inv[perm[i]] = uidx[i] : lookup position -> index of its row in the unique list */
 int ctr_invert_perm(ctr_handle* h, ctr_stream s, const uint32_t* perm, const uint32_t* uidx, int64_t n, uint32_t* inv);
 
+/* ---- peer memory over NVLink 5 / NVSwitch (multi-GPU) ------------------------------------------------
+ * The reference has no multi-device code (one tf.Session, one device); these entry points are what a row-sharded
+ * deployment of models/deepfm.py:78 (embedding_lookup) / :151 (minimize) needs between the shards.  Each rank
+ * allocates ONE slab, exports it (CUDA IPC) and maps the slabs of its peers; kernels then store straight into the
+ * peer's slab, so "owner gathers rows -> all-to-all -> requester" is ONE kernel whose stores travel over NVLink while
+ * its loads are still in flight, and so is "sum the gradient partials of a row -> all-to-all -> owner".
+ * Lifetime: alloc/open/close/free are host-synchronous set-up calls (not for the step loop). */
+#define CTR_MAX_PEERS 16
+#define CTR_IPC_HANDLE_BYTES 64
+int ctr_peer_alloc(ctr_handle* h, int64_t bytes, void** slab, void* ipc_handle /*[CTR_IPC_HANDLE_BYTES] out*/);
+int ctr_peer_open(ctr_handle* h, const void* ipc_handle, void** slab);
+int ctr_peer_close(ctr_handle* h, void* slab);
+int ctr_peer_free(ctr_handle* h, void* slab);
+
+/* where the rows of one source list go: the list is a concatenation of `world` segments, segment p = rows
+ * [seg_end[p-1], seg_end[p]) -> rows dst_row[p], dst_row[p]+1, ... of the buffer at byte offset dst_off in peer p's slab */
+typedef struct ctr_peer_route {
+    int32_t  world, rank;
+    void*    slab[CTR_MAX_PEERS];      /* peer p's slab as mapped into THIS process (slab[rank] = the own slab) */
+    uint32_t seg_end[CTR_MAX_PEERS];
+    uint32_t dst_row[CTR_MAX_PEERS];
+    int64_t  dst_off;
+} ctr_peer_route;
+
+/* all-ranks barrier on `stream` (one 32-thread CTA): releases everything this rank stored into peer slabs before it,
+ * and returns once every peer has done the same.  flags_off: byte offset of CTR_MAX_PEERS uint32 arrival words in
+ * every slab (zero-initialised once); epoch must grow by 1 per barrier on every rank.  A peer that does not arrive
+ * within timeout_ms sets *status (device uint32, own memory) to 1 + the peer's rank instead of hanging the GPU. */
+int ctr_peer_barrier(ctr_handle* h, ctr_stream s, const ctr_peer_route* rt, int64_t flags_off, uint32_t epoch,
+                     uint32_t* status, int timeout_ms);
+
+/* fused owner gather + vector all-to-all: row i of the request list (keys of the rows peers asked this rank for,
+ * grouped by peer) is read from the table and stored into the requesting peer's staging buffer:
+ *   peer(i).buf[dst_row + (i - seg_begin), :width] = table[idx[i] & mask, :width], columns [width, dst_stride) = 0 */
+int ctr_gather_rows_push(ctr_handle* h, ctr_stream s, const float* table, int table_stride, const uint32_t* idx,
+                         int64_t n_rows, int idx_mask_bits, int width, int dst_stride, const ctr_peer_route* rt);
+
+/* fused ctr_embed_bwd_finalize + gradient all-to-all: the summed gradient row of run u (u < rt->seg_end[world-1];
+ * later runs = the padding key, dropped) is stored into the owner's receive buffer */
+int ctr_embed_bwd_finalize_push(ctr_handle* h, ctr_stream s, const uint32_t* seg_start, const uint32_t* n_unique,
+                                int64_t n_max, int width, int grad_stride, const float* part,
+                                const ctr_peer_route* rt);
+
 /* ---- timing experiments (not part of the product path) -----------------------------------------------------
  * with CTR_GEMM_DBG & 8 in the environment the TF32 forward/dgrad GEMM records %globaltimer at its phase boundaries
  * (8 slots per CTA: start, setup done, last MMA committed, accumulator ready, epilogue done, CTA synced, TMEM freed);

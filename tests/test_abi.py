@@ -39,12 +39,14 @@ def test_ctypes_prototypes_match_header(lib_built):
                 return _lib._P_CFG
             if "ctr_adam_hp" in a:
                 return _lib._P_HP
-            if "ctr_handle**" in a.replace(" ", ""):
+            if "ctr_peer_route" in a:
+                return _lib._P_RT
+            if "ctr_handle**" in a.replace(" ", "") or "void**" in a.replace(" ", ""):
                 return C.POINTER(C.c_void_p)
             return C.c_void_p
         ty = " ".join(a.split()[:-1])
         return {"int": C.c_int32, "int64_t": C.c_int64, "uint64_t": C.c_uint64, "float": C.c_float,
-                "ctr_stream": C.c_void_p, "int32_t": C.c_int32}[ty]
+                "ctr_stream": C.c_void_p, "int32_t": C.c_int32, "uint32_t": C.c_uint32}[ty]
     for ret, name, args in _header_protos():
         want = [t for t in (ctype(x) for x in args.split(",")) if t is not None]
         res, have = _lib._PROTOS[name]
