@@ -143,3 +143,58 @@ extern "C" int ctr_gather_rows_push(ctr_handle* h, ctr_stream s, const float* ta
     CTR_CHECK_LAUNCH(h, "gather_rows_push");
     return CTR_OK;
 }
+
+// ------------------------------------------------------------------------------------------------ merge of sorted segments
+struct SegEnds {
+    uint32_t end[CTR_MAX_PEERS];
+};
+
+__global__ void __launch_bounds__(256)
+merge_segments_kernel(const uint32_t* __restrict__ keys, uint32_t n, const SegEnds se, int world,
+                      uint32_t* __restrict__ out_keys, uint32_t* __restrict__ out_idx) {
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+        int p = 0;
+        uint32_t pb = 0;
+        for (int q = 0; q < world - 1; ++q) {
+            const bool past = j >= se.end[q];
+            p += past ? 1 : 0;
+            pb = past ? se.end[q] : pb;
+        }
+        const uint32_t key = __ldg(keys + j);
+        uint32_t pos = j - pb;                       // entries of the own segment before this one
+        uint32_t qb = 0;
+        for (int q = 0; q < world; ++q) {
+            const uint32_t qe = se.end[q];
+            if (q != p) {                            // entries of segment q that sort before (q < p: before or equal)
+                uint32_t lo = qb, hi = qe;
+                while (lo < hi) {
+                    const uint32_t mid = (lo + hi) >> 1;
+                    const uint32_t v = __ldg(keys + mid);
+                    const bool before = q < p ? v <= key : v < key;
+                    lo = before ? mid + 1 : lo;
+                    hi = before ? hi : mid;
+                }
+                pos += lo - qb;
+            }
+            qb = qe;
+        }
+        out_keys[pos] = key;
+        out_idx[pos] = j;
+    }
+}
+
+extern "C" int ctr_merge_sorted_segments(ctr_handle* h, ctr_stream s, const uint32_t* keys, int64_t n, const uint32_t* seg_end,
+                                         int world, uint32_t* out_keys, uint32_t* out_idx) {
+    CTR_REQUIRE(h, keys && seg_end && out_keys && out_idx && world >= 1 && world <= CTR_MAX_PEERS && n >= 0 && n < (1ll << 32),
+                "merge_sorted_segments: bad args");
+    CTR_REQUIRE(h, (int64_t) seg_end[world - 1] == n, "merge_sorted_segments: segments do not cover the list");
+    if (n == 0) return CTR_OK;
+    SegEnds se;
+    for (int p = 0; p < CTR_MAX_PEERS; ++p) se.end[p] = p < world ? seg_end[p] : (uint32_t) n;
+    int64_t blocks = ctr_cdiv(n, 256);
+    int64_t cap = (int64_t) h->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    merge_segments_kernel<<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(keys, (uint32_t) n, se, world, out_keys, out_idx);
+    CTR_CHECK_LAUNCH(h, "merge_sorted_segments");
+    return CTR_OK;
+}

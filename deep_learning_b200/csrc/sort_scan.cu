@@ -1,18 +1,19 @@
-// Stable LSD radix sort (8-bit digits), flag scans and run-length structure of sorted keys.
+// Stable LSD radix sort (9-bit digits), flag scans and run-length structure of sorted keys.
 // These are the integer half of K4 (the deterministic replacement of TF's unique +
 // unsorted_segment_sum) and of the AUC; all results are bit-exact and order-deterministic.
 #include "ctr_common.cuh"
 
 namespace {
 
-constexpr int RADIX_BITS = 8;
+constexpr int RADIX_BITS = 9;                            // 27-bit row keys (1e8 rows, any shard count) sort in 3 passes
 constexpr int RADIX = 1 << RADIX_BITS;
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 8;                            // keys per thread (16: 95 registers, 2 CTAs/SM, 1.4 waves at 1.7 M keys)
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;     // 2048 keys per block
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr int WARP_SPAN = SORT_TILE / SORT_WARPS;        // 256 consecutive keys per warp
-static_assert(SORT_THREADS == RADIX, "one thread per digit is assumed");
+constexpr int DIGITS_PER_THREAD = RADIX / SORT_THREADS;
+static_assert(DIGITS_PER_THREAD * SORT_THREADS == RADIX, "whole digits per thread");
 
 // ---- pass 1: per-block digit histogram, stored digit-major hist[d * nblk + blk] ---------------
 __global__ void __launch_bounds__(SORT_THREADS)
@@ -79,28 +80,43 @@ radix_scan_rows_kernel(uint32_t* __restrict__ hist, int nblk, uint32_t* __restri
 }
 
 // ---- pass 3: stable scatter ------------------------------------------------------------------
-// Warp w owns keys [w*512, (w+1)*512) of the tile and walks them in 16 rounds of 32 consecutive keys;
+// Warp w owns keys [w*256, (w+1)*256) of the tile and walks them in 8 rounds of 32 consecutive keys;
 // __match_any_sync ranks equal digits inside a round in lane (= index) order, a per-warp counter
-// table carries ranks across rounds, and a cross-warp exclusive sum finishes the tile-local rank.
+// table carries ranks across rounds, a cross-warp exclusive sum and a scan over the digits finish the tile-local
+// rank.  The tile is then ordered in shared memory and written out from there: consecutive threads store consecutive
+// positions of a digit's run, so a warp store touches a few sectors instead of 32.
 __global__ void __launch_bounds__(SORT_THREADS)
 radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift,
                      const uint32_t* __restrict__ hist, const uint32_t* __restrict__ tot, int nblk) {
     __shared__ uint32_t wcnt[SORT_WARPS][RADIX];   // per-warp digit counts -> per-warp bases
-    __shared__ uint32_t dbase[RADIX];              // global base of each digit for this block
+    __shared__ uint32_t dbase[RADIX];              // global position of the digit's first key of this tile, minus lstart
+    __shared__ uint32_t lstart[RADIX];             // tile-local start of each digit
+    __shared__ uint32_t skey[SORT_TILE], sval[SORT_TILE];
     __shared__ uint32_t sm[33];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int d0 = threadIdx.x * DIGITS_PER_THREAD;        // this thread's digits in the digit-indexed steps
     for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&wcnt[0][0])[i] = 0;
-    // digit bases: exclusive scan of the 256 row totals + this block's offset inside the row
+    // digit bases: exclusive scan of the row totals + this block's offset inside the row
     {
-        uint32_t t = tot[threadIdx.x];
+        uint32_t t[DIGITS_PER_THREAD], sum = 0;
+#pragma unroll
+        for (int j = 0; j < DIGITS_PER_THREAD; ++j) {
+            t[j] = tot[d0 + j];
+            sum += t[j];
+        }
         uint32_t total;
-        uint32_t ex = block_excl_scan(t, sm, &total);   // includes the __syncthreads for wcnt zeroing
-        dbase[threadIdx.x] = ex + hist[(int64_t) threadIdx.x * nblk + blockIdx.x];
+        uint32_t ex = block_excl_scan(sum, sm, &total);   // includes the __syncthreads for wcnt zeroing
+#pragma unroll
+        for (int j = 0; j < DIGITS_PER_THREAD; ++j) {
+            dbase[d0 + j] = ex + hist[(int64_t) (d0 + j) * nblk + blockIdx.x];
+            ex += t[j];
+        }
     }
     __syncthreads();
 
-    const int64_t wbase = (int64_t) blockIdx.x * SORT_TILE + (int64_t) w * WARP_SPAN;
+    const int64_t tbase = (int64_t) blockIdx.x * SORT_TILE;
+    const int64_t wbase = tbase + (int64_t) w * WARP_SPAN;
     uint32_t key[SORT_ITEMS];
     uint32_t off[SORT_ITEMS];   // rank among equal digits inside this warp's span
 #pragma unroll
@@ -129,15 +145,28 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         __syncwarp();
     }
     __syncthreads();
-    // cross-warp exclusive sum per digit (thread d handles digit d)
+    // cross-warp exclusive sum per digit, then the tile-local start of each digit
     {
-        uint32_t run = 0;
-        int d = threadIdx.x;
+        uint32_t cnt[DIGITS_PER_THREAD], sum = 0;
 #pragma unroll
-        for (int ww = 0; ww < SORT_WARPS; ++ww) {
-            uint32_t c = wcnt[ww][d];
-            wcnt[ww][d] = run;
-            run += c;
+        for (int j = 0; j < DIGITS_PER_THREAD; ++j) {
+            uint32_t run = 0;
+#pragma unroll
+            for (int ww = 0; ww < SORT_WARPS; ++ww) {
+                uint32_t c = wcnt[ww][d0 + j];
+                wcnt[ww][d0 + j] = run;
+                run += c;
+            }
+            cnt[j] = run;
+            sum += run;
+        }
+        uint32_t total;
+        uint32_t ex = block_excl_scan(sum, sm, &total);
+#pragma unroll
+        for (int j = 0; j < DIGITS_PER_THREAD; ++j) {
+            lstart[d0 + j] = ex;
+            dbase[d0 + j] -= ex;
+            ex += cnt[j];
         }
     }
     __syncthreads();
@@ -146,9 +175,21 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         int64_t i = wbase + it * 32 + lane;
         if (i < n) {
             uint32_t d = (key[it] >> shift) & (RADIX - 1);
-            uint32_t pos = dbase[d] + wcnt[w][d] + off[it];
-            keys_out[pos] = key[it];
-            vals_out[pos] = vals_in[i];
+            uint32_t lp = lstart[d] + wcnt[w][d] + off[it];
+            skey[lp] = key[it];
+            sval[lp] = vals_in[i];
+        }
+    }
+    __syncthreads();
+    const int nvalid = (int) (n - tbase < (int64_t) SORT_TILE ? n - tbase : (int64_t) SORT_TILE);
+#pragma unroll
+    for (int it = 0; it < SORT_ITEMS; ++it) {
+        int idx = it * SORT_THREADS + threadIdx.x;
+        if (idx < nvalid) {
+            uint32_t k = skey[idx];
+            uint32_t pos = dbase[(k >> shift) & (RADIX - 1)] + (uint32_t) idx;
+            keys_out[pos] = k;
+            vals_out[pos] = sval[idx];
         }
     }
 }

@@ -170,6 +170,7 @@ class CtrEngine:
     def _stream(self) -> int:
         return torch.cuda.current_stream(self.dev).cuda_stream
 
+    _sort_B = None         # batch size whose id sort forward() still has to enqueue (train steps only)
     phase_marks = None     # list of (name, event) when a timing script asks for the main-stream phase picture
 
     def _mark(self, name: str) -> None:
@@ -383,6 +384,12 @@ class CtrEngine:
     def forward(self, B: int, with_loss: bool) -> None:
         s, st, h = self.spec, self._stream(), self.h
         self._embed_forward(B)
+        if self._sort_B is not None:
+            # the id sort starts BEHIND the gather: K1 is the HBM-bound kernel of the step and a co-running radix sort took
+            # 20 % of its bandwidth; under the tensor-core GEMMs that follow the sort is close to free, and its result is
+            # only needed after the MLP backward
+            self._launch_sort(self._sort_B)
+            self._sort_B = None
         self._mark("embed")
         x, ldx = self.x0, s.x0_ld
         for i, (k_, h_) in enumerate(self._layer_dims()):
@@ -515,7 +522,7 @@ class CtrEngine:
 
     def _launch_sort(self, B: int) -> None:
         """sort ids -> (keys, perm), run-length structure -> (uniq, seg_start, uidx, n_unique); enqueued on
-        the side stream right after the batch upload so it overlaps the forward pass"""
+        the side stream right behind the gather (K1) so it overlaps the MLP"""
         s, h = self.spec, self.h
         if not s.ids_ld:
             return
@@ -573,7 +580,7 @@ class CtrEngine:
             ev_call = torch.cuda.Event()
             ev_call.record(torch.cuda.current_stream(self.dev))
         B = self.load_batch(batch) if batch is not None else self.last_batch
-        self._launch_sort(B)
+        self._sort_B = B                    # enqueued by forward(), right behind the gather
         self._mark("load")
         self.forward(B, with_loss=True)
         self._mark("head")

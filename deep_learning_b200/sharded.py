@@ -197,11 +197,11 @@ class ShardedCtrEngine(CtrEngine):
         with torch.cuda.stream(stream):
             _shard.exchange(pl.uniq[:pl.U], pl.send_counts, pl.recv_counts, out=pl.req, group=self.group_plan)   # #1b
             if self.train_mode and n_req:
-                pl.o_keys[:n_req].copy_(pl.req[:n_req])
-                torch.arange(n_req, out=pl.o_idx[:n_req])
                 ws, wsn = ptr(pl.o_ws), pl.o_ws.numel()
-                # stable sort by local row: equal rows keep peer order, so the owner's sum is order-fixed
-                h.call("ctr_sort_pairs", st, ptr(pl.o_keys), ptr(pl.o_idx), n_req, sp.local_bits, ws, wsn)
+                # every peer's slice is already ascending: a stable merge (equal rows keep peer order, so the owner's
+                # sum is order-fixed) replaces the radix sort of the request list
+                ends = (C.c_uint32 * self.world)(*vec[0])
+                h.call("ctr_merge_sorted_segments", st, ptr(pl.req), n_req, ends, self.world, ptr(pl.o_keys), ptr(pl.o_idx))
                 h.call("ctr_unique_segments", st, ptr(pl.o_keys), n_req, ptr(pl.o_uniq), ptr(pl.o_seg), ptr(pl.o_uidx),
                        ptr(pl.o_nuniq), ws, wsn)
             pl.ev_ready.record(stream)

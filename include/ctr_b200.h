@@ -347,6 +347,13 @@ int ctr_embed_bwd_finalize_push(ctr_handle* h, ctr_stream s, const uint32_t* seg
                                 int64_t n_max, int width, int grad_stride, const float* part,
                                 const ctr_peer_route* rt);
 
+/* owner side of the gradient exchange: `keys` is a concatenation of `world` segments (peer-major, segment p ends at
+ * seg_end[p], a HOST array), each ascending and duplicate-free (a slice of the requester's unique list).  Writes their
+ * stable merge -- out_keys ascending, equal keys in peer order, out_idx[i] = position of that entry in `keys` -- by
+ * ranking every entry with one binary search per segment: one launch instead of a radix sort of the list. */
+int ctr_merge_sorted_segments(ctr_handle* h, ctr_stream s, const uint32_t* keys, int64_t n, const uint32_t* seg_end,
+                              int world, uint32_t* out_keys, uint32_t* out_idx);
+
 /* ---- timing experiments (not part of the product path) -----------------------------------------------------
  * with CTR_GEMM_DBG & 8 in the environment the TF32 forward/dgrad GEMM records %globaltimer at its phase boundaries
  * (8 slots per CTA: start, setup done, last MMA committed, accumulator ready, epilogue done, CTA synced, TMEM freed);

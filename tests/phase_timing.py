@@ -44,6 +44,9 @@ def main():
         eng.train_step(batches[i % NB], next_batch=batches[(i + 1) % NB] if pf else None)
     torch.cuda.synchronize()
     steps = 20
+    names = os.environ.get("TIMERS", "")
+    if names:     # per-entry-point durations (events on the launching stream, so side-stream kernels are seen too)
+        eng.h.timers = {n: [] for n in names.split(",")}
     eng.phase_marks = []
     for i in range(steps):
         eng.train_step(batches[i % NB], next_batch=batches[(i + 1) % NB] if pf else None)
@@ -60,6 +63,10 @@ def main():
             tot += avg
             print("%-32s %8.1f us" % (k, avg))
         print("%-32s %8.1f us per step" % ("total", tot))
+        if names:
+            for n, ev in eng.h.timers.items():
+                if ev:
+                    print("  %-30s %8.1f us x %.1f per step" % (n, sum(a.elapsed_time(b) for a, b in ev) * 1e3 / len(ev), len(ev) / steps))
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
