@@ -80,10 +80,14 @@ _PROTOS = {
     "ctr_shard_counts": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp]),
     "ctr_embed_bwd_partials": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_i64, c_vp,
                                        c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "ctr_embed_bwd_partials_weighted": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_i64, c_vp,
+                                                c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "ctr_embed_bwd_finalize": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "ctr_cont_bwd_ws_bytes": (c_i64, [c_vp, _P_CFG]),
     "ctr_fm_cont_bwd": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
     "ctr_scalar_segment_add": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i32, c_i64, c_vp]),
+    "ctr_scalar_gathered_l2": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_f32, c_i64, c_i64, c_i32, c_f32, c_vp,
+                                       c_vp]),
     "ctr_segment_sum_rows": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i32, c_i32, c_vp, c_i32]),
     "ctr_adam_rows_ws_bytes": (c_i64, [c_vp, c_i64]),
     "ctr_adam_rows": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp,
@@ -102,6 +106,9 @@ _PROTOS = {
     "ctr_merge_sorted_segments": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_i32, c_vp, c_vp]),
     "ctr_debug_gemm_trace": (c_i32, [c_vp, c_i32]),
     "ctr_invert_perm": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
+    "ctr_parse_lines": (c_i32, [c_vp, c_i64, c_i32, c_i32, c_i32, c_i32, c_i32, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                c_vp, c_vp, c_vp]),
+    "ctr_parse_tfrecords": (c_i32, [c_vp, c_i64, c_i32, c_i32, c_i32, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
 }
 
 EXPORTS = tuple(_PROTOS)

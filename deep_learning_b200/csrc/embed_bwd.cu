@@ -25,7 +25,7 @@ embed_bwd_partials_kernel(const ctr_embed_cfg cfg, const uint32_t* __restrict__ 
                           const float* __restrict__ sum_e, const float* __restrict__ dlogit,
                           const float* __restrict__ w_fm, const float* __restrict__ inv_cnt_emb,
                           const float* __restrict__ inv_cnt_first, const float* __restrict__ cont_grad,
-                          float* __restrict__ part) {
+                          const float* __restrict__ slot_weight, float* __restrict__ part) {
     constexpr int G = K / 4;   // lanes per chunk walker: lane q owns coordinates 4q..4q+3
     constexpr int UN = 4;      // lookups in flight per walker
     const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
@@ -91,7 +91,11 @@ embed_bwd_partials_kernel(const ctr_embed_cfg cfg, const uint32_t* __restrict__ 
                     } else {
                         const int jm = field_of_slot[slot - Fc];
                         const int fld = Fc + jm;
-                        const float sc_e = inv_cnt_emb[(int64_t) b * Fm + jm], sc_w = inv_cnt_first[(int64_t) b * Fm + jm];
+                        float sc_e = inv_cnt_emb[(int64_t) b * Fm + jm], sc_w = inv_cnt_first[(int64_t) b * Fm + jm];
+                        if (slot_weight) {   // weighted pooling (models/dnn_multi_textline.py:96-101): d row = w[b,t] * upstream / count
+                            const float sw = __ldg(slot_weight + (int64_t) b * cfg.M + (slot - Fc));
+                            sc_e *= sw; sc_w *= sw;
+                        }
                         float4 g = __ldg(reinterpret_cast<const float4*>(dx0 + (int64_t) b * dx0_ld + fld * K + q * 4));
                         if (use_fm) {
                             const float dl = __ldg(dlogit + b);
@@ -524,6 +528,38 @@ scalar_segment_add_kernel(const uint32_t* __restrict__ uniq, const uint32_t* __r
     }
 }
 
+// l2 term over GATHERED scalar weights (models/wdl_textline.py:264-269,284-286: the regulariser sees the [B, W+H] lookup
+// result, not the table).  A row looked up c times carries c * w^2 / 2 in the loss and scale * c * w in its gradient.
+__global__ void __launch_bounds__(256)
+scalar_gathered_l2_runs_kernel(const uint32_t* __restrict__ uniq, const uint32_t* __restrict__ seg_start,
+                               const uint32_t* __restrict__ n_unique, int64_t n_max, const float* __restrict__ w, float scale,
+                               int64_t rows, float* __restrict__ grad, float* __restrict__ sq) {
+    int64_t U = *n_unique;
+    if (U > n_max) U = n_max;
+    for (int64_t u = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; u < n_max; u += (int64_t) gridDim.x * blockDim.x) {
+        float q = 0.f;
+        if (u < U) {
+            const uint32_t key = uniq[u];
+            if (key != CTR_PAD_KEY && (int64_t) key < rows) {
+                const float c = (float) (seg_start[u + 1] - seg_start[u]), x = w[key];
+                grad[key] += scale * c * x;       // keys are unique: one writer per row
+                q = c * x * x;
+            }
+        }
+        sq[u] = q;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+scalar_gathered_l2_dense_kernel(const float* __restrict__ w, float scale, int64_t lo, int n, float count,
+                                float* __restrict__ grad, float* __restrict__ sq) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const float x = w[lo + j];
+    grad[lo + j] += scale * count * x;
+    sq[j] = count * x * x;
+}
+
 __global__ void __launch_bounds__(256)
 segment_sum_rows_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ n_unique, int64_t n_max,
                         const uint32_t* __restrict__ perm, const float* __restrict__ src, int src_stride, int width,
@@ -550,11 +586,28 @@ inline int cont_blocks(ctr_handle* h, int B) {
 
 int ctr_check_embed_cfg(ctr_handle* h, const ctr_embed_cfg* c);   // embed_fwd.cu
 
+extern "C" int ctr_embed_bwd_partials_weighted(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg,
+                                               const uint32_t* sorted_keys, const uint32_t* perm, const uint32_t* uidx,
+                                               int64_t n, const int32_t* field_of_slot, const float* x0, const float* dx0,
+                                               int64_t dx0_ld, const float* sum_e, const float* dlogit, const float* w_fm,
+                                               const float* inv_cnt_emb, const float* inv_cnt_first, const float* cont_grad,
+                                               const float* slot_weight, float* part);
+
 extern "C" int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const uint32_t* sorted_keys,
                                       const uint32_t* perm, const uint32_t* uidx, int64_t n, const int32_t* field_of_slot,
                                       const float* x0, const float* dx0, int64_t dx0_ld, const float* sum_e,
                                       const float* dlogit, const float* w_fm, const float* inv_cnt_emb,
                                       const float* inv_cnt_first, const float* cont_grad, float* part) {
+    return ctr_embed_bwd_partials_weighted(h, s, cfg, sorted_keys, perm, uidx, n, field_of_slot, x0, dx0, dx0_ld, sum_e, dlogit,
+                                           w_fm, inv_cnt_emb, inv_cnt_first, cont_grad, nullptr, part);
+}
+
+extern "C" int ctr_embed_bwd_partials_weighted(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg,
+                                               const uint32_t* sorted_keys, const uint32_t* perm, const uint32_t* uidx,
+                                               int64_t n, const int32_t* field_of_slot, const float* x0, const float* dx0,
+                                               int64_t dx0_ld, const float* sum_e, const float* dlogit, const float* w_fm,
+                                               const float* inv_cnt_emb, const float* inv_cnt_first, const float* cont_grad,
+                                               const float* slot_weight, float* part) {
     int rc = ctr_check_embed_cfg(h, cfg);
     if (rc) return rc;
     CTR_REQUIRE(h, sorted_keys && perm && uidx && dx0 && part && n >= 0, "embed_bwd_partials: null pointer");
@@ -566,6 +619,7 @@ extern "C" int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_emb
     CTR_REQUIRE(h, !cfg->use_fm || (x0 && sum_e && dlogit && w_fm), "embed_bwd_partials: FM inputs null");
     CTR_REQUIRE(h, cfg->M == 0 || (field_of_slot && inv_cnt_emb && inv_cnt_first), "embed_bwd_partials: multi inputs null");
     CTR_REQUIRE(h, dx0_ld >= (int64_t) (cfg->Fc + cfg->Fm) * cfg->k, "embed_bwd_partials: dx0_ld too small");
+    CTR_REQUIRE(h, !slot_weight || cfg->M > 0, "embed_bwd_partials: slot_weight without multi-valued slots");
     if (n == 0) return CTR_OK;
     const int64_t chunks = ctr_cdiv(n, CH);
     const int64_t threads = chunks * (cfg->k / 4);
@@ -573,7 +627,7 @@ extern "C" int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_emb
 #define LAUNCH_BP(KK)                                                                                                  \
     embed_bwd_partials_kernel<KK><<<blocks, 256, 0, ctr_st(s)>>>(*cfg, sorted_keys, perm, uidx, n, field_of_slot, x0, dx0, \
                                                                 dx0_ld, sum_e, dlogit, w_fm, inv_cnt_emb, inv_cnt_first,   \
-                                                                cont_grad, part)
+                                                                cont_grad, slot_weight, part)
     switch (cfg->k) {
         case 4: LAUNCH_BP(4); break;
         case 8: LAUNCH_BP(8); break;
@@ -729,6 +783,25 @@ extern "C" int ctr_scalar_segment_add(ctr_handle* h, ctr_stream s, const uint32_
     scalar_segment_add_kernel<<<grid_for(h, n_max * 8), 256, 0, ctr_st(s)>>>(uniq, seg_start, n_unique, n_max, perm, src,
                                                                              (uint32_t) ld, dst_rows, dst);
     CTR_CHECK_LAUNCH(h, "scalar_segment_add");
+    return CTR_OK;
+}
+
+extern "C" int ctr_scalar_gathered_l2(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const uint32_t* seg_start,
+                                      const uint32_t* n_unique, int64_t n_max, const float* w, float scale, int64_t rows,
+                                      int64_t dense_lo, int dense_n, float dense_count, float* grad, float* sq) {
+    CTR_REQUIRE(h, uniq && seg_start && n_unique && w && grad && sq && rows > 0 && n_max >= 0 && dense_n >= 0 &&
+                       dense_lo >= 0 && dense_lo + dense_n <= rows, "scalar_gathered_l2: bad args");
+    if (n_max > 0) {
+        scalar_gathered_l2_runs_kernel<<<grid_for(h, n_max), 256, 0, ctr_st(s)>>>(uniq, seg_start, n_unique, n_max, w, scale,
+                                                                                 rows, grad, sq);
+        CTR_CHECK_LAUNCH(h, "scalar_gathered_l2_runs");
+    }
+    if (dense_n > 0) {
+        // second launch on the same stream: a wide id may alias a dense row (quirk Q4), so the two never write concurrently
+        scalar_gathered_l2_dense_kernel<<<(unsigned) ctr_cdiv((int64_t) dense_n, 256), 256, 0, ctr_st(s)>>>(
+            w, scale, dense_lo, dense_n, dense_count, grad, sq + n_max);
+        CTR_CHECK_LAUNCH(h, "scalar_gathered_l2_dense");
+    }
     return CTR_OK;
 }
 

@@ -109,3 +109,29 @@ def from_pickled_batch(blob: bytes, id_dtype=np.int32) -> Dict[str, np.ndarray]:
     if len(d.get("wide_feats", [])) == n and n > 0:
         out["wide_feats"] = np.asarray(d["wide_feats"]).astype(id_dtype).reshape(n, -1)
     return out
+
+
+def canonical_batch(d: Dict, spec) -> Dict:
+    """Batch dict with the key names the engine reads.  The textline generation splits the ids over `cat_feats` /
+    `cate_feats` + `mul_cat_feats` (+ `mul_cat_feats_value`) and calls the labels `labels`
+    (utils/data_loader_textline.py:30-34, utils/data_loader_load.py:236-242, where the wide ids are stored as
+    `wide_feats_value` while models/wdl_textline.py:62 reads `wide_feats`: both are accepted)."""
+    if "cate_feats" in d and (spec.M == 0 or "mul_cat_feats" not in d) and "wide_feats_value" not in d:
+        return d
+    out = dict(d)
+    single = d["cate_feats"] if "cate_feats" in d else d["cat_feats"]
+    mul = d.get("mul_cat_feats", d.get("mul_cate_feats"))
+    if spec.M and mul is not None and np.ndim(mul) == 2 and np.shape(single)[1] == spec.Fc:
+        cat = torch.cat if isinstance(single, torch.Tensor) else np.concatenate
+        mul = mul.to(single.dtype) if isinstance(single, torch.Tensor) else np.asarray(mul).astype(np.asarray(single).dtype)
+        out["cate_feats"] = cat([single, mul], 1)
+        val = d.get("mul_cat_feats_value", d.get("mul_cate_feats_value"))
+        if val is not None:
+            out["multi_feats_value"] = val
+    else:
+        out["cate_feats"] = single
+    if "wide_feats" not in d and "wide_feats_value" in d:
+        out["wide_feats"] = d["wide_feats_value"]
+    if "label" not in d and "labels" in d:
+        out["label"] = d["labels"]
+    return out

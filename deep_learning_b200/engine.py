@@ -49,7 +49,12 @@ class CtrEngine:
         self.id_bytes = 8 if s.id_dtype == "int64" else 4
 
         # ---- parameters ---------------------------------------------------------------------
-        self.table = torch.zeros(self.rows_local, s.table_stride, **f32)
+        if (s.frozen_rows or s.weighted_pool) and self.world > 1:
+            raise NotImplementedError("%s: frozen rows / weighted pooling are single-GPU only" % s.alg)
+        # frozen rows (a reference tf.constant looked up like a table, models/dnn_multi_textline.py:46-48) sit behind the
+        # trainable rows: every update kernel is told `rows_local` and never touches them
+        self.table = torch.zeros(self.rows_local + s.frozen_rows, s.table_stride, **f32)
+        self.frozen_off = torch.from_numpy(s.frozen_slot_offset()).to(dev, self.id_torch) if s.frozen_rows else None
         self.dense_shapes = s.dense_param_shapes()
         # flat buffer ordered by regulariser group so Adam needs at most three launches
         order = {"none": 0, "l2": 1, "l1": 2}
@@ -82,6 +87,7 @@ class CtrEngine:
             self._in.append(dict(ids=torch.zeros(B, max(s.ids_ld, 1), dtype=self.id_torch, device=dev),
                                  cont=torch.zeros(B, max(s.C, 1), **f32), vec=torch.zeros(B, max(s.V, 1), **f32),
                                  label=torch.zeros(B, **f32),
+                                 sw=torch.zeros(B, max(s.M, 1), **f32) if s.weighted_pool else None,
                                  wide=torch.zeros(B, max(s.wide_fields, 1), dtype=self.id_torch, device=dev) if s.head == "wdl" else None))
         self._in_free = [torch.cuda.Event(), torch.cuda.Event()]
         self._in_used = [False, False]
@@ -142,6 +148,7 @@ class CtrEngine:
             if s.head == "wdl":
                 # wide ids get their own sorted run structure (gradient of the scalar gather, models/wdl.py:240-246)
                 nw = B * s.wide_fields
+                self.w_sq = torch.zeros(nw + s.hidden[-1] + 1, **f32) if s.gathered_l2 else None
                 self.w_keys, self.w_perm, self.w_uidx, self.w_uniq = (torch.zeros(max(nw, 1), **u32) for _ in range(4))
                 self.w_seg_start = torch.zeros(nw + 2, **u32)
                 self.w_n_unique = torch.zeros(1, **u32)
@@ -222,6 +229,9 @@ class CtrEngine:
         emb = t(emb_np)
         first = t(np.asarray(p[s.first_name], dtype=np.float32).reshape(s.table_rows)[self.rank::self.world]) if s.has_first else None
         self.h.call("ctr_table_pack", st, ptr(emb), ptr(first), emb.shape[0], s.k, s.table_stride, ptr(table))
+        if s.frozen_rows and table is self.table:
+            fz = t(np.asarray(p[s.frozen_name], dtype=np.float32).reshape(s.frozen_rows, s.k))
+            self.h.call("ctr_table_pack", st, ptr(fz), None, s.frozen_rows, s.k, s.table_stride, ptr(table[self.rows_local:]))
         for name, shp in self.dense_shapes:
             a = np.asarray(p[name], dtype=np.float32).reshape(shp)
             if name == "deep_0":
@@ -283,6 +293,11 @@ class CtrEngine:
         first = torch.empty(self.rows_local, dtype=torch.float32, device=self.dev) if s.has_first else None
         self.h.call("ctr_table_unpack", st, ptr(table), self.rows_local, s.k, s.table_stride, ptr(emb), ptr(first))
         out[s.emb_name] = self._assemble_rows(emb)
+        if s.frozen_rows:
+            fz = torch.zeros(s.frozen_rows, s.k, dtype=torch.float32, device=self.dev)
+            if table is self.table:      # the Adam slots of a constant are zero
+                self.h.call("ctr_table_unpack", st, ptr(table[self.rows_local:]), s.frozen_rows, s.k, s.table_stride, ptr(fz), None)
+            out[s.frozen_name] = fz.cpu().numpy()
         if s.has_first:
             out[s.first_name] = self._assemble_rows(first.reshape(-1, 1))
         for name, shp in self.dense_shapes:
@@ -315,6 +330,7 @@ class CtrEngine:
         self._cur_in = i
         t = self._in[i]
         self.ids, self.cont, self.vec, self.label, self.wide = t["ids"], t["cont"], t["vec"], t["label"], t["wide"]
+        self.sw = t["sw"]
 
     def load_batch(self, batch: Dict, non_blocking: bool = True, skip_ids: bool = False) -> int:
         """Make `batch` (host or device arrays/tensors, reference key names) the current device batch.  Returns B
@@ -347,6 +363,13 @@ class CtrEngine:
                 raise ValueError("cate_feats has %d columns, model expects %d" % (cate.shape[1], s.ids_ld))
             if not skip_ids:
                 tgt["ids"][:B].copy_(cate, non_blocking=non_blocking)
+                if self.frozen_off is not None:      # 'tag' slots address the frozen rows behind the trainable table
+                    tgt["ids"][:B] += self.frozen_off
+        if s.weighted_pool:
+            sw = as_t(batch["multi_feats_value"] if "multi_feats_value" in batch else batch["mul_cat_feats_value"], torch.float32)
+            if sw.shape[1] != s.M:
+                raise ValueError("multi_feats_value has %d columns, model expects %d" % (sw.shape[1], s.M))
+            tgt["sw"][:B].copy_(sw, non_blocking=non_blocking)
         cont = as_t(batch["cont_feats"], torch.float32)
         if s.alg == "dnn" and "vector_feats" in batch and batch["vector_feats"] is not None:
             vec = as_t(batch["vector_feats"], torch.float32)
@@ -371,7 +394,7 @@ class CtrEngine:
         s, st, h = self.spec, self._stream(), self.h
         cfg = self._cfg(B)
         if s.Fm:
-            h.call("ctr_pooled_gather_fwd", st, cfg, ptr(self.table), ptr(self.ids), ptr(self.multi_start), None,
+            h.call("ctr_pooled_gather_fwd", st, cfg, ptr(self.table), ptr(self.ids), ptr(self.multi_start), ptr(self.sw),
                    ptr(self.x0), ptr(self.pooled_first), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first))
         h.call("ctr_fm_gather_fwd", st, cfg, ptr(self.table), ptr(self.ids), 0, ptr(self.cont), ptr(self.vec),
                ptr(self._cont_rows()), ptr(self.pooled_first), ptr(self.x0), ptr(self.fm), ptr(self.sum_e))
@@ -479,9 +502,10 @@ class CtrEngine:
             if self.n_extra:
                 h.call("ctr_fm_cont_bwd", st, cfg, ptr(self.cont), ptr(self._cont_rows()), ptr(self.sum_e),
                        ptr(self.dlogit), ptr(w_fm), ptr(self.cont_grad), ws, wsn)
-            h.call("ctr_embed_bwd_partials", st, cfg, ptr(self.keys), ptr(self.perm), ptr(self.uidx), n,
+            h.call("ctr_embed_bwd_partials_weighted", st, cfg, ptr(self.keys), ptr(self.perm), ptr(self.uidx), n,
                    ptr(self.field_of_slot), ptr(self.x0), ptr(self.dx0), self.dx0_ld, ptr(self.sum_e), ptr(self.dlogit),
-                   ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.part))
+                   ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.sw),
+                   ptr(self.part))
             self._mark("partials")
             self._sparse_update(B, n, hp)
             self._mark("sparse_update")
@@ -490,7 +514,7 @@ class CtrEngine:
         if self.adam_mode == "tf_dense":
             # TF1 Adam moves EVERY row each step (m, v decay; theta -= lr_t*m/(sqrt(v)+eps)) -- exact mode
             h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
-                   self.table.numel(), 0.0, 0.0, ptr(self.touched), s.table_stride, hp)
+                   self.rows_local * s.table_stride, 0.0, 0.0, ptr(self.touched), s.table_stride, hp)
         # ---- dense side: one Adam launch per regulariser group ---------------------------------------------
         for gi, (l2, l1) in enumerate(((0.0, 0.0), (s.l2_reg, 0.0), (0.0, s.l2_reg))):
             a, b = self.groups[gi]
@@ -530,7 +554,7 @@ class CtrEngine:
         self.ev_batch.record(main)
         self.side.wait_event(self.ev_batch)
         n = B * s.ids_ld + self.n_extra
-        key_bits = max(1, int(s.table_rows - 1).bit_length())
+        key_bits = max(1, int(s.table_rows + s.frozen_rows - 1).bit_length())
         st, ws, wsn = self.side.cuda_stream, ptr(self.ws_sort), self.ws_sort.numel()
         h.call("ctr_sort_ids", st, ptr(self.ids), self.id_bytes, B, s.ids_ld, 0, s.ids_ld, 0, int(s.zero_row0),
                s.cont_base, self.n_extra, 1, 0, key_bits, ptr(self.keys), ptr(self.perm), ws, wsn)
@@ -562,6 +586,38 @@ class CtrEngine:
         self.h.call("ctr_scalar_segment_add", self._stream(), ptr(self.w_uniq), ptr(self.w_seg_start), ptr(self.w_n_unique),
                     B * s.wide_fields, ptr(self.w_perm), ptr(self.dlogit), s.wide_fields, s.wide_rows + s.hidden[-1],
                     ptr(self.view("wdl_weights", self.grad)))
+        self._gathered_l2_term(B)
+
+    def _gathered_l2_term(self, B: int) -> None:
+        """quirk Q6 (models/wdl_textline.py:264-269,284-286): l2 over the gathered [B, W+H] weights; the deep rows
+        W..W+H-1 are looked up once per sample.  Gradient goes on top of the wdl_weights gradient, the local share of the
+        loss term into self.loss BEFORE the dense reduction, so the sum over ranks is the term of the global batch."""
+        s = self.spec
+        if not (s.gathered_l2 and s.l2_reg > 0):
+            return
+        nw, H = B * s.wide_fields, s.hidden[-1]
+        self.h.call("ctr_scalar_gathered_l2", self._stream(), ptr(self.w_uniq), ptr(self.w_seg_start), ptr(self.w_n_unique),
+                    nw, ptr(self.view("wdl_weights")), s.l2_reg, s.wide_rows + H, s.wide_fields, H, float(B),
+                    ptr(self.view("wdl_weights", self.grad)), ptr(self.w_sq))
+        self.h.call("ctr_reduce", self._stream(), ptr(self.w_sq), nw + H, 0, ptr(self.reg_terms[3:4]), ptr(self.ws),
+                    self.ws.numel())
+        self.loss.add_(self.reg_terms[3:4], alpha=0.5 * s.l2_reg)
+
+    def eval_loss(self, batch: Optional[Dict] = None) -> torch.Tensor:
+        """`sess.run([label, out, loss])` without the optimizer (the evaluation half of the textline fit loops,
+        models/wdl_textline.py:313, models/dnn_multi_textline.py:185): the loss of `batch` under the current weights,
+        scores in self.score.  One GPU."""
+        if not self.train_mode or self.world > 1:
+            raise _lib.CtrError("eval_loss needs a single-GPU training engine")
+        s = self.spec
+        B = self.load_batch(batch) if batch is not None else self.last_batch
+        self.forward(B, with_loss=True)
+        if s.gathered_l2 and s.l2_reg > 0:
+            self._sort_wide(B, self._stream())
+            self._gathered_l2_term(B)
+        reg = self._reg_loss()
+        loss = self.loss.clone()
+        return loss if reg is None else loss + reg
 
     # ---- public step API -------------------------------------------------------------------------------
     def train_step(self, batch: Optional[Dict] = None, next_batch: Optional[Dict] = None) -> torch.Tensor:

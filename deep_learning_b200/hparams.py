@@ -35,3 +35,8 @@ class ModelParams:
     alg_name: str = "deepfm"
     action_type: str = "train"
     num_batch_size: int = 100           # print_num_batch (local_run_test.py:79)
+    print_iter: int = 10                # textline fit loops (local_run_textline.py:189)
+    word2vec_embedding_path: str = ""   # models/dnn_multi_textline.py:32
+    word2vec_rows: int = 0              # rows of that table when the weights are injected instead of loaded
+    max_data_size: int = 1 << 62        # utils/data_loader_load.py:45
+    vector_field_size: int = 0          # utils/data_loader_load.py:109 (its spelling of vector_feats_size)

@@ -34,6 +34,9 @@ def init_weights(spec: ModelSpec, seed: int = 2019, with_table: bool = True) -> 
         p["weight_mat"] = g.uniform(-lim, lim, size=(R, k)).astype(np.float32)
     else:
         p[spec.emb_name] = g.normal(0.0, 0.01, size=(R, k)).astype(np.float32)
+    if spec.frozen_rows and with_table:
+        # stand-in for the word2vec table the reference loads from disk (models/dnn_multi_textline.py:46-48)
+        p[spec.frozen_name] = g.normal(0.0, 0.1, size=(spec.frozen_rows, k)).astype(np.float32)
     if spec.first_name and with_table:
         p[spec.first_name] = g.uniform(0.0, 1.0, size=(R, 1)).astype(np.float32)
     shapes = dict(spec.dense_param_shapes())
@@ -86,8 +89,8 @@ class BaseDeepModel:
     # ---- batch decoding ---------------------------------------------------------------------------
     def _decode(self, item) -> Dict:
         if isinstance(item, (bytes, bytearray)):
-            return _data.from_pickled_batch(bytes(item), np.int64 if self.spec.id_dtype == "int64" else np.int32)
-        return item
+            item = _data.from_pickled_batch(bytes(item), np.int64 if self.spec.id_dtype == "int64" else np.int32)
+        return _data.canonical_batch(item, self.spec)
 
     # ---- persistence: the reference exports a SavedModel (.pb, models/deepfm.py:193-211) and, for the
     # tf.data generation, a Saver checkpoint with the Adam slots (models/deepfm_multi.py:308-310).
@@ -198,6 +201,48 @@ class BaseDeepModel:
             except Exception as e:
                 print("Fail to export saved model, exception: {}".format(e))
                 sys.stdout.flush()
+
+    # ---- textline generation: fit(print_iter, num_batch_size) (models/wdl_textline.py:302-357,
+    # models/dnn_multi_textline.py:174-228) ---------------------------------------------------------------
+    def _fit_c(self, print_iter: int, num_batch_size: int) -> None:
+        """Every pass of the loop first EVALUATES one batch of the iterator (`sess.run([label, out, loss])`: the iterator
+        advances, no update) and then, unless it just printed, TRAINS on the next one (`sess.run([loss, optimizer])`).
+        Every `print_iter`-th evaluated batch is kept for the AUC; after `num_batch_size` kept batches the AUC of those
+        batches is printed with sum(losses) / (count * print_iter)."""
+        it = iter(self.data_dict)
+        pred_list, label_list, losses, count = [], [], [], 0
+        start_time = time.time()
+        i = 0
+        while True:
+            try:
+                b = self._decode(next(it))
+                losses.append(self.engine.eval_loss(b))
+                if i % print_iter == 0 and i > 0:
+                    count += 1
+                    B = self.engine.last_batch
+                    label_list.append(self.engine.label[:B].clone())
+                    pred_list.append(self.engine.score[:B].clone())
+                if count == num_batch_size:
+                    total_loss = float(torch.stack(losses).sum().item() / (count * print_iter))
+                    auc = self.engine.auc(torch.cat(pred_list), torch.cat(label_list))
+                    end_time = time.time()
+                    print("[{}] test auc:{}\t loss:{} time:{:.2f}s".format(i, auc, total_loss, end_time - start_time))
+                    sys.stdout.flush()
+                    start_time = time.time()
+                    pred_list, label_list, losses, count = [], [], [], 0
+                else:
+                    self.engine.train_step(self._decode(next(it)))
+            except StopIteration:      # replaces tf.errors.OutOfRangeError
+                print("--------------End of Dataset-------------")
+                sys.stdout.flush()
+                if self.model_pb:
+                    try:
+                        self.save(self.model_pb)
+                    except Exception as e:
+                        print("Fail to export saved model, exception: {}".format(e))
+                        sys.stdout.flush()
+                break
+            i += 1
 
     @staticmethod
     def get_val_data(sess, data: Iterable) -> List[Dict]:

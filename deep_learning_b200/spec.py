@@ -37,6 +37,11 @@ class ModelSpec:
     wide_fields: int = 0        # W (wdl)
     wide_rows: int = 0          # rows of wdl_weights minus H (wdl)
     id_dtype: str = "int32"
+    gathered_l2: bool = False   # wdl_textline quirk Q6: the l2 term runs over the GATHERED wdl_weights [B, W+H]
+    weighted_pool: bool = False  # multi-valued slots carry a weight (mul_cat_feats_value, models/dnn_multi_textline.py:96-101)
+    frozen_name: Optional[str] = None     # reference constant appended to the table as never-updated rows ('tags_emb')
+    frozen_rows: int = 0
+    frozen_fields: Tuple[int, ...] = ()   # multi-valued fields that look up the frozen rows (feat_name == 'tag')
 
     @property
     def Fm(self) -> int:
@@ -113,6 +118,15 @@ class ModelSpec:
         cont = np.arange(C)
         second = C + Fc + Fm + np.arange(k)
         return np.concatenate([single, multi, cont, second]).astype(np.int64)
+
+    def frozen_slot_offset(self) -> np.ndarray:
+        """per column of the id matrix: what to add to a raw id so it addresses the frozen rows appended behind the
+        trainable table (slots of the `frozen_fields`), 0 elsewhere"""
+        off = np.zeros(max(self.ids_ld, 1), dtype=np.int64)
+        for j in self.frozen_fields:
+            s0, s1 = self.multi_ranges[j]
+            off[self.Fc + s0:self.Fc + s1] = self.table_rows
+        return off
 
     def multi_start(self) -> np.ndarray:
         if not self.multi_ranges:
@@ -199,6 +213,29 @@ def spec_from_hparams(alg: str, hp) -> ModelSpec:
                          table_rows=int(hp.cate_feats_size), emb_name="feats_emb", first_name=None, zero_row0=True,
                          multi_ranges=_ranges(hp) if alg == "dnn_multi_cate" else [], head="dnn", l2_reg=l2,
                          reg={"deep_res": "l2"}, id_dtype="int64")
+    if alg == "dnn_multi_textline":
+        # models/dnn_multi_textline.py:16-48,69-161: its own attribute spellings (cat_field_size, cat_index_size) are
+        # accepted next to the canonical ones; row-0-zero `weight_mat`, frozen word2vec constant for the 'tag' field,
+        # weighted pooling, L1 on the tower weights
+        g = lambda a, b: int(getattr(hp, a, 0) or getattr(hp, b, 0))
+        ranges = getattr(hp, "multi_feats_range", None) or getattr(hp, "mul_cat_index_range", [])
+        frozen = tuple(j for j, r in enumerate(ranges) if len(r) > 2 and r[2] == "tag")
+        w2v = int(getattr(hp, "word2vec_rows", 0))
+        if frozen and w2v <= 0:
+            raise ValueError("dnn_multi_textline: a 'tag' field needs word2vec_rows (rows of the frozen tags_emb table)")
+        return ModelSpec(alg, C=int(hp.cont_field_size), V=0, Fc=g("cate_field_size", "cat_field_size"), k=k, hidden=H,
+                         table_rows=g("cate_feats_size", "cat_index_size"), emb_name="weight_mat", first_name=None,
+                         zero_row0=True, multi_ranges=[(int(r[0]), int(r[1])) for r in ranges], head="dnn", l2_reg=l2,
+                         reg={"deep_%d" % i: "l1" for i in range(len(H))}, weighted_pool=True,
+                         frozen_name="tags_emb" if frozen else None, frozen_rows=w2v if frozen else 0,
+                         frozen_fields=frozen)
+    if alg == "wdl_textline":
+        # models/wdl_textline.py:43-50 (row-0-zero table), :278-294 (l2 on the gathered wdl_weights, quirk Q6)
+        reg = {"deep_%d" % i: "l2" for i in range(len(H))}
+        return ModelSpec(alg, C=int(hp.cont_field_size), V=0, Fc=int(hp.cate_field_size), k=k, hidden=H,
+                         table_rows=int(hp.cate_index_size), emb_name="weight_mat", first_name=None, zero_row0=True,
+                         head="wdl", head_w_name="wdl_weights", head_b_name="wdl_bias", l2_reg=l2, reg=reg,
+                         wide_fields=int(hp.wide_field_size), wide_rows=int(hp.cate_index_size), gathered_l2=True)
     if alg == "wdl":
         reg = {"deep_%d" % i: "l2" for i in range(len(H))}
         reg["wdl_weights"] = "l2"

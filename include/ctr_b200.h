@@ -240,6 +240,15 @@ int ctr_embed_bwd_partials(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg
                            const float* cont_grad /*[C, grad_stride] or NULL: gradient of the appended
                            continuous-field entries (perm >= B*ids_ld), from ctr_fm_cont_bwd */,
                            float* part);
+/* same with per-slot weights of the multi-valued block (slot_weight [B, M] or NULL): the gradient of slot (b, t) is
+ * additionally scaled by slot_weight[b, t] -- the backward of the weighted pooling of
+ * models/dnn_multi_textline.py:96-102 (sum_t w[b,t] * E[b,t,:] / count). */
+int ctr_embed_bwd_partials_weighted(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg,
+                                    const uint32_t* sorted_keys, const uint32_t* perm, const uint32_t* uidx, int64_t n,
+                                    const int32_t* field_of_slot, const float* x0, const float* dx0, int64_t dx0_ld,
+                                    const float* sum_e, const float* dlogit, const float* w_fm,
+                                    const float* inv_cnt_emb, const float* inv_cnt_first, const float* cont_grad,
+                                    const float* slot_weight, float* part);
 /* grads[u, :] = sum of the partials of run u, in chunk order (deterministic) */
 int ctr_embed_bwd_finalize(ctr_handle* h, ctr_stream s, const uint32_t* seg_start, const uint32_t* n_unique,
                            int64_t n_max, int width, int grad_stride, const float* part, float* grads);
@@ -258,6 +267,16 @@ int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const
 int ctr_scalar_segment_add(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const uint32_t* seg_start,
                            const uint32_t* n_unique, int64_t n_max, const uint32_t* perm, const float* src,
                            int ld, int64_t dst_rows, float* dst);
+
+/* l2 regulariser over GATHERED scalar weights (models/wdl_textline.py:264-269 overwrites weights["wdl_weights"] with
+ * the [B, W+H] lookup result before :284-286 regularises it):  for run u of the sorted wide ids with c = run length,
+ *   grad[uniq[u]] += scale * c * w[uniq[u]],  sq[u] = c * w^2   (sq[u] = 0 for u >= *n_unique);
+ * then for the dense_n rows from dense_lo (the deep-projection rows, each looked up dense_count = B times):
+ *   grad[r] += scale * dense_count * w[r],  sq[n_max + j] = dense_count * w[r]^2.
+ * loss term = scale/2 * sum(sq[0 .. n_max + dense_n))  (ctr_reduce mode 0).  Deterministic: one writer per row. */
+int ctr_scalar_gathered_l2(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const uint32_t* seg_start,
+                           const uint32_t* n_unique, int64_t n_max, const float* w, float scale, int64_t rows,
+                           int64_t dense_lo, int dense_n, float dense_count, float* grad, float* sq);
 
 /* owner-side reduction of row gradients received from several peers (multi-GPU):
  *   dst[u, :width] = sum_{i in run u} src[perm[i], :width]   in run order.  The runs come from a STABLE sort of
@@ -359,6 +378,36 @@ int ctr_merge_sorted_segments(ctr_handle* h, ctr_stream s, const uint32_t* keys,
  * (8 slots per CTA: start, setup done, last MMA committed, accumulator ready, epilogue done, CTA synced, TMEM freed);
  * this copies the last launch's records to the host. */
 int ctr_debug_gemm_trace(unsigned long long* host, int n_ctas);
+
+/* ---- host-side input decoding ---------------------------------------------
+ * No handle, no stream, no device work: bytes in host memory -> row-major arrays in caller-owned (pinned) host
+ * memory.  The caller then issues one cudaMemcpyAsync per tensor.
+ *
+ * ctr_parse_lines replaces the per-line Python of utils/data_loader_load.py:94-139 (load_process), :142-184
+ * (load_test) and the tf.data graphs of utils/data_loader_load.py:187-243 / utils/data_loader_textline.py:4-36.
+ * Line format: `label,c c c,id id id[,third]` -- columns split on ',', values on ONE space (str.split(" ")).
+ *   n_cont     floats in column 1 (the reference's cont_field_size: continuous values followed by the vector block)
+ *   n_cate     integer ids in column 2
+ *   third_kind 0: no column 3;  1: n_third integer ids (wide_feats, :125-127);  2: n_third `id=value` pairs
+ *              (get_libsvm_value, :12-21) -> host_third_ids + host_third_vals
+ *   id_bytes   4 or 8: element size of host_cate / host_third_ids
+ * Floats are converted like Python's float() followed by a cast to float32.  Only complete lines (terminated by a
+ * newline) are consumed, at most max_rows of them; blank lines are skipped.  *host_consumed = bytes to drop from the
+ * front of the buffer before the next call.  n_threads <= 0: all host threads.
+ * Returns CTR_E_INVALID on a malformed line, with *host_bad_line = its index among the non-blank lines. */
+int ctr_parse_lines(const char* host_buf, int64_t len, int n_cont, int n_cate, int third_kind, int n_third,
+                    int id_bytes, int64_t max_rows, int n_threads, float* host_label, float* host_cont,
+                    void* host_cate, void* host_third_ids, float* host_third_vals, int64_t* host_n_rows,
+                    int64_t* host_consumed, int64_t* host_bad_line);
+
+/* TFRecord framing + tf.Example decoding for the FixedLenFeature spec of utils/data_loader.py:7-24:
+ *   label [1] f32, cont_feats [n_cont] f32 (n_cont = 0: key not in the spec, the *_cate generation), vector_feats
+ *   [n_vec] f32, cate_feats [n_cate] i64.  Unknown keys are ignored, a missing key is an error (no defaults in the
+ *   reference spec).  verify_crc != 0 checks both masked CRC-32C words of every record.
+ * Only complete records are consumed, at most max_rows. */
+int ctr_parse_tfrecords(const char* host_buf, int64_t len, int n_cont, int n_vec, int n_cate, int verify_crc,
+                        int64_t max_rows, float* host_label, float* host_cont, float* host_vec,
+                        int64_t* host_cate, int64_t* host_n_rows, int64_t* host_consumed);
 
 #ifdef __cplusplus
 }

@@ -58,6 +58,7 @@ class HParams:
     restore_model_checkpoint: str = ""
     model_restore: int = 0
     cate_feats_conf_path: str = ""
+    word2vec_rows: int = 0                # rows of the frozen `tags_emb` constant (models/dnn_multi_textline.py:47-48)
 
 
 # --------------------------------------------------------------------------------------
@@ -406,16 +407,88 @@ def _dnn_variant_loss(fwd):
     return loss_fn
 
 
+def wdl_textline_forward(p, batch, hp: HParams, with_gathered: bool = False):
+    """models/wdl_textline.py:43-50 (row-0-zero embedding table), :133-235 (deep part), :237-276 (wide & deep).
+    Same index construction as models/wdl.py (quirk Q4: deep weights alias wide ids W..W+H-1)."""
+    C, Fc, k, W = hp.cont_field_size, hp.cate_field_size, hp.embedding_size, hp.wide_field_size
+    cate, cont, wide = batch['cate_feats'].long(), batch['cont_feats'], batch['wide_feats'].long()
+    B = cont.shape[0]
+    H = hp.hidden_units[-1]
+    embeddings = zero_row0(p['weight_mat'])                                    # :50
+    cat_emb = embedding_lookup(embeddings, cate).reshape(B, Fc * k)            # :142-143
+    dense_vector = torch.cat([cont, cat_emb], dim=1)                           # :190
+    deep = mlp_tower(dense_vector, p, len(hp.hidden_units))                    # :215-221
+    deep_index_add = torch.arange(H).unsqueeze(0).expand(B, H) + W             # :232
+    idx = torch.cat([wide, deep_index_add], dim=1)                             # :262
+    val = torch.cat([torch.ones(B, W, dtype=cont.dtype), deep], dim=1)         # :263
+    gathered = embedding_lookup(p['wdl_weights'], idx).reshape(B, W + H)       # :264-269
+    out = (gathered * val).sum(dim=1, keepdim=True) + p['wdl_bias']            # :271-273
+    if with_gathered:
+        return out, torch.sigmoid(out), gathered
+    return out, torch.sigmoid(out)
+
+
+def wdl_textline_loss(p, batch, hp: HParams):
+    """models/wdl_textline.py:278-294.  Quirk Q6: `self.weights["wdl_weights"]` was overwritten at :264 by the
+    GATHERED tensor [B, W+H], so the l2 term sums w^2 over every lookup of the batch (a row looked up c times counts
+    c times, each deep row counts B times) instead of over the table."""
+    out, score, gathered = wdl_textline_forward(p, batch, hp, with_gathered=True)
+    loss = log_loss(batch['label'], score)
+    if hp.l2_reg > 0:
+        loss = loss + l2_regularizer(hp.l2_reg, gathered)
+        for i in range(len(hp.hidden_units)):
+            loss = loss + l2_regularizer(hp.l2_reg, p['deep_%d' % i])
+    return loss, out, score
+
+
+def dnn_multi_textline_forward(p, batch, hp: HParams):
+    """models/dnn_multi_textline.py:37-48 (row-0-zero `weight_mat`, frozen `tags_emb` constant), :69-151.
+    Batch keys are the canonical ones of this repo: cate_feats = [cat_feats | mul_cat_feats] (the reference feeds the two
+    blocks as separate tensors, :55-57), multi_feats_value = mul_cat_feats_value.  Weighted pooling (:94-103): the count
+    is taken on the UNWEIGHTED rows (row sum != 0), the sum on the weighted ones."""
+    Fc, k = hp.cate_field_size, hp.embedding_size
+    cate, cont, val = batch['cate_feats'].long(), batch['cont_feats'], batch['multi_feats_value']
+    B = cont.shape[0]
+    embeddings = zero_row0(p['weight_mat'])                                    # :44
+    cat_emb = embedding_lookup(embeddings, cate[:, :Fc]).reshape(B, Fc * k)    # :73-74
+    multi = cate[:, Fc:]
+    pooled = []
+    for item in hp.multi_feats_range:                                          # :77-110
+        s, e, name = int(item[0]), int(item[1]), item[2]
+        table = p['tags_emb'].detach() if name == 'tag' else embeddings        # :84-90: tf.constant has no gradient
+        emb = embedding_lookup(table, multi[:, s:e])
+        nonzero = (emb.sum(dim=2) != 0).sum(dim=1, keepdim=True).to(emb.dtype)  # :93-94
+        wsum = (emb * val[:, s:e].unsqueeze(2)).sum(dim=1)                     # :96-101
+        safe = torch.where(nonzero == 0, torch.ones_like(nonzero), nonzero)
+        pooled.append(torch.where(nonzero == 0, torch.zeros_like(wsum), wsum / safe))   # :102 div_no_nan
+    dense_vector = torch.cat([cont, cat_emb] + pooled, dim=1)                  # :113-114
+    deep = mlp_tower(dense_vector, p, len(hp.hidden_units))
+    out = deep @ p['deep_res'] + p['deep_res_bias']                            # :151
+    return out, torch.sigmoid(out)
+
+
+def dnn_multi_textline_loss(p, batch, hp: HParams):
+    """models/dnn_multi_textline.py:153-161 -- L1 on the tower weights, as models/dnn.py (quirk Q5)."""
+    out, score = dnn_multi_textline_forward(p, batch, hp)
+    loss = log_loss(batch['label'], score)
+    if hp.l2_reg > 0:
+        for i in range(len(hp.hidden_units)):
+            loss = loss + l1_regularizer(hp.l2_reg, p['deep_%d' % i])
+    return loss, out, score
+
+
 FORWARD = {'deepfm': deepfm_forward, 'deepfm_multi': deepfm_multi_forward, 'wdl': wdl_forward,
            'dnn': dnn_forward, 'dnn_multi': dnn_multi_forward,
            'deepfm_cate': deepfm_cate_forward, 'deepfm_multi_cate': deepfm_multi_cate_forward,
-           'dnn_pipeline': dnn_pipeline_forward, 'dnn_cate': dnn_pipeline_forward, 'dnn_multi_cate': dnn_multi_cate_forward}
+           'dnn_pipeline': dnn_pipeline_forward, 'dnn_cate': dnn_pipeline_forward, 'dnn_multi_cate': dnn_multi_cate_forward,
+           'wdl_textline': wdl_textline_forward, 'dnn_multi_textline': dnn_multi_textline_forward}
 LOSS = {'deepfm': deepfm_loss, 'deepfm_multi': deepfm_multi_loss, 'wdl': wdl_loss,
         'dnn': dnn_loss, 'dnn_multi': dnn_multi_loss,
         'deepfm_cate': _deepfm_variant_loss(deepfm_cate_forward),
         'deepfm_multi_cate': _deepfm_variant_loss(deepfm_multi_cate_forward),
         'dnn_pipeline': _dnn_variant_loss(dnn_pipeline_forward), 'dnn_cate': _dnn_variant_loss(dnn_pipeline_forward),
-        'dnn_multi_cate': _dnn_variant_loss(dnn_multi_cate_forward)}
+        'dnn_multi_cate': _dnn_variant_loss(dnn_multi_cate_forward),
+        'wdl_textline': wdl_textline_loss, 'dnn_multi_textline': dnn_multi_textline_loss}
 # variants without a continuous block read cont_field_size as 0 (their model files never define it)
 NO_CONT = ('deepfm_cate', 'deepfm_multi_cate', 'dnn_cate', 'dnn_multi_cate')
 
@@ -437,8 +510,10 @@ def deep_input_size(alg: str, hp: HParams) -> int:
         return hp.vector_feats_size + hp.cate_field_size * k
     if alg == 'dnn_pipeline':
         return hp.cont_field_size + hp.vector_feats_size + hp.cate_field_size * k
-    if alg == 'wdl':
+    if alg in ('wdl', 'wdl_textline'):
         return hp.cont_field_size + hp.cate_field_size * k
+    if alg == 'dnn_multi_textline':
+        return hp.cont_field_size + (hp.cate_field_size + hp.multi_field_size) * k
     if alg == 'dnn':
         return hp.cont_field_size + hp.vector_feats_size + hp.cate_field_size * k
     raise ValueError(alg)
@@ -454,11 +529,13 @@ def param_shapes(alg: str, hp: HParams) -> Dict[str, Tuple[int, ...]]:
     elif alg == 'deepfm_multi':                           # models/deepfm_multi.py:124-128
         R = hp.cate_feats_size + hp.cont_field_size
         s['feats_emb'] = (R, k); s['fm_first_order_emb'] = (R, 1)
-    elif alg == 'wdl':                                    # models/wdl.py:43-47,231-236
+    elif alg in ('wdl', 'wdl_textline'):                  # models/wdl.py:43-47,231-236, models/wdl_textline.py:44-47,253-256
         s['weight_mat'] = (hp.cate_index_size, k)
         s['wdl_weights'] = (hp.cate_index_size + H[-1], 1); s['wdl_bias'] = (1,)
     elif alg == 'dnn':                                    # models/dnn.py:49-52
         s['weight_mat'] = (hp.cate_feats_size, k)
+    elif alg == 'dnn_multi_textline':                     # models/dnn_multi_textline.py:38-48 (tags_emb: frozen constant)
+        s['weight_mat'] = (hp.cate_feats_size, k); s['tags_emb'] = (hp.word2vec_rows, k)
     elif alg in ('dnn_multi', 'dnn_pipeline', 'dnn_cate', 'dnn_multi_cate'):   # models/dnn_multi.py:71-73, dnn_pipeline.py:69-71
         s['feats_emb'] = (hp.cate_feats_size, k)
     elif alg in ('deepfm_cate', 'deepfm_multi_cate'):     # models/deepfm_cate.py:73-77
@@ -472,7 +549,7 @@ def param_shapes(alg: str, hp: HParams) -> Dict[str, Tuple[int, ...]]:
     if alg in ('deepfm_cate', 'deepfm_multi_cate'):
         F = hp.cate_field_size + (hp.multi_field_size if alg == 'deepfm_multi_cate' else 0)
         s['deep_fm_weight'] = (F + k + H[-1], 1); s['deep_fm_bias'] = (1,)
-    if alg in ('dnn', 'dnn_multi', 'dnn_pipeline', 'dnn_cate', 'dnn_multi_cate'):
+    if alg in ('dnn', 'dnn_multi', 'dnn_pipeline', 'dnn_cate', 'dnn_multi_cate', 'dnn_multi_textline'):
         s['deep_res'] = (H[-1], 1); s['deep_res_bias'] = (1, 1)
     return s
 
@@ -489,6 +566,8 @@ def init_params(alg: str, hp: HParams, seed: int = 2019, dtype=torch.float64) ->
             a = g.normal(0.0, 0.01, size=shp)
         elif name in ('feats', 'fm_first_order_emb'):
             a = g.uniform(0.0, 1.0, size=shp)
+        elif name == 'tags_emb':
+            a = g.normal(0.0, 0.1, size=shp)
         elif name == 'weight_mat':
             lim = math.sqrt(6.0 / (shp[0] + shp[1])); a = g.uniform(-lim, lim, size=shp)
         elif name == 'wdl_weights':
@@ -594,6 +673,13 @@ def touched_rows(alg: str, batch, hp: HParams) -> Dict[str, Tensor]:
         out['feats_emb'] = mk; out['fm_first_order_emb'] = mk
     elif alg == 'wdl':
         out['weight_mat'] = mask(shapes['weight_mat'][0], cate)
+    elif alg == 'wdl_textline':
+        out['weight_mat'] = mask(shapes['weight_mat'][0], cate, drop0=True)
+    elif alg == 'dnn_multi_textline':
+        Fc = hp.cate_field_size
+        cols = [cate[:, :Fc].reshape(-1)] + [cate[:, Fc + int(r[0]):Fc + int(r[1])].reshape(-1)
+                                             for r in hp.multi_feats_range if r[2] != 'tag']
+        out['weight_mat'] = mask(shapes['weight_mat'][0], torch.cat(cols), drop0=True)
     elif alg == 'dnn':
         out['weight_mat'] = mask(shapes['weight_mat'][0], cate)
     elif alg in ('dnn_multi', 'dnn_pipeline', 'dnn_cate', 'dnn_multi_cate'):

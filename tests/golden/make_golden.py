@@ -27,8 +27,9 @@ from deep_learning_b200 import data as D   # noqa: E402
 
 BASE = ("deepfm", "deepfm_multi", "wdl", "dnn", "dnn_multi")
 VARIANTS = ("deepfm_cate", "deepfm_multi_cate", "dnn_pipeline", "dnn_cate", "dnn_multi_cate")
+TEXTLINE = ("wdl_textline", "dnn_multi_textline")
 MULTI = ("deepfm_multi", "dnn_multi", "deepfm_multi_cate", "dnn_multi_cate")
-ROW0 = MULTI + ("deepfm_cate", "dnn_cate", "dnn_pipeline")          # row-0-zero tables: id 0 is padding
+ROW0 = MULTI + ("deepfm_cate", "dnn_cate", "dnn_pipeline", "wdl_textline")          # row-0-zero tables: id 0 is padding
 
 
 def tiny_hp(alg):
@@ -40,25 +41,31 @@ def tiny_hp(alg):
         kw.update(cont_field_size=0)
     if alg in VARIANTS:
         kw.update(vector_feats_size=2)
-    if alg == "wdl":
+    if alg in ("wdl", "wdl_textline"):
         kw.update(cate_index_size=60, wide_field_size=5)
+    if alg == "dnn_multi_textline":
+        kw.update(cate_feats_size=81, multi_feats_size=8, multi_field_size=2, multi_feats_range=[[0, 3, "kw"], [3, 8, "tag"]],
+                  word2vec_rows=12)
     return O.HParams(**kw)
 
 
 def tiny_batch(alg, hp, seed):
+    if alg == "dnn_multi_textline":
+        import ctr_helpers as H
+        return H.make_textline_batch(hp, seed)
     multi, row0 = alg in MULTI, alg in ROW0
     if multi:
         sizes, msizes, tops = D.field_sizes(60, 5), [10, 10], [3, 5]
     else:
         sizes, msizes, tops = D.field_sizes(hp.cate_feats_size - (1 if row0 else 0), 5), [], []
     return D.synthetic_batch(hp.batch_size, hp.cont_field_size, hp.cate_field_size, sizes, seed, V=hp.vector_feats_size,
-                             multi_top_n=tops, multi_sizes=msizes, wide=hp.wide_field_size if alg == "wdl" else 0,
+                             multi_top_n=tops, multi_sizes=msizes, wide=hp.wide_field_size if alg in ("wdl", "wdl_textline") else 0,
                              dist="uniform", reserve_zero=row0, id_dtype=torch.int64 if row0 else torch.int32)
 
 
 def main():
     only = sys.argv[1:]      # optional: regenerate just these models (the committed files of the others stay byte-identical)
-    for alg in (only or BASE + VARIANTS):
+    for alg in (only or BASE + VARIANTS + TEXTLINE):
         hp = tiny_hp(alg)
         p = O.init_params(alg, hp, seed=2019, dtype=torch.float64)
         # golden inputs are the fp32-representable values (what gets injected into the CUDA engine)

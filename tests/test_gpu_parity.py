@@ -162,6 +162,51 @@ def test_variants_behind_the_same_kernels(alg):
     _run_parity(alg, hp, steps=2, B=256, adam_mode="lazy")
 
 
+@pytest.mark.parametrize("alg", ["wdl_textline", "dnn_multi_textline"])
+def test_textline_models(alg):
+    """models/wdl_textline.py (row-0-zero table, l2 over the GATHERED wdl_weights -- quirk Q6) and
+    models/dnn_multi_textline.py (weighted pooling, frozen word2vec rows for the 'tag' field, L1 on the tower)"""
+    hp = H.hp_textline(alg, l2_reg=1e-4)
+    eng = _run_parity(alg, hp, steps=3, B=256)
+    _run_parity(alg, hp, steps=2, B=200, adam_mode="lazy")
+    if alg == "dnn_multi_textline":
+        # the constant never moves and carries no Adam state
+        p0 = O.init_params(alg, hp, seed=2019, dtype=torch.float64)
+        assert np.array_equal(eng.get_weights()["tags_emb"], p0["tags_emb"].float().numpy())
+        m, v = eng.get_optimizer_state()
+        assert not m["tags_emb"].any() and not v["tags_emb"].any()
+
+
+def test_textline_module_fit_loop(tmp_path, capsys):
+    """launcher-facing surface of the textline generation (local_run_textline.py:186-189): DeepModel(mp, iterator)
+    .fit(print_iter, num_batch_size) alternates an evaluated batch and a trained batch, prints the AUC of the kept
+    evaluation batches, exports at the end of the iterator; predict() reloads the export"""
+    import deep_learning_b200.models.wdl_textline as alg_model
+    from deep_learning_b200 import data as D
+    hp = H.hp_textline("wdl_textline", batch_size=128)
+    hp.model_pb = str(tmp_path / "pb")
+    batches = [H.make_batch("wdl_textline", hp, seed=500 + s, B=128) for s in range(21)]
+    # the loader stores the wide ids under `wide_feats_value` and the labels under `labels` (utils/data_loader_load.py:236-242)
+    raw = [{"labels": b["label"], "cont_feats": b["cont_feats"], "cate_feats": b["cate_feats"], "wide_feats_value": b["wide_feats"]}
+           for b in batches]
+    m = alg_model.DeepModel(hp, iter(raw), adam_mode="lazy")
+    m.fit(print_iter=2, num_batch_size=2)
+    out = capsys.readouterr().out
+    assert "test auc:" in out and "End of Dataset" in out
+    # 21 batches: passes 0..3 evaluate one and train one (8), pass 4 evaluates, prints and does not train (9), passes 5..8
+    # again (17), pass 9 evaluates + prints (18), pass 10 evaluates 18 and trains 19, pass 11 evaluates 20 and runs dry
+    assert m.engine.global_step == 9
+    # the evaluated loss is the oracle's loss of that batch under the current weights
+    w = {k: torch.from_numpy(v).double() for k, v in m.engine.get_weights().items()}
+    ob = H.oracle_batch(batches[0], torch.float64)
+    ref = float(O.LOSS["wdl_textline"](w, ob, hp)[0])
+    got = float(m.engine.eval_loss(batches[0]).item())
+    assert abs(got - ref) < 1e-5 * max(1.0, abs(ref))
+    val = [D.to_pickled_batch(b) for b in batches[:2]]
+    auc = alg_model.predict(val, hp.model_pb, args=hp)
+    assert 0.0 <= auc <= 1.0
+
+
 def test_deepfm_tf32_tensor_core_path():
     """tcgen05 TF32 MLP inside the full step: logits/loss/params within 2e-3"""
     _run_parity("deepfm", H.hp_c1(), steps=2, precision="tf32", adam_mode="lazy")

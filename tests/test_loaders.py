@@ -1,0 +1,218 @@
+"""CPU: the native input decoders (csrc/host_loader.cu through deep_learning_b200/loaders.py) against the oracle
+(oracle/loader_oracle.py: the reference's plain-Python load_process / load_test run as written, and restatements of
+its tf.data decoders).  Ids, labels and shapes bit-exact; floats bit-exact (Python float() then a float32 cast)."""
+import ctypes as C
+import os
+import pickle
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import loader_oracle as LO
+from deep_learning_b200 import loaders as L
+from deep_learning_b200 import data as D
+from deep_learning_b200.hparams import ModelParams
+
+
+def _fmt(x):
+    return repr(float(np.float32(x)))
+
+
+def _write_lines(path, n, C_, Fc, third=None, n_third=0, seed=0, newline_at_end=True, awkward=False):
+    g = np.random.RandomState(seed)
+    lines = []
+    for i in range(n):
+        cont = g.rand(C_).astype(np.float32) * (1000.0 if awkward else 1.0)
+        toks = [_fmt(v) for v in cont]
+        if awkward and C_ >= 4:
+            toks[0], toks[1], toks[2], toks[3] = "1e-3", "-0.0", "3", "0.1000000014901161193847656250000001"
+        cate = g.randint(0, 100000, size=Fc)
+        cols = [str(int(g.rand() < 0.3)), " ".join(toks), " ".join(str(v) for v in cate)]
+        if third == "wide":
+            cols.append(" ".join(str(v) for v in g.randint(0, 5000, size=n_third)))
+        if third == "libsvm":
+            cols.append(" ".join("%d=%s" % (a, _fmt(b)) for a, b in zip(g.randint(0, 900, size=n_third), g.rand(n_third) * 3)))
+        lines.append(",".join(cols))
+    txt = "\n".join(lines) + ("\n" if newline_at_end else "")
+    with open(path, "w") as f:
+        f.write(txt)
+
+
+def _mp(**kw):
+    mp = ModelParams(**kw)
+    return mp
+
+
+@pytest.fixture(scope="module")
+def lib_ready(lib_built):
+    return lib_built
+
+
+def test_load_process_equals_the_reference_python(tmp_path, lib_ready):
+    """utils/data_loader_load.py:61-139 run as written vs the native parser: two files, a short last batch, a last line
+    without a newline, awkward float spellings, the vector block split off the tail of column 1"""
+    d = str(tmp_path) + "/"
+    _write_lines(d + "part-000", 700, 9, 6, seed=1, awkward=True)
+    _write_lines(d + "part-001", 333, 9, 6, seed=2, newline_at_end=False)
+    open(d + "_SUCCESS", "w").close()                       # not a "part" file: ignored by get_file_list
+    mp = _mp(alg_name="deepfm", batch_size=256, cont_field_size=9, vector_field_size=3, cate_field_size=6)
+    files = L.get_file_list(d)
+    assert [os.path.basename(f) for f in files] == ["part-000", "part-001"]
+    ref = [pickle.loads(b) for b in LO.load_process(mp, files)]
+    got = L.load_process(mp, files, pin=False)
+    assert len(got) == len(ref) == 5 and got[-1]["labels"].shape[0] == 1033 - 4 * 256
+    for g_, r in zip(got, ref):
+        assert np.array_equal(g_["cate_feats"].numpy(), LO.feed(r["cate_feats"], np.int32))
+        assert np.array_equal(g_["cont_feats"].numpy(), LO.feed(r["cont_feats"], np.float32))
+        assert np.array_equal(g_["vector_feats"].numpy(), LO.feed(r["vector_feats"], np.float32))
+        assert np.array_equal(g_["labels"].numpy(), LO.feed(r["labels"], np.float32))
+        assert g_["cont_feats"].shape[1] == 6 and g_["vector_feats"].shape[1] == 3
+    # the reference wire format on request: decodes to the same arrays through the generation-A decoder
+    pk = L.load_process(mp, files, as_pickle=True, pin=False)
+    back = D.from_pickled_batch(pk[0])
+    assert np.array_equal(back["cate_feats"], got[0]["cate_feats"].numpy())
+    assert np.array_equal(back["cont_feats"], got[0]["cont_feats"].numpy())
+
+
+def test_load_process_max_data_size_and_wide_column(tmp_path, lib_ready):
+    d = str(tmp_path) + "/"
+    _write_lines(d + "part-0", 50, 4, 3, third="wide", n_third=5, seed=3)
+    mp = _mp(alg_name="wdl_textline", batch_size=16, cont_field_size=4, cate_field_size=3, wide_field_size=5)
+    mp.max_data_size = 20
+    ref = [pickle.loads(b) for b in LO.load_process(mp, [d + "part-0"])]
+    got = L.load_process(mp, [d + "part-0"], pin=False)
+    assert sum(len(r["labels"]) for r in ref) == 21 == sum(g_["labels"].shape[0] for g_ in got)   # :45 keeps max+1 lines
+    for g_, r in zip(got, ref):
+        assert np.array_equal(g_["wide_feats"].numpy(), LO.feed(r["wide_feats"], np.int32))
+        assert np.array_equal(g_["cate_feats"].numpy(), LO.feed(r["cate_feats"], np.int32))
+
+
+def test_load_test_index_value_form(tmp_path, lib_ready):
+    d = str(tmp_path) + "/"
+    _write_lines(d + "part-0", 40, 5, 4, seed=4)
+    mp = _mp(alg_name="deepfm", batch_size=32, cont_field_size=5, vector_field_size=0, cate_field_size=4)
+    ref = [pickle.loads(b) for b in LO.load_test(mp, [d + "part-0"])]
+    got = L.load_test(mp, [d + "part-0"], pin=False)
+    assert len(ref) == len(got) == 2
+    for g_, r in zip(got, ref):
+        for k, dt in (("labels", np.float32), ("cont_feats_index", np.int32), ("cont_feats_value", np.float32),
+                      ("cate_feats_index", np.int32), ("cate_feats_value", np.int32)):
+            assert np.array_equal(g_[k].numpy(), LO.feed(r[k], dt)), k
+
+
+@pytest.mark.parametrize("alg,third,n_third", [("wdl_textline", "wide", 7), ("dnn_multi_textline", "libsvm", 6),
+                                               ("deepfm_textline", None, 0)])
+def test_textline_iterator(tmp_path, lib_ready, alg, third, n_third):
+    """utils/data_loader_load.py:187-252: drop_remainder=True, repeat(epochs), batches run across file boundaries"""
+    d = str(tmp_path) + "/"
+    _write_lines(d + "part-a", 130, 5, 4, third=third, n_third=n_third, seed=5)
+    _write_lines(d + "part-b", 75, 5, 4, third=third, n_third=n_third, seed=6)
+    mp = _mp(alg_name=alg, batch_size=64, epochs=2, cont_field_size=5, vector_field_size=2, cate_field_size=4,
+             wide_field_size=n_third, multi_feats_size=n_third)
+    files = [d + "part-a", d + "part-b"]
+    ref = list(LO.textline_batches(mp, files))
+    got = list(L.textline_process(mp, files, pin=False))
+    assert len(ref) == len(got) == 2 * (205 // 64)
+    for g_, r in zip(got, ref):
+        for k in r:
+            if r[k].size or k in g_:
+                assert np.array_equal(g_[k].numpy(), r[k]), k
+    # small chunks: lines straddling chunk boundaries are carried over, results identical
+    sc = L.schema_for(mp, "textline")
+    blocks = L.LineBlocks(files, sc, chunk_bytes=997)
+    small = list(L._rebatch(blocks, 64, True, sc.names, False))
+    for a, b in zip(small, got[:3]):
+        for k in a:
+            assert torch.equal(a[k], b[k]), k
+
+
+def test_dnn_multi_textline_loader_keeps_short_batch(tmp_path, lib_ready):
+    """utils/data_loader_textline.py:39-44: batch() without drop_remainder; its own key names"""
+    d = str(tmp_path) + "/"
+    _write_lines(d + "part-999", 21, 3, 2, third="libsvm", n_third=4, seed=7)
+    mp = _mp(alg_name="dnn_multi_textline", batch_size=8, epochs=1, cont_field_size=3, cate_field_size=2, multi_feats_size=4)
+    got = list(L.dnn_multi_process(d + "part-999", 8, 1, mp=mp, pin=False))
+    assert [b["labels"].shape[0] for b in got] == [8, 8, 5]
+    assert set(got[0]) >= {"labels", "cont_feats", "cat_feats", "mul_cat_feats", "mul_cat_feats_value"}
+    mp2 = _mp(alg_name="dnn_multi_textline", batch_size=8, epochs=1, cont_field_size=3, cate_field_size=2, multi_feats_size=4)
+    ref = list(LO.textline_batches(mp2, [d + "part-999"], drop_remainder=False))
+    for g_, r in zip(got, ref):
+        assert np.array_equal(g_["mul_cat_feats"].numpy(), r["mul_cate_feats"])
+        assert np.array_equal(g_["mul_cat_feats_value"].numpy(), r["mul_cate_feats_value"])
+        assert np.array_equal(g_["cat_feats"].numpy(), r["cate_feats"])
+
+
+def test_malformed_lines_are_reported(tmp_path, lib_ready):
+    d = str(tmp_path) + "/"
+    mp = _mp(alg_name="deepfm", batch_size=4, cont_field_size=2, vector_field_size=0, cate_field_size=2)
+    for bad in ("1,0.5 0.25,3\n", "1,0.5,3 4\n", "1,0.5 x,3 4\n", "1,0.5 0.25,3 4.5\n", "1,0.5  0.25,3 4\n", "1\n"):
+        with open(d + "part-0", "w") as f:
+            f.write("0,0.5 0.25,3 4\n" + bad)
+        with pytest.raises(ValueError, match="malformed line 1"):
+            L.load_process(mp, [d + "part-0"], pin=False)
+    with open(d + "part-0", "w") as f:
+        f.write("0,0.5 0.25,3 4\n\n \n1, 7 1e2 ,3 4\r\n")          # blank lines skipped, CRLF tolerated, float() strips blanks
+    try:
+        got = L.load_process(mp, [d + "part-0"], pin=False)
+    except ValueError:
+        got = None
+    # " 7" after the comma is the token "" then "7" for str.split(" "): float("") raises in the reference too
+    assert got is None
+
+
+def test_crc32c_known_answer_and_tfrecord_roundtrip(tmp_path, lib_ready):
+    """RFC 3720 check value pins the CRC; Examples written by the oracle's writer (packed and unpacked list encodings,
+    an extra key the spec does not name) are decoded by the native reader"""
+    assert LO.crc32c(b"123456789") == 0xE3069283
+    g = np.random.RandomState(8)
+    n, C_, V, Fc, M = 150, 4, 3, 5, 6
+    rows = [{"label": g.rand(1).round(), "cont_feats": g.rand(C_), "vector_feats": g.randn(V),
+             "cate_feats": g.randint(0, 2 ** 40, size=Fc + M), "ignored": g.rand(2)} for _ in range(n)]
+    rows[3]["cate_feats"][0] = -7                                   # negative int64: 10-byte varint
+    d = str(tmp_path) + "/"
+    LO.write_tfrecord(d + "part-r-00000", [LO.encode_example(r, packed=True) for r in rows[:80]])
+    LO.write_tfrecord(d + "part-r-00001", [LO.encode_example(r, packed=False) for r in rows[80:]])
+    mp = _mp(alg_name="deepfm_multi", batch_size=32, epochs=2, cont_field_size=C_, vector_feats_size=V, cate_field_size=Fc,
+             multi_feats_size=M)
+    files = L.get_file_list(d)
+    ref = list(LO.pipeline_batches(mp, files, "train"))
+    got = list(L.pipeline_process(mp, files, "train", pin=False))
+    assert len(ref) == len(got) == 2 * (n // 32)
+    for g_, r in zip(got, ref):
+        for k in ("label", "cont_feats", "vector_feats", "cate_feats"):
+            assert np.array_equal(g_[k].numpy(), r[k]), k
+        assert g_["cate_feats"].dtype == torch.int64 and g_["label"].shape == (32, 1)
+    assert len(list(L.pipeline_process(mp, files, "predict", pin=False))) == n // 32       # no repeat outside training
+    # tiny chunks: records straddle chunk boundaries
+    small = list(L.TFRecordBatches(mp, files, "predict", pin=False, chunk_bytes=301))
+    for a, b in zip(small, got):
+        assert torch.equal(a["cate_feats"], b["cate_feats"]) and torch.equal(a["cont_feats"], b["cont_feats"])
+    # *_cate generation: no cont_feats key in the spec (utils/data_loader.py:10-16)
+    mpc = _mp(alg_name="deepfm_multi_cate", batch_size=32, epochs=1, cont_field_size=0, vector_feats_size=V, cate_field_size=Fc,
+              multi_feats_size=M)
+    gc = list(L.pipeline_process(mpc, files, "train", pin=False))
+    assert gc[0]["cont_feats"].shape == (32, 0) and torch.equal(gc[0]["cate_feats"], got[0]["cate_feats"])
+    # seeded shuffle keeps the multiset of records
+    sh = list(L.pipeline_process(mp, files, "predict", pin=False, shuffle_seed=1))
+    a = torch.cat([b["cate_feats"] for b in sh]); b_ = torch.cat([b["cate_feats"] for b in got[:n // 32]])
+    assert not torch.equal(a, b_)
+
+
+def test_tfrecord_corruption_is_detected(tmp_path, lib_ready):
+    d = str(tmp_path) + "/"
+    row = {"label": np.ones(1), "cont_feats": np.zeros(2), "vector_feats": np.zeros(1), "cate_feats": np.arange(3)}
+    LO.write_tfrecord(d + "part-0", [LO.encode_example(row)] * 4)
+    mp = _mp(alg_name="deepfm_multi", batch_size=2, epochs=1, cont_field_size=2, vector_feats_size=1, cate_field_size=3)
+    assert len(list(L.pipeline_process(mp, [d + "part-0"], "train", pin=False))) == 2
+    blob = bytearray(open(d + "part-0", "rb").read())
+    blob[30] ^= 0x40
+    open(d + "part-1", "wb").write(bytes(blob))
+    with pytest.raises(ValueError, match="corrupt TFRecord"):
+        list(L.pipeline_process(mp, [d + "part-1"], "train", pin=False))
+    open(d + "part-2", "wb").write(bytes(open(d + "part-0", "rb").read()[:-5]))
+    with pytest.raises(ValueError, match="truncated"):
+        list(L.pipeline_process(mp, [d + "part-2"], "train", pin=False))
+    mp_bad = _mp(alg_name="deepfm_multi", batch_size=2, epochs=1, cont_field_size=3, vector_feats_size=1, cate_field_size=3)
+    with pytest.raises(ValueError):                                  # FixedLenFeature([3]) against 2 stored values
+        list(L.pipeline_process(mp_bad, [d + "part-0"], "train", pin=False))

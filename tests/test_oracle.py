@@ -176,3 +176,97 @@ def test_data_formats_roundtrip():
     assert d["label"].shape == (7, 1)
     sizes = D.field_sizes(10 ** 8, 26)
     assert sum(sizes) == 10 ** 8 and min(sizes) >= 2
+
+
+# ---- textline models: models/wdl_textline.py, models/dnn_multi_textline.py -----------------------
+@pytest.mark.parametrize("alg", ["wdl_textline", "dnn_multi_textline"])
+def test_textline_autograd_matches_finite_differences(alg):
+    hp = H.hp_textline(alg, hidden_units=[8, 4], l2_reg=1e-2)
+    p = O.init_params(alg, hp)
+    b = H.oracle_batch(H.make_batch(alg, hp, seed=1, B=16), torch.float64)
+    loss, _, _, grads = O.loss_and_grads(alg, p, b, hp)
+    rng = np.random.RandomState(0)
+    for name in p:
+        gflat = grads[name].reshape(-1)
+        if name == "tags_emb":       # tf.constant: no gradient even though it shapes the output
+            assert not gflat.any()
+            continue
+        nz = torch.nonzero(gflat).reshape(-1)
+        idx = int(nz[rng.randint(len(nz))]) if len(nz) else 0
+        eps = 1e-6
+        q = {k: v.clone() for k, v in p.items()}
+        q[name].reshape(-1)[idx] += eps
+        lp = float(O.LOSS[alg](q, b, hp)[0])
+        q[name].reshape(-1)[idx] -= 2 * eps
+        lm = float(O.LOSS[alg](q, b, hp)[0])
+        fd = (lp - lm) / (2 * eps)
+        assert abs(fd - float(gflat[idx])) < 1e-6 * max(1.0, abs(fd)) + 1e-9, (name, fd, float(gflat[idx]))
+
+
+def test_wdl_textline_l2_runs_over_the_gathered_weights():
+    """quirk Q6 (models/wdl_textline.py:264-269,284-286): known answer for the regulariser.  With wide ids {5, 5} for
+    sample 0 and {5, 9} for sample 1, W = 2, H = 4, the term is l2/2 * (3*w5^2 + w9^2 + B * sum_{r=2..5} w_r^2); row 5 is
+    both a wide id and a deep row (quirk Q4), so it counts 3 + B times."""
+    hp = O.HParams(hidden_units=[4], batch_size=2, embedding_size=4, cont_field_size=1, cate_field_size=1, cate_index_size=12,
+                   wide_field_size=2, l2_reg=0.5)
+    p = O.init_params("wdl_textline", hp)
+    b = {"cate_feats": torch.tensor([[3], [0]]), "cont_feats": torch.rand(2, 1, dtype=torch.float64),
+         "wide_feats": torch.tensor([[5, 5], [5, 9]]), "label": torch.tensor([[1.0], [0.0]], dtype=torch.float64)}
+    loss, out, score = O.wdl_textline_loss(p, b, hp)
+    w = p["wdl_weights"].reshape(-1)
+    cnt = torch.zeros(16, dtype=torch.float64)
+    cnt[5] += 3; cnt[9] += 1; cnt[2:6] += 2
+    want = O.log_loss(b["label"], score) + 0.5 * hp.l2_reg * (cnt * w * w).sum() + O.l2_regularizer(hp.l2_reg, p["deep_0"])
+    assert abs(float(loss) - float(want)) < 1e-14
+    # id 0 reads the zero row: sample 1's embedding block is all zeros whatever weight_mat[0] holds
+    q = {k: v.clone() for k, v in p.items()}
+    q["weight_mat"][0] += 1.0
+    assert torch.equal(O.wdl_textline_forward(q, b, hp)[0], out)
+    # the table-wide l2 of models/wdl.py is a different number
+    assert abs(float(O.wdl_loss(p, b, hp)[0]) - float(loss)) > 1e-6
+
+
+def test_weighted_pooling_known_answer():
+    """models/dnn_multi_textline.py:93-102: count on the UNWEIGHTED rows (row sum != 0), sum on the weighted ones.
+    One trainable field [7, 0, 9] with weights [2, 5, 0.5]: id 0 is the zero row -> count 2, pooled = (2*r7 + 0.5*r9)/2.
+    One 'tag' field [0, 1] with weights [1, 3]: row 0 of the frozen table is a REAL row -> count 2."""
+    hp = O.HParams(hidden_units=[4], batch_size=1, embedding_size=2, cont_field_size=1, cate_field_size=1, cate_feats_size=12,
+                   multi_feats_size=5, multi_field_size=2, multi_feats_range=[[0, 3, "kw"], [3, 5, "tag"]], word2vec_rows=3,
+                   l2_reg=0.0)
+    p = O.init_params("dnn_multi_textline", hp)
+    p["deep_0"] = torch.eye(7, 4, dtype=torch.float64)            # tower passes the first 4 inputs through
+    p["deep_bias_0"] = torch.full((1, 4), 10.0, dtype=torch.float64)   # keeps the ReLU open
+    p["deep_res"] = torch.tensor([[0.0], [0.0], [0.0], [1.0]], dtype=torch.float64)
+    p["deep_res_bias"] = torch.zeros(1, 1, dtype=torch.float64)
+    b = {"cate_feats": torch.tensor([[4, 7, 0, 9, 0, 1]]), "cont_feats": torch.zeros(1, 1, dtype=torch.float64),
+         "multi_feats_value": torch.tensor([[2.0, 5.0, 0.5, 1.0, 3.0]], dtype=torch.float64),
+         "label": torch.ones(1, 1, dtype=torch.float64)}
+    out, _ = O.dnn_multi_textline_forward(p, b, hp)
+    W, T = p["weight_mat"], p["tags_emb"]
+    pooled_kw = (2.0 * W[7] + 0.5 * W[9]) / 2.0
+    # input order [cont(1) | cat_emb(2) | pooled kw(2) | pooled tag(2)]; output picks input 3 = pooled_kw[0] (+ bias 10)
+    assert abs(float(out) - (float(pooled_kw[0]) + 10.0)) < 1e-14
+    p["deep_res"] = torch.zeros(4, 1, dtype=torch.float64)
+    p["deep_0"] = torch.zeros(7, 4, dtype=torch.float64); p["deep_0"][5, 0] = 1.0
+    p["deep_res"][0, 0] = 1.0
+    out, _ = O.dnn_multi_textline_forward(p, b, hp)
+    pooled_tag = (1.0 * T[0] + 3.0 * T[1]) / 2.0
+    assert abs(float(out) - (float(pooled_tag[0]) + 10.0)) < 1e-14
+
+
+def test_textline_batch_keys_are_mapped():
+    """utils/data_loader_textline.py:30-34 key names -> the canonical batch the engine reads"""
+    from deep_learning_b200 import data as D
+    from deep_learning_b200.spec import spec_from_hparams
+    hp = H.hp_textline("dnn_multi_textline")
+    spec = spec_from_hparams("dnn_multi_textline", hp)
+    b = H.make_batch("dnn_multi_textline", hp, seed=3, B=8)
+    Fc = hp.cate_field_size
+    raw = {"labels": b["label"], "cont_feats": b["cont_feats"], "cat_feats": b["cate_feats"][:, :Fc],
+           "mul_cat_feats": b["cate_feats"][:, Fc:], "mul_cat_feats_value": b["multi_feats_value"]}
+    c = D.canonical_batch(raw, spec)
+    assert torch.equal(c["cate_feats"], b["cate_feats"]) and torch.equal(c["multi_feats_value"], b["multi_feats_value"])
+    assert torch.equal(c["label"], b["label"])
+    assert spec.frozen_rows == 300 and spec.frozen_fields == (1,) and spec.weighted_pool
+    off = spec.frozen_slot_offset()
+    assert off[:Fc + 5].sum() == 0 and (off[Fc + 5:] == spec.table_rows).all()
