@@ -26,6 +26,16 @@ class AdamHP(C.Structure):
     _fields_ = [("lr_t", c_f32), ("beta1", c_f32), ("beta2", c_f32), ("eps", c_f32)]
 
 
+MAX_LAYERS = 8
+
+
+class DenseLayout(C.Structure):
+    """mirror of `ctr_dense_layout`"""
+    _fields_ = [("group_end", c_i64 * 3), ("reg_scale", c_f32), ("n_layers", c_i32), ("w_off", c_i64 * MAX_LAYERS),
+                ("K", c_i32 * MAX_LAYERS), ("N", c_i32 * MAX_LAYERS), ("ld_kmajor", c_i64 * MAX_LAYERS),
+                ("w_kmajor", c_vp * MAX_LAYERS), ("w_rounded", c_vp * MAX_LAYERS)]
+
+
 MAX_PEERS = 16
 IPC_HANDLE_BYTES = 64
 
@@ -39,6 +49,7 @@ class PeerRoute(C.Structure):
 _P_CFG = C.POINTER(EmbedCfg)
 _P_RT = C.POINTER(PeerRoute)
 _P_HP = C.POINTER(AdamHP)
+_P_LAY = C.POINTER(DenseLayout)
 
 # name -> (restype, [argtypes]) ; the first two args (handle, stream) are added for every entry
 # except the handle-management ones.  Kept in header order.
@@ -83,6 +94,7 @@ _PROTOS = {
     "ctr_embed_bwd_partials_weighted": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_i64, c_vp,
                                                 c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "ctr_embed_bwd_finalize": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
+    "ctr_dense_update": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, _P_LAY, _P_HP]),
     "ctr_cont_bwd_ws_bytes": (c_i64, [c_vp, _P_CFG]),
     "ctr_fm_cont_bwd": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
     "ctr_scalar_segment_add": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i32, c_i64, c_vp]),

@@ -407,6 +407,40 @@ adam_dense_kernel(float* __restrict__ theta, float* __restrict__ m, float* __res
     }
 }
 
+// whole dense side of one step in ONE launch: TF1 Adam over the flat parameter buffer (three regulariser groups by
+// position) and, for the tower weights, the K-major and TF32-rounded copies the tcgen05 GEMMs of the next step read.
+// Replaces 2-3 adam_dense + 2 launches per layer (8 launches of a few microseconds each at config 4).
+__global__ void __launch_bounds__(256)
+dense_update_kernel(float* __restrict__ theta, float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g,
+                    const ctr_dense_layout lay, const ctr_adam_hp hp) {
+    const int64_t n = lay.group_end[2];
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        const float th = theta[i];
+        float gi = g[i];
+        if (i >= lay.group_end[1]) gi += lay.reg_scale * (th > 0.f ? 1.f : (th < 0.f ? -1.f : 0.f));     // l1 group
+        else if (i >= lay.group_end[0]) gi = fmaf(lay.reg_scale, th, gi);                                 // l2 group
+        const float mm = hp.beta1 * m[i] + (1.f - hp.beta1) * gi;
+        const float vv = hp.beta2 * v[i] + (1.f - hp.beta2) * gi * gi;
+        m[i] = mm;
+        v[i] = vv;
+        const float nt = th - hp.lr_t * mm / (sqrtf(vv) + hp.eps);
+        theta[i] = nt;
+#pragma unroll 1
+        for (int l = 0; l < lay.n_layers; ++l) {
+            const int64_t r = i - lay.w_off[l];
+            if (r >= 0 && r < (int64_t) lay.K[l] * lay.N[l]) {
+                const float q = ctr_round_tf32(nt);
+                if (lay.w_rounded[l]) lay.w_rounded[l][r] = q;
+                if (lay.w_kmajor[l]) {
+                    const int row = (int) (r / lay.N[l]), col = (int) (r - (int64_t) row * lay.N[l]);
+                    lay.w_kmajor[l][(int64_t) col * lay.ld_kmajor[l] + row] = q;
+                }
+                break;
+            }
+        }
+    }
+}
+
 __global__ void clear_flags_kernel(uint8_t* __restrict__ f, int64_t n) {
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) f[i] = 0;
 }
@@ -742,6 +776,21 @@ extern "C" int ctr_adam_dense(ctr_handle* h, ctr_stream s, float* theta, float* 
         clear_flags_kernel<<<grid_for(h, nf), 256, 0, ctr_st(s)>>>(skip, nf);
         CTR_CHECK_LAUNCH(h, "clear_flags");
     }
+    return CTR_OK;
+}
+
+extern "C" int ctr_dense_update(ctr_handle* h, ctr_stream s, float* theta, float* m, float* v, const float* g,
+                                const ctr_dense_layout* lay, const ctr_adam_hp* hp) {
+    CTR_REQUIRE(h, theta && m && v && g && lay && hp, "dense_update: null pointer");
+    CTR_REQUIRE(h, lay->group_end[0] >= 0 && lay->group_end[0] <= lay->group_end[1] && lay->group_end[1] <= lay->group_end[2] &&
+                       lay->n_layers >= 0 && lay->n_layers <= CTR_MAX_LAYERS, "dense_update: bad layout");
+    for (int l = 0; l < lay->n_layers; ++l)
+        CTR_REQUIRE(h, lay->K[l] > 0 && lay->N[l] > 0 && lay->w_off[l] >= 0 &&
+                           lay->w_off[l] + (int64_t) lay->K[l] * lay->N[l] <= lay->group_end[2] &&
+                           (!lay->w_kmajor[l] || lay->ld_kmajor[l] >= lay->K[l]), "dense_update: bad layer %d", l);
+    if (lay->group_end[2] == 0) return CTR_OK;
+    dense_update_kernel<<<grid_for(h, lay->group_end[2]), 256, 0, ctr_st(s)>>>(theta, m, v, g, *lay, *hp);
+    CTR_CHECK_LAUNCH(h, "dense_update");
     return CTR_OK;
 }
 

@@ -5,14 +5,16 @@ hot path is a call into libctr_b200.so through `_lib.Handle.call`.
 """
 from __future__ import annotations
 
+import ctypes as C
 import math
+import os
 from typing import Dict, List, Optional
 
 import numpy as np
 import torch
 
 from . import _lib
-from ._lib import AdamHP, EmbedCfg, ptr
+from ._lib import DenseLayout, MAX_LAYERS, AdamHP, EmbedCfg, ptr
 from .spec import ModelSpec
 
 ADAM_BETA1, ADAM_BETA2, ADAM_EPS = 0.9, 0.999, 1e-8   # tf.train.AdamOptimizer defaults (models/deepfm.py:161)
@@ -138,6 +140,9 @@ class CtrEngine:
             # the id sort depends only on the batch: it runs on a side stream underneath the forward pass
             self.side = torch.cuda.Stream(device=dev)
             self.ev_batch, self.ev_sorted = torch.cuda.Event(), torch.cuda.Event()
+            self.aux = torch.cuda.Stream(device=dev)
+            self.ev_head, self.ev_cont = torch.cuda.Event(), torch.cuda.Event()
+            self.ws_cont = torch.zeros(_ru(max(self.h.query("ctr_cont_bwd_ws_bytes", cfg), 256), 256), dtype=torch.uint8, device=dev)
             self.ws_sort = torch.zeros(_ru(max(self.h.query("ctr_sort_ws_bytes", n), 4 * (n // 2048 + 8)), 256),
                                        dtype=torch.uint8, device=dev)
             ws_bytes = max(ws_bytes, self.h.query("ctr_cont_bwd_ws_bytes", cfg),
@@ -312,9 +317,101 @@ class CtrEngine:
             out[name] = a
         return out
 
+    # ---- per-shard checkpoint (the reference's tf.train.Saver stores every variable with its Adam
+    # slots and the step counters, models/deepfm_multi.py:269-278,308-310) ---------------------------------------------------
+    @staticmethod
+    def shard_file(path: str, rank: int, world: int) -> str:
+        return os.path.join(path, "shard-%05d-of-%05d.npz" % (rank, world))
+
+    def save_shard(self, path: str) -> str:
+        """Write THIS rank's state: its rows of the table (device layout, no all-gather), their Adam slots, the replicated
+        dense buffer and the step counters.  Every rank calls it; the files of one checkpoint are
+        `shard-<rank>-of-<world>.npz`."""
+        s = self.spec
+        os.makedirs(path, exist_ok=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        R = self.rows_local
+        blob = {"meta": np.asarray([self.world, self.rank, s.table_rows, s.k, s.table_stride, self.global_step, self.n_dense,
+                                    int(self.train_mode)], dtype=np.int64),
+                "powers": np.asarray([self.beta1_power, self.beta2_power], dtype=np.float64),
+                "table": self.table[:R].cpu().numpy(), "theta": self.theta.cpu().numpy()}
+        if s.frozen_rows:
+            blob["frozen"] = self.table[R:].cpu().numpy()
+        if self.train_mode:
+            blob.update({"m_table": self.m_table[:R].cpu().numpy(), "v_table": self.v_table[:R].cpu().numpy(),
+                         "m": self.m.cpu().numpy(), "v": self.v.cpu().numpy()})
+        f = self.shard_file(path, self.rank, self.world)
+        tmp = f + ".tmp.npz"
+        np.savez(tmp, **blob)
+        os.replace(tmp, f)           # a crash mid-write never leaves a half-written shard under the final name
+        return f
+
+    def load_shard(self, path: str) -> None:
+        """Restore from `save_shard` files.  Same world size: each rank reads its own file.  Different world size (train
+        on 8, serve on 1): each rank walks all old shards and keeps the rows it owns now (row id = local * W_old + r_old,
+        new owner id % W_new, new local row id // W_new)."""
+        s = self.spec
+        files = sorted(f for f in os.listdir(path) if f.startswith("shard-") and f.endswith(".npz") and ".tmp" not in f)
+        if not files:
+            raise FileNotFoundError("no shard-*.npz under %s" % path)
+        w_old = int(files[0].split("-of-")[1].split(".")[0])
+        if len(files) != w_old:
+            raise ValueError("checkpoint %s is incomplete: %d of %d shards" % (path, len(files), w_old))
+        R = self.rows_local
+        mine = [self.rank] if w_old == self.world else range(w_old)
+        first = True
+        for r_old in mine:
+            z = np.load(self.shard_file(path, r_old, w_old))
+            meta = z["meta"]
+            if int(meta[2]) != s.table_rows or int(meta[3]) != s.k or int(meta[4]) != s.table_stride or int(meta[6]) != self.n_dense:
+                raise ValueError("checkpoint %s was written for another model (rows %d k %d)" % (path, meta[2], meta[3]))
+            has_opt = bool(meta[7]) and self.train_mode
+            pairs = [("table", self.table)] + ([("m_table", self.m_table), ("v_table", self.v_table)] if has_opt else [])
+            if w_old == self.world:
+                for name, dst in pairs:
+                    dst[:R].copy_(torch.from_numpy(z[name]))
+            else:
+                n_old = z["table"].shape[0]
+                ids = np.arange(n_old, dtype=np.int64) * w_old + r_old
+                keep = (ids % self.world == self.rank) & (ids < s.table_rows)
+                loc = torch.from_numpy(ids[keep] // self.world).to(self.dev)
+                for name, dst in pairs:
+                    dst[loc] = torch.from_numpy(z[name][keep]).to(self.dev)
+            if first:
+                self.theta.copy_(torch.from_numpy(z["theta"]))
+                if s.frozen_rows:
+                    self.table[R:].copy_(torch.from_numpy(z["frozen"]))
+                if has_opt:
+                    self.m.copy_(torch.from_numpy(z["m"])); self.v.copy_(torch.from_numpy(z["v"]))
+                self.global_step = int(meta[5])
+                self.beta1_power, self.beta2_power = float(z["powers"][0]), float(z["powers"][1])
+                first = False
+        self._refresh_transposes()
+        torch.cuda.current_stream(self.dev).synchronize()
+
     def _assemble_rows(self, shard: torch.Tensor) -> np.ndarray:
         """full [table_rows, w] host array from this rank's shard (one GPU: the shard IS the table)"""
         return shard.cpu().numpy()
+
+    def _dense_layout(self) -> DenseLayout:
+        """positions of the regulariser groups and of the tower weights in the flat buffer (built once)"""
+        if self._lay is None:
+            s, lay = self.spec, DenseLayout()
+            for gi in range(3):
+                lay.group_end[gi] = self.groups[gi][1]
+            lay.reg_scale = float(s.l2_reg)
+            dims = self._layer_dims()
+            if self.wt is not None and len(dims) > MAX_LAYERS:
+                raise ValueError("at most %d tower layers on the TF32 path" % MAX_LAYERS)
+            lay.n_layers = len(dims) if self.wt is not None else 0
+            for i, (k_, h_) in enumerate(dims[:lay.n_layers]):
+                lay.w_off[i], lay.K[i], lay.N[i], lay.ld_kmajor[i] = self.off["deep_%d" % i], k_, h_, _ru(k_, 4)
+                lay.w_kmajor[i] = self.wt[i].data_ptr()
+                lay.w_rounded[i] = self.wr[i].data_ptr() if self.wr is not None else None
+            self._lay = lay
+        return self._lay
+
+    _lay = None
 
     def _refresh_transposes(self) -> None:
         if self.wt is None:
@@ -477,6 +574,15 @@ class CtrEngine:
         # head-weight gradients were written by ctr_head_fwd
         if s.head == "wdl":
             self._wdl_wide_grad(B)
+        if s.ids_ld and self.n_extra:
+            # gradient of the C continuous-field rows: needs only dlogit / sum_e / cont, so it runs on its own stream
+            # underneath the tower's backward GEMMs (26 us off the critical path at config 4), with its own workspace
+            main = torch.cuda.current_stream(self.dev)
+            self.ev_head.record(main)
+            self.aux.wait_event(self.ev_head)
+            h.call("ctr_fm_cont_bwd", self.aux.cuda_stream, cfg, ptr(self.cont), ptr(self._cont_rows()), ptr(self.sum_e),
+                   ptr(self.dlogit), ptr(w_fm), ptr(self.cont_grad), ptr(self.ws_cont), self.ws_cont.numel())
+            self.ev_cont.record(self.aux)
         # dz[0] already holds the gradient through the last ReLU (written by ctr_head_fwd)
         cur = 0
         for i in range(L - 1, -1, -1):
@@ -500,8 +606,7 @@ class CtrEngine:
             torch.cuda.current_stream(self.dev).wait_event(self.ev_sorted)
             self._mark("wait_sort")
             if self.n_extra:
-                h.call("ctr_fm_cont_bwd", st, cfg, ptr(self.cont), ptr(self._cont_rows()), ptr(self.sum_e),
-                       ptr(self.dlogit), ptr(w_fm), ptr(self.cont_grad), ws, wsn)
+                torch.cuda.current_stream(self.dev).wait_event(self.ev_cont)
             h.call("ctr_embed_bwd_partials_weighted", st, cfg, ptr(self.keys), ptr(self.perm), ptr(self.uidx), n,
                    ptr(self.field_of_slot), ptr(self.x0), ptr(self.dx0), self.dx0_ld, ptr(self.sum_e), ptr(self.dlogit),
                    ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.sw),
@@ -515,13 +620,8 @@ class CtrEngine:
             # TF1 Adam moves EVERY row each step (m, v decay; theta -= lr_t*m/(sqrt(v)+eps)) -- exact mode
             h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
                    self.rows_local * s.table_stride, 0.0, 0.0, ptr(self.touched), s.table_stride, hp)
-        # ---- dense side: one Adam launch per regulariser group ---------------------------------------------
-        for gi, (l2, l1) in enumerate(((0.0, 0.0), (s.l2_reg, 0.0), (0.0, s.l2_reg))):
-            a, b = self.groups[gi]
-            if b > a:
-                h.call("ctr_adam_dense", st, ptr(self.theta[a:b]), ptr(self.m[a:b]), ptr(self.v[a:b]),
-                       ptr(self.grad[a:b]), b - a, l2, l1, None, 1, hp)
-        self._refresh_transposes()
+        # ---- dense side: Adam over the flat buffer + the GEMM-side weight copies, one launch ---------------------------
+        h.call("ctr_dense_update", st, ptr(self.theta), ptr(self.m), ptr(self.v), ptr(self.grad), C.byref(self._dense_layout()), hp)
         self.beta1_power *= ADAM_BETA1
         self.beta2_power *= ADAM_BETA2
         self.global_step += 1

@@ -309,6 +309,26 @@ int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const ui
 int ctr_adam_dense(ctr_handle* h, ctr_stream s, float* theta, float* m, float* v, const float* g, int64_t n,
                    float l2, float l1, uint8_t* skip, int skip_group, const ctr_adam_hp* hp);
 
+/* The whole dense side of a step in one launch: TF1 Adam over the flat parameter buffer [0, group_end[2]) with the
+ * regulariser gradient chosen by position -- [0, group_end[0]) none, [group_end[0], group_end[1]) + reg_scale * theta (l2),
+ * [group_end[1], group_end[2]) + reg_scale * sign(theta) (l1: models/dnn.py:90) -- and, for each tower weight
+ * W_l [K,N] at w_off[l], the copies the tcgen05 GEMMs read next step: w_rounded[l][K,N] = rna_tf32(W) and
+ * w_kmajor[l][N, ld_kmajor] = rna_tf32(W)^T (either may be NULL).  Same arithmetic as ctr_adam_dense + ctr_transpose +
+ * ctr_round_tf32_copy. */
+#define CTR_MAX_LAYERS 8
+typedef struct ctr_dense_layout {
+    int64_t group_end[3];
+    float reg_scale;
+    int32_t n_layers;
+    int64_t w_off[CTR_MAX_LAYERS];
+    int32_t K[CTR_MAX_LAYERS], N[CTR_MAX_LAYERS];
+    int64_t ld_kmajor[CTR_MAX_LAYERS];
+    float* w_kmajor[CTR_MAX_LAYERS];
+    float* w_rounded[CTR_MAX_LAYERS];
+} ctr_dense_layout;
+int ctr_dense_update(ctr_handle* h, ctr_stream s, float* theta, float* m, float* v, const float* g,
+                     const ctr_dense_layout* lay, const ctr_adam_hp* hp);
+
 /* ---- AUC -------------------------------------------------------------------------------
  * replaces sklearn.metrics.roc_auc_score(labels, scores) (models/deepfm.py:231,253): exact
  * tie-aware rank statistic in integers; *auc_out is a device double (NaN if one class only). */

@@ -38,6 +38,8 @@ def main():
         hp = H.hp_multi(B=192)
     elif alg == "wdl":
         hp = H.hp_c1(cate_index_size=10000, wide_field_size=20)
+    elif alg == "wdl_textline":
+        hp = H.hp_textline(alg, l2_reg=1e-4)
     else:
         hp = H.hp_c1()
     Bl = 96 if alg in ("deepfm_multi", "dnn_multi") else 128          # samples per rank
@@ -119,6 +121,34 @@ def main():
         assert np.percentile(d, 99.9) < 2e-3, (n, float(np.percentile(d, 99.9)), float(d.max()))
     if rank == 0:
         print("prefetched free-running steps ok")
+    # ---- per-shard checkpoint: every rank writes its rows; a fresh sharded engine restored from them
+    # continues bit-identically, and ONE GPU re-shards the same files (world -> 1) to the assembled weights
+    import tempfile
+    ck = [tempfile.mkdtemp(prefix="ctr_ckpt_") if rank == 0 else None]
+    dist.broadcast_object_list(ck, src=0)
+    eng.save_shard(ck[0])
+    dist.barrier()
+    eng2 = ShardedCtrEngine(spec, Bl, learning_rate=hp.learning_rate, precision="fp32", adam_mode=adam_mode)
+    eng2.load_shard(ck[0])
+    nxt = [H.make_batch(alg, hp, seed=9000 + r, B=Bl) for r in range(world)]
+    la, lb = float(eng.train_step(nxt[rank]).item()), float(eng2.train_step(nxt[rank]).item())
+    wa, wb = eng.get_weights(), eng2.get_weights()
+    assert la == lb and eng.global_step == eng2.global_step
+    for n in wa:
+        assert np.array_equal(wa[n], wb[n]), "restored shard diverges: %s" % n
+    eng2.save_shard(ck[0])
+    dist.barrier()
+    if rank == 0:
+        from deep_learning_b200.engine import CtrEngine
+        one = CtrEngine(spec, Bl, learning_rate=hp.learning_rate, precision="fp32", adam_mode=adam_mode)
+        one.load_shard(ck[0])
+        w1 = one.get_weights()
+        for n in wb:
+            assert np.array_equal(w1[n], wb[n]), "re-sharded %d -> 1 differs: %s" % (world, n)
+        assert one.global_step == eng2.global_step
+        print("per-shard checkpoint ok (restore + reshard %d -> 1)" % world)
+        import shutil
+        shutil.rmtree(ck[0], ignore_errors=True)
     dist.barrier()
     if rank == 0:
         print("MGPU PARITY OK alg=%s adam=%s world=%d" % (alg, adam_mode, world))

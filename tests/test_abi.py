@@ -41,6 +41,8 @@ def test_ctypes_prototypes_match_header(lib_built):
                 return _lib._P_HP
             if "ctr_peer_route" in a:
                 return _lib._P_RT
+            if "ctr_dense_layout" in a:
+                return _lib._P_LAY
             if "ctr_handle**" in a.replace(" ", "") or "void**" in a.replace(" ", ""):
                 return C.POINTER(C.c_void_p)
             return C.c_void_p

@@ -171,3 +171,91 @@ def test_mlp_tf32_tcgen05_gemms(hd, B, K, N):
     torch.cuda.synchronize()
     assert H.rel_err(dW.cpu(), X.double().T @ dZ.double()) < 2e-3, "wgrad"
     assert H.rel_err(db.cpu(), dZ.double().sum(0)) < 1e-5
+
+
+@pytest.mark.parametrize("B,H,n_fm,w_off,with_extra", [(1000, 400, 55, 55, False),     # config 4: w_deep slice 220 B into the head weight
+                                                       (257, 128, 38, 38, False), (64, 512, 0, 0, True),
+                                                       (77, 10, 7, 3, False),           # H % 4 != 0: scalar kernel
+                                                       (4096, 400, 0, 20, True)])       # wdl: extra = wide sum
+def test_head_fwd_both_kernels_match_fp64(hd, B, H, n_fm, w_off, with_extra):
+    """ctr_head_fwd (models/deepfm.py:128-152 + the gradient through the last ReLU + head-weight gradients): the 128-bit
+    kernel and the scalar one against an fp64 restatement, 1e-6 relative; pad columns of fm / deep hold garbage"""
+    from deep_learning_b200._lib import ptr
+    g = torch.Generator(device="cuda"); g.manual_seed(B + H)
+    fm_ld, deep_ld, lddz = (n_fm + 3) // 4 * 4 + 4, H + 4 + (4 - H % 4) % 4, (H + 3) // 4 * 4
+    fm = torch.randn(B, fm_ld, generator=g, device="cuda")
+    deep = torch.relu(torch.randn(B, deep_ld, generator=g, device="cuda"))
+    wall = torch.randn(w_off + H + 8, generator=g, device="cuda") * 0.1
+    w_fm = torch.randn(max(n_fm, 1), generator=g, device="cuda") * 0.1
+    w_deep = wall[w_off:w_off + H]
+    bias = torch.randn(1, generator=g, device="cuda")
+    extra = torch.randn(B, generator=g, device="cuda") if with_extra else None
+    label = (torch.rand(B, generator=g, device="cuda") < 0.3).float()
+    logit, score, dlogit = (torch.zeros(B, device="cuda") for _ in range(3))
+    dz = torch.full((B, lddz), 7.0, device="cuda")
+    loss = torch.zeros(1, device="cuda")
+    g_fm, g_deep, g_bias = torch.zeros(max(n_fm, 1), device="cuda"), torch.zeros(H, device="cuda"), torch.zeros(1, device="cuda")
+    wsn = hd.query("ctr_head_ws_bytes", B, n_fm, H)
+    ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
+    hd.call("ctr_head_fwd", _st(), B, 2 * B, ptr(fm) if n_fm else None, fm_ld, n_fm, ptr(w_fm) if n_fm else None, ptr(deep), deep_ld, H,
+            ptr(w_deep), ptr(extra), ptr(bias), ptr(label), ptr(logit), ptr(score), ptr(dlogit), ptr(dz), lddz, 0, ptr(loss),
+            ptr(g_fm) if n_fm else None, ptr(g_deep), ptr(g_bias), ptr(ws), wsn)
+    d64 = lambda t: t.double().cpu()
+    z = d64(deep[:, :H]) @ d64(w_deep) + d64(bias)
+    if n_fm:
+        z = z + d64(fm[:, :n_fm]) @ d64(w_fm[:n_fm])
+    if with_extra:
+        z = z + d64(extra)
+    p = torch.sigmoid(z)
+    y = d64(label)
+    eps = 1e-7
+    want_loss = (-y * torch.log(p + eps) - (1 - y) * torch.log(1 - p + eps)).sum() / (2 * B)
+    dl = (-y / (p + eps) + (1 - y) / (1 - p + eps)) * p * (1 - p) / (2 * B)
+    rel = lambda a, b: float((d64(a) - b).abs().max() / max(float(b.abs().max()), 1e-30))
+    assert rel(logit, z) < 2e-6 and rel(score, p) < 2e-6 and rel(dlogit, dl) < 2e-5
+    assert abs(float(loss) - float(want_loss)) < 2e-6 * max(1.0, abs(float(want_loss)))
+    want_dz = dl[:, None] * d64(w_deep)[None, :] * (d64(deep[:, :H]) > 0)
+    assert rel(dz[:, :H], want_dz) < 2e-5
+    assert (dz[:, H:] == 7.0).all()                                       # nothing written past column H
+    assert rel(g_deep, (dl[:, None] * d64(deep[:, :H])).sum(0)) < 2e-5
+    assert abs(float(g_bias) - float(dl.sum())) < 2e-5 * float(dl.abs().sum())
+    if n_fm:
+        assert rel(g_fm[:n_fm], (dl[:, None] * d64(fm[:, :n_fm])).sum(0)) < 2e-5
+
+
+def test_dense_update_equals_the_separate_launches(hd):
+    """ctr_dense_update == ctr_adam_dense per regulariser group + ctr_transpose + ctr_round_tf32_copy, bit for bit"""
+    import ctypes as C
+    from deep_learning_b200._lib import ptr, AdamHP, DenseLayout
+    g = torch.Generator(device="cuda"); g.manual_seed(5)
+    K, N = 37, 24
+    ends = [1024, 2048, 3328]
+    n = ends[2]
+    th = torch.randn(n, generator=g, device="cuda"); th[100:110] = 0.0
+    m, v = torch.randn(n, generator=g, device="cuda") * 0.01, torch.rand(n, generator=g, device="cuda") * 0.01
+    gr = torch.randn(n, generator=g, device="cuda")
+    hp = AdamHP(lr_t=1e-2, beta1=0.9, beta2=0.999, eps=1e-8)
+    offs = [0, 1024 + 64, 2048 + 256]        # one [37, 24] weight matrix in each group, not at the group starts
+    a = [t.clone() for t in (th, m, v)]
+    for gi, (lo, hi) in enumerate(zip([0] + ends[:2], ends)):
+        l2, l1 = (0.0, 0.0) if gi == 0 else ((0.3, 0.0) if gi == 1 else (0.0, 0.3))
+        hd.call("ctr_adam_dense", _st(), ptr(a[0][lo:hi]), ptr(a[1][lo:hi]), ptr(a[2][lo:hi]), ptr(gr[lo:hi]), hi - lo, l2, l1,
+                None, 1, hp)
+    wt_a = [torch.zeros(N, 40, device="cuda") for _ in offs]
+    wr_a = [torch.zeros(K, N, device="cuda") for _ in offs]
+    for i, o in enumerate(offs):
+        hd.call("ctr_transpose", _st(), ptr(a[0][o:o + K * N]), K, N, ptr(wt_a[i]), 40, 1)
+        hd.call("ctr_round_tf32_copy", _st(), ptr(a[0][o:o + K * N]), ptr(wr_a[i]), K * N)
+    b = [t.clone() for t in (th, m, v)]
+    wt_b = [torch.zeros(N, 40, device="cuda") for _ in offs]
+    wr_b = [torch.zeros(K, N, device="cuda") for _ in offs]
+    lay = DenseLayout()
+    for i in range(3):
+        lay.group_end[i] = ends[i]
+        lay.w_off[i], lay.K[i], lay.N[i], lay.ld_kmajor[i] = offs[i], K, N, 40
+        lay.w_kmajor[i], lay.w_rounded[i] = wt_b[i].data_ptr(), wr_b[i].data_ptr()
+    lay.reg_scale, lay.n_layers = 0.3, 3
+    hd.call("ctr_dense_update", _st(), ptr(b[0]), ptr(b[1]), ptr(b[2]), ptr(gr), C.byref(lay), hp)
+    torch.cuda.synchronize()
+    for x, y in zip(a + wt_a + wr_a, b + wt_b + wr_b):
+        assert torch.equal(x, y)

@@ -24,7 +24,7 @@ def _run(world, alg, adam_mode):
 
 
 @pytest.mark.parametrize("alg,adam_mode", [("deepfm", "lazy"), ("deepfm", "tf_dense"), ("deepfm_multi", "lazy"),
-                                           ("wdl", "lazy"), ("dnn", "lazy")])
+                                           ("wdl", "lazy"), ("dnn", "lazy"), ("wdl_textline", "lazy")])
 def test_sharded_loopback_world1(alg, adam_mode):
     _run(1, alg, adam_mode)
 
