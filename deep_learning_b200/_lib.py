@@ -113,6 +113,9 @@ _PROTOS = {
     "ctr_peer_close": (c_i32, [c_vp, c_vp]),
     "ctr_peer_free": (c_i32, [c_vp, c_vp]),
     "ctr_peer_barrier": (c_i32, [c_vp, c_vp, _P_RT, c_i64, C.c_uint32, c_vp, c_i32]),
+    "ctr_peer_bcast": (c_i32, [c_vp, c_vp, c_vp, c_i32, _P_RT]),
+    "ctr_peer_push_rows": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, _P_RT]),
+    "ctr_peer_reduce_sum": (c_i32, [c_vp, c_vp, _P_RT, c_i64, c_vp]),
     "ctr_gather_rows_push": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_i64, c_i32, c_i32, c_i32, _P_RT]),
     "ctr_embed_bwd_finalize_push": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, _P_RT]),
     "ctr_merge_sorted_segments": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_i32, c_vp, c_vp]),

@@ -144,6 +144,82 @@ extern "C" int ctr_gather_rows_push(ctr_handle* h, ctr_stream s, const float* ta
     return CTR_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ plain pushes + reduction
+// rows of 32-bit words -> their routed position in the owning peer's buffer (the id-plan key exchange: width 1)
+__global__ void __launch_bounds__(256)
+push_rows_kernel(const uint32_t* __restrict__ src, int64_t n, int width, const PeerRoute rt) {
+    const int64_t total = n * width;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t i = t / width;
+        const int c = (int) (t - i * width);
+        reinterpret_cast<uint32_t*>(route_row(rt, (uint32_t) i, width))[c] = src[t];
+    }
+}
+
+// the same n words into EVERY peer's slab at the route's byte offset (the per-owner unique counts of the id plan)
+__global__ void __launch_bounds__(256)
+bcast_words_kernel(const uint32_t* __restrict__ src, int n, const PeerRoute rt) {
+    const int total = n * rt.world;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+        const int p = t / n, i = t - p * n;
+        reinterpret_cast<uint32_t*>(rt.buf[p])[i] = src[i];
+    }
+}
+
+// out[i] = sum over ranks, in rank order, of the buffer at the route's byte offset in every slab: the data-parallel sum of
+// the dense gradients read straight out of peer memory.  Same order on every rank => bitwise identical replicas.
+__global__ void __launch_bounds__(256)
+peer_reduce_sum_kernel(const PeerRoute rt, int64_t n4, float4* __restrict__ out) {
+    for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t) gridDim.x * blockDim.x) {
+        float4 v[CTR_MAX_PEERS];
+#pragma unroll
+        for (int p = 0; p < CTR_MAX_PEERS; ++p)
+            if (p < rt.world) v[p] = *(reinterpret_cast<const float4*>(rt.buf[p]) + i);      // all loads in flight together
+        float4 a = v[0];
+#pragma unroll
+        for (int p = 1; p < CTR_MAX_PEERS; ++p)
+            if (p < rt.world) { a.x += v[p].x; a.y += v[p].y; a.z += v[p].z; a.w += v[p].w; }
+        out[i] = a;
+    }
+}
+
+static inline bool route_ok(const ctr_peer_route* rt) {
+    return rt && rt->world >= 1 && rt->world <= CTR_MAX_PEERS && rt->rank >= 0 && rt->rank < rt->world && rt->dst_off >= 0;
+}
+
+extern "C" int ctr_peer_push_rows(ctr_handle* h, ctr_stream s, const uint32_t* src, int64_t n_rows, int width,
+                                  const ctr_peer_route* rt) {
+    CTR_REQUIRE(h, src && route_ok(rt) && width > 0 && n_rows >= 0 && n_rows < (1ll << 32) && rt->dst_off % 4 == 0,
+                "peer_push_rows: bad args");
+    CTR_REQUIRE(h, (int64_t) rt->seg_end[rt->world - 1] == n_rows, "peer_push_rows: route does not cover the list");
+    if (n_rows == 0) return CTR_OK;
+    int64_t blocks = ctr_cdiv(n_rows * width, 256);
+    const int64_t cap = (int64_t) h->sm_count * 4;
+    if (blocks > cap) blocks = cap;
+    push_rows_kernel<<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(src, n_rows, width, make_route(rt));
+    CTR_CHECK_LAUNCH(h, "peer_push_rows");
+    return CTR_OK;
+}
+
+extern "C" int ctr_peer_bcast(ctr_handle* h, ctr_stream s, const uint32_t* src, int n_words, const ctr_peer_route* rt) {
+    CTR_REQUIRE(h, src && route_ok(rt) && n_words > 0 && n_words <= (1 << 20) && rt->dst_off % 4 == 0, "peer_bcast: bad args");
+    bcast_words_kernel<<<(unsigned) ctr_cdiv((int64_t) n_words * rt->world, 256), 256, 0, ctr_st(s)>>>(src, n_words, make_route(rt));
+    CTR_CHECK_LAUNCH(h, "peer_bcast");
+    return CTR_OK;
+}
+
+extern "C" int ctr_peer_reduce_sum(ctr_handle* h, ctr_stream s, const ctr_peer_route* rt, int64_t n, float* out) {
+    CTR_REQUIRE(h, out && route_ok(rt) && n >= 0 && n % 4 == 0 && rt->dst_off % 16 == 0 &&
+                       (reinterpret_cast<uintptr_t>(out) & 15) == 0, "peer_reduce_sum: n must be a multiple of 4, buffers 16-byte aligned");
+    if (n == 0) return CTR_OK;
+    int64_t blocks = ctr_cdiv(n / 4, 256);
+    const int64_t cap = (int64_t) h->sm_count * 2;
+    if (blocks > cap) blocks = cap;
+    peer_reduce_sum_kernel<<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(make_route(rt), n / 4, reinterpret_cast<float4*>(out));
+    CTR_CHECK_LAUNCH(h, "peer_reduce_sum");
+    return CTR_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ merge of sorted segments
 struct SegEnds {
     uint32_t end[CTR_MAX_PEERS];

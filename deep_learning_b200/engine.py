@@ -182,6 +182,7 @@ class CtrEngine:
     def _stream(self) -> int:
         return torch.cuda.current_stream(self.dev).cuda_stream
 
+    host_prof = None       # tests/host_timing.py
     _sort_B = None         # batch size whose id sort forward() still has to enqueue (train steps only)
     phase_marks = None     # list of (name, event) when a timing script asks for the main-stream phase picture
 
@@ -600,6 +601,7 @@ class CtrEngine:
                        1.0, ptr(self.dx0), self.dx0_ld)
         hp = self._adam_hp()
         self._mark("mlp_bwd")
+        self._begin_dense_reduce()          # every dense gradient is final: the reduction runs under the sparse side
         # ---- sparse side: sort -> runs -> partials -> Adam on touched rows ------------------------------
         if s.ids_ld:
             n = B * s.ids_ld + self.n_extra
@@ -621,7 +623,7 @@ class CtrEngine:
             h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
                    self.rows_local * s.table_stride, 0.0, 0.0, ptr(self.touched), s.table_stride, hp)
         # ---- dense side: Adam over the flat buffer + the GEMM-side weight copies, one launch ---------------------------
-        h.call("ctr_dense_update", st, ptr(self.theta), ptr(self.m), ptr(self.v), ptr(self.grad), C.byref(self._dense_layout()), hp)
+        h.call("ctr_dense_update", st, ptr(self.theta), ptr(self.m), ptr(self.v), ptr(self._dense_grad()), C.byref(self._dense_layout()), hp)
         self.beta1_power *= ADAM_BETA1
         self.beta2_power *= ADAM_BETA2
         self.global_step += 1
@@ -641,8 +643,15 @@ class CtrEngine:
         w_fm = self._head_parts()[0]
         return w_fm.data_ptr() + 4 * (s.Fc + s.Fm + s.C)
 
+    def _dense_grad(self) -> torch.Tensor:
+        """the buffer the dense update reads (sharded engines: the sum over ranks)"""
+        return self.grad
+
+    def _begin_dense_reduce(self) -> None:
+        """data-parallel hook: start summing the dense gradients over ranks (no-op on one GPU)"""
+
     def _reduce_dense_grads(self) -> None:
-        """data-parallel hook: sum the dense gradients over ranks (no-op on one GPU)"""
+        """data-parallel hook: the dense gradients are summed over ranks from here on (no-op on one GPU)"""
 
     def _launch_sort(self, B: int) -> None:
         """sort ids -> (keys, perm), run-length structure -> (uniq, seg_start, uidx, n_unique); enqueued on

@@ -25,14 +25,15 @@ import torch.distributed as dist
 from . import shard as _shard
 from ._lib import AdamHP, EmbedCfg, ptr
 from .peer import PeerSlab
-from .engine import CtrEngine, _ru
+from .engine import CtrEngine, _ALIGN, _ru
 from .spec import ModelSpec
 
 
 class _IdPlan:
     """Every id-derived structure of one batch (requester side and owner side)."""
 
-    def __init__(self, eng: "ShardedCtrEngine"):
+    def __init__(self, eng: "ShardedCtrEngine", slot: int = 0):
+        self.slot = slot
         s, dev, B = eng.spec, eng.dev, eng.Bmax
         n = eng.n_max
         u32 = dict(dtype=torch.int32, device=dev)     # raw 32-bit storage; the library reads it as uint32
@@ -41,8 +42,8 @@ class _IdPlan:
         self.seg_start = torch.zeros(n + 2, **u32)
         self.n_unique = torch.zeros(1, **u32)
         self.counts = torch.zeros(eng.world, **u32)
-        self.counts_host = torch.zeros(eng.world * eng.world + 1, dtype=torch.int64).pin_memory()   # matrix + peer status
-        self.route_v = self.route_g = None
+        self.counts_host = torch.zeros(eng.world * eng.world + 2, dtype=torch.int32).pin_memory()   # matrix + 2 status words
+        self.route_v = self.route_g = self.route_k = None
         self.ws_sort = torch.zeros(_ru(max(eng.h.query("ctr_sort_ws_bytes", n), 4 * (n // 2048 + 8)), 256),
                                    dtype=torch.uint8, device=dev)
         self.ev_local, self.ev_ready, self.ev_free = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
@@ -58,7 +59,10 @@ class _IdPlan:
             return
         cap = max(int(n_req * 1.25), 1024)
         u32 = dict(dtype=torch.int32, device=eng.dev)
-        self.req = torch.zeros(cap, **u32)
+        if eng.exchange_mode == "peer":       # peers store their requests straight into this rank's slab
+            self.req = eng.slab.tensor(eng._req_off[self.slot], (eng._req_cap,), torch.int32)
+        else:
+            self.req = torch.zeros(cap, **u32)
         if eng.train_mode:
             self.o_keys, self.o_idx, self.o_uniq, self.o_uidx = (torch.zeros(cap, **u32) for _ in range(4))
             self.o_seg = torch.zeros(cap + 2, **u32)
@@ -88,25 +92,43 @@ class ShardedCtrEngine(CtrEngine):
         if not self.train_mode:
             self.side = torch.cuda.Stream(device=dev)
         self._ids_external = True
-        self.plans = [_IdPlan(self), _IdPlan(self)]
         self.cur: Optional[_IdPlan] = None
         # "peer": owners / requesters store rows straight into the peer's staging buffer over NVLink (fused kernels);
         # "nccl": gather -> all_to_all_single -> consume
         self.exchange_mode = os.environ.get("CTR_EXCHANGE", "peer" if world > 1 else "nccl")
         if self.exchange_mode not in ("peer", "nccl"):
             raise ValueError("CTR_EXCHANGE must be peer or nccl")
-        self.peer_status = torch.zeros(1, dtype=torch.int32, device=dev)
-        self._epoch, self._rows_dirty = 0, False
+        self.peer_status = torch.zeros(2, dtype=torch.int32, device=dev)      # [0] step barriers, [1] id-plan barriers
+        self._epoch, self._pepoch, self._rows_dirty = 0, 0, False
         if self.exchange_mode == "peer":
-            row_bytes = self.wire * 4
-            self._flags_off, self._rows_off = 0, 256
+            # slab layout: arrival words of the step barriers | of the id-plan barriers | count matrix x 2 plan slots |
+            # received rows | received gradients | requested keys x 2 plan slots | dense gradients (read by every peer)
+            row_bytes, W = self.wire * 4, world
+            self._flags_off, self._pflags_off, self._mat_off = 0, 64, 128
+            self._rows_off = _ru(self._mat_off + 2 * W * W * 4, 256)
             self._g_off = self._rows_off + _ru((self.n_max + 1) * row_bytes, 256)
             self._g_cap = self.n_max if self.train_mode else 0
-            self.slab = PeerSlab(self.h, self._g_off + _ru(max(self._g_cap, 1) * row_bytes, 256), group, dev)
+            self._req_cap = max(self.n_max, 1)
+            r0 = self._g_off + _ru(max(self._g_cap, 1) * row_bytes, 256)
+            self._req_off = [r0, r0 + _ru(self._req_cap * 4, 256)]
+            self._dense_off = self._req_off[1] + _ru(self._req_cap * 4, 256)
+            n_dense = self.n_dense + _ALIGN
+            self.slab = PeerSlab(self.h, self._dense_off + _ru((n_dense if self.train_mode else 1) * 4, 256), group, dev)
             self.rows_recv = self.slab.tensor(self._rows_off, (self.n_max + 1, self.wire))
             self.g_recv = self.slab.tensor(self._g_off, (max(self._g_cap, 1), self.wire)) if self.train_mode else None
+            self._rt0 = self.slab.route([0] * W, [0] * W, 0)
+            self._rt_counts = [self.slab.route([0] * W, [0] * W, self._mat_off + (sl * W * W + rank * W) * 4) for sl in range(2)]
+            self._mat_view = [self.slab.tensor(self._mat_off + sl * W * W * 4, (W * W,), torch.int32) for sl in range(2)]
+            if self.train_mode:
+                # the dense gradients live in the slab: after the gradient barrier every rank sums all replicas' buffers
+                # in rank order straight out of peer memory (no collective, bitwise identical results on every rank)
+                self.grad = self.slab.tensor(self._dense_off, (n_dense,))
+                self.grad_red = torch.zeros(n_dense, **f32)
+                self._rt_dense = self.slab.route([0] * W, [0] * W, self._dense_off)
+                self.ev_bar, self.ev_red = torch.cuda.Event(), torch.cuda.Event()
         else:
             self.rows_recv = torch.zeros(self.n_max + 1, self.wire, **f32)
+        self.plans = [_IdPlan(self, 0), _IdPlan(self, 1)]
         self.cont_buf = torch.zeros(max(s.C, 1), self.wire, **f32)
         self.grads_send = (torch.zeros(max(self.n_max, 1), self.wire, **f32)
                            if self.train_mode and self.exchange_mode == "nccl" else None)
@@ -168,10 +190,18 @@ class ShardedCtrEngine(CtrEngine):
                ptr(pl.n_unique), ws, wsn)
         h.call("ctr_shard_counts", st, ptr(pl.uniq), ptr(pl.n_unique), self.world, sp.local_bits, ptr(pl.counts))
         h.call("ctr_invert_perm", st, ptr(pl.perm), ptr(pl.uidx), n, ptr(pl.inv))
+        W = self.world
         with torch.cuda.stream(stream):
-            send = pl.counts.to(torch.int64)
-            mat = _shard.gather_counts(send, self.group_plan)         # exchange #1a: every rank learns every split
-            pl.counts_host.copy_(torch.cat([mat.reshape(-1), self.peer_status.to(torch.int64)]), non_blocking=True)
+            if self.exchange_mode == "peer":
+                # exchange #1a without a collective: my counts row goes into every peer's matrix, one barrier later the
+                # whole matrix is in the own slab
+                h.call("ctr_peer_bcast", st, ptr(pl.counts), W, C.byref(self._rt_counts[pl.slot]))
+                self._plan_barrier(st)
+                pl.counts_host[:W * W].copy_(self._mat_view[pl.slot], non_blocking=True)
+            else:
+                mat = _shard.gather_counts(pl.counts, self.group_plan)     # exchange #1a: every rank learns every split
+                pl.counts_host[:W * W].copy_(mat.reshape(-1), non_blocking=True)
+            pl.counts_host[W * W:].copy_(self.peer_status, non_blocking=True)
             pl.ev_local.record(stream)
         pl.B = B
 
@@ -179,10 +209,16 @@ class ShardedCtrEngine(CtrEngine):
         """host reads the split sizes (NCCL wants them on the host), then on `stream`: the key all-to-all and the
         owner-side stable sort + run structure of the requested rows"""
         h, sp = self.h, self.plan
-        pl.ev_local.synchronize()
+        if self.host_prof is not None:
+            import time
+            t0 = time.perf_counter()
+            pl.ev_local.synchronize()
+            self.host_prof["sync_s"] += time.perf_counter() - t0
+        else:
+            pl.ev_local.synchronize()
         flat, W = pl.counts_host.tolist(), self.world
-        if flat[-1]:
-            raise RuntimeError("peer barrier timed out waiting for rank %d" % (flat[-1] - 1))
+        if flat[W * W] or flat[W * W + 1]:
+            raise RuntimeError("peer barrier timed out waiting for rank %d" % ((flat[W * W] or flat[W * W + 1]) - 1))
         mat = [flat[p * W:(p + 1) * W] for p in range(W)]
         pl.send_counts, pl.recv_counts, vec, grad = _shard.peer_routes(mat, self.rank)
         pl.U, pl.n_req = sum(pl.send_counts), sum(pl.recv_counts)
@@ -193,9 +229,17 @@ class ShardedCtrEngine(CtrEngine):
                 raise RuntimeError("peer exchange: %d rows requested of one owner, receive buffer holds %d" % (worst, self._g_cap))
             pl.route_v = self.slab.route(vec[0], vec[1], self._rows_off)
             pl.route_g = self.slab.route(grad[0], grad[1], self._g_off)
+            pl.route_k = self.slab.route(grad[0], grad[1], self._req_off[pl.slot])     # keys travel like the gradients will
+            if max(pl.n_req, pl.U) > self._req_cap:
+                raise RuntimeError("peer exchange: %d keys requested of this owner, request buffer holds %d" % (pl.n_req, self._req_cap))
         n_req, st = pl.n_req, stream.cuda_stream
         with torch.cuda.stream(stream):
-            _shard.exchange(pl.uniq[:pl.U], pl.send_counts, pl.recv_counts, out=pl.req, group=self.group_plan)   # #1b
+            if self.exchange_mode == "peer":
+                # exchange #1b without a collective: every requester stores its keys into the owner's request list
+                h.call("ctr_peer_push_rows", st, ptr(pl.uniq), pl.U, 1, C.byref(pl.route_k))
+                self._plan_barrier(st)
+            else:
+                _shard.exchange(pl.uniq[:pl.U], pl.send_counts, pl.recv_counts, out=pl.req, group=self.group_plan)   # #1b
             if self.train_mode and n_req:
                 ws, wsn = ptr(pl.o_ws), pl.o_ws.numel()
                 # every peer's slice is already ascending: a stable merge (equal rows keep peer order, so the owner's
@@ -245,6 +289,7 @@ class ShardedCtrEngine(CtrEngine):
         return B
 
     _pending_exchange: Optional[_IdPlan] = None
+    host_prof = None       # tests/host_timing.py: seconds the host spent blocked on the split-size read
 
     def _prefetch_next(self, next_batch: Optional[Dict], ev_call) -> None:
         """start the id plan of the next batch on the side stream (upload ids, sort, de-dup, counts all-to-all)"""
@@ -334,6 +379,7 @@ class ShardedCtrEngine(CtrEngine):
             self._mark("finalize")
             self._barrier(st)
             self._rows_dirty = False
+            self._launch_peer_reduce()           # the dense gradients of every replica were complete before this barrier
         else:
             h.call("ctr_embed_bwd_finalize", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
                    ptr(self.part), ptr(self.grads_send))
@@ -354,14 +400,50 @@ class ShardedCtrEngine(CtrEngine):
         self.h.call("ctr_peer_barrier", st, C.byref(self.cur.route_v), self._flags_off, self._epoch, ptr(self.peer_status),
                     int(os.environ.get("CTR_PEER_TIMEOUT_MS", 10000)))
 
-    def _reduce_dense_grads(self) -> None:
-        # dlogit already carries 1/B_global, so a plain SUM over ranks is the global-batch gradient; the loss
-        # share rides in the tail slot of the same buffer
+    _dense_work = None
+
+    def _begin_dense_reduce(self) -> None:
+        # dlogit already carries 1/B_global, so a plain SUM over ranks is the global-batch gradient; the loss share rides
+        # in the tail slot of the same buffer.  Issued as soon as the last weight gradient is queued: NCCL's stream runs it
+        # underneath the sparse backward (partials, gradient exchange, row Adam), which touches neither buffer.
         self.grad[self.n_dense:self.n_dense + 1].copy_(self.loss)
-        dist.all_reduce(self.grad, group=self.group)
+        if self.exchange_mode != "peer":
+            self._dense_work = dist.all_reduce(self.grad, group=self.group, async_op=True)
+
+    def _plan_barrier(self, st: int) -> None:
+        """barrier of the id-plan exchanges: its own arrival words and epoch, since it runs on another stream than the step's"""
+        self._pepoch += 1
+        self.h.call("ctr_peer_barrier", st, C.byref(self._rt0), self._pflags_off, self._pepoch, ptr(self.peer_status[1:]),
+                    int(os.environ.get("CTR_PEER_TIMEOUT_MS", 10000)))
+
+    def _launch_peer_reduce(self) -> None:
+        """after a step barrier: every replica's dense gradients are visible -> sum them on the aux stream"""
+        main = torch.cuda.current_stream(self.dev)
+        self.ev_bar.record(main)
+        self.aux.wait_event(self.ev_bar)
+        self.h.call("ctr_peer_reduce_sum", self.aux.cuda_stream, C.byref(self._rt_dense), self.n_dense + _ALIGN, ptr(self.grad_red))
+        self.ev_red.record(self.aux)
+        self._red_pending = True
+
+    _red_pending = False
+
+    def _dense_grad(self) -> torch.Tensor:
+        return self.grad_red if (self.exchange_mode == "peer" and self.train_mode) else self.grad
+
+    def _reduce_dense_grads(self) -> None:
+        if self.exchange_mode == "peer":
+            if not self._red_pending:            # no sparse side this step: the barrier has not happened yet
+                self._barrier(self._stream())
+                self._launch_peer_reduce()
+            torch.cuda.current_stream(self.dev).wait_event(self.ev_red)
+            self._red_pending = False
+            return
+        if self._dense_work is not None:
+            self._dense_work.wait()          # stream-side wait: the main stream continues behind the collective
+            self._dense_work = None
 
     def _global_loss(self) -> torch.Tensor:
-        return self.grad[self.n_dense:self.n_dense + 1].clone()
+        return self._dense_grad()[self.n_dense:self.n_dense + 1].clone()
 
     def predict(self, batch: Optional[Dict] = None) -> torch.Tensor:
         out = super().predict(batch)

@@ -374,6 +374,20 @@ typedef struct ctr_peer_route {
 int ctr_peer_barrier(ctr_handle* h, ctr_stream s, const ctr_peer_route* rt, int64_t flags_off, uint32_t epoch,
                      uint32_t* status, int timeout_ms);
 
+/* The three small exchanges of a sharded step, as stores / loads over peer memory instead of NCCL collectives (whose
+ * host-side enqueue cost, ~0.3 ms each through torch.distributed, made the multi-GPU step host-bound):
+ *   ctr_peer_bcast       the same n_words 32-bit words into EVERY slab at rt->dst_off (replaces the all-gather of the
+ *                        per-owner unique counts, SURVEY 8e collective #1a); seg_end / dst_row are not used
+ *   ctr_peer_push_rows   row i of `src` ([n_rows, width] 32-bit words) to its routed row of the buffer at rt->dst_off in the
+ *                        owning peer's slab (replaces the all-to-all of the de-duplicated ids, #1b: width 1)
+ *   ctr_peer_reduce_sum  out[i] = sum_p slab[p][dst_off + 4 i], p in rank order (replaces the dense-gradient allreduce, #4;
+ *                        same order on every rank: replicas stay bitwise identical).  n % 4 == 0.
+ * All need a ctr_peer_barrier between the writer's store and the reader's load. */
+int ctr_peer_bcast(ctr_handle* h, ctr_stream s, const uint32_t* src, int n_words, const ctr_peer_route* rt);
+int ctr_peer_push_rows(ctr_handle* h, ctr_stream s, const uint32_t* src, int64_t n_rows, int width,
+                       const ctr_peer_route* rt);
+int ctr_peer_reduce_sum(ctr_handle* h, ctr_stream s, const ctr_peer_route* rt, int64_t n, float* out);
+
 /* fused owner gather + vector all-to-all: row i of the request list (keys of the rows peers asked this rank for,
  * grouped by peer) is read from the table and stored into the requesting peer's staging buffer:
  *   peer(i).buf[dst_row + (i - seg_begin), :width] = table[idx[i] & mask, :width], columns [width, dst_stride) = 0 */
