@@ -177,6 +177,7 @@ class Handle:
         self.sm_count = self.lib.ctr_sm_count(h)
         self.has_tcgen05 = bool(self.lib.ctr_has_tcgen05(h))
         self.timers = None     # name -> [events] when bench.py profiles selected entry points
+        self._fn = {}          # entry point name -> bound ctypes function (getattr on a CDLL is a dict miss + a dlsym wrapper)
 
     def call(self, name: str, stream: int, *args):
         tm = self.timers.get(name) if self.timers is not None else None
@@ -185,7 +186,10 @@ class Handle:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             ts = torch.cuda.ExternalStream(stream) if stream else torch.cuda.current_stream()
             e0.record(ts)        # events go on the stream the kernel is launched on
-        rc = getattr(self.lib, name)(self.h, stream, *args)
+        fn = self._fn.get(name)
+        if fn is None:
+            fn = self._fn[name] = getattr(self.lib, name)
+        rc = fn(self.h, stream, *args)
         if rc != 0:
             raise CtrError("%s failed (%d): %s" % (name, rc, self.lib.ctr_last_error(self.h).decode()))
         if tm is not None:

@@ -610,6 +610,34 @@ segment_sum_rows_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* 
     }
 }
 
+// 128-bit form: one thread per (run, 4 columns); strides are multiples of 4 floats, so the pad columns of a row ride along
+__global__ void __launch_bounds__(256)
+segment_sum_rows_vec_kernel(const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ n_unique, int64_t n_max,
+                            const uint32_t* __restrict__ perm, const float* __restrict__ src, int src_stride, int nq,
+                            float* __restrict__ dst, int dst_stride) {
+    int64_t U = *n_unique;
+    if (U > n_max) U = n_max;
+    const int64_t total = U * nq;
+    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
+        const int64_t u = t / nq;
+        const int q = (int) (t - u * nq);
+        const uint32_t s0 = __ldg(seg_start + u), s1 = __ldg(seg_start + u + 1);
+        float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+        uint32_t i = s0;
+        for (; i + 2 <= s1; i += 2) {        // two contributions in flight; the additions stay in run order
+            const float4 x = __ldg(reinterpret_cast<const float4*>(src + (int64_t) __ldg(perm + i) * src_stride) + q);
+            const float4 y = __ldg(reinterpret_cast<const float4*>(src + (int64_t) __ldg(perm + i + 1) * src_stride) + q);
+            a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+            a.x += y.x; a.y += y.y; a.z += y.z; a.w += y.w;
+        }
+        if (i < s1) {
+            const float4 x = __ldg(reinterpret_cast<const float4*>(src + (int64_t) __ldg(perm + i) * src_stride) + q);
+            a.x += x.x; a.y += x.y; a.z += x.z; a.w += x.w;
+        }
+        *(reinterpret_cast<float4*>(dst + u * dst_stride) + q) = a;
+    }
+}
+
 inline int cont_blocks(ctr_handle* h, int B) {
     int64_t nb = ctr_cdiv(B > 0 ? B : 1, 128);
     int64_t cap = (int64_t) h->sm_count * 2;
@@ -860,6 +888,15 @@ extern "C" int ctr_segment_sum_rows(ctr_handle* h, ctr_stream s, const uint32_t*
     CTR_REQUIRE(h, seg_start && n_unique && perm && src && dst && width > 0 && src_stride >= width && dst_stride >= width &&
                        n_max >= 0, "segment_sum_rows: bad args");
     if (n_max == 0) return CTR_OK;
+    const int nq = (width + 3) / 4;
+    if (src_stride % 4 == 0 && dst_stride % 4 == 0 && nq * 4 <= src_stride && nq * 4 <= dst_stride &&
+        ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0) {
+        int64_t blocks = ctr_cdiv(n_max * nq, 256);      // no cap: a thread's work is one short dependent chain
+        segment_sum_rows_vec_kernel<<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(seg_start, n_unique, n_max, perm, src, src_stride,
+                                                                              nq, dst, dst_stride);
+        CTR_CHECK_LAUNCH(h, "segment_sum_rows_vec");
+        return CTR_OK;
+    }
     segment_sum_rows_kernel<<<grid_for(h, n_max * width), 256, 0, ctr_st(s)>>>(seg_start, n_unique, n_max, perm, src,
                                                                               src_stride, width, dst, dst_stride);
     CTR_CHECK_LAUNCH(h, "segment_sum_rows");

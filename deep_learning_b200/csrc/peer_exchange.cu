@@ -96,32 +96,50 @@ extern "C" int ctr_peer_barrier(ctr_handle* h, ctr_stream s, const ctr_peer_rout
 // one thread per (row, 4 columns): 128-bit table load (L1-bypassing: every row is wanted once), 128-bit store into the
 // requester's staging buffer -- consecutive rows of a segment are consecutive at the destination, so the NVLink
 // stores of a warp are contiguous
+constexpr int GP_UN = 4;       // rows in flight per thread: the id -> row -> NVLink store chain is latency, not bandwidth
 __global__ void __launch_bounds__(256)
 gather_rows_push_kernel(const float* __restrict__ table, int table_stride, const uint32_t* __restrict__ idx, int64_t n,
                         uint32_t mask, int width, int ds, const PeerRoute rt) {
     const int nq = ds >> 2;
     const int64_t total = n * nq;
-    for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
-        const int64_t i = t / nq;
-        const int q = (int) (t - i * nq);
-        const uint32_t key = __ldg(idx + i);
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        const int c = q * 4;
-        if (key != CTR_PAD_KEY && c < width) {
-            const float* src = table + (int64_t) (key & mask) * table_stride + c;
-            if (c + 4 <= table_stride) {
-                v = ctr_ldg_f4_stream(src);
-            } else {
-                v.x = src[0];
-                if (c + 1 < table_stride) v.y = src[1];
-                if (c + 2 < table_stride) v.z = src[2];
-            }
-            if (c + 1 >= width) v.y = 0.f;
-            if (c + 2 >= width) v.z = 0.f;
-            if (c + 3 >= width) v.w = 0.f;
+    const int64_t nthreads = (int64_t) gridDim.x * blockDim.x;
+    for (int64_t t0 = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t0 < total; t0 += nthreads * GP_UN) {
+        float4 v[GP_UN];
+        int64_t ii[GP_UN];
+        int cc[GP_UN];
+        uint32_t key[GP_UN];
+#pragma unroll
+        for (int k = 0; k < GP_UN; ++k) {        // item k of this thread is nthreads apart: a warp still reads consecutive items
+            const int64_t t = t0 + k * nthreads;
+            ii[k] = t < total ? t / nq : -1;
+            cc[k] = t < total ? (int) (t - ii[k] * nq) * 4 : 0;
+            key[k] = ii[k] >= 0 ? __ldg(idx + ii[k]) : CTR_PAD_KEY;
         }
-        float* dst = route_row(rt, (uint32_t) i, ds);
-        *reinterpret_cast<float4*>(dst + c) = v;
+#pragma unroll
+        for (int k = 0; k < GP_UN; ++k) {
+            v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int c = cc[k];
+            if (key[k] != CTR_PAD_KEY && c < width) {
+                const float* src = table + (int64_t) (key[k] & mask) * table_stride + c;
+                if (c + 4 <= table_stride) {
+                    v[k] = ctr_ldg_f4_stream(src);
+                } else {
+                    v[k].x = src[0];
+                    if (c + 1 < table_stride) v[k].y = src[1];
+                    if (c + 2 < table_stride) v[k].z = src[2];
+                }
+                if (c + 1 >= width) v[k].y = 0.f;
+                if (c + 2 >= width) v[k].z = 0.f;
+                if (c + 3 >= width) v[k].w = 0.f;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < GP_UN; ++k) {
+            if (ii[k] >= 0) {
+                float* dst = route_row(rt, (uint32_t) ii[k], ds);
+                *reinterpret_cast<float4*>(dst + cc[k]) = v[k];
+            }
+        }
     }
 }
 
@@ -135,7 +153,7 @@ extern "C" int ctr_gather_rows_push(ctr_handle* h, ctr_stream s, const float* ta
     CTR_REQUIRE(h, (int64_t) rt->seg_end[rt->world - 1] == n_rows, "gather_rows_push: route does not cover the request list");
     if (n_rows == 0) return CTR_OK;
     uint32_t mask = (idx_mask_bits <= 0 || idx_mask_bits >= 32) ? 0xFFFFFFFFu : ((1u << idx_mask_bits) - 1u);
-    int64_t blocks = ctr_cdiv(n_rows * (dst_stride / 4), 256);
+    int64_t blocks = ctr_cdiv(n_rows * (dst_stride / 4), 256 * GP_UN);
     int64_t cap = (int64_t) h->sm_count * 8;
     if (blocks > cap) blocks = cap;
     gather_rows_push_kernel<<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(table, table_stride, idx, n_rows, mask, width,

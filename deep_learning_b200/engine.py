@@ -179,8 +179,23 @@ class CtrEngine:
                         table_stride=s.table_stride, x0_ld=s.x0_ld, fm_ld=s.fm_ld, grad_stride=s.grad_stride,
                         round_tf32=int(self.prec == 1))
 
+    # the stream a step runs on is looked up ONCE per public call (torch.cuda.current_stream costs ~7 us of host time, and a
+    # step asked for it ~20 times: the multi-GPU step is close to host-bound)
+    _main_cached = None
+    _st_cached = None
+
+    def _main_stream(self) -> torch.cuda.Stream:
+        return self._main_cached if self._main_cached is not None else torch.cuda.current_stream(self.dev)
+
     def _stream(self) -> int:
-        return torch.cuda.current_stream(self.dev).cuda_stream
+        return self._st_cached if self._st_cached is not None else torch.cuda.current_stream(self.dev).cuda_stream
+
+    def _pin_stream(self) -> None:
+        self._main_cached = torch.cuda.current_stream(self.dev)
+        self._st_cached = self._main_cached.cuda_stream
+
+    def _unpin_stream(self) -> None:
+        self._main_cached = self._st_cached = None
 
     host_prof = None       # tests/host_timing.py
     _sort_B = None         # batch size whose id sort forward() still has to enqueue (train steps only)
@@ -189,15 +204,24 @@ class CtrEngine:
     def _mark(self, name: str) -> None:
         if self.phase_marks is not None:
             ev = torch.cuda.Event(enable_timing=True)
-            ev.record(torch.cuda.current_stream(self.dev))
+            ev.record(self._main_stream())
             self.phase_marks.append((name, ev))
+
+    @property
+    def _vw(self) -> Dict:
+        d = self.__dict__.get("_vw_cache")
+        if d is None:
+            d = self.__dict__["_vw_cache"] = {}
+        return d
 
     def view(self, name: str, buf: Optional[torch.Tensor] = None) -> torch.Tensor:
         """flat-buffer view of a dense parameter (internal layout)"""
         buf = self.theta if buf is None else buf
-        shp = self.shape[name]
-        n = int(np.prod(shp))
-        return buf[self.off[name]: self.off[name] + n]
+        rng = self._vw.get(name)
+        if rng is None:
+            o = self.off[name]
+            rng = self._vw[name] = (o, o + int(np.prod(self.shape[name])))
+        return buf[rng[0]:rng[1]]
 
     def _w(self, i: int, buf=None):
         return self.view("deep_%d" % i, buf)
@@ -246,7 +270,7 @@ class CtrEngine:
                 perm = np.concatenate([s.head_fm_perm(), s.n_fm + np.arange(s.hidden[-1])])
                 a = a[perm, :]
             self.view(name, flat).copy_(t(a).reshape(-1))
-        torch.cuda.current_stream(self.dev).synchronize()
+        self._main_stream().synchronize()
 
     def set_optimizer_state(self, m: Dict[str, np.ndarray], v: Dict[str, np.ndarray], global_step: int,
                             beta1_power: float, beta2_power: float) -> None:
@@ -330,7 +354,7 @@ class CtrEngine:
         `shard-<rank>-of-<world>.npz`."""
         s = self.spec
         os.makedirs(path, exist_ok=True)
-        torch.cuda.current_stream(self.dev).synchronize()
+        self._main_stream().synchronize()
         R = self.rows_local
         blob = {"meta": np.asarray([self.world, self.rank, s.table_rows, s.k, s.table_stride, self.global_step, self.n_dense,
                                     int(self.train_mode)], dtype=np.int64),
@@ -388,7 +412,7 @@ class CtrEngine:
                 self.beta1_power, self.beta2_power = float(z["powers"][0]), float(z["powers"][1])
                 first = False
         self._refresh_transposes()
-        torch.cuda.current_stream(self.dev).synchronize()
+        self._main_stream().synchronize()
 
     def _assemble_rows(self, shard: torch.Tensor) -> np.ndarray:
         """full [table_rows, w] host array from this rank's shard (one GPU: the shard IS the table)"""
@@ -435,7 +459,7 @@ class CtrEngine:
         (may be < max_batch for the short last batch, models/deepfm.py:178).  A batch announced as `next_batch`
         of the previous train_step is already on the device: the buffer sets just flip."""
         if self._pf_id is not None and self._pf_id == id(batch):
-            torch.cuda.current_stream(self.dev).wait_event(self._pf_event)
+            self._main_stream().wait_event(self._pf_event)
             self._use_inputs(1 - self._cur_in)
             self._pf_id = None
             self.last_batch = self._pf_B
@@ -578,7 +602,7 @@ class CtrEngine:
         if s.ids_ld and self.n_extra:
             # gradient of the C continuous-field rows: needs only dlogit / sum_e / cont, so it runs on its own stream
             # underneath the tower's backward GEMMs (26 us off the critical path at config 4), with its own workspace
-            main = torch.cuda.current_stream(self.dev)
+            main = self._main_stream()
             self.ev_head.record(main)
             self.aux.wait_event(self.ev_head)
             h.call("ctr_fm_cont_bwd", self.aux.cuda_stream, cfg, ptr(self.cont), ptr(self._cont_rows()), ptr(self.sum_e),
@@ -605,10 +629,10 @@ class CtrEngine:
         # ---- sparse side: sort -> runs -> partials -> Adam on touched rows ------------------------------
         if s.ids_ld:
             n = B * s.ids_ld + self.n_extra
-            torch.cuda.current_stream(self.dev).wait_event(self.ev_sorted)
+            self._main_stream().wait_event(self.ev_sorted)
             self._mark("wait_sort")
             if self.n_extra:
-                torch.cuda.current_stream(self.dev).wait_event(self.ev_cont)
+                self._main_stream().wait_event(self.ev_cont)
             h.call("ctr_embed_bwd_partials_weighted", st, cfg, ptr(self.keys), ptr(self.perm), ptr(self.uidx), n,
                    ptr(self.field_of_slot), ptr(self.x0), ptr(self.dx0), self.dx0_ld, ptr(self.sum_e), ptr(self.dlogit),
                    ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.sw),
@@ -659,7 +683,7 @@ class CtrEngine:
         s, h = self.spec, self.h
         if not s.ids_ld:
             return
-        main = torch.cuda.current_stream(self.dev)
+        main = self._main_stream()
         self.ev_batch.record(main)
         self.side.wait_event(self.ev_batch)
         n = B * s.ids_ld + self.n_extra
@@ -683,7 +707,7 @@ class CtrEngine:
                    max(1, int(rows - 1).bit_length()), ptr(self.w_keys), ptr(self.w_perm), ws, wsn)
             h.call("ctr_unique_segments", st, ptr(self.w_keys), nw, ptr(self.w_uniq), ptr(self.w_seg_start),
                    ptr(self.w_uidx), ptr(self.w_n_unique), ws, wsn)
-            self.ev_sorted_w.record(self.side if st == self.side.cuda_stream else torch.cuda.current_stream(self.dev))
+            self.ev_sorted_w.record(self.side if st == self.side.cuda_stream else self._main_stream())
 
     def _wdl_wide_grad(self, B: int) -> None:
         """d wdl_weights[id] += sum of dlogit over the wide lookups of id (added on top of the deep-projection
@@ -691,7 +715,7 @@ class CtrEngine:
         s = self.spec
         if not s.wide_fields:
             return
-        torch.cuda.current_stream(self.dev).wait_event(self.ev_sorted_w)
+        self._main_stream().wait_event(self.ev_sorted_w)
         self.h.call("ctr_scalar_segment_add", self._stream(), ptr(self.w_uniq), ptr(self.w_seg_start), ptr(self.w_n_unique),
                     B * s.wide_fields, ptr(self.w_perm), ptr(self.dlogit), s.wide_fields, s.wide_rows + s.hidden[-1],
                     ptr(self.view("wdl_weights", self.grad)))
@@ -730,6 +754,13 @@ class CtrEngine:
 
     # ---- public step API -------------------------------------------------------------------------------
     def train_step(self, batch: Optional[Dict] = None, next_batch: Optional[Dict] = None) -> torch.Tensor:
+        self._pin_stream()
+        try:
+            return self._train_step(batch, next_batch)
+        finally:
+            self._unpin_stream()
+
+    def _train_step(self, batch: Optional[Dict] = None, next_batch: Optional[Dict] = None) -> torch.Tensor:
         """One `sess.run([loss, optimizer])` (models/deepfm.py:181).  Returns the loss as a device
         scalar tensor (log-loss + regulariser); call .item() to read it.  `next_batch` (optional) is the batch the
         NEXT call will train on: the input pipeline knows it one step ahead (the reference's tf.data iterator
@@ -743,7 +774,7 @@ class CtrEngine:
             # whatever produced `next_batch` was enqueued before this call: work on other streams that reads it waits
             # for this point of the main stream and no later one
             ev_call = torch.cuda.Event()
-            ev_call.record(torch.cuda.current_stream(self.dev))
+            ev_call.record(self._main_stream())
         B = self.load_batch(batch) if batch is not None else self.last_batch
         self._sort_B = B                    # enqueued by forward(), right behind the gather
         self._mark("load")
@@ -775,7 +806,7 @@ class CtrEngine:
         self._pf_id = id(next_batch)
 
     def _end_step(self) -> None:
-        self._in_free[self._cur_in].record(torch.cuda.current_stream(self.dev))
+        self._in_free[self._cur_in].record(self._main_stream())
         self._in_used[self._cur_in] = True
 
     def _global_loss(self) -> torch.Tensor:

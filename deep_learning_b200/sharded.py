@@ -260,7 +260,7 @@ class ShardedCtrEngine(CtrEngine):
         return self.plans[1] if self.cur is self.plans[0] else self.plans[0]
 
     def load_batch(self, batch: Dict, non_blocking: bool = True, skip_ids: bool = False) -> int:
-        main = torch.cuda.current_stream(self.dev)
+        main = self._main_stream()
         pl = next((c for c in self.plans if c.in_flight and c.batch_id == id(batch)), None)
         if pl is not None:                         # prefetched during the previous step
             B = super().load_batch(batch, non_blocking, skip_ids=True)     # (flips the input sets if it was uploaded too)
@@ -314,7 +314,7 @@ class ShardedCtrEngine(CtrEngine):
     def _end_step(self) -> None:
         super()._end_step()
         if self.cur is not None:
-            self.cur.ev_free.record(torch.cuda.current_stream(self.dev))
+            self.cur.ev_free.record(self._main_stream())
             if self.cur.batch_id is None:
                 self.cur.batch_id = -1             # marks ev_free as recorded
 
@@ -324,7 +324,7 @@ class ShardedCtrEngine(CtrEngine):
 
     def _embed_forward(self, B: int) -> None:
         s, st, h, sp, pl = self.spec, self._stream(), self.h, self.plan, self.cur
-        main = torch.cuda.current_stream(self.dev)
+        main = self._main_stream()
         if pl.on_side:
             main.wait_event(pl.ev_ready)
         U, n_req = pl.U, pl.n_req
@@ -418,7 +418,7 @@ class ShardedCtrEngine(CtrEngine):
 
     def _launch_peer_reduce(self) -> None:
         """after a step barrier: every replica's dense gradients are visible -> sum them on the aux stream"""
-        main = torch.cuda.current_stream(self.dev)
+        main = self._main_stream()
         self.ev_bar.record(main)
         self.aux.wait_event(self.ev_bar)
         self.h.call("ctr_peer_reduce_sum", self.aux.cuda_stream, C.byref(self._rt_dense), self.n_dense + _ALIGN, ptr(self.grad_red))
@@ -435,7 +435,7 @@ class ShardedCtrEngine(CtrEngine):
             if not self._red_pending:            # no sparse side this step: the barrier has not happened yet
                 self._barrier(self._stream())
                 self._launch_peer_reduce()
-            torch.cuda.current_stream(self.dev).wait_event(self.ev_red)
+            self._main_stream().wait_event(self.ev_red)
             self._red_pending = False
             return
         if self._dense_work is not None:
