@@ -14,6 +14,7 @@ import numpy as np
 import torch
 
 from . import _lib
+from . import shard as _shard
 from ._lib import DenseLayout, MAX_LAYERS, AdamHP, EmbedCfg, ptr
 from .spec import ModelSpec
 
@@ -198,6 +199,7 @@ class CtrEngine:
         self._main_cached = self._st_cached = None
 
     host_prof = None       # tests/host_timing.py
+    _pf_obj = None
     _sort_B = None         # batch size whose id sort forward() still has to enqueue (train steps only)
     phase_marks = None     # list of (name, event) when a timing script asks for the main-stream phase picture
 
@@ -396,10 +398,8 @@ class CtrEngine:
                 for name, dst in pairs:
                     dst[:R].copy_(torch.from_numpy(z[name]))
             else:
-                n_old = z["table"].shape[0]
-                ids = np.arange(n_old, dtype=np.int64) * w_old + r_old
-                keep = (ids % self.world == self.rank) & (ids < s.table_rows)
-                loc = torch.from_numpy(ids[keep] // self.world).to(self.dev)
+                keep, loc_np = _shard.reshard_rows(z["table"].shape[0], w_old, r_old, self.world, self.rank, s.table_rows)
+                loc = torch.from_numpy(loc_np).to(self.dev)
                 for name, dst in pairs:
                     dst[loc] = torch.from_numpy(z[name][keep]).to(self.dev)
             if first:
@@ -461,10 +461,10 @@ class CtrEngine:
         if self._pf_id is not None and self._pf_id == id(batch):
             self._main_stream().wait_event(self._pf_event)
             self._use_inputs(1 - self._cur_in)
-            self._pf_id = None
+            self._pf_id = self._pf_obj = None
             self.last_batch = self._pf_B
             return self._pf_B
-        self._pf_id = None
+        self._pf_id = self._pf_obj = None
         B = self._copy_inputs(batch, self._in[self._cur_in], non_blocking, skip_ids)
         self.last_batch = B
         return B
@@ -804,6 +804,7 @@ class CtrEngine:
             self._pf_B = self._copy_inputs(next_batch, self._in[other], True, self._ids_external)
         self._pf_event.record(cs)
         self._pf_id = id(next_batch)
+        self._pf_obj = next_batch          # keeps the object alive, so its id cannot be recycled while the upload is pending
 
     def _end_step(self) -> None:
         self._in_free[self._cur_in].record(self._main_stream())

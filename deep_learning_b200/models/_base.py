@@ -56,6 +56,20 @@ def init_weights(spec: ModelSpec, seed: int = 2019, with_table: bool = True) -> 
     return p
 
 
+def _lookahead(items: Iterable):
+    """(item, next item or None) pairs: the engine uploads / plans the next batch underneath the current step when it is
+    told one step ahead what comes next (the reference's tf.data iterator prefetches the same way, utils/data_loader.py:29-40)"""
+    it = iter(items)
+    try:
+        cur = next(it)
+    except StopIteration:
+        return
+    for nxt in it:
+        yield cur, nxt
+        cur = nxt
+    yield cur, None
+
+
 class BaseDeepModel:
     ALG = ""
     GENERATION = "A"     # "A": feed_dict / pickled batches; "B": iterator of batch dicts
@@ -139,8 +153,8 @@ class BaseDeepModel:
         losses, num_samples = [], 0       # never reset between epochs, as in the reference (:168-169)
         for epoch in range(self.epochs):
             st = time.time()
-            for item in train_data:
-                loss = self.engine.train_step(self._decode(item))
+            for b, nb in _lookahead(self._decode(item) for item in train_data):
+                loss = self.engine.train_step(b, next_batch=nb)
                 losses.append(loss)
                 num_samples += self.batch_size
             total_loss = float(torch.stack(losses).sum().item() * self.batch_size / max(num_samples, 1))
@@ -178,8 +192,8 @@ class BaseDeepModel:
         print("Start of training")
         start_time = time.time()
         batch_count, i = 0, 0
-        for item in self.data_dict:       # StopIteration replaces tf.errors.OutOfRangeError
-            loss = self.engine.train_step(self._decode(item))
+        for b, nb in _lookahead(self._decode(item) for item in self.data_dict):   # the end of the iterator replaces tf.errors.OutOfRangeError
+            loss = self.engine.train_step(b, next_batch=nb)
             if batch_count == print_num_batch:
                 batch_end_time = time.time()
                 auc = self.eval(None, val_data)

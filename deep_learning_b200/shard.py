@@ -23,6 +23,7 @@ from __future__ import annotations
 
 from typing import List, Optional, Sequence, Tuple
 
+import numpy as np
 import torch
 import torch.distributed as dist
 
@@ -121,3 +122,12 @@ def peer_routes(mat: Sequence[Sequence[int]], rank: int):
     vec = (ends(recv), [sum(int(mat[p][o]) for o in range(rank)) for p in range(world)])
     grad = (ends(send), [sum(int(mat[p][o]) for p in range(rank)) for o in range(world)])
     return send, recv, vec, grad
+
+
+def reshard_rows(n_old_local: int, w_old: int, r_old: int, w_new: int, r_new: int, table_rows: int):
+    """Rows of an old shard (rank r_old of w_old: local row l holds id l * w_old + r_old) that rank r_new of w_new owns
+    now: (boolean mask over the old shard's rows, their new local rows id // w_new).  Used when a per-shard checkpoint
+    is restored at another world size (train on 8, serve on 1)."""
+    ids = np.arange(n_old_local, dtype=np.int64) * w_old + r_old
+    keep = (ids % w_new == r_new) & (ids < table_rows)
+    return keep, ids[keep] // w_new

@@ -309,6 +309,7 @@ class ShardedCtrEngine(CtrEngine):
             pl.ids[:B].copy_(cate.to(self.id_torch) if cate.dtype != self.id_torch else cate, non_blocking=True)
         self._build_local(pl, B, self.side)
         pl.batch_id, pl.in_flight, pl.on_side = id(next_batch), True, True
+        pl.batch_obj = next_batch             # keeps the id from being recycled while the plan is pending
         self._pending_exchange = pl
 
     def _end_step(self) -> None:

@@ -335,3 +335,92 @@ def test_per_shard_checkpoint_resume_bit_identical(tmp_path):
                     hp.batch_size, adam_mode="lazy")
     with pytest.raises(ValueError):
         other.load_shard(str(tmp_path))
+
+
+# ---- BASELINE.json configurations at their FULL batch sizes (the oracle finishes a step in seconds) --------------------------
+def test_config1_deepfm_multi_full_batch_16k():
+    """configs[1]: models/deepfm_multi.py, multi-valued fields with the mean combiner, k=16, batch 16K"""
+    _run_parity("deepfm_multi", H.hp_multi(B=16384), steps=1, adam_mode="lazy")
+
+
+def test_config2_wdl_full_batch_64k():
+    """configs[2]: models/wdl.py Criteo shape (13 dense + 26 sparse, k=16, MLP 400-400-400), batch 64K (200K-row table)"""
+    _run_parity("wdl", H.hp_criteo(B=65536, rows=200000), steps=1, adam_mode="lazy")
+
+
+@pytest.mark.parametrize("precision", ["fp32", "tf32"])
+def test_config3_deepfm_criteo_full_batch_64k(precision):
+    """configs[3] / north-star workload on one GPU: DeepFM Criteo shape, k=16, batch 64K (200K-row table so the fp64 oracle
+    holds the dense gradient): FP32 path 1e-5, TF32 tensor-core path 2e-3"""
+    _run_parity("deepfm", H.hp_criteo(B=65536, rows=200000), steps=1, precision=precision, adam_mode="lazy")
+
+
+def test_config4_predict_sweep_matches_oracle():
+    """configs[4]: predict-only, batch 1K .. 256K through one engine (short batches reuse the buffers of the largest)"""
+    hp = H.hp_criteo(B=262144, rows=200000)
+    p = O.init_params("deepfm", hp, seed=2019, dtype=torch.float64)
+    eng = _engine("deepfm", hp, p, 262144)
+    for B in (1024, 16384, 65536, 262144):
+        b = H.make_batch("deepfm", hp, seed=50 + B % 97, B=B)
+        _, score_ref = O.deepfm_forward(p, H.oracle_batch(b, torch.float64), hp)
+        score = eng.predict(b).cpu().numpy()
+        assert score.shape == (B,)
+        assert np.max(np.abs(score - score_ref.numpy().reshape(-1))) < 1e-5, B
+
+
+def test_text_files_through_the_native_loader_train_identically(tmp_path, capsys):
+    """SURVEY.md 8f N1 end to end: `part-*` text files -> loaders.load_process (native decoder, pinned batches) ->
+    DeepModel.fit == the same model fitted on the reference's pickled batches of the same rows (bit-identical weights)"""
+    from deep_learning_b200 import data as D, loaders as L
+    from deep_learning_b200.hparams import ModelParams
+    import deep_learning_b200.models.deepfm as alg_model
+    hp = H.hp_c1(batch_size=128, epochs=1)
+    batches = [H.make_batch("deepfm", hp, seed=900 + s, B=128 if s < 3 else 70) for s in range(4)]     # short last batch
+    d = str(tmp_path) + "/"
+    with open(d + "part-00000", "w") as f:
+        for b in batches:
+            for r in range(b["label"].shape[0]):
+                f.write("%d,%s,%s\n" % (int(b["label"][r, 0]), " ".join(repr(float(x)) for x in b["cont_feats"][r]),
+                                        " ".join(str(int(x)) for x in b["cate_feats"][r])))
+    mp = ModelParams(alg_name="deepfm", batch_size=128, cont_field_size=hp.cont_field_size, cate_field_size=hp.cate_field_size)
+    loaded = L.load_input_file(mp, d, "load")
+    assert [int(x["labels"].shape[0]) for x in loaded] == [128, 128, 128, 70]
+    assert torch.equal(loaded[3]["cate_feats"], batches[3]["cate_feats"]) and torch.equal(loaded[1]["cont_feats"], batches[1]["cont_feats"])
+    val = [D.to_pickled_batch(batches[0])]
+    ma = alg_model.DeepModel(hp, adam_mode="lazy")
+    ma.fit(loaded, val)
+    mb = alg_model.DeepModel(hp, adam_mode="lazy")
+    mb.fit([D.to_pickled_batch(b) for b in batches], val)
+    wa, wb = ma.engine.get_weights(), mb.engine.get_weights()
+    for n in wa:
+        assert np.array_equal(wa[n], wb[n]), n
+    assert ma.engine.global_step == 4
+
+
+def test_tfrecords_through_the_native_loader_feed_generation_b(tmp_path, capsys):
+    """TFRecord files -> loaders.pipeline_process -> the generation-B fit loop (models/deepfm_multi.py): same weights as
+    feeding the tensors directly"""
+    from oracle import loader_oracle as LO
+    from deep_learning_b200 import loaders as L
+    from deep_learning_b200.hparams import ModelParams
+    import deep_learning_b200.models.deepfm_multi as alg_model
+    hp = H.hp_multi(B=64)
+    batches = [H.make_batch("deepfm_multi", hp, seed=950 + s, B=64) for s in range(3)]
+    d = str(tmp_path) + "/"
+    rows = []
+    for b in batches:
+        for r in range(64):
+            rows.append(LO.encode_example({"label": b["label"][r].numpy(), "cont_feats": b["cont_feats"][r].numpy(),
+                                           "vector_feats": b["vector_feats"][r].numpy(), "cate_feats": b["cate_feats"][r].numpy()}))
+    LO.write_tfrecord(d + "part-r-00000", rows)
+    mp = ModelParams(alg_name="deepfm_multi", batch_size=64, epochs=1, cont_field_size=hp.cont_field_size,
+                     vector_feats_size=hp.vector_feats_size, cate_field_size=hp.cate_field_size, multi_feats_size=hp.multi_feats_size)
+    val = [batches[0]]
+    ma = alg_model.DeepModel(hp, L.load_tfrecord_input_file(mp, d, "train"), adam_mode="lazy")
+    ma.fit(100, iter(val))
+    mb = alg_model.DeepModel(hp, iter(batches), adam_mode="lazy")
+    mb.fit(100, iter(val))
+    wa, wb = ma.engine.get_weights(), mb.engine.get_weights()
+    for n in wa:
+        assert np.array_equal(wa[n], wb[n]), n
+    assert ma.engine.global_step == 3

@@ -38,3 +38,27 @@ def test_routes_reproduce_the_all_to_all_layout(world):
     for r in range(world):
         assert rows_recv[r] == uniq[r]                      # vectors arrive in the requester's unique-list order
         assert g_recv[r] == req[r]                          # gradients arrive peer-major, rank 0's rows first
+
+
+def test_reshard_rows_partition_every_id_exactly_once():
+    """per-shard checkpoints restored at another world size (CtrEngine.load_shard): every row id of the table ends up on
+    exactly one new rank, at local row id // w_new"""
+    import numpy as np
+    from deep_learning_b200 import shard as S
+    R = 1003
+    for w_old, w_new in ((8, 1), (2, 1), (1, 4), (8, 3), (3, 8)):
+        seen = np.zeros(R, dtype=np.int64)
+        for r_new in range(w_new):
+            rows_new = (R + w_new - 1) // w_new
+            got = np.full(rows_new, -1, dtype=np.int64)
+            for r_old in range(w_old):
+                n_old = (R + w_old - 1) // w_old            # shards are allocated to the rounded-up size
+                keep, loc = S.reshard_rows(n_old, w_old, r_old, w_new, r_new, R)
+                ids = np.arange(n_old, dtype=np.int64)[keep] * w_old + r_old
+                assert (ids % w_new == r_new).all() and (ids < R).all()
+                assert (got[loc] == -1).all()
+                got[loc] = ids
+                seen[ids] += 1
+            valid = got[got >= 0]
+            assert np.array_equal(valid, np.arange(len(got))[got >= 0] * w_new + r_new)
+        assert (seen == 1).all()
