@@ -104,6 +104,8 @@ _PROTOS = {
     "ctr_adam_rows_ws_bytes": (c_i64, [c_vp, c_i64]),
     "ctr_adam_rows": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp,
                               c_i32, c_i64, c_vp, c_vp, c_i64, c_vp, c_i32, _P_HP]),
+    "ctr_adam_rows_gathered": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp,
+                                       c_i32, c_i64, c_vp, c_vp, c_i32, _P_HP]),
     "ctr_adam_dense": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_f32, c_f32, c_vp, c_i32, _P_HP]),
     "ctr_auc_ws_bytes": (c_i64, [c_vp, c_i64]),
     "ctr_auc": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i64]),

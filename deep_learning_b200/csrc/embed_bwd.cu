@@ -263,7 +263,9 @@ adam_rows_vec_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __res
                      const float* __restrict__ grads, const uint32_t* __restrict__ seg_start, int gs, int has_first,
                      float* __restrict__ table, float* __restrict__ m, float* __restrict__ v, int stride, int64_t table_rows,
                      uint8_t* __restrict__ touched, uint32_t* __restrict__ long_list, const float* __restrict__ fm_w2,
-                     const ctr_adam_hp hp) {
+                     const uint32_t* __restrict__ perm, const ctr_adam_hp hp) {
+    // perm != NULL (owner side of the sharded step): run u is the contributions grads[perm[i]], i in [seg_start[u],
+    // seg_start[u+1]) -- one row per requesting peer, in peer order -- summed here instead of by ctr_segment_sum_rows
     constexpr int G = K / 4;
     int64_t U = n_rows ? (int64_t) *n_rows : n_max;
     if (U > n_max) U = n_max;
@@ -277,7 +279,11 @@ adam_rows_vec_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __res
         if (row >= table_rows) continue;
         const float* p = grads + u * gs;
         int np = 1;
-        if (seg_start) {
+        uint32_t r0 = 0;
+        if (perm) {
+            r0 = __ldg(seg_start + u);
+            np = (int) (__ldg(seg_start + u + 1) - r0);
+        } else if (seg_start) {
             const uint32_t s0 = __ldg(seg_start + u), s1 = __ldg(seg_start + u + 1);
             const int64_t c0 = s0 / CH;
             const int64_t npl = (int64_t) ((s1 - 1) / CH) - c0 + 1;
@@ -297,11 +303,12 @@ adam_rows_vec_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __res
         if (first) { th1 = table[row * stride + K]; m1 = m[row * stride + K]; v1 = v[row * stride + K]; }
         float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
         float g1 = 0.f, D = 0.f;
-        for (int i = 0; i < np; ++i) {       // partials in chunk order
-            const float4 a = __ldg(reinterpret_cast<const float4*>(p + (int64_t) i * gs + q * 4));
+        for (int i = 0; i < np; ++i) {       // partials in chunk order / peer contributions in run order
+            const float* pi = perm ? grads + (int64_t) __ldg(perm + r0 + i) * gs : p + (int64_t) i * gs;
+            const float4 a = __ldg(reinterpret_cast<const float4*>(pi + q * 4));
             g.x += a.x; g.y += a.y; g.z += a.z; g.w += a.w;
-            if (first) g1 += __ldg(p + (int64_t) i * gs + K);
-            if (fm_w2) D += __ldg(p + (int64_t) i * gs + K + 1);
+            if (first) g1 += __ldg(pi + K);
+            if (fm_w2) D += __ldg(pi + K + 1);
         }
         if (fm_w2) {
             const float4 w2 = make_float4(__ldg(fm_w2 + q * 4), __ldg(fm_w2 + q * 4 + 1), __ldg(fm_w2 + q * 4 + 2), __ldg(fm_w2 + q * 4 + 3));
@@ -770,7 +777,7 @@ extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_id
         const unsigned grid = grid_for(h, n_max * (emb_k / 4));
 #define LAUNCH_AV(KK)                                                                                                         \
     adam_rows_vec_kernel<KK><<<grid, 256, 0, ctr_st(s)>>>(row_ids, n_rows, n_max, mask, grads, seg_start, grad_stride, has_first, \
-                                                          table, m, v, table_stride, table_rows, touched, long_list, fm_w2, *hp)
+                                                          table, m, v, table_stride, table_rows, touched, long_list, fm_w2, nullptr, *hp)
         switch (emb_k) {
             case 4: LAUNCH_AV(4); break;
             case 8: LAUNCH_AV(8); break;
@@ -790,6 +797,35 @@ extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_id
                                                                                  touched, long_list, fm_w2, emb_k, *hp);
         CTR_CHECK_LAUNCH(h, "adam_rows_long");
     }
+    return CTR_OK;
+}
+
+extern "C" int ctr_adam_rows_gathered(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
+                                      int local_bits, const float* src, const uint32_t* perm, const uint32_t* seg_start,
+                                      int src_stride, int width, float* table, float* m, float* v, int table_stride,
+                                      int64_t table_rows, uint8_t* touched, const float* fm_w2, int emb_k, const ctr_adam_hp* hp) {
+    CTR_REQUIRE(h, row_ids && n_rows && src && perm && seg_start && table && m && v && hp, "adam_rows_gathered: null pointer");
+    CTR_REQUIRE(h, n_max >= 0 && table_rows > 0 && (emb_k == 4 || emb_k == 8 || emb_k == 16 || emb_k == 32) &&
+                       (width == emb_k || width == emb_k + 1) && table_stride % 4 == 0 && table_stride >= width &&
+                       src_stride % 4 == 0 && src_stride >= width + (fm_w2 ? (emb_k + 2 - width) : 0),
+                "adam_rows_gathered: embedding-row shapes only (k = 4/8/16/32, strides multiples of 4)");
+    CTR_REQUIRE(h, ((reinterpret_cast<uintptr_t>(table) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v) |
+                     reinterpret_cast<uintptr_t>(src)) & 15) == 0, "adam_rows_gathered: buffers must be 16-byte aligned");
+    if (n_max == 0) return CTR_OK;
+    const uint32_t mask = (local_bits <= 0 || local_bits >= 32) ? 0xFFFFFFFFu : ((1u << local_bits) - 1u);
+    const int has_first = width == emb_k + 1;
+    const unsigned grid = (unsigned) ctr_cdiv(n_max * (emb_k / 4), 256);
+#define LAUNCH_AG(KK)                                                                                                          \
+    adam_rows_vec_kernel<KK><<<grid, 256, 0, ctr_st(s)>>>(row_ids, n_rows, n_max, mask, src, seg_start, src_stride, has_first,    \
+                                                          table, m, v, table_stride, table_rows, touched, nullptr, fm_w2, perm, *hp)
+    switch (emb_k) {
+        case 4: LAUNCH_AG(4); break;
+        case 8: LAUNCH_AG(8); break;
+        case 16: LAUNCH_AG(16); break;
+        default: LAUNCH_AG(32); break;
+    }
+#undef LAUNCH_AG
+    CTR_CHECK_LAUNCH(h, "adam_rows_gathered");
     return CTR_OK;
 }
 

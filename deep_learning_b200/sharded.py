@@ -389,6 +389,12 @@ class ShardedCtrEngine(CtrEngine):
         self._mark("a2a_grads")
         if not n_req:
             return
+        if os.environ.get("CTR_OWNER_UPDATE", "fused") == "fused":
+            # sum of the peers' contributions (fixed peer order) + TF1 Adam on the owned row, one launch
+            h.call("ctr_adam_rows_gathered", st, ptr(pl.o_uniq), ptr(pl.o_nuniq), n_req, sp.local_bits, ptr(self.g_recv),
+                   ptr(pl.o_idx), ptr(pl.o_seg), self.wire, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table),
+                   s.table_stride, self.rows_local, ptr(self.touched), self._fm_w2(), s.k, hp)
+            return
         h.call("ctr_segment_sum_rows", st, ptr(pl.o_seg), ptr(pl.o_nuniq), n_req, ptr(pl.o_idx), ptr(self.g_recv),
                self.wire, s.grad_width, ptr(self.g_own), self.wire)
         h.call("ctr_adam_rows", st, ptr(pl.o_uniq), ptr(pl.o_nuniq), n_req, sp.local_bits, ptr(self.g_own), None,

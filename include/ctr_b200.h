@@ -302,6 +302,14 @@ int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const ui
                   uint8_t* touched, void* ws, int64_t ws_bytes /* ctr_adam_rows_ws_bytes(); needed when seg_start != NULL:
                   runs spread over many chunks (hot rows) are queued and reduced by one warp each */,
                   const float* fm_w2, int emb_k, const ctr_adam_hp* hp);
+/* Owner side of the sharded step in one launch: run u of the (stable-sorted) request list is the gradient rows
+ * src[perm[i]], i in [seg_start[u], seg_start[u+1]) -- one per requesting peer, in fixed peer order; they are summed in
+ * that order and TF1 Adam is applied to table row (row_ids[u] & mask).  == ctr_segment_sum_rows + ctr_adam_rows bit for
+ * bit, without the intermediate [U, stride] buffer.  Embedding-row shapes only (emb_k = 4/8/16/32, width = emb_k [+1]). */
+int ctr_adam_rows_gathered(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
+                           int local_bits, const float* src, const uint32_t* perm, const uint32_t* seg_start,
+                           int src_stride, int width, float* table, float* m, float* v, int table_stride,
+                           int64_t table_rows, uint8_t* touched, const float* fm_w2, int emb_k, const ctr_adam_hp* hp);
 /* dense TF1 Adam over n floats: g_eff = (g ? g[i] : 0) + l2*theta + l1*sign(theta).
  * skip ([n/skip_group] bytes or NULL): elements whose group flag is 1 are left alone and the flag is
  * cleared (rows already updated by ctr_adam_rows).  This is the exact `tf_dense` mode: TF1 Adam

@@ -190,3 +190,52 @@ def test_scalar_segment_add_matches_add_at(hd):
     got = dst.cpu().numpy()
     assert np.max(np.abs(got - ref)) < 1e-4 * max(1.0, np.abs(ref).max())
     assert np.array_equal(got[rows:], dst0[rows:])
+
+
+@pytest.mark.parametrize("k,has_first,use_fm", [(16, 1, 1), (16, 0, 0), (8, 1, 0), (32, 1, 1), (4, 0, 0)])
+def test_adam_rows_gathered_equals_segment_sum_then_adam(hd, k, has_first, use_fm):
+    """owner side of the sharded step: the fused sum-of-peer-contributions + TF1 Adam kernel equals
+    ctr_segment_sum_rows followed by ctr_adam_rows bit for bit (same addition order), incl. masked keys (local_bits),
+    a padding key and the FM e-term"""
+    from deep_learning_b200._lib import AdamHP
+    g = np.random.RandomState(100 + k + has_first)
+    n, R, local_bits = 6000, 900, 10
+    width = k + has_first
+    wire = (k + 2 + 3) // 4 * 4 if use_fm else (width + 3) // 4 * 4
+    stride = (width + 7) // 8 * 8
+    rows = g.randint(0, R, size=n)
+    owner_hi = g.randint(0, 4, size=n) << local_bits            # high bits = requesting peer's view: masked off
+    keys = np.sort((rows | owner_hi).astype(np.uint32) & np.uint32((1 << local_bits) - 1)).astype(np.uint32)
+    keys[-3:] = 0xFFFFFFFF                                       # padding run: skipped
+    perm = g.permutation(n).astype(np.uint32)
+    src = g.standard_normal((n, wire)).astype(np.float32)
+    t_keys = _u32(keys)
+    uniq = torch.zeros(n + 8, dtype=torch.int32, device="cuda")
+    seg = torch.zeros(n + 8, dtype=torch.int32, device="cuda")
+    uidx = torch.zeros(n + 8, dtype=torch.int32, device="cuda")
+    nun = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ws = torch.zeros(4 * (n // 2048 + 8) + 256, dtype=torch.uint8, device="cuda")
+    hd.call("ctr_unique_segments", _st(), _ptr(t_keys), n, _ptr(uniq), _ptr(seg), _ptr(uidx), _ptr(nun), _ptr(ws), ws.numel())
+    t_src, t_perm = torch.from_numpy(src).cuda(), _u32(perm)
+    w2 = torch.from_numpy(g.standard_normal(k).astype(np.float32)).cuda() if use_fm else None
+    hp = AdamHP(lr_t=1e-2, beta1=0.9, beta2=0.999, eps=1e-8)
+    tabs = [torch.from_numpy(g.standard_normal((1 << local_bits, stride)).astype(np.float32)).cuda() for _ in range(2)]
+    ms = [torch.from_numpy((g.standard_normal((1 << local_bits, stride)) * 0.01).astype(np.float32)).cuda() for _ in range(2)]
+    vs = [torch.from_numpy((g.rand(1 << local_bits, stride) * 0.01).astype(np.float32)).cuda() for _ in range(2)]
+    a = [tabs[0].clone(), ms[0].clone(), vs[0].clone()]
+    b = [tabs[0].clone(), ms[0].clone(), vs[0].clone()]
+    touched = [torch.zeros(1 << local_bits, dtype=torch.uint8, device="cuda") for _ in range(2)]
+    # separate launches
+    gw = k + 2 if use_fm else width
+    own = torch.zeros(n, wire, device="cuda")
+    hd.call("ctr_segment_sum_rows", _st(), _ptr(seg), _ptr(nun), n, _ptr(t_perm), _ptr(t_src), wire, gw, _ptr(own), wire)
+    hd.call("ctr_adam_rows", _st(), _ptr(uniq), _ptr(nun), n, local_bits, _ptr(own), None, wire, width, _ptr(a[0]), _ptr(a[1]),
+            _ptr(a[2]), stride, R, _ptr(touched[0]), None, 0, _ptr(w2), k, hp)
+    # fused
+    hd.call("ctr_adam_rows_gathered", _st(), _ptr(uniq), _ptr(nun), n, local_bits, _ptr(t_src), _ptr(t_perm), _ptr(seg), wire, width,
+            _ptr(b[0]), _ptr(b[1]), _ptr(b[2]), stride, R, _ptr(touched[1]), _ptr(w2), k, hp)
+    torch.cuda.synchronize()
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+    assert torch.equal(touched[0], touched[1]) and int(touched[0].sum()) == len(np.unique(keys[:-3]))
+    assert not torch.equal(a[0], tabs[0])
