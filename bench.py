@@ -269,7 +269,8 @@ def main():
         "dtype": "f32" if a.precision == "fp32" else "tf32", "data": "synthetic",
         "config": {"workload": "DeepFM Criteo-shape: 13 cont + 26 single-valued cate, k=16, MLP 400-400-400, "
                                "batch %d per GPU, table %d rows x (16+1) f32%s, ids %s, Adam lazy (touched rows)"
-                               % (B, R, " row-sharded over %d GPUs (ids/vectors/grads all-to-all, dense allreduce)" % world
+                               % (B, R, " row-sharded over %d GPUs (ids / vectors / gradients / dense-gradient sum exchanged through NVLink peer memory, "
+                                  "no collective in the step)" % world
                                   if world > 1 else "", a.dist),
                    "batch_per_gpu": B, "global_batch": B * world, "parallelism": "dp%d+rowshard%d" % (world, world) if world > 1 else "single",
                    "table_rows": R, "unique_rows_last_step": n_unique, "mlp_precision": a.precision,
