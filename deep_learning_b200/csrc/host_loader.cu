@@ -69,6 +69,7 @@ inline bool parse_float_tok(const char* p, const char* e, float* out) {
     if (n == 0 || n >= sizeof(tmp)) return false;
     memcpy(tmp, p, n);
     tmp[n] = 0;
+    if (memchr(tmp, 'x', n) || memchr(tmp, 'X', n)) return false;     // strtod reads hex floats, Python's float() does not
     char* end = nullptr;
     const double d = strtod(tmp, &end);
     if (end == tmp) return false;

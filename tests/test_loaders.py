@@ -216,3 +216,48 @@ def test_tfrecord_corruption_is_detected(tmp_path, lib_ready):
     mp_bad = _mp(alg_name="deepfm_multi", batch_size=2, epochs=1, cont_field_size=3, vector_feats_size=1, cate_field_size=3)
     with pytest.raises(ValueError):                                  # FixedLenFeature([3]) against 2 stored values
         list(L.pipeline_process(mp_bad, [d + "part-0"], "train", pin=False))
+
+
+def _parse_one(line, n_cont, n_cate):
+    sc = L._LineSchema(n_cont, 0, n_cate)
+    blk, _ = L.LineBlocks([], sc, n_threads=1)._parse((line + "\n").encode())
+    return blk
+
+
+def test_number_spellings_follow_python(lib_ready):
+    """the decoder accepts exactly the spellings the reference's conversion (Python float()/int() on str.split tokens, then
+    a float32 / int32 cast) turns into finite numbers, with the same value bit for bit: exponents, signs, leading zeros,
+    long mantissas (strtod path), denormals, values that overflow float32 to inf"""
+    from hypothesis import given, settings, strategies as st
+
+    spell = st.one_of(
+        st.floats(allow_nan=False, allow_infinity=False, width=32).map(lambda x: repr(float(x))),
+        st.floats(allow_nan=False, allow_infinity=False).map(lambda x: "%.17g" % x),
+        st.floats(min_value=-1e6, max_value=1e6, allow_nan=False).map(lambda x: "%.4f" % x),
+        st.floats(allow_nan=False, allow_infinity=False, width=32).map(lambda x: "%e" % x),
+        st.integers(min_value=-10 ** 12, max_value=10 ** 12).map(str),
+        st.sampled_from(["0", "-0", "+3", "007", "1e5", "1E-3", ".5", "5.", "1e39", "-1e-46", "0.1000000000000000055511151231257827",
+                         "123456789012345678901234567890", "4.9406564584124654e-324"]))
+
+    @settings(max_examples=300, deadline=None)
+    @given(st.lists(spell, min_size=3, max_size=3), st.lists(st.integers(min_value=0, max_value=2 ** 31 - 1), min_size=2, max_size=2))
+    def check(toks, ids):
+        line = "1," + " ".join(toks) + "," + " ".join(str(i) for i in ids)
+        blk = _parse_one(line, 3, 2)
+        with np.errstate(over="ignore"):
+            want = np.asarray([float(t) for t in toks], dtype=np.float64).astype(np.float32)
+        assert np.array_equal(blk["cont"].numpy().reshape(-1).view(np.uint32), want.view(np.uint32)), toks
+        assert blk["cate"].numpy().reshape(-1).tolist() == ids
+    check()
+
+
+@pytest.mark.parametrize("tok", ["", " ", "1e", "--1", "1.2.3", "0x10", "1,5", "abc", "1 2"])
+def test_tokens_python_rejects_are_rejected(lib_ready, tok):
+    try:
+        float(tok)
+        ok_py = True
+    except ValueError:
+        ok_py = False
+    assert not ok_py or tok in ("1 2",)
+    with pytest.raises(ValueError):
+        _parse_one("1,0.5 %s 0.25,3 4" % tok, 3, 2)
