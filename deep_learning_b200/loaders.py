@@ -15,6 +15,8 @@ from __future__ import annotations
 import ctypes as C
 import os
 import pickle
+import queue
+import threading
 from typing import Dict, Iterable, Iterator, List, Optional, Sequence
 
 import numpy as np
@@ -23,6 +25,51 @@ import torch
 from . import _lib
 
 CHUNK_BYTES = 32 << 20
+
+
+class Prefetch:
+    """Re-iterable wrapper: a background thread decodes up to `depth` batches ahead (tf.data's prefetch; the native decoders
+    run without the GIL, so decoding overlaps the training loop's Python).  Exceptions of the producer surface in the
+    consumer; abandoning the iterator stops the producer."""
+
+    def __init__(self, source: Iterable, depth: int = 2):
+        self.source, self.depth = source, max(1, int(depth))
+
+    def __iter__(self):
+        q: "queue.Queue" = queue.Queue(self.depth)
+        stop = threading.Event()
+        END, ERR = object(), object()
+
+        def put(item) -> bool:
+            while not stop.is_set():
+                try:
+                    q.put(item, timeout=0.1)
+                    return True
+                except queue.Full:
+                    continue
+            return False
+
+        def run():
+            try:
+                for item in self.source:
+                    if not put(item):
+                        return
+                put(END)
+            except BaseException as e:      # noqa: BLE001 -- handed to the consumer
+                put((ERR, e))
+
+        th = threading.Thread(target=run, daemon=True, name="ctr-loader-prefetch")
+        th.start()
+        try:
+            while True:
+                item = q.get()
+                if item is END:
+                    return
+                if isinstance(item, tuple) and len(item) == 2 and item[0] is ERR:
+                    raise item[1]
+                yield item
+        finally:
+            stop.set()
 
 
 def _host(shape, dtype, pin: bool) -> torch.Tensor:
@@ -216,9 +263,11 @@ def load_test(mp, file_dir_list: Sequence[str], pin: bool = True) -> List[Dict]:
     return out
 
 
-def textline_process(mp, filenames: Sequence[str], pin: bool = True) -> TextLineBatches:
-    """utils/data_loader_load.py:246-252: batch(drop_remainder=True).repeat(epochs)"""
-    return TextLineBatches(filenames, schema_for(mp, "textline"), mp.batch_size, mp.epochs, drop_remainder=True, pin=pin)
+def textline_process(mp, filenames: Sequence[str], pin: bool = True, prefetch: int = 2):
+    """utils/data_loader_load.py:246-252: batch(drop_remainder=True).repeat(epochs); `prefetch` batches are decoded ahead
+    on a background thread (0: decode in the consumer's thread)"""
+    it = TextLineBatches(filenames, schema_for(mp, "textline"), mp.batch_size, mp.epochs, drop_remainder=True, pin=pin)
+    return Prefetch(it, prefetch) if prefetch else it
 
 
 def dnn_multi_process(filenames, batch_size: int, epochs: int, mp=None, pin: bool = True) -> TextLineBatches:
@@ -307,11 +356,12 @@ class TFRecordBatches:
                 yield b
 
 
-def pipeline_process(mp, file_dir_list: Sequence[str], action_type: str, **kw) -> TFRecordBatches:
-    """utils/data_loader.py:27-40"""
-    return TFRecordBatches(mp, file_dir_list, action_type, **kw)
+def pipeline_process(mp, file_dir_list: Sequence[str], action_type: str, prefetch: int = 2, **kw):
+    """utils/data_loader.py:27-40; `prefetch` batches are decoded ahead on a background thread (0: none)"""
+    it = TFRecordBatches(mp, file_dir_list, action_type, **kw)
+    return Prefetch(it, prefetch) if prefetch else it
 
 
-def load_tfrecord_input_file(mp, input_path: str, action_type: str, **kw) -> TFRecordBatches:
+def load_tfrecord_input_file(mp, input_path: str, action_type: str, **kw):
     """utils/data_loader.py:43-46 (`load_input_file` of that module)"""
     return pipeline_process(mp, get_file_list(input_path), action_type, **kw)

@@ -261,3 +261,31 @@ def test_tokens_python_rejects_are_rejected(lib_ready, tok):
     assert not ok_py or tok in ("1 2",)
     with pytest.raises(ValueError):
         _parse_one("1,0.5 %s 0.25,3 4" % tok, 3, 2)
+
+
+def test_background_prefetch_keeps_order_and_surfaces_errors(tmp_path, lib_ready):
+    d = str(tmp_path) + "/"
+    _write_lines(d + "part-a", 300, 4, 3, seed=11)
+    mp = _mp(alg_name="deepfm_textline", batch_size=32, epochs=2, cont_field_size=4, vector_field_size=0, cate_field_size=3)
+    plain = list(L.textline_process(mp, [d + "part-a"], pin=False, prefetch=0))
+    ahead = L.textline_process(mp, [d + "part-a"], pin=False, prefetch=3)
+    for run in range(2):                                   # re-iterable
+        got = list(ahead)
+        assert len(got) == len(plain) == 2 * (300 // 32)
+        for a, b in zip(got, plain):
+            assert torch.equal(a["cate_feats"], b["cate_feats"]) and torch.equal(a["cont_feats"], b["cont_feats"])
+    it = iter(ahead)                                        # abandoning the iterator must not hang the producer
+    next(it)
+    del it
+    with open(d + "part-b", "w") as f:
+        f.write("1,0.5 0.5 0.5 0.5,1 2 3\n" * 40 + "1,0.5 oops 0.5 0.5,1 2 3\n")
+    bad = L.textline_process(mp, [d + "part-b"], pin=False, prefetch=2)
+    with pytest.raises(ValueError, match="malformed"):
+        list(bad)
+    # the threaded decoder and the single-threaded one agree
+    sc = L.schema_for(mp, "textline")
+    buf = open(d + "part-a", "rb").read() * 20
+    a, _ = L.LineBlocks([], sc, n_threads=1)._parse(buf)
+    b, _ = L.LineBlocks([], sc, n_threads=7)._parse(buf)
+    for k in a:
+        assert torch.equal(a[k], b[k]), k
