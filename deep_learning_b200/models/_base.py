@@ -95,7 +95,10 @@ class BaseDeepModel:
         self.model_restore = getattr(args, "model_restore", 0)
         self.data_dict = data_dict
         self.spec = spec_from_hparams(self.ALG, args)
-        self.engine = CtrEngine(self.spec, max_batch or self.batch_size, device=device,
+        eng_cls = CtrEngine
+        if self.spec.split_fm:
+            from ..split_engine import SplitFmEngine as eng_cls      # deepfm_pipeline: two-row lookup per feature (quirk Q2)
+        self.engine = eng_cls(self.spec, max_batch or self.batch_size, device=device,
                                 learning_rate=self.learning_rate, decay_steps=self.decay_steps,
                                 decay_rate=self.decay_rate, precision=precision, adam_mode=adam_mode)
         self.engine.set_weights(weights if weights is not None else init_weights(self.spec, self.random_seed))

@@ -42,6 +42,7 @@ class ModelSpec:
     frozen_name: Optional[str] = None     # reference constant appended to the table as never-updated rows ('tags_emb')
     frozen_rows: int = 0
     frozen_fields: Tuple[int, ...] = ()   # multi-valued fields that look up the frozen rows (feat_name == 'tag')
+    split_fm: bool = False      # quirk Q2 (models/deepfm_pipeline.py:89,120): the FM part reads row id + C, the deep part row id
 
     @property
     def Fm(self) -> int:
@@ -213,6 +214,15 @@ def spec_from_hparams(alg: str, hp) -> ModelSpec:
                          table_rows=int(hp.cate_feats_size), emb_name="feats_emb", first_name=None, zero_row0=True,
                          multi_ranges=_ranges(hp) if alg == "dnn_multi_cate" else [], head="dnn", l2_reg=l2,
                          reg={"deep_res": "l2"}, id_dtype="int64")
+    if alg == "deepfm_pipeline":
+        # models/deepfm_pipeline.py:76-169: table rows [C continuous | cate_feats_size categorical], row 0 zeroed, FM ids
+        # shifted by C while the deep part uses the raw ids (quirk Q2); head order [cont | cate | second | deep]
+        C, Fc = int(hp.cont_field_size), int(hp.cate_field_size)
+        return ModelSpec(alg, C=C, V=int(hp.vector_feats_size), Fc=Fc, k=k, hidden=H, table_rows=C + int(hp.cate_feats_size),
+                         emb_name="feats_emb", first_name="fm_first_order_emb", use_fm=True, fm_cont=True, zero_row0=True,
+                         cont_base=0, head="deepfm", head_w_name="deep_fm_weight", head_b_name="deep_fm_bias",
+                         first_order_ref="cont_single_multi", l2_reg=l2, reg={"deep_fm_weight": "l2"}, id_dtype="int64",
+                         split_fm=True)
     if alg == "dnn_multi_textline":
         # models/dnn_multi_textline.py:16-48,69-161: its own attribute spellings (cat_field_size, cat_index_size) are
         # accepted next to the canonical ones; row-0-zero `weight_mat`, frozen word2vec constant for the 'tag' field,

@@ -407,6 +407,33 @@ def _dnn_variant_loss(fwd):
     return loss_fn
 
 
+def deepfm_pipeline_forward(p, batch, hp: HParams):
+    """models/deepfm_pipeline.py:76-169.  Table rows: [C continuous-field rows | cate_feats_size categorical rows], row 0
+    zeroed (:83-86) -- so continuous field 0 has no weight at all.  Quirk Q2: the FM part looks categorical ids up at
+    id + C (:89), the deep part at the RAW id (:120): one feature reads two different rows, and raw ids below C alias the
+    continuous-field rows."""
+    C, Fc, k = hp.cont_field_size, hp.cate_field_size, hp.embedding_size
+    cate, cont, vec = batch['cate_feats'].long()[:, :Fc], batch['cont_feats'], batch['vector_feats']
+    B = cate.shape[0]
+    feats_emb = zero_row0(p['feats_emb'])                                      # :83-84
+    first_tab = zero_row0(p['fm_first_order_emb'])                             # :85-86
+    cont_index = torch.arange(C).unsqueeze(0).expand(B, C)                     # :58-61
+    idx = torch.cat([cont_index, cate + C], dim=1)                             # :89-90
+    val = torch.cat([cont, torch.ones(B, Fc, dtype=cont.dtype)], dim=1)        # :91
+    F = C + Fc
+    first_order = embedding_lookup(first_tab, idx).reshape(B, F) * val         # :95-97
+    e = embedding_lookup(feats_emb, idx) * val.reshape(B, F, 1)                # :102-104
+    sum_e = e.sum(dim=1)
+    second_order = 0.5 * (sum_e * sum_e - (e * e).sum(dim=1))                  # :105-109
+    fm_res = torch.cat([first_order, second_order], dim=1)                     # :114
+    cat_emb = embedding_lookup(feats_emb, cate).reshape(B, Fc * k)             # :120-121 (raw ids)
+    dense_vector = torch.cat([cont, vec, cat_emb], dim=1)                      # :123-124
+    deep = mlp_tower(dense_vector, p, len(hp.hidden_units))                    # :149-154
+    feats_input = torch.cat([fm_res, deep], dim=1)                             # :158
+    out = feats_input @ p['deep_fm_weight'] + p['deep_fm_bias']                # :172
+    return out, torch.sigmoid(out)
+
+
 def wdl_textline_forward(p, batch, hp: HParams, with_gathered: bool = False):
     """models/wdl_textline.py:43-50 (row-0-zero embedding table), :133-235 (deep part), :237-276 (wide & deep).
     Same index construction as models/wdl.py (quirk Q4: deep weights alias wide ids W..W+H-1)."""
@@ -481,14 +508,16 @@ FORWARD = {'deepfm': deepfm_forward, 'deepfm_multi': deepfm_multi_forward, 'wdl'
            'dnn': dnn_forward, 'dnn_multi': dnn_multi_forward,
            'deepfm_cate': deepfm_cate_forward, 'deepfm_multi_cate': deepfm_multi_cate_forward,
            'dnn_pipeline': dnn_pipeline_forward, 'dnn_cate': dnn_pipeline_forward, 'dnn_multi_cate': dnn_multi_cate_forward,
-           'wdl_textline': wdl_textline_forward, 'dnn_multi_textline': dnn_multi_textline_forward}
+           'wdl_textline': wdl_textline_forward, 'dnn_multi_textline': dnn_multi_textline_forward,
+           'deepfm_pipeline': deepfm_pipeline_forward}
 LOSS = {'deepfm': deepfm_loss, 'deepfm_multi': deepfm_multi_loss, 'wdl': wdl_loss,
         'dnn': dnn_loss, 'dnn_multi': dnn_multi_loss,
         'deepfm_cate': _deepfm_variant_loss(deepfm_cate_forward),
         'deepfm_multi_cate': _deepfm_variant_loss(deepfm_multi_cate_forward),
         'dnn_pipeline': _dnn_variant_loss(dnn_pipeline_forward), 'dnn_cate': _dnn_variant_loss(dnn_pipeline_forward),
         'dnn_multi_cate': _dnn_variant_loss(dnn_multi_cate_forward),
-        'wdl_textline': wdl_textline_loss, 'dnn_multi_textline': dnn_multi_textline_loss}
+        'wdl_textline': wdl_textline_loss, 'dnn_multi_textline': dnn_multi_textline_loss,
+        'deepfm_pipeline': _deepfm_variant_loss(deepfm_pipeline_forward)}     # models/deepfm_pipeline.py:177-183
 # variants without a continuous block read cont_field_size as 0 (their model files never define it)
 NO_CONT = ('deepfm_cate', 'deepfm_multi_cate', 'dnn_cate', 'dnn_multi_cate')
 
@@ -500,7 +529,7 @@ NO_CONT = ('deepfm_cate', 'deepfm_multi_cate', 'dnn_cate', 'dnn_multi_cate')
 # --------------------------------------------------------------------------------------
 def deep_input_size(alg: str, hp: HParams) -> int:
     k = hp.embedding_size
-    if alg == 'deepfm':
+    if alg in ('deepfm', 'deepfm_pipeline'):
         return hp.cont_field_size + hp.vector_feats_size + hp.cate_field_size * k
     if alg in ('deepfm_multi', 'dnn_multi'):
         return hp.cont_field_size + hp.vector_feats_size + (hp.cate_field_size + hp.multi_field_size) * k
@@ -526,6 +555,9 @@ def param_shapes(alg: str, hp: HParams) -> Dict[str, Tuple[int, ...]]:
     if alg == 'deepfm':                                   # models/deepfm.py:57-60
         R = hp.cont_field_size + hp.cate_feats_size
         s['feats_emb'] = (R, k); s['feats'] = (R, 1)
+    elif alg == 'deepfm_pipeline':                        # models/deepfm_pipeline.py:77-81
+        R = hp.cont_field_size + hp.cate_feats_size
+        s['feats_emb'] = (R, k); s['fm_first_order_emb'] = (R, 1)
     elif alg == 'deepfm_multi':                           # models/deepfm_multi.py:124-128
         R = hp.cate_feats_size + hp.cont_field_size
         s['feats_emb'] = (R, k); s['fm_first_order_emb'] = (R, 1)
@@ -543,7 +575,7 @@ def param_shapes(alg: str, hp: HParams) -> Dict[str, Tuple[int, ...]]:
     prev = d0
     for i, h in enumerate(H):
         s['deep_%d' % i] = (prev, h); s['deep_bias_%d' % i] = (1, h); prev = h
-    if alg in ('deepfm', 'deepfm_multi'):
+    if alg in ('deepfm', 'deepfm_multi', 'deepfm_pipeline'):
         F = hp.cont_field_size + hp.cate_field_size + (hp.multi_field_size if alg == 'deepfm_multi' else 0)
         s['deep_fm_weight'] = (F + k + H[-1], 1); s['deep_fm_bias'] = (1,)
     if alg in ('deepfm_cate', 'deepfm_multi_cate'):
@@ -670,6 +702,11 @@ def touched_rows(alg: str, batch, hp: HParams) -> Dict[str, Tensor]:
         R = shapes['feats_emb'][0]
         mk = mask(R, cate, drop0=True)
         mk[hp.cate_feats_size:hp.cate_feats_size + hp.cont_field_size] = True
+        out['feats_emb'] = mk; out['fm_first_order_emb'] = mk
+    elif alg == 'deepfm_pipeline':
+        C = hp.cont_field_size
+        mk = mask(shapes['feats_emb'][0], torch.cat([cate.reshape(-1), cate.reshape(-1) + C]), drop0=True)
+        mk[1:C] = True                                # continuous-field rows (row 0 is cut out of the graph)
         out['feats_emb'] = mk; out['fm_first_order_emb'] = mk
     elif alg == 'wdl':
         out['weight_mat'] = mask(shapes['weight_mat'][0], cate)

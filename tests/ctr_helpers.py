@@ -64,7 +64,7 @@ def make_batch(alg, hp, seed, B=None, dist="zipf", id_dtype=None):
     if alg == "dnn_multi_textline":
         return make_textline_batch(hp, seed, B)
     multi = alg in ("deepfm_multi", "dnn_multi", "deepfm_multi_cate", "dnn_multi_cate")
-    reserve = multi or alg in ("deepfm_cate", "dnn_cate", "dnn_pipeline", "wdl_textline")   # row-0-zero models: id 0 is padding
+    reserve = multi or alg in ("deepfm_cate", "dnn_cate", "dnn_pipeline", "wdl_textline", "deepfm_pipeline")   # row-0-zero models: id 0 is padding
     n_single_rows = (hp.cate_index_size if alg == "wdl_textline" else hp.cate_feats_size) - (1 if reserve else 0)
     if multi:
         Fm = hp.multi_field_size

@@ -27,9 +27,9 @@ from deep_learning_b200 import data as D   # noqa: E402
 
 BASE = ("deepfm", "deepfm_multi", "wdl", "dnn", "dnn_multi")
 VARIANTS = ("deepfm_cate", "deepfm_multi_cate", "dnn_pipeline", "dnn_cate", "dnn_multi_cate")
-TEXTLINE = ("wdl_textline", "dnn_multi_textline")
+TEXTLINE = ("wdl_textline", "dnn_multi_textline", "deepfm_pipeline")
 MULTI = ("deepfm_multi", "dnn_multi", "deepfm_multi_cate", "dnn_multi_cate")
-ROW0 = MULTI + ("deepfm_cate", "dnn_cate", "dnn_pipeline", "wdl_textline")          # row-0-zero tables: id 0 is padding
+ROW0 = MULTI + ("deepfm_cate", "dnn_cate", "dnn_pipeline", "wdl_textline", "deepfm_pipeline")          # row-0-zero tables: id 0 is padding
 
 
 def tiny_hp(alg):
@@ -39,7 +39,7 @@ def tiny_hp(alg):
         kw.update(cate_feats_size=81, multi_feats_size=8, multi_field_size=2, multi_feats_range=[[0, 3, "m0"], [3, 8, "m1"]])
     if alg in O.NO_CONT:
         kw.update(cont_field_size=0)
-    if alg in VARIANTS:
+    if alg in VARIANTS or alg == "deepfm_pipeline":
         kw.update(vector_feats_size=2)
     if alg in ("wdl", "wdl_textline"):
         kw.update(cate_index_size=60, wide_field_size=5)
@@ -50,6 +50,15 @@ def tiny_hp(alg):
 
 
 def tiny_batch(alg, hp, seed):
+    if alg == "deepfm_pipeline":
+        b = _tiny_batch("deepfm_pipeline", hp, seed)
+        b["cate_feats"][0, 0] = 0          # padding ids: the deep part reads the zero row, the FM part row C (quirk Q2)
+        b["cate_feats"][3, 2] = 0
+        return b
+    return _tiny_batch(alg, hp, seed)
+
+
+def _tiny_batch(alg, hp, seed):
     if alg == "dnn_multi_textline":
         import ctr_helpers as H
         return H.make_textline_batch(hp, seed)

@@ -270,3 +270,63 @@ def test_textline_batch_keys_are_mapped():
     assert spec.frozen_rows == 300 and spec.frozen_fields == (1,) and spec.weighted_pool
     off = spec.frozen_slot_offset()
     assert off[:Fc + 5].sum() == 0 and (off[Fc + 5:] == spec.table_rows).all()
+
+
+def test_deepfm_pipeline_reads_two_rows_per_feature():
+    """quirk Q2 (models/deepfm_pipeline.py:89,120) as a known answer: one sample, one categorical field with id 5, C = 2.
+    FM row = 5 + 2 = 7, deep row = 5; continuous field 0 sits on the zeroed row 0 and contributes nothing."""
+    hp = O.HParams(hidden_units=[2], batch_size=1, embedding_size=2, cont_field_size=2, cate_field_size=1, cate_feats_size=10,
+                   vector_feats_size=0, l2_reg=0.0)
+    p = O.init_params("deepfm_pipeline", hp)
+    p["deep_0"] = torch.zeros(4, 2, dtype=torch.float64); p["deep_0"][2, 0] = 1.0; p["deep_0"][3, 1] = 1.0   # passes the embedding
+    p["deep_bias_0"] = torch.full((1, 2), 5.0, dtype=torch.float64)
+    w = torch.zeros(3 + 2 + 2, 1, dtype=torch.float64)
+    p["deep_fm_bias"] = torch.zeros(1, dtype=torch.float64)
+    b = {"cate_feats": torch.tensor([[5]]), "cont_feats": torch.tensor([[3.0, 0.5]], dtype=torch.float64),
+         "vector_feats": torch.zeros(1, 0, dtype=torch.float64), "label": torch.ones(1, 1, dtype=torch.float64)}
+    E, Wf = p["feats_emb"], p["fm_first_order_emb"]
+    # first order: [cont0 * w[0] (zeroed) | cont1 * w[1] | w[7]]
+    for j, want in enumerate([0.0, 0.5 * float(Wf[1]), float(Wf[7])]):
+        w.zero_(); w[j] = 1.0; p["deep_fm_weight"] = w.clone()
+        assert abs(float(O.deepfm_pipeline_forward(p, b, hp)[0]) - want) < 1e-14, j
+    # second order over e = [0, 0.5 * E[1], E[7]]
+    e = torch.stack([torch.zeros(2, dtype=torch.float64), 0.5 * E[1], E[7]])
+    second = 0.5 * (e.sum(0) ** 2 - (e ** 2).sum(0))
+    w.zero_(); w[3] = 1.0; p["deep_fm_weight"] = w.clone()
+    assert abs(float(O.deepfm_pipeline_forward(p, b, hp)[0]) - float(second[0])) < 1e-14
+    # deep part sees the RAW id's row
+    w.zero_(); w[5] = 1.0; p["deep_fm_weight"] = w.clone()
+    assert abs(float(O.deepfm_pipeline_forward(p, b, hp)[0]) - (float(E[5, 0]) + 5.0)) < 1e-14
+    # a raw id below C aliases a continuous-field row; padding id 0 reads zeros in the deep part but row C in the FM part
+    b0 = dict(b, cate_feats=torch.tensor([[0]]))
+    assert abs(float(O.deepfm_pipeline_forward(p, b0, hp)[0]) - 5.0) < 1e-14
+    w.zero_(); w[2] = 1.0; p["deep_fm_weight"] = w.clone()
+    assert abs(float(O.deepfm_pipeline_forward(p, b0, hp)[0]) - float(Wf[2])) < 1e-14
+
+
+def test_deepfm_pipeline_autograd_matches_finite_differences():
+    hp = H.hp_c1(vector_feats_size=3, hidden_units=[8, 4], l2_reg=1e-2)
+    p = O.init_params("deepfm_pipeline", hp)
+    bt = H.make_batch("deepfm_pipeline", hp, seed=1, B=16)
+    bt["cate_feats"][0, 0] = 0
+    b = H.oracle_batch(bt, torch.float64)
+    loss, _, _, grads = O.loss_and_grads("deepfm_pipeline", p, b, hp)
+    assert not grads["feats_emb"][0].any() and not grads["fm_first_order_emb"][0].any()      # row 0 is cut out of the graph
+    rng = np.random.RandomState(0)
+    for name in p:
+        gflat = grads[name].reshape(-1)
+        nz = torch.nonzero(gflat).reshape(-1)
+        idx = int(nz[rng.randint(len(nz))])
+        eps = 1e-6
+        q = {k: v.clone() for k, v in p.items()}
+        q[name].reshape(-1)[idx] += eps
+        lp = float(O.LOSS["deepfm_pipeline"](q, b, hp)[0])
+        q[name].reshape(-1)[idx] -= 2 * eps
+        lm = float(O.LOSS["deepfm_pipeline"](q, b, hp)[0])
+        fd = (lp - lm) / (2 * eps)
+        assert abs(fd - float(gflat[idx])) < 1e-6 * max(1.0, abs(fd)) + 1e-9, (name, fd, float(gflat[idx]))
+    # the lazy-Adam row mask covers the support of the table gradient (a dead ReLU can zero a structurally touched row)
+    tr = O.touched_rows("deepfm_pipeline", b, hp)
+    support = (grads["feats_emb"].abs().sum(1) + grads["fm_first_order_emb"].abs().sum(1)) > 0
+    assert not (support & ~tr["feats_emb"]).any() and not tr["feats_emb"][0]
+    assert tr["feats_emb"][hp.cont_field_size]          # padding id 0 -> FM row C is touched
