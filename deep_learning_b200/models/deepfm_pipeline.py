@@ -4,7 +4,6 @@
     predict(predict_data, model_pb, args=mp)                                 # local_run_test.py:82
 
 Quirk Q2 is reproduced: the FM part reads row id + cont_field_size, the deep part the raw id (split_engine.py).
-UNVERIFIED ON GPU in round 1 (see split_engine.py): needs CTR_UNVERIFIED=1.
 """
 import sys
 

@@ -13,9 +13,9 @@ entry points:
             contributions of a row hit through both lists BEFORE TF1 Adam -- one Adam step per row, as TensorFlow applies
             the summed IndexedSlices of one variable.
 
-STATUS: composed and reviewed, CPU restatement + golden vectors in place (tests/golden/deepfm_pipeline_tiny.npz),
-but NOT yet run on a GPU (the round's GPU budget was spent): constructing it needs CTR_UNVERIFIED=1, and its GPU parity
-test (tests/test_gpu_parity.py::test_deepfm_pipeline_split_fm) is skipped without it.
+Parity: tests/test_gpu_parity.py::test_deepfm_pipeline_split_fm (K1 fast path and general kernel, TF-exact and lazy Adam,
+padding ids and ids that alias the continuous-field rows), 1e-5 against the CPU restatement; golden vectors in
+tests/golden/deepfm_pipeline_tiny.npz.
 """
 from __future__ import annotations
 
@@ -34,9 +34,6 @@ class SplitFmEngine(CtrEngine):
     def __init__(self, spec: ModelSpec, max_batch: int, **kw):
         if not spec.split_fm:
             raise ValueError("SplitFmEngine is for split_fm specs (deepfm_pipeline)")
-        if os.environ.get("CTR_UNVERIFIED") != "1":
-            raise NotImplementedError("deepfm_pipeline: the split-FM step has not been verified on a GPU yet; set CTR_UNVERIFIED=1 "
-                                      "to run it (tests/test_gpu_parity.py::test_deepfm_pipeline_split_fm checks it)")
         if kw.get("world", 1) != 1:
             raise NotImplementedError("deepfm_pipeline: single GPU only")
         super().__init__(spec, max_batch, **kw)

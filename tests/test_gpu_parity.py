@@ -426,9 +426,6 @@ def test_tfrecords_through_the_native_loader_feed_generation_b(tmp_path, capsys)
     assert ma.engine.global_step == 3
 
 
-@pytest.mark.skipif(__import__("os").environ.get("CTR_UNVERIFIED") != "1",
-                    reason="deepfm_pipeline's composition (split_engine.py) was written after the round's GPU budget was spent: "
-                           "run with CTR_UNVERIFIED=1 first thing next round")
 @pytest.mark.parametrize("V", [0, 3])
 def test_deepfm_pipeline_split_fm(V):
     """models/deepfm_pipeline.py (quirk Q2: FM row id + C, deep row id; row 0 zeroed) through SplitFmEngine, composed from
