@@ -20,11 +20,9 @@ tests/golden/deepfm_pipeline_tiny.npz.
 from __future__ import annotations
 
 import ctypes as C
-import os
 
 import torch
 
-from . import _lib
 from ._lib import EmbedCfg, ptr
 from .engine import ADAM_BETA1, ADAM_BETA2, CtrEngine, _ru
 from .spec import ModelSpec
