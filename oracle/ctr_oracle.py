@@ -3,13 +3,17 @@
 Only `tests/`, `__graft_entry__.smoke()` and `bench.py`'s `cpu_baseline` / `--impl reference`
 legs may import this module; the product (`deep_learning_b200/`) never does.
 
-PARITY UNPINNED: the reference (RodJohn/deep_learning) ships no tests, golden vectors or
-fixtures for this path, and its arithmetic lives in TensorFlow 1.x (un-vendored, unpinned,
-1.13-1.15 by the .pyc tags) which cannot be installed here (no wheel for py3.12, no network).
-This file therefore RESTATES the TF graph of each model file op by op on PyTorch-CPU tensors
-(`tf.nn.embedding_lookup` -> index, `tf.matmul` -> `@`, ...), takes gradients with autograd on
-that same graph (what `Optimizer.minimize` does), and hand-writes TF1's Adam.  The one piece of
-the path whose real implementation IS present (scikit-learn's `roc_auc_score`) pins `roc_auc`.
+PARITY: the reference (RodJohn/deep_learning) ships no tests, golden vectors or fixtures for this
+path, and its arithmetic lives in TensorFlow 1.x (un-vendored, unpinned, 1.13-1.15 by the .pyc
+tags) which cannot be installed here (no wheel for py3.12, no network): against TensorFlow's own
+kernels this file is PARITY UNPINNED.  What it IS pinned to: all 13 files of the reference's
+`models/`, imported unmodified and run through their own `fit` under a TF1 graph-mode stand-in
+(tests/golden/tf1_shim.py, generator tests/golden/make_ref_golden.py); this file reproduces the
+recorded losses, evaluation outputs and final variables (tests/golden/ref_*.npz) to 1e-12
+(tests/test_ref_golden.py).  The file RESTATES the TF graph of each model file op by op on
+PyTorch-CPU tensors (`tf.nn.embedding_lookup` -> index, `tf.matmul` -> `@`, ...), takes gradients
+with autograd on that same graph (what `Optimizer.minimize` does), and hand-writes TF1's Adam.
+scikit-learn's `roc_auc_score` (its real implementation is present) pins `roc_auc`.
 
 Every function cites the reference lines it follows (paths relative to /root/reference).
 All functions take a `dtype`: float64 is the order-free truth used by the parity tests,
