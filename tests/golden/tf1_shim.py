@@ -620,6 +620,12 @@ def count_nonzero(input_tensor, axis=None, keepdims=None, dtype=int64, name=None
 
 
 def reshape(tensor, shape, name=None):
+    if _any_eager(tensor, shape):
+        a, shp = _eager_value(tensor), [int(d) for d in _eager_value(shape).reshape(-1)]
+        if int(np.prod(shp)) != a.size:
+            raise ValueError("InvalidArgumentError: Input to reshape is a tensor with %d values, but the requested shape "
+                             "has %d" % (a.size, int(np.prod(shp))))
+        return _Eager(a.reshape(shp))
     x = convert_to_tensor(tensor)
 
     def run(ctx, a):
@@ -899,6 +905,199 @@ class Session:
         return out[0] if single else out
 
 
+# ------------------------------------------------------------------------------------------------ tf.data + string ops
+# `Dataset.map` functions of the reference (utils/data_loader_load.py:187-240, utils/data_loader_textline.py:4-36) run
+# once per ELEMENT here, on eager values: numpy arrays (dtype=object for strings) behind a thin wrapper.
+class _Eager:
+    def __init__(self, a):
+        self.a = a if isinstance(a, np.ndarray) else np.asarray(a)
+
+    def __getitem__(self, idx):
+        return _Eager(self.a[idx])
+
+    @property
+    def shape(self):
+        return TensorShape(list(self.a.shape))
+
+
+def _eager_value(x):
+    if isinstance(x, _Eager):
+        return x.a
+    if isinstance(x, (list, tuple)):
+        return np.array([_eager_value(e) for e in x], dtype=object if any(
+            isinstance(e, _Eager) and e.a.dtype == object for e in x) else None)
+    return np.asarray(x)
+
+
+def _any_eager(*xs):
+    for x in xs:
+        if isinstance(x, _Eager) or (isinstance(x, (list, tuple)) and any(isinstance(e, _Eager) for e in x)):
+            return True
+    return False
+
+
+class _SparseStrings:
+    def __init__(self, indices, values, dense_shape):
+        self.indices, self.values, self.dense_shape = _Eager(indices), _Eager(values), _Eager(dense_shape)
+
+
+def string_split(source, delimiter=" ", skip_empty=True):
+    """tf.string_split: the tokens of every entry of a 1-D string tensor, row-major; empty tokens are skipped by default;
+    dense_shape = [entries, longest row]"""
+    src = _eager_value(source).reshape(-1)
+    idx, vals, longest = [], [], 0
+    for r, entry in enumerate(src):
+        toks = str(entry).split(delimiter) if delimiter != "" else list(str(entry))
+        if skip_empty:
+            toks = [t for t in toks if t != ""]
+        for c, t in enumerate(toks):
+            idx.append((r, c))
+            vals.append(t)
+        longest = max(longest, len(toks))
+    v = np.empty(len(vals), dtype=object)
+    v[:] = vals
+    return _SparseStrings(np.asarray(idx, dtype=np.int64).reshape(-1, 2), v, np.asarray([len(src), longest], dtype=np.int64))
+
+
+def string_to_number(string_tensor, out_type=float32, name=None):
+    """tf.string_to_number: every entry must be a valid number of the output type (InvalidArgumentError otherwise);
+    float32 results are the float32 nearest to the decimal (Python float() then a float32 cast: the same value except
+    for decimals within 2^-53 of a float32 rounding boundary)"""
+    a = _eager_value(string_tensor)
+    dt = _as_dtype(out_type)
+    flat = a.reshape(-1)
+    if dt.is_float:
+        out = np.empty(flat.shape, dtype=np.float32)
+        for i, t in enumerate(flat):
+            t = str(t)
+            if t != t.strip() or "_" in t or "x" in t.lower() and "inf" not in t.lower():
+                raise ValueError("InvalidArgumentError: StringToNumberOp could not correctly convert string: " + t)
+            try:
+                out[i] = np.float32(float(t))
+            except ValueError:
+                raise ValueError("InvalidArgumentError: StringToNumberOp could not correctly convert string: " + t) from None
+    else:
+        out = np.empty(flat.shape, dtype=np.int32 if out_type is int32 else np.int64)
+        for i, t in enumerate(flat):
+            t = str(t)
+            ok = t.lstrip("+-").isdigit() and t == t.strip() and len(t) - len(t.lstrip("+-")) <= 1 and t.isascii()
+            if not ok or not (np.iinfo(out.dtype).min <= int(t) <= np.iinfo(out.dtype).max):
+                raise ValueError("InvalidArgumentError: StringToNumberOp could not correctly convert string: " + t)
+            out[i] = int(t)
+    return _Eager(out.reshape(a.shape))
+
+
+def split(value, num_or_size_splits, axis=0, name=None):
+    a = _eager_value(value)
+    if not isinstance(num_or_size_splits, int) or a.shape[axis] % num_or_size_splits:
+        raise ValueError("InvalidArgumentError: dimension %d is not divisible by %r" % (a.shape[axis], num_or_size_splits))
+    return [_Eager(p) for p in np.split(a, num_or_size_splits, axis=axis)]
+
+
+def squeeze(input, axis=None, name=None):
+    a = _eager_value(input)
+    ax = _axes(axis)
+    if ax is not None and any(a.shape[i] != 1 for i in ax):
+        raise ValueError("InvalidArgumentError: can not squeeze a dimension that is not 1")
+    return _Eager(np.squeeze(a, axis=ax))
+
+
+class _Dataset:
+    def __init__(self, make):
+        self._make = make                     # () -> iterator over elements
+
+    def map(self, fn, num_parallel_calls=None):
+        def to_np(v):
+            return v.a if isinstance(v, _Eager) else np.asarray(v, dtype=np.int32 if isinstance(v, int) else None)
+
+        def gen():
+            for e in self._make():
+                out = fn(_Eager(np.array(e, dtype=object)))
+                yield {k: to_np(v) for k, v in out.items()}
+        return _Dataset(gen)
+
+    def batch(self, batch_size, drop_remainder=False):
+        def gen():
+            buf = []
+            for e in self._make():
+                buf.append(e)
+                if len(buf) == batch_size:
+                    yield self._stack(buf)
+                    buf = []
+            if buf and not drop_remainder:
+                yield self._stack(buf)
+        return _Dataset(gen)
+
+    @staticmethod
+    def _stack(buf):
+        out = {}
+        for k in buf[0]:
+            shapes = {e[k].shape for e in buf}
+            if len(shapes) != 1:
+                raise ValueError("InvalidArgumentError: Cannot batch tensors with different shapes in component %s: %s" % (
+                    k, sorted(shapes)))
+            out[k] = np.stack([e[k] for e in buf])
+        return out
+
+    def repeat(self, count=None):
+        def gen():
+            n = 0
+            while count is None or n < count:
+                yield from self._make()
+                n += 1
+        return _Dataset(gen)
+
+    def prefetch(self, n):
+        return self
+
+    def make_one_shot_iterator(self):
+        return _OneShotIterator(self._make())
+
+
+class _OneShotIterator:
+    def __init__(self, it):
+        self._it = it
+
+    def get_next(self):
+        import itertools
+        try:
+            first = next(self._it)
+        except StopIteration:
+            raise ValueError("the stand-in needs one element to learn the component types") from None
+        spec = {k: (float32 if v.dtype.kind == "f" else int64, [None] + list(v.shape[1:])) for k, v in first.items()}
+        return BatchSource(itertools.chain([first], self._it), spec).tensors
+
+
+def _text_line_dataset(filenames, **kw):
+    """tf.data.TextLineDataset: the lines of the files in order, line terminator removed"""
+    if kw:
+        raise TypeError("TextLineDataset argument(s) %s not handled by the TF1 stand-in" % sorted(kw))
+    names = [filenames] if isinstance(filenames, str) else list(filenames)
+
+    def gen():
+        for fn in names:
+            with open(fn, "r", newline="\n") as f:
+                for line in f:
+                    yield line[:-1] if line.endswith("\n") else line
+    return _Dataset(gen)
+
+
+data = types.SimpleNamespace(TextLineDataset=_text_line_dataset)
+
+
+# ------------------------------------------------------------------------------------------------ file system
+def _fast_gfile(name, mode="r"):
+    return open(name, mode)                      # tf.gfile.FastGFile on a local path: a Python file object
+
+
+def _list_directory(path):
+    import os
+    return os.listdir(path)                      # tf.gfile.ListDirectory: entry names, order unspecified
+
+
+gfile = types.SimpleNamespace(FastGFile=_fast_gfile, ListDirectory=_list_directory)
+
+
 # ------------------------------------------------------------------------------------------------ saved-model stubs
 class _SavedModelBuilder:
     def __init__(self, export_dir):
@@ -922,7 +1121,7 @@ def install():
               "random_normal", "random_uniform", "zeros", "ones", "placeholder", "placeholder_with_default",
               "errors", "add", "subtract", "multiply", "div_no_nan", "square", "identity", "reduce_sum",
               "reduce_mean", "count_nonzero", "reshape", "concat", "tile", "matmul", "sigmoid", "nn", "losses",
-              "contrib", "train", "Session"):
+              "contrib", "train", "Session", "gfile", "data", "string_split", "string_to_number", "split", "squeeze"):
         setattr(tf, k, getattr(me, k))
     tag_constants = _module("tensorflow.python.saved_model.tag_constants", SERVING="serve")
     signature_constants = _module("tensorflow.python.saved_model.signature_constants",

@@ -130,3 +130,41 @@ def test_symbols_the_model_files_do_not_use_are_absent():
         for k in [k for k in sys.modules if k == "tensorflow" or k.startswith("tensorflow.")]:
             if getattr(sys.modules[k], "__file__", None) is None:
                 del sys.modules[k]
+
+
+def test_string_split_skips_empty_tokens_and_reports_the_longest_row():
+    sp = tf.string_split([tf._Eager(np.array("1=0.5 2=0.25  3=1", dtype=object))], " ")
+    assert list(sp.values.a) == ["1=0.5", "2=0.25", "3=1"] and list(sp.dense_shape.a) == [1, 3]
+    kv = tf.string_split(sp.values, "=")
+    assert list(kv.dense_shape.a) == [3, 2]
+    ids, vals = tf.split(tf.reshape(kv.values, shape=kv.dense_shape), num_or_size_splits=2, axis=1)
+    assert tf.squeeze(tf.string_to_number(ids, out_type=tf.int32), axis=1).a.tolist() == [1, 2, 3]
+    assert tf.squeeze(tf.string_to_number(vals, out_type=tf.float32), axis=1).a.tolist() == [0.5, 0.25, 1.0]
+    ragged = tf.string_split(tf._Eager(np.array(["1=2", "3"], dtype=object)), "=")
+    with pytest.raises(ValueError):          # 3 values cannot fill the [2, 2] dense shape: the reference's reshape fails too
+        tf.reshape(ragged.values, shape=ragged.dense_shape)
+
+
+@pytest.mark.parametrize("tok,typ", [("abc", tf.float32), ("1.5", tf.int32), ("", tf.float32), ("99999999999", tf.int32),
+                                     (" 1", tf.int32), ("1_0", tf.float32)])
+def test_string_to_number_rejects_what_is_not_a_number_of_the_type(tok, typ):
+    with pytest.raises(ValueError):
+        tf.string_to_number(tf._Eager(np.array([tok], dtype=object)), out_type=typ)
+
+
+def test_text_line_dataset_batches_across_files_and_repeats(tmp_path):
+    a, b = str(tmp_path / "a"), str(tmp_path / "b")
+    open(a, "w").write("1\n2\n3\n")
+    open(b, "w").write("4\n5")                 # no newline at the end of the last line
+    ds = tf.data.TextLineDataset([a, b]).map(lambda line: {"x": tf.string_to_number([line], out_type=tf.int32)})
+    nxt = ds.batch(2, drop_remainder=True).repeat(2).make_one_shot_iterator().get_next()
+    got = []
+    with tf.Session() as sess:
+        with pytest.raises(tf.errors.OutOfRangeError):
+            while True:
+                got.append(sess.run(nxt["x"]).ravel().tolist())
+    assert got == [[1, 2], [3, 4], [1, 2], [3, 4]]                 # 5 is dropped in both epochs
+    keep = tf.data.TextLineDataset(a).map(lambda line: {"x": tf.string_to_number([line], out_type=tf.int32)}).batch(2)
+    nxt = keep.make_one_shot_iterator().get_next()
+    with tf.Session() as sess:
+        assert [sess.run(nxt["x"]).ravel().tolist() for _ in range(2)] == [[1, 2], [3]]
