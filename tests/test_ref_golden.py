@@ -20,7 +20,7 @@ from oracle import ctr_oracle as O
 from golden import make_golden as G
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-FILES = sorted(glob.glob(os.path.join(HERE, "golden", "ref_*.npz")))
+FILES = sorted(f for f in glob.glob(os.path.join(HERE, "golden", "ref_*.npz")) if not f.endswith("ref_loader.npz"))
 ALGS = [os.path.basename(f)[4:-4] for f in FILES]
 
 TOL = 1e-12          # float64 on both sides, same operation order up to summation order inside torch reductions
