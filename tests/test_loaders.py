@@ -289,3 +289,87 @@ def test_background_prefetch_keeps_order_and_surfaces_errors(tmp_path, lib_ready
     b, _ = L.LineBlocks([], sc, n_threads=7)._parse(buf)
     for k in a:
         assert torch.equal(a[k], b[k]), k
+
+
+def _official_example_class():
+    """tensorflow.Example built from its published schema (tensorflow/core/example/{example,feature}.proto) on the
+    protobuf runtime that IS installed here: an independent implementation of the wire format"""
+    from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+    T = descriptor_pb2.FieldDescriptorProto
+    f = descriptor_pb2.FileDescriptorProto(name="ctr_test_example.proto", package="ctr_test", syntax="proto3")
+
+    def msg(name):
+        m = f.message_type.add()
+        m.name = name
+        return m
+
+    def field(m, name, num, typ, label=T.LABEL_OPTIONAL, type_name=None, oneof=None):
+        x = m.field.add()
+        x.name, x.number, x.type, x.label = name, num, typ, label
+        if type_name:
+            x.type_name = ".ctr_test." + type_name
+        if oneof is not None:
+            x.oneof_index = oneof
+        return x
+
+    field(msg("BytesList"), "value", 1, T.TYPE_BYTES, T.LABEL_REPEATED)
+    field(msg("FloatList"), "value", 1, T.TYPE_FLOAT, T.LABEL_REPEATED)        # proto3: packed by default
+    field(msg("Int64List"), "value", 1, T.TYPE_INT64, T.LABEL_REPEATED)
+    feat = msg("Feature")
+    feat.oneof_decl.add().name = "kind"
+    field(feat, "bytes_list", 1, T.TYPE_MESSAGE, type_name="BytesList", oneof=0)
+    field(feat, "float_list", 2, T.TYPE_MESSAGE, type_name="FloatList", oneof=0)
+    field(feat, "int64_list", 3, T.TYPE_MESSAGE, type_name="Int64List", oneof=0)
+    feats = msg("Features")
+    entry = feats.nested_type.add()
+    entry.name = "FeatureEntry"
+    entry.options.map_entry = True
+    field(entry, "key", 1, T.TYPE_STRING)
+    field(entry, "value", 2, T.TYPE_MESSAGE, type_name="Feature")
+    field(feats, "feature", 1, T.TYPE_MESSAGE, T.LABEL_REPEATED, type_name="Features.FeatureEntry")
+    field(msg("Example"), "features", 1, T.TYPE_MESSAGE, type_name="Features")
+    pool = descriptor_pool.DescriptorPool()
+    pool.Add(f)
+    return message_factory.GetMessageClass(pool.FindMessageTypeByName("ctr_test.Example"))
+
+
+def test_tf_example_wire_format_against_the_protobuf_runtime(tmp_path, lib_ready):
+    """the oracle's hand-written encoder / decoder and the native reader against google.protobuf itself"""
+    Example = _official_example_class()
+    g = np.random.RandomState(9)
+    n, C_, V, Fc = 70, 3, 2, 5
+    rows = [{"label": g.rand(1).round(), "cont_feats": g.rand(C_), "vector_feats": g.randn(V),
+             "cate_feats": g.randint(-5, 2 ** 45, size=Fc)} for _ in range(n)]
+    payloads = []
+    for r in rows:
+        ex = Example()
+        for k, v in r.items():
+            if k == "cate_feats":
+                ex.features.feature[k].int64_list.value.extend(int(x) for x in v)
+            else:
+                ex.features.feature[k].float_list.value.extend(float(x) for x in v)
+        payloads.append(ex.SerializeToString())
+        # official bytes -> oracle decoder
+        back = LO.decode_example(payloads[-1])
+        assert np.array_equal(back["cate_feats"], r["cate_feats"])
+        for k in ("label", "cont_feats", "vector_feats"):
+            assert np.array_equal(back[k], np.asarray(r[k], dtype=np.float32)), k
+        # oracle encoder (both list encodings) -> official parser
+        for packed in (True, False):
+            ex2 = Example.FromString(LO.encode_example(r, packed=packed))
+            assert list(ex2.features.feature["cate_feats"].int64_list.value) == [int(x) for x in r["cate_feats"]]
+            assert np.array_equal(np.asarray(ex2.features.feature["cont_feats"].float_list.value, dtype=np.float32),
+                                  np.asarray(r["cont_feats"], dtype=np.float32))
+            assert set(ex2.features.feature) == set(r)
+    # official bytes -> record framing -> native reader
+    d = str(tmp_path) + "/"
+    LO.write_tfrecord(d + "part-r-00000", payloads)
+    mp = _mp(alg_name="deepfm_pipeline", batch_size=32, epochs=1, cont_field_size=C_, vector_feats_size=V, cate_field_size=Fc)
+    got = list(L.pipeline_process(mp, [d + "part-r-00000"], "predict", pin=False))
+    assert len(got) == n // 32
+    for j, b in enumerate(got):
+        sl = rows[32 * j: 32 * j + 32]
+        assert np.array_equal(b["cate_feats"].numpy(), np.stack([r["cate_feats"] for r in sl]))
+        assert np.array_equal(b["cont_feats"].numpy(), np.stack([r["cont_feats"] for r in sl]).astype(np.float32))
+        assert np.array_equal(b["vector_feats"].numpy(), np.stack([r["vector_feats"] for r in sl]).astype(np.float32))
+        assert np.array_equal(b["label"].numpy(), np.stack([r["label"] for r in sl]).astype(np.float32))
