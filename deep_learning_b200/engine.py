@@ -16,6 +16,10 @@ import torch
 from . import _lib
 from . import shard as _shard
 from ._lib import DenseLayout, MAX_LAYERS, AdamHP, EmbedCfg, ptr
+
+# where the side-stream id sort starts: behind the gather (default; it then shares the machine with the forward GEMMs and
+# the head kernel, which it slows from 64 to 95 us) or behind the head kernel (shares it with the backward GEMMs)
+_SORT_AFTER_HEAD = os.environ.get("CTR_SORT_AT", "embed") == "head"
 from .spec import ModelSpec
 
 ADAM_BETA1, ADAM_BETA2, ADAM_EPS = 0.9, 0.999, 1e-8   # tf.train.AdamOptimizer defaults (models/deepfm.py:161)
@@ -529,7 +533,7 @@ class CtrEngine:
     def forward(self, B: int, with_loss: bool) -> None:
         s, st, h = self.spec, self._stream(), self.h
         self._embed_forward(B)
-        if self._sort_B is not None:
+        if self._sort_B is not None and not _SORT_AFTER_HEAD:
             # the id sort starts BEHIND the gather: K1 is the HBM-bound kernel of the step and a co-running radix sort took
             # 20 % of its bandwidth; under the tensor-core GEMMs that follow the sort is close to free, and its result is
             # only needed after the MLP backward
@@ -562,6 +566,9 @@ class CtrEngine:
                ptr(self.dlogit) if with_loss else None,
                ptr(self.dz[0]) if (with_loss and self.train_mode) else None, s.hidden[-1], int(self.prec == 1),
                ptr(self.loss) if with_loss else None, ptr(g_fm), ptr(g_deep), ptr(g_bias), ptr(self.ws), self.ws.numel())
+        if self._sort_B is not None:        # CTR_SORT_AT=head: the sort runs under the backward GEMMs instead (A/B knob)
+            self._launch_sort(self._sort_B)
+            self._sort_B = None
 
     def global_batch(self, B: int) -> int:
         """samples the loss is a mean over (all ranks' batches when sharded)"""
