@@ -173,3 +173,83 @@ def test_product_fit_loop_consumes_batches_like_the_reference_fit(alg, capsys):
         else:
             assert tag == ("val", e % len(val))
             e += 1
+
+
+class _OracleEngine:
+    """the oracle behind the engine interface the product's fit loops use (test double: lets those loops run on CPU with
+    real numbers, so what they PRINT can be held against what the reference's `fit` printed)"""
+
+    def __init__(self, alg, hp, p):
+        self.alg, self.hp, self.p, self.st = alg, hp, p, O.adam_init(p)
+        self.last_batch, self.label, self.score = 0, None, None
+
+    @staticmethod
+    def _ob(b):
+        out = {}
+        for k, v in b.items():
+            if k == "tag":
+                continue
+            t = torch.as_tensor(v)
+            out[k] = t.double() if t.is_floating_point() else t.long()
+        return out
+
+    def train_step(self, b, next_batch=None):
+        loss, self.p = O.train_step(self.alg, self.p, self.st, self._ob(b), self.hp, adam_mode="tf_dense")
+        return loss.detach()
+
+    def predict(self, b):
+        return O.FORWARD[self.alg](self.p, self._ob(b), self.hp)[1].detach().reshape(-1)
+
+    def eval_loss(self, b):
+        ob = self._ob(b)
+        loss, _, score = O.LOSS[self.alg](self.p, ob, self.hp)
+        self.last_batch, self.label, self.score = ob["label"].shape[0], ob["label"].reshape(-1), score.detach().reshape(-1)
+        return loss.detach()
+
+    def auc(self, scores, labels):
+        return O.roc_auc(labels.numpy().reshape(-1), scores.numpy().reshape(-1))
+
+
+def _progress_lines(text):
+    """(iteration tag, auc, loss) of every progress line, whatever the generation's format"""
+    out = []
+    for line in text.splitlines():
+        m = re.match(r"\[(\d+)\]\s*(?:valid-auc=|val_auc:|test auc:)([0-9.eE+-]+)\s*loss[=:]([0-9.eE+-]+)", line)
+        if m:
+            out.append((int(m.group(1)), float(m.group(2)), float(m.group(3))))
+    return out
+
+
+@pytest.mark.parametrize("alg", ALGS)
+def test_product_fit_prints_what_the_reference_fit_printed(alg, capsys):
+    """deep_learning_b200/models/_base.py `_fit_a/_fit_b/_fit_c` (running-loss bookkeeping, evaluation cadence, line
+    formats) driven over the recorded batches with the oracle as engine: the progress lines carry the reference's
+    iteration tags, AUCs and losses"""
+    from deep_learning_b200.models._base import BaseDeepModel
+    z = np.load(os.path.join(HERE, "golden", "ref_%s.npz" % alg))
+    hp = G.tiny_hp(alg)
+    family = str(z["family"])
+    p = {k[5:]: torch.from_numpy(z[k]).double() for k in z.files if k.startswith("init/")}
+    m = object.__new__(BaseDeepModel)
+    m.engine = _OracleEngine(alg, hp, p)
+    m._decode = lambda item: item
+    m.epochs, m.batch_size, m.metric_type = 1, hp.batch_size, "auc"
+    m.model_pb = m.save_model_checkpoint = m.restore_model_checkpoint = None
+    m.model_restore = 0
+    n_train = len([k for k in z.files if k.startswith("train") and k.endswith("/label")])
+    train = [{k.split("/", 1)[1]: z[k] for k in z.files if k.startswith("train%d/" % i)} for i in range(n_train)]
+    val = [{k.split("/", 1)[1]: z[k] for k in z.files if k.startswith("val%d/" % i)} for i in range(int(z["n_val"]))]
+    if family == "feed":
+        m._fit_a(train, val)
+    elif family == "pipe":
+        m.data_dict = iter(train)
+        m._fit_b(1, iter(val))
+    else:
+        m.data_dict = iter(train)
+        m._fit_c(2, 1)
+    got, want = _progress_lines(capsys.readouterr().out), _progress_lines(str(z["fit_stdout"]))
+    assert want and len(got) == len(want), (got, want)
+    for (gi, ga, gl), (wi, wa, wl) in zip(got, want):
+        assert gi == wi
+        tol = 6e-6 if family == "feed" else 1e-12          # generation A prints %.5f
+        assert abs(ga - wa) <= tol and abs(gl - wl) <= tol, (alg, gi, (ga, gl), (wa, wl))
