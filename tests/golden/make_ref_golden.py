@@ -152,6 +152,7 @@ def generate(alg):
     with tempfile.TemporaryDirectory() as tmp, contextlib.redirect_stdout(log):
         args = ref_args(alg, hp, tmp)
         if alg in FEED:
+            args.epochs = 2                   # the running loss of generation A is never reset between epochs (:168-169)
             init, losses, evals = run_feed_model(alg, hp, mod, args, batches, val)
         elif alg in PIPE:
             init, losses, evals, batches, val = run_pipe_model(alg, hp, mod, args, batches, val)
@@ -173,6 +174,7 @@ def generate(alg):
         for k, v in b.items():
             out["val%d/%s" % (i, k)] = v
     out["losses"] = np.asarray(losses, dtype=np.float64)
+    out["epochs"] = np.int64(2 if alg in FEED else 1)
     out["events"] = np.array(classify.events)          # order of train steps (T) and evaluations (E) as `fit` issued them
     out["family"] = np.array("feed" if alg in FEED else "pipe" if alg in PIPE else "text")
     for i, e in enumerate(evals):

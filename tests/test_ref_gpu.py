@@ -41,12 +41,13 @@ def test_cuda_reproduces_the_reference_run(alg):
     family, events, n_val = str(z["family"]), str(z["events"]), int(z["n_val"])
     B = hp.batch_size
     t = e = pulled = 0
+    ntb = len([k for k in z.files if k.startswith("train") and k.endswith("/label")])
     for ev in events:
         if family == "text":
             b = _batch(z, "train%d" % pulled)
             pulled += 1
         elif ev == "T":
-            b = _batch(z, "train%d" % t)
+            b = _batch(z, "train%d" % (t % ntb))
         else:
             b = _batch(z, "val%d" % (e % n_val))
         if ev == "T":
