@@ -10,6 +10,9 @@ if [ "$N" = "1" ]; then
   timeout 200 python tests/phase_timing.py > gpurun_out/phases_n1.txt 2>&1
   timeout 300 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
       --log-file gpurun_out/launches_n1.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launch.log 2>&1
+  # one-off probes for open design questions; each bounded, none touches the library
+  nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/probe_gather4 tools/probe_gather4.cu \
+      && timeout 120 /tmp/probe_gather4 > gpurun_out/probe_gather4.txt 2>&1
 else
   TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
   timeout 300 $TR tests/mgpu_parity.py deepfm lazy > gpurun_out/parity_n$N.log 2>&1; echo "parity rc $?" >> gpurun_out/parity_n$N.log
