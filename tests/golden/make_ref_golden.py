@@ -142,7 +142,15 @@ def run_feed_model(alg, hp, mod, args, batches, val):
 
 
 def generate(alg):
-    hp = G.tiny_hp(alg)
+    out = run_reference(alg, G.tiny_hp(alg))
+    path = os.path.join(HERE, "ref_%s.npz" % alg)
+    np.savez_compressed(path, **out)
+    print("%-20s %6d bytes  steps=%d  losses=%s" % (alg, os.path.getsize(path), len(out["losses"]),
+                                                     np.array2string(out["losses"], precision=6)))
+
+
+def run_reference(alg, hp):
+    """the reference's model file for `alg`, built with `hp` and run through its own `fit`: everything recorded"""
     S.reset_default_graph()
     np.random.seed(2019)                      # the reference draws the MLP weights from numpy's global generator
     mod = load_reference_model(alg)
@@ -181,10 +189,7 @@ def generate(alg):
         out["eval%d" % i] = np.asarray(e, dtype=np.float64)
     gs = [v for v in S.global_variables() if not v.dtype.is_float and v.value.dim() == 0]
     out["global_step"] = np.int64(int(gs[0].value)) if gs else np.int64(-1)
-    path = os.path.join(HERE, "ref_%s.npz" % alg)
-    np.savez_compressed(path, **out)
-    print("%-20s %6d bytes  steps=%d  losses=%s" % (alg, os.path.getsize(path), len(losses),
-                                                     np.array2string(out["losses"], precision=6)))
+    return out
 
 
 def classify(rec):

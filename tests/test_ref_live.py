@@ -1,0 +1,51 @@
+"""CPU, build container only (skipped where /root/reference is absent): the reference's model files are run LIVE under
+the TensorFlow-1.x stand-in at configurations other than the committed fixtures' -- one tower layer and three, no
+regulariser, other embedding widths, batch sizes, continuous / vector widths -- and the oracle must reproduce each run
+to 1e-12 (same replay as tests/test_ref_golden.py).  Widens the pin beyond one shape per model."""
+import copy
+import os
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import ctr_oracle as O
+from golden import make_golden as G
+from test_ref_golden import ALGS, _Files, replay_with_oracle
+
+pytestmark = pytest.mark.skipif(not os.path.isdir("/root/reference/models"), reason="needs /root/reference (build container)")
+
+
+def _variant(alg, which):
+    hp = copy.deepcopy(G.tiny_hp(alg))
+    if which == "shallow_noreg":
+        hp.hidden_units, hp.embedding_size, hp.l2_reg, hp.learning_rate, hp.batch_size = [6], 3, 0.0, 5e-3, 8
+    else:
+        hp.hidden_units, hp.embedding_size, hp.l2_reg, hp.batch_size = [5, 7, 3], 8, 1e-2, 24
+        if alg not in O.NO_CONT:
+            hp.cont_field_size = 4
+        if hp.vector_feats_size:
+            hp.vector_feats_size = 3
+    return hp
+
+
+@pytest.fixture(scope="module")
+def generator():
+    here = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    sys.path.insert(0, here)
+    import make_ref_golden as M
+    M.S.install()
+    yield M
+    for k in [k for k in sys.modules if k == "tensorflow" or k.startswith("tensorflow.")]:
+        if getattr(sys.modules[k], "__file__", None) is None:
+            del sys.modules[k]
+
+
+@pytest.mark.parametrize("which", ["shallow_noreg", "deep_wide"])
+@pytest.mark.parametrize("alg", ALGS)
+def test_oracle_reproduces_live_reference_runs(alg, which, generator, capsys):
+    hp = _variant(alg, which)
+    z = _Files(generator.run_reference(alg, hp))
+    capsys.readouterr()
+    assert int(z["n_train"]) >= 3
+    replay_with_oracle(alg, z, hp)
