@@ -373,3 +373,39 @@ def test_tf_example_wire_format_against_the_protobuf_runtime(tmp_path, lib_ready
         assert np.array_equal(b["cont_feats"].numpy(), np.stack([r["cont_feats"] for r in sl]).astype(np.float32))
         assert np.array_equal(b["vector_feats"].numpy(), np.stack([r["vector_feats"] for r in sl]).astype(np.float32))
         assert np.array_equal(b["label"].numpy(), np.stack([r["label"] for r in sl]).astype(np.float32))
+
+
+def test_tfrecord_framing_against_tensorboard(tmp_path, lib_ready):
+    """TensorBoard ships its own implementation of the TFRecord container (masked CRC-32C, length/CRC framing): its
+    writer's files through the oracle and the native reader, the oracle writer's files through its CRC-checking reader"""
+    rw = pytest.importorskip("tensorboard.summary.writer.record_writer")
+    pw = pytest.importorskip("tensorboard.compat.tensorflow_stub.pywrap_tensorflow")
+    for blob in (b"", b"a", b"123456789", bytes(range(256)) * 5):
+        assert LO.crc32c(blob) == pw.crc32c(blob) and LO.masked_crc(blob) == rw.masked_crc32c(blob)
+    g = np.random.RandomState(12)
+    n, C_, V, Fc = 40, 2, 1, 3
+    rows = [{"label": g.rand(1).round(), "cont_feats": g.rand(C_), "vector_feats": g.randn(V),
+             "cate_feats": g.randint(0, 2 ** 33, size=Fc)} for _ in range(n)]
+    payloads = [LO.encode_example(r) for r in rows]
+    d = str(tmp_path) + "/"
+    with open(d + "part-tb", "wb") as f:                       # written by TensorBoard's RecordWriter
+        w = rw.RecordWriter(f)
+        for p in payloads:
+            w.write(p)
+        w.flush()
+    LO.write_tfrecord(d + "part-own", payloads)                 # written by the oracle
+    assert open(d + "part-tb", "rb").read() == open(d + "part-own", "rb").read()
+    rd = pw.PyRecordReader_New(d + "part-own")                  # TensorBoard's reader checks both CRCs of every record
+    back = []
+    while True:
+        try:
+            rd.GetNext()
+        except Exception as e:
+            assert type(e).__name__ == "OutOfRangeError", e
+            break
+        back.append(rd.record())
+    assert back == payloads
+    mp = _mp(alg_name="deepfm_pipeline", batch_size=8, epochs=1, cont_field_size=C_, vector_feats_size=V, cate_field_size=Fc)
+    got = list(L.pipeline_process(mp, [d + "part-tb"], "predict", pin=False))
+    assert len(got) == n // 8
+    assert np.array_equal(torch.cat([b["cate_feats"] for b in got]).numpy(), np.stack([r["cate_feats"] for r in rows]))
