@@ -330,3 +330,23 @@ def test_deepfm_pipeline_autograd_matches_finite_differences():
     support = (grads["feats_emb"].abs().sum(1) + grads["fm_first_order_emb"].abs().sum(1)) > 0
     assert not (support & ~tr["feats_emb"]).any() and not tr["feats_emb"][0]
     assert tr["feats_emb"][hp.cont_field_size]          # padding id 0 -> FM row C is touched
+
+
+def test_tf1_adam_against_torch_optim_adam_over_ten_steps():
+    """an independent implementation of the moment updates and both bias corrections: torch.optim.Adam computes
+    theta -= lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps), which is TF1's lr*sqrt(1-b2^t)/(1-b1^t) * m/(sqrt(v) + eps_tf)
+    exactly when eps = eps_tf / sqrt(1-b2^t); with that per-step eps the two must agree over many steps, on gradients
+    spanning the scale where eps matters (1e-9 .. 1)"""
+    g = torch.Generator().manual_seed(5)
+    p0 = {"w": torch.randn(7, 3, generator=g, dtype=torch.float64)}
+    hp = O.HParams(learning_rate=1e-2)
+    p, st = {k: v.clone() for k, v in p0.items()}, O.adam_init(p0)
+    w = p0["w"].clone().requires_grad_(True)
+    opt = torch.optim.Adam([w], lr=hp.learning_rate, betas=(O.ADAM_BETA1, O.ADAM_BETA2), eps=O.ADAM_EPS)
+    for t in range(1, 11):
+        grad = torch.randn(7, 3, generator=g, dtype=torch.float64) * torch.logspace(-9, 0, 21, dtype=torch.float64).reshape(7, 3)
+        p = O.tf1_adam_step(p, {"w": grad}, st, hp)
+        opt.param_groups[0]["eps"] = O.ADAM_EPS / math.sqrt(1 - O.ADAM_BETA2 ** t)
+        w.grad = grad.clone()
+        opt.step()
+        assert float((p["w"] - w.detach()).abs().max()) < 1e-14, t
