@@ -35,6 +35,7 @@ import make_golden as G   # noqa: E402
 from oracle import ctr_oracle as O   # noqa: E402
 
 REF = "/root/reference"
+PREDICT_MARK = "#### predict ####"
 N_TRAIN = 3
 
 FEED = ("deepfm", "dnn", "wdl")                                        # fit(train_data, val_data): pickled batches
@@ -138,6 +139,8 @@ def run_feed_model(alg, hp, mod, args, batches, val):
     with Recorder() as rec:
         model.fit([pack(b) for b in batches], [pack(b) for b in val])
     losses, evals = classify(rec)
+    print(PREDICT_MARK)
+    model.predict([pack(b) for b in val])          # models/deepfm.py:233-255: reload the exported model, score, print the AUC
     return rec.init_snap, losses, evals
 
 
@@ -168,8 +171,10 @@ def run_reference(alg, hp):
             init, losses, evals, batches, val = run_text_model(alg, hp, mod, args, batches, val)
     p0, names = match_params(alg, hp, init)
     p1, _ = match_params(alg, hp, snapshot())
+    fit_log, _, predict_log = log.getvalue().partition(PREDICT_MARK)
     out = {"n_train": np.int64(len(losses)), "n_val": np.int64(len(val)), "n_eval": np.int64(len(evals)),
-           "fit_stdout": np.array("\n".join(l for l in log.getvalue().splitlines() if "auc" in l))}       # sklearn's AUC as `fit` printed it
+           "fit_stdout": np.array("\n".join(l for l in fit_log.splitlines() if "auc" in l)),       # sklearn's AUC as `fit` printed it
+           "predict_stdout": np.array("\n".join(l for l in predict_log.splitlines() if "auc" in l))}
     for k, v in getattr(run_text_model, "extra", {}).items():
         out["init/" + k] = out["final/" + k] = v
     run_text_model.extra = {}
@@ -183,6 +188,9 @@ def run_reference(alg, hp):
             out["val%d/%s" % (i, k)] = v
     out["losses"] = np.asarray(losses, dtype=np.float64)
     out["epochs"] = np.int64(2 if alg in FEED else 1)
+    # the batches the reference's predict() scored after fit: the validation set, which the textline loop holds as the
+    # two batches of the stream behind the train batches
+    out["predict_on"] = np.array(["train%d" % (N_TRAIN + i) for i in range(2)] if alg in TEXT else ["val0", "val1"])
     out["events"] = np.array(classify.events)          # order of train steps (T) and evaluations (E) as `fit` issued them
     out["family"] = np.array("feed" if alg in FEED else "pipe" if alg in PIPE else "text")
     for i, e in enumerate(evals):
@@ -222,6 +230,8 @@ def run_pipe_model(alg, hp, mod, args, batches, val):
     with Recorder() as rec:
         model.fit(1, val_src.tensors)                 # evaluate after every train step from the second on
     losses, evals = classify(rec)
+    print(PREDICT_MARK)
+    mod.predict(S.BatchSource(val, keys).tensors, args.model_pb)          # models/deepfm_multi.py:383-418
     return rec.init_snap, losses, evals, batches, val
 
 
@@ -254,6 +264,11 @@ def run_text_model(alg, hp, mod, args, batches, val):
     with Recorder() as rec:
         model.fit(2, 1)
     losses, evals = classify(rec)
+    print(PREDICT_MARK)
+    if alg == "wdl_textline":                      # models/wdl_textline.py:362-386: pickled batches
+        mod.predict([pickle.dumps(f) for f in feed[len(batches):len(batches) + len(val)]], args.model_pb)
+    else:                                          # models/dnn_multi_textline.py:233-256: plain dicts
+        mod.predict(feed[len(batches):len(batches) + len(val)], args.model_pb)
     extra = {"tags_emb": tags} if alg == "dnn_multi_textline" else {}
     run_text_model.extra = extra
     # the stream as consumed: which batches were evaluated, which were trained on, is the reference loop's business

@@ -856,8 +856,7 @@ def _default_session():
 
 class Session:
     def __init__(self, target="", graph=None, config=None):
-        if graph is not None and graph is not _graph:
-            raise NotImplementedError("a second graph (SavedModel loading) is outside the path the stand-in runs")
+        self.graph = graph if graph is not None else _graph      # a fresh Graph() until loader.load binds a saved one
 
     def __enter__(self):
         _sessions.append(self)
@@ -872,9 +871,9 @@ class Session:
 
     def _lookup(self, f):
         if isinstance(f, str):
-            if f not in _graph.by_name:
+            if f not in self.graph.by_name:
                 raise KeyError("The name %r refers to a Tensor which does not exist" % f)
-            return _graph.by_name[f]
+            return self.graph.by_name[f]
         return f
 
     def run(self, fetches, feed_dict=None):
@@ -1099,9 +1098,41 @@ gfile = types.SimpleNamespace(FastGFile=_fast_gfile, ListDirectory=_list_directo
 
 
 # ------------------------------------------------------------------------------------------------ saved-model stubs
+_saved_models = {}
+
+
 class _SavedModelBuilder:
+    """SavedModelBuilder(dir).add_meta_graph_and_variables(sess, tags, ...).save(): here the "file" is an entry of a
+    process-wide registry holding the graph (its names and variables), which is all `loader.load` + `run("score:0")` need"""
+
     def __init__(self, export_dir):
-        raise RuntimeError("SavedModel export is not part of the path the stand-in runs")
+        if export_dir in _saved_models:
+            raise AssertionError("Export directory already exists, and isn't empty: " + str(export_dir))
+        self._dir, self._graph = export_dir, None
+
+    def add_meta_graph_and_variables(self, sess, tags, signature_def_map=None, clear_devices=False, legacy_init_op=None,
+                                     **kw):
+        if kw:
+            raise TypeError("SavedModelBuilder argument(s) %s not handled by the TF1 stand-in" % sorted(kw))
+        for v in sess.graph.variables:
+            if v.value is None:
+                raise RuntimeError("FailedPreconditionError: attempting to save uninitialized value " + v.name)
+        self._graph, self._tags = sess.graph, list(tags)
+
+    def save(self):
+        if self._graph is None:
+            raise AssertionError("Graph state including variables and assets has not been saved yet")
+        _saved_models[self._dir] = (self._graph, self._tags)
+        return self._dir
+
+
+def _loader_load(sess, tags, export_dir):
+    if export_dir not in _saved_models:
+        raise IOError("SavedModel file does not exist at: " + str(export_dir))
+    graph, saved_tags = _saved_models[export_dir]
+    if list(tags) != saved_tags:
+        raise RuntimeError("MetaGraphDef associated with tags %r could not be found in SavedModel" % (list(tags),))
+    sess.graph = graph
 
 
 def _module(name, **attrs):
@@ -1136,7 +1167,7 @@ def install():
                  signature_def_utils=signature_def_utils, tag_constants=tag_constants, utils=utils)
     py = _module("tensorflow.python", saved_model=sm)
     tf.python = py
-    tf.saved_model = types.SimpleNamespace(tag_constants=tag_constants)
+    tf.saved_model = types.SimpleNamespace(tag_constants=tag_constants, loader=types.SimpleNamespace(load=_loader_load))
     mods = {"tensorflow": tf, "tensorflow.python": py, "tensorflow.python.saved_model": sm,
             "tensorflow.python.saved_model.builder": builder,
             "tensorflow.python.saved_model.signature_constants": signature_constants,

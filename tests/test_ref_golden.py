@@ -269,3 +269,26 @@ def test_product_fit_prints_what_the_reference_fit_printed(alg, capsys):
         assert gi == wi
         tol = 6e-6 if family == "feed" else 1e-12          # generation A prints %.5f
         assert abs(ga - wa) <= tol and abs(gl - wl) <= tol, (alg, gi, (ga, gl), (wa, wl))
+
+
+@pytest.mark.parametrize("alg", ALGS)
+def test_reference_predict_after_export(alg, capsys):
+    """the reference's predict (method or module function: reload the exported model, run "score:0" batch by batch, print
+    scikit-learn's AUC; models/deepfm.py:233-255, models/deepfm_multi.py:383-418, models/wdl_textline.py:362-386) ran after
+    `fit` when the fixture was made.  The oracle's scores under the final variables give that AUC, and the product's
+    `_predict_a` prints the same line."""
+    from deep_learning_b200.models._base import BaseDeepModel
+    z = np.load(os.path.join(HERE, "golden", "ref_%s.npz" % alg))
+    hp = G.tiny_hp(alg)
+    line = str(z["predict_stdout"]).strip()
+    assert re.fullmatch(r"val of auc:\d\.\d{5}", line), line
+    p = {k[6:]: torch.from_numpy(z[k]).double() for k in z.files if k.startswith("final/")}
+    names = [str(n) for n in z["predict_on"]]
+    m = object.__new__(BaseDeepModel)
+    m.engine = _OracleEngine(alg, hp, p)
+    m._decode = lambda item: item
+    m.model_pb = None
+    batches = [{k.split("/", 1)[1]: z[k] for k in z.files if k.startswith(n + "/")} for n in names]
+    auc = m._predict_a(batches)
+    assert capsys.readouterr().out.strip().splitlines()[-1] == line
+    assert abs(auc - float(line.split(":")[1])) < 6e-6

@@ -168,3 +168,28 @@ def test_text_line_dataset_batches_across_files_and_repeats(tmp_path):
     nxt = keep.make_one_shot_iterator().get_next()
     with tf.Session() as sess:
         assert [sess.run(nxt["x"]).ravel().tolist() for _ in range(2)] == [[1, 2], [3]]
+
+
+def test_saved_model_registry_round_trip():
+    """export -> Session(graph=Graph()) -> loader.load -> run by tensor name, as the reference's predict() does"""
+    x = tf.placeholder(tf.float32, [None, 2], name="x_in")
+    w = tf.Variable(np.array([[2.0], [3.0]]), dtype=np.float32)
+    tf.identity(tf.matmul(x, w), name="score")
+    with tf.Session() as sess:
+        sess.run(tf.global_variables_initializer())
+        b = tf._SavedModelBuilder("/nowhere/pb")
+        with pytest.raises(AssertionError):
+            b.save()                                        # nothing added yet
+        b.add_meta_graph_and_variables(sess, ["serve"], signature_def_map={}, clear_devices=True, legacy_init_op=None)
+        b.save()
+    with pytest.raises(AssertionError):
+        tf._SavedModelBuilder("/nowhere/pb")                # TF refuses an export directory that exists
+    tf.reset_default_graph()                                # the training graph is gone; only the export remains
+    s2 = tf.Session(graph=tf.Graph())
+    with pytest.raises(KeyError):
+        s2.run("score:0", feed_dict={})
+    with pytest.raises(IOError):
+        tf._loader_load(s2, ["serve"], "/nowhere/else")
+    tf._loader_load(s2, ["serve"], "/nowhere/pb")
+    assert s2.run("score:0", feed_dict={"x_in:0": [[1.0, 1.0]]}).tolist() == [[5.0]]
+    del tf._saved_models["/nowhere/pb"]
