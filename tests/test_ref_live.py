@@ -49,3 +49,35 @@ def test_oracle_reproduces_live_reference_runs(alg, which, generator, capsys):
     capsys.readouterr()
     assert int(z["n_train"]) >= 3
     replay_with_oracle(alg, z, hp)
+
+
+@pytest.mark.parametrize("alg", ALGS)
+def test_product_initial_distributions_follow_the_reference(alg, generator, capsys):
+    """`models/_base.py::init_weights` against the variables the reference's own constructors initialise (drawn by the
+    stand-in with the parameters the reference code passes: stddev / bounds / glorot scales).  Values cannot match (TF's
+    generators are not reproducible); location, scale and support must."""
+    from deep_learning_b200.models._base import init_weights
+    from deep_learning_b200.spec import spec_from_hparams
+    hp = copy.deepcopy(G.tiny_hp(alg))
+    hp.hidden_units, hp.embedding_size = [48, 24], 8
+    if alg in ("wdl", "wdl_textline"):
+        hp.cate_index_size = 3000
+    else:
+        hp.cate_feats_size = 3000
+    z = generator.run_reference(alg, hp)
+    capsys.readouterr()
+    mine = init_weights(spec_from_hparams(alg, hp), seed=7)
+    ref = {k[5:]: np.asarray(v) for k, v in z.items() if k.startswith("init/") and k != "init/tags_emb"}
+    assert set(ref) <= set(mine), sorted(set(ref) - set(mine))
+    for name, r in ref.items():
+        m = np.asarray(mine[name], dtype=np.float64)
+        assert m.shape == r.shape, (alg, name, m.shape, r.shape)
+        n = r.size
+        if n < 400:
+            continue                                     # biases of a few elements: shape only
+        tol = 4.0 / np.sqrt(n)                            # ~4 sigma of the sampling error of a scale estimate
+        assert abs(m.std() / r.std() - 1) < 1.5 * tol + 0.02, (alg, name, m.std(), r.std())
+        assert abs(m.mean() - r.mean()) < 6 * r.std() / np.sqrt(n) + 1e-12, (alg, name, m.mean(), r.mean())
+        # support: a uniform draw has hard bounds, a normal draw does not
+        kurt = lambda a: float(np.mean((a - a.mean()) ** 4) / a.var() ** 2)
+        assert abs(kurt(m) - kurt(r)) < 0.5, (alg, name, kurt(m), kurt(r))          # uniform 1.8 vs normal 3.0
