@@ -5,6 +5,7 @@
 // tf.data graphs of utils/data_loader_load.py:187-243, utils/data_loader_textline.py:4-36 and
 // utils/data_loader.py:7-40 (TFRecordDataset + parse_single_example).  No device code in this file.
 #include <cerrno>
+#include <charconv>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
@@ -33,40 +34,72 @@ inline void store_id(void* base, int id_bytes, int64_t pos, long long v) {
 const double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
                            1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
 
-inline bool fast_decimal(const char* p, const char* e, double* out) {
+// eight ASCII digits at once (little-endian SWAR, the well-known fast_float / simdjson arithmetic)
+inline uint64_t load8(const char* p) {
+    uint64_t v;
+    memcpy(&v, p, 8);
+    return v;
+}
+inline bool eight_digits(uint64_t v) {
+    return ((v & 0xF0F0F0F0F0F0F0F0ull) | (((v + 0x0606060606060606ull) & 0xF0F0F0F0F0F0F0F0ull) >> 4)) == 0x3333333333333333ull;
+}
+inline uint32_t parse8(uint64_t v) {
+    const uint64_t mask = 0x000000FF000000FFull;
+    const uint64_t mul1 = 0x000F424000000064ull;      // 100 + (1000000 << 32)
+    const uint64_t mul2 = 0x0000271000000001ull;      // 1 + (10000 << 32)
+    v -= 0x3030303030303030ull;
+    v = (v * 10) + (v >> 8);
+    v = (((v & mask) * mul1) + (((v >> 16) & mask) * mul2)) >> 32;
+    return (uint32_t) v;
+}
+
+// scans [-+]digits[.digits] from p and stops at the first other character; returns that position, or nullptr when the
+// spelling is not of this form or the value is outside the exact fast path (the caller then takes the whole token
+// through parse_float_slow)
+inline const char* scan_decimal(const char* p, const char* e, double* out) {
     bool neg = false;
     if (p < e && (*p == '-' || *p == '+')) neg = *p++ == '-';
     uint64_t m = 0;
     int nd = 0, frac = 0;
-    bool dot = false;
-    for (; p < e; ++p) {
-        const char c = *p;
-        if (c >= '0' && c <= '9') {
-            if (m > (((uint64_t) 1 << 53) - 10) / 10) return false;
-            m = m * 10 + (uint64_t) (c - '0');
-            ++nd;
-            if (dot) ++frac;
-        } else if (c == '.' && !dot) {
-            dot = true;
-        } else {
-            return false;
+    for (; p < e && *p >= '0' && *p <= '9'; ++p, ++nd) {
+        if (nd >= 19) return nullptr;
+        m = m * 10 + (uint64_t) (*p - '0');
+    }
+    if (p < e && *p == '.') {
+        ++p;
+        while (e - p >= 8 && nd + 8 <= 19) {
+            const uint64_t w = load8(p);
+            if (!eight_digits(w)) break;
+            m = m * 100000000ull + parse8(w);
+            p += 8; nd += 8; frac += 8;
+        }
+        for (; p < e && *p >= '0' && *p <= '9'; ++p, ++nd, ++frac) {
+            if (nd >= 19) return nullptr;
+            m = m * 10 + (uint64_t) (*p - '0');
         }
     }
-    if (nd == 0 || frac > 22) return false;
+    if (nd == 0 || frac > 22 || m >= ((uint64_t) 1 << 53)) return nullptr;
     const double d = (double) m / kPow10[frac];
     *out = neg ? -d : d;
-    return true;
+    return p;
 }
 
-inline bool parse_float_tok(const char* p, const char* e, float* out) {
-    double fd;
-    if (fast_decimal(p, e, &fd)) {
-        *out = (float) fd;
-        return true;
+// everything the fast path leaves: long mantissas and exponents through std::from_chars (correctly rounded, = strtod),
+// the remaining spellings Python's float() accepts (leading '+', inf, nan, surrounding blanks) through strtod
+inline bool parse_float_slow(const char* p, const char* e, float* out) {
+    const size_t n = (size_t) (e - p);
+    if (n == 0) return false;
+    const char* f = (*p == '-') ? p + 1 : p;
+    if (f < e && ((*f >= '0' && *f <= '9') || *f == '.')) {
+        double d;
+        const std::from_chars_result r = std::from_chars(p, e, d);
+        if (r.ec == std::errc() && r.ptr == e) {
+            *out = (float) d;
+            return true;
+        }
     }
     char tmp[64];
-    const size_t n = (size_t) (e - p);
-    if (n == 0 || n >= sizeof(tmp)) return false;
+    if (n >= sizeof(tmp)) return false;
     memcpy(tmp, p, n);
     tmp[n] = 0;
     if (memchr(tmp, 'x', n) || memchr(tmp, 'X', n)) return false;     // strtod reads hex floats, Python's float() does not
@@ -77,6 +110,47 @@ inline bool parse_float_tok(const char* p, const char* e, float* out) {
     if (*end != 0) return false;
     *out = (float) d;
     return true;
+}
+
+inline bool parse_float_tok(const char* p, const char* e, float* out) {
+    double fd;
+    if (scan_decimal(p, e, &fd) == e) {
+        *out = (float) fd;
+        return true;
+    }
+    return parse_float_slow(p, e, out);
+}
+
+// one float of a `sep`-separated list inside [a, q): value stored, *next = end of the token (at `sep` or at q)
+inline bool next_float(const char* a, const char* q, char sep, float* out, const char** next) {
+    double fd;
+    const char* b = scan_decimal(a, q, &fd);
+    if (b && (b == q || *b == sep)) {
+        *out = (float) fd;
+        *next = b;
+        return true;
+    }
+    b = (const char*) memchr(a, sep, (size_t) (q - a));
+    if (!b) b = q;
+    *next = b;
+    return parse_float_slow(a, b, out);
+}
+
+inline bool parse_int_tok(const char* p, const char* e, long long* out);
+// one non-negative decimal id of a `sep`-separated list; anything else goes through parse_int_tok
+inline bool next_int(const char* a, const char* q, char sep, long long* out, const char** next) {
+    const char* b = a;
+    long long v = 0;
+    for (; b < q && *b >= '0' && *b <= '9' && b - a < 18; ++b) v = v * 10 + (*b - '0');
+    if (b > a && (b == q || *b == sep)) {
+        *out = v;
+        *next = b;
+        return true;
+    }
+    b = (const char*) memchr(a, sep, (size_t) (q - a));
+    if (!b) b = q;
+    *next = b;
+    return parse_int_tok(a, b, out);
 }
 
 inline bool parse_int_tok(const char* p, const char* e, long long* out) {
@@ -123,8 +197,8 @@ bool parse_line(const char* p, const char* e, const LineCfg& c, int64_t row, flo
     {
         const char* a = p;
         for (int j = 0; j < c.n_cont; ++j) {
-            const char* b = tok_end(a, q, ' ');
-            if (!parse_float_tok(a, b, cont + row * (int64_t) c.n_cont + j)) return false;
+            const char* b;
+            if (!next_float(a, q, ' ', cont + row * (int64_t) c.n_cont + j, &b)) return false;
             if (j + 1 < c.n_cont) {
                 if (b == q) return false;
                 a = b + 1;
@@ -140,9 +214,9 @@ bool parse_line(const char* p, const char* e, const LineCfg& c, int64_t row, flo
     {
         const char* a = p;
         for (int j = 0; j < c.n_cate; ++j) {
-            const char* b = tok_end(a, q, ' ');
+            const char* b;
             long long v;
-            if (!parse_int_tok(a, b, &v)) return false;
+            if (!next_int(a, q, ' ', &v, &b)) return false;
             store_id(cate, c.id_bytes, row * (int64_t) c.n_cate + j, v);
             if (j + 1 < c.n_cate) {
                 if (b == q) return false;

@@ -409,3 +409,23 @@ def test_tfrecord_framing_against_tensorboard(tmp_path, lib_ready):
     got = list(L.pipeline_process(mp, [d + "part-tb"], "predict", pin=False))
     assert len(got) == n // 8
     assert np.array_equal(torch.cat([b["cate_feats"] for b in got]).numpy(), np.stack([r["cate_feats"] for r in rows]))
+
+
+def test_decimal_fast_path_boundaries(lib_ready):
+    """the digit scanner's corners, each against Python float() + float32 cast: mantissas around 2^53 (the exact-division
+    limit, beyond it std::from_chars), fraction lengths around the 8-digit blocks, 19 and 20 digits, leading zeros, the
+    float32 rounding boundary of 0.1, signs, and a token that ends the column"""
+    g = np.random.RandomState(3)
+    toks = ["0.9007199254740991", "0.9007199254740992", "0.9007199254740993", "9007199254740993", "9007199254740992.5",
+            "0.95488135218620300", "0.1234567", "0.12345678", "0.123456789", "0.1234567812345678", "0.12345678123456789",
+            "1234567890123456789", "12345678901234567890", "0.0000000000000000000012345", "00000000.5", "-0.00000001",
+            "0.100000001490116119384765625", "0.10000000149011611938476562500000001", "0.0999999940395355224609375",
+            "+1.5", "-.5", "5.", "16777217", "16777216.999999999", "3.4028235677973366e38", "1e-45", "0.7e-45"]
+    toks += [repr(float(np.float32(v))) for v in g.rand(200)] + ["%.19f" % v for v in g.rand(100)] + ["%.12f" % (v * 1e6) for v in g.rand(100)]
+    for i in range(0, len(toks) - 2, 3):
+        t3 = toks[i:i + 3]
+        blk = _parse_one("0," + " ".join(t3) + ",7 8", 3, 2)
+        with np.errstate(over="ignore"):
+            want = np.asarray([float(t) for t in t3], dtype=np.float64).astype(np.float32)
+        assert np.array_equal(blk["cont"].numpy().reshape(-1).view(np.uint32), want.view(np.uint32)), t3
+        assert blk["cate"].numpy().reshape(-1).tolist() == [7, 8]
