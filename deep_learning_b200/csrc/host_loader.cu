@@ -232,11 +232,12 @@ bool parse_line(const char* p, const char* e, const LineCfg& c, int64_t row, flo
     q = tok_end(p, e, ',');
     const char* a = p;
     for (int j = 0; j < c.n_third; ++j) {
-        const char* b = tok_end(a, q, ' ');
+        const char* b;
         long long v;
         if (c.third_kind == 1) {           // wide ids (utils/data_loader_load.py:125-127)
-            if (!parse_int_tok(a, b, &v)) return false;
+            if (!next_int(a, q, ' ', &v, &b)) return false;
         } else {                           // id=value pairs (get_libsvm_value, utils/data_loader_load.py:12-21)
+            b = tok_end(a, q, ' ');
             const char* eq = tok_end(a, b, '=');
             if (eq == b || !parse_int_tok(a, eq, &v)) return false;
             if (!parse_float_tok(eq + 1, b, third_vals + row * (int64_t) c.n_third + j)) return false;
