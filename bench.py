@@ -130,9 +130,11 @@ def main():
     if a.impl == "reference":
         if rank != 0:
             return
-        cb = cpu_reference_arm(max(2, min(a.steps, 5)), 1)
+        # exactly the K steps and W warm-ups asked for (one step of the sample is ~0.15 s on 16 cores); K capped at 200
+        k_run, w_run = max(1, min(a.steps, 200)), max(1, min(a.warmup, 10))
+        cb = cpu_reference_arm(k_run, w_run)
         line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus,
-                "steps": a.steps, "warmup": a.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+                "steps": k_run, "warmup": w_run, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": "DeepFM Criteo-shape 13 cont + 26 cate k=16 MLP 400x3 (CPU sample: " + cb["sample"] + ")"},
                 "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
@@ -289,7 +291,7 @@ def main():
         line["exchange"] = {"unique_rows_requested_rank0": int(eng.U), "rows_served_rank0": int(eng.n_req),
                             "wire_bytes_per_row": 4 + 2 * 4 * eng.wire}
     if not a.no_cpu_baseline and world == 1:
-        cb = cpu_reference_arm(3, 1)
+        cb = cpu_reference_arm(60, 2)          # ~10 s of CPU work on the box's host cores
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
     print(json.dumps(line))
     if world > 1:
