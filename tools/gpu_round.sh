@@ -8,6 +8,8 @@ if [ "$N" = "1" ]; then
   python -m pytest tests -m gpu -q > gpurun_out/pytest.log 2>&1; echo "pytest rc $?" >> gpurun_out/pytest.log
   timeout 300 python bench.py --steps 30 --warmup 5 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err
   timeout 200 python tests/phase_timing.py > gpurun_out/phases_n1.txt 2>&1
+  # A/B knobs that are in the tree but default off
+  CTR_SORT_AT=head timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/bench_n1_sort_at_head.json 2> gpurun_out/bench_n1_sort_at_head.err
   timeout 300 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
       --log-file gpurun_out/launches_n1.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launch.log 2>&1
   # one-off probes for open design questions; each bounded, none touches the library
