@@ -77,3 +77,20 @@ def test_product_never_imports_oracle():
             if f.endswith(".py"):
                 txt = open(os.path.join(dp, f)).read()
                 assert "oracle" not in txt.replace("no oracle", ""), os.path.join(dp, f)
+
+
+def test_gpu_probes_still_compile(tmp_path):
+    """tools/probe_gather4.cu is run by tools/gpu_round.sh on the GPU box: keep it assembling for sm_100a (and keep the
+    instruction it is about in the SASS)"""
+    import shutil
+    import subprocess
+    nvcc = "/usr/local/cuda/bin/nvcc" if os.path.exists("/usr/local/cuda/bin/nvcc") else shutil.which("nvcc")
+    if not nvcc:
+        pytest.skip("no nvcc")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    obj = str(tmp_path / "probe.o")
+    r = subprocess.run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-c", os.path.join(root, "tools", "probe_gather4.cu"),
+                        "-o", obj], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    sass = subprocess.run([os.path.join(os.path.dirname(nvcc), "cuobjdump"), "-sass", obj], capture_output=True, text=True).stdout
+    assert "UTMALDG.2D.GATHER4" in sass
