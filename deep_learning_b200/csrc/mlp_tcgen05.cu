@@ -158,7 +158,7 @@ struct EpiParams {
     int round_out;          // round outputs to tf32 (they feed the next tensor-core GEMM)
     int col0;               // first global output column of this CTA's slab (dropout hash index)
     int n_total;            // row pitch of the dropout hash index (the full N)
-    int dbg;                // timing experiments only (CTR_GEMM_DBG): 1 skip global stores, 2 skip MMAs, 4 skip TMA loads
+    int dbg;                // experiments only (CTR_GEMM_DBG): 1 skip global stores, 2 skip MMAs, 4 skip TMA loads, 16 direct 256-bit epilogue
     unsigned long long* trace;   // CTR_GEMM_DBG & 8: per-CTA phase timestamps (8 slots per CTA)
     unsigned* sm_slots;     // split2 stagger: per-SM arrival counters (zeroed before the launch), or null
     unsigned stagger_ns;    // the second CTA to arrive on an SM starts this much later (first wave only)
@@ -404,6 +404,71 @@ __device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp
     }
 }
 
+// EXPERIMENT (CTR_GEMM_DBG & 16, default off, not yet run on a GPU): the same epilogue without the shared-memory
+// transposition.  Blackwell has 256-bit global accesses (STG.E.ENL2.256 / LDG.E.ENL2.256): with the accumulator in the
+// 32x32b layout (lane = row, 32 consecutive columns per lane) a lane stores one complete 32-byte sector per instruction,
+// so every sector is written whole although a warp touches 32 different rows; four instructions complete each 128-byte
+// line.  Frees the shared-memory port (the transposition was ~28 B/clk of the 128 the MMAs and TMA fills compete for) at
+// the price of 4x the L2 requests per byte of the coalesced stores.  The 16x256b attempt above had the same request
+// count but 64-bit accesses, i.e. 4x the instructions as well.
+__device__ __forceinline__ void stg_f8(float* p, const float* v) {
+    asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
+                 "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+}
+__device__ __forceinline__ void ldg_f8_stream(const float* p, float* v) {
+    asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]) : "l"(p));
+}
+
+template <bool BIAS, bool RELU, bool MASK, int EW>
+__device__ __forceinline__ void epilogue_rows_direct(uint32_t tmem_base, int ewarp, int lane, int m0, int N, float* C,
+                                                     int64_t ldc, const EpiParams& ep, uint32_t sbias) {
+    const int q = ewarp & 3, half = ewarp >> 2;
+    const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
+    const int nchunks = (N + 31) / 32;
+    const int64_t row = m0 + q * 32 + lane;
+    float* dst_row = C + row * ldc;
+    const float* msk_row = MASK ? ep.mask + row * ep.ldmask : nullptr;
+    const float scale = ep.mask_scale;
+    float mk[32];                                         // ONE buffer: group g of the next sub-tile is requested as soon as
+                                                          // group g of this one has been consumed (a second buffer spills
+                                                          // under the persistent kernel's 128-register cap)
+    auto load_group = [&](int c, int g) {
+        if (c < nchunks && c * 32 + 8 * g < N) ldg_f8_stream(msk_row + c * 32 + 8 * g, mk + 8 * g);
+    };
+    if (MASK) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) load_group(half, g);
+    }
+    for (int c = half; c < nchunks; c += EW / 4) {
+        const int c0 = c * 32;
+        uint32_t r[32];
+        tmem_ld32_issue(lane_addr + (uint32_t) c0, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (c0 + 8 * g < N) {                         // N % 8 == 0: a group of eight columns is valid together
+                float v[8];
+                float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+                if (BIAS) {                               // every lane reads the same address: a broadcast, no bank conflict
+                    b0 = lds_f4(sbias + (uint32_t) ((c0 + 8 * g) * 4));
+                    b1 = lds_f4(sbias + (uint32_t) ((c0 + 8 * g + 4) * 4));
+                }
+                const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    float x = __uint_as_float(r[8 * g + i]);
+                    if (BIAS) x += bb[i];
+                    if (MASK) x = mk[8 * g + i] > 0.f ? x * scale : 0.f;
+                    v[i] = RELU ? cvt_tf32_relu(x) : cvt_tf32(x);
+                }
+                stg_f8(dst_row + c0 + 8 * g, v);
+            }
+            if (MASK) load_group(c + EW / 4, g);
+        }
+    }
+}
+
 // shared memory: [ pipeline stages, reused as epilogue staging | PipeBars | staged bias ]
 __host__ __device__ constexpr size_t pipe_region(size_t stage_total, int ew) {
     return stage_total > (size_t) ew * EPI_TILE_FLOATS * 4 ? stage_total : (size_t) ew * EPI_TILE_FLOATS * 4;
@@ -419,12 +484,21 @@ __device__ __forceinline__ void epilogue_prepare(int m0, int M, int N, const Epi
     asm volatile("bar.sync 1, %0;" ::"r"(EW * 32) : "memory");      // epilogue warps only
 }
 
-template <int EW>
+template <int EW, bool DIRECT = false>
 __device__ __forceinline__ void epilogue_dispatch(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
                                                   int64_t ldc, const EpiParams& ep, float* stage, uint32_t sbias) {
     const bool fast = m0 + BLOCK_M <= M && (N & 3) == 0 && (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
                       ep.round_out && !(ep.keep < 1.f) && !(ep.dbg & 7) &&
                       (!ep.mask || ((ep.ldmask & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.mask) & 15) == 0));
+    if (DIRECT && fast && (N & 7) == 0 && (ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(C) & 31) == 0 &&
+        (!ep.mask || ((ep.ldmask & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.mask) & 31) == 0))) {
+        if (ep.mask) epilogue_rows_direct<false, false, true, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, sbias);
+        else if (ep.bias && ep.relu) epilogue_rows_direct<true, true, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, sbias);
+        else if (ep.bias) epilogue_rows_direct<true, false, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, sbias);
+        else if (ep.relu) epilogue_rows_direct<false, true, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, sbias);
+        else epilogue_rows_direct<false, false, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, sbias);
+        return;
+    }
     if (fast) {
         if (ep.mask) epilogue_rows_fast<false, false, true, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
         else if (ep.bias && ep.relu) epilogue_rows_fast<true, true, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
@@ -680,7 +754,7 @@ constexpr size_t pair_persistent_smem(size_t stage_total, int ew) {
 // 128 registers per thread (not the 204 a lone 320-thread CTA could have): the CTA owns its SM for the whole launch, and
 // the side stream's id sort (radix scatter: 256 threads x 96 registers, 10 KB of shared memory) must still fit next to it,
 // or that work only runs in the gaps between GEMMs and lands on the step's critical path
-template <int EW>
+template <int EW, bool DIRECT = false>
 __global__ void __cluster_dims__(2, 1, 1) __maxnreg__(128)
 gemm_tn_pair_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N,
                                int R, int n_each, int nmma, int nstages, float* __restrict__ C, int64_t ldc, EpiParams ep) {
@@ -790,7 +864,7 @@ gemm_tn_pair_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
             tc_fence_after();
             if (threadIdx.x == 0) TRACE_FINE(256 + 4 * (int) u + 2);
             if (Nu > 0)
-                epilogue_dispatch<EW>(tmem_base + buf * BUF_COLS, warp, lane, m0, M, Nu, C + n0, ldc, epu, estage,
+                epilogue_dispatch<EW, DIRECT>(tmem_base + buf * BUF_COLS, warp, lane, m0, M, Nu, C + n0, ldc, epu, estage,
                                       smem_u32(sbias) + (uint32_t) (n0 * 4));
             tc_fence_before();
             __syncwarp();
@@ -1002,6 +1076,15 @@ int launch_tn(ctr_handle* h, cudaStream_t st, int M, int N, int R, const float* 
         const int n_tiles = (int) ctr_cdiv(M, 2 * BLOCK_M);
         const int max_cl = h->sm_count / 2;
         const unsigned ctas = 2u * (unsigned) (n_tiles < max_cl ? n_tiles : max_cl);
+        if (gemm_dbg() & 16) {      // experiment: transposition-free epilogue on 256-bit stores (separate instantiation, so
+                                    // the default kernel's code and register allocation stay exactly as measured)
+            static bool attr_direct = false;
+            if (!attr_direct) {
+                CTR_CUDA(h, cudaFuncSetAttribute(gemm_tn_pair_persistent_kernel<8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+                attr_direct = true;
+            }
+            gemm_tn_pair_persistent_kernel<8, true><<<ctas, nthreads(8), smem, st>>>(tmA, tmB, M, Ne, R, n_each, nmma, nstages, C, ldc, ep);
+        } else
         gemm_tn_pair_persistent_kernel<8><<<ctas, nthreads(8), smem, st>>>(tmA, tmB, M, Ne, R, n_each, nmma, nstages, C, ldc, ep);
         CTR_CHECK_LAUNCH(h, "gemm_tn_pair_persistent_kernel");
         return CTR_OK;

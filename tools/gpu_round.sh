@@ -9,6 +9,8 @@ if [ "$N" = "1" ]; then
   timeout 300 python bench.py --steps 30 --warmup 5 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err
   timeout 200 python tests/phase_timing.py > gpurun_out/phases_n1.txt 2>&1
   # A/B knobs that are in the tree but default off
+  CTR_GEMM_DBG=16 timeout 300 python -m pytest tests/test_gpu_kernels.py -q -k 'gemm or mlp' > gpurun_out/pytest_gemm_direct_epilogue.log 2>&1
+  CTR_GEMM_DBG=16 timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/bench_n1_direct_epilogue.json 2> gpurun_out/bench_n1_direct_epilogue.err
   CTR_SORT_AT=head timeout 300 python bench.py --steps 30 --warmup 5 --no-cpu-baseline > gpurun_out/bench_n1_sort_at_head.json 2> gpurun_out/bench_n1_sort_at_head.err
   timeout 300 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
       --log-file gpurun_out/launches_n1.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launch.log 2>&1
