@@ -81,3 +81,55 @@ def test_product_initial_distributions_follow_the_reference(alg, generator, caps
         # support: a uniform draw has hard bounds, a normal draw does not
         kurt = lambda a: float(np.mean((a - a.mean()) ** 4) / a.var() ** 2)
         assert abs(kurt(m) - kurt(r)) < 0.5, (alg, name, kurt(m), kurt(r))          # uniform 1.8 vs normal 3.0
+
+
+@pytest.mark.parametrize("alg", ALGS)
+def test_module_surface_matches_the_reference_module(alg, generator):
+    """drop-in surface: every public callable of /root/reference/models/<alg>.py that a launcher can reach (DeepModel, its
+    fit / evaluate / eval / predict / get_val_data, the module-level predict) exists in deep_learning_b200/models/<alg>.py
+    with the same positional parameter names in the same order"""
+    import importlib
+    import inspect
+    ref = generator.load_reference_model(alg)
+    mine = importlib.import_module("deep_learning_b200.models." + alg)
+
+    def params(fn):
+        return [p.name for p in inspect.signature(fn).parameters.values()
+                if p.kind in (p.POSITIONAL_ONLY, p.POSITIONAL_OR_KEYWORD) and p.name != "self"]
+
+    assert hasattr(mine, "DeepModel")
+    ref_init = params(ref.DeepModel.__init__)
+    assert params(mine.DeepModel.__init__)[:len(ref_init)] == ref_init, (alg, params(mine.DeepModel.__init__), ref_init)
+    for name in ("fit", "evaluate", "eval", "predict", "get_val_data"):
+        if hasattr(ref.DeepModel, name):
+            assert hasattr(mine.DeepModel, name), (alg, name)
+            want, got = params(getattr(ref.DeepModel, name)), params(getattr(mine.DeepModel, name))
+            assert got[:len(want)] == want, (alg, name, got, want)
+    if hasattr(ref, "predict"):
+        assert hasattr(mine, "predict"), alg
+        want, got = params(ref.predict), params(mine.predict)
+        assert got[:len(want)] == want, (alg, got, want)
+
+
+def test_loader_surface_matches_the_reference_loaders(generator):
+    """deep_learning_b200/loaders.py keeps the reference loader functions' names and leading positional parameters
+    (utils/data_loader_load.py, utils/data_loader.py, utils/data_loader_textline.py); where two reference modules use
+    one name for different things the product's second name is listed"""
+    import importlib
+    import inspect
+    from deep_learning_b200 import loaders as L
+
+    def params(fn):
+        return [p.name for p in inspect.signature(fn).parameters.values()
+                if p.kind in (p.POSITIONAL_ONLY, p.POSITIONAL_OR_KEYWORD)]
+
+    RL = importlib.import_module("utils.data_loader_load")
+    RP = importlib.import_module("utils.data_loader")
+    RT = importlib.import_module("utils.data_loader_textline")
+    pairs = [(RL.load_process, L.load_process), (RL.load_test, L.load_test), (RL.textline_process, L.textline_process),
+             (RL.load_input_file, L.load_input_file), (RL.get_file_list, L.get_file_list),
+             (RP.pipeline_process, L.pipeline_process), (RP.load_input_file, L.load_tfrecord_input_file),
+             (RT.dnn_multi_process, L.dnn_multi_process)]
+    for ref, mine in pairs:
+        want, got = params(ref), params(mine)
+        assert got[:len(want)] == want, (ref.__module__, ref.__name__, got, want)
