@@ -40,3 +40,12 @@ class ModelParams:
     word2vec_rows: int = 0              # rows of that table when the weights are injected instead of loaded
     max_data_size: int = 1 << 62        # utils/data_loader_load.py:45
     vector_field_size: int = 0          # utils/data_loader_load.py:109 (its spelling of vector_feats_size)
+    # the rest of what the launchers' own ModelParams classes carry (local_run.py:17-38, local_run_test.py:17-45,
+    # local_run_textline.py:17-67), so a launcher can fill this bag attribute for attribute
+    dropout_keep_deep: List[float] = field(default_factory=lambda: [1, 1, 1, 1, 1])   # local_run.py:30 (never below 1 there)
+    feat_conf_path: str = ""            # local_run.py:20
+    cont_feats_conf_path: str = ""      # local_run_textline.py:60
+    train_path: str = ""                # local_run.py:21
+    predict_path: str = ""              # local_run.py:22
+    pred_path: str = ""                 # local_run_textline.py:58
+    multi_cate_field_size: int = 0      # local_run_textline.py:61; width of the libsvm column (utils/data_loader_load.py:73-78)

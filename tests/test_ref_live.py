@@ -133,3 +133,21 @@ def test_loader_surface_matches_the_reference_loaders(generator):
     for ref, mine in pairs:
         want, got = params(ref), params(mine)
         assert got[:len(want)] == want, (ref.__module__, ref.__name__, got, want)
+
+
+def test_hyper_parameter_bag_carries_every_launcher_attribute():
+    """every attribute the reference launchers' own ModelParams classes set (local_run*.py; parsed, not imported: the
+    launchers import modules that do not exist) is a field of deep_learning_b200.hparams.ModelParams"""
+    import ast
+    import glob
+    from deep_learning_b200.hparams import ModelParams
+    mp, seen = ModelParams(), set()
+    for f in sorted(glob.glob("/root/reference/local_run*.py")):
+        for c in ast.walk(ast.parse(open(f).read())):
+            if isinstance(c, ast.ClassDef) and c.name == "ModelParams":
+                for n in ast.walk(c):
+                    if isinstance(n, ast.Attribute) and isinstance(n.value, ast.Name) and n.value.id == "self" and \\
+                            isinstance(n.ctx, ast.Store):
+                        seen.add(n.attr)
+    assert len(seen) > 25
+    assert not [a for a in sorted(seen) if not hasattr(mp, a)]
