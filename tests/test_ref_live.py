@@ -146,8 +146,8 @@ def test_hyper_parameter_bag_carries_every_launcher_attribute():
         for c in ast.walk(ast.parse(open(f).read())):
             if isinstance(c, ast.ClassDef) and c.name == "ModelParams":
                 for n in ast.walk(c):
-                    if isinstance(n, ast.Attribute) and isinstance(n.value, ast.Name) and n.value.id == "self" and \\
-                            isinstance(n.ctx, ast.Store):
+                    if isinstance(n, ast.Attribute) and isinstance(n.value, ast.Name) and n.value.id == "self" \
+                            and isinstance(n.ctx, ast.Store):
                         seen.add(n.attr)
     assert len(seen) > 25
     assert not [a for a in sorted(seen) if not hasattr(mp, a)]
