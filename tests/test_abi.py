@@ -94,3 +94,38 @@ def test_gpu_probes_still_compile(tmp_path):
     assert r.returncode == 0, r.stderr
     sass = subprocess.run([os.path.join(os.path.dirname(nvcc), "cuobjdump"), "-sass", obj], capture_output=True, text=True).stdout
     assert "UTMALDG.2D.GATHER4" in sass
+
+
+def test_no_undefined_names_in_files_that_only_run_on_the_gpu_box():
+    """most of the step drivers, bench.py and the -m gpu tests never execute in the CPU suite: a name used but never
+    bound anywhere in its file (a removed import, a typo) would first show on the GPU box.  File-level heuristic."""
+    import ast
+    import builtins
+    import glob
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    files = glob.glob(os.path.join(root, "deep_learning_b200", "**", "*.py"), recursive=True) + \
+        glob.glob(os.path.join(root, "tests", "*.py")) + [os.path.join(root, "bench.py"), os.path.join(root, "__graft_entry__.py")]
+    assert len(files) > 40
+    bad = {}
+    for f in files:
+        tree = ast.parse(open(f).read())
+        bound = set(dir(builtins)) | {"__file__"}
+        for n in ast.walk(tree):
+            if isinstance(n, (ast.Import, ast.ImportFrom)):
+                bound.update((a.asname or a.name).split(".")[0] for a in n.names)
+            elif isinstance(n, (ast.FunctionDef, ast.AsyncFunctionDef, ast.Lambda)):
+                if not isinstance(n, ast.Lambda):
+                    bound.add(n.name)
+                a = n.args
+                bound.update(x.arg for x in a.args + a.kwonlyargs + a.posonlyargs)
+                bound.update(x.arg for x in (a.vararg, a.kwarg) if x)
+            elif isinstance(n, ast.ClassDef):
+                bound.add(n.name)
+            elif isinstance(n, ast.Name) and isinstance(n.ctx, (ast.Store, ast.Del)):
+                bound.add(n.id)
+            elif isinstance(n, ast.ExceptHandler) and n.name:
+                bound.add(n.name)
+        used = {n.id for n in ast.walk(tree) if isinstance(n, ast.Name) and isinstance(n.ctx, ast.Load)}
+        if used - bound:
+            bad[os.path.relpath(f, root)] = sorted(used - bound)
+    assert not bad, bad
