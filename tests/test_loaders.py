@@ -429,3 +429,42 @@ def test_decimal_fast_path_boundaries(lib_ready):
             want = np.asarray([float(t) for t in t3], dtype=np.float64).astype(np.float32)
         assert np.array_equal(blk["cont"].numpy().reshape(-1).view(np.uint32), want.view(np.uint32)), t3
         assert blk["cate"].numpy().reshape(-1).tolist() == [7, 8]
+
+
+def test_tf_example_fuzz_against_the_protobuf_runtime(tmp_path, lib_ready):
+    """random Examples serialised by google.protobuf (extra features of all three kinds, empty lists, values at the
+    int64 / float32 extremes) through the native reader: same rows as the official parser gives back"""
+    from hypothesis import given, settings, strategies as st
+    Example = _official_example_class()
+    C_, V, Fc = 3, 2, 4
+    d = str(tmp_path) + "/"
+    mp = _mp(alg_name="deepfm_pipeline", batch_size=1, epochs=1, cont_field_size=C_, vector_feats_size=V, cate_field_size=Fc)
+    f32 = st.floats(width=32, allow_nan=False)
+    i64 = st.integers(min_value=-2 ** 63, max_value=2 ** 63 - 1)
+    counter = [0]
+
+    @settings(max_examples=60, deadline=None)
+    @given(st.lists(f32, min_size=C_, max_size=C_), st.lists(f32, min_size=V, max_size=V), st.lists(i64, min_size=Fc, max_size=Fc),
+           st.sampled_from([0.0, 1.0]), st.lists(f32, max_size=3), st.lists(i64, max_size=3), st.lists(st.binary(max_size=5), max_size=2))
+    def check(cont, vec, cate, label, extra_f, extra_i, extra_b):
+        ex = Example()
+        ex.features.feature["zz_extra_f"].float_list.value.extend(extra_f)
+        ex.features.feature["cate_feats"].int64_list.value.extend(cate)
+        ex.features.feature["aa_extra_i"].int64_list.value.extend(extra_i)
+        ex.features.feature["label"].float_list.value.append(label)
+        ex.features.feature["vector_feats"].float_list.value.extend(vec)
+        ex.features.feature["extra_b"].bytes_list.value.extend(extra_b)
+        ex.features.feature["cont_feats"].float_list.value.extend(cont)
+        counter[0] += 1
+        path = d + "part-%d" % counter[0]
+        LO.write_tfrecord(path, [ex.SerializeToString()])
+        (b,) = list(L.pipeline_process(mp, [path], "predict", pin=False))
+        back = Example.FromString(ex.SerializeToString())
+        assert b["cate_feats"].numpy().reshape(-1).tolist() == list(back.features.feature["cate_feats"].int64_list.value)
+        want = np.asarray(list(back.features.feature["cont_feats"].float_list.value), dtype=np.float32)
+        assert np.array_equal(b["cont_feats"].numpy().reshape(-1).view(np.uint32), want.view(np.uint32))
+        want = np.asarray(list(back.features.feature["vector_feats"].float_list.value), dtype=np.float32)
+        assert np.array_equal(b["vector_feats"].numpy().reshape(-1).view(np.uint32), want.view(np.uint32))
+        assert float(b["label"].numpy().reshape(-1)[0]) == label
+        os.remove(path)
+    check()
