@@ -23,7 +23,11 @@ class EmbedCfg(C.Structure):
 
 class AdamHP(C.Structure):
     """mirror of `ctr_adam_hp`"""
-    _fields_ = [("lr_t", c_f32), ("beta1", c_f32), ("beta2", c_f32), ("eps", c_f32)]
+    _fields_ = [("lr_t", c_f32), ("beta1", c_f32), ("beta2", c_f32), ("eps", c_f32), ("c1", c_f32), ("c2", c_f32)]
+
+    def __init__(self, lr_t, beta1, beta2, eps, c1=None, c2=None):
+        # c1 = 1 - beta1, c2 = 1 - beta2 from the exact (double) betas, rounded once (see include/ctr_b200.h)
+        super().__init__(lr_t, beta1, beta2, eps, 1.0 - beta1 if c1 is None else c1, 1.0 - beta2 if c2 is None else c2)
 
 
 MAX_LAYERS = 8

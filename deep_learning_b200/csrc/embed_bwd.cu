@@ -237,8 +237,8 @@ adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restric
             const float D = seg_start ? sum_run_partials(grads, seg_start, u, emb_k + 1, gs) : grads[u * gs + emb_k + 1];
             g = fmaf(-fm_w2[j] * table[o], D, g);
         }
-        const float mm = hp.beta1 * m[o] + (1.f - hp.beta1) * g;
-        const float vv = hp.beta2 * v[o] + (1.f - hp.beta2) * g * g;
+        const float mm = hp.beta1 * m[o] + hp.c1 * g;
+        const float vv = hp.beta2 * v[o] + hp.c2 * g * g;
         m[o] = mm;
         v[o] = vv;
         table[o] -= hp.lr_t * mm / (sqrtf(vv) + hp.eps);
@@ -247,7 +247,7 @@ adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restric
 }
 
 __device__ __forceinline__ void adam4(float4& th, float4& mm, float4& vv, const float4 g, const ctr_adam_hp& hp) {
-    const float b1 = hp.beta1, b2 = hp.beta2, c1 = 1.f - hp.beta1, c2 = 1.f - hp.beta2;
+    const float b1 = hp.beta1, b2 = hp.beta2, c1 = hp.c1, c2 = hp.c2;
     mm.x = b1 * mm.x + c1 * g.x; mm.y = b1 * mm.y + c1 * g.y; mm.z = b1 * mm.z + c1 * g.z; mm.w = b1 * mm.w + c1 * g.w;
     vv.x = b2 * vv.x + c2 * g.x * g.x; vv.y = b2 * vv.y + c2 * g.y * g.y;
     vv.z = b2 * vv.z + c2 * g.z * g.z; vv.w = b2 * vv.w + c2 * g.w * g.w;
@@ -320,8 +320,8 @@ adam_rows_vec_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __res
         *reinterpret_cast<float4*>(v + o) = vv;
         *reinterpret_cast<float4*>(table + o) = th;
         if (first) {
-            m1 = hp.beta1 * m1 + (1.f - hp.beta1) * g1;
-            v1 = hp.beta2 * v1 + (1.f - hp.beta2) * g1 * g1;
+            m1 = hp.beta1 * m1 + hp.c1 * g1;
+            v1 = hp.beta2 * v1 + hp.c2 * g1 * g1;
             m[row * stride + K] = m1;
             v[row * stride + K] = v1;
             table[row * stride + K] = th1 - hp.lr_t * m1 / (sqrtf(v1) + hp.eps);
@@ -387,8 +387,8 @@ adam_rows_long_kernel(const uint32_t* __restrict__ row_ids, uint32_t mask, const
             float g = pick(j);
             const int64_t o = row * stride + j;
             if (fm_w2 && j < emb_k) g = fmaf(-fm_w2[j] * table[o], D, g);
-            const float mm = hp.beta1 * m[o] + (1.f - hp.beta1) * g;
-            const float vv = hp.beta2 * v[o] + (1.f - hp.beta2) * g * g;
+            const float mm = hp.beta1 * m[o] + hp.c1 * g;
+            const float vv = hp.beta2 * v[o] + hp.c2 * g * g;
             m[o] = mm;
             v[o] = vv;
             table[o] -= hp.lr_t * mm / (sqrtf(vv) + hp.eps);
@@ -406,8 +406,8 @@ adam_dense_kernel(float* __restrict__ theta, float* __restrict__ m, float* __res
         float gi = g ? g[i] : 0.f;
         if (l2 != 0.f) gi = fmaf(l2, th, gi);
         if (l1 != 0.f) gi += l1 * (th > 0.f ? 1.f : (th < 0.f ? -1.f : 0.f));
-        const float mm = hp.beta1 * m[i] + (1.f - hp.beta1) * gi;
-        const float vv = hp.beta2 * v[i] + (1.f - hp.beta2) * gi * gi;
+        const float mm = hp.beta1 * m[i] + hp.c1 * gi;
+        const float vv = hp.beta2 * v[i] + hp.c2 * gi * gi;
         m[i] = mm;
         v[i] = vv;
         theta[i] = th - hp.lr_t * mm / (sqrtf(vv) + hp.eps);
@@ -426,8 +426,8 @@ dense_update_kernel(float* __restrict__ theta, float* __restrict__ m, float* __r
         float gi = g[i];
         if (i >= lay.group_end[1]) gi += lay.reg_scale * (th > 0.f ? 1.f : (th < 0.f ? -1.f : 0.f));     // l1 group
         else if (i >= lay.group_end[0]) gi = fmaf(lay.reg_scale, th, gi);                                 // l2 group
-        const float mm = hp.beta1 * m[i] + (1.f - hp.beta1) * gi;
-        const float vv = hp.beta2 * v[i] + (1.f - hp.beta2) * gi * gi;
+        const float mm = hp.beta1 * m[i] + hp.c1 * gi;
+        const float vv = hp.beta2 * v[i] + hp.c2 * gi * gi;
         m[i] = mm;
         v[i] = vv;
         const float nt = th - hp.lr_t * mm / (sqrtf(vv) + hp.eps);
@@ -755,6 +755,7 @@ extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_id
                              uint8_t* touched, void* ws, int64_t ws_bytes, const float* fm_w2, int emb_k,
                              const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, row_ids && grads && table && m && v && hp, "adam_rows: null pointer");
+    CTR_REQUIRE(h, hp->c1 > 0.f && hp->c2 > 0.f, "adam_rows: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
     CTR_REQUIRE(h, width > 0 && grad_stride >= width && table_stride >= width && n_max >= 0 && table_rows > 0,
                 "adam_rows: bad sizes");
     CTR_REQUIRE(h, !fm_w2 || (emb_k > 0 && emb_k <= width && grad_stride >= emb_k + 2), "adam_rows: fm_w2 needs grad_stride >= emb_k + 2");
@@ -805,6 +806,7 @@ extern "C" int ctr_adam_rows_gathered(ctr_handle* h, ctr_stream s, const uint32_
                                       int src_stride, int width, float* table, float* m, float* v, int table_stride,
                                       int64_t table_rows, uint8_t* touched, const float* fm_w2, int emb_k, const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, row_ids && n_rows && src && perm && seg_start && table && m && v && hp, "adam_rows_gathered: null pointer");
+    CTR_REQUIRE(h, hp->c1 > 0.f && hp->c2 > 0.f, "adam_rows_gathered: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
     CTR_REQUIRE(h, n_max >= 0 && table_rows > 0 && (emb_k == 4 || emb_k == 8 || emb_k == 16 || emb_k == 32) &&
                        (width == emb_k || width == emb_k + 1) && table_stride % 4 == 0 && table_stride >= width &&
                        src_stride % 4 == 0 && src_stride >= width + (fm_w2 ? (emb_k + 2 - width) : 0),
@@ -832,6 +834,7 @@ extern "C" int ctr_adam_rows_gathered(ctr_handle* h, ctr_stream s, const uint32_
 extern "C" int ctr_adam_dense(ctr_handle* h, ctr_stream s, float* theta, float* m, float* v, const float* g, int64_t n,
                               float l2, float l1, uint8_t* skip, int skip_group, const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, theta && m && v && hp && n >= 0 && (!skip || skip_group > 0), "adam_dense: bad args");
+    CTR_REQUIRE(h, hp->c1 > 0.f && hp->c2 > 0.f, "adam_dense: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
     if (n == 0) return CTR_OK;
     adam_dense_kernel<<<grid_for(h, n), 256, 0, ctr_st(s)>>>(theta, m, v, g, n, l2, l1, skip, skip_group, *hp);
     CTR_CHECK_LAUNCH(h, "adam_dense");
@@ -846,6 +849,7 @@ extern "C" int ctr_adam_dense(ctr_handle* h, ctr_stream s, float* theta, float* 
 extern "C" int ctr_dense_update(ctr_handle* h, ctr_stream s, float* theta, float* m, float* v, const float* g,
                                 const ctr_dense_layout* lay, const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, theta && m && v && g && lay && hp, "dense_update: null pointer");
+    CTR_REQUIRE(h, hp->c1 > 0.f && hp->c2 > 0.f, "dense_update: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
     CTR_REQUIRE(h, lay->group_end[0] >= 0 && lay->group_end[0] <= lay->group_end[1] && lay->group_end[1] <= lay->group_end[2] &&
                        lay->n_layers >= 0 && lay->n_layers <= CTR_MAX_LAYERS, "dense_update: bad layout");
     for (int l = 0; l < lay->n_layers; ++l)

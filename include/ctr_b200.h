@@ -292,7 +292,11 @@ int ctr_segment_sum_rows(ctr_handle* h, ctr_stream s, const uint32_t* seg_start,
  * fm_w2 ([emb_k] second-order head weights, or NULL): g[j] -= fm_w2[j] * theta[j] * grads[u, emb_k + 1] for j < emb_k
  * before the update (the e-term ctr_embed_bwd_partials leaves out).  emb_k > 0 with width == emb_k (+1) selects the
  * 128-bit row kernel; emb_k = 0: generic width. */
-typedef struct ctr_adam_hp { float lr_t, beta1, beta2, eps; } ctr_adam_hp;
+/* c1 = 1 - beta1 and c2 = 1 - beta2 are passed in, rounded ONCE from the exact values: formed on the device as
+ * 1.f - 0.999f they would be 0.00099998713 (1.3e-5 low), which scales v by the same factor and -- because lr_t's own
+ * sqrt(1 - beta2^t) is computed exactly on the host -- leaves a systematic 6.5e-6 * lr drift per step (TensorFlow's
+ * float32 kernel makes the same rounding in BOTH places, where it cancels).  Entry points reject c1 <= 0 or c2 <= 0. */
+typedef struct ctr_adam_hp { float lr_t, beta1, beta2, eps, c1, c2; } ctr_adam_hp;
 int64_t ctr_adam_rows_ws_bytes(ctr_handle* h, int64_t n_max);
 int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
                   int local_bits, const float* grads, const uint32_t* seg_start /* non-NULL: `grads` is the

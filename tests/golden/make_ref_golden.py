@@ -275,11 +275,38 @@ def run_text_model(alg, hp, mod, args, batches, val):
     return rec.init_snap, losses, [np.concatenate([np.asarray(e[1]).ravel(), [e[2]]]) for e in evals], allb[:src.n_pulled], []
 
 
+def generate_fp32_floor(alg):
+    """The SAME run with the stand-in computing in float32 (TF's arithmetic type), from the same initial variables and
+    batches: how far float32 arithmetic itself lands from the float64 fixture.  tests/golden/fp32floor_<model>.npz holds
+    only the results (losses, evaluations, final variables); tests/test_ref_gpu.py reports the CUDA path's distance to
+    the float64 fixture next to this floor."""
+    assert S.F is torch.float32, "run with TF1_SHIM_FLOAT=float32"
+    out = run_reference(alg, G.tiny_hp(alg))
+    z = np.load(os.path.join(HERE, "ref_%s.npz" % alg))
+    for k in z.files:                          # same run: identical initial variables (after float32 rounding) and batches
+        if k.startswith(("init/", "train", "val")) and z[k].dtype.kind in "fi":
+            assert np.array_equal(np.asarray(out[k], dtype=np.float32), z[k].astype(np.float32)), (alg, k)
+    assert str(out["events"]) == str(z["events"])
+    keep = {k: np.asarray(v, dtype=np.float64) for k, v in out.items()
+            if k.startswith(("final/", "eval")) or k == "losses"}
+    path = os.path.join(HERE, "fp32floor_%s.npz" % alg)
+    np.savez_compressed(path, **keep)
+    worst = max(float(np.max(np.abs(keep[k] - z[k])) / max(float(np.max(np.abs(z[k]))), 1e-30))
+                for k in keep if k.startswith("final/"))
+    print("%-20s %6d bytes  worst final-variable deviation of float32 from the float64 fixture: %.2e" % (
+        alg, os.path.getsize(path), worst))
+
+
 def main():
     if not os.path.isdir(REF):
         raise SystemExit("needs /root/reference (build container only); the committed ref_*.npz are its outputs")
     S.install()
-    for alg in (sys.argv[1:] or FEED + PIPE + TEXT):
+    argv = [a for a in sys.argv[1:] if a != "--fp32-floor"]
+    if "--fp32-floor" in sys.argv[1:]:         # TF1_SHIM_FLOAT=float32 python tests/golden/make_ref_golden.py --fp32-floor
+        for alg in (argv or FEED + PIPE + TEXT):
+            generate_fp32_floor(alg)
+        return
+    for alg in (argv or FEED + PIPE + TEXT):
         generate(alg)
 
 

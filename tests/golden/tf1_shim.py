@@ -24,7 +24,11 @@ import types
 import numpy as np
 import torch
 
-F = torch.float64
+# arithmetic type of the stand-in: float64 (the fixtures; order-free truth) or, with TF1_SHIM_FLOAT=float32, TF's own
+# float32 -- used ONLY to measure how far float32 arithmetic itself drifts from the float64 fixtures (the "fp32 floor"
+# recorded beside them by make_ref_golden.py)
+import os as _os
+F = torch.float32 if _os.environ.get("TF1_SHIM_FLOAT", "float64") == "float32" else torch.float64
 
 
 class _DType:
@@ -227,12 +231,12 @@ def _to_torch(v, dtype=None):
         t = v
     else:
         a = np.asarray(v)
-        if a.dtype == np.float32:
+        if a.dtype == np.float32 and F is torch.float64:
             a = a.astype(np.float64)          # exact
         t = torch.from_numpy(np.ascontiguousarray(a)) if a.shape else torch.tensor(a.item(), dtype=F if a.dtype.kind == 'f' else torch.int64)
     if dtype is not None:
         t = t.to(dtype.tt)
-    elif t.dtype in (torch.float32, torch.float16):
+    elif t.is_floating_point() and t.dtype != F:
         t = t.to(F)
     elif t.dtype in (torch.int32, torch.int16, torch.int8, torch.uint8):
         t = t.to(torch.int64)
@@ -428,13 +432,13 @@ def _shape_static(shape):
 
 def random_normal(shape, mean=0.0, stddev=1.0, dtype=None, seed=None, name=None):
     gen = _generator()
-    return Tensor(lambda ctx: torch.randn(_int_list(ctx, shape), generator=gen, dtype=F) * stddev + mean, (),
+    return Tensor(lambda ctx: (torch.randn(_int_list(ctx, shape), generator=gen, dtype=torch.float64) * stddev + mean).to(F), (),
                   name=name, dtype=float32, shape=_shape_static(shape))
 
 
 def random_uniform(shape, minval=0.0, maxval=1.0, dtype=None, seed=None, name=None):
     gen = _generator()
-    return Tensor(lambda ctx: torch.rand(_int_list(ctx, shape), generator=gen, dtype=F) * (maxval - minval) + minval,
+    return Tensor(lambda ctx: (torch.rand(_int_list(ctx, shape), generator=gen, dtype=torch.float64) * (maxval - minval) + minval).to(F),
                   (), name=name, dtype=float32, shape=_shape_static(shape))
 
 

@@ -1,7 +1,15 @@
 """-m gpu: the CUDA path against runs of the reference's own model files (tests/golden/ref_<model>.npz, see
 tests/test_ref_golden.py for how they were made): same initial variables, the train steps and evaluations of the
-reference's `fit` replayed in its order over its batches, FP32 path, TF1 dense Adam.  Bars: every step's loss and
-every evaluation output 1e-5, final variables 2e-5 relative to the tensor's scale (BASELINE.json)."""
+reference's `fit` replayed in its order over its batches, FP32 path, TF1 dense Adam, FREE-RUNNING (no re-injection
+between steps).  Bars: every step's loss, every evaluation output and every final variable 1e-5 relative to the
+tensor's scale (BASELINE.json's FP32 tolerance, unrelaxed).
+
+Beside the bar, the float32 floor: tests/golden/fp32floor_<model>.npz hold the SAME reference runs with the stand-in
+computing in float32 (TF's arithmetic type; `make_ref_golden.py --fp32-floor`).  Their distance to the float64
+fixtures is what float32 arithmetic costs by itself (1e-7 .. 8e-7 on the final variables); the CUDA path must stay
+within FLOOR_FACTOR of it (or under ABS_FLOOR where the floor is only the final rounding), so a systematic error far
+above float32 noise -- round 1's `1.f - 0.999f` in the Adam kernels was 55x the floor -- fails even when it is under
+1e-5.  `tools/parity_report.py` prints the measured table (committed under profiles/)."""
 import os
 
 import numpy as np
@@ -14,34 +22,39 @@ from test_ref_golden import ALGS, HERE, LOGIT_EVAL
 
 pytestmark = pytest.mark.gpu
 
+BAR = 1e-5                # BASELINE.json, FP32 path
+FLOOR_FACTOR = 8.0        # two float32 implementations with different summation orders: a few times the floor
+ABS_FLOOR = 2e-6          # where the float32 floor is only the final rounding (1e-8 .. 1e-7)
+
 
 def _batch(z, prefix):
     return {k.split("/", 1)[1]: torch.from_numpy(z[k]) for k in z.files if k.startswith(prefix + "/")}
 
 
-# SplitFmEngine has run on a GPU at k=16 / 256-128 towers only (tests/test_gpu_parity.py); the fixture's k=4 shape had no
-# GPU run when this file was written (the round's GPU budget was spent), so that one case may not fail the suite yet
-_CASES = [pytest.param(a, marks=pytest.mark.xfail(reason="first GPU run of SplitFmEngine at k=4", strict=False))
-          if a == "deepfm_pipeline" else a for a in ALGS]
+def _rel(a, ref):
+    a, ref = np.asarray(a, np.float64).reshape(-1), np.asarray(ref, np.float64).reshape(-1)
+    return float(np.max(np.abs(a - ref)) / max(1.0, float(np.max(np.abs(ref)))))
 
 
-@pytest.mark.parametrize("alg", _CASES)
-def test_cuda_reproduces_the_reference_run(alg):
+def replay(alg, precision="fp32", adam_mode="tf_dense"):
+    """-> [(what, err, floor)]: the CUDA path's and the float32 stand-in's distance to the float64 fixture"""
     from deep_learning_b200.engine import CtrEngine
     from deep_learning_b200.spec import spec_from_hparams
     z = np.load(os.path.join(HERE, "golden", "ref_%s.npz" % alg))
+    zf = np.load(os.path.join(HERE, "golden", "fp32floor_%s.npz" % alg))
     hp = tiny_hp(alg)
     spec = spec_from_hparams(alg, hp)
     cls = CtrEngine
     if spec.split_fm:
         from deep_learning_b200.split_engine import SplitFmEngine as cls
     eng = cls(spec, hp.batch_size, learning_rate=hp.learning_rate, decay_steps=hp.learning_rate_decay_steps,
-              decay_rate=hp.learning_rate_decay_rate, precision="fp32", adam_mode="tf_dense")
+              decay_rate=hp.learning_rate_decay_rate, precision=precision, adam_mode=adam_mode)
     eng.set_weights({k[5:]: z[k].astype(np.float32) for k in z.files if k.startswith("init/")})
     family, events, n_val = str(z["family"]), str(z["events"]), int(z["n_val"])
     B = hp.batch_size
     t = e = pulled = 0
     ntb = len([k for k in z.files if k.startswith("train") and k.endswith("/label")])
+    rows = []
     for ev in events:
         if family == "text":
             b = _batch(z, "train%d" % pulled)
@@ -52,7 +65,8 @@ def test_cuda_reproduces_the_reference_run(alg):
             b = _batch(z, "val%d" % (e % n_val))
         if ev == "T":
             loss, ref = float(eng.train_step(b).item()), float(z["losses"][t])
-            assert abs(loss - ref) < 1e-5 * max(1.0, abs(ref)), (alg, t, loss, ref)
+            rows.append(("loss step %d" % t, abs(loss - ref) / max(1.0, abs(ref)),
+                         abs(float(zf["losses"][t]) - ref) / max(1.0, abs(ref))))
             t += 1
         else:
             ref = z["eval%d" % e].reshape(-1)
@@ -64,8 +78,18 @@ def test_cuda_reproduces_the_reference_run(alg):
                 got = eng.logit[:B].cpu().numpy()
             else:
                 got = eng.predict(b).cpu().numpy()
-            assert got.shape == ref.shape and np.max(np.abs(got - ref)) < 1e-5 * max(1.0, float(np.max(np.abs(ref)))), (alg, e)
+            assert got.shape == ref.shape, (alg, e)
+            rows.append(("eval %d" % e, _rel(got, ref), _rel(zf["eval%d" % e], ref)))
             e += 1
     got = eng.get_weights()
     for k in [k[6:] for k in z.files if k.startswith("final/")]:
-        assert H.rel_err(got[k].reshape(-1), z["final/" + k].reshape(-1)) < 2e-5, (alg, k)
+        ref = z["final/" + k].reshape(-1)
+        rows.append(("final " + k, H.rel_err(got[k].reshape(-1), ref), H.rel_err(zf["final/" + k].reshape(-1), ref)))
+    return rows
+
+
+@pytest.mark.parametrize("alg", ALGS)
+def test_cuda_reproduces_the_reference_run(alg):
+    for what, err, floor in replay(alg):
+        assert err < BAR, (alg, what, err, floor)
+        assert err <= max(FLOOR_FACTOR * floor, ABS_FLOOR), (alg, what, err, floor)

@@ -5,7 +5,8 @@ set -x
 mkdir -p gpurun_out
 N=${1:-1}
 if [ "$N" = "1" ]; then
-  python -m pytest tests -m gpu -q > gpurun_out/pytest.log 2>&1; echo "pytest rc $?" >> gpurun_out/pytest.log
+  python -m pytest tests -m gpu -q -s > gpurun_out/pytest.log 2>&1; echo "pytest rc $?" >> gpurun_out/pytest.log
+  timeout 300 python tools/parity_report.py > gpurun_out/parity_report.txt 2>&1
   timeout 300 python bench.py --steps 30 --warmup 5 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err
   timeout 200 python tests/phase_timing.py > gpurun_out/phases_n1.txt 2>&1
   # A/B knobs that are in the tree but default off
