@@ -40,8 +40,72 @@ def peaks():
     return 6650.0, 1400.0, "fallback"
 
 
+class NvmlClockSampler:
+    """SM clock / throttle reasons through NVML, every ~2 ms from a thread, plus one synchronous sample at each end of
+    the timed region (the driver's 20-step region lasts ~20 ms: a 100 ms nvidia-smi poll cannot land inside it)."""
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
+
+    def __init__(self, index: int):
+        import pynvml
+        self.nv = pynvml
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:                                    # NVML counts physical devices; CUDA_VISIBLE_DEVICES may renumber them
+            try:
+                index = int(vis.split(",")[index])
+            except ValueError:
+                pass
+        self.dev = pynvml.nvmlDeviceGetHandleByIndex(index)
+        self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.dev, pynvml.NVML_CLOCK_SM))
+        self.rows, self.on = [], False
+        self.t = None
+
+    def sample(self):
+        nv = self.nv
+        try:
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.dev)
+        except Exception:
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.dev)
+        self.rows.append((time.time(), float(nv.nvmlDeviceGetClockInfo(self.dev, nv.NVML_CLOCK_SM)), int(r)))
+
+    def start(self):
+        self.on = True
+        self.sample()
+
+        def loop():
+            while self.on:
+                self.sample()
+                time.sleep(0.002)
+        self.t = threading.Thread(target=loop, daemon=True)
+        self.t.start()
+
+    def stop(self, t0, t1):
+        self.sample()
+        self.on = False
+        self.t.join(timeout=1.0)
+        rows = [r for r in self.rows if t0 <= r[0] <= t1 + 0.005] or self.rows[-1:]
+        sm = sorted(r[1] for r in rows)
+        bits = 0
+        for r in rows:
+            bits |= r[2]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.mx, "reasons": [n for n, b in self.REASONS if bits & b],
+                "samples": len(rows), "how": "NVML, sampled during the timed region"}
+
+
+def clock_sampler(index: int):
+    try:
+        c = NvmlClockSampler(index)
+        return c
+    except Exception:
+        return ClockSampler(index)
+
+
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region"""
+    """fallback: nvidia-smi clocks / throttle reasons sampled DURING the timed region"""
+
+    def start(self):
+        pass
+
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -86,7 +150,7 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_reference_arm(steps, warmup, batch=4096, rows=2_000_000):
+def cpu_reference_arm(steps, warmup, batch=4096, rows=2_000_000, adam_mode="tf_dense"):
     """The reference's CPU path, restated (oracle, fp32, all host threads): one train step =
     forward + log-loss + autodiff + TF1 dense Adam over the whole table, on a bounded sample of the
     workload (same field shapes; batch and table rows reduced so the run ends in tens of seconds)."""
@@ -100,14 +164,16 @@ def cpu_reference_arm(steps, warmup, batch=4096, rows=2_000_000):
     st = O.adam_init(p)
     batches = [H.oracle_batch(H.make_batch("deepfm", hp, seed=2020 + i), torch.float32) for i in range(2)]
     for i in range(warmup):
-        _, p = O.train_step("deepfm", p, st, batches[i % 2], hp)
+        _, p = O.train_step("deepfm", p, st, batches[i % 2], hp, adam_mode=adam_mode)
     t0 = time.perf_counter()
     for i in range(steps):
-        _, p = O.train_step("deepfm", p, st, batches[i % 2], hp)
+        _, p = O.train_step("deepfm", p, st, batches[i % 2], hp, adam_mode=adam_mode)
     dt = time.perf_counter() - t0
-    return {"value": batch * steps / dt, "unit": UNIT, "cores": cores, "kind": "port",
+    return {"value": batch * steps / dt, "unit": UNIT, "cores": cores, "kind": "port", "adam_mode": adam_mode,
             "sample": "oracle fp32 (PyTorch-CPU restatement of models/deepfm.py; TensorFlow 1.x not installable), "
-                      "%d steps of batch %d, table %d rows, TF1 dense Adam" % (steps, batch, rows),
+                      "%d steps of batch %d, table %d rows, %s" % (
+                          steps, batch, rows, "TF1 dense Adam (the reference's semantics: every row moves every step)"
+                          if adam_mode == "tf_dense" else "lazy Adam (touched rows only: the GPU arm's headline mode)"),
             "ms_per_step": dt / steps * 1e3}
 
 
@@ -122,6 +188,8 @@ def main():
     ap.add_argument("--precision", default=os.environ.get("CTR_PRECISION", "tf32"))
     ap.add_argument("--dist", default="zipf")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--adam-mode", default="lazy", choices=("lazy", "tf_dense"))
+    ap.add_argument("--no-extras", action="store_true", help="skip the untimed sub-records (fp32, tf_dense, sustained, TF32 peak)")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -133,7 +201,7 @@ def main():
         # exactly the K steps and W warm-ups asked for (one step of the sample is ~0.15 s on 16 cores); K capped at 200
         k_run, w_run = max(1, min(a.steps, 200)), max(1, min(a.warmup, 10))
         cb = cpu_reference_arm(k_run, w_run)
-        line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus,
+        line = {"impl": "reference", "adam_mode": "tf_dense", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": a.gpus,
                 "steps": k_run, "warmup": w_run, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": "DeepFM Criteo-shape 13 cont + 26 cate k=16 MLP 400x3 (CPU sample: " + cb["sample"] + ")"},
@@ -144,7 +212,6 @@ def main():
 
     import torch
     import torch.distributed as dist
-    import ctr_helpers as H
     from deep_learning_b200 import data as D
     from deep_learning_b200.engine import CtrEngine
     from deep_learning_b200.models._base import init_weights
@@ -157,16 +224,16 @@ def main():
     hp = hparams(B, R)
     spec = spec_from_hparams("deepfm", hp)
     if world > 1:
-        # keep stdout to the one JSON line: NCCL prints its version banner there at VERSION level and above
-        os.environ.pop("NCCL_DEBUG", None)
-        if os.environ.get("CTR_NCCL_DEBUG"):
-            os.environ["NCCL_DEBUG"] = os.environ["CTR_NCCL_DEBUG"]
+        # stdout carries the one JSON line: NCCL's log (version banner, communicator / nranks lines at INFO) goes to
+        # stderr instead of being switched off
+        if os.environ.get("NCCL_DEBUG") and not os.environ.get("NCCL_DEBUG_FILE"):
+            os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
         # configs[3]: the ~1e8-row tables row-sharded over the ranks (owner = id mod N), B samples per GPU (weak scaling)
         dist.init_process_group("nccl", device_id=dev)
         from deep_learning_b200.sharded import ShardedCtrEngine
-        eng = ShardedCtrEngine(spec, B, device=dev, learning_rate=hp.learning_rate, precision=a.precision, adam_mode="lazy")
+        eng = ShardedCtrEngine(spec, B, device=dev, learning_rate=hp.learning_rate, precision=a.precision, adam_mode=a.adam_mode)
     else:
-        eng = CtrEngine(spec, B, device=dev, learning_rate=hp.learning_rate, precision=a.precision, adam_mode="lazy")
+        eng = CtrEngine(spec, B, device=dev, learning_rate=hp.learning_rate, precision=a.precision, adam_mode=a.adam_mode)
     eng.init_table_on_device(seed=2019)
     eng.set_dense_weights(init_weights(spec, 2019, with_table=False))     # same seed on every rank: replicas start equal
 
@@ -197,9 +264,10 @@ def main():
     sync()
     eng.h.timers = {"ctr_fm_gather_fwd": []}      # the roofline kernel is timed inside the timed region (one event pair per step)
     l0 = eng.h.launches
-    clocks = ClockSampler(local)
+    clocks = clock_sampler(local)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync()
+    clocks.start()
     t0 = time.time()
     torch.cuda.profiler.start()      # `ncu --profile-from-start off` captures exactly the timed steps
     e0.record()
@@ -217,8 +285,9 @@ def main():
     # ---- per-kernel table: the same steps again with a CUDA event pair around each selected entry point, on the stream
     # it launches on.  Kept out of the timed region above (only the roofline kernel is timed there): ~60 extra event
     # records per step are host work, and the multi-GPU step is close to host-bound.
-    timed = ("ctr_fm_gather_fwd", "ctr_embed_bwd_partials", "ctr_adam_rows", "ctr_sort_ids", "ctr_mlp_fwd",
-             "ctr_mlp_bwd_data", "ctr_mlp_bwd_weight")
+    timed = ("ctr_fm_gather_fwd", "ctr_embed_bwd_partials_weighted", "ctr_adam_rows", "ctr_adam_rows_gathered",
+             "ctr_sort_ids", "ctr_unique_segments", "ctr_mlp_fwd", "ctr_mlp_bwd_data", "ctr_mlp_bwd_weight", "ctr_head_fwd",
+             "ctr_fm_cont_bwd", "ctr_dense_update", "ctr_gather_rows_push", "ctr_embed_bwd_finalize_push", "ctr_peer_barrier")
     eng.h.timers = {n: [] for n in timed}
     for i in range(a.steps):
         eng.train_step(dev_batches[i % NB], next_batch=dev_batches[(i + 1) % NB])
@@ -238,6 +307,74 @@ def main():
     e1.record()
     sync()
     e2e_ms = max_over_ranks(e0.elapsed_time(e1))
+
+    layer_dims, table_gb = eng._layer_dims(), eng.table.numel() * 4 / 1e9
+    exch = ({"unique_rows_requested_rank0": int(eng.U), "rows_served_rank0": int(eng.n_req),
+             "wire_bytes_per_row": 4 + 2 * 4 * eng.wire} if world > 1 else None)
+
+    # ---- untimed sub-records (one GPU only): the regimes BASELINE.md section 4 lists beside the headline --------------
+    extras = {}
+    if world == 1 and not a.no_extras:
+        def timed_steps(engine, batches, steps, warm=3, k1=False):
+            for i in range(warm):
+                engine.train_step(batches[i % len(batches)], next_batch=batches[(i + 1) % len(batches)])
+            sync()
+            engine.h.timers = {"ctr_fm_gather_fwd": []} if k1 else None
+            x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            x0.record()
+            for i in range(steps):
+                engine.train_step(batches[i % len(batches)], next_batch=batches[(i + 1) % len(batches)])
+            x1.record()
+            sync()
+            ev = engine.h.timers["ctr_fm_gather_fwd"] if k1 else []
+            engine.h.timers = None
+            t = x0.elapsed_time(x1) / steps
+            return t, (sum(x.elapsed_time(y) for x, y in ev) / len(ev) if ev else None)
+
+        # (a) the same loop for >= 3 s: clocks settle under the power cap (the 20-step region above runs at burst clocks)
+        n_sus = max(int(3000.0 / (ms / a.steps)), a.steps)
+        cs = clock_sampler(local)
+        cs.start()
+        ts0 = time.time()
+        t_sus, _ = timed_steps(eng, dev_batches, n_sus, warm=0)
+        extras["sustained"] = {"value": B / (t_sus * 1e-3), "unit": UNIT, "ms_per_step": t_sus, "steps": n_sus,
+                               "clocks": cs.stop(ts0, time.time())}
+        # (b) uniform ids: no duplicates inside a batch, every row read misses L2 -- the regime where K1 is an HBM test
+        ub = [D.synthetic_batch(B, spec.C, spec.Fc, sizes, seed=3020 + i, dist="uniform", device=dev) for i in range(NB)]
+        t_u, k1_u = timed_steps(eng, ub, 10, k1=True)
+        extras["uniform_ids"] = {"value": B / (t_u * 1e-3), "unit": UNIT, "ms_per_step": t_u, "k1_ms": k1_u,
+                                 "unique_rows_last_step": int(eng.n_unique.item())}
+        del ub
+        # (c) TF32 GEMM rate of the library GEMM on this GPU (cuBLAS through torch.matmul, allow_tf32), burst: the
+        # denominator of mlp.frac -- MEASURED_PEAKS.json holds bf16 only
+        torch.backends.cuda.matmul.allow_tf32 = True
+        ga, gb = torch.randn(8192, 8192, device=dev), torch.randn(8192, 8192, device=dev)
+        best = 1e9
+        for i in range(8):
+            x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            x0.record()
+            gc = ga @ gb
+            x1.record()
+            torch.cuda.synchronize(dev)
+            if i >= 2:
+                best = min(best, x0.elapsed_time(x1))
+        extras["tf32_gemm_peak_tflops"] = 2 * 8192 ** 3 / (best * 1e-3) / 1e12
+        del ga, gb, gc
+    if world == 1 and not a.no_extras:
+        # (d) the reference's arithmetic type and (e) its optimizer semantics, on the same workload
+        host_w = init_weights(spec, 2019, with_table=False)
+        del eng
+        torch.cuda.empty_cache()
+        for key, prec, mode, steps in (("fp32", "fp32", a.adam_mode, 10), ("tf_dense", a.precision, "tf_dense", 5)):
+            e2 = CtrEngine(spec, B, device=dev, learning_rate=hp.learning_rate, precision=prec, adam_mode=mode)
+            e2.init_table_on_device(seed=2019)
+            e2.set_dense_weights(host_w)
+            t2, _ = timed_steps(e2, dev_batches, steps, warm=3)
+            extras[key] = {"value": B / (t2 * 1e-3), "unit": UNIT, "ms_per_step": t2, "steps": steps,
+                           "mlp_precision": prec, "adam_mode": mode}
+            del e2
+            torch.cuda.empty_cache()
+        eng = None
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -263,36 +400,50 @@ def main():
     for n, (avg, cnt) in kern.items():
         per_step = avg * cnt / a.steps
         kernels[n] = {"ms_per_call": round(avg, 4), "calls_per_step": cnt / a.steps, "share_of_step": round(per_step / step_ms, 4)}
-    mlp_flops = 3 * 2 * sum(k_ * h_ for k_, h_ in eng._layer_dims()) * B
+    mlp_flops = 3 * 2 * sum(k_ * h_ for k_, h_ in layer_dims) * B
     mlp_ms = sum(kern[n][0] * kern[n][1] for n in ("ctr_mlp_fwd", "ctr_mlp_bwd_data", "ctr_mlp_bwd_weight")) / a.steps
+    tf32_peak = extras.get("tf32_gemm_peak_tflops")
+    mlp_tfl = mlp_flops / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else None
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": W,
+        "metric": METRIC, "adam_mode": a.adam_mode, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": W,
         "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if a.precision == "fp32" else "tf32", "data": "synthetic",
         "config": {"workload": "DeepFM Criteo-shape: 13 cont + 26 single-valued cate, k=16, MLP 400-400-400, "
-                               "batch %d per GPU, table %d rows x (16+1) f32%s, ids %s, Adam lazy (touched rows)"
+                               "batch %d per GPU, table %d rows x (16+1) f32%s, ids %s, Adam %s"
                                % (B, R, " row-sharded over %d GPUs (ids / vectors / gradients / dense-gradient sum exchanged through NVLink peer memory, "
                                   "no collective in the step)" % world
-                                  if world > 1 else "", a.dist),
+                                  if world > 1 else "", a.dist,
+                                  "lazy (touched rows only; not the reference's semantics, see tf_dense sub-record)"
+                                  if a.adam_mode == "lazy" else "tf_dense (TF1 semantics: every row moves every step)"),
                    "batch_per_gpu": B, "global_batch": B * world, "parallelism": "dp%d+rowshard%d" % (world, world) if world > 1 else "single",
                    "table_rows": R, "unique_rows_last_step": n_unique, "mlp_precision": a.precision,
                    "l2_flush": "working set per step (~0.9 GB activations + random rows of a %.1f GB table) >> 126 MB L2; "
-                               "%d rotating batches" % (eng.table.numel() * 4 / 1e9, NB)},
+                               "%d rotating batches" % (table_gb, NB)},
         "clocks": clk,
         "e2e": {"value": world * B * a.steps / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": 4 * world},
         "gpu_launches": int(launches),
         "roofline": {"kernel": "fm_gather_fast_kernel<16,true,false> (ctr_fm_gather_fwd)", "bound": "hbm", "achieved": k1_gbs, "peak": hbm,
                      "unit": "GB/s", "frac": k1_gbs / hbm, "traffic": traffic, "peak_source": which,
                      "algorithmic_bytes_per_launch": k1_bytes},
-        "mlp": {"achieved_tflops": mlp_flops / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else None, "ms_per_step": mlp_ms},
+        "mlp": {"achieved_tflops": mlp_tfl, "ms_per_step": mlp_ms, "bound": "tensor (TF32) / HBM for the fp32 activations",
+                "peak_tflops": tf32_peak, "peak_source": "cuBLAS TF32 8192^3 through torch.matmul, measured in this run (burst)",
+                "frac": (mlp_tfl / tf32_peak) if (mlp_tfl and tf32_peak) else None},
         "kernels": kernels,
     }
-    if world > 1:
-        line["exchange"] = {"unique_rows_requested_rank0": int(eng.U), "rows_served_rank0": int(eng.n_req),
-                            "wire_bytes_per_row": 4 + 2 * 4 * eng.wire}
+    for k in ("sustained", "uniform_ids", "fp32", "tf_dense"):
+        if k in extras:
+            line[k] = extras[k]
+    if "uniform_ids" in extras and extras["uniform_ids"]["k1_ms"]:
+        u = extras["uniform_ids"]
+        u["k1_achieved_gbs"] = k1_bytes / (u["k1_ms"] * 1e-3) / 1e9
+        u["k1_frac"] = u["k1_achieved_gbs"] / hbm
+    if exch is not None:
+        line["exchange"] = exch
     if not a.no_cpu_baseline and world == 1:
         cb = cpu_reference_arm(60, 2)          # ~10 s of CPU work on the box's host cores
-        line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "adam_mode")}
+        cl = cpu_reference_arm(60, 2, adam_mode="lazy")      # like for like with the GPU arm's lazy Adam
+        line["cpu_baseline_lazy"] = {k: cl[k] for k in ("value", "unit", "cores", "kind", "sample", "adam_mode")}
     print(json.dumps(line))
     if world > 1:
         dist.barrier()

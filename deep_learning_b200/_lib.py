@@ -18,16 +18,23 @@ class EmbedCfg(C.Structure):
     """mirror of `ctr_embed_cfg` (include/ctr_b200.h)"""
     _fields_ = [(n, c_i32) for n in (
         "B", "id_bytes", "ids_ld", "Fc", "Fm", "M", "C", "V", "k", "has_first", "use_fm", "fm_cont",
-        "zero_row0", "count_rule", "combiner", "table_stride", "x0_ld", "fm_ld", "grad_stride", "round_tf32")]
+        "zero_row0", "count_rule", "combiner", "table_stride", "x0_ld", "fm_ld", "grad_stride", "round_tf32",
+        "reserved0")] + [("table_rows", c_i64), ("status", c_vp)]
+
+
+STATUS_WORDS = 4          # CTR_STATUS_WORDS: [step barrier, plan barrier, bad id, spare]
 
 
 class AdamHP(C.Structure):
     """mirror of `ctr_adam_hp`"""
-    _fields_ = [("lr_t", c_f32), ("beta1", c_f32), ("beta2", c_f32), ("eps", c_f32), ("c1", c_f32), ("c2", c_f32)]
+    _fields_ = [("lr_t", c_f32), ("beta1", c_f32), ("beta2", c_f32), ("eps", c_f32), ("c1", c_f32), ("c2", c_f32),
+                ("guard", c_vp)]
 
-    def __init__(self, lr_t, beta1, beta2, eps, c1=None, c2=None):
-        # c1 = 1 - beta1, c2 = 1 - beta2 from the exact (double) betas, rounded once (see include/ctr_b200.h)
-        super().__init__(lr_t, beta1, beta2, eps, 1.0 - beta1 if c1 is None else c1, 1.0 - beta2 if c2 is None else c2)
+    def __init__(self, lr_t, beta1, beta2, eps, c1=None, c2=None, guard=None):
+        # c1 = 1 - beta1, c2 = 1 - beta2 from the exact (double) betas, rounded once (see include/ctr_b200.h);
+        # guard: device pointer of the engine's status words (the update is skipped while they report a fault)
+        super().__init__(lr_t, beta1, beta2, eps, 1.0 - beta1 if c1 is None else c1, 1.0 - beta2 if c2 is None else c2,
+                         guard)
 
 
 MAX_LAYERS = 8
@@ -70,7 +77,7 @@ _PROTOS = {
     "ctr_table_unpack": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp]),
     "ctr_pooled_gather_fwd": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "ctr_fm_gather_fwd": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
-    "ctr_scalar_gather_sum": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp]),
+    "ctr_scalar_gather_sum": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i64, c_vp, c_vp]),
     "ctr_mlp_fwd": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp, c_vp, c_i32, c_f32,
                             c_u64, c_vp, c_i64]),
     "ctr_mlp_bwd_data": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp, c_i64, c_f32,
@@ -89,7 +96,7 @@ _PROTOS = {
     "ctr_reduce": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64]),
     "ctr_sort_ws_bytes": (c_i64, [c_vp, c_i64]),
     "ctr_sort_ids": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_i32, c_i32, c_i64, c_i32, c_i64, c_i32,
-                             c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64]),
+                             c_i32, c_i32, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp, c_i64]),
     "ctr_sort_pairs": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_i64]),
     "ctr_unique_segments": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
     "ctr_shard_counts": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp]),
@@ -156,7 +163,7 @@ def load(path: str = LIB_PATH) -> C.CDLL:
         fn.restype = res
         if args is not None:
             fn.argtypes = args
-    if lib.ctr_abi_version() != 1:
+    if lib.ctr_abi_version() != 2:
         raise CtrError("ABI version mismatch")
     if lib.ctr_sizeof_embed_cfg() != C.sizeof(EmbedCfg):
         raise CtrError("ctr_embed_cfg layout mismatch")

@@ -55,6 +55,15 @@ static inline int64_t ctr_align(int64_t a, int64_t b) { return ctr_cdiv(a, b) * 
 // ---------------------------------------------------------------------------- device side
 #ifdef __CUDACC__
 
+// an id outside its table: remember the field (status word CTR_STATUS_BAD_ID; only ever set on the error path)
+__device__ __forceinline__ void ctr_flag_bad_id(uint32_t* status, int field) {
+    if (status) atomicMax(status + CTR_STATUS_BAD_ID, 1u + (uint32_t) field);
+}
+// optimizer kernels: true while the engine's status words say the step must not move the weights
+__device__ __forceinline__ bool ctr_guard_tripped(const uint32_t* guard) {
+    return guard && (guard[CTR_STATUS_STEP_BARRIER] | guard[CTR_STATUS_PLAN_BARRIER] | guard[CTR_STATUS_BAD_ID]) != 0u;
+}
+
 __device__ __forceinline__ int64_t ctr_load_id(const void* ids, int id_bytes, int64_t i) {
     return id_bytes == 8 ? reinterpret_cast<const int64_t*>(ids)[i]
                          : (int64_t) reinterpret_cast<const int32_t*>(ids)[i];

@@ -213,6 +213,7 @@ adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restric
                  float* __restrict__ table, float* __restrict__ m, float* __restrict__ v, int stride, int64_t table_rows,
                  uint8_t* __restrict__ touched, uint32_t* __restrict__ long_list, const float* __restrict__ fm_w2, int emb_k,
                  const ctr_adam_hp hp) {
+    if (ctr_guard_tripped(hp.guard)) return;
     int64_t U = n_rows ? (int64_t) *n_rows : n_max;
     if (U > n_max) U = n_max;
     const int64_t total = U * width;
@@ -267,6 +268,7 @@ adam_rows_vec_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __res
     // perm != NULL (owner side of the sharded step): run u is the contributions grads[perm[i]], i in [seg_start[u],
     // seg_start[u+1]) -- one row per requesting peer, in peer order -- summed here instead of by ctr_segment_sum_rows
     constexpr int G = K / 4;
+    if (ctr_guard_tripped(hp.guard)) return;
     int64_t U = n_rows ? (int64_t) *n_rows : n_max;
     if (U > n_max) U = n_max;
     const int64_t total = U * G;
@@ -341,6 +343,7 @@ adam_rows_long_kernel(const uint32_t* __restrict__ row_ids, uint32_t mask, const
                       const float* __restrict__ fm_w2, int emb_k, const ctr_adam_hp hp) {
     const int lane = threadIdx.x & 31;
     const int gs4 = gs >> 2;
+    if (ctr_guard_tripped(hp.guard)) return;
     const uint32_t nlong = long_list[0];
     const int64_t nwarps = ((int64_t) gridDim.x * blockDim.x) >> 5;
     for (int64_t w = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < nlong; w += nwarps) {
@@ -400,6 +403,7 @@ adam_rows_long_kernel(const uint32_t* __restrict__ row_ids, uint32_t mask, const
 __global__ void __launch_bounds__(256)
 adam_dense_kernel(float* __restrict__ theta, float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g,
                   int64_t n, float l2, float l1, uint8_t* __restrict__ skip, int skip_group, const ctr_adam_hp hp) {
+    if (ctr_guard_tripped(hp.guard)) return;
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         if (skip && skip[i / skip_group]) continue;
         const float th = theta[i];
@@ -420,6 +424,7 @@ adam_dense_kernel(float* __restrict__ theta, float* __restrict__ m, float* __res
 __global__ void __launch_bounds__(256)
 dense_update_kernel(float* __restrict__ theta, float* __restrict__ m, float* __restrict__ v, const float* __restrict__ g,
                     const ctr_dense_layout lay, const ctr_adam_hp hp) {
+    if (ctr_guard_tripped(hp.guard)) return;
     const int64_t n = lay.group_end[2];
     for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         const float th = theta[i];

@@ -18,6 +18,10 @@ struct f4 {
 };
 
 __device__ __forceinline__ float4 f4_zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+__device__ __forceinline__ float4 f4_nan() {
+    const float n = __int_as_float(0x7fc00000);
+    return make_float4(n, n, n, n);
+}
 __device__ __forceinline__ void f4_acc(float4& s, float4& q, const float4 e) {
     s.x += e.x; s.y += e.y; s.z += e.z; s.w += e.w;
     q.x = fmaf(e.x, e.x, q.x); q.y = fmaf(e.y, e.y, q.y); q.z = fmaf(e.z, e.z, q.z); q.w = fmaf(e.w, e.w, q.w);
@@ -57,13 +61,15 @@ fm_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, c
     // ---- single-valued fields: gather ------------------------------------------------
     for (int f0 = 0; f0 < Fc; f0 += RPW * UNR) {
         int64_t rid[UNR];
-        bool ok[UNR], live[UNR];
+        bool ok[UNR], live[UNR], bad[UNR];
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
             int f = f0 + u * RPW + r;
             ok[u] = f < Fc;
             rid[u] = ok[u] ? ctr_load_id(ids, cfg.id_bytes, idrow + f) + id_offset : 0;
-            live[u] = ok[u] && !(zero0 && rid[u] == 0);
+            bad[u] = ok[u] && cfg.table_rows > 0 && (uint64_t) rid[u] >= (uint64_t) cfg.table_rows;
+            if (bad[u]) ctr_flag_bad_id(cfg.status, f);
+            live[u] = ok[u] && !bad[u] && !(zero0 && rid[u] == 0);
         }
         float4 e[UNR];
         float w[UNR];
@@ -72,6 +78,7 @@ fm_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, c
             const float* row = table + rid[u] * (int64_t) stride;
             e[u] = live[u] ? __ldg(reinterpret_cast<const float4*>(row + q * 4)) : f4_zero();
             w[u] = (USE_FM && live[u] && has_first && q == 0) ? __ldg(row + K) : 0.f;
+            if (bad[u]) e[u] = f4_nan();      // tf.nn.embedding_lookup raises here: the sample's logit / loss / score turn NaN
         }
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
@@ -212,7 +219,14 @@ fm_gather_fast_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, 
             id_t id_l = my_id;
             if (f0 > 0) id_l = f0 + lane < Fc ? idp[b * (int64_t) cfg.ids_ld + f0 + lane] : (id_t) 0;
             // row index as u32 (tables have < 2^32 rows); lanes past Fc carry id 0 -> a valid row that is never used
-            const uint32_t row_l = (uint32_t) ((int64_t) id_l + id_offset);
+            uint32_t row_l = (uint32_t) ((int64_t) id_l + id_offset);
+            // an id outside the table (tf.nn.embedding_lookup raises): no memory is read for it, the row reads as NaN
+            const bool bad_l = cfg.table_rows > 0 && (uint64_t) ((int64_t) id_l + id_offset) >= (uint64_t) cfg.table_rows;
+            const uint32_t badmask = __ballot_sync(0xffffffffu, bad_l);
+            if (bad_l) {
+                ctr_flag_bad_id(cfg.status, f0 + lane);
+                row_l = 0;
+            }
             float4 e[UNR];
             uint32_t row[UNR];
 #pragma unroll
@@ -232,6 +246,11 @@ fm_gather_fast_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, 
 #pragma unroll
                 for (int u = 0; u < UNR; ++u)
                     if (row[u] == 0) e[u] = f4_zero();
+            }
+            if (badmask) {             // warp-uniform, error path only
+#pragma unroll
+                for (int u = 0; u < UNR; ++u)
+                    if ((badmask >> (u * RPW + r)) & 1u) e[u] = f4_nan();
             }
 #pragma unroll
             for (int u = 0; u < UNR; ++u) {
@@ -316,9 +335,11 @@ pooled_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ tabl
         int t = t0 + r;
         bool ok = t < s1;
         int64_t rid = ok ? ctr_load_id(ids, cfg.id_bytes, idrow + t) : 0;
-        bool live = ok && !(zero0 && rid == 0);
+        const bool bad = ok && cfg.table_rows > 0 && (uint64_t) rid >= (uint64_t) cfg.table_rows;
+        if (bad) ctr_flag_bad_id(cfg.status, cfg.Fc + t);
+        bool live = ok && !bad && !(zero0 && rid == 0);
         const float* row = table + rid * (int64_t) stride;
-        float4 e = live ? __ldg(reinterpret_cast<const float4*>(row + q * 4)) : f4_zero();
+        float4 e = live ? __ldg(reinterpret_cast<const float4*>(row + q * 4)) : (bad ? f4_nan() : f4_zero());
         float w = (live && has_first && q == 0) ? __ldg(row + K) : 0.f;
         float sw = (ok && slot_weight) ? slot_weight[b * (int64_t) cfg.M + t] : 1.f;
         // row sum over the k coordinates (models/deepfm_multi.py:84 axis_2_sum)
@@ -362,12 +383,20 @@ pooled_gather_fwd_kernel(const ctr_embed_cfg cfg, const float* __restrict__ tabl
 }
 
 __global__ void scalar_gather_sum_kernel(const float* __restrict__ table, const void* __restrict__ ids, int id_bytes,
-                                         int B, int W, float* __restrict__ out) {
+                                         int B, int W, int64_t rows, uint32_t* __restrict__ status, float* __restrict__ out) {
     const int lane = threadIdx.x & 31;
     const int64_t b = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (b >= B) return;
     float acc = 0.f;
-    for (int j = lane; j < W; j += 32) acc += __ldg(table + ctr_load_id(ids, id_bytes, b * (int64_t) W + j));
+    for (int j = lane; j < W; j += 32) {
+        const int64_t id = ctr_load_id(ids, id_bytes, b * (int64_t) W + j);
+        if (rows > 0 && (uint64_t) id >= (uint64_t) rows) {
+            ctr_flag_bad_id(status, j);
+            acc = __int_as_float(0x7fc00000);
+        } else {
+            acc += __ldg(table + id);
+        }
+    }
     acc = ctr_warp_sum(acc);
     if (lane == 0) out[b] = acc;
 }
@@ -489,12 +518,12 @@ extern "C" int ctr_pooled_gather_fwd(ctr_handle* h, ctr_stream s, const ctr_embe
 }
 
 extern "C" int ctr_scalar_gather_sum(ctr_handle* h, ctr_stream s, const float* table, const void* ids, int id_bytes,
-                                     int B, int W, float* out) {
+                                     int B, int W, int64_t rows, uint32_t* status, float* out) {
     CTR_REQUIRE(h, table && ids && out && (id_bytes == 4 || id_bytes == 8) && B >= 0 && W >= 0,
                 "scalar_gather_sum: bad args");
     if (B == 0) return CTR_OK;
     scalar_gather_sum_kernel<<<(unsigned) ctr_cdiv((int64_t) B * 32, 256), 256, 0, ctr_st(s)>>>(table, ids, id_bytes, B,
-                                                                                               W, out);
+                                                                                               W, rows, status, out);
     CTR_CHECK_LAUNCH(h, "scalar_gather_sum");
     return CTR_OK;
 }

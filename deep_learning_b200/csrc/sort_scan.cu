@@ -205,7 +205,7 @@ __global__ void copy_pairs_kernel(const uint32_t* __restrict__ ka, const uint32_
 
 __global__ void build_keys_kernel(const void* __restrict__ ids, int id_bytes, int64_t rows, int64_t ld, int col0,
                                   int ncols, int64_t id_offset, int drop_zero, int64_t extra_base, int n_extra,
-                                  int n_shards, int local_bits,
+                                  int n_shards, int local_bits, int64_t id_limit, uint32_t* __restrict__ status,
                                   uint32_t* __restrict__ keys, uint32_t* __restrict__ perm) {
     int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     int64_t n = rows * ncols;
@@ -218,6 +218,10 @@ __global__ void build_keys_kernel(const void* __restrict__ ids, int id_bytes, in
         p = r * ld + col0 + c;
         id = ctr_load_id(ids, id_bytes, p) + id_offset;
         pad = drop_zero && id == 0;
+        if (id_limit > 0 && (uint64_t) id >= (uint64_t) id_limit) {      // no gradient for a lookup that read nothing
+            ctr_flag_bad_id(status, col0 + c);
+            pad = true;
+        }
     } else {
         p = rows * ld + (i - n);
         id = extra_base + (i - n);
@@ -384,7 +388,8 @@ extern "C" int ctr_sort_pairs(ctr_handle* h, ctr_stream s, uint32_t* keys, uint3
 extern "C" int ctr_sort_ids(ctr_handle* h, ctr_stream s, const void* ids, int id_bytes, int64_t rows, int64_t ld,
                             int col0, int ncols, int64_t id_offset, int drop_zero, int64_t extra_base, int n_extra,
                             int n_shards, int local_bits,
-                            int key_bits, uint32_t* keys_out, uint32_t* perm_out, void* ws, int64_t ws_bytes) {
+                            int key_bits, int64_t id_limit, uint32_t* status, uint32_t* keys_out, uint32_t* perm_out,
+                            void* ws, int64_t ws_bytes) {
     CTR_REQUIRE(h, ids && keys_out && perm_out && (id_bytes == 4 || id_bytes == 8), "sort_ids: bad pointers");
     CTR_REQUIRE(h, rows >= 0 && ncols >= 0 && col0 >= 0 && col0 + ncols <= ld, "sort_ids: bad shape");
     CTR_REQUIRE(h, n_shards >= 1 && (n_shards == 1 || (local_bits > 0 && local_bits < 31)), "sort_ids: bad sharding");
@@ -393,7 +398,7 @@ extern "C" int ctr_sort_ids(ctr_handle* h, ctr_stream s, const void* ids, int id
     if (n == 0) return CTR_OK;
     build_keys_kernel<<<(unsigned) ctr_cdiv(n, 256), 256, 0, ctr_st(s)>>>(ids, id_bytes, rows, ld, col0, ncols, id_offset,
                                                                          drop_zero, extra_base, n_extra, n_shards,
-                                                                         local_bits, keys_out, perm_out);
+                                                                         local_bits, id_limit, status, keys_out, perm_out);
     CTR_CHECK_LAUNCH(h, "build_keys");
     return ctr_sort_pairs(h, s, keys_out, perm_out, n, drop_zero ? 32 : key_bits, ws, ws_bytes);
 }

@@ -51,6 +51,13 @@ class CtrEngine:
             raise _lib.CtrError("precision='tf32' needs an sm_100 device")
         self.global_step, self.beta1_power, self.beta2_power = 0, ADAM_BETA1, ADAM_BETA2
         s, B, dev = spec, self.Bmax, self.dev
+        # device status words (include/ctr_b200.h CTR_STATUS_*): [step barrier, plan barrier, bad id, spare].  Kernels set
+        # them, the optimizer kernels refuse to move weights while one is set, check_status() turns them into an exception
+        self.status = torch.zeros(_lib.STATUS_WORDS, dtype=torch.int32, device=dev)
+        self._status_host = torch.zeros(_lib.STATUS_WORDS, dtype=torch.int32).pin_memory()
+        self._status_ev = torch.cuda.Event()
+        self._status_pending = False
+        self._steps_done = self._steps_verified = self._steps_at_snap = 0     # train steps enqueued / known to be applied
         f32 = dict(dtype=torch.float32, device=dev)
         self.id_torch = torch.int64 if s.id_dtype == "int64" else torch.int32
         self.id_bytes = 8 if s.id_dtype == "int64" else 4
@@ -182,7 +189,49 @@ class CtrEngine:
                         Fm=s.Fm, M=s.M, C=s.C, V=s.V, k=s.k, has_first=int(s.has_first), use_fm=int(s.use_fm),
                         fm_cont=int(s.fm_cont), zero_row0=int(s.zero_row0), count_rule=0, combiner=0,
                         table_stride=s.table_stride, x0_ld=s.x0_ld, fm_ld=s.fm_ld, grad_stride=s.grad_stride,
-                        round_tf32=int(self.prec == 1))
+                        round_tf32=int(self.prec == 1), reserved0=0, table_rows=self._id_limit(),
+                        status=self.status.data_ptr())
+
+    def _id_limit(self) -> int:
+        """ids K1/K2 may be fed: rows of the (single-GPU) table incl. the frozen rows behind it"""
+        return int(self.spec.table_rows + self.spec.frozen_rows)
+
+    # ---- fault reporting ------------------------------------------------------------------------------------------
+    def _snapshot_status(self) -> None:
+        """queue a copy of the status words to pinned host memory behind the step (no host wait)"""
+        self._status_host.copy_(self.status, non_blocking=True)
+        self._status_ev.record(self._main_stream())
+        self._status_pending = True
+        self._steps_at_snap = self._steps_done
+
+    def check_status(self, wait: bool = True) -> None:
+        """Raise if a kernel reported a fault: an id outside its table (tf.nn.embedding_lookup raises
+        InvalidArgumentError there, models/deepfm.py:78,85,98) or a peer barrier that timed out.  The weights were not
+        touched by the faulty step (the optimizer kernels check the same words).  Called by the fit / predict loops right
+        after they read a loss or score (already synchronised, so it costs nothing), by get_weights and by the
+        checkpoint writers; wait=False only looks if the snapshot has already landed."""
+        if not self._status_pending:
+            self._snapshot_status()
+        if not wait and not self._status_ev.query():
+            return
+        self._status_ev.synchronize()
+        self._status_pending = False
+        st = self._status_host.tolist()
+        if not any(st[:3]):
+            self._steps_verified = self._steps_at_snap
+            return
+        # the status words are sticky and stop every optimizer kernel: no step since the last clean snapshot was applied,
+        # so the host-side step counters go back by as many steps
+        lost = self._steps_done - self._steps_verified
+        self.global_step -= lost
+        self.beta1_power /= ADAM_BETA1 ** lost
+        self.beta2_power /= ADAM_BETA2 ** lost
+        self._steps_verified = self._steps_done
+        self.status.zero_()
+        if st[2]:
+            raise _lib.CtrError("id out of range in column %d of cate_feats / wide_feats (table has %d rows): the step "
+                                "was not applied" % (st[2] - 1, self._id_limit()))
+        raise _lib.CtrError("peer barrier timed out waiting for rank %d: the step was not applied" % ((st[0] or st[1]) - 1))
 
     # the stream a step runs on is looked up ONCE per public call (torch.cuda.current_stream costs ~7 us of host time, and a
     # step asked for it ~20 times: the multi-GPU step is close to host-bound)
@@ -316,6 +365,7 @@ class CtrEngine:
                 blk[:, s.k] = torch.rand(r1 - r0, generator=g, device=self.dev)
 
     def get_weights(self) -> Dict[str, np.ndarray]:
+        self.check_status()
         return self._dump(self.table, self.theta)
 
     def get_optimizer_state(self):
@@ -360,6 +410,7 @@ class CtrEngine:
         `shard-<rank>-of-<world>.npz`."""
         s = self.spec
         os.makedirs(path, exist_ok=True)
+        self.check_status()          # a faulted step never reaches a checkpoint
         self._main_stream().synchronize()
         R = self.rows_local
         blob = {"meta": np.asarray([self.world, self.rank, s.table_rows, s.k, s.table_stride, self.global_step, self.n_dense,
@@ -550,7 +601,7 @@ class CtrEngine:
         extra = None
         if s.head == "wdl":
             h.call("ctr_scalar_gather_sum", st, ptr(self.view("wdl_weights")), ptr(self.wide), self.id_bytes, B,
-                   s.wide_fields, ptr(self.wide_sum))
+                   s.wide_fields, s.wide_rows + s.hidden[-1], ptr(self.status), ptr(self.wide_sum))
             extra = self.wide_sum
         lab = self.label if with_loss else None
         g_fm = g_deep = g_bias = None
@@ -593,7 +644,7 @@ class CtrEngine:
         global_step (models/deepfm.py:159-162), then lr_t = lr*sqrt(1-b2^t)/(1-b1^t)."""
         lr = self.lr0 * self.decay_rate ** math.floor(self.global_step / self.decay_steps)
         lr_t = lr * math.sqrt(1.0 - self.beta2_power) / (1.0 - self.beta1_power)
-        return AdamHP(lr_t=lr_t, beta1=ADAM_BETA1, beta2=ADAM_BETA2, eps=ADAM_EPS)
+        return AdamHP(lr_t=lr_t, beta1=ADAM_BETA1, beta2=ADAM_BETA2, eps=ADAM_EPS, guard=self.status.data_ptr())
 
     def backward_and_update(self, B: int) -> None:
         s, st, h = self.spec, self._stream(), self.h
@@ -658,6 +709,7 @@ class CtrEngine:
         self.beta1_power *= ADAM_BETA1
         self.beta2_power *= ADAM_BETA2
         self.global_step += 1
+        self._steps_done += 1
 
     def _sparse_update(self, B: int, n: int, hp: AdamHP) -> None:
         """per-run partial gradients (self.part) -> TF1 Adam on the touched rows of the local table"""
@@ -697,7 +749,8 @@ class CtrEngine:
         key_bits = max(1, int(s.table_rows + s.frozen_rows - 1).bit_length())
         st, ws, wsn = self.side.cuda_stream, ptr(self.ws_sort), self.ws_sort.numel()
         h.call("ctr_sort_ids", st, ptr(self.ids), self.id_bytes, B, s.ids_ld, 0, s.ids_ld, 0, int(s.zero_row0),
-               s.cont_base, self.n_extra, 1, 0, key_bits, ptr(self.keys), ptr(self.perm), ws, wsn)
+               s.cont_base, self.n_extra, 1, 0, key_bits, self._id_limit(), ptr(self.status), ptr(self.keys), ptr(self.perm),
+               ws, wsn)
         h.call("ctr_unique_segments", st, ptr(self.keys), n, ptr(self.uniq), ptr(self.seg_start), ptr(self.uidx),
                ptr(self.n_unique), ws, wsn)
         self.ev_sorted.record(self.side)
@@ -711,7 +764,7 @@ class CtrEngine:
             rows = s.wide_rows + s.hidden[-1]
             ws, wsn = ptr(self.ws_sort_w), self.ws_sort_w.numel()
             h.call("ctr_sort_ids", st, ptr(self.wide), self.id_bytes, B, s.wide_fields, 0, s.wide_fields, 0, 0, 0, 0, 1, 0,
-                   max(1, int(rows - 1).bit_length()), ptr(self.w_keys), ptr(self.w_perm), ws, wsn)
+                   max(1, int(rows - 1).bit_length()), rows, ptr(self.status), ptr(self.w_keys), ptr(self.w_perm), ws, wsn)
             h.call("ctr_unique_segments", st, ptr(self.w_keys), nw, ptr(self.w_uniq), ptr(self.w_seg_start),
                    ptr(self.w_uidx), ptr(self.w_n_unique), ws, wsn)
             self.ev_sorted_w.record(self.side if st == self.side.cuda_stream else self._main_stream())
@@ -775,6 +828,8 @@ class CtrEngine:
         de-duplication and id exchange of step i+1 off the critical path of step i."""
         if not self.train_mode:
             raise _lib.CtrError("engine was created with train=False")
+        if self._status_pending:
+            self.check_status(wait=False)      # a fault of an earlier step whose snapshot has landed: raise now
         self._mark("start")
         ev_call = None
         if next_batch is not None:
@@ -816,6 +871,7 @@ class CtrEngine:
     def _end_step(self) -> None:
         self._in_free[self._cur_in].record(self._main_stream())
         self._in_used[self._cur_in] = True
+        self._snapshot_status()            # read by the next public call (or check_status) without a host wait
 
     def _global_loss(self) -> torch.Tensor:
         """log-loss of the global batch (sharded engines read it back from the gradient allreduce)"""

@@ -149,7 +149,9 @@ class BaseDeepModel:
 
     def predict_scores(self, batch) -> np.ndarray:
         """`session.run("score:0", feed_dict)` for one batch: [B,1] host array."""
-        return self.engine.predict(self._decode(batch)).cpu().numpy().reshape(-1, 1)
+        out = self.engine.predict(self._decode(batch)).cpu().numpy().reshape(-1, 1)
+        self.engine.check_status()        # an id outside its table raises here, as tf.nn.embedding_lookup does
+        return out
 
     # ---- generation A: fit(train_data, val_data) (models/deepfm.py:164-214) -----------------------------
     def _fit_a(self, train_data: List, val_data: List) -> None:

@@ -7,7 +7,6 @@ import ctypes as C
 from typing import List, Sequence
 
 import torch
-import torch.distributed as dist
 
 from ._lib import IPC_HANDLE_BYTES, MAX_PEERS, Handle, PeerRoute
 
@@ -22,25 +21,30 @@ class _Region:
 
 
 class PeerSlab:
-    def __init__(self, h: Handle, nbytes: int, group, device: torch.device):
-        world, rank = dist.get_world_size(group), dist.get_rank(group)
+    def __init__(self, h: Handle, nbytes: int, comm, device: torch.device):
+        """comm: deep_learning_b200.comm.DistComm (one process per GPU: CUDA IPC) or LoopbackComm (ranks are threads of
+        one process on one GPU: the slabs share an address space and their addresses are handed over as they are)"""
+        world, rank = comm.world, comm.rank
         if world > MAX_PEERS:
             raise ValueError("PeerSlab: at most %d ranks" % MAX_PEERS)
         self.h, self.world, self.rank, self.nbytes, self.device = h, world, rank, int(nbytes), device
+        self.loopback = bool(comm.is_loopback)
         own, handle = C.c_void_p(), C.create_string_buffer(IPC_HANDLE_BYTES)
         h.invoke("ctr_peer_alloc", self.nbytes, C.byref(own), handle)
         self.own = own.value
-        handles: List[bytes] = [b""] * world
-        dist.all_gather_object(handles, bytes(handle.raw), group=group)
         self.ptrs: List[int] = []
-        for r in range(world):
-            if r == rank:
-                self.ptrs.append(self.own)
-                continue
-            p = C.c_void_p()
-            h.invoke("ctr_peer_open", C.create_string_buffer(handles[r], IPC_HANDLE_BYTES), C.byref(p))
-            self.ptrs.append(p.value)
-        dist.barrier(group)              # nobody stores into a slab before everyone has zeroed and mapped theirs
+        if self.loopback:
+            self.ptrs = [int(p) for p in comm.all_gather_object(self.own)]
+        else:
+            handles: List[bytes] = comm.all_gather_object(bytes(handle.raw))
+            for r in range(world):
+                if r == rank:
+                    self.ptrs.append(self.own)
+                    continue
+                p = C.c_void_p()
+                h.invoke("ctr_peer_open", C.create_string_buffer(handles[r], IPC_HANDLE_BYTES), C.byref(p))
+                self.ptrs.append(p.value)
+        comm.barrier()                   # nobody stores into a slab before everyone has zeroed and mapped theirs
         self._closed = False
 
     def tensor(self, offset: int, shape: Sequence[int], dtype=torch.float32) -> torch.Tensor:
@@ -60,6 +64,6 @@ class PeerSlab:
         self._closed = True
         torch.cuda.synchronize(self.device)
         for r, p in enumerate(self.ptrs):
-            if r != self.rank:
+            if r != self.rank and not self.loopback:
                 self.h.invoke("ctr_peer_close", p)
         self.h.invoke("ctr_peer_free", self.own)

@@ -23,6 +23,7 @@ import torch
 import torch.distributed as dist
 
 from . import shard as _shard
+from .comm import as_comm
 from ._lib import AdamHP, EmbedCfg, ptr
 from .peer import PeerSlab
 from .engine import CtrEngine, _ALIGN, _ru
@@ -74,14 +75,17 @@ class _IdPlan:
 
 class ShardedCtrEngine(CtrEngine):
     def __init__(self, spec: ModelSpec, max_batch: int, group=None, **kw):
-        if not dist.is_initialized():
-            raise RuntimeError("ShardedCtrEngine needs an initialised torch.distributed process group")
-        self.group = group
-        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        # `group`: a torch.distributed process group (None = the default one), or a comm.LoopbackComm (N ranks as N threads
+        # of one process on one GPU: the arrangement the 1-GPU test box uses to run the world-N step)
+        self.comm = as_comm(group)
+        world, rank = self.comm.world, self.comm.rank
+        self.group = None if self.comm.is_loopback else group
         # the id plans of step i+1 are built under step i on a side stream: their collectives get a communicator of their
         # own, or they would queue in front of step i's vector / gradient exchanges (one communicator = one FIFO)
-        ranks = dist.get_process_group_ranks(group) if group is not None else list(range(dist.get_world_size()))
-        self.group_plan = dist.new_group(ranks=ranks) if world > 1 else group
+        self.group_plan = self.group
+        if not self.comm.is_loopback and world > 1 and os.environ.get("CTR_EXCHANGE", "peer") == "nccl":
+            ranks = dist.get_process_group_ranks(group) if group is not None else list(range(dist.get_world_size()))
+            self.group_plan = dist.new_group(ranks=ranks)
         self.plan = _shard.ShardPlan(spec.table_rows, world)
         self.wire = spec.grad_stride          # floats per row on the wire (k [+1], rounded up to 4): vectors and gradients
         super().__init__(spec, max_batch, world=world, rank=rank, **kw)
@@ -98,7 +102,9 @@ class ShardedCtrEngine(CtrEngine):
         self.exchange_mode = os.environ.get("CTR_EXCHANGE", "peer" if world > 1 else "nccl")
         if self.exchange_mode not in ("peer", "nccl"):
             raise ValueError("CTR_EXCHANGE must be peer or nccl")
-        self.peer_status = torch.zeros(2, dtype=torch.int32, device=dev)      # [0] step barriers, [1] id-plan barriers
+        if self.comm.is_loopback:
+            self.exchange_mode = "peer"       # the peer-memory path is the one under test; there is no NCCL between threads
+        self.peer_status = self.status[:2]      # [0] step barriers, [1] id-plan barriers: words of the engine's status array
         self._epoch, self._pepoch, self._rows_dirty = 0, 0, False
         if self.exchange_mode == "peer":
             # slab layout: arrival words of the step barriers | of the id-plan barriers | count matrix x 2 plan slots |
@@ -113,7 +119,7 @@ class ShardedCtrEngine(CtrEngine):
             self._req_off = [r0, r0 + _ru(self._req_cap * 4, 256)]
             self._dense_off = self._req_off[1] + _ru(self._req_cap * 4, 256)
             n_dense = self.n_dense + _ALIGN
-            self.slab = PeerSlab(self.h, self._dense_off + _ru((n_dense if self.train_mode else 1) * 4, 256), group, dev)
+            self.slab = PeerSlab(self.h, self._dense_off + _ru((n_dense if self.train_mode else 1) * 4, 256), self.comm, dev)
             self.rows_recv = self.slab.tensor(self._rows_off, (self.n_max + 1, self.wire))
             self.g_recv = self.slab.tensor(self._g_off, (max(self._g_cap, 1), self.wire)) if self.train_mode else None
             self._rt0 = self.slab.route([0] * W, [0] * W, 0)
@@ -158,6 +164,7 @@ class ShardedCtrEngine(CtrEngine):
     def _cfg(self, B: int) -> EmbedCfg:
         cfg = super()._cfg(B)
         cfg.id_bytes = 4             # lookups index the staging buffer by their position in the unique list
+        cfg.table_rows = 0           # positions are valid by construction; the fed ids are range-checked by ctr_sort_ids
         cfg.zero_row0 = 0            # padding ids share one all-zero staging row instead
         cfg.table_stride = self.wire
         return cfg
@@ -167,8 +174,7 @@ class ShardedCtrEngine(CtrEngine):
         return self.cont_buf if (s.use_fm and s.fm_cont) else None
 
     def _assemble_rows(self, shard_rows: torch.Tensor) -> np.ndarray:
-        parts = [torch.empty_like(shard_rows) for _ in range(self.world)]
-        dist.all_gather(parts, shard_rows.contiguous(), group=self.group)
+        parts = self.comm.all_gather_tensor(shard_rows)
         R = self.spec.table_rows
         full = np.zeros((R,) + tuple(shard_rows.shape[1:]), dtype=np.float32)
         for o, t in enumerate(parts):
@@ -185,7 +191,8 @@ class ShardedCtrEngine(CtrEngine):
         n = B * s.ids_ld + self.n_extra
         ws, wsn = ptr(pl.ws_sort), pl.ws_sort.numel()
         h.call("ctr_sort_ids", st, ptr(pl.ids), self.id_bytes, B, s.ids_ld, 0, s.ids_ld, 0, int(s.zero_row0),
-               s.cont_base, self.n_extra, self.world, sp.local_bits, sp.key_bits, ptr(pl.keys), ptr(pl.perm), ws, wsn)
+               s.cont_base, self.n_extra, self.world, sp.local_bits, sp.key_bits, int(s.table_rows), ptr(self.status),
+               ptr(pl.keys), ptr(pl.perm), ws, wsn)
         h.call("ctr_unique_segments", st, ptr(pl.keys), n, ptr(pl.uniq), ptr(pl.seg_start), ptr(pl.uidx),
                ptr(pl.n_unique), ws, wsn)
         h.call("ctr_shard_counts", st, ptr(pl.uniq), ptr(pl.n_unique), self.world, sp.local_bits, ptr(pl.counts))
@@ -404,6 +411,9 @@ class ShardedCtrEngine(CtrEngine):
     def _barrier(self, st: int) -> None:
         """all ranks: everything stored into peer slabs so far is visible, and every peer is at the same point"""
         self._epoch += 1
+        if self.comm.is_loopback:
+            self.comm.device_barrier(st)
+            return
         self.h.call("ctr_peer_barrier", st, C.byref(self.cur.route_v), self._flags_off, self._epoch, ptr(self.peer_status),
                     int(os.environ.get("CTR_PEER_TIMEOUT_MS", 10000)))
 
@@ -420,6 +430,9 @@ class ShardedCtrEngine(CtrEngine):
     def _plan_barrier(self, st: int) -> None:
         """barrier of the id-plan exchanges: its own arrival words and epoch, since it runs on another stream than the step's"""
         self._pepoch += 1
+        if self.comm.is_loopback:
+            self.comm.device_barrier(st)
+            return
         self.h.call("ctr_peer_barrier", st, C.byref(self._rt0), self._pflags_off, self._pepoch, ptr(self.peer_status[1:]),
                     int(os.environ.get("CTR_PEER_TIMEOUT_MS", 10000)))
 

@@ -95,13 +95,13 @@ class SplitFmEngine(CtrEngine):
         ws, wsn = ptr(self.ws_sort), self.ws_sort.numel()
         # list A: FM lookups at id + C, then the continuous rows 1..C-1 (row 0 is cut out of the graph)
         h.call("ctr_sort_ids", st, ptr(self.ids), self.id_bytes, B, s.ids_ld, 0, s.Fc, s.C, 1, 1, max(s.C - 1, 0), 1, 0, key_bits,
-               ptr(self.keys), ptr(self.perm), ws, wsn)
+               int(s.table_rows), ptr(self.status), ptr(self.keys), ptr(self.perm), ws, wsn)
         h.call("ctr_unique_segments", st, ptr(self.keys), nA, ptr(self.ukeys), ptr(self.seg_start), ptr(self.uidx),
                ptr(self.n_unique), ws, wsn)
         # list B: deep lookups at the raw id, id 0 dropped
         wsb, wsbn = ptr(self.ws_b), self.ws_b.numel()
         h.call("ctr_sort_ids", st, ptr(self.ids), self.id_bytes, B, s.ids_ld, 0, s.Fc, 0, 1, 0, 0, 1, 0, key_bits,
-               ptr(self.keys_b), ptr(self.perm_b), wsb, wsbn)
+               int(s.table_rows), ptr(self.status), ptr(self.keys_b), ptr(self.perm_b), wsb, wsbn)
         h.call("ctr_unique_segments", st, ptr(self.keys_b), nB, ptr(self.ukeys[self.nA_cap:]), ptr(self.seg_b), ptr(self.uidx_b),
                ptr(self.nuniq_b), wsb, wsbn)
         self.ev_sorted.record(self.side)
@@ -166,3 +166,4 @@ class SplitFmEngine(CtrEngine):
         self.beta1_power *= ADAM_BETA1
         self.beta2_power *= ADAM_BETA2
         self.global_step += 1
+        self._steps_done += 1

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define CTR_ABI_VERSION 1
+#define CTR_ABI_VERSION 2
 
 #define CTR_OK              0
 #define CTR_E_INVALID      -1   /* bad argument / unsupported shape */
@@ -71,7 +71,22 @@ typedef struct ctr_embed_cfg {
     int32_t fm_ld;         /* floats per fm row */
     int32_t grad_stride;   /* floats per gradient row (multiple of 4, >= k + has_first) */
     int32_t round_tf32;    /* TF32 tower: write X0 rounded-to-nearest tf32 (tensor cores truncate fp32 operands) */
+    int32_t reserved0;
+    int64_t table_rows;    /* rows a fed id (+ id_offset) may address: [0, table_rows).  tf.nn.embedding_lookup raises
+                              InvalidArgumentError for anything else (models/deepfm.py:78,85,98); here such a lookup reads
+                              no memory, yields NaN (so logit, loss and score of the sample are NaN) and sets the status
+                              word.  0 = unchecked. */
+    uint32_t* status;      /* device, CTR_STATUS_WORDS words (see below) or NULL */
 } ctr_embed_cfg;
+
+/* Device status words shared by the kernels of one engine (all zero = healthy).  Kernels only ever set them; the host
+ * clears them.  The optimizer entry points take the same array as ctr_adam_hp.guard and leave every weight untouched
+ * while word 0, 1 or 2 is non-zero: a batch with a bad id or a step whose peer barrier timed out must not move the
+ * model. */
+#define CTR_STATUS_WORDS       4
+#define CTR_STATUS_STEP_BARRIER 0   /* 1 + rank that did not arrive (ctr_peer_barrier on the step's stream) */
+#define CTR_STATUS_PLAN_BARRIER 1   /* same, id-plan barriers */
+#define CTR_STATUS_BAD_ID       2   /* 1 + field (column of cate_feats / wide_feats) of an id outside its table */
 
 /* ---- handle ------------------------------------------------------------------------- */
 int  ctr_abi_version(void);
@@ -118,9 +133,10 @@ int ctr_fm_gather_fwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg,
                       const float* pooled_first,
                       float* x0, float* fm, float* sum_e);
 
-/* scalar-table gather-sum: out[b] = sum_j table[ids[b,j]]   (wide part, models/wdl.py:240-246) */
+/* scalar-table gather-sum: out[b] = sum_j table[ids[b,j]]   (wide part, models/wdl.py:240-246).  ids outside
+ * [0, rows) contribute NaN and set status word CTR_STATUS_BAD_ID (rows = 0: unchecked; status may be NULL). */
 int ctr_scalar_gather_sum(ctr_handle* h, ctr_stream s, const float* table, const void* ids, int id_bytes,
-                          int B, int W, float* out);
+                          int B, int W, int64_t rows, uint32_t* status, float* out);
 
 /* ---- K3: MLP tower ---------------------------------------------------------------------
  * replaces the matmul/add/relu/dropout loop (models/deepfm.py:121-126) and what
@@ -205,7 +221,9 @@ int ctr_sort_ids(ctr_handle* h, ctr_stream s, const void* ids, int id_bytes, int
                  int64_t extra_base, int n_extra /* appends ids extra_base+c with perm = rows*ld + c: the
                  continuous-field rows, so their gradient rides the same segment-reduce */,
                  int n_shards, int local_bits,
-                 int key_bits, uint32_t* keys_out, uint32_t* perm_out, void* ws, int64_t ws_bytes);
+                 int key_bits, int64_t id_limit /* ids (+ id_offset) outside [0, id_limit) become padding keys (no
+                 gradient) and set status word CTR_STATUS_BAD_ID; 0 = unchecked */, uint32_t* status /* or NULL */,
+                 uint32_t* keys_out, uint32_t* perm_out, void* ws, int64_t ws_bytes);
 /* generic stable pair sort (also used by ctr_auc) */
 int ctr_sort_pairs(ctr_handle* h, ctr_stream s, uint32_t* keys, uint32_t* vals, int64_t n, int key_bits,
                    void* ws, int64_t ws_bytes);
@@ -296,7 +314,11 @@ int ctr_segment_sum_rows(ctr_handle* h, ctr_stream s, const uint32_t* seg_start,
  * 1.f - 0.999f they would be 0.00099998713 (1.3e-5 low), which scales v by the same factor and -- because lr_t's own
  * sqrt(1 - beta2^t) is computed exactly on the host -- leaves a systematic 6.5e-6 * lr drift per step (TensorFlow's
  * float32 kernel makes the same rounding in BOTH places, where it cancels).  Entry points reject c1 <= 0 or c2 <= 0. */
-typedef struct ctr_adam_hp { float lr_t, beta1, beta2, eps, c1, c2; } ctr_adam_hp;
+typedef struct ctr_adam_hp {
+    float lr_t, beta1, beta2, eps, c1, c2;
+    const uint32_t* guard;   /* device status words (CTR_STATUS_WORDS) or NULL: the update is skipped while one of the
+                                first three is non-zero */
+} ctr_adam_hp;
 int64_t ctr_adam_rows_ws_bytes(ctr_handle* h, int64_t n_max);
 int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
                   int local_bits, const float* grads, const uint32_t* seg_start /* non-NULL: `grads` is the

@@ -27,7 +27,7 @@ def main():
         kb = lb + (world - 1).bit_length()
 
         def sort(i):
-            hd.call("ctr_sort_ids", st, ptr(ids[i]), 4, B, Fc, 0, Fc, 0, 0, Fc, C, world, lb, kb, ptr(keys), ptr(perm), ptr(ws), wsn)
+            hd.call("ctr_sort_ids", st, ptr(ids[i]), 4, B, Fc, 0, Fc, 0, 0, Fc, C, world, lb, kb, 0, None, ptr(keys), ptr(perm), ptr(ws), wsn)
 
         def uniqf(i):
             hd.call("ctr_unique_segments", st, ptr(keys), n, ptr(uniq), ptr(seg), ptr(uidx), ptr(nu), ptr(ws), wsn)

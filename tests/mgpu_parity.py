@@ -27,10 +27,19 @@ import ctr_helpers as H              # noqa: E402
 def main():
     alg = sys.argv[1] if len(sys.argv) > 1 else "deepfm"
     adam_mode = sys.argv[2] if len(sys.argv) > 2 else "lazy"
-    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from deep_learning_b200.comm import DistComm
+    run(DistComm(None), alg, adam_mode)
+    dist.destroy_process_group()
+
+
+def run(comm, alg="deepfm", adam_mode="lazy"):
+    """the parity body; `comm` is a DistComm (one process per GPU, torchrun) or a LoopbackComm (N ranks as threads on one
+    GPU: tests/test_gpu_sharded_loopback.py)"""
+    rank, world = comm.rank, comm.world
+    group = comm if comm.is_loopback else None
     from deep_learning_b200.sharded import ShardedCtrEngine
     from deep_learning_b200.spec import spec_from_hparams
 
@@ -46,7 +55,7 @@ def main():
     spec = spec_from_hparams(alg, hp)
     p = O.init_params(alg, hp, seed=2019, dtype=torch.float64)
     st = O.adam_init(p)
-    eng = ShardedCtrEngine(spec, Bl, learning_rate=hp.learning_rate, precision="fp32", adam_mode=adam_mode)
+    eng = ShardedCtrEngine(spec, Bl, group=group, learning_rate=hp.learning_rate, precision="fp32", adam_mode=adam_mode)
     eng.set_weights({k: v.numpy() for k, v in p.items()})
     back = eng.get_weights()
     for n in p:      # shards re-assemble to the injected tables bit-exactly
@@ -124,11 +133,10 @@ def main():
     # ---- per-shard checkpoint: every rank writes its rows; a fresh sharded engine restored from them
     # continues bit-identically, and ONE GPU re-shards the same files (world -> 1) to the assembled weights
     import tempfile
-    ck = [tempfile.mkdtemp(prefix="ctr_ckpt_") if rank == 0 else None]
-    dist.broadcast_object_list(ck, src=0)
+    ck = [comm.broadcast_object(tempfile.mkdtemp(prefix="ctr_ckpt_") if rank == 0 else None, src=0)]
     eng.save_shard(ck[0])
-    dist.barrier()
-    eng2 = ShardedCtrEngine(spec, Bl, learning_rate=hp.learning_rate, precision="fp32", adam_mode=adam_mode)
+    comm.barrier()
+    eng2 = ShardedCtrEngine(spec, Bl, group=group, learning_rate=hp.learning_rate, precision="fp32", adam_mode=adam_mode)
     eng2.load_shard(ck[0])
     nxt = [H.make_batch(alg, hp, seed=9000 + r, B=Bl) for r in range(world)]
     la, lb = float(eng.train_step(nxt[rank]).item()), float(eng2.train_step(nxt[rank]).item())
@@ -137,7 +145,7 @@ def main():
     for n in wa:
         assert np.array_equal(wa[n], wb[n]), "restored shard diverges: %s" % n
     eng2.save_shard(ck[0])
-    dist.barrier()
+    comm.barrier()
     if rank == 0:
         from deep_learning_b200.engine import CtrEngine
         one = CtrEngine(spec, Bl, learning_rate=hp.learning_rate, precision="fp32", adam_mode=adam_mode)
@@ -149,10 +157,11 @@ def main():
         print("per-shard checkpoint ok (restore + reshard %d -> 1)" % world)
         import shutil
         shutil.rmtree(ck[0], ignore_errors=True)
-    dist.barrier()
+    comm.barrier()
     if rank == 0:
-        print("MGPU PARITY OK alg=%s adam=%s world=%d" % (alg, adam_mode, world))
-    dist.destroy_process_group()
+        print("MGPU PARITY OK alg=%s adam=%s world=%d%s" % (alg, adam_mode, world, " (loopback: ranks as threads on one GPU)"
+                                                             if comm.is_loopback else ""))
+    return True
 
 
 if __name__ == "__main__":

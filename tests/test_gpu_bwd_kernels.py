@@ -39,7 +39,7 @@ def _sort_runs(hd, ids_t, B, Fc, rows, n_extra=0, extra_base=0):
     wsn = max(hd.query("ctr_sort_ws_bytes", n), 4 * (n // 2048 + 8)) + 256
     ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
     hd.call("ctr_sort_ids", _st(), _ptr(ids_t), 4, B, Fc, 0, Fc, 0, 0, extra_base, n_extra, 1, 0,
-            max(1, int(rows - 1).bit_length()), _ptr(keys), _ptr(perm), _ptr(ws), wsn)
+            max(1, int(rows - 1).bit_length()), 0, None, _ptr(keys), _ptr(perm), _ptr(ws), wsn)
     uniq = torch.zeros(n + 8, dtype=torch.int32, device="cuda")
     seg = torch.zeros(n + 8, dtype=torch.int32, device="cuda")
     uidx = torch.zeros(n + 8, dtype=torch.int32, device="cuda")

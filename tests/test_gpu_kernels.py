@@ -69,7 +69,7 @@ def test_sort_ids_sharded_keys_and_counts(hd):
     n = B * F + 3
     keys, perm = (torch.zeros(n, dtype=torch.int32, device="cuda") for _ in range(2))
     wsn = hd.query("ctr_sort_ws_bytes", n); ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
-    hd.call("ctr_sort_ids", _st(), ptr(d), 8, B, F, 0, F, 0, 1, 4000, 3, N, bits, 32, ptr(keys), ptr(perm), ptr(ws), wsn)
+    hd.call("ctr_sort_ids", _st(), ptr(d), 8, B, F, 0, F, 0, 1, 4000, 3, N, bits, 32, 0, None, ptr(keys), ptr(perm), ptr(ws), wsn)
     flat = np.r_[ids.reshape(-1), 4000 + np.arange(3)]
     pad = np.r_[ids.reshape(-1) == 0, np.zeros(3, bool)]
     ref = np.where(pad, 0xFFFFFFFF, ((flat % N) << bits) | (flat // N)).astype(np.uint32)
