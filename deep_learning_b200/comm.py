@@ -11,7 +11,7 @@ Two carriers with one interface:
                     different ranks that wait on one another must not share a GPU: nothing guarantees co-residency).
                     Everything else -- routes, fused gather/push and finalize/push kernels, owner-side merge and Adam,
                     the dense-gradient reduction out of the slabs, id-plan prefetch -- is the production code path.
-                    This is what lets a 1-GPU box run the world-2/4/8 step against the oracle
+                    This is what lets a 1-GPU box run the world-2/4/8 parity check of the step
                     (tests/test_gpu_sharded_loopback.py).
 """
 from __future__ import annotations
