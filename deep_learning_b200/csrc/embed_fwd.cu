@@ -307,6 +307,178 @@ fm_gather_fast_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, 
     }
 }
 
+// ---- async-copy plumbing of the staged K1 ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t) __cvta_generic_to_shared(p); }
+// LDGSTS: global -> shared without a register round trip; src_bytes < size zero-fills the rest (0 = a row of zeros
+// without touching memory: padding id 0 of the row-0-zero models, ids outside the table)
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// K1, staged path (same shapes as the fast path above, Fc <= 32).  The register-staged kernel above is ISSUE-bound
+// (ncu, profiles/r01h: 403 warp instructions per sample, issue slots 60 % busy, DRAM 39 %) and its bytes in flight are
+// capped by the register file.  Here a warp owns a ring of NS gathered-row images in shared memory:
+//   fill     the 16-byte chunks of a sample's rows go global -> shared with cp.async (LDGSTS): no destination
+//            registers, zero-fill for padding ids; the first-order weights ride along as 4-byte copies;
+//   consume  LAG samples later each lane reads its chunks back (conflict-free 128-bit LDS), accumulates the FM sums and
+//            stores the (TF32-rounded) chunk to X0 with an immediate offset from ONE per-sample base pointer.
+// The loads of NS-1 samples (1.7 KB each) are in flight per warp whatever the register budget.
+// (A TMA bulk store of the finished row image, cp.async.bulk shared -> global, was tried first: its bulk groups count on
+// the same scoreboard as the LDGSTS groups -- both wait with DEPBAR.LE SB0 -- so every fill wait also waited for the
+// previous row's store; and it needs the rounded values written back to shared memory plus a proxy fence per row.)
+template <int K, bool USE_FM, bool ID64, int NS>
+__global__ void __launch_bounds__(256)
+fm_gather_stage_kernel(const ctr_embed_cfg cfg, const float* __restrict__ table, const void* __restrict__ ids,
+                       const int64_t id_offset, const float* __restrict__ cont, const float* __restrict__ cont_rows,
+                       float* __restrict__ x0, float* __restrict__ fm, float* __restrict__ sum_e) {
+    constexpr int LPR = K / 4;                                   // lanes (16-byte chunks) per row
+    constexpr int RPW = 32 / LPR;                                // rows per warp-wide chunk sweep
+    constexpr int CS = 2;                                        // continuous-row slots per lane
+    constexpr int LAG = NS - 1;                                  // samples between fill and consume
+    constexpr int H = RPW >= 8 ? 3 : 2;
+    constexpr int NV = 8 >> H;
+    constexpr int BF_MASK = LPR < 4 ? (3 & ~(LPR - 1)) : 0;
+    constexpr int XTRA = 36;                                     // per slot behind the rows: 32 first-order words, 1 fault mask
+    typedef typename std::conditional<ID64, int64_t, int32_t>::type id_t;
+    extern __shared__ __align__(16) float k1_smem[];
+    const int lane = threadIdx.x & 31;
+    const int r = lane / LPR, q = lane % LPR;
+    const int Fc = cfg.Fc, C = cfg.C, B = cfg.B;
+    const bool has_first = cfg.has_first != 0, zero0 = cfg.zero_row0 != 0, rnd = cfg.round_tf32 != 0;
+    const bool fm_cont = USE_FM && cfg.fm_cont != 0;
+    const int cont_col = Fc * K;
+    const int tail = cfg.x0_ld - cont_col;      // continuous values + pad columns (<= 32, checked by the launcher)
+    const int slot_f = cont_col + XTRA;
+    float* const wbase = k1_smem + (size_t) ((threadIdx.x >> 5) * NS) * slot_f;
+    const int nw = (int) ((gridDim.x * blockDim.x) >> 5);
+    const int b0 = (int) ((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (b0 >= B) return;
+    const int n_local = (B - b0 + nw - 1) / nw;
+
+    const int stride = cfg.table_stride;
+    float4 crow[CS];
+    float cw = 0.f;
+#pragma unroll
+    for (int s = 0; s < CS; ++s) {
+        const int c = s * RPW + r;
+        crow[s] = (fm_cont && c < C) ? __ldg(reinterpret_cast<const float4*>(cont_rows + c * (int64_t) stride + q * 4)) : f4_zero();
+    }
+    if (fm_cont && has_first && lane < C) cw = __ldg(cont_rows + lane * (int64_t) stride + K);
+
+    const id_t* __restrict__ idp = reinterpret_cast<const id_t*>(ids);
+    const char* __restrict__ tbytes = reinterpret_cast<const char*>(table);
+    const uint32_t stride_b = (uint32_t) stride * 4u;
+    const uint32_t s_base = smem_u32(wbase);
+    id_t nx_id = lane < Fc ? idp[b0 * (int64_t) cfg.ids_ld + lane] : (id_t) 0;
+    float nx_x = lane < C ? cont[b0 * (int64_t) C + lane] : 0.f;
+
+    for (int t = 0; t < n_local + LAG; ++t) {
+        // ---------------------------------------------------------------- fill: sample t -> ring slot t % NS
+        // (the slot was last read by this warp's consume of sample t - NS, earlier in program order)
+        if (t < n_local) {
+            const int b = b0 + t * nw;
+            const id_t id_l = nx_id;
+            if (t + 1 < n_local && lane < Fc) nx_id = idp[(b + nw) * (int64_t) cfg.ids_ld + lane];
+            const int64_t rix = (int64_t) id_l + id_offset;
+            const bool bad_l = lane < Fc && cfg.table_rows > 0 && (uint64_t) rix >= (uint64_t) cfg.table_rows;
+            const uint32_t row_l = bad_l ? 0u : (uint32_t) rix;
+            const uint32_t zmask = __ballot_sync(0xffffffffu, bad_l || lane >= Fc || (zero0 && row_l == 0u));
+            const uint32_t badmask = __ballot_sync(0xffffffffu, bad_l);
+            const uint32_t s_slot = s_base + (uint32_t) ((t % NS) * slot_f) * 4u;
+#pragma unroll
+            for (int j = 0; j < LPR; ++j) {                              // Fc <= 32: at most LPR sweeps of 32 chunks
+                const int f = r + j * RPW;                               // field of chunk lane + 32 j
+                const uint32_t rw = __shfl_sync(0xffffffffu, row_l, f & 31);
+                if (f < Fc)
+                    cp_async16(s_slot + (uint32_t) (lane + 32 * j) * 16u, tbytes + (uint64_t) rw * stride_b + q * 16,
+                               ((zmask >> f) & 1u) ? 0u : 16u);
+            }
+            if (USE_FM && lane < Fc)             // first-order weight of field `lane` (0 without the column / for padding)
+                cp_async4(s_slot + (uint32_t) (cont_col + lane) * 4u, tbytes + (uint64_t) row_l * stride_b + K * 4,
+                          (has_first && !((zmask >> lane) & 1u)) ? 4u : 0u);
+            if (lane == 0) wbase[(t % NS) * slot_f + cont_col + 32] = __uint_as_float(badmask);
+            if (bad_l) ctr_flag_bad_id(cfg.status, lane);
+        }
+        cp_async_commit();                       // one group per iteration (empty in the drain) keeps the wait count fixed
+        // ---------------------------------------------------------------- consume: sample t - LAG
+        const int tc = t - LAG;
+        if (tc < 0) continue;                    // (warp-uniform)
+        cp_async_wait<LAG>();
+        __syncwarp();
+        const int b = b0 + tc * nw;
+        const float* const slot = wbase + (tc % NS) * slot_f;
+        float* __restrict__ x0row = x0 + b * (int64_t) cfg.x0_ld;
+        const float my_x = nx_x;
+        if (tc + 1 < n_local && lane < C) nx_x = cont[(b + nw) * (int64_t) C + lane];
+        const uint32_t badmask = __float_as_uint(slot[cont_col + 32]);
+        float4 as = f4_zero(), aq = f4_zero();
+#pragma unroll
+        for (int j = 0; j < LPR; ++j) {
+            const int f = r + j * RPW;
+            if (f < Fc) {
+                float4 e = reinterpret_cast<const float4*>(slot)[lane + 32 * j];
+                if (badmask && ((badmask >> f) & 1u)) e = f4_nan();      // an id outside the table: tf.nn.embedding_lookup raises
+                float4 o = e;
+                if (rnd) o = make_float4(ctr_round_tf32_fast(e.x), ctr_round_tf32_fast(e.y), ctr_round_tf32_fast(e.z), ctr_round_tf32_fast(e.w));
+                reinterpret_cast<float4*>(x0row)[lane + 32 * j] = o;
+                if (USE_FM) f4_acc(as, aq, e);
+            }
+        }
+        // continuous values, then the pad columns: the 1.0 at column D0 is the bias row of the layer-0 weight-gradient GEMM
+        if (lane < tail) x0row[cont_col + lane] = lane < C ? (rnd ? ctr_round_tf32_fast(my_x) : my_x) : (lane == C ? 1.f : 0.f);
+        if (USE_FM) {
+            float* __restrict__ fmrow = fm + b * (int64_t) cfg.fm_ld;
+            if (lane < Fc) {
+                float w = slot[cont_col + lane];
+                if (badmask && ((badmask >> lane) & 1u)) w = __int_as_float(0x7fc00000);
+                fmrow[lane] = w;
+            }
+            if (lane < C) fmrow[Fc + lane] = cw * my_x;          // cw is 0 without fm_cont / first-order weights
+            if (fm_cont) {
+#pragma unroll
+                for (int s = 0; s < CS; ++s) {
+                    const float x = __shfl_sync(0xffffffffu, my_x, (s * RPW + r) & 31);     // slots c >= C hold zero rows
+                    f4_acc(as, aq, make_float4(crow[s].x * x, crow[s].y * x, crow[s].z * x, crow[s].w * x));
+                }
+            }
+            float v[8] = {as.x, as.y, as.z, as.w, aq.x, aq.y, aq.z, aq.w};
+#pragma unroll
+            for (int j = 0; j < H; ++j) {        // halving exchange: each level keeps half of the values, summed over the pair
+                const int o = 16 >> j, n = 4 >> j;
+                const bool hi = (lane & o) != 0;
+#pragma unroll
+                for (int i = 0; i < n; ++i) {
+                    const float keep = hi ? v[i + n] : v[i], send = hi ? v[i] : v[i + n];
+                    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+                }
+            }
+#pragma unroll
+            for (int o = 16 >> H; o >= LPR; o >>= 1) {
+#pragma unroll
+                for (int i = 0; i < NV; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], o);
+            }
+            // lanes with bit 16 clear hold sum e, their partners sum e^2, of coordinate q*4 + comp
+#pragma unroll
+            for (int i = 0; i < NV; ++i) {
+                const float sq = __shfl_xor_sync(0xffffffffu, v[i], 16);
+                if ((lane & (16 | BF_MASK)) == 0) {
+                    const int comp = (((lane & 8) ? 2 : 0) | ((H >= 3 && (lane & 4)) ? 1 : 0)) + i;
+                    const int j = q * 4 + comp;
+                    fmrow[Fc + C + j] = 0.5f * (v[i] * v[i] - sq);      // models/deepfm.py:88-92
+                    sum_e[b * (int64_t) K + j] = v[i];
+                }
+            }
+        }
+        __syncwarp();        // every lane is done with the slot before the next fill overwrites it
+    }
+}
+
 // K2: one warp per (sample, multi-valued field)
 template <int K>
 __global__ void __launch_bounds__(256)
@@ -435,6 +607,62 @@ extern "C" int ctr_fm_gather_fwd(ctr_handle* h, ctr_stream s, const ctr_embed_cf
         const int lpr = cfg->k / 4, rpw = 32 / lpr;
         const bool fast = cfg->Fm == 0 && cfg->V == 0 && cfg->C <= 2 * rpw && cfg->C <= 32 &&
                           cfg->x0_ld - cfg->Fc * cfg->k <= 32 && cfg->k <= 32 && getenv("CTR_K1_GENERAL") == nullptr;
+        // staged path (cp.async ring + TMA bulk store of the X0 row) unless CTR_K1=regs asks for the register-staged kernel
+        static const char* k1_mode = getenv("CTR_K1");
+        const bool staged = fast && cfg->Fc <= 32 && cfg->Fc > 0 &&
+                            (reinterpret_cast<uintptr_t>(x0) & 15) == 0 && (reinterpret_cast<uintptr_t>(table) & 15) == 0 &&
+                            !(k1_mode && strcmp(k1_mode, "regs") == 0);
+        if (staged) {
+            static int sms = 0, ns_sel = 0, cta_cap = 0;
+            if (!sms) {
+                int dev = 0;
+                cudaGetDevice(&dev);
+                cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+                const char* e = getenv("CTR_K1_NS");
+                ns_sel = (e && atoi(e) == 6) ? 6 : 4;
+                e = getenv("CTR_K1_CTAS");
+                cta_cap = e ? atoi(e) : 0;
+            }
+            static int occ_s[4][2][2][2];
+            const int ki = cfg->k == 4 ? 0 : cfg->k == 8 ? 1 : cfg->k == 16 ? 2 : 3, fi = cfg->use_fm ? 1 : 0, ii = cfg->id_bytes == 8,
+                      ni = ns_sel == 6;
+            const size_t smem = (size_t) 8 * ns_sel * (cfg->Fc * cfg->k + 36) * 4;
+            CTR_REQUIRE(h, smem <= 227 * 1024, "fm_gather_fwd: embedding block too wide for the staged kernel");
+#define LAUNCH_STAGE(KK, FM_, I64, NS_)                                                                                \
+    {                                                                                                                  \
+        auto kern = fm_gather_stage_kernel<KK, FM_, I64, NS_>;                                                         \
+        int& o = occ_s[ki][fi][ii][ni];                                                                                \
+        if (!o) {                                                                                                      \
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);                       \
+            int q = 0;                                                                                                 \
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&q, kern, 256, smem);                                        \
+            o = q > 0 ? q : 1;                                                                                         \
+        }                                                                                                              \
+        const int per_sm = (cta_cap > 0 && cta_cap < o) ? cta_cap : o;                                                 \
+        const int64_t want = ctr_cdiv((int64_t) cfg->B, 8), cap = (int64_t) sms * per_sm;                              \
+        kern<<<(unsigned) (want < cap ? want : cap), 256, smem, ctr_st(s)>>>(*cfg, table, ids, id_offset, cont,        \
+                                                                            cont_rows, x0, fm, sum_e);                 \
+    }
+#define LAUNCH_STAGE_N(KK, FM_, I64) \
+    if (ni) LAUNCH_STAGE(KK, FM_, I64, 6) else LAUNCH_STAGE(KK, FM_, I64, 4)
+#define LAUNCH_STAGE_K(KK)                                                           \
+    if (cfg->use_fm) {                                                               \
+        if (ii) { LAUNCH_STAGE_N(KK, true, true) } else { LAUNCH_STAGE_N(KK, true, false) }   \
+    } else {                                                                         \
+        if (ii) { LAUNCH_STAGE_N(KK, false, true) } else { LAUNCH_STAGE_N(KK, false, false) } \
+    }
+            switch (cfg->k) {
+                case 4: LAUNCH_STAGE_K(4) break;
+                case 8: LAUNCH_STAGE_K(8) break;
+                case 16: LAUNCH_STAGE_K(16) break;
+                default: LAUNCH_STAGE_K(32) break;
+            }
+#undef LAUNCH_STAGE_K
+#undef LAUNCH_STAGE_N
+#undef LAUNCH_STAGE
+            CTR_CHECK_LAUNCH(h, "fm_gather_fwd(staged)");
+            return CTR_OK;
+        }
         if (fast) {
             static int occ[4][2][2];         // resident CTAs per SM of each instantiation, queried once
             static int sms = 0;
