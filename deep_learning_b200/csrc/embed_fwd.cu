@@ -608,10 +608,13 @@ extern "C" int ctr_fm_gather_fwd(ctr_handle* h, ctr_stream s, const ctr_embed_cf
         const bool fast = cfg->Fm == 0 && cfg->V == 0 && cfg->C <= 2 * rpw && cfg->C <= 32 &&
                           cfg->x0_ld - cfg->Fc * cfg->k <= 32 && cfg->k <= 32 && getenv("CTR_K1_GENERAL") == nullptr;
         // staged path (cp.async ring + TMA bulk store of the X0 row) unless CTR_K1=regs asks for the register-staged kernel
+        // measured (profiles/r02b_k1_variants.txt, B = 64K, Zipf / uniform ids): register-staged 47.3 / 57.9 us, staged
+        // 57.0 / 67.9 us whatever the ring depth (4, 6) or CTAs per SM (2, 3, 4) -- so neither kernel is bound by bytes in
+        // flight; the staged kernel stays selectable (CTR_K1=staged) and covered by the parity tests
         static const char* k1_mode = getenv("CTR_K1");
         const bool staged = fast && cfg->Fc <= 32 && cfg->Fc > 0 &&
                             (reinterpret_cast<uintptr_t>(x0) & 15) == 0 && (reinterpret_cast<uintptr_t>(table) & 15) == 0 &&
-                            !(k1_mode && strcmp(k1_mode, "regs") == 0);
+                            (k1_mode && strcmp(k1_mode, "staged") == 0);
         if (staged) {
             static int sms = 0, ns_sel = 0, cta_cap = 0;
             if (!sms) {

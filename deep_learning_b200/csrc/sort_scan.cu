@@ -203,35 +203,52 @@ __global__ void copy_pairs_kernel(const uint32_t* __restrict__ ka, const uint32_
     }
 }
 
-__global__ void build_keys_kernel(const void* __restrict__ ids, int id_bytes, int64_t rows, int64_t ld, int col0,
-                                  int ncols, int64_t id_offset, int drop_zero, int64_t extra_base, int n_extra,
-                                  int n_shards, int local_bits, int64_t id_limit, uint32_t* __restrict__ status,
-                                  uint32_t* __restrict__ keys, uint32_t* __restrict__ perm) {
-    int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
-    int64_t n = rows * ncols;
-    if (i >= n + n_extra) return;
-    int64_t p, id;
-    bool pad = false;
-    if (i < n) {
-        int64_t r = i / ncols;
-        int c = (int) (i - r * ncols);
-        p = r * ld + col0 + c;
-        id = ctr_load_id(ids, id_bytes, p) + id_offset;
-        pad = drop_zero && id == 0;
-        if (id_limit > 0 && (uint64_t) id >= (uint64_t) id_limit) {      // no gradient for a lookup that read nothing
-            ctr_flag_bad_id(status, col0 + c);
-            pad = true;
-        }
-    } else {
-        p = rows * ld + (i - n);
-        id = extra_base + (i - n);
+// ids -> (key, flat position) pairs, fused with the per-block digit histogram of the FIRST radix pass (the pairs are
+// produced tile by tile in exactly the order radix_scatter_kernel will read them, so its histogram pass is free)
+__global__ void __launch_bounds__(SORT_THREADS)
+build_keys_kernel(const void* __restrict__ ids, int id_bytes, int64_t rows, int64_t ld, int col0, int ncols,
+                  int64_t id_offset, int drop_zero, int64_t extra_base, int n_extra, int n_shards, int local_bits,
+                  int64_t id_limit, uint32_t* __restrict__ status, uint32_t* __restrict__ keys, uint32_t* __restrict__ perm,
+                  uint32_t* __restrict__ hist, int nblk) {
+    __shared__ uint32_t sh[RADIX];
+    if (hist) {
+        for (int i = threadIdx.x; i < RADIX; i += SORT_THREADS) sh[i] = 0;
+        __syncthreads();
     }
-    uint32_t key;
-    if (pad) key = CTR_PAD_KEY;
-    else if (n_shards > 1) key = ((uint32_t) (id % n_shards) << local_bits) | (uint32_t) (id / n_shards);
-    else key = (uint32_t) id;
-    keys[i] = key;
-    perm[i] = (uint32_t) p;
+    const int64_t n = rows * ncols;
+    const int64_t base = (int64_t) blockIdx.x * SORT_TILE;
+#pragma unroll 4
+    for (int it = 0; it < SORT_ITEMS; ++it) {
+        const int64_t i = base + it * SORT_THREADS + threadIdx.x;
+        if (i >= n + n_extra) break;
+        int64_t p, id;
+        bool pad = false;
+        if (i < n) {
+            int64_t r = i / ncols;
+            int c = (int) (i - r * ncols);
+            p = r * ld + col0 + c;
+            id = ctr_load_id(ids, id_bytes, p) + id_offset;
+            pad = drop_zero && id == 0;
+            if (id_limit > 0 && (uint64_t) id >= (uint64_t) id_limit) {      // no gradient for a lookup that read nothing
+                ctr_flag_bad_id(status, col0 + c);
+                pad = true;
+            }
+        } else {
+            p = rows * ld + (i - n);
+            id = extra_base + (i - n);
+        }
+        uint32_t key;
+        if (pad) key = CTR_PAD_KEY;
+        else if (n_shards > 1) key = ((uint32_t) (id % n_shards) << local_bits) | (uint32_t) (id / n_shards);
+        else key = (uint32_t) id;
+        keys[i] = key;
+        perm[i] = (uint32_t) p;
+        if (hist) atomicAdd(&sh[key & (RADIX - 1)], 1u);
+    }
+    if (hist) {
+        __syncthreads();
+        for (int d = threadIdx.x; d < RADIX; d += SORT_THREADS) hist[(int64_t) d * nblk + blockIdx.x] = sh[d];
+    }
 }
 
 // ---- generic 3-phase flag scan ------------------------------------------------------------------
@@ -239,10 +256,6 @@ constexpr int SCAN_THREADS = 256;
 constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;   // 2048
 
-struct HeadFlag {   // 1 where a new run of equal keys starts
-    const uint32_t* keys;
-    __device__ __forceinline__ uint32_t operator()(int64_t i) const { return (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u; }
-};
 struct PosLabel {   // 1 where the label of the i-th sorted element is positive
     const float* labels;
     const uint32_t* perm;
@@ -280,20 +293,6 @@ __global__ void __maxnreg__(24) scan_phase2(uint32_t* __restrict__ blk, int nblk
     }
 }
 
-struct UniqueOut {
-    const uint32_t* keys;
-    uint32_t* uniq;
-    uint32_t* seg_start;
-    uint32_t* uidx;
-    __device__ __forceinline__ void operator()(int64_t i, uint32_t incl, uint32_t flag) const {
-        uint32_t u = incl - 1u;
-        uidx[i] = u;
-        if (flag) {
-            uniq[u] = keys[i];
-            seg_start[u] = (uint32_t) i;
-        }
-    }
-};
 struct ExclOut {   // out[i] = exclusive prefix
     uint32_t* out;
     __device__ __forceinline__ void operator()(int64_t i, uint32_t incl, uint32_t flag) const { out[i] = incl - flag; }
@@ -319,10 +318,6 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_phase3(F f, int64_t n, cons
             out(base + it, run, fl[it]);
         }
     }
-}
-
-__global__ void seg_tail_kernel(const uint32_t* __restrict__ n_unique, uint32_t* __restrict__ seg_start, uint32_t n) {
-    seg_start[*n_unique] = n;
 }
 
 __global__ void shard_counts_kernel(const uint32_t* __restrict__ uniq, const uint32_t* __restrict__ n_unique,
@@ -352,36 +347,57 @@ extern "C" int64_t ctr_sort_ws_bytes(ctr_handle*, int64_t n) {
     return ctr_align(n * 4, 256) * 2 + ctr_align((int64_t) RADIX * nb * 4, 256) + RADIX * 4 + 256;
 }
 
+// `passes` stable LSD passes from (ka, va), ping-ponging with (kb, vb); the result is in (ka, va) when passes is even,
+// else in (kb, vb).  first_hist_ready: hist already holds the per-block histogram of pass 0 (build_keys_kernel).
+static int sort_passes(ctr_handle* h, cudaStream_t st, uint32_t* ka, uint32_t* va, uint32_t* kb, uint32_t* vb, int64_t n,
+                       int passes, uint32_t* hist, uint32_t* tot, bool first_hist_ready) {
+    const int nblk = sort_nblk(n);
+    for (int pass = 0; pass < passes; ++pass) {
+        int shift = pass * RADIX_BITS;
+        if (!(pass == 0 && first_hist_ready)) {
+            radix_hist_kernel<<<nblk, SORT_THREADS, 0, st>>>(ka, n, shift, hist, nblk);
+            h->launches += 1;
+        }
+        radix_scan_rows_kernel<<<RADIX, 1024, 0, st>>>(hist, nblk, tot);
+        radix_scatter_kernel<<<nblk, SORT_THREADS, 0, st>>>(ka, va, kb, vb, n, shift, hist, tot, nblk);
+        h->launches += 1;
+        uint32_t* t;
+        t = ka; ka = kb; kb = t;
+        t = va; va = vb; vb = t;
+        CTR_CHECK_LAUNCH(h, "sort pass");
+    }
+    return CTR_OK;
+}
+
+struct SortWs {
+    uint32_t *k2, *v2, *hist, *tot;
+};
+static SortWs carve_sort_ws(void* ws, int64_t n) {
+    const int nblk = sort_nblk(n);
+    char* p = (char*) ws;
+    SortWs w;
+    w.k2 = (uint32_t*) p; p += ctr_align(n * 4, 256);
+    w.v2 = (uint32_t*) p; p += ctr_align(n * 4, 256);
+    w.hist = (uint32_t*) p; p += ctr_align((int64_t) RADIX * nblk * 4, 256);
+    w.tot = (uint32_t*) p;
+    return w;
+}
+
 extern "C" int ctr_sort_pairs(ctr_handle* h, ctr_stream s, uint32_t* keys, uint32_t* vals, int64_t n, int key_bits,
                               void* ws, int64_t ws_bytes) {
     CTR_REQUIRE(h, keys && vals && ws && n >= 0 && key_bits >= 1 && key_bits <= 32, "sort_pairs: bad args");
     CTR_REQUIRE(h, n < (int64_t) 1 << 31, "sort_pairs: n too large");
     if (n == 0) return CTR_OK;
     if (ws_bytes < ctr_sort_ws_bytes(h, n)) return ctr_fail(h, CTR_E_WORKSPACE, "sort_pairs: ws too small");
-    const int nblk = sort_nblk(n);
-    char* p = (char*) ws;
-    uint32_t* k2 = (uint32_t*) p; p += ctr_align(n * 4, 256);
-    uint32_t* v2 = (uint32_t*) p; p += ctr_align(n * 4, 256);
-    uint32_t* hist = (uint32_t*) p; p += ctr_align((int64_t) RADIX * nblk * 4, 256);
-    uint32_t* tot = (uint32_t*) p;
+    const SortWs w = carve_sort_ws(ws, n);
     const int passes = (key_bits + RADIX_BITS - 1) / RADIX_BITS;
-    uint32_t *ka = keys, *va = vals, *kb = k2, *vb = v2;
     cudaStream_t st = ctr_st(s);
-    for (int pass = 0; pass < passes; ++pass) {
-        int shift = pass * RADIX_BITS;
-        radix_hist_kernel<<<nblk, SORT_THREADS, 0, st>>>(ka, n, shift, hist, nblk);
-        radix_scan_rows_kernel<<<RADIX, 1024, 0, st>>>(hist, nblk, tot);
-        radix_scatter_kernel<<<nblk, SORT_THREADS, 0, st>>>(ka, va, kb, vb, n, shift, hist, tot, nblk);
-        uint32_t* t;
-        t = ka; ka = kb; kb = t;
-        t = va; va = vb; vb = t;
+    int rc = sort_passes(h, st, keys, vals, w.k2, w.v2, n, passes, w.hist, w.tot, false);
+    if (rc) return rc;
+    if (passes & 1) {        // in-place contract: an odd pass count ends in the workspace
+        copy_pairs_kernel<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>(w.k2, w.v2, keys, vals, n);
+        CTR_CHECK_LAUNCH(h, "sort_pairs copy");
     }
-    h->launches += 3ull * passes - 1;
-    if (ka != keys) {
-        copy_pairs_kernel<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>(ka, va, keys, vals, n);
-        h->launches += 1;
-    }
-    CTR_CHECK_LAUNCH(h, "sort_pairs");
     return CTR_OK;
 }
 
@@ -394,14 +410,124 @@ extern "C" int ctr_sort_ids(ctr_handle* h, ctr_stream s, const void* ids, int id
     CTR_REQUIRE(h, rows >= 0 && ncols >= 0 && col0 >= 0 && col0 + ncols <= ld, "sort_ids: bad shape");
     CTR_REQUIRE(h, n_shards >= 1 && (n_shards == 1 || (local_bits > 0 && local_bits < 31)), "sort_ids: bad sharding");
     CTR_REQUIRE(h, n_extra >= 0 && rows * ld + n_extra < ((int64_t) 1 << 32), "sort_ids: flat positions exceed 32 bits");
+    CTR_REQUIRE(h, key_bits >= 1 && key_bits <= 32, "sort_ids: bad key_bits");
     int64_t n = rows * ncols + n_extra;
     if (n == 0) return CTR_OK;
-    build_keys_kernel<<<(unsigned) ctr_cdiv(n, 256), 256, 0, ctr_st(s)>>>(ids, id_bytes, rows, ld, col0, ncols, id_offset,
-                                                                         drop_zero, extra_base, n_extra, n_shards,
-                                                                         local_bits, id_limit, status, keys_out, perm_out);
+    CTR_REQUIRE(h, ws && n < (int64_t) 1 << 31, "sort_ids: n too large / no workspace");
+    if (ws_bytes < ctr_sort_ws_bytes(h, n)) return ctr_fail(h, CTR_E_WORKSPACE, "sort_ids: ws too small");
+    const SortWs w = carve_sort_ws(ws, n);
+    // padding keys (0xFFFFFFFF) must sort behind every real key: all 32 bits when ids can be dropped.  (Ids outside
+    // id_limit also become padding keys, but that batch is a fault: the status word stops the optimizer, the order of its
+    // key list no longer matters, and the healthy path does not pay a fourth pass for it.)
+    const int passes = ((drop_zero ? 32 : key_bits) + RADIX_BITS - 1) / RADIX_BITS;
+    // the pairs are built where an odd / even number of ping-pong passes ends in (keys_out, perm_out): no final copy
+    uint32_t *k0 = (passes & 1) ? w.k2 : keys_out, *v0 = (passes & 1) ? w.v2 : perm_out;
+    uint32_t *k1 = (passes & 1) ? keys_out : w.k2, *v1 = (passes & 1) ? perm_out : w.v2;
+    const int nblk = sort_nblk(n);
+    build_keys_kernel<<<nblk, SORT_THREADS, 0, ctr_st(s)>>>(ids, id_bytes, rows, ld, col0, ncols, id_offset, drop_zero,
+                                                          extra_base, n_extra, n_shards, local_bits, id_limit, status,
+                                                          k0, v0, w.hist, nblk);
     CTR_CHECK_LAUNCH(h, "build_keys");
-    return ctr_sort_pairs(h, s, keys_out, perm_out, n, drop_zero ? 32 : key_bits, ws, ws_bytes);
+    return sort_passes(h, ctr_st(s), k0, v0, k1, v1, n, passes, w.hist, w.tot, true);
 }
+
+namespace {
+// ---- run-length structure of sorted keys in two launches --------------------------------------------------------------
+// Warp w of a block owns 256 consecutive keys and walks them in 8 rounds of 32 (coalesced); a round's head flags are one
+// ballot, so ranks inside the warp are popcounts of register-held ballots.  Pass 1 writes the flag count of each
+// 2048-key tile; pass 2 recomputes the flags (the keys are L2-resident), lets every block sum the counts of the tiles
+// before it (a few loads per thread) and emits uidx / uniq / seg_start.  The last block also writes *n_unique and
+// seg_start[U] = n.
+constexpr int UQ_ROUNDS = 8;
+constexpr int UQ_TILE = SCAN_THREADS * UQ_ROUNDS;       // 2048
+__device__ __forceinline__ uint32_t uq_flags(const uint32_t* __restrict__ keys, int64_t n, int64_t wbase, int lane,
+                                             uint32_t (&bal)[UQ_ROUNDS], uint32_t (&k)[UQ_ROUNDS]) {
+    uint32_t prev = (lane == 0 && wbase > 0 && wbase < n) ? keys[wbase - 1] : 0u;
+#pragma unroll
+    for (int r = 0; r < UQ_ROUNDS; ++r) {
+        const int64_t i = wbase + r * 32 + lane;
+        k[r] = i < n ? keys[i] : 0u;
+    }
+    uint32_t total = 0;
+#pragma unroll
+    for (int r = 0; r < UQ_ROUNDS; ++r) {
+        const int64_t i = wbase + r * 32 + lane;
+        uint32_t up = __shfl_up_sync(0xffffffffu, k[r], 1);
+        if (lane == 0) up = prev;
+        const bool flag = i < n && (i == 0 || k[r] != up);
+        bal[r] = __ballot_sync(0xffffffffu, flag);
+        total += __popc(bal[r]);
+        prev = __shfl_sync(0xffffffffu, k[r], 31);
+    }
+    return total;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+unique_count_kernel(const uint32_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ blk) {
+    __shared__ uint32_t wtot[SCAN_THREADS / 32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t bal[UQ_ROUNDS], k[UQ_ROUNDS];
+    const uint32_t t = uq_flags(keys, n, (int64_t) blockIdx.x * UQ_TILE + w * (32 * UQ_ROUNDS), lane, bal, k);
+    if (lane == 0) wtot[w] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t s = 0;
+#pragma unroll
+        for (int i = 0; i < SCAN_THREADS / 32; ++i) s += wtot[i];
+        blk[blockIdx.x] = s;
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+unique_emit_kernel(const uint32_t* __restrict__ keys, int64_t n, const uint32_t* __restrict__ blk, uint32_t* __restrict__ uniq,
+                   uint32_t* __restrict__ seg_start, uint32_t* __restrict__ uidx, uint32_t* __restrict__ n_unique) {
+    __shared__ uint32_t wtot[SCAN_THREADS / 32], red[SCAN_THREADS / 32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    // flags of the tiles before this one
+    uint32_t before = 0;
+    for (int j = threadIdx.x; j < (int) blockIdx.x; j += SCAN_THREADS) before += blk[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) before += __shfl_xor_sync(0xffffffffu, before, o);
+    if (lane == 0) red[w] = before;
+    const int64_t wbase = (int64_t) blockIdx.x * UQ_TILE + w * (32 * UQ_ROUNDS);
+    uint32_t bal[UQ_ROUNDS], k[UQ_ROUNDS];
+    const uint32_t t = uq_flags(keys, n, wbase, lane, bal, k);
+    if (lane == 0) wtot[w] = t;
+    __syncthreads();
+    uint32_t run = 0, all = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_THREADS / 32; ++i) {
+        run += red[i];
+        if (i < w) run += wtot[i];
+        all += wtot[i];
+    }
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < UQ_ROUNDS; ++r) {
+        const int64_t i = wbase + r * 32 + lane;
+        const bool flag = (bal[r] >> lane) & 1u;
+        const uint32_t incl = run + __popc(bal[r] & lt) + (flag ? 1u : 0u);
+        if (i < n) {
+            const uint32_t u = incl - 1u;
+            uidx[i] = u;
+            if (flag) {
+                uniq[u] = k[r];
+                seg_start[u] = (uint32_t) i;
+            }
+        }
+        run += __popc(bal[r]);
+    }
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) {
+        uint32_t tot_before = 0;
+#pragma unroll
+        for (int i = 0; i < SCAN_THREADS / 32; ++i) tot_before += red[i];
+        const uint32_t U = tot_before + all;
+        *n_unique = U;
+        seg_start[U] = (uint32_t) n;
+    }
+}
+
+}  // namespace
 
 extern "C" int ctr_unique_segments(ctr_handle* h, ctr_stream s, const uint32_t* sorted_keys, int64_t n, uint32_t* uniq,
                                    uint32_t* seg_start, uint32_t* uidx, uint32_t* n_unique, void* ws, int64_t ws_bytes) {
@@ -412,15 +538,12 @@ extern "C" int ctr_unique_segments(ctr_handle* h, ctr_stream s, const uint32_t* 
         CTR_CUDA(h, cudaMemsetAsync(seg_start, 0, 4, st));
         return CTR_OK;
     }
-    int nblk = (int) ctr_cdiv(n, SCAN_TILE);
+    int nblk = (int) ctr_cdiv(n, UQ_TILE);
     if (ws_bytes < (int64_t) (nblk + 2) * 4) return ctr_fail(h, CTR_E_WORKSPACE, "unique_segments: ws too small");
     uint32_t* blk = (uint32_t*) ws;
-    HeadFlag f{sorted_keys};
-    scan_phase1<HeadFlag><<<nblk, SCAN_THREADS, 0, st>>>(f, n, blk);
-    scan_phase2<<<1, 1024, 0, st>>>(blk, nblk, n_unique);
-    scan_phase3<HeadFlag, UniqueOut><<<nblk, SCAN_THREADS, 0, st>>>(f, n, blk, UniqueOut{sorted_keys, uniq, seg_start, uidx});
-    seg_tail_kernel<<<1, 1, 0, st>>>(n_unique, seg_start, (uint32_t) n);
-    h->launches += 3;
+    unique_count_kernel<<<nblk, SCAN_THREADS, 0, st>>>(sorted_keys, n, blk);
+    h->launches += 1;
+    unique_emit_kernel<<<nblk, SCAN_THREADS, 0, st>>>(sorted_keys, n, blk, uniq, seg_start, uidx, n_unique);
     CTR_CHECK_LAUNCH(h, "unique_segments");
     return CTR_OK;
 }
