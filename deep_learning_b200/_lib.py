@@ -54,7 +54,10 @@ IPC_HANDLE_BYTES = 64
 class PeerRoute(C.Structure):
     """mirror of `ctr_peer_route`"""
     _fields_ = [("world", c_i32), ("rank", c_i32), ("slab", c_vp * MAX_PEERS), ("seg_end", C.c_uint32 * MAX_PEERS),
-                ("dst_row", C.c_uint32 * MAX_PEERS), ("dst_off", c_i64)]
+                ("dst_row", C.c_uint32 * MAX_PEERS), ("dst_off", c_i64), ("dyn", c_vp)]
+
+
+ROUTE_WORDS, PLAN_VEC, PLAN_GRAD, PLAN_NREQ, PLAN_U, PLAN_WORDS = 48, 0, 48, 96, 97, 128     # include/ctr_b200.h CTR_PLAN_*
 
 
 _P_CFG = C.POINTER(EmbedCfg)
@@ -98,7 +101,7 @@ _PROTOS = {
     "ctr_sort_ids": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_i32, c_i32, c_i64, c_i32, c_i64, c_i32,
                              c_i32, c_i32, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp, c_i64]),
     "ctr_sort_pairs": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_i64]),
-    "ctr_unique_segments": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
+    "ctr_unique_segments": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
     "ctr_shard_counts": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp]),
     "ctr_embed_bwd_partials": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_vp, c_i64, c_vp,
                                        c_vp, c_vp, c_vp, c_vp, c_vp, c_vp]),
@@ -131,7 +134,9 @@ _PROTOS = {
     "ctr_peer_reduce_sum": (c_i32, [c_vp, c_vp, _P_RT, c_i64, c_vp]),
     "ctr_gather_rows_push": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_vp, c_i64, c_i32, c_i32, c_i32, _P_RT]),
     "ctr_embed_bwd_finalize_push": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, _P_RT]),
-    "ctr_merge_sorted_segments": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_i32, c_vp, c_vp]),
+    "ctr_merge_sorted_segments": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_vp, c_i32, c_vp, c_vp, c_vp]),
+    "ctr_peer_plan_routes": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i64, c_i64, c_vp, c_vp]),
+    "ctr_zero_row_at": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp]),
     "ctr_debug_gemm_trace": (c_i32, [c_vp, c_i32]),
     "ctr_invert_perm": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp]),
     "ctr_parse_lines": (c_i32, [c_vp, c_i64, c_i32, c_i32, c_i32, c_i32, c_i32, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp,

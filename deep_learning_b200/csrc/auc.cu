@@ -73,7 +73,7 @@ extern "C" int ctr_auc(ctr_handle* h, ctr_stream s, const float* scores, const f
     int rc = ctr_sort_pairs(h, s, keys, idx, n, 32, sort_ws, sort_bytes);
     if (rc) return rc;
     // uniq output is not needed: alias it onto the (now free) sort workspace head
-    rc = ctr_unique_segments(h, s, keys, n, (uint32_t*) sort_ws, seg, uidx, ngroups, blk, (n / 2048 + 4) * 4);
+    rc = ctr_unique_segments(h, s, keys, n, (uint32_t*) sort_ws, seg, uidx, ngroups, blk, (n / 2048 + 4) * 4, nullptr);
     if (rc) return rc;
     rc = ctr_scan_pos_labels(h, st, labels, idx, n, cum, blk);
     if (rc) return rc;

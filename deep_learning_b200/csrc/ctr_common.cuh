@@ -61,7 +61,8 @@ __device__ __forceinline__ void ctr_flag_bad_id(uint32_t* status, int field) {
 }
 // optimizer kernels: true while the engine's status words say the step must not move the weights
 __device__ __forceinline__ bool ctr_guard_tripped(const uint32_t* guard) {
-    return guard && (guard[CTR_STATUS_STEP_BARRIER] | guard[CTR_STATUS_PLAN_BARRIER] | guard[CTR_STATUS_BAD_ID]) != 0u;
+    return guard && (guard[CTR_STATUS_STEP_BARRIER] | guard[CTR_STATUS_PLAN_BARRIER] | guard[CTR_STATUS_BAD_ID] |
+                     guard[CTR_STATUS_EXCHANGE]) != 0u;
 }
 
 __device__ __forceinline__ int64_t ctr_load_id(const void* ids, int id_bytes, int64_t i) {

@@ -159,7 +159,10 @@ embed_bwd_finalize_kernel(const uint32_t* __restrict__ seg_start, const uint32_t
                           int width, int gs, const float* __restrict__ part, float* __restrict__ grads, const PeerRoute rt) {
     int64_t U = *n_unique;
     if (U > n_max) U = n_max;
-    if (PUSH && U > (int64_t) rt.seg_end[rt.world - 1]) U = rt.seg_end[rt.world - 1];
+    if (PUSH) {
+        const int64_t routed = route_total(rt, (int64_t) rt.seg_end[rt.world - 1]);     // runs past it = the padding key
+        if (U > routed) U = routed;
+    }
     auto out_row = [&](int64_t u) -> float* { return PUSH ? route_row(rt, (uint32_t) u, gs) : grads + u * gs; };
     const int nq = (width + 3) >> 2;                 // column quads per row
     const int64_t total = U * nq;
@@ -727,7 +730,7 @@ extern "C" int ctr_embed_bwd_finalize(ctr_handle* h, ctr_stream s, const uint32_
     CTR_REQUIRE(h, grad_stride % 4 == 0 && ((reinterpret_cast<uintptr_t>(part) | reinterpret_cast<uintptr_t>(grads)) & 15) == 0,
                 "embed_bwd_finalize: grad_stride must be a multiple of 4 and part / grads 16-byte aligned");
     embed_bwd_finalize_kernel<false><<<grid_for(h, n_max * ((width + 3) / 4)), 256, 0, ctr_st(s)>>>(
-        seg_start, n_unique, n_max, width, grad_stride, part, grads, PeerRoute());
+        seg_start, n_unique, n_max, width, grad_stride, part, grads, PeerRoute{});
     CTR_CHECK_LAUNCH(h, "embed_bwd_finalize");
     return CTR_OK;
 }
@@ -740,9 +743,12 @@ extern "C" int ctr_embed_bwd_finalize_push(ctr_handle* h, ctr_stream s, const ui
     CTR_REQUIRE(h, rt->world >= 1 && rt->world <= CTR_MAX_PEERS && grad_stride % 4 == 0 && rt->dst_off % 16 == 0 &&
                        (reinterpret_cast<uintptr_t>(part) & 15) == 0,
                 "embed_bwd_finalize_push: grad_stride must be a multiple of 4, buffers 16-byte aligned");
-    const int64_t U = rt->seg_end[rt->world - 1];
-    if (n_max == 0 || U == 0) return CTR_OK;
-    if (U < n_max) n_max = U;
+    if (!rt->dyn) {           // host-side route: the list length is known here
+        const int64_t U = rt->seg_end[rt->world - 1];
+        if (U == 0) return CTR_OK;
+        if (U < n_max) n_max = U;
+    }
+    if (n_max == 0) return CTR_OK;
     embed_bwd_finalize_kernel<true><<<grid_for(h, n_max * ((width + 3) / 4)), 256, 0, ctr_st(s)>>>(
         seg_start, n_unique, n_max, width, grad_stride, part, nullptr, make_route(rt));
     CTR_CHECK_LAUNCH(h, "embed_bwd_finalize_push");

@@ -101,6 +101,7 @@ __global__ void __launch_bounds__(256)
 gather_rows_push_kernel(const float* __restrict__ table, int table_stride, const uint32_t* __restrict__ idx, int64_t n,
                         uint32_t mask, int width, int ds, const PeerRoute rt) {
     const int nq = ds >> 2;
+    n = route_total(rt, n);
     const int64_t total = n * nq;
     const int64_t nthreads = (int64_t) gridDim.x * blockDim.x;
     for (int64_t t0 = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t0 < total; t0 += nthreads * GP_UN) {
@@ -150,8 +151,8 @@ extern "C" int ctr_gather_rows_push(ctr_handle* h, ctr_stream s, const float* ta
     CTR_REQUIRE(h, rt->world >= 1 && rt->world <= CTR_MAX_PEERS && dst_stride % 4 == 0 && table_stride % 4 == 0 &&
                        rt->dst_off % 16 == 0 && (reinterpret_cast<uintptr_t>(table) & 15) == 0,
                 "gather_rows_push: strides must be multiples of 4 floats, buffers 16-byte aligned");
-    CTR_REQUIRE(h, (int64_t) rt->seg_end[rt->world - 1] == n_rows, "gather_rows_push: route does not cover the request list");
-    if (n_rows == 0) return CTR_OK;
+    CTR_REQUIRE(h, rt->dyn || (int64_t) rt->seg_end[rt->world - 1] == n_rows, "gather_rows_push: route does not cover the request list");
+    if (n_rows == 0) return CTR_OK;      // (with a device route block n_rows is the capacity of the request list)
     uint32_t mask = (idx_mask_bits <= 0 || idx_mask_bits >= 32) ? 0xFFFFFFFFu : ((1u << idx_mask_bits) - 1u);
     int64_t blocks = ctr_cdiv(n_rows * (dst_stride / 4), 256 * GP_UN);
     int64_t cap = (int64_t) h->sm_count * 8;
@@ -166,6 +167,7 @@ extern "C" int ctr_gather_rows_push(ctr_handle* h, ctr_stream s, const float* ta
 // rows of 32-bit words -> their routed position in the owning peer's buffer (the id-plan key exchange: width 1)
 __global__ void __launch_bounds__(256)
 push_rows_kernel(const uint32_t* __restrict__ src, int64_t n, int width, const PeerRoute rt) {
+    n = route_total(rt, n);
     const int64_t total = n * width;
     for (int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t) gridDim.x * blockDim.x) {
         const int64_t i = t / width;
@@ -209,7 +211,7 @@ extern "C" int ctr_peer_push_rows(ctr_handle* h, ctr_stream s, const uint32_t* s
                                   const ctr_peer_route* rt) {
     CTR_REQUIRE(h, src && route_ok(rt) && width > 0 && n_rows >= 0 && n_rows < (1ll << 32) && rt->dst_off % 4 == 0,
                 "peer_push_rows: bad args");
-    CTR_REQUIRE(h, (int64_t) rt->seg_end[rt->world - 1] == n_rows, "peer_push_rows: route does not cover the list");
+    CTR_REQUIRE(h, rt->dyn || (int64_t) rt->seg_end[rt->world - 1] == n_rows, "peer_push_rows: route does not cover the list");
     if (n_rows == 0) return CTR_OK;
     int64_t blocks = ctr_cdiv(n_rows * width, 256);
     const int64_t cap = (int64_t) h->sm_count * 4;
@@ -238,14 +240,78 @@ extern "C" int ctr_peer_reduce_sum(ctr_handle* h, ctr_stream s, const ctr_peer_r
     return CTR_OK;
 }
 
+// ------------------------------------------------------------------------------------------------ device-side routing
+// one warp: lane p / lane o walks the (tiny) count matrix.  See ctr_peer_plan_routes in the header for the layout.
+__global__ void __launch_bounds__(32)
+plan_routes_kernel(const uint32_t* __restrict__ mat, int world, int rank, int64_t req_cap, int64_t grad_cap,
+                   uint32_t* __restrict__ plan, uint32_t* __restrict__ status) {
+    const int l = threadIdx.x;
+    uint32_t recv = 0, send = 0, v_dst = 0, g_dst = 0, col = 0;
+    if (l < world) {
+        recv = mat[l * world + rank];                      // rows peer l requests of me
+        send = mat[rank * world + l];                      // rows I request of owner l
+        for (int o = 0; o < rank; ++o) v_dst += mat[l * world + o];       // where my rows start in peer l's unique list
+        for (int p = 0; p < rank; ++p) g_dst += mat[p * world + l];       // where my rows start in owner l's receive buffer
+        for (int p = 0; p < world; ++p) col += mat[p * world + l];        // everything owner l will receive
+    }
+    uint32_t r_inc = recv, s_inc = send;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t a = __shfl_up_sync(0xffffffffu, r_inc, o), b = __shfl_up_sync(0xffffffffu, s_inc, o);
+        if (l >= o) { r_inc += a; s_inc += b; }
+    }
+    const uint32_t n_req = __shfl_sync(0xffffffffu, r_inc, world - 1), U = __shfl_sync(0xffffffffu, s_inc, world - 1);
+    if (l < CTR_MAX_PEERS) {
+        plan[CTR_PLAN_VEC + l] = l < world ? r_inc : n_req;
+        plan[CTR_PLAN_VEC + 16 + l] = v_dst;
+        plan[CTR_PLAN_GRAD + l] = l < world ? s_inc : U;
+        plan[CTR_PLAN_GRAD + 16 + l] = g_dst;
+    }
+    if (l == 0) {
+        plan[CTR_PLAN_VEC + 32] = n_req;
+        plan[CTR_PLAN_GRAD + 32] = U;
+        plan[CTR_PLAN_NREQ] = n_req;
+        plan[CTR_PLAN_U] = U;
+    }
+    // the same matrix on every rank => the same verdict on every rank
+    const bool over = l < world && ((int64_t) col > grad_cap || (int64_t) col > req_cap);
+    const uint32_t who = __ballot_sync(0xffffffffu, over);
+    if (l == 0 && who && status) status[CTR_STATUS_EXCHANGE] = (uint32_t) __ffs(who);
+}
+
+extern "C" int ctr_peer_plan_routes(ctr_handle* h, ctr_stream s, const uint32_t* mat, int world, int rank, int64_t req_cap,
+                                    int64_t grad_cap, uint32_t* plan, uint32_t* status) {
+    CTR_REQUIRE(h, mat && plan && world >= 1 && world <= CTR_MAX_PEERS && rank >= 0 && rank < world && req_cap >= 0 && grad_cap >= 0,
+                "peer_plan_routes: bad args");
+    plan_routes_kernel<<<1, 32, 0, ctr_st(s)>>>(mat, world, rank, req_cap, grad_cap, plan, status);
+    CTR_CHECK_LAUNCH(h, "peer_plan_routes");
+    return CTR_OK;
+}
+
+__global__ void zero_row_at_kernel(float* __restrict__ buf, int stride, int width, const uint32_t* __restrict__ row_index) {
+    float* row = buf + (int64_t) *row_index * stride;
+    for (int j = threadIdx.x; j < width; j += blockDim.x) row[j] = 0.f;
+}
+
+extern "C" int ctr_zero_row_at(ctr_handle* h, ctr_stream s, float* buf, int stride, int width, const uint32_t* row_index) {
+    CTR_REQUIRE(h, buf && row_index && width > 0 && stride >= width, "zero_row_at: bad args");
+    zero_row_at_kernel<<<1, 64, 0, ctr_st(s)>>>(buf, stride, width, row_index);
+    CTR_CHECK_LAUNCH(h, "zero_row_at");
+    return CTR_OK;
+}
+
 // ------------------------------------------------------------------------------------------------ merge of sorted segments
 struct SegEnds {
     uint32_t end[CTR_MAX_PEERS];
 };
 
 __global__ void __launch_bounds__(256)
-merge_segments_kernel(const uint32_t* __restrict__ keys, uint32_t n, const SegEnds se, int world,
-                      uint32_t* __restrict__ out_keys, uint32_t* __restrict__ out_idx) {
+merge_segments_kernel(const uint32_t* __restrict__ keys, uint32_t n, SegEnds se, int world,
+                      uint32_t* __restrict__ out_keys, uint32_t* __restrict__ out_idx, const uint32_t* __restrict__ se_dev) {
+    if (se_dev) {                 // split sizes known to the device only
+        for (int q = 0; q < CTR_MAX_PEERS; ++q) se.end[q] = __ldg(se_dev + (q < world ? q : world - 1));
+        n = se.end[world - 1];
+    }
     for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
         int p = 0;
         uint32_t pb = 0;
@@ -278,17 +344,17 @@ merge_segments_kernel(const uint32_t* __restrict__ keys, uint32_t n, const SegEn
 }
 
 extern "C" int ctr_merge_sorted_segments(ctr_handle* h, ctr_stream s, const uint32_t* keys, int64_t n, const uint32_t* seg_end,
-                                         int world, uint32_t* out_keys, uint32_t* out_idx) {
-    CTR_REQUIRE(h, keys && seg_end && out_keys && out_idx && world >= 1 && world <= CTR_MAX_PEERS && n >= 0 && n < (1ll << 32),
-                "merge_sorted_segments: bad args");
-    CTR_REQUIRE(h, (int64_t) seg_end[world - 1] == n, "merge_sorted_segments: segments do not cover the list");
+                                         int world, uint32_t* out_keys, uint32_t* out_idx, const uint32_t* seg_end_dev) {
+    CTR_REQUIRE(h, keys && (seg_end || seg_end_dev) && out_keys && out_idx && world >= 1 && world <= CTR_MAX_PEERS && n >= 0 &&
+                       n < (1ll << 32), "merge_sorted_segments: bad args");
+    CTR_REQUIRE(h, seg_end_dev || (int64_t) seg_end[world - 1] == n, "merge_sorted_segments: segments do not cover the list");
     if (n == 0) return CTR_OK;
     SegEnds se;
-    for (int p = 0; p < CTR_MAX_PEERS; ++p) se.end[p] = p < world ? seg_end[p] : (uint32_t) n;
+    for (int p = 0; p < CTR_MAX_PEERS; ++p) se.end[p] = seg_end_dev ? 0u : (p < world ? seg_end[p] : (uint32_t) n);
     int64_t blocks = ctr_cdiv(n, 256);
     int64_t cap = (int64_t) h->sm_count * 8;
     if (blocks > cap) blocks = cap;
-    merge_segments_kernel<<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(keys, (uint32_t) n, se, world, out_keys, out_idx);
+    merge_segments_kernel<<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(keys, (uint32_t) n, se, world, out_keys, out_idx, seg_end_dev);
     CTR_CHECK_LAUNCH(h, "merge_sorted_segments");
     return CTR_OK;
 }

@@ -463,8 +463,9 @@ __device__ __forceinline__ uint32_t uq_flags(const uint32_t* __restrict__ keys, 
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS)
-unique_count_kernel(const uint32_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ blk) {
+unique_count_kernel(const uint32_t* __restrict__ keys, int64_t n, uint32_t* __restrict__ blk, const uint32_t* __restrict__ n_dev) {
     __shared__ uint32_t wtot[SCAN_THREADS / 32];
+    if (n_dev) n = (int64_t) *n_dev < n ? (int64_t) *n_dev : n;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     uint32_t bal[UQ_ROUNDS], k[UQ_ROUNDS];
     const uint32_t t = uq_flags(keys, n, (int64_t) blockIdx.x * UQ_TILE + w * (32 * UQ_ROUNDS), lane, bal, k);
@@ -480,8 +481,10 @@ unique_count_kernel(const uint32_t* __restrict__ keys, int64_t n, uint32_t* __re
 
 __global__ void __launch_bounds__(SCAN_THREADS)
 unique_emit_kernel(const uint32_t* __restrict__ keys, int64_t n, const uint32_t* __restrict__ blk, uint32_t* __restrict__ uniq,
-                   uint32_t* __restrict__ seg_start, uint32_t* __restrict__ uidx, uint32_t* __restrict__ n_unique) {
+                   uint32_t* __restrict__ seg_start, uint32_t* __restrict__ uidx, uint32_t* __restrict__ n_unique,
+                   const uint32_t* __restrict__ n_dev) {
     __shared__ uint32_t wtot[SCAN_THREADS / 32], red[SCAN_THREADS / 32];
+    if (n_dev) n = (int64_t) *n_dev < n ? (int64_t) *n_dev : n;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     // flags of the tiles before this one
     uint32_t before = 0;
@@ -530,7 +533,8 @@ unique_emit_kernel(const uint32_t* __restrict__ keys, int64_t n, const uint32_t*
 }  // namespace
 
 extern "C" int ctr_unique_segments(ctr_handle* h, ctr_stream s, const uint32_t* sorted_keys, int64_t n, uint32_t* uniq,
-                                   uint32_t* seg_start, uint32_t* uidx, uint32_t* n_unique, void* ws, int64_t ws_bytes) {
+                                   uint32_t* seg_start, uint32_t* uidx, uint32_t* n_unique, void* ws, int64_t ws_bytes,
+                                   const uint32_t* n_dev) {
     CTR_REQUIRE(h, sorted_keys && uniq && seg_start && uidx && n_unique && ws && n >= 0, "unique_segments: bad args");
     cudaStream_t st = ctr_st(s);
     if (n == 0) {
@@ -541,9 +545,9 @@ extern "C" int ctr_unique_segments(ctr_handle* h, ctr_stream s, const uint32_t* 
     int nblk = (int) ctr_cdiv(n, UQ_TILE);
     if (ws_bytes < (int64_t) (nblk + 2) * 4) return ctr_fail(h, CTR_E_WORKSPACE, "unique_segments: ws too small");
     uint32_t* blk = (uint32_t*) ws;
-    unique_count_kernel<<<nblk, SCAN_THREADS, 0, st>>>(sorted_keys, n, blk);
+    unique_count_kernel<<<nblk, SCAN_THREADS, 0, st>>>(sorted_keys, n, blk, n_dev);
     h->launches += 1;
-    unique_emit_kernel<<<nblk, SCAN_THREADS, 0, st>>>(sorted_keys, n, blk, uniq, seg_start, uidx, n_unique);
+    unique_emit_kernel<<<nblk, SCAN_THREADS, 0, st>>>(sorted_keys, n, blk, uniq, seg_start, uidx, n_unique, n_dev);
     CTR_CHECK_LAUNCH(h, "unique_segments");
     return CTR_OK;
 }

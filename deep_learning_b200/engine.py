@@ -217,7 +217,7 @@ class CtrEngine:
         self._status_ev.synchronize()
         self._status_pending = False
         st = self._status_host.tolist()
-        if not any(st[:3]):
+        if not any(st[:4]):
             self._steps_verified = self._steps_at_snap
             return
         # the status words are sticky and stop every optimizer kernel: no step since the last clean snapshot was applied,
@@ -231,6 +231,9 @@ class CtrEngine:
         if st[2]:
             raise _lib.CtrError("id out of range in column %d of cate_feats / wide_feats (table has %d rows): the step "
                                 "was not applied" % (st[2] - 1, self._id_limit()))
+        if st[3]:
+            raise _lib.CtrError("row exchange: owner %d would receive more rows than its buffers hold (capacity = one rank's "
+                                "lookups per step): the step was not applied" % (st[3] - 1))
         raise _lib.CtrError("peer barrier timed out waiting for rank %d: the step was not applied" % ((st[0] or st[1]) - 1))
 
     # the stream a step runs on is looked up ONCE per public call (torch.cuda.current_stream costs ~7 us of host time, and a
@@ -752,7 +755,7 @@ class CtrEngine:
                s.cont_base, self.n_extra, 1, 0, key_bits, self._id_limit(), ptr(self.status), ptr(self.keys), ptr(self.perm),
                ws, wsn)
         h.call("ctr_unique_segments", st, ptr(self.keys), n, ptr(self.uniq), ptr(self.seg_start), ptr(self.uidx),
-               ptr(self.n_unique), ws, wsn)
+               ptr(self.n_unique), ws, wsn, None)
         self.ev_sorted.record(self.side)
         self._sort_wide(B, st)
 
@@ -766,7 +769,7 @@ class CtrEngine:
             h.call("ctr_sort_ids", st, ptr(self.wide), self.id_bytes, B, s.wide_fields, 0, s.wide_fields, 0, 0, 0, 0, 1, 0,
                    max(1, int(rows - 1).bit_length()), rows, ptr(self.status), ptr(self.w_keys), ptr(self.w_perm), ws, wsn)
             h.call("ctr_unique_segments", st, ptr(self.w_keys), nw, ptr(self.w_uniq), ptr(self.w_seg_start),
-                   ptr(self.w_uidx), ptr(self.w_n_unique), ws, wsn)
+                   ptr(self.w_uidx), ptr(self.w_n_unique), ws, wsn, None)
             self.ev_sorted_w.record(self.side if st == self.side.cuda_stream else self._main_stream())
 
     def _wdl_wide_grad(self, B: int) -> None:

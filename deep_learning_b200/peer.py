@@ -51,11 +51,14 @@ class PeerSlab:
         typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
         return torch.as_tensor(_Region(self, self.own + int(offset), shape, typestr), device=self.device)
 
-    def route(self, seg_end: Sequence[int], dst_row: Sequence[int], dst_off: int) -> PeerRoute:
+    def route(self, seg_end: Sequence[int], dst_row: Sequence[int], dst_off: int, dyn: int = 0) -> PeerRoute:
+        """placement of a routed list in the peers' buffers at byte offset dst_off; `dyn` (device address of a route block
+        written by ctr_peer_plan_routes) makes the kernels take segment ends / destination rows from the device"""
         rt = PeerRoute()
         rt.world, rt.rank, rt.dst_off = self.world, self.rank, int(dst_off)
         for p in range(self.world):
             rt.slab[p], rt.seg_end[p], rt.dst_row[p] = self.ptrs[p], int(seg_end[p]), int(dst_row[p])
+        rt.dyn = int(dyn) if dyn else None
         return rt
 
     def close(self) -> None:

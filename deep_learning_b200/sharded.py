@@ -24,7 +24,7 @@ import torch.distributed as dist
 
 from . import shard as _shard
 from .comm import as_comm
-from ._lib import AdamHP, EmbedCfg, ptr
+from ._lib import AdamHP, EmbedCfg, PLAN_GRAD, PLAN_NREQ, PLAN_U, PLAN_VEC, PLAN_WORDS, ptr
 from .peer import PeerSlab
 from .engine import CtrEngine, _ALIGN, _ru
 from .spec import ModelSpec
@@ -43,6 +43,7 @@ class _IdPlan:
         self.seg_start = torch.zeros(n + 2, **u32)
         self.n_unique = torch.zeros(1, **u32)
         self.counts = torch.zeros(eng.world, **u32)
+        self.plan_dev = torch.zeros(PLAN_WORDS, **u32)     # routes / n_req / U as ctr_peer_plan_routes leaves them
         self.counts_host = torch.zeros(eng.world * eng.world + 2, dtype=torch.int32).pin_memory()   # matrix + 2 status words
         self.route_v = self.route_g = self.route_k = None
         self.ws_sort = torch.zeros(_ru(max(eng.h.query("ctr_sort_ws_bytes", n), 4 * (n // 2048 + 8)), 256),
@@ -68,9 +69,18 @@ class _IdPlan:
             self.o_keys, self.o_idx, self.o_uniq, self.o_uidx = (torch.zeros(cap, **u32) for _ in range(4))
             self.o_seg = torch.zeros(cap + 2, **u32)
             self.o_nuniq = torch.zeros(1, **u32)
-            self.o_ws = torch.zeros(_ru(max(eng.h.query("ctr_sort_ws_bytes", cap), 4 * (cap // 2048 + 8)), 256),
-                                    dtype=torch.uint8, device=eng.dev)
+            self.o_ws = torch.zeros(_ru(4 * (cap // 2048 + 8), 256), dtype=torch.uint8, device=eng.dev)
         self.cap = cap
+
+    def bind_device_routes(self, eng: "ShardedCtrEngine") -> None:
+        """peer mode: the three routes of this plan slot, built ONCE -- slab pointers and buffer offsets are static, segment
+        ends and destination rows come from the plan block on the device (no host read of the split sizes)"""
+        base = self.plan_dev.data_ptr()
+        z = [0] * eng.world
+        self.route_v = eng.slab.route(z, z, eng._rows_off, dyn=base + 4 * PLAN_VEC)
+        self.route_g = eng.slab.route(z, z, eng._g_off, dyn=base + 4 * PLAN_GRAD)
+        self.route_k = eng.slab.route(z, z, eng._req_off[self.slot], dyn=base + 4 * PLAN_GRAD)   # keys travel like the gradients
+        self.ensure_owner(eng, eng._req_cap)
 
 
 class ShardedCtrEngine(CtrEngine):
@@ -135,12 +145,29 @@ class ShardedCtrEngine(CtrEngine):
         else:
             self.rows_recv = torch.zeros(self.n_max + 1, self.wire, **f32)
         self.plans = [_IdPlan(self, 0), _IdPlan(self, 1)]
+        if self.exchange_mode == "peer":
+            for pl in self.plans:
+                pl.bind_device_routes(self)
         self.cont_buf = torch.zeros(max(s.C, 1), self.wire, **f32)
         self.grads_send = (torch.zeros(max(self.n_max, 1), self.wire, **f32)
                            if self.train_mode and self.exchange_mode == "nccl" else None)
         self._row_cap = 0
         self._ensure_rows(self.n_max)
-        self.U = self.n_req = 0
+
+    @property
+    def U(self) -> int:
+        """unique rows of the current batch on this rank (padding run excluded).  Peer mode: only the device knows it
+        during the step; this reads it back (a host wait -- for tests and reports, never in the step)"""
+        if self.cur is None:
+            return 0
+        return int(self.cur.plan_dev[PLAN_U].item()) if self.cur.U is None else int(self.cur.U)
+
+    @property
+    def n_req(self) -> int:
+        """rows the peers requested of this rank for the current batch"""
+        if self.cur is None:
+            return 0
+        return int(self.cur.plan_dev[PLAN_NREQ].item()) if self.cur.n_req is None else int(self.cur.n_req)
 
     def _ensure_rows(self, n_req: int) -> None:
         """owner-side float staging (vectors out, gradients in) grows with the largest request seen"""
@@ -154,7 +181,8 @@ class ShardedCtrEngine(CtrEngine):
         if self.train_mode:
             if not peer:
                 self.g_recv = torch.zeros(cap, self.wire, **f32)
-            self.g_own = torch.zeros(cap, self.wire, **f32)
+            if not peer or os.environ.get("CTR_OWNER_UPDATE", "fused") != "fused":
+                self.g_own = torch.zeros(cap, self.wire, **f32)
         self._row_cap = cap
 
     # ---- layout hooks ------------------------------------------------------------------------------------------
@@ -194,28 +222,46 @@ class ShardedCtrEngine(CtrEngine):
                s.cont_base, self.n_extra, self.world, sp.local_bits, sp.key_bits, int(s.table_rows), ptr(self.status),
                ptr(pl.keys), ptr(pl.perm), ws, wsn)
         h.call("ctr_unique_segments", st, ptr(pl.keys), n, ptr(pl.uniq), ptr(pl.seg_start), ptr(pl.uidx),
-               ptr(pl.n_unique), ws, wsn)
+               ptr(pl.n_unique), ws, wsn, None)
         h.call("ctr_shard_counts", st, ptr(pl.uniq), ptr(pl.n_unique), self.world, sp.local_bits, ptr(pl.counts))
         h.call("ctr_invert_perm", st, ptr(pl.perm), ptr(pl.uidx), n, ptr(pl.inv))
         W = self.world
+        if self.exchange_mode == "peer":
+            # exchange #1a without a collective: my counts row goes into every peer's matrix; one barrier later the whole
+            # matrix is in the own slab and ONE small kernel turns it into this rank's routes, n_req and U -- on the device.
+            # The host never reads the split sizes: nothing in the step waits for the GPU, so the host can run ahead
+            h.call("ctr_peer_bcast", st, ptr(pl.counts), W, C.byref(self._rt_counts[pl.slot]))
+            self._plan_barrier(st)
+            h.call("ctr_peer_plan_routes", st, ptr(self._mat_view[pl.slot]), W, self.rank, self._req_cap,
+                   self._g_cap if self.train_mode else self._req_cap, ptr(pl.plan_dev), ptr(self.status))
+            # exchange #1b: every requester stores its unique keys into the owner's request list
+            h.call("ctr_peer_push_rows", st, ptr(pl.uniq), n, 1, C.byref(pl.route_k))
+            self._plan_barrier(st)
+            if self.train_mode:
+                # every peer's slice is already ascending: a stable merge (equal rows keep peer order, so the owner's
+                # sum is order-fixed) replaces a radix sort of the request list
+                cap = self._req_cap
+                h.call("ctr_merge_sorted_segments", st, ptr(pl.req), cap, None, W, ptr(pl.o_keys), ptr(pl.o_idx),
+                       pl.plan_dev.data_ptr() + 4 * PLAN_VEC)
+                h.call("ctr_unique_segments", st, ptr(pl.o_keys), cap, ptr(pl.o_uniq), ptr(pl.o_seg), ptr(pl.o_uidx),
+                       ptr(pl.o_nuniq), ptr(pl.o_ws), pl.o_ws.numel(), pl.plan_dev.data_ptr() + 4 * PLAN_NREQ)
+            pl.ev_ready.record(stream)
+            pl.B, pl.U, pl.n_req = B, None, None
+            return
+        # CTR_EXCHANGE=nccl (the collective fallback): NCCL wants the split sizes on the host
         with torch.cuda.stream(stream):
-            if self.exchange_mode == "peer":
-                # exchange #1a without a collective: my counts row goes into every peer's matrix, one barrier later the
-                # whole matrix is in the own slab
-                h.call("ctr_peer_bcast", st, ptr(pl.counts), W, C.byref(self._rt_counts[pl.slot]))
-                self._plan_barrier(st)
-                pl.counts_host[:W * W].copy_(self._mat_view[pl.slot], non_blocking=True)
-            else:
-                mat = _shard.gather_counts(pl.counts, self.group_plan)     # exchange #1a: every rank learns every split
-                pl.counts_host[:W * W].copy_(mat.reshape(-1), non_blocking=True)
+            mat = _shard.gather_counts(pl.counts, self.group_plan)     # exchange #1a: every rank learns every split
+            pl.counts_host[:W * W].copy_(mat.reshape(-1), non_blocking=True)
             pl.counts_host[W * W:].copy_(self.peer_status, non_blocking=True)
             pl.ev_local.record(stream)
         pl.B = B
 
     def _build_exchange(self, pl: _IdPlan, stream: torch.cuda.Stream) -> None:
-        """host reads the split sizes (NCCL wants them on the host), then on `stream`: the key all-to-all and the
-        owner-side stable sort + run structure of the requested rows"""
+        """CTR_EXCHANGE=nccl only (the peer-memory path plans its routes on the device, see _build_local): the host reads
+        the split sizes, then on `stream`: the key all-to-all and the owner-side merge + run structure"""
         h, sp = self.h, self.plan
+        if self.exchange_mode == "peer":
+            return
         if self.host_prof is not None:
             import time
             t0 = time.perf_counter()
@@ -252,16 +298,15 @@ class ShardedCtrEngine(CtrEngine):
                 # every peer's slice is already ascending: a stable merge (equal rows keep peer order, so the owner's
                 # sum is order-fixed) replaces the radix sort of the request list
                 ends = (C.c_uint32 * self.world)(*vec[0])
-                h.call("ctr_merge_sorted_segments", st, ptr(pl.req), n_req, ends, self.world, ptr(pl.o_keys), ptr(pl.o_idx))
+                h.call("ctr_merge_sorted_segments", st, ptr(pl.req), n_req, ends, self.world, ptr(pl.o_keys), ptr(pl.o_idx), None)
                 h.call("ctr_unique_segments", st, ptr(pl.o_keys), n_req, ptr(pl.o_uniq), ptr(pl.o_seg), ptr(pl.o_uidx),
-                       ptr(pl.o_nuniq), ws, wsn)
+                       ptr(pl.o_nuniq), ws, wsn, None)
             pl.ev_ready.record(stream)
 
     def _activate(self, pl: _IdPlan) -> None:
         self.cur = pl
         self.ids, self.keys, self.perm, self.uidx, self.uniq = pl.ids, pl.keys, pl.perm, pl.uidx, pl.uniq
         self.seg_start, self.n_unique = pl.seg_start, pl.n_unique
-        self.U, self.n_req = pl.U, pl.n_req
 
     def _other_plan(self) -> _IdPlan:
         return self.plans[1] if self.cur is self.plans[0] else self.plans[0]
@@ -317,7 +362,7 @@ class ShardedCtrEngine(CtrEngine):
         self._build_local(pl, B, self.side)
         pl.batch_id, pl.in_flight, pl.on_side = id(next_batch), True, True
         pl.batch_obj = next_batch             # keeps the id from being recycled while the plan is pending
-        self._pending_exchange = pl
+        self._pending_exchange = pl if self.exchange_mode != "peer" else None
 
     def _end_step(self) -> None:
         super()._end_step()
@@ -335,29 +380,32 @@ class ShardedCtrEngine(CtrEngine):
         main = self._main_stream()
         if pl.on_side:
             main.wait_event(pl.ev_ready)
-        U, n_req = pl.U, pl.n_req
         self._mark("wait_plan")
-        self._ensure_rows(n_req)
         if self.exchange_mode == "peer":
             # owners read their [v | w] rows and store them straight into the requester's staging buffer, in the
-            # requester's unique-list order; the barrier is the only other launch of exchange #2
+            # requester's unique-list order; the barrier is the only other launch of exchange #2.  The request list's
+            # length and the placement come from the plan block on the device (the launch is sized by the capacity)
             if self._rows_dirty:                 # no gradient barrier since the last forward (predict): peers may still read
                 self._barrier(st)
-            if n_req:
-                h.call("ctr_gather_rows_push", st, ptr(self.table), s.table_stride, ptr(pl.req), n_req, sp.local_bits,
-                       s.row_width, self.wire, C.byref(pl.route_v))
+            h.call("ctr_gather_rows_push", st, ptr(self.table), s.table_stride, ptr(pl.req), self._req_cap, sp.local_bits,
+                   s.row_width, self.wire, C.byref(pl.route_v))
             self._mark("owner_gather")
             self._barrier(st)
             self._rows_dirty = True
+            self._mark("a2a_vectors")
+            # the run of padding ids (key 0xFFFFFFFF), if any, is unique index U: an all-zero staging row
+            h.call("ctr_zero_row_at", st, ptr(self.rows_recv), self.wire, self.wire, pl.plan_dev.data_ptr() + 4 * PLAN_U)
         else:
+            U, n_req = pl.U, pl.n_req
+            self._ensure_rows(n_req)
             # owners gather [v | w] rows; all-to-all #2 returns them in the requester's unique-list order
             if n_req:
                 h.call("ctr_gather_rows", st, ptr(self.table), s.table_stride, ptr(pl.req), None, n_req, sp.local_bits,
                        s.row_width, ptr(self.rows_send), self.wire)
             self._mark("owner_gather")
             _shard.exchange(self.rows_send[:n_req], pl.recv_counts, pl.send_counts, out=self.rows_recv, group=self.group)
-        self._mark("a2a_vectors")
-        self.rows_recv[U].zero_()    # the run of padding ids (key 0xFFFFFFFF), if any, is unique index U
+            self._mark("a2a_vectors")
+            self.rows_recv[U].zero_()    # the run of padding ids (key 0xFFFFFFFF), if any, is unique index U
         if s.use_fm and s.fm_cont and s.C:
             h.call("ctr_gather_rows", st, ptr(self.rows_recv), self.wire, ptr(pl.inv[B * s.ids_ld:]), None, s.C, 0,
                    s.row_width, ptr(self.cont_buf), self.wire)
@@ -381,6 +429,7 @@ class ShardedCtrEngine(CtrEngine):
             self._pending_exchange = None
         U, n_req = pl.U, pl.n_req
         if self.exchange_mode == "peer":
+            n_req = self._req_cap            # the device knows the real count (*o_nuniq); this only bounds the launch
             # one gradient row per unique key, summed and stored straight into its owner's receive buffer (exchange #3)
             h.call("ctr_embed_bwd_finalize_push", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
                    ptr(self.part), C.byref(pl.route_g))
@@ -396,6 +445,7 @@ class ShardedCtrEngine(CtrEngine):
         self._mark("a2a_grads")
         if not n_req:
             return
+        self._ensure_rows(n_req)
         if os.environ.get("CTR_OWNER_UPDATE", "fused") == "fused":
             # sum of the peers' contributions (fixed peer order) + TF1 Adam on the owned row, one launch
             h.call("ctr_adam_rows_gathered", st, ptr(pl.o_uniq), ptr(pl.o_nuniq), n_req, sp.local_bits, ptr(self.g_recv),

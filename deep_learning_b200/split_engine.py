@@ -97,13 +97,13 @@ class SplitFmEngine(CtrEngine):
         h.call("ctr_sort_ids", st, ptr(self.ids), self.id_bytes, B, s.ids_ld, 0, s.Fc, s.C, 1, 1, max(s.C - 1, 0), 1, 0, key_bits,
                int(s.table_rows), ptr(self.status), ptr(self.keys), ptr(self.perm), ws, wsn)
         h.call("ctr_unique_segments", st, ptr(self.keys), nA, ptr(self.ukeys), ptr(self.seg_start), ptr(self.uidx),
-               ptr(self.n_unique), ws, wsn)
+               ptr(self.n_unique), ws, wsn, None)
         # list B: deep lookups at the raw id, id 0 dropped
         wsb, wsbn = ptr(self.ws_b), self.ws_b.numel()
         h.call("ctr_sort_ids", st, ptr(self.ids), self.id_bytes, B, s.ids_ld, 0, s.Fc, 0, 1, 0, 0, 1, 0, key_bits,
                int(s.table_rows), ptr(self.status), ptr(self.keys_b), ptr(self.perm_b), wsb, wsbn)
         h.call("ctr_unique_segments", st, ptr(self.keys_b), nB, ptr(self.ukeys[self.nA_cap:]), ptr(self.seg_b), ptr(self.uidx_b),
-               ptr(self.nuniq_b), wsb, wsbn)
+               ptr(self.nuniq_b), wsb, wsbn, None)
         self.ev_sorted.record(self.side)
 
     # ---- backward + update (dense part as CtrEngine.backward_and_update) ---------------------------------------------------
@@ -153,9 +153,9 @@ class SplitFmEngine(CtrEngine):
         h.call("ctr_embed_bwd_finalize", st, ptr(self.seg_b), ptr(self.nuniq_b), nB, s.grad_width, gs, ptr(self.part_b),
                ptr(self.gcat[self.nA_cap:]))
         # rows reached through both lists: merge the two sorted key lists, sum per row, ONE TF1 Adam step per row
-        h.call("ctr_merge_sorted_segments", st, ptr(self.ukeys), nT, self.ends, 2, ptr(self.m_keys), ptr(self.m_idx))
+        h.call("ctr_merge_sorted_segments", st, ptr(self.ukeys), nT, self.ends, 2, ptr(self.m_keys), ptr(self.m_idx), None)
         h.call("ctr_unique_segments", st, ptr(self.m_keys), nT, ptr(self.o_uniq), ptr(self.o_seg), ptr(self.o_uidx),
-               ptr(self.o_nuniq), ptr(self.ws_m), self.ws_m.numel())
+               ptr(self.o_nuniq), ptr(self.ws_m), self.ws_m.numel(), None)
         h.call("ctr_adam_rows_gathered", st, ptr(self.o_uniq), ptr(self.o_nuniq), nT, 0, ptr(self.gcat), ptr(self.m_idx),
                ptr(self.o_seg), gs, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
                self.rows_local, ptr(self.touched), self._fm_w2(), s.k, hp)

@@ -81,8 +81,8 @@ typedef struct ctr_embed_cfg {
 
 /* Device status words shared by the kernels of one engine (all zero = healthy).  Kernels only ever set them; the host
  * clears them.  The optimizer entry points take the same array as ctr_adam_hp.guard and leave every weight untouched
- * while word 0, 1 or 2 is non-zero: a batch with a bad id or a step whose peer barrier timed out must not move the
- * model. */
+ * while any word is non-zero: a batch with a bad id, a step whose peer barrier timed out or an exchange that would
+ * overflow a buffer must not move the model. */
 #define CTR_STATUS_WORDS       4
 #define CTR_STATUS_STEP_BARRIER 0   /* 1 + rank that did not arrive (ctr_peer_barrier on the step's stream) */
 #define CTR_STATUS_PLAN_BARRIER 1   /* same, id-plan barriers */
@@ -228,10 +228,11 @@ int ctr_sort_ids(ctr_handle* h, ctr_stream s, const void* ids, int id_bytes, int
 int ctr_sort_pairs(ctr_handle* h, ctr_stream s, uint32_t* keys, uint32_t* vals, int64_t n, int key_bits,
                    void* ws, int64_t ws_bytes);
 /* run-length structure of sorted keys: uniq[u], seg_start[u] (seg_start[U] = n), uidx[i] = index of
- * the run containing i, *n_unique = U (device).  Bit-exact against numpy.unique. ws >= 4*(n/2048+2) B*/
+ * the run containing i, *n_unique = U (device).  Bit-exact against numpy.unique. ws >= 4*(n/2048+2) B.
+ * n_dev (device word or NULL): the element count when only the device knows it; n is then the capacity. */
 int ctr_unique_segments(ctr_handle* h, ctr_stream s, const uint32_t* sorted_keys, int64_t n,
                         uint32_t* uniq, uint32_t* seg_start, uint32_t* uidx, uint32_t* n_unique,
-                        void* ws, int64_t ws_bytes);
+                        void* ws, int64_t ws_bytes, const uint32_t* n_dev);
 /* counts[o] = number of unique keys owned by shard o (keys >> local_bits == o), o < n_shards;
  * keys equal to 0xFFFFFFFF (dropped) are not counted. */
 int ctr_shard_counts(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const uint32_t* n_unique,
@@ -399,7 +400,32 @@ typedef struct ctr_peer_route {
     uint32_t seg_end[CTR_MAX_PEERS];
     uint32_t dst_row[CTR_MAX_PEERS];
     int64_t  dst_off;
+    const uint32_t* dyn;               /* NULL, or a DEVICE route block of CTR_ROUTE_WORDS words written by
+                                          ctr_peer_plan_routes: [0,16) seg_end, [16,32) dst_row, [32] total rows.  When set,
+                                          the kernels take the placement (and the row count) from it and the host never
+                                          needs to know the split sizes: the sharded step has no host synchronisation */
 } ctr_peer_route;
+#define CTR_ROUTE_WORDS 48
+/* layout of the plan block ctr_peer_plan_routes writes (uint32 words) */
+#define CTR_PLAN_VEC    0     /* route of the vectors: source = rows peers requested of this rank (peer-major) */
+#define CTR_PLAN_GRAD   48    /* route of the gradients and of the requested keys: source = this rank's unique list */
+#define CTR_PLAN_NREQ   96    /* rows requested of this rank, all peers */
+#define CTR_PLAN_U      97    /* this rank's unique rows (padding run excluded) */
+#define CTR_PLAN_WORDS  128
+#define CTR_STATUS_EXCHANGE 3  /* status word: 1 + owner whose receive / request buffer would overflow */
+
+/* Device-side routing.  mat[p * world + o] = unique rows rank p requests of owner o (every rank holds the same matrix
+ * once the per-owner counts have been broadcast: ctr_peer_bcast + barrier).  Writes this rank's plan block:
+ *   vectors    seg_end = prefix sums of column `rank`, dst_row[p] = sum_{o < rank} mat[p][o]   (p's unique-list offset)
+ *   gradients  seg_end = prefix sums of row `rank`,    dst_row[o] = sum_{p < rank} mat[p][o]   (behind the ranks before)
+ * -- the layout an all_to_all_single with these split sizes would produce -- plus n_req and U.  If an owner would
+ * receive more than grad_cap rows, or this rank more than req_cap requests, status word CTR_STATUS_EXCHANGE is set
+ * (every rank sees the same matrix, so every rank reaches the same verdict) and the optimizer kernels stand down. */
+int ctr_peer_plan_routes(ctr_handle* h, ctr_stream s, const uint32_t* mat, int world, int rank, int64_t req_cap,
+                         int64_t grad_cap, uint32_t* plan, uint32_t* status);
+/* buf[row_index[0], :width] = 0 (row index read on the device: the all-zero staging row of the padding ids sits
+ * behind the unique rows, whose count only the device knows) */
+int ctr_zero_row_at(ctr_handle* h, ctr_stream s, float* buf, int stride, int width, const uint32_t* row_index);
 
 /* all-ranks barrier on `stream` (one 32-thread CTA): releases everything this rank stored into peer slabs before it,
  * and returns once every peer has done the same.  flags_off: byte offset of CTR_MAX_PEERS uint32 arrival words in
@@ -437,9 +463,10 @@ int ctr_embed_bwd_finalize_push(ctr_handle* h, ctr_stream s, const uint32_t* seg
 /* owner side of the gradient exchange: `keys` is a concatenation of `world` segments (peer-major, segment p ends at
  * seg_end[p], a HOST array), each ascending and duplicate-free (a slice of the requester's unique list).  Writes their
  * stable merge -- out_keys ascending, equal keys in peer order, out_idx[i] = position of that entry in `keys` -- by
- * ranking every entry with one binary search per segment: one launch instead of a radix sort of the list. */
+ * ranking every entry with one binary search per segment: one launch instead of a radix sort of the list.
+ * seg_end_dev (device, world words) replaces seg_end and n (then only a capacity for the launch) when non-NULL. */
 int ctr_merge_sorted_segments(ctr_handle* h, ctr_stream s, const uint32_t* keys, int64_t n, const uint32_t* seg_end,
-                              int world, uint32_t* out_keys, uint32_t* out_idx);
+                              int world, uint32_t* out_keys, uint32_t* out_idx, const uint32_t* seg_end_dev);
 
 /* ---- timing experiments (not part of the product path) -----------------------------------------------------
  * with CTR_GEMM_DBG & 8 in the environment the TF32 forward/dgrad GEMM records %globaltimer at its phase boundaries

@@ -30,7 +30,7 @@ def main():
             hd.call("ctr_sort_ids", st, ptr(ids[i]), 4, B, Fc, 0, Fc, 0, 0, Fc, C, world, lb, kb, 0, None, ptr(keys), ptr(perm), ptr(ws), wsn)
 
         def uniqf(i):
-            hd.call("ctr_unique_segments", st, ptr(keys), n, ptr(uniq), ptr(seg), ptr(uidx), ptr(nu), ptr(ws), wsn)
+            hd.call("ctr_unique_segments", st, ptr(keys), n, ptr(uniq), ptr(seg), ptr(uidx), ptr(nu), ptr(ws), wsn, None)
         for name, fn in (("ctr_sort_ids", sort), ("ctr_unique_segments", uniqf)):
             for i in range(4):
                 fn(i)

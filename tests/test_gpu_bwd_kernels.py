@@ -44,7 +44,7 @@ def _sort_runs(hd, ids_t, B, Fc, rows, n_extra=0, extra_base=0):
     seg = torch.zeros(n + 8, dtype=torch.int32, device="cuda")
     uidx = torch.zeros(n + 8, dtype=torch.int32, device="cuda")
     nun = torch.zeros(1, dtype=torch.int32, device="cuda")
-    hd.call("ctr_unique_segments", _st(), _ptr(keys), n, _ptr(uniq), _ptr(seg), _ptr(uidx), _ptr(nun), _ptr(ws), wsn)
+    hd.call("ctr_unique_segments", _st(), _ptr(keys), n, _ptr(uniq), _ptr(seg), _ptr(uidx), _ptr(nun), _ptr(ws), wsn, None)
     return n, keys, perm, uniq, seg, uidx, nun
 
 
@@ -158,7 +158,7 @@ def test_segment_sum_rows_in_run_order(hd):
     uidx = torch.zeros(n + 8, dtype=torch.int32, device="cuda")
     nun = torch.zeros(1, dtype=torch.int32, device="cuda")
     ws = torch.zeros(4 * (n // 2048 + 8) + 256, dtype=torch.uint8, device="cuda")
-    hd.call("ctr_unique_segments", _st(), _ptr(t_keys), n, _ptr(uniq), _ptr(seg), _ptr(uidx), _ptr(nun), _ptr(ws), ws.numel())
+    hd.call("ctr_unique_segments", _st(), _ptr(t_keys), n, _ptr(uniq), _ptr(seg), _ptr(uidx), _ptr(nun), _ptr(ws), ws.numel(), None)
     U = int(nun.item())
     dst = torch.zeros(U, stride, device="cuda")
     t_src = torch.from_numpy(src).cuda()
@@ -215,7 +215,7 @@ def test_adam_rows_gathered_equals_segment_sum_then_adam(hd, k, has_first, use_f
     uidx = torch.zeros(n + 8, dtype=torch.int32, device="cuda")
     nun = torch.zeros(1, dtype=torch.int32, device="cuda")
     ws = torch.zeros(4 * (n // 2048 + 8) + 256, dtype=torch.uint8, device="cuda")
-    hd.call("ctr_unique_segments", _st(), _ptr(t_keys), n, _ptr(uniq), _ptr(seg), _ptr(uidx), _ptr(nun), _ptr(ws), ws.numel())
+    hd.call("ctr_unique_segments", _st(), _ptr(t_keys), n, _ptr(uniq), _ptr(seg), _ptr(uidx), _ptr(nun), _ptr(ws), ws.numel(), None)
     t_src, t_perm = torch.from_numpy(src).cuda(), _u32(perm)
     w2 = torch.from_numpy(g.standard_normal(k).astype(np.float32)).cuda() if use_fm else None
     hp = AdamHP(lr_t=1e-2, beta1=0.9, beta2=0.999, eps=1e-8)

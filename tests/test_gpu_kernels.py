@@ -49,7 +49,7 @@ def test_unique_segments_bit_exact(hd, n):
     uniq, uidx = torch.zeros(n, dtype=torch.int32, device="cuda"), torch.zeros(n, dtype=torch.int32, device="cuda")
     seg = torch.zeros(n + 2, dtype=torch.int32, device="cuda"); nu = torch.zeros(1, dtype=torch.int32, device="cuda")
     ws = torch.zeros(4 * (n // 2048 + 8), dtype=torch.uint8, device="cuda")
-    hd.call("ctr_unique_segments", _st(), ptr(k), n, ptr(uniq), ptr(seg), ptr(uidx), ptr(nu), ptr(ws), ws.numel())
+    hd.call("ctr_unique_segments", _st(), ptr(k), n, ptr(uniq), ptr(seg), ptr(uidx), ptr(nu), ptr(ws), ws.numel(), None)
     ru, rstart, rinv = np.unique(keys, return_index=True, return_inverse=True)
     U = int(nu.item())
     assert U == len(ru)
@@ -78,7 +78,7 @@ def test_sort_ids_sharded_keys_and_counts(hd):
     assert np.array_equal(_u32(perm), np.arange(n, dtype=np.uint32)[order])
     uniq, uidx = torch.zeros(n, dtype=torch.int32, device="cuda"), torch.zeros(n, dtype=torch.int32, device="cuda")
     seg = torch.zeros(n + 2, dtype=torch.int32, device="cuda"); nu = torch.zeros(1, dtype=torch.int32, device="cuda")
-    hd.call("ctr_unique_segments", _st(), ptr(keys), n, ptr(uniq), ptr(seg), ptr(uidx), ptr(nu), ptr(ws), wsn)
+    hd.call("ctr_unique_segments", _st(), ptr(keys), n, ptr(uniq), ptr(seg), ptr(uidx), ptr(nu), ptr(ws), wsn, None)
     cnt = torch.zeros(N, dtype=torch.int32, device="cuda")
     hd.call("ctr_shard_counts", _st(), ptr(uniq), ptr(nu), N, bits, ptr(cnt))
     ru = np.unique(ref); ru = ru[ru != 0xFFFFFFFF]

@@ -69,7 +69,7 @@ def test_merge_sorted_segments_is_the_stable_sort(hd, world):
     ends = (C.c_uint32 * world)(*np.cumsum([len(s) for s in segs]).tolist())
     t_keys = torch.from_numpy(keys.view(np.int32)).cuda()
     ok, oi = torch.zeros(n, dtype=torch.int32, device="cuda"), torch.zeros(n, dtype=torch.int32, device="cuda")
-    hd.call("ctr_merge_sorted_segments", _st(), ptr(t_keys), n, ends, world, ptr(ok), ptr(oi))
+    hd.call("ctr_merge_sorted_segments", _st(), ptr(t_keys), n, ends, world, ptr(ok), ptr(oi), None)
     order = np.argsort(keys, kind="stable")
     assert np.array_equal(ok.cpu().numpy().view(np.uint32), keys[order])
     assert np.array_equal(oi.cpu().numpy().view(np.uint32), order.astype(np.uint32))
@@ -118,3 +118,103 @@ def test_barrier_single_rank_and_timeout_flag(hd):
     hd.call("ctr_peer_barrier", _st(), C.byref(rt), 0, 2, ptr(status), 50)
     assert int(status.item()) == 2                            # 1 + the missing peer's rank
     assert int(flags[1][0].item()) == 2                       # the own arrival was still published
+
+
+# ---- device-side routing (the sharded step without a host read of the split sizes) ---------------------------------------
+@pytest.mark.parametrize("world", [1, 2, 3, 8])
+def test_plan_routes_equals_the_host_formula(hd, world):
+    """ctr_peer_plan_routes == deep_learning_b200.shard.peer_routes for every rank of a random count matrix"""
+    from deep_learning_b200 import _lib
+    from deep_learning_b200._lib import ptr
+    from deep_learning_b200.shard import peer_routes
+    g = np.random.RandomState(40 + world)
+    mat = g.randint(0, 500, size=(world, world)).astype(np.int32)
+    mat[0, -1] = 0
+    t_mat = torch.from_numpy(mat.reshape(-1).copy()).cuda()
+    for rank in range(world):
+        plan = torch.full((_lib.PLAN_WORDS,), -1, dtype=torch.int32, device="cuda")
+        status = torch.zeros(_lib.STATUS_WORDS, dtype=torch.int32, device="cuda")
+        hd.call("ctr_peer_plan_routes", _st(), ptr(t_mat), world, rank, 10 ** 9, 10 ** 9, ptr(plan), ptr(status))
+        p = plan.cpu().numpy()
+        send, recv, vec, grad = peer_routes(mat.tolist(), rank)
+        assert p[_lib.PLAN_VEC:_lib.PLAN_VEC + world].tolist() == vec[0] and p[_lib.PLAN_VEC + 16:_lib.PLAN_VEC + 16 + world].tolist() == vec[1]
+        assert p[_lib.PLAN_GRAD:_lib.PLAN_GRAD + world].tolist() == grad[0] and p[_lib.PLAN_GRAD + 16:_lib.PLAN_GRAD + 16 + world].tolist() == grad[1]
+        assert p[_lib.PLAN_VEC + 32] == p[_lib.PLAN_NREQ] == sum(recv) and p[_lib.PLAN_GRAD + 32] == p[_lib.PLAN_U] == sum(send)
+        assert status.cpu().numpy().tolist() == [0, 0, 0, 0]
+    # capacity: the first owner that would receive more than the buffers hold is reported (1 + owner), same on every rank
+    worst = mat.sum(axis=0)
+    cap = int(np.sort(worst)[-1]) - 1
+    first = int(np.argmax(worst > cap))
+    for rank in range(world):
+        status = torch.zeros(_lib.STATUS_WORDS, dtype=torch.int32, device="cuda")
+        hd.call("ctr_peer_plan_routes", _st(), ptr(t_mat), world, rank, 10 ** 9, cap, ptr(plan), ptr(status))
+        assert status.cpu().numpy().tolist() == [0, 0, 0, 1 + first]
+
+
+def test_kernels_follow_a_device_route_block(hd):
+    """gather+push, key push, merge and run structure with placement and counts read from a plan block on the device
+    == the same calls with host-side routes"""
+    from deep_learning_b200 import _lib
+    from deep_learning_b200._lib import ptr
+    g = np.random.RandomState(77)
+    world, rank = 3, 1
+    mat = np.array([[40, 25, 0], [31, 7, 64], [0, 90, 12]], dtype=np.int32)
+    t_mat = torch.from_numpy(mat.reshape(-1).copy()).cuda()
+    plan = torch.zeros(_lib.PLAN_WORDS, dtype=torch.int32, device="cuda")
+    status = torch.zeros(_lib.STATUS_WORDS, dtype=torch.int32, device="cuda")
+    hd.call("ctr_peer_plan_routes", _st(), ptr(t_mat), world, rank, 10 ** 6, 10 ** 6, ptr(plan), ptr(status))
+    from deep_learning_b200.shard import peer_routes
+    send, recv, vec, grad = peer_routes(mat.tolist(), rank)
+    n_req, U, cap = sum(recv), sum(send), 400
+    # gather + push along the vector route
+    k, stride, wire, R, lb = 16, 24, 20, 500, 10
+    table = g.standard_normal((R, stride)).astype(np.float32)
+    req = g.randint(0, R, size=cap).astype(np.uint32)
+    t_table, t_req = torch.from_numpy(table).cuda(), torch.from_numpy(req.view(np.int32)).cuda()
+    rows_of = [int(max(vec[1])) + int(max(recv)) + 4] * world
+
+    def bufs():
+        return [torch.full((rows_of[p], wire), 7.0, device="cuda") for p in range(world)]
+    a, b = bufs(), bufs()
+    rt_host = _route(a, recv, vec[1], rank=rank)
+    hd.call("ctr_gather_rows_push", _st(), ptr(t_table), stride, ptr(t_req), n_req, lb, k + 1, wire, C.byref(rt_host))
+    rt_dev = _route(b, [0] * world, [0] * world, rank=rank)
+    rt_dev.dyn = plan.data_ptr() + 4 * _lib.PLAN_VEC
+    hd.call("ctr_gather_rows_push", _st(), ptr(t_table), stride, ptr(t_req), cap, lb, k + 1, wire, C.byref(rt_dev))
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+    # key push along the gradient route (width 1)
+    uniq = torch.arange(1000, 1000 + cap, dtype=torch.int32, device="cuda")
+    ka = [torch.full((300,), -1, dtype=torch.int32, device="cuda") for _ in range(world)]
+    kb = [t.clone() for t in ka]
+    rt_host = _route(ka, send, grad[1], rank=rank)
+    hd.call("ctr_peer_push_rows", _st(), ptr(uniq), U, 1, C.byref(rt_host))
+    rt_dev = _route(kb, [0] * world, [0] * world, rank=rank)
+    rt_dev.dyn = plan.data_ptr() + 4 * _lib.PLAN_GRAD
+    hd.call("ctr_peer_push_rows", _st(), ptr(uniq), cap, 1, C.byref(rt_dev))
+    for x, y in zip(ka, kb):
+        assert torch.equal(x, y)
+    # merge + run structure of a request list whose length only the device knows
+    segs = [np.sort(g.choice(5000, size=c, replace=False)).astype(np.uint32) for c in recv]
+    keys = np.concatenate(segs + [np.full(cap - n_req, 0xDEADBEEF, np.uint32)])
+    t_keys = torch.from_numpy(keys.view(np.int32)).cuda()
+    ok, oi = (torch.full((cap,), -1, dtype=torch.int32, device="cuda") for _ in range(2))
+    hd.call("ctr_merge_sorted_segments", _st(), ptr(t_keys), cap, None, world, ptr(ok), ptr(oi), plan.data_ptr() + 4 * _lib.PLAN_VEC)
+    order = np.argsort(keys[:n_req], kind="stable")
+    assert np.array_equal(ok.cpu().numpy().view(np.uint32)[:n_req], keys[:n_req][order])
+    assert np.array_equal(oi.cpu().numpy().view(np.uint32)[:n_req], order.astype(np.uint32))
+    assert np.all(ok.cpu().numpy()[n_req:] == -1)
+    uq, seg, uidx = (torch.full((cap + 2,), -1, dtype=torch.int32, device="cuda") for _ in range(3))
+    nu = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ws = torch.zeros(4096, dtype=torch.uint8, device="cuda")
+    hd.call("ctr_unique_segments", _st(), ptr(ok), cap, ptr(uq), ptr(seg), ptr(uidx), ptr(nu), ptr(ws), ws.numel(),
+            plan.data_ptr() + 4 * _lib.PLAN_NREQ)
+    want, first = np.unique(keys[:n_req], return_index=False), None
+    Uo = int(nu.item())
+    assert Uo == len(want) and np.array_equal(uq.cpu().numpy().view(np.uint32)[:Uo], want)
+    assert int(seg[Uo].item()) == n_req
+    # the all-zero staging row behind the unique rows
+    buf = torch.full((50, wire), 3.0, device="cuda")
+    hd.call("ctr_zero_row_at", _st(), ptr(buf), wire, wire, plan.data_ptr() + 4 * _lib.PLAN_U)
+    got = buf.cpu().numpy()
+    assert np.all(got[U] == 0.0) and np.all(np.delete(got, U, axis=0) == 3.0)

@@ -7,6 +7,7 @@ N=${1:-1}
 if [ "$N" = "1" ]; then
   python -m pytest tests -m gpu -q -s > gpurun_out/pytest.log 2>&1; echo "pytest rc $?" >> gpurun_out/pytest.log
   timeout 300 python tools/parity_report.py > gpurun_out/parity_report.txt 2>&1
+  timeout 600 python tests/loopback_parity.py > gpurun_out/parity_loopback.txt 2>&1
   timeout 400 python bench.py --steps 30 --warmup 5 > gpurun_out/bench_n1.json 2> gpurun_out/bench_n1.err
   timeout 200 python tests/phase_timing.py > gpurun_out/phases_n1.txt 2>&1
   timeout 300 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none -c 400 --csv \
