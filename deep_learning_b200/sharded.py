@@ -114,6 +114,9 @@ class ShardedCtrEngine(CtrEngine):
             raise ValueError("CTR_EXCHANGE must be peer or nccl")
         if self.comm.is_loopback:
             self.exchange_mode = "peer"       # the peer-memory path is the one under test; there is no NCCL between threads
+        # peer mode plans its routes on the device (no host read in the step); CTR_PLAN=host keeps the earlier host-side
+        # planning (one host wait per step for the split sizes) as an A/B and a fallback
+        self.device_plan = self.exchange_mode == "peer" and os.environ.get("CTR_PLAN", "device") == "device"
         self.peer_status = self.status[:2]      # [0] step barriers, [1] id-plan barriers: words of the engine's status array
         self._epoch, self._pepoch, self._rows_dirty = 0, 0, False
         if self.exchange_mode == "peer":
@@ -145,7 +148,7 @@ class ShardedCtrEngine(CtrEngine):
         else:
             self.rows_recv = torch.zeros(self.n_max + 1, self.wire, **f32)
         self.plans = [_IdPlan(self, 0), _IdPlan(self, 1)]
-        if self.exchange_mode == "peer":
+        if self.device_plan:
             for pl in self.plans:
                 pl.bind_device_routes(self)
         self.cont_buf = torch.zeros(max(s.C, 1), self.wire, **f32)
@@ -226,7 +229,7 @@ class ShardedCtrEngine(CtrEngine):
         h.call("ctr_shard_counts", st, ptr(pl.uniq), ptr(pl.n_unique), self.world, sp.local_bits, ptr(pl.counts))
         h.call("ctr_invert_perm", st, ptr(pl.perm), ptr(pl.uidx), n, ptr(pl.inv))
         W = self.world
-        if self.exchange_mode == "peer":
+        if self.device_plan:
             # exchange #1a without a collective: my counts row goes into every peer's matrix; one barrier later the whole
             # matrix is in the own slab and ONE small kernel turns it into this rank's routes, n_req and U -- on the device.
             # The host never reads the split sizes: nothing in the step waits for the GPU, so the host can run ahead
@@ -248,19 +251,25 @@ class ShardedCtrEngine(CtrEngine):
             pl.ev_ready.record(stream)
             pl.B, pl.U, pl.n_req = B, None, None
             return
-        # CTR_EXCHANGE=nccl (the collective fallback): NCCL wants the split sizes on the host
+        # host-side planning (CTR_PLAN=host, or CTR_EXCHANGE=nccl: NCCL wants the split sizes on the host)
         with torch.cuda.stream(stream):
-            mat = _shard.gather_counts(pl.counts, self.group_plan)     # exchange #1a: every rank learns every split
-            pl.counts_host[:W * W].copy_(mat.reshape(-1), non_blocking=True)
+            if self.exchange_mode == "peer":
+                h.call("ctr_peer_bcast", st, ptr(pl.counts), W, C.byref(self._rt_counts[pl.slot]))
+                self._plan_barrier(st)
+                pl.counts_host[:W * W].copy_(self._mat_view[pl.slot], non_blocking=True)
+            else:
+                mat = _shard.gather_counts(pl.counts, self.group_plan)     # exchange #1a: every rank learns every split
+                pl.counts_host[:W * W].copy_(mat.reshape(-1), non_blocking=True)
             pl.counts_host[W * W:].copy_(self.peer_status, non_blocking=True)
             pl.ev_local.record(stream)
         pl.B = B
 
     def _build_exchange(self, pl: _IdPlan, stream: torch.cuda.Stream) -> None:
-        """CTR_EXCHANGE=nccl only (the peer-memory path plans its routes on the device, see _build_local): the host reads
-        the split sizes, then on `stream`: the key all-to-all and the owner-side merge + run structure"""
+        """host-side planning only (CTR_PLAN=host / CTR_EXCHANGE=nccl; the default peer-memory path plans its routes on the
+        device, see _build_local): the host reads the split sizes, then on `stream`: the key exchange and the owner-side
+        merge + run structure"""
         h, sp = self.h, self.plan
-        if self.exchange_mode == "peer":
+        if self.device_plan:
             return
         if self.host_prof is not None:
             import time
@@ -362,7 +371,7 @@ class ShardedCtrEngine(CtrEngine):
         self._build_local(pl, B, self.side)
         pl.batch_id, pl.in_flight, pl.on_side = id(next_batch), True, True
         pl.batch_obj = next_batch             # keeps the id from being recycled while the plan is pending
-        self._pending_exchange = pl if self.exchange_mode != "peer" else None
+        self._pending_exchange = None if self.device_plan else pl
 
     def _end_step(self) -> None:
         super()._end_step()
@@ -387,14 +396,19 @@ class ShardedCtrEngine(CtrEngine):
             # length and the placement come from the plan block on the device (the launch is sized by the capacity)
             if self._rows_dirty:                 # no gradient barrier since the last forward (predict): peers may still read
                 self._barrier(st)
-            h.call("ctr_gather_rows_push", st, ptr(self.table), s.table_stride, ptr(pl.req), self._req_cap, sp.local_bits,
-                   s.row_width, self.wire, C.byref(pl.route_v))
+            n_list = self._req_cap if self.device_plan else pl.n_req
+            if n_list:
+                h.call("ctr_gather_rows_push", st, ptr(self.table), s.table_stride, ptr(pl.req), n_list, sp.local_bits,
+                       s.row_width, self.wire, C.byref(pl.route_v))
             self._mark("owner_gather")
             self._barrier(st)
             self._rows_dirty = True
             self._mark("a2a_vectors")
             # the run of padding ids (key 0xFFFFFFFF), if any, is unique index U: an all-zero staging row
-            h.call("ctr_zero_row_at", st, ptr(self.rows_recv), self.wire, self.wire, pl.plan_dev.data_ptr() + 4 * PLAN_U)
+            if self.device_plan:
+                h.call("ctr_zero_row_at", st, ptr(self.rows_recv), self.wire, self.wire, pl.plan_dev.data_ptr() + 4 * PLAN_U)
+            else:
+                self.rows_recv[pl.U].zero_()
         else:
             U, n_req = pl.U, pl.n_req
             self._ensure_rows(n_req)
@@ -429,7 +443,8 @@ class ShardedCtrEngine(CtrEngine):
             self._pending_exchange = None
         U, n_req = pl.U, pl.n_req
         if self.exchange_mode == "peer":
-            n_req = self._req_cap            # the device knows the real count (*o_nuniq); this only bounds the launch
+            if self.device_plan:
+                n_req = self._req_cap        # the device knows the real count (*o_nuniq); this only bounds the launch
             # one gradient row per unique key, summed and stored straight into its owner's receive buffer (exchange #3)
             h.call("ctr_embed_bwd_finalize_push", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
                    ptr(self.part), C.byref(pl.route_g))

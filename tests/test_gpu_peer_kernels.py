@@ -128,8 +128,9 @@ def test_plan_routes_equals_the_host_formula(hd, world):
     from deep_learning_b200._lib import ptr
     from deep_learning_b200.shard import peer_routes
     g = np.random.RandomState(40 + world)
-    mat = g.randint(0, 500, size=(world, world)).astype(np.int32)
-    mat[0, -1] = 0
+    mat = g.randint(1, 500, size=(world, world)).astype(np.int32)
+    if world > 1:
+        mat[0, -1] = 0
     t_mat = torch.from_numpy(mat.reshape(-1).copy()).cuda()
     for rank in range(world):
         plan = torch.full((_lib.PLAN_WORDS,), -1, dtype=torch.int32, device="cuda")
@@ -214,7 +215,7 @@ def test_kernels_follow_a_device_route_block(hd):
     assert Uo == len(want) and np.array_equal(uq.cpu().numpy().view(np.uint32)[:Uo], want)
     assert int(seg[Uo].item()) == n_req
     # the all-zero staging row behind the unique rows
-    buf = torch.full((50, wire), 3.0, device="cuda")
+    buf = torch.full((U + 20, wire), 3.0, device="cuda")
     hd.call("ctr_zero_row_at", _st(), ptr(buf), wire, wire, plan.data_ptr() + 4 * _lib.PLAN_U)
     got = buf.cpu().numpy()
     assert np.all(got[U] == 0.0) and np.all(np.delete(got, U, axis=0) == 3.0)
