@@ -53,18 +53,15 @@ def _run_parity(alg, hp, steps, precision="fp32", adam_mode="tf_dense", B=None, 
         _, p32 = O.train_step(alg, O.to_dtype(p, torch.float32), st32, H.oracle_batch(b, torch.float32), hp, adam_mode=adam_mode)
         # train step
         loss = float(eng.train_step(b).item())
-        if precision == "tf32":
-            # forward value against the true-relu oracle; GRADIENTS against the oracle evaluated on the branch each
-            # ReLU unit took on the device (a pre-activation within TF32 rounding of 0 may land on either side:
-            # the function is continuous there, its derivative jumps -- tests/diag_tf32.py counts these flips)
-            loss_true = float(O.LOSS[alg](p, ob, hp)[0])
-            assert abs(loss - loss_true) < tol * max(1.0, abs(loss_true)), "loss step %d" % step
-            masks = [a[:B, :h_].cpu() > 0 for a, h_ in zip(eng.acts, eng.spec.hidden)]
-            with O.relu_branches(masks):
-                loss_ref, p = O.train_step(alg, p, st, ob, hp, adam_mode=adam_mode)
-        else:
+        # forward value (loss) against the true-ReLU oracle; GRADIENTS against the oracle evaluated on the branch each ReLU
+        # unit took on the device: a pre-activation within rounding of 0 (TF32: tests/diag_tf32.py counts the flips; float32:
+        # about one unit in a million, see tests/mgpu_parity.py) may land on either side of the kink -- the function is
+        # continuous there, its derivative jumps, and Adam near its epsilon amplifies the jump
+        loss_true = float(O.LOSS[alg](p, ob, hp)[0])
+        assert abs(loss - loss_true) < tol * max(1.0, abs(loss_true)), "loss step %d" % step
+        masks = [a[:B, :h_].cpu() > 0 for a, h_ in zip(eng.acts, eng.spec.hidden)]
+        with O.relu_branches(masks):
             loss_ref, p = O.train_step(alg, p, st, ob, hp, adam_mode=adam_mode)
-            assert abs(loss - float(loss_ref)) < tol * max(1.0, abs(float(loss_ref))), "loss step %d" % step
         got = eng.get_weights()
         got_m, _ = eng.get_optimizer_state()
         for n in p:
