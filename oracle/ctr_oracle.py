@@ -63,6 +63,7 @@ class HParams:
     model_restore: int = 0
     cate_feats_conf_path: str = ""
     word2vec_rows: int = 0                # rows of the frozen `tags_emb` constant (models/dnn_multi_textline.py:47-48)
+    deep_feature_size: int = 0            # test_model/DCN.py:16: width of the dense feature vector
 
 
 # --------------------------------------------------------------------------------------
@@ -508,12 +509,77 @@ def dnn_multi_textline_loss(p, batch, hp: HParams):
     return loss, out, score
 
 
+# --------------------------------------------------------------------------------------
+# test_model/ extras: "models awaiting further development" that share the path
+# --------------------------------------------------------------------------------------
+def sigmoid_cross_entropy_with_logits(labels: Tensor, logits: Tensor) -> Tensor:
+    """tf.nn.sigmoid_cross_entropy_with_logits (third-party TF 1.x, documented formula):
+    max(x, 0) - x * z + log(1 + exp(-|x|)), element-wise."""
+    return torch.clamp(logits, min=0) - logits * labels + torch.log1p(torch.exp(-torch.abs(logits)))
+
+
+def wdl_ftrl_forward(p, batch, hp: HParams):
+    """test_model/wdl.py:53-119: models/wdl.py with the deep-projection rows placed BEHIND the wide ids
+    (`+ cate_feats_size`, :110 -- the un-aliased intent quirk Q4 of models/wdl.py misses)."""
+    C, Fc, k, W = hp.cont_field_size, hp.cate_field_size, hp.embedding_size, hp.wide_field_size
+    cate, cont, wide = batch['cate_feats'].long(), batch['cont_feats'], batch['wide_feats'].long()
+    B = cont.shape[0]
+    H = hp.hidden_units[-1]
+    cat_emb = embedding_lookup(p['weight_mat'], cate).reshape(B, Fc * k)       # :67-68
+    deep = mlp_tower(torch.cat([cont, cat_emb], dim=1), p, len(hp.hidden_units))   # :69, :93-97
+    idx = torch.cat([wide, torch.arange(H).unsqueeze(0).expand(B, H) + hp.cate_feats_size], dim=1)    # :106-111
+    val = torch.cat([torch.ones(B, W, dtype=cont.dtype), deep], dim=1)         # :112
+    w = embedding_lookup(p['wdl_weights'], idx).reshape(B, W + H)              # :113-114
+    out = (w * val).sum(dim=1, keepdim=True) + p['wdl_bias']                   # :115
+    return out, torch.sigmoid(out)                                            # :119  (`self.out` IS the sigmoid from here on)
+
+
+def wdl_ftrl_loss(p, batch, hp: HParams):
+    """test_model/wdl.py:119-131: sigmoid_cross_entropy_with_logits fed the ALREADY-sigmoided value as `logits`
+    (as written), mean over the batch, l2 on wdl_weights and every deep_i."""
+    out, score = wdl_ftrl_forward(p, batch, hp)
+    loss = sigmoid_cross_entropy_with_logits(batch['label'], score).mean()
+    if hp.l2_reg > 0:
+        loss = loss + l2_regularizer(hp.l2_reg, p['wdl_weights'])
+        for i in range(len(hp.hidden_units)):
+            loss = loss + l2_regularizer(hp.l2_reg, p['deep_%d' % i])
+    return loss, out, score
+
+
+DCN_CROSS_LAYERS = 2          # test_model/DCN.py:28
+
+
+def dcn_forward(p, batch, hp: HParams):
+    """test_model/DCN.py:43-103.  Dense features only; the deep tower has NO activation (:66-70: matmul + bias +
+    dropout(1)); cross layer l: x_{l+1} = x0 * (x_l . w_l) + b_l + x_l (:84-86: tensordot(matmul(x0, x_l^T), w_l, 1)
+    contracts the last axis, i.e. sum_j x0_i x_l_j w_j)."""
+    x0 = batch['features']
+    deep = x0
+    for i in range(len(hp.hidden_units)):
+        deep = deep @ p['deep_layer_%d' % i] + p['deep_layer_bias_%d' % i]
+    xl = x0
+    for i in range(DCN_CROSS_LAYERS):
+        s = xl @ p['cross_layer_%d' % i]                                        # [B, 1]
+        xl = x0 * s + p['cross_bias_%d' % i].reshape(1, -1) + xl
+    out = torch.cat([xl, deep], dim=1) @ p['concat_projection'] + p['concat_bias']     # :101-102
+    return out, torch.sigmoid(out)
+
+
+def dcn_loss(p, batch, hp: HParams):
+    """test_model/DCN.py:105-111: log_loss + l2 on concat_projection."""
+    out, score = dcn_forward(p, batch, hp)
+    loss = log_loss(batch['label'], score)
+    if hp.l2_reg > 0:
+        loss = loss + l2_regularizer(hp.l2_reg, p['concat_projection'])
+    return loss, out, score
+
+
 FORWARD = {'deepfm': deepfm_forward, 'deepfm_multi': deepfm_multi_forward, 'wdl': wdl_forward,
            'dnn': dnn_forward, 'dnn_multi': dnn_multi_forward,
            'deepfm_cate': deepfm_cate_forward, 'deepfm_multi_cate': deepfm_multi_cate_forward,
            'dnn_pipeline': dnn_pipeline_forward, 'dnn_cate': dnn_pipeline_forward, 'dnn_multi_cate': dnn_multi_cate_forward,
            'wdl_textline': wdl_textline_forward, 'dnn_multi_textline': dnn_multi_textline_forward,
-           'deepfm_pipeline': deepfm_pipeline_forward}
+           'deepfm_pipeline': deepfm_pipeline_forward, 'wdl_ftrl': wdl_ftrl_forward, 'dcn': dcn_forward}
 LOSS = {'deepfm': deepfm_loss, 'deepfm_multi': deepfm_multi_loss, 'wdl': wdl_loss,
         'dnn': dnn_loss, 'dnn_multi': dnn_multi_loss,
         'deepfm_cate': _deepfm_variant_loss(deepfm_cate_forward),
@@ -521,7 +587,12 @@ LOSS = {'deepfm': deepfm_loss, 'deepfm_multi': deepfm_multi_loss, 'wdl': wdl_los
         'dnn_pipeline': _dnn_variant_loss(dnn_pipeline_forward), 'dnn_cate': _dnn_variant_loss(dnn_pipeline_forward),
         'dnn_multi_cate': _dnn_variant_loss(dnn_multi_cate_forward),
         'wdl_textline': wdl_textline_loss, 'dnn_multi_textline': dnn_multi_textline_loss,
-        'deepfm_pipeline': _deepfm_variant_loss(deepfm_pipeline_forward)}     # models/deepfm_pipeline.py:177-183
+        'deepfm_pipeline': _deepfm_variant_loss(deepfm_pipeline_forward),     # models/deepfm_pipeline.py:177-183
+        'wdl_ftrl': wdl_ftrl_loss, 'dcn': dcn_loss}
+# which optimizer `.minimize` runs: tf.train.AdamOptimizer everywhere in models/; test_model/wdl.py:136 uses FTRL
+OPTIMIZER = {'wdl_ftrl': 'ftrl'}
+# the files of test_model/ (every other key of FORWARD is models/<key>.py)
+TEST_MODEL_FILES = {'wdl_ftrl': 'test_model/wdl.py', 'dcn': 'test_model/DCN.py'}
 # variants without a continuous block read cont_field_size as 0 (their model files never define it)
 NO_CONT = ('deepfm_cate', 'deepfm_multi_cate', 'dnn_cate', 'dnn_multi_cate')
 
@@ -549,6 +620,10 @@ def deep_input_size(alg: str, hp: HParams) -> int:
         return hp.cont_field_size + (hp.cate_field_size + hp.multi_field_size) * k
     if alg == 'dnn':
         return hp.cont_field_size + hp.vector_feats_size + hp.cate_field_size * k
+    if alg == 'wdl_ftrl':
+        return hp.cont_field_size + hp.cate_field_size * k
+    if alg == 'dcn':
+        return hp.deep_feature_size
     raise ValueError(alg)
 
 
@@ -570,6 +645,17 @@ def param_shapes(alg: str, hp: HParams) -> Dict[str, Tuple[int, ...]]:
         s['wdl_weights'] = (hp.cate_index_size + H[-1], 1); s['wdl_bias'] = (1,)
     elif alg == 'dnn':                                    # models/dnn.py:49-52
         s['weight_mat'] = (hp.cate_feats_size, k)
+    elif alg == 'wdl_ftrl':                               # test_model/wdl.py:61-64,101-103
+        s['weight_mat'] = (hp.cate_feats_size, k)
+        s['wdl_weights'] = (hp.cate_feats_size + H[-1], 1); s['wdl_bias'] = (1,)
+    if alg == 'dcn':                                      # test_model/DCN.py:49-99 (its own variable names)
+        prev = d0
+        for i, h in enumerate(H):
+            s['deep_layer_%d' % i] = (prev, h); s['deep_layer_bias_%d' % i] = (1, h); prev = h
+        for i in range(DCN_CROSS_LAYERS):
+            s['cross_layer_%d' % i] = (d0, 1); s['cross_bias_%d' % i] = (d0, 1)
+        s['concat_projection'] = (d0 + H[-1], 1); s['concat_bias'] = ()
+        return s
     elif alg == 'dnn_multi_textline':                     # models/dnn_multi_textline.py:38-48 (tags_emb: frozen constant)
         s['weight_mat'] = (hp.cate_feats_size, k); s['tags_emb'] = (hp.word2vec_rows, k)
     elif alg in ('dnn_multi', 'dnn_pipeline', 'dnn_cate', 'dnn_multi_cate'):   # models/dnn_multi.py:71-73, dnn_pipeline.py:69-71
@@ -610,6 +696,13 @@ def init_params(alg: str, hp: HParams, seed: int = 2019, dtype=torch.float64) ->
             a = g.normal(0.0, math.sqrt(2.0 / shp[0]), size=shp)
         elif name in ('deep_fm_bias', 'wdl_bias'):
             a = g.normal(0.0, 1.0, size=shp)
+        elif name == 'concat_bias':                       # test_model/DCN.py:99: tf.constant(0.01); drawn here so its gradient path is exercised
+            a = g.normal(0.01, 0.1, size=shp)
+        elif name.startswith('deep_layer_bias_'):
+            w = shapes['deep_layer_%s' % name.split('_')[-1]]
+            a = g.normal(0.0, math.sqrt(2.0 / (w[0] + w[1])), size=shp)
+        elif name.startswith(('cross_layer_', 'cross_bias_')):
+            a = g.normal(0.0, math.sqrt(2.0 / (2 * shp[0])), size=shp)
         elif name.startswith('deep_bias_'):
             w = shapes['deep_%s' % name.split('_')[-1]]
             a = g.normal(0.0, math.sqrt(2.0 / (w[0] + w[1])), size=shp)
@@ -618,7 +711,7 @@ def init_params(alg: str, hp: HParams, seed: int = 2019, dtype=torch.float64) ->
         else:   # deep_i, deep_fm_weight, deep_res
             a = g.normal(0.0, math.sqrt(2.0 / (shp[0] + shp[1])), size=shp)
         # round to fp32 so fp64 oracle and fp32 device start from IDENTICAL values
-        p[name] = torch.from_numpy(a.astype(np.float32)).to(dtype)
+        p[name] = torch.from_numpy(np.asarray(a, dtype=np.float32)).to(dtype)
     return p
 
 
@@ -685,8 +778,44 @@ def tf1_adam_step(p, grads, st: AdamState, hp: HParams, lazy_rows: Optional[Dict
     return newp
 
 
+FTRL_INIT_ACCUM, FTRL_LR_POWER = 0.1, -0.5      # tf.train.FtrlOptimizer defaults (test_model/wdl.py:136): l1 = l2 = 0
+
+
+def ftrl_init(p: Dict[str, Tensor]) -> AdamState:
+    """FtrlOptimizer slots in the AdamState container: m <- `accum` (initial_accumulator_value 0.1), v <- `linear` (0)."""
+    return AdamState({n: torch.full_like(t, FTRL_INIT_ACCUM) for n, t in p.items()},
+                     {n: torch.zeros_like(t) for n, t in p.items()})
+
+
+def tf1_ftrl_step(p, grads, st: AdamState, hp: HParams, sparse_rows: Dict[str, Tensor]):
+    """tf.train.FtrlOptimizer (TF 1.x ftrl.py -> ApplyFtrl / SparseApplyFtrl kernels; third-party, restated from the
+    published kernel) with its defaults lr_power = -0.5, l1 = l2 = 0:
+        accum' = accum + g^2 ;  linear += g - (sqrt(accum') - sqrt(accum)) / lr * var
+        var    = -linear / (sqrt(accum') / lr)        (|linear| > l1 = 0; else 0)
+    Variables whose gradient is an IndexedSlices (the embedding table: its only consumer is embedding_lookup) take the
+    SPARSE apply: only the looked-up rows change (`sparse_rows`: name -> row mask)."""
+    lr = exponential_decay(hp.learning_rate, st.global_step, hp.learning_rate_decay_steps, hp.learning_rate_decay_rate)
+    newp = {}
+    for n, var in p.items():
+        g = grads[n].to(var.dtype)
+        accum, linear = st.m[n], st.v[n]
+        accum_new = accum + g * g
+        linear_new = linear + g - (torch.sqrt(accum_new) - torch.sqrt(accum)) / lr * var
+        quadratic = torch.sqrt(accum_new) / lr
+        nv = torch.where(linear_new.abs() > 0, -linear_new / quadratic, torch.zeros_like(var))
+        if n in sparse_rows:
+            mask = sparse_rows[n].reshape(-1, *([1] * (var.dim() - 1)))
+            accum_new = torch.where(mask, accum_new, accum); linear_new = torch.where(mask, linear_new, linear)
+            nv = torch.where(mask, nv, var)
+        st.m[n], st.v[n], newp[n] = accum_new, linear_new, nv
+    st.global_step += 1
+    return newp
+
+
 def touched_rows(alg: str, batch, hp: HParams) -> Dict[str, Tensor]:
     """Row masks for adam_mode='lazy': rows whose gradient is structurally non-zero this step."""
+    if alg == 'dcn':
+        return {}
     cate = batch['cate_feats'].long()
     shapes = param_shapes(alg, hp)
     out = {}
@@ -712,7 +841,7 @@ def touched_rows(alg: str, batch, hp: HParams) -> Dict[str, Tensor]:
         mk = mask(shapes['feats_emb'][0], torch.cat([cate.reshape(-1), cate.reshape(-1) + C]), drop0=True)
         mk[1:C] = True                                # continuous-field rows (row 0 is cut out of the graph)
         out['feats_emb'] = mk; out['fm_first_order_emb'] = mk
-    elif alg == 'wdl':
+    elif alg in ('wdl', 'wdl_ftrl'):
         out['weight_mat'] = mask(shapes['weight_mat'][0], cate)
     elif alg == 'wdl_textline':
         out['weight_mat'] = mask(shapes['weight_mat'][0], cate, drop0=True)
@@ -734,8 +863,14 @@ def touched_rows(alg: str, batch, hp: HParams) -> Dict[str, Tensor]:
 def train_step(alg, p, st: AdamState, batch, hp: HParams, adam_mode: str = 'tf_dense'):
     """One `sess.run([loss, optimizer])` (models/deepfm.py:181): returns (loss, new params)."""
     loss, out, score, grads = loss_and_grads(alg, p, batch, hp)
+    if OPTIMIZER.get(alg) == 'ftrl':      # sparse apply for the table, dense for the rest -- whatever adam_mode says
+        return loss, tf1_ftrl_step(p, grads, st, hp, touched_rows(alg, batch, hp))
     lazy = touched_rows(alg, batch, hp) if adam_mode == 'lazy' else None
     return loss, tf1_adam_step(p, grads, st, hp, lazy)
+
+
+def optimizer_init(alg: str, p: Dict[str, Tensor]) -> AdamState:
+    return ftrl_init(p) if OPTIMIZER.get(alg) == 'ftrl' else adam_init(p)
 
 
 # --------------------------------------------------------------------------------------

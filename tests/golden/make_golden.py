@@ -43,6 +43,10 @@ def tiny_hp(alg):
         kw.update(vector_feats_size=2)
     if alg in ("wdl", "wdl_textline"):
         kw.update(cate_index_size=60, wide_field_size=5)
+    if alg == "wdl_ftrl":                  # test_model/wdl.py: one size for the table and the wide ids
+        kw.update(wide_field_size=5)
+    if alg == "dcn":                       # test_model/DCN.py: a dense feature vector only
+        kw.update(deep_feature_size=7)
     if alg == "dnn_multi_textline":
         kw.update(cate_feats_size=81, multi_feats_size=8, multi_field_size=2, multi_feats_range=[[0, 3, "kw"], [3, 8, "tag"]],
                   word2vec_rows=12)
@@ -59,6 +63,10 @@ def tiny_batch(alg, hp, seed):
 
 
 def _tiny_batch(alg, hp, seed):
+    if alg == "dcn":
+        g = torch.Generator(); g.manual_seed(seed)
+        return {"features": torch.randn(hp.batch_size, hp.deep_feature_size, generator=g),
+                "label": (torch.rand(hp.batch_size, 1, generator=g) < 0.3).float()}
     if alg == "dnn_multi_textline":
         import ctr_helpers as H
         return H.make_textline_batch(hp, seed)
@@ -68,7 +76,7 @@ def _tiny_batch(alg, hp, seed):
     else:
         sizes, msizes, tops = D.field_sizes(hp.cate_feats_size - (1 if row0 else 0), 5), [], []
     return D.synthetic_batch(hp.batch_size, hp.cont_field_size, hp.cate_field_size, sizes, seed, V=hp.vector_feats_size,
-                             multi_top_n=tops, multi_sizes=msizes, wide=hp.wide_field_size if alg in ("wdl", "wdl_textline") else 0,
+                             multi_top_n=tops, multi_sizes=msizes, wide=hp.wide_field_size if alg in ("wdl", "wdl_textline", "wdl_ftrl") else 0,
                              dist="uniform", reserve_zero=row0, id_dtype=torch.int64 if row0 else torch.int32)
 
 

@@ -38,7 +38,8 @@ REF = "/root/reference"
 PREDICT_MARK = "#### predict ####"
 N_TRAIN = 3
 
-FEED = ("deepfm", "dnn", "wdl")                                        # fit(train_data, val_data): pickled batches
+FEED = ("deepfm", "dnn", "wdl", "wdl_ftrl", "dcn")                     # fit(train_data, val_data): pickled batches
+MODELS_FEED = FEED[:3]                                                 # the ones under models/ (the other two: test_model/)
 PIPE = ("deepfm_multi", "deepfm_cate", "deepfm_multi_cate", "deepfm_pipeline", "dnn_multi", "dnn_cate",
         "dnn_multi_cate", "dnn_pipeline")                              # fit(print_num_batch, predict_data): tf.data
 TEXT = ("wdl_textline", "dnn_multi_textline")                          # fit(print_iter, num_batch_size): tf.data
@@ -55,12 +56,12 @@ def ref_args(alg, hp, tmp):
         multi_feats_range=[list(r) for r in hp.multi_feats_range], save_model_checkpoint=os.path.join(tmp, "ckpt"),
         restore_model_checkpoint=os.path.join(tmp, "ckpt"), model_restore=0, cate_feats_conf_path="",
         cat_field_size=hp.cate_field_size, cat_index_size=hp.cate_feats_size, cat_feat_conf_path="",
-        word2vec_embedding_path="")
+        word2vec_embedding_path="", deep_feature_size=hp.deep_feature_size)
     return a
 
 
 def load_reference_model(alg):
-    path = os.path.join(REF, "models", alg + ".py")
+    path = os.path.join(REF, O.TEST_MODEL_FILES.get(alg, os.path.join("models", alg + ".py")))
     spec = importlib.util.spec_from_file_location("reference_models_" + alg, path)
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
@@ -126,12 +127,14 @@ class Recorder:
 def run_feed_model(alg, hp, mod, args, batches, val):
     """models/deepfm.py:164-214, models/dnn.py:98-146, models/wdl.py:287-341"""
     def pack(b):
+        if alg == "dcn":                      # test_model/DCN.py:131-135
+            return pickle.dumps({"features": b["features"], "labels": b["label"]})
         d = {"cont_feats": b["cont_feats"], "cate_feats": b["cate_feats"], "labels": b["label"]}
         if alg == "deepfm":
             d["vector_feats"] = b["vector_feats"]
         if alg == "dnn":                      # models/dnn.py:28: one float block holds [cont | vector]
             d["cont_feats"] = np.concatenate([b["cont_feats"], b["vector_feats"]], axis=1)
-        if alg == "wdl":
+        if alg in ("wdl", "wdl_ftrl"):
             d["wide_feats"] = b["wide_feats"]
         return pickle.dumps(d)
 
@@ -206,7 +209,7 @@ def classify(rec):
     rec.events = ""
     for names, out, feed in rec.calls:
         names = [str(n) for n in names]
-        if any(n.startswith("Adam") for n in names):
+        if any(n.startswith(("Adam", "Ftrl")) for n in names):
             losses.append(out[0])
             rec.events += "T"
         elif any(n.startswith(("init", "group", "IteratorGetNext")) for n in names):

@@ -699,8 +699,36 @@ def matmul(a, b, name=None):
     return Tensor(lambda ctx, x, y: x @ y, [a, b], name=name, dtype=a.dtype, shape=shp)
 
 
+def _matmul_t(a, b, transpose_a=False, transpose_b=False, name=None):
+    """tf.matmul incl. the batched form with transpose flags (test_model/DCN.py:85: [B,D,1] x [B,D,1]^T -> [B,D,D])"""
+    if not transpose_a and not transpose_b:
+        return matmul(a, b, name=name)
+    a, b = convert_to_tensor(a), convert_to_tensor(b)
+
+    def run(ctx, x, y):
+        return (x.transpose(-1, -2) if transpose_a else x) @ (y.transpose(-1, -2) if transpose_b else y)
+    return Tensor(run, [a, b], name=name, dtype=a.dtype, shape=None)
+
+
+def tensordot(a, b, axes, name=None):
+    """tf.tensordot with an integer `axes`: contracts the last `axes` axes of a with the first `axes` of b"""
+    if not isinstance(axes, int):
+        raise NotImplementedError("tensordot with explicit axis lists")
+    a, b = convert_to_tensor(a), convert_to_tensor(b)
+    return Tensor(lambda ctx, x, y: torch.tensordot(x, y, dims=axes), [a, b], name=name, dtype=a.dtype, shape=None)
+
+
 def sigmoid(x, name=None):
-    return _unary(torch.sigmoid, x, name)
+    return _unary(torch.sigmoid, x, name or "Sigmoid")          # TF names the op: test_model/DCN.py:190 fetches "Sigmoid:0"
+
+
+def _sigmoid_cross_entropy_with_logits(_sentinel=None, labels=None, logits=None, name=None):
+    """documented formula: max(x, 0) - x * z + log(1 + exp(-|x|))"""
+    if _sentinel is not None:
+        raise ValueError("Only call `sigmoid_cross_entropy_with_logits` with named arguments (labels=..., logits=...)")
+    z, x = convert_to_tensor(labels), convert_to_tensor(logits)
+    return Tensor(lambda ctx, zz, xx: torch.clamp(xx, min=0) - xx * zz + torch.log1p(torch.exp(-xx.abs())), [z, x], name=name,
+                  dtype=x.dtype, shape=lambda: _static(x))
 
 
 def _relu(x, name=None):
@@ -734,10 +762,13 @@ def _embedding_lookup(params, ids, partition_strategy="mod", name=None, validate
         sp, si = _static(p), _static(i)
         return None if sp is None or si is None else si + sp[1:]
 
-    return Tensor(run, [p, i], name=name, dtype=p.dtype, shape=shp)
+    t = Tensor(run, [p, i], name=name, dtype=p.dtype, shape=shp)
+    t._is_gather = True          # its gradient w.r.t. `params` is an IndexedSlices (sparse optimizer applies look at this)
+    return t
 
 
-nn = types.SimpleNamespace(embedding_lookup=_embedding_lookup, dropout=_dropout, relu=_relu, sigmoid=sigmoid)
+nn = types.SimpleNamespace(embedding_lookup=_embedding_lookup, dropout=_dropout, relu=_relu, sigmoid=sigmoid,
+                           sigmoid_cross_entropy_with_logits=_sigmoid_cross_entropy_with_logits)
 
 
 # ------------------------------------------------------------------------------------------------ losses / regularisers
@@ -833,6 +864,81 @@ class _AdamOptimizer:
         return Operation(run, (), name="Adam")
 
 
+def _consumers(root):
+    """id(tensor) -> nodes of the graph under `root` that read it"""
+    seen, out, stack = set(), {}, [root]
+    while stack:
+        n = stack.pop()
+        if id(n) in seen:
+            continue
+        seen.add(id(n))
+        for i in getattr(n, "_inputs", ()):
+            if isinstance(i, Tensor):
+                out.setdefault(id(i), []).append(n)
+                stack.append(i)
+    return out
+
+
+class _FtrlOptimizer:
+    """tf.train.FtrlOptimizer (ftrl.py -> ApplyFtrl / SparseApplyFtrl, published kernels; l2_shrinkage 0):
+        accum' = accum + g^2 ; linear += g - (accum'^(-p) - accum^(-p)) / lr * var ; quadratic = accum'^(-p) / lr + 2 l2
+        var = (sign(linear) l1 - linear) / quadratic if |linear| > l1 else 0          (p = learning_rate_power)
+    A variable read ONLY through embedding_lookup has an IndexedSlices gradient: the sparse kernel touches the looked-up
+    rows alone (duplicates summed first); any other variable takes the dense kernel."""
+
+    def __init__(self, learning_rate, learning_rate_power=-0.5, initial_accumulator_value=0.1, l1_regularization_strength=0.0,
+                 l2_regularization_strength=0.0, use_locking=False, name="Ftrl", **kw):
+        if kw:
+            raise NotImplementedError("FtrlOptimizer arguments %s" % sorted(kw))
+        self.lr, self.p, self.a0 = learning_rate, float(learning_rate_power), float(initial_accumulator_value)
+        self.l1, self.l2 = float(l1_regularization_strength), float(l2_regularization_strength)
+        self.accum, self.linear = {}, {}
+
+    def _reset(self):
+        self.accum, self.linear = {}, {}
+
+    def minimize(self, loss, global_step=None, var_list=None):
+        g = _graph
+        g.optimizer_slots.append(self._reset)
+        self._reset()
+        lr = convert_to_tensor(self.lr)
+        users = _consumers(loss)
+
+        def run(ctx):
+            vs = list(var_list) if var_list is not None else [v for v in g.variables if v.trainable]
+            lv = loss._eval(ctx)
+            grads = torch.autograd.grad(lv, [v.value for v in vs], allow_unused=True, retain_graph=True)
+            if all(gr is None for gr in grads):
+                raise ValueError("No gradients provided for any variable")
+            lrv = float(lr._eval(ctx))
+            with torch.no_grad():
+                for var, gr in zip(vs, grads):
+                    if gr is None:
+                        continue
+                    k = id(var)
+                    if k not in self.accum:
+                        self.accum[k], self.linear[k] = torch.full_like(var.value, self.a0), torch.zeros_like(var.value)
+                    acc, lin, w = self.accum[k], self.linear[k], var.value
+                    acc_new = acc + gr * gr
+                    lin_new = lin + gr - (acc_new.pow(-self.p) - acc.pow(-self.p)) / lrv * w
+                    quad = acc_new.pow(-self.p) / lrv + 2 * self.l2
+                    w_new = torch.where(lin_new.abs() > self.l1, (torch.sign(lin_new) * self.l1 - lin_new) / quad, torch.zeros_like(w))
+                    use = users.get(k, [])
+                    if use and all(getattr(n, "_is_gather", False) and n._inputs[0] is var for n in use):
+                        rows = torch.zeros(w.shape[0], dtype=torch.bool)
+                        for n in use:
+                            rows[n._inputs[1]._eval(ctx).reshape(-1)] = True
+                        mk = rows.reshape(-1, *([1] * (w.dim() - 1)))
+                        acc_new, lin_new, w_new = torch.where(mk, acc_new, acc), torch.where(mk, lin_new, lin), torch.where(mk, w_new, w)
+                    self.accum[k], self.linear[k] = acc_new, lin_new
+                    var.value = w_new.detach().requires_grad_(True)
+                if global_step is not None:
+                    global_step.value = global_step.value + 1
+            return None
+
+        return Operation(run, (), name="Ftrl")
+
+
 class _Saver:
     def __init__(self, *a, **k):
         pass
@@ -844,7 +950,7 @@ class _Saver:
         raise NotImplementedError("checkpoint restore is outside the path the stand-in runs")
 
 
-train = types.SimpleNamespace(AdamOptimizer=_AdamOptimizer, exponential_decay=_exponential_decay, Saver=_Saver,
+train = types.SimpleNamespace(AdamOptimizer=_AdamOptimizer, FtrlOptimizer=_FtrlOptimizer, exponential_decay=_exponential_decay, Saver=_Saver,
                               latest_checkpoint=lambda d: None)
 
 
@@ -1155,9 +1261,10 @@ def install():
               "tables_initializer", "group", "variable_scope", "get_variable_scope", "name_scope", "get_variable",
               "random_normal", "random_uniform", "zeros", "ones", "placeholder", "placeholder_with_default",
               "errors", "add", "subtract", "multiply", "div_no_nan", "square", "identity", "reduce_sum",
-              "reduce_mean", "count_nonzero", "reshape", "concat", "tile", "matmul", "sigmoid", "nn", "losses",
+              "reduce_mean", "count_nonzero", "reshape", "concat", "tile", "tensordot", "sigmoid", "nn", "losses",
               "contrib", "train", "Session", "gfile", "data", "string_split", "string_to_number", "split", "squeeze"):
         setattr(tf, k, getattr(me, k))
+    tf.matmul = _matmul_t
     tag_constants = _module("tensorflow.python.saved_model.tag_constants", SERVING="serve")
     signature_constants = _module("tensorflow.python.saved_model.signature_constants",
                                   PREDICT_METHOD_NAME="tensorflow/serving/predict",

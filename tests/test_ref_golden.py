@@ -22,6 +22,10 @@ from golden import make_golden as G
 HERE = os.path.dirname(os.path.abspath(__file__))
 FILES = sorted(f for f in glob.glob(os.path.join(HERE, "golden", "ref_*.npz")) if not f.endswith("ref_loader.npz"))
 ALGS = [os.path.basename(f)[4:-4] for f in FILES]
+# fixtures of models/*.py (the 13 files the product has a CUDA path and a drop-in module for).  The two test_model/ files
+# (wdl_ftrl, dcn) are pinned at the ORACLE level only so far -- their CUDA path is not built, so the
+# GPU replay (tests/test_ref_gpu.py) and the live surface checks (tests/test_ref_live.py) run over MODEL_ALGS
+MODEL_ALGS = [a for a in ALGS if a not in O.TEST_MODEL_FILES]
 
 TOL = 1e-12          # float64 on both sides, same operation order up to summation order inside torch reductions
 
@@ -42,7 +46,7 @@ def _n_train_batches(z):
 
 
 def test_every_model_file_of_the_reference_has_a_fixture():
-    assert set(ALGS) == set(O.FORWARD), "ref_*.npz must cover every models/*.py the oracle restates"
+    assert set(ALGS) >= set(O.FORWARD) - set(O.TEST_MODEL_FILES), "ref_*.npz must cover every models/*.py the oracle restates"
 
 
 @pytest.mark.parametrize("alg", ALGS)
@@ -62,7 +66,7 @@ class _Files(dict):
 def replay_with_oracle(alg, z, hp):
     p = {k[5:]: torch.from_numpy(z[k]).double() for k in z.files if k.startswith("init/")}
     assert set(p) == set(O.param_shapes(alg, hp))
-    st = O.adam_init(p)
+    st = O.optimizer_init(alg, p)          # Adam slots, or FTRL's for test_model/wdl.py
     family, events = str(z["family"]), str(z["events"])
     n_val = int(z["n_val"])
     t = e = pulled = 0
@@ -196,7 +200,7 @@ class _OracleEngine:
     real numbers, so what they PRINT can be held against what the reference's `fit` printed)"""
 
     def __init__(self, alg, hp, p):
-        self.alg, self.hp, self.p, self.st = alg, hp, p, O.adam_init(p)
+        self.alg, self.hp, self.p, self.st = alg, hp, p, O.optimizer_init(alg, p)
         self.last_batch, self.label, self.score = 0, None, None
 
     @staticmethod

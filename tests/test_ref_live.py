@@ -11,7 +11,7 @@ import pytest
 
 from oracle import ctr_oracle as O
 from golden import make_golden as G
-from test_ref_golden import ALGS, _Files, replay_with_oracle
+from test_ref_golden import MODEL_ALGS as ALGS, _Files, replay_with_oracle
 
 pytestmark = pytest.mark.skipif(not os.path.isdir("/root/reference/models"), reason="needs /root/reference (build container)")
 
