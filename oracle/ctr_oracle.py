@@ -22,6 +22,7 @@ float32 matches TF's arithmetic type and is what the CPU baseline times.
 from __future__ import annotations
 
 import math
+import threading
 from dataclasses import dataclass, field
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -95,7 +96,9 @@ def nonzero_reduce_mean(emb: Tensor) -> Tensor:
 # side in a reduced-precision (TF32) run.  Tests that check GRADIENTS of such a run pin the branch each unit
 # took (`with relu_branches(masks)`), so the comparison is same-branch and the tolerance measures rounding,
 # not the jump of d relu at 0.  Forward values (logit / score / loss) are always compared with the true relu.
-_RELU_BRANCHES: Optional[List[Tensor]] = None
+# per THREAD: the loopback multi-GPU tests run N ranks as N threads of one process, each calling this module on its own
+# batch; a process-wide override would leak one rank's masks into another rank's forward
+_RELU = threading.local()
 
 
 class relu_branches:
@@ -105,13 +108,12 @@ class relu_branches:
         self.masks = masks
 
     def __enter__(self):
-        global _RELU_BRANCHES
-        self.prev, _RELU_BRANCHES = _RELU_BRANCHES, self.masks
+        self.prev = getattr(_RELU, "masks", None)
+        _RELU.masks = self.masks
         return self
 
     def __exit__(self, *exc):
-        global _RELU_BRANCHES
-        _RELU_BRANCHES = self.prev
+        _RELU.masks = self.prev
         return False
 
 
@@ -119,7 +121,8 @@ def mlp_tower(x: Tensor, p: Dict[str, Tensor], n_layers: int) -> Tensor:
     """models/deepfm.py:121-126: dropout(keep=1) is the identity; relu(x @ W_i + b_i)."""
     for i in range(n_layers):
         z = x @ p['deep_%d' % i] + p['deep_bias_%d' % i]
-        x = torch.relu(z) if _RELU_BRANCHES is None else z * _RELU_BRANCHES[i].to(z.dtype)
+        masks = getattr(_RELU, "masks", None)
+        x = torch.relu(z) if masks is None else z * masks[i].to(z.dtype)
     return x
 
 

@@ -350,3 +350,32 @@ def test_tf1_adam_against_torch_optim_adam_over_ten_steps():
         w.grad = grad.clone()
         opt.step()
         assert float((p["w"] - w.detach()).abs().max()) < 1e-14, t
+
+
+def test_relu_branch_override_is_per_thread():
+    """the loopback multi-GPU tests run N ranks as N threads, each calling the oracle on its own batch: the masks one
+    rank pins with `relu_branches` (global batch, 256 rows) must not reach another rank's 128-row forward"""
+    import threading
+    import ctr_helpers as H
+    hp = H.hp_c1()
+    p = O.init_params("deepfm", hp)
+    b128 = H.oracle_batch(H.make_batch("deepfm", hp, seed=1, B=128), torch.float64)
+    want = O.FORWARD["deepfm"](p, b128, hp)[0]
+    masks = [torch.zeros(256, h, dtype=torch.bool) for h in hp.hidden_units]      # would zero the tower AND mis-size it
+    go, done, box = threading.Event(), threading.Event(), {}
+
+    def other():
+        go.wait()
+        try:
+            box["out"] = O.FORWARD["deepfm"](p, b128, hp)[0]
+        except Exception as e:           # noqa: BLE001 -- reported below
+            box["err"] = e
+        done.set()
+    t = threading.Thread(target=other)
+    t.start()
+    with O.relu_branches(masks):
+        go.set()
+        done.wait()
+    t.join()
+    assert "err" not in box, box.get("err")
+    assert torch.equal(box["out"], want)
