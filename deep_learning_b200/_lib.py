@@ -97,6 +97,7 @@ _PROTOS = {
     "ctr_colsum_ws_bytes": (c_i64, [c_vp, c_i32, c_i32]),
     "ctr_colsum": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64]),
     "ctr_reduce": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64]),
+    "ctr_reduce_static": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_vp]),
     "ctr_sort_ws_bytes": (c_i64, [c_vp, c_i64]),
     "ctr_sort_ids": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i64, c_i64, c_i32, c_i32, c_i64, c_i32, c_i64, c_i32,
                              c_i32, c_i32, c_i32, c_i64, c_vp, c_vp, c_vp, c_vp, c_i64]),

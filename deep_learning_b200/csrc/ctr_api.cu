@@ -4,6 +4,26 @@
 extern "C" int ctr_abi_version(void) { return CTR_ABI_VERSION; }
 extern "C" int ctr_sizeof_embed_cfg(void) { return (int) sizeof(ctr_embed_cfg); }
 
+// Scratch of ctr_reduce_static: the block partials of one reduction, in device memory that exists from the moment the
+// library is loaded (every GPU that loads it holds these 4 KB until the process exits) -- so that entry point never
+// allocates.  NB in HOST code `g_reduce_scratch` is only a stand-in for the symbol, not a device address: the address a
+// kernel can use comes from cudaGetSymbolAddress, taken per device with that device current (resolve_reduce_scratch).
+static __device__ __align__(256) float g_reduce_scratch[CTR_REDUCE_STATIC_MAX_PARTIALS];
+
+// once per handle (= per device), at set-up: the handle's device is made current for the lookup and the caller's
+// current device is restored.  No allocation: the array is part of the loaded module.
+static void resolve_reduce_scratch(ctr_handle* h) {
+    int cur = -1;
+    cudaError_t e = cudaGetDevice(&cur);
+    if (e == cudaSuccess && cur != h->device) e = cudaSetDevice(h->device);
+    void* p = nullptr;
+    if (e == cudaSuccess) e = cudaGetSymbolAddress(&p, g_reduce_scratch);
+    if (cur >= 0 && cur != h->device) cudaSetDevice(cur);
+    h->reduce_scratch = e == cudaSuccess ? static_cast<float*>(p) : nullptr;
+    h->reduce_scratch_rc = (int) e;
+    if (e != cudaSuccess) cudaGetLastError();      // a failed lookup must not poison the next launch check
+}
+
 extern "C" int ctr_create(int device, ctr_handle** out) {
     if (!out) return CTR_E_INVALID;
     *out = nullptr;
@@ -18,6 +38,7 @@ extern "C" int ctr_create(int device, ctr_handle** out) {
     h->cc_minor = prop.minor;
     h->err[0] = 0;
     h->launches = 0;
+    resolve_reduce_scratch(h);     // set-up for ctr_reduce_static only; a failure is reported by that entry point, not here
     *out = h;
     return CTR_OK;
 }
@@ -203,5 +224,30 @@ extern "C" int ctr_reduce(ctr_handle* h, ctr_stream s, const float* x, int64_t n
     CTR_CHECK_LAUNCH(h, "reduce_pass1");
     reduce_pass2<<<1, 256, 0, ctr_st(s)>>>(part, (int) blocks, out);
     CTR_CHECK_LAUNCH(h, "reduce_pass2");
+    return CTR_OK;
+}
+
+// ctr_reduce for callers that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+// cudaMalloc): same two kernels, same block slices, so the result is bit-identical to ctr_reduce -- the block partials go
+// to the file-scope static array instead of a caller workspace.  Calls no cudaMalloc / cudaFree / allocating routine.
+// Nothing in the scratch has to start at zero: pass 1 overwrites partials [0, blocks) and pass 2 reads exactly those, so
+// whatever the previous call left behind is never read.  ALL calls on a device share the one array: two calls that
+// overlap on the GPU (different streams, no ordering between them) race; calls on one stream are ordered and safe.
+extern "C" int ctr_reduce_static(ctr_handle* h, ctr_stream s, const float* x, int64_t n, int mode, float* out) {
+    CTR_REQUIRE(h, x && out && n >= 0 && mode >= 0 && mode <= 2, "reduce_static: bad args");
+    CTR_REQUIRE(h, n <= CTR_REDUCE_STATIC_MAX_N, "reduce_static: n = %lld exceeds the static scratch's limit of %lld elements; "
+                "use ctr_reduce with a caller workspace", (long long) n, (long long) CTR_REDUCE_STATIC_MAX_N);
+    if (!h->reduce_scratch)
+        return ctr_fail(h, CTR_E_CUDA, "reduce_static: cudaGetSymbolAddress of the scratch failed on device %d at ctr_create: %s",
+                        h->device, cudaGetErrorString((cudaError_t) h->reduce_scratch_rc));
+    int64_t blocks = ctr_cdiv(n > 0 ? n : 1, 4096);
+    if (blocks > CTR_REDUCE_STATIC_MAX_PARTIALS) blocks = CTR_REDUCE_STATIC_MAX_PARTIALS;
+    float* part = h->reduce_scratch;
+    if (mode == 0) reduce_pass1<0><<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(x, n, part);
+    else if (mode == 1) reduce_pass1<1><<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(x, n, part);
+    else reduce_pass1<2><<<(unsigned) blocks, 256, 0, ctr_st(s)>>>(x, n, part);
+    CTR_CHECK_LAUNCH(h, "reduce_static pass1");
+    reduce_pass2<<<1, 256, 0, ctr_st(s)>>>(part, (int) blocks, out);
+    CTR_CHECK_LAUNCH(h, "reduce_static pass2");
     return CTR_OK;
 }

@@ -13,6 +13,8 @@ struct ctr_handle {
     int cc_major, cc_minor;
     unsigned long long launches;   // kernels launched through this handle
     char err[512];
+    float* reduce_scratch;         // device address of ctr_api.cu's static scratch ON THIS HANDLE'S DEVICE (ctr_reduce_static)
+    int reduce_scratch_rc;         // cudaError_t of the cudaGetSymbolAddress that produced it
 };
 
 #define CTR_PAD_KEY 0xFFFFFFFFu

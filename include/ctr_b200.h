@@ -204,6 +204,18 @@ int ctr_colsum(ctr_handle* h, ctr_stream s, const float* X, int64_t ldx, int B, 
  * models/dnn.py:90).  ws >= 4*1024 B */
 int ctr_reduce(ctr_handle* h, ctr_stream s, const float* x, int64_t n, int mode, float* out,
                void* ws, int64_t ws_bytes);
+/* ctr_reduce without a workspace argument and WITHOUT ANY ALLOCATION.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  The block partials live in a file-scope `static __device__` array of
+ * CTR_REDUCE_STATIC_MAX_PARTIALS floats (4 KB; every GPU that loads the library holds it until the process exits), whose
+ * device address is taken once per handle at ctr_create (cudaGetSymbolAddress with that device current).  Same kernels
+ * and block slices as ctr_reduce: bit-identical results.  Limits: n <= CTR_REDUCE_STATIC_MAX_N, larger n is rejected
+ * with CTR_E_INVALID and a message.  Every call on a device shares the array (it keeps the last call's partials, which
+ * are never read: each call overwrites the partials it sums), so calls that OVERLAP on the GPU race -- issue them on one
+ * stream or order them with events. */
+#define CTR_REDUCE_STATIC_MAX_PARTIALS 1024
+#define CTR_REDUCE_STATIC_MAX_N ((int64_t) 1 << 28)   /* 268 M floats (1 GiB): at most 1024 addends per thread, as ctr_reduce's callers have */
+int ctr_reduce_static(ctr_handle* h, ctr_stream s, const float* x, int64_t n, int mode, float* out);
 
 /* ---- K4: sparse backward = sort / segment-reduce / Adam ----------------------------------
  * replaces the IndexedSlices gradient of tf.nn.embedding_lookup, TF's unique +
