@@ -295,11 +295,20 @@ CATE_ALG = ("deepfm_cate", "dnn_cate", "dnn_multi_cate", "deepfm_multi_cate")   
 
 class TFRecordBatches:
     """TFRecordDataset(files).map(parse_single_example).batch(B, drop_remainder=True)[.repeat(epochs)]
-    (utils/data_loader.py:27-40).  The reference also shuffles with a 10-batch buffer and no seed (:30); records are
-    kept in file order here unless `shuffle_seed` is given (a seeded shuffle inside each window of 10 batches)."""
+    (utils/data_loader.py:27-40).  The reference shuffles with a 10-batch buffer before batching (:30), from TF's
+    unseeded generator, which nothing here can reproduce; what IS kept is that a training run does not see the file order:
+    `shuffle_seed="default"` means a seeded shuffle inside each window of 10 batches for action_type == "train" (seed
+    2019, the model files' random_seed, advanced by one per epoch) and file order for every other action type (scoring
+    does not depend on the order, and a deterministic order keeps evaluations comparable).  `shuffle_seed=None` opts out
+    (file order), an int picks the seed for any action type."""
+    DEFAULT_SEED = 2019
 
     def __init__(self, mp, files: Sequence[str], action_type: str = "train", pin: bool = True, verify_crc: bool = True,
-                 shuffle_seed: Optional[int] = None, chunk_bytes: int = CHUNK_BYTES):
+                 shuffle_seed="default", chunk_bytes: int = CHUNK_BYTES):
+        if isinstance(shuffle_seed, str):
+            if shuffle_seed != "default":
+                raise ValueError("shuffle_seed: an int, None or 'default'")
+            shuffle_seed = self.DEFAULT_SEED if action_type == "train" else None
         self.files, self.B, self.pin, self.crc, self.chunk = list(files), int(mp.batch_size), pin, int(verify_crc), chunk_bytes
         self.epochs = int(mp.epochs) if action_type == "train" else 1
         self.has_cont = getattr(mp, "alg_name", "") not in CATE_ALG
@@ -339,8 +348,8 @@ class TFRecordBatches:
                             raise ValueError("%s: truncated TFRecord (%d trailing bytes)" % (path, len(rest)))
                         break
 
-    def _shuffled(self, blocks):
-        g = torch.Generator(); g.manual_seed(self.seed)
+    def _shuffled(self, blocks, epoch: int = 0):
+        g = torch.Generator(); g.manual_seed(self.seed + epoch)
         win = self.B * 10
         for big in _rebatch(blocks, win, False, {k: k for k in ("label", "cont", "vec", "cate")}, False):
             perm = torch.randperm(big["label"].shape[0], generator=g)
@@ -348,8 +357,8 @@ class TFRecordBatches:
 
     def __iter__(self):
         names = {"label": "label", "cont": "cont_feats", "vec": "vector_feats", "cate": "cate_feats"}
-        for _ in range(self.epochs):
-            blocks = self._blocks() if self.seed is None else self._shuffled(self._blocks())
+        for epoch in range(self.epochs):
+            blocks = self._blocks() if self.seed is None else self._shuffled(self._blocks(), epoch)
             for b in _rebatch(blocks, self.B, True, names, self.pin):
                 if not self.has_cont:
                     b["cont_feats"] = b["cont_feats"][:, :0]

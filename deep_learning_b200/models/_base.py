@@ -6,10 +6,13 @@ argument is accepted and ignored.
 """
 from __future__ import annotations
 
+import dataclasses
+import json
 import math
 import os
 import sys
 import time
+import types
 from typing import Dict, Iterable, List, Optional
 
 import numpy as np
@@ -70,6 +73,97 @@ def _lookahead(items: Iterable):
     yield cur, None
 
 
+EXPORT_FORMAT = 2          # 1: variables only (round 1); 2: + alg, hyper-parameters, serving signature
+
+
+def hparams_to_dict(args) -> Dict:
+    """the JSON-able attributes of a hyper-parameter bag (ModelParams, SimpleNamespace, a launcher's own class)"""
+    src = dataclasses.asdict(args) if dataclasses.is_dataclass(args) else dict(vars(args))
+    out = {}
+    for k, v in src.items():
+        if k.startswith("_"):
+            continue
+        if isinstance(v, (bool, int, float, str)) or v is None:
+            out[k] = v
+        elif isinstance(v, (list, tuple)):
+            try:
+                json.dumps(v)
+                out[k] = list(v)
+            except TypeError:
+                pass
+        elif isinstance(v, (np.integer, np.floating)):
+            out[k] = v.item()
+    return out
+
+
+def serving_signature(spec) -> Dict:
+    """The reference's signature_def (models/deepfm.py:193-201, models/wdl.py:320-328): tensor names, dtypes and
+    per-sample widths of the inputs, and the output `score:0` [B, 1]."""
+    ids = spec.id_dtype
+    inputs = {"cont_feats": {"tensor": "cont_feats:0", "dtype": "float32", "width": spec.C},
+              "vector_feats": {"tensor": "vector_feats:0", "dtype": "float32", "width": spec.V},
+              "cate_feats": {"tensor": "cate_feats:0", "dtype": ids, "width": spec.ids_ld},
+              "input_data_size": {"tensor": "input_data_size:0", "dtype": "int32", "width": None}}
+    if spec.head == "wdl":
+        inputs["wide_feats"] = {"tensor": "wide_feats:0", "dtype": ids, "width": spec.wide_fields}
+    if spec.weighted_pool:
+        inputs["multi_feats_value"] = {"tensor": "mul_cat_feats_value:0", "dtype": "float32", "width": spec.M}
+    return {"method_name": "tensorflow/serving/predict", "inputs": inputs,
+            "outputs": {"output": {"tensor": "score:0", "dtype": "float32", "width": 1}}}
+
+
+def read_export_meta(path: str) -> Dict:
+    """alg / hyper-parameters / signature of an export written by `save`"""
+    z = np.load(os.path.join(path, "model.npz"))
+    if "meta/json" not in z.files:
+        raise ValueError("%s is a variables-only export (format 1): pass the hyper-parameter bag as args=mp" % path)
+    return json.loads(str(z["meta/json"]))
+
+
+def hparams_from_export(path: str):
+    """the hyper-parameter bag an export was written with, as an attribute holder"""
+    return types.SimpleNamespace(**read_export_meta(path)["hparams"])
+
+
+class ExportedModel:
+    """`tf.saved_model.loader.load(session, [SERVING], model_pb)` + `session.run("score:0", feed_dict)` by tensor NAME
+    (models/deepfm.py:237-250, models/wdl.py:364-377): everything comes from the export directory."""
+
+    def __init__(self, model_pb: str, max_batch: Optional[int] = None, **kw):
+        import importlib
+        meta = read_export_meta(model_pb)
+        self.meta, self.signature = meta, meta["signature"]
+        mod = importlib.import_module("deep_learning_b200.models." + meta["alg"])
+        args = types.SimpleNamespace(**meta["hparams"])
+        if max_batch:
+            kw["max_batch"] = max_batch
+        self.model = mod.DeepModel(args, **kw) if meta["generation"] == "A" else mod.DeepModel(args, None, **kw)
+        self.model.restore(model_pb)
+        self._by_tensor = {v["tensor"]: k for k, v in self.signature["inputs"].items()}
+
+    def run(self, fetches, feed_dict: Dict) -> np.ndarray:
+        """fetches: "score:0" (or the signature's output key); feed_dict keyed by tensor name ("cate_feats:0") or by
+        signature key ("cate_feats").  Returns [B, 1] float32 like the reference's session.run."""
+        out = self.signature["outputs"]["output"]["tensor"]
+        if fetches not in (out, "output", "score"):
+            raise KeyError("%r is not an output of this export (have %r)" % (fetches, out))
+        batch = {}
+        for k, v in feed_dict.items():
+            key = self._by_tensor.get(k, k)
+            if key not in self.signature["inputs"]:
+                raise KeyError("%r is not an input of this export (have %s)" % (k, sorted(self._by_tensor)))
+            batch[key] = v
+        n = batch.pop("input_data_size", None)
+        if "vector_feats" not in batch and self.model.spec.V == 0 and "cate_feats" in batch:
+            batch["vector_feats"] = np.zeros((len(batch["cate_feats"]), 0), np.float32)
+        scores = self.model.predict_scores(batch)
+        return scores if n is None else scores[:int(np.asarray(n).reshape(-1)[0])]
+
+
+def load_exported(model_pb: str, **kw) -> ExportedModel:
+    return ExportedModel(model_pb, **kw)
+
+
 class BaseDeepModel:
     ALG = ""
     GENERATION = "A"     # "A": feed_dict / pickled batches; "B": iterator of batch dicts
@@ -112,8 +206,14 @@ class BaseDeepModel:
     # ---- persistence: the reference exports a SavedModel (.pb, models/deepfm.py:193-211) and, for the
     # tf.data generation, a Saver checkpoint with the Adam slots (models/deepfm_multi.py:308-310).
     def save(self, path: str, with_optimizer: bool = False) -> None:
+        """The export is SELF-DESCRIBING, like the reference's SavedModel (models/deepfm.py:193-211): beside the variables
+        it carries the model file's name, the hyper-parameter bag and the named-tensor serving signature, so
+        `load_exported(path)` / module-level `predict(data, model_pb)` need nothing else (local_run_test.py:82)."""
         os.makedirs(path, exist_ok=True)
         blob = {"w/" + k: v for k, v in self.engine.get_weights().items()}
+        blob["meta/json"] = np.array(json.dumps({"format": EXPORT_FORMAT, "alg": self.ALG, "generation": self.GENERATION,
+                                                 "hparams": hparams_to_dict(self.args),
+                                                 "signature": serving_signature(self.spec)}))
         if with_optimizer:
             e = self.engine
             blob.update({"opt/m_table": e.m_table.cpu().numpy(), "opt/v_table": e.v_table.cpu().numpy(),

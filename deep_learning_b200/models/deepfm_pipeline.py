@@ -7,7 +7,7 @@ Quirk Q2 is reproduced: the FM part reads row id + cont_field_size, the deep par
 """
 import sys
 
-from ._base import BaseDeepModel
+from ._base import BaseDeepModel, hparams_from_export
 
 
 class DeepModel(BaseDeepModel):
@@ -24,8 +24,8 @@ class DeepModel(BaseDeepModel):
 
 def predict(predict_data, model_pb, args=None, **kw):
     """models/deepfm_pipeline.py:320-352"""
-    if args is None:
-        raise ValueError("predict(predict_data, model_pb, args=mp): the hyper-parameter bag is required")
+    if args is None:          # the export is self-describing: its own hyper-parameter bag (models/_base.py save)
+        args = hparams_from_export(model_pb)
     m = DeepModel(args, None, **kw)
     m.restore(model_pb)
     auc = m._auc(list(predict_data))

@@ -5,7 +5,7 @@
 """
 import sys
 
-from ._base import BaseDeepModel
+from ._base import BaseDeepModel, hparams_from_export
 
 
 class DeepModel(BaseDeepModel):
@@ -21,10 +21,10 @@ class DeepModel(BaseDeepModel):
 
 
 def predict(predict_data, model_pb, args=None, **kw):
-    """models/dnn_cate.py predict().  The reference reloads the exported graph, which carries its own shapes; the npz
-    export here carries only variables, so the hyper-parameter bag is passed as `args`."""
-    if args is None:
-        raise ValueError("predict(predict_data, model_pb, args=mp): the hyper-parameter bag is required")
+    """models/dnn_cate.py predict().  The reference reloads the exported graph, which carries its own shapes; the
+    export here carries the hyper-parameter bag too, so `args` is optional (an override)."""
+    if args is None:          # the export is self-describing: its own hyper-parameter bag (models/_base.py save)
+        args = hparams_from_export(model_pb)
     m = DeepModel(args, None, **kw)
     m.restore(model_pb)
     auc = m._auc(list(predict_data))

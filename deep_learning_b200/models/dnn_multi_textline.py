@@ -13,7 +13,7 @@ import sys
 
 import numpy as np
 
-from ._base import BaseDeepModel, init_weights
+from ._base import BaseDeepModel, hparams_from_export, init_weights
 
 
 class DeepModel(BaseDeepModel):
@@ -44,8 +44,8 @@ class DeepModel(BaseDeepModel):
 
 def predict(data_out, model_pb, args=None, **kw):
     """models/dnn_multi_textline.py:231-256"""
-    if args is None:
-        raise ValueError("predict(data_out, model_pb, args=mp): the hyper-parameter bag is required")
+    if args is None:          # the export is self-describing: its own hyper-parameter bag (models/_base.py save)
+        args = hparams_from_export(model_pb)
     m = DeepModel(args, None, **kw)
     m.restore(model_pb)
     auc = m._auc(list(data_out))

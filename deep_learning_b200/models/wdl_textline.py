@@ -9,7 +9,7 @@ GATHERED wdl_weights (:264-269 overwrite the variable with the lookup result bef
 """
 import sys
 
-from ._base import BaseDeepModel
+from ._base import BaseDeepModel, hparams_from_export
 
 
 class DeepModel(BaseDeepModel):
@@ -25,10 +25,10 @@ class DeepModel(BaseDeepModel):
 
 
 def predict(data_out, model_pb, args=None, **kw):
-    """models/wdl_textline.py:360-386: `data_out` is the pickled-batch list of utils/data_loader_load.py:94-139.  The npz
-    export carries only variables, so the hyper-parameter bag is passed as `args`."""
-    if args is None:
-        raise ValueError("predict(data_out, model_pb, args=mp): the hyper-parameter bag is required")
+    """models/wdl_textline.py:360-386: `data_out` is the pickled-batch list of utils/data_loader_load.py:94-139.  The
+    export carries the hyper-parameter bag too, so `args` is optional (an override)."""
+    if args is None:          # the export is self-describing: its own hyper-parameter bag (models/_base.py save)
+        args = hparams_from_export(model_pb)
     m = DeepModel(args, None, **kw)
     m.restore(model_pb)
     auc = m._auc(list(data_out))

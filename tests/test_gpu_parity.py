@@ -413,7 +413,7 @@ def test_tfrecords_through_the_native_loader_feed_generation_b(tmp_path, capsys)
     mp = ModelParams(alg_name="deepfm_multi", batch_size=64, epochs=1, cont_field_size=hp.cont_field_size,
                      vector_feats_size=hp.vector_feats_size, cate_field_size=hp.cate_field_size, multi_feats_size=hp.multi_feats_size)
     val = [batches[0]]
-    ma = alg_model.DeepModel(hp, L.load_tfrecord_input_file(mp, d, "train"), adam_mode="lazy")
+    ma = alg_model.DeepModel(hp, L.load_tfrecord_input_file(mp, d, "train", shuffle_seed=None), adam_mode="lazy")     # file order: same batches as `mb`
     ma.fit(100, iter(val))
     mb = alg_model.DeepModel(hp, iter(batches), adam_mode="lazy")
     mb.fit(100, iter(val))

@@ -177,7 +177,7 @@ def test_crc32c_known_answer_and_tfrecord_roundtrip(tmp_path, lib_ready):
              multi_feats_size=M)
     files = L.get_file_list(d)
     ref = list(LO.pipeline_batches(mp, files, "train"))
-    got = list(L.pipeline_process(mp, files, "train", pin=False))
+    got = list(L.pipeline_process(mp, files, "train", pin=False, shuffle_seed=None))       # file order: comparable record by record
     assert len(ref) == len(got) == 2 * (n // 32)
     for g_, r in zip(got, ref):
         for k in ("label", "cont_feats", "vector_feats", "cate_feats"):
@@ -191,12 +191,27 @@ def test_crc32c_known_answer_and_tfrecord_roundtrip(tmp_path, lib_ready):
     # *_cate generation: no cont_feats key in the spec (utils/data_loader.py:10-16)
     mpc = _mp(alg_name="deepfm_multi_cate", batch_size=32, epochs=1, cont_field_size=0, vector_feats_size=V, cate_field_size=Fc,
               multi_feats_size=M)
-    gc = list(L.pipeline_process(mpc, files, "train", pin=False))
+    gc = list(L.pipeline_process(mpc, files, "train", pin=False, shuffle_seed=None))
     assert gc[0]["cont_feats"].shape == (32, 0) and torch.equal(gc[0]["cate_feats"], got[0]["cate_feats"])
     # seeded shuffle keeps the multiset of records
     sh = list(L.pipeline_process(mp, files, "predict", pin=False, shuffle_seed=1))
     a = torch.cat([b["cate_feats"] for b in sh]); b_ = torch.cat([b["cate_feats"] for b in got[:n // 32]])
     assert not torch.equal(a, b_)
+    # the DEFAULT for training is that shuffle (the reference never trains in file order, utils/data_loader.py:30): same
+    # records, another order, and the second epoch differs from the first; scoring keeps file order.  (Shuffle comes BEFORE
+    # batch(drop_remainder) there, so WHICH records fall into the dropped remainder changes with the order: an epoch is a
+    # duplicate-free selection of (n // 32) * 32 of the file's records.)
+    tr = list(L.pipeline_process(mp, files, "train", pin=False))
+    e0 = torch.cat([b["cate_feats"] for b in tr[:n // 32]]); e1 = torch.cat([b["cate_feats"] for b in tr[n // 32:]])
+    every = set(tuple(int(x) for x in r["cate_feats"]) for r in rows)
+    for e in (e0, e1):
+        recs = [tuple(r) for r in e.tolist()]
+        assert len(recs) == (n // 32) * 32 == len(set(recs)) and set(recs) <= every
+    assert not torch.equal(e0, b_) and not torch.equal(e0, e1)
+    again = list(L.pipeline_process(mp, files, "train", pin=False))
+    assert all(torch.equal(x["cate_feats"], y["cate_feats"]) for x, y in zip(tr, again))           # seeded: reproducible
+    pr = list(L.pipeline_process(mp, files, "predict", pin=False))
+    assert torch.equal(torch.cat([b["cate_feats"] for b in pr]), b_)
 
 
 def test_tfrecord_corruption_is_detected(tmp_path, lib_ready):
