@@ -177,7 +177,28 @@ def cpu_reference_arm(steps, warmup, batch=4096, rows=2_000_000, adam_mode="tf_d
             "ms_per_step": dt / steps * 1e3}
 
 
+_JSON_OUT = None
+
+
+def _guard_stdout():
+    """stdout must carry exactly ONE JSON line, but libraries write to file descriptor 1 behind Python's back (NCCL prints
+    its version banner and, at NCCL_DEBUG=INFO, its whole log there; pointing NCCL_DEBUG_FILE at /dev/stderr did not
+    hold on the GPU box).  Keep a private duplicate of fd 1 for the line and make fd 1 an alias of stderr for everybody
+    else: NCCL's log stays visible (the driver checks the communicator's rank count in it) and cannot corrupt the line."""
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    _JSON_OUT.write(json.dumps(line) + "\n")
+    _JSON_OUT.flush()
+
+
 def main():
+    _guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=30)
@@ -207,7 +228,7 @@ def main():
                 "config": {"workload": "DeepFM Criteo-shape 13 cont + 26 cate k=16 MLP 400x3 (CPU sample: " + cb["sample"] + ")"},
                 "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
                 "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        emit(line)
         return
 
     import torch
@@ -224,10 +245,7 @@ def main():
     hp = hparams(B, R)
     spec = spec_from_hparams("deepfm", hp)
     if world > 1:
-        # stdout carries the one JSON line: NCCL's log (version banner, communicator / nranks lines at INFO) goes to
-        # stderr instead of being switched off
-        if os.environ.get("NCCL_DEBUG") and not os.environ.get("NCCL_DEBUG_FILE"):
-            os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
+        # NCCL_DEBUG is left as the launcher set it: its log goes to what is now stderr (_guard_stdout), not switched off
         # configs[3]: the ~1e8-row tables row-sharded over the ranks (owner = id mod N), B samples per GPU (weak scaling)
         dist.init_process_group("nccl", device_id=dev)
         from deep_learning_b200.sharded import ShardedCtrEngine
@@ -444,7 +462,7 @@ def main():
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample", "adam_mode")}
         cl = cpu_reference_arm(60, 2, adam_mode="lazy")      # like for like with the GPU arm's lazy Adam
         line["cpu_baseline_lazy"] = {k: cl[k] for k in ("value", "unit", "cores", "kind", "sample", "adam_mode")}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
