@@ -20,6 +20,13 @@ from ._lib import DenseLayout, MAX_LAYERS, AdamHP, EmbedCfg, ptr
 # where the side-stream id sort starts: behind the gather (default; it then shares the machine with the forward GEMMs and
 # the head kernel, which it slows from 64 to 95 us) or behind the head kernel (shares it with the backward GEMMs)
 _SORT_AFTER_HEAD = os.environ.get("CTR_SORT_AT", "embed") == "head"
+# order of the backward pass.  "serial" (default): wgrad/dgrad layer by layer, the sparse side (partials, [gradient
+# exchange], row Adam) behind the last GEMM.  "overlap" (opt-in): the data gradients of all layers first, then the sparse
+# side on its own stream UNDER the weight-gradient GEMMs.  Same kernels, same arithmetic, parity-green in both orders.
+# Measured on one B200 (round 2, B = 64K): overlap 1.052 ms/step against 1.022 serial -- the sparse side is fully hidden
+# (12 us of waiting left) but the three weight-gradient GEMMs take 364 us with it underneath against ~200 us alone: the
+# interference (HBM bandwidth, SM slots) costs more than the 169 us the sparse kernels take by themselves.
+_BWD_OVERLAP = os.environ.get("CTR_BWD_ORDER", "serial") == "overlap"
 from .spec import ModelSpec
 
 ADAM_BETA1, ADAM_BETA2, ADAM_EPS = 0.9, 0.999, 1e-8   # tf.train.AdamOptimizer defaults (models/deepfm.py:161)
@@ -135,7 +142,9 @@ class CtrEngine:
             self.m, self.v = (torch.zeros(cur, **f32) for _ in range(2))
             self.grad = torch.zeros(cur + _ALIGN, **f32)     # tail slot [cur] carries the loss share through the allreduce
             maxh = max(s.hidden)
-            self.dz = [torch.zeros(B, maxh, **f32) for _ in range(2)]
+            # one dZ per layer: the data gradients of ALL layers run first (so dX0 exists early and the sparse side can
+            # start), the weight gradients read these buffers afterwards (CTR_BWD_ORDER=serial needs only two)
+            self.dz = [torch.zeros(B, maxh, **f32) for _ in range(max(2, len(s.hidden)))]
             self.dx0_ld = _ru(max(s.E, 4), 4)
             self.dx0 = torch.zeros(B, self.dx0_ld, **f32)
             self.n_extra = s.C if (s.use_fm and s.fm_cont) else 0
@@ -154,6 +163,12 @@ class CtrEngine:
             self.ev_batch, self.ev_sorted = torch.cuda.Event(), torch.cuda.Event()
             self.aux = torch.cuda.Stream(device=dev)
             self.ev_head, self.ev_cont = torch.cuda.Event(), torch.cuda.Event()
+            # the sparse backward (partials -> [exchange] -> row Adam) runs on its own stream underneath the weight-gradient
+            # GEMMs; it has its own workspace (the GEMMs' split-K partials live in self.ws at the same time)
+            self.sparse_stream = torch.cuda.Stream(device=dev)
+            self.ev_dx0, self.ev_sparse = torch.cuda.Event(), torch.cuda.Event()
+            self.ws_sparse = torch.zeros(_ru(max(self.h.query("ctr_adam_rows_ws_bytes", n), 4 * (n // 2048 + 8), 4096), 256),
+                                         dtype=torch.uint8, device=dev)
             self.ws_cont = torch.zeros(_ru(max(self.h.query("ctr_cont_bwd_ws_bytes", cfg), 256), 256), dtype=torch.uint8, device=dev)
             self.ws_sort = torch.zeros(_ru(max(self.h.query("ctr_sort_ws_bytes", n), 4 * (n // 2048 + 8)), 256),
                                        dtype=torch.uint8, device=dev)
@@ -670,6 +685,9 @@ class CtrEngine:
                    ptr(self.dlogit), ptr(w_fm), ptr(self.cont_grad), ptr(self.ws_cont), self.ws_cont.numel())
             self.ev_cont.record(self.aux)
         # dz[0] already holds the gradient through the last ReLU (written by ctr_head_fwd)
+        if self.bwd_overlap and s.ids_ld:
+            self._backward_overlapped(B, cfg, dims, w_fm)
+            return
         cur = 0
         for i in range(L - 1, -1, -1):
             k_, h_ = dims[i]
@@ -714,12 +732,90 @@ class CtrEngine:
         self.global_step += 1
         self._steps_done += 1
 
+    class _OnStream:
+        """while active, every helper of the engine enqueues on `stream` instead of the step's main stream"""
+
+        def __init__(self, eng, stream):
+            self.eng, self.stream = eng, stream
+
+        def __enter__(self):
+            e = self.eng
+            self.saved = (e._main_cached, e._st_cached, e._on_sparse)
+            e._main_cached, e._st_cached, e._on_sparse = self.stream, self.stream.cuda_stream, True
+
+        def __exit__(self, *exc):
+            e = self.eng
+            e._main_cached, e._st_cached, e._on_sparse = self.saved
+            return False
+
+    _on_sparse = False
+    bwd_overlap = _BWD_OVERLAP      # (the sharded engine turns it off outside the peer-memory exchange)
+
+    def _backward_overlapped(self, B: int, cfg, dims, w_fm) -> None:
+        """Backward with the sparse side underneath the weight-gradient GEMMs.
+        main stream   : dgrad L-1 .. dgrad 0 (-> dX0) | wgrad L-1 .. wgrad 0 | dense reduce + dense update | wait(sparse)
+        sparse stream :                  wait(dX0, sort, cont) -> partials -> [finalize/push, barrier] -> row Adam
+        The weight gradients do not depend on the data gradient of their own layer, only on dZ of that layer, which the
+        dgrad chain has already produced (one dZ buffer per layer)."""
+        s, st, h = self.spec, self._stream(), self.h
+        L = len(s.hidden)
+        ws, wsn = ptr(self.ws), self.ws.numel()
+        main = self._main_stream()
+        for i in range(L - 1, 0, -1):                      # dz[j] is dZ of layer L-1-j
+            j = L - 1 - i
+            k_, h_ = dims[i]
+            h.call("ctr_mlp_bwd_data", st, self.prec, B, k_, h_, ptr(self.dz[j]), h_, ptr(self._wd(i)), ptr(self.acts[i - 1]),
+                   self.act_ld[i - 1], 1.0, ptr(self.dz[j + 1]), k_)
+        if s.E:      # only the embedding columns of X0 carry parameters: canonical order puts them first
+            h.call("ctr_mlp_bwd_data", st, self.prec, B, s.E, dims[0][1], ptr(self.dz[L - 1]), dims[0][1], ptr(self._wd(0)), None, 0,
+                   1.0, ptr(self.dx0), self.dx0_ld)
+        self.ev_dx0.record(main)
+        hp = self._adam_hp()
+        self._mark("mlp_bwd_data")
+        # ---- sparse side, on its own stream ---------------------------------------------------------------------
+        sp = self.sparse_stream
+        sp.wait_event(self.ev_dx0)
+        sp.wait_event(self.ev_sorted)
+        if self.n_extra:
+            sp.wait_event(self.ev_cont)
+        n = B * s.ids_ld + self.n_extra
+        with self._OnStream(self, sp):
+            self.h.call("ctr_embed_bwd_partials_weighted", sp.cuda_stream, cfg, ptr(self.keys), ptr(self.perm), ptr(self.uidx), n,
+                        ptr(self.field_of_slot), ptr(self.x0), ptr(self.dx0), self.dx0_ld, ptr(self.sum_e), ptr(self.dlogit),
+                        ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.sw),
+                        ptr(self.part))
+            self._sparse_update(B, n, hp)
+            if self.adam_mode == "tf_dense":
+                # TF1 Adam moves EVERY row each step (m, v decay; theta -= lr_t*m/(sqrt(v)+eps)) -- exact mode
+                h.call("ctr_adam_dense", sp.cuda_stream, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
+                       self.rows_local * s.table_stride, 0.0, 0.0, ptr(self.touched), s.table_stride, hp)
+        self.ev_sparse.record(sp)
+        # ---- weight gradients on the main stream, the sparse side running underneath ----------------------------------
+        for i in range(L - 1, -1, -1):
+            k_, h_ = dims[i]
+            x, ldx = (self.acts[i - 1], self.act_ld[i - 1]) if i > 0 else (self.x0, s.x0_ld)
+            h.call("ctr_mlp_bwd_weight", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self.dz[L - 1 - i]), h_,
+                   ptr(self._w(i, self.grad)), ptr(self._b(i, self.grad)), ws, wsn, 1)
+        self._mark("mlp_bwd_weight")
+        self._begin_dense_reduce()
+        self._reduce_dense_grads()
+        self._mark("dense_reduce")
+        h.call("ctr_dense_update", st, ptr(self.theta), ptr(self.m), ptr(self.v), ptr(self._dense_grad()), C.byref(self._dense_layout()), hp)
+        # the table is final (and, sharded, every peer past its gradient barrier) before anything that follows on the main
+        # stream: the next step's gather, get_weights, a checkpoint
+        main.wait_event(self.ev_sparse)
+        self._mark("sparse_done")
+        self.beta1_power *= ADAM_BETA1
+        self.beta2_power *= ADAM_BETA2
+        self.global_step += 1
+        self._steps_done += 1
+
     def _sparse_update(self, B: int, n: int, hp: AdamHP) -> None:
         """per-run partial gradients (self.part) -> TF1 Adam on the touched rows of the local table"""
         s, st = self.spec, self._stream()
         self.h.call("ctr_adam_rows", st, ptr(self.uniq), ptr(self.n_unique), n, 0, ptr(self.part), ptr(self.seg_start),
                     s.grad_stride, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
-                    self.rows_local, ptr(self.touched), ptr(self.ws), self.ws.numel(), self._fm_w2(), s.k, hp)
+                    self.rows_local, ptr(self.touched), ptr(self.ws_sparse), self.ws_sparse.numel(), self._fm_w2(), s.k, hp)
 
     def _fm_w2(self):
         """device pointer of the k second-order head weights (the e-term of the FM gradient is applied in ctr_adam_rows)"""

@@ -117,13 +117,19 @@ class ShardedCtrEngine(CtrEngine):
         # peer mode plans its routes on the device (no host read in the step); CTR_PLAN=host keeps the earlier host-side
         # planning (one host wait per step for the split sizes) as an A/B and a fallback
         self.device_plan = self.exchange_mode == "peer" and os.environ.get("CTR_PLAN", "device") == "device"
+        if self.exchange_mode != "peer":
+            # torch.distributed collectives run on torch's CURRENT stream, not on the engine's sparse stream: the
+            # overlapped backward order is only valid where the exchange is a kernel on the stream it is given
+            self.bwd_overlap = False
         self.peer_status = self.status[:2]      # [0] step barriers, [1] id-plan barriers: words of the engine's status array
-        self._epoch, self._pepoch, self._rows_dirty = 0, 0, False
+        self._epoch, self._pepoch, self._sepoch, self._rows_dirty = 0, 0, 0, False
         if self.exchange_mode == "peer":
             # slab layout: arrival words of the step barriers | of the id-plan barriers | count matrix x 2 plan slots |
             # received rows | received gradients | requested keys x 2 plan slots | dense gradients (read by every peer)
             row_bytes, W = self.wire * 4, world
-            self._flags_off, self._pflags_off, self._mat_off = 0, 64, 128
+            # three independent sets of arrival words: step barriers on the main stream, id-plan barriers on the side
+            # stream, gradient barriers on the sparse stream (they can be in flight at the same time)
+            self._flags_off, self._pflags_off, self._sflags_off, self._mat_off = 0, 64, 128, 192
             self._rows_off = _ru(self._mat_off + 2 * W * W * 4, 256)
             self._g_off = self._rows_off + _ru((self.n_max + 1) * row_bytes, 256)
             self._g_cap = self.n_max if self.train_mode else 0
@@ -451,7 +457,10 @@ class ShardedCtrEngine(CtrEngine):
             self._mark("finalize")
             self._barrier(st)
             self._rows_dirty = False
-            self._launch_peer_reduce()           # the dense gradients of every replica were complete before this barrier
+            if not self._on_sparse:
+                self._launch_peer_reduce()       # the dense gradients of every replica were complete before this barrier
+            # (overlapped backward: the weight gradients are still being computed on the main stream; their reduction
+            # gets a barrier of its own behind them, _reduce_dense_grads)
         else:
             h.call("ctr_embed_bwd_finalize", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
                    ptr(self.part), ptr(self.grads_send))
@@ -475,11 +484,16 @@ class ShardedCtrEngine(CtrEngine):
 
     def _barrier(self, st: int) -> None:
         """all ranks: everything stored into peer slabs so far is visible, and every peer is at the same point"""
-        self._epoch += 1
+        if self._on_sparse:          # issued from the sparse stream (overlapped backward): its own words and epoch
+            self._sepoch += 1
+            flags, epoch = self._sflags_off, self._sepoch
+        else:
+            self._epoch += 1
+            flags, epoch = self._flags_off, self._epoch
         if self.comm.is_loopback:
             self.comm.device_barrier(st)
             return
-        self.h.call("ctr_peer_barrier", st, C.byref(self.cur.route_v), self._flags_off, self._epoch, ptr(self.peer_status),
+        self.h.call("ctr_peer_barrier", st, C.byref(self.cur.route_v), flags, epoch, ptr(self.peer_status),
                     int(os.environ.get("CTR_PEER_TIMEOUT_MS", 10000)))
 
     _dense_work = None
