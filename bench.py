@@ -288,6 +288,11 @@ def main():
     clocks.start()
     t0 = time.time()
     torch.cuda.profiler.start()      # `ncu --profile-from-start off` captures exactly the timed steps
+    # behind the host barrier + synchronize the ranks are still milliseconds apart (8 processes leaving an NCCL barrier):
+    # one device-side rank barrier puts every rank's start event at the same instant, so a short timed window measures
+    # steps and not the start-up skew (it was ~0.1 ms per step over 30 steps at N=8: 1.36 ms against 1.25 per rank)
+    if world > 1:
+        eng.align_ranks()
     e0.record()
     for i in range(a.steps):
         eng.train_step(dev_batches[i % NB], next_batch=dev_batches[(i + 1) % NB])
@@ -319,6 +324,8 @@ def main():
     for i in range(2):
         float(eng.train_step(host_batches[i % NB], next_batch=host_batches[(i + 1) % NB]).item())
     sync()
+    if world > 1:
+        eng.align_ranks()
     e0.record()
     for i in range(a.steps):
         loss = float(eng.train_step(host_batches[i % NB], next_batch=host_batches[(i + 1) % NB]).item())

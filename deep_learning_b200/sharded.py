@@ -496,6 +496,18 @@ class ShardedCtrEngine(CtrEngine):
         self.h.call("ctr_peer_barrier", st, C.byref(self.cur.route_v), flags, epoch, ptr(self.peer_status),
                     int(os.environ.get("CTR_PEER_TIMEOUT_MS", 10000)))
 
+    def align_ranks(self) -> None:
+        """One device-side rank barrier on the current stream (peer-memory mode; a no-op otherwise).  For timing harnesses:
+        processes leave a HOST barrier milliseconds apart, so the early ranks' first step would otherwise wait for the latest
+        rank's host inside the timed window; after this call every rank's stream is at the same instant."""
+        if self.exchange_mode != "peer" or self.cur is None:
+            return
+        self._pin_stream()
+        try:
+            self._barrier(self._stream())
+        finally:
+            self._unpin_stream()
+
     _dense_work = None
 
     def _begin_dense_reduce(self) -> None:
