@@ -22,19 +22,21 @@ class EmbedCfg(C.Structure):
         "reserved0")] + [("table_rows", c_i64), ("status", c_vp)]
 
 
+HEAD_SCE_ON_SCORE, HEAD_NO_RELU_GATE = 1, 2          # CTR_HEAD_* flags of ctr_head_fwd
 STATUS_WORDS = 4          # CTR_STATUS_WORDS: [step barrier, plan barrier, bad id, spare]
 
 
 class AdamHP(C.Structure):
     """mirror of `ctr_adam_hp`"""
     _fields_ = [("lr_t", c_f32), ("beta1", c_f32), ("beta2", c_f32), ("eps", c_f32), ("c1", c_f32), ("c2", c_f32),
-                ("guard", c_vp)]
+                ("guard", c_vp), ("kind", c_i32), ("reserved", c_i32)]
+    ADAM, FTRL = 0, 1
 
-    def __init__(self, lr_t, beta1, beta2, eps, c1=None, c2=None, guard=None):
+    def __init__(self, lr_t, beta1=0.9, beta2=0.999, eps=1e-8, c1=None, c2=None, guard=None, kind=0):
         # c1 = 1 - beta1, c2 = 1 - beta2 from the exact (double) betas, rounded once (see include/ctr_b200.h);
         # guard: device pointer of the engine's status words (the update is skipped while they report a fault)
         super().__init__(lr_t, beta1, beta2, eps, 1.0 - beta1 if c1 is None else c1, 1.0 - beta2 if c2 is None else c2,
-                         guard)
+                         guard, kind, 0)
 
 
 MAX_LAYERS = 8
@@ -92,7 +94,7 @@ _PROTOS = {
     "ctr_round_tf32_copy": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64]),
     "ctr_head_ws_bytes": (c_i64, [c_vp, c_i32, c_i32, c_i32]),
     "ctr_head_fwd": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp,
-                             c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
+                             c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i32]),
     "ctr_head_bwd_deep": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64, c_vp, c_i64]),
     "ctr_colsum_ws_bytes": (c_i64, [c_vp, c_i32, c_i32]),
     "ctr_colsum": (c_i32, [c_vp, c_vp, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_i64]),
@@ -169,7 +171,7 @@ def load(path: str = LIB_PATH) -> C.CDLL:
         fn.restype = res
         if args is not None:
             fn.argtypes = args
-    if lib.ctr_abi_version() != 2:
+    if lib.ctr_abi_version() != 3:
         raise CtrError("ABI version mismatch")
     if lib.ctr_sizeof_embed_cfg() != C.sizeof(EmbedCfg):
         raise CtrError("ctr_embed_cfg layout mismatch")

@@ -209,6 +209,33 @@ embed_bwd_finalize_kernel(const uint32_t* __restrict__ seg_start, const uint32_t
     }
 }
 
+// One element of the optimizer step, shared by every update kernel of this file.
+//   kind 0  TF1 Adam (adam.py, epsilon-hat form):  m <- b1 m + c1 g ; v <- b2 v + c2 g^2 ; th -= lr_t m / (sqrt(v) + eps)
+//   kind 1  TF1 FTRL (ftrl.py -> ApplyFtrl / SparseApplyFtrl with the defaults lr_power = -0.5, l1 = l2 = 0;
+//           test_model/wdl.py:136), slot m = `accum`, slot v = `linear`, hp.lr_t = the (decayed) learning rate:
+//             accum' = accum + g^2 ; linear += g - (sqrt(accum') - sqrt(accum)) / lr * th ; th = -linear / (sqrt(accum') / lr)
+//           (th = 0 where linear == 0: a looked-up weight whose gradient has always been zero is SET to zero, as the
+//           TF kernel does)
+__device__ __forceinline__ void opt_update(float& th, float& m, float& v, const float g, const ctr_adam_hp& hp) {
+    if (hp.kind == 1) {
+        // sqrt(accum') - sqrt(accum) is written as g^2 / (sqrt(accum') + sqrt(accum)): the same number without the
+        // cancellation (accum = 0.1, g^2 ~ 1e-8: in float32 the difference of the two roots keeps 1-2 digits, and it is
+        // multiplied by th / lr.  The reference's own file run in float32 lands 1.5e-4 from its float64 run for this reason,
+        // tests/golden/fp32floor_wdl_ftrl.npz)
+        const float gg = g * g;
+        const float acc_new = m + gg;
+        const float sq_new = sqrtf(acc_new);
+        const float lin = v + g - gg / (sq_new + sqrtf(m)) / hp.lr_t * th;
+        m = acc_new;
+        v = lin;
+        th = lin != 0.f ? -lin / (sq_new / hp.lr_t) : 0.f;
+        return;
+    }
+    m = hp.beta1 * m + hp.c1 * g;
+    v = hp.beta2 * v + hp.c2 * g * g;
+    th -= hp.lr_t * m / (sqrtf(v) + hp.eps);
+}
+
 // generic width (any table): one thread per (row, coordinate)
 __global__ void __launch_bounds__(256)
 adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restrict__ n_rows, int64_t n_max, uint32_t mask,
@@ -241,22 +268,18 @@ adam_rows_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restric
             const float D = seg_start ? sum_run_partials(grads, seg_start, u, emb_k + 1, gs) : grads[u * gs + emb_k + 1];
             g = fmaf(-fm_w2[j] * table[o], D, g);
         }
-        const float mm = hp.beta1 * m[o] + hp.c1 * g;
-        const float vv = hp.beta2 * v[o] + hp.c2 * g * g;
+        float th_ = table[o], mm = m[o], vv = v[o];
+        opt_update(th_, mm, vv, g, hp);
         m[o] = mm;
         v[o] = vv;
-        table[o] -= hp.lr_t * mm / (sqrtf(vv) + hp.eps);
+        table[o] = th_;
         if (j == 0 && touched) touched[row] = 1;
     }
 }
 
 __device__ __forceinline__ void adam4(float4& th, float4& mm, float4& vv, const float4 g, const ctr_adam_hp& hp) {
-    const float b1 = hp.beta1, b2 = hp.beta2, c1 = hp.c1, c2 = hp.c2;
-    mm.x = b1 * mm.x + c1 * g.x; mm.y = b1 * mm.y + c1 * g.y; mm.z = b1 * mm.z + c1 * g.z; mm.w = b1 * mm.w + c1 * g.w;
-    vv.x = b2 * vv.x + c2 * g.x * g.x; vv.y = b2 * vv.y + c2 * g.y * g.y;
-    vv.z = b2 * vv.z + c2 * g.z * g.z; vv.w = b2 * vv.w + c2 * g.w * g.w;
-    th.x -= hp.lr_t * mm.x / (sqrtf(vv.x) + hp.eps); th.y -= hp.lr_t * mm.y / (sqrtf(vv.y) + hp.eps);
-    th.z -= hp.lr_t * mm.z / (sqrtf(vv.z) + hp.eps); th.w -= hp.lr_t * mm.w / (sqrtf(vv.w) + hp.eps);
+    opt_update(th.x, mm.x, vv.x, g.x, hp); opt_update(th.y, mm.y, vv.y, g.y, hp);
+    opt_update(th.z, mm.z, vv.z, g.z, hp); opt_update(th.w, mm.w, vv.w, g.w, hp);
 }
 
 // embedding tables (row = K coordinates [+ first-order weight]): K/4 lanes per row, 128-bit accesses, every load of a
@@ -325,11 +348,10 @@ adam_rows_vec_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __res
         *reinterpret_cast<float4*>(v + o) = vv;
         *reinterpret_cast<float4*>(table + o) = th;
         if (first) {
-            m1 = hp.beta1 * m1 + hp.c1 * g1;
-            v1 = hp.beta2 * v1 + hp.c2 * g1 * g1;
+            opt_update(th1, m1, v1, g1, hp);
             m[row * stride + K] = m1;
             v[row * stride + K] = v1;
-            table[row * stride + K] = th1 - hp.lr_t * m1 / (sqrtf(v1) + hp.eps);
+            table[row * stride + K] = th1;
         }
         if (q == 0 && touched) touched[row] = 1;
     }
@@ -393,11 +415,11 @@ adam_rows_long_kernel(const uint32_t* __restrict__ row_ids, uint32_t mask, const
             float g = pick(j);
             const int64_t o = row * stride + j;
             if (fm_w2 && j < emb_k) g = fmaf(-fm_w2[j] * table[o], D, g);
-            const float mm = hp.beta1 * m[o] + hp.c1 * g;
-            const float vv = hp.beta2 * v[o] + hp.c2 * g * g;
+            float th_ = table[o], mm = m[o], vv = v[o];
+            opt_update(th_, mm, vv, g, hp);
             m[o] = mm;
             v[o] = vv;
-            table[o] -= hp.lr_t * mm / (sqrtf(vv) + hp.eps);
+            table[o] = th_;
         }
         if (lane == 0 && touched) touched[row] = 1;
     }
@@ -413,11 +435,11 @@ adam_dense_kernel(float* __restrict__ theta, float* __restrict__ m, float* __res
         float gi = g ? g[i] : 0.f;
         if (l2 != 0.f) gi = fmaf(l2, th, gi);
         if (l1 != 0.f) gi += l1 * (th > 0.f ? 1.f : (th < 0.f ? -1.f : 0.f));
-        const float mm = hp.beta1 * m[i] + hp.c1 * gi;
-        const float vv = hp.beta2 * v[i] + hp.c2 * gi * gi;
+        float nt_ = th, mm = m[i], vv = v[i];
+        opt_update(nt_, mm, vv, gi, hp);
         m[i] = mm;
         v[i] = vv;
-        theta[i] = th - hp.lr_t * mm / (sqrtf(vv) + hp.eps);
+        theta[i] = nt_;
     }
 }
 
@@ -434,11 +456,10 @@ dense_update_kernel(float* __restrict__ theta, float* __restrict__ m, float* __r
         float gi = g[i];
         if (i >= lay.group_end[1]) gi += lay.reg_scale * (th > 0.f ? 1.f : (th < 0.f ? -1.f : 0.f));     // l1 group
         else if (i >= lay.group_end[0]) gi = fmaf(lay.reg_scale, th, gi);                                 // l2 group
-        const float mm = hp.beta1 * m[i] + hp.c1 * gi;
-        const float vv = hp.beta2 * v[i] + hp.c2 * gi * gi;
+        float nt = th, mm = m[i], vv = v[i];
+        opt_update(nt, mm, vv, gi, hp);
         m[i] = mm;
         v[i] = vv;
-        const float nt = th - hp.lr_t * mm / (sqrtf(vv) + hp.eps);
         theta[i] = nt;
 #pragma unroll 1
         for (int l = 0; l < lay.n_layers; ++l) {
@@ -766,7 +787,7 @@ extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_id
                              uint8_t* touched, void* ws, int64_t ws_bytes, const float* fm_w2, int emb_k,
                              const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, row_ids && grads && table && m && v && hp, "adam_rows: null pointer");
-    CTR_REQUIRE(h, hp->c1 > 0.f && hp->c2 > 0.f, "adam_rows: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
+    CTR_REQUIRE(h, (hp->kind == 1 ? hp->lr_t > 0.f : (hp->c1 > 0.f && hp->c2 > 0.f)) && (hp->kind == 0 || hp->kind == 1), "adam_rows: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
     CTR_REQUIRE(h, width > 0 && grad_stride >= width && table_stride >= width && n_max >= 0 && table_rows > 0,
                 "adam_rows: bad sizes");
     CTR_REQUIRE(h, !fm_w2 || (emb_k > 0 && emb_k <= width && grad_stride >= emb_k + 2), "adam_rows: fm_w2 needs grad_stride >= emb_k + 2");
@@ -817,7 +838,7 @@ extern "C" int ctr_adam_rows_gathered(ctr_handle* h, ctr_stream s, const uint32_
                                       int src_stride, int width, float* table, float* m, float* v, int table_stride,
                                       int64_t table_rows, uint8_t* touched, const float* fm_w2, int emb_k, const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, row_ids && n_rows && src && perm && seg_start && table && m && v && hp, "adam_rows_gathered: null pointer");
-    CTR_REQUIRE(h, hp->c1 > 0.f && hp->c2 > 0.f, "adam_rows_gathered: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
+    CTR_REQUIRE(h, (hp->kind == 1 ? hp->lr_t > 0.f : (hp->c1 > 0.f && hp->c2 > 0.f)) && (hp->kind == 0 || hp->kind == 1), "adam_rows_gathered: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
     CTR_REQUIRE(h, n_max >= 0 && table_rows > 0 && (emb_k == 4 || emb_k == 8 || emb_k == 16 || emb_k == 32) &&
                        (width == emb_k || width == emb_k + 1) && table_stride % 4 == 0 && table_stride >= width &&
                        src_stride % 4 == 0 && src_stride >= width + (fm_w2 ? (emb_k + 2 - width) : 0),
@@ -845,7 +866,7 @@ extern "C" int ctr_adam_rows_gathered(ctr_handle* h, ctr_stream s, const uint32_
 extern "C" int ctr_adam_dense(ctr_handle* h, ctr_stream s, float* theta, float* m, float* v, const float* g, int64_t n,
                               float l2, float l1, uint8_t* skip, int skip_group, const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, theta && m && v && hp && n >= 0 && (!skip || skip_group > 0), "adam_dense: bad args");
-    CTR_REQUIRE(h, hp->c1 > 0.f && hp->c2 > 0.f, "adam_dense: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
+    CTR_REQUIRE(h, (hp->kind == 1 ? hp->lr_t > 0.f : (hp->c1 > 0.f && hp->c2 > 0.f)) && (hp->kind == 0 || hp->kind == 1), "adam_dense: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
     if (n == 0) return CTR_OK;
     adam_dense_kernel<<<grid_for(h, n), 256, 0, ctr_st(s)>>>(theta, m, v, g, n, l2, l1, skip, skip_group, *hp);
     CTR_CHECK_LAUNCH(h, "adam_dense");
@@ -860,7 +881,7 @@ extern "C" int ctr_adam_dense(ctr_handle* h, ctr_stream s, float* theta, float* 
 extern "C" int ctr_dense_update(ctr_handle* h, ctr_stream s, float* theta, float* m, float* v, const float* g,
                                 const ctr_dense_layout* lay, const ctr_adam_hp* hp) {
     CTR_REQUIRE(h, theta && m && v && g && lay && hp, "dense_update: null pointer");
-    CTR_REQUIRE(h, hp->c1 > 0.f && hp->c2 > 0.f, "dense_update: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
+    CTR_REQUIRE(h, (hp->kind == 1 ? hp->lr_t > 0.f : (hp->c1 > 0.f && hp->c2 > 0.f)) && (hp->kind == 0 || hp->kind == 1), "dense_update: ctr_adam_hp.c1 / c2 (= 1 - beta, from the exact betas) must be set");
     CTR_REQUIRE(h, lay->group_end[0] >= 0 && lay->group_end[0] <= lay->group_end[1] && lay->group_end[1] <= lay->group_end[2] &&
                        lay->n_layers >= 0 && lay->n_layers <= CTR_MAX_LAYERS, "dense_update: bad layout");
     for (int l = 0; l < lay->n_layers; ++l)

@@ -4,6 +4,21 @@
 
 namespace {
 
+// per-sample loss and d loss / d logit (before the 1 / B_global factor) for score p = sigmoid(z), label y
+//   flags & CTR_HEAD_SCE_ON_SCORE == 0: tf.losses.log_loss (models/deepfm.py:151-152):  -y log(p+e) - (1-y) log(1-p+e)
+//   flags & CTR_HEAD_SCE_ON_SCORE:      test_model/wdl.py:119-121 feeds the ALREADY-sigmoided value to
+//       tf.nn.sigmoid_cross_entropy_with_logits: with x = p in (0,1):  x - x y + log(1 + exp(-x)); d/dx = sigmoid(x) - y,
+//       and dx/dz = p (1 - p)
+__device__ __forceinline__ void head_loss(float p, float y, int flags, float eps, float& loss, float& dl_dz) {
+    if (flags & CTR_HEAD_SCE_ON_SCORE) {
+        loss = p - p * y + log1pf(expf(-p));
+        dl_dz = (1.f / (1.f + expf(-p)) - y) * p * (1.f - p);
+    } else {
+        loss = -y * logf(p + eps) - (1.f - y) * logf(1.f - p + eps);
+        dl_dz = (-y / (p + eps) + (1.f - y) / (1.f - p + eps)) * p * (1.f - p);
+    }
+}
+
 constexpr float LOG_LOSS_EPS = 1e-7f;   // tf.losses.log_loss default epsilon
 
 // One warp walks HEAD_SPW consecutive samples; lane l owns columns l, l+32, ... of the deep row (and of the fm row),
@@ -23,7 +38,8 @@ head_fwd_kernel(int B, float inv_bg, const float* __restrict__ fm, int64_t fm_ld
                 const float* __restrict__ extra, const float* __restrict__ bias, const float* __restrict__ label,
                 float* __restrict__ logit, float* __restrict__ score, float* __restrict__ dlogit,
                 float* __restrict__ dz_last, int64_t lddz, int round_tf32, float* __restrict__ loss_part,
-                float* __restrict__ colpart) {
+                float* __restrict__ colpart, int flags) {
+    const bool gate = (flags & CTR_HEAD_NO_RELU_GATE) == 0;      // dz_last passes through the tower's last ReLU
     extern __shared__ float sm[];                  // [HEAD_WARPS][H + n_fm + 1] when colpart, else [HEAD_WARPS]
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int ncol = H + n_fm + 1;
@@ -71,9 +87,11 @@ head_fwd_kernel(int B, float inv_bg, const float* __restrict__ fm, int64_t fm_ld
         }
         if (label) {
             const float y = label[b];
-            lsum += -y * logf(p + LOG_LOSS_EPS) - (1.f - y) * logf(1.f - p + LOG_LOSS_EPS);
             // d/dz [ -y log(p+e) - (1-y) log(1-p+e) ] = (-y/(p+e) + (1-y)/(1-p+e)) * p(1-p), mean over the global batch
-            const float dl = (-y / (p + LOG_LOSS_EPS) + (1.f - y) / (1.f - p + LOG_LOSS_EPS)) * p * (1.f - p) * inv_bg;
+            float l_, d_;
+            head_loss(p, y, flags, LOG_LOSS_EPS, l_, d_);
+            lsum += l_;
+            const float dl = d_ * inv_bg;
             if (lane == 0 && dlogit) dlogit[b] = dl;
             if (dz_last) {
                 // gradient through the last ReLU: dZ_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)
@@ -82,7 +100,7 @@ head_fwd_kernel(int B, float inv_bg, const float* __restrict__ fm, int64_t fm_ld
                 for (int t = 0; t < HEAD_MAXT; ++t) {
                     const int j = lane + 32 * t;
                     if (j < H) {
-                        const float g = rd[t] > 0.f ? dl * wd[t] : 0.f;
+                        const float g = (!gate || rd[t] > 0.f) ? dl * wd[t] : 0.f;
                         o[j] = round_tf32 ? ctr_round_tf32(g) : g;
                     }
                 }
@@ -149,7 +167,8 @@ head_fwd_vec_kernel(int B, float inv_bg, const float* __restrict__ fm, int64_t f
                     const float* __restrict__ extra, const float* __restrict__ bias, const float* __restrict__ label,
                     float* __restrict__ logit, float* __restrict__ score, float* __restrict__ dlogit,
                     float* __restrict__ dz_last, int64_t lddz, int round_tf32, float* __restrict__ loss_part,
-                    float* __restrict__ colpart) {
+                    float* __restrict__ colpart, int flags) {
+    const bool gate = (flags & CTR_HEAD_NO_RELU_GATE) == 0;
     extern __shared__ float sm[];                  // [HV_WARPS][H + n_fm + 1] when colpart, else [HV_WARPS]
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int ncol = H + n_fm + 1;
@@ -207,8 +226,10 @@ head_fwd_vec_kernel(int B, float inv_bg, const float* __restrict__ fm, int64_t f
         }
         if (label) {
             const float y = label[b];
-            lsum += -y * logf(p + LOG_LOSS_EPS) - (1.f - y) * logf(1.f - p + LOG_LOSS_EPS);
-            const float dl = (-y / (p + LOG_LOSS_EPS) + (1.f - y) / (1.f - p + LOG_LOSS_EPS)) * p * (1.f - p) * inv_bg;
+            float l_, d_;
+            head_loss(p, y, flags, LOG_LOSS_EPS, l_, d_);
+            lsum += l_;
+            const float dl = d_ * inv_bg;
             if (lane == 0 && dlogit) dlogit[b] = dl;
             if (dz_last) {
                 float* o = dz_last + b * lddz;
@@ -217,10 +238,10 @@ head_fwd_vec_kernel(int B, float inv_bg, const float* __restrict__ fm, int64_t f
                     const int j = 4 * lane + 128 * t;
                     if (j < H) {
                         float4 g;
-                        g.x = cur[t].x > 0.f ? dl * wd[t].x : 0.f;
-                        g.y = cur[t].y > 0.f ? dl * wd[t].y : 0.f;
-                        g.z = cur[t].z > 0.f ? dl * wd[t].z : 0.f;
-                        g.w = cur[t].w > 0.f ? dl * wd[t].w : 0.f;
+                        g.x = (!gate || cur[t].x > 0.f) ? dl * wd[t].x : 0.f;
+                        g.y = (!gate || cur[t].y > 0.f) ? dl * wd[t].y : 0.f;
+                        g.z = (!gate || cur[t].z > 0.f) ? dl * wd[t].z : 0.f;
+                        g.w = (!gate || cur[t].w > 0.f) ? dl * wd[t].w : 0.f;
                         if (round_tf32) g = make_float4(ctr_round_tf32(g.x), ctr_round_tf32(g.y), ctr_round_tf32(g.z), ctr_round_tf32(g.w));
                         *reinterpret_cast<float4*>(o + j) = g;
                     }
@@ -372,7 +393,7 @@ extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, int64_t B_global
                             const float* w_fm, const float* deep, int64_t deep_ld, int H, const float* w_deep,
                             const float* extra, const float* bias, const float* label, float* logit, float* score,
                             float* dlogit, float* dz_last, int64_t lddz, int round_tf32, float* loss_out,
-                            float* g_fm, float* g_deep, float* g_bias, void* ws, int64_t ws_bytes) {
+                            float* g_fm, float* g_deep, float* g_bias, void* ws, int64_t ws_bytes, int flags) {
     CTR_REQUIRE(h, B >= 0 && n_fm >= 0 && H >= 0, "head_fwd: negative sizes");
     CTR_REQUIRE(h, n_fm == 0 || (fm && w_fm), "head_fwd: fm inputs null");
     CTR_REQUIRE(h, H == 0 || (deep && w_deep), "head_fwd: deep inputs null");
@@ -396,11 +417,11 @@ extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, int64_t B_global
     if (vec)
         head_fwd_vec_kernel<<<nblk, 256, smem, ctr_st(s)>>>(B, inv_bg, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra,
                                                             bias, label, logit, score, dlogit, dz_last, lddz, round_tf32,
-                                                            loss_out ? part : nullptr, colpart);
+                                                            loss_out ? part : nullptr, colpart, flags);
     else
         head_fwd_kernel<<<nblk, 256, smem, ctr_st(s)>>>(B, inv_bg, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra, bias,
                                                         label, logit, score, dlogit, dz_last, lddz, round_tf32,
-                                                        loss_out ? part : nullptr, colpart);
+                                                        loss_out ? part : nullptr, colpart, flags);
     CTR_CHECK_LAUNCH(h, "head_fwd");
     if (label && loss_out) {
         loss_final_kernel<<<1, 1024, 0, ctr_st(s)>>>(part, nblk, inv_bg, loss_out);

@@ -30,6 +30,7 @@ _BWD_OVERLAP = os.environ.get("CTR_BWD_ORDER", "serial") == "overlap"
 from .spec import ModelSpec
 
 ADAM_BETA1, ADAM_BETA2, ADAM_EPS = 0.9, 0.999, 1e-8   # tf.train.AdamOptimizer defaults (models/deepfm.py:161)
+FTRL_INIT_ACCUM = 0.1                                 # tf.train.FtrlOptimizer default (test_model/wdl.py:136)
 PREC = {"fp32": 0, "tf32": 1}
 _ALIGN = 64   # floats; keeps every dense parameter 256-byte aligned inside the flat buffer
 
@@ -140,6 +141,11 @@ class CtrEngine:
         if train:
             self.m_table, self.v_table = torch.zeros_like(self.table), torch.zeros_like(self.table)
             self.m, self.v = (torch.zeros(cur, **f32) for _ in range(2))
+            if s.optimizer == "ftrl":
+                # FtrlOptimizer's slots: m holds `accum` (initial_accumulator_value 0.1), v holds `linear` (0); the row
+                # kernels are its sparse apply, so the step never sweeps the whole table whatever adam_mode says
+                self.m_table.fill_(FTRL_INIT_ACCUM)
+                self.m.fill_(FTRL_INIT_ACCUM)
             self.grad = torch.zeros(cur + _ALIGN, **f32)     # tail slot [cur] carries the loss share through the allreduce
             maxh = max(s.hidden)
             # one dZ per layer: the data gradients of ALL layers run first (so dX0 exists early and the sparse side can
@@ -315,8 +321,10 @@ class CtrEngine:
             return w[:s.n_fm], w[s.n_fm:s.n_fm + H], self.view(s.head_b_name, buf)
         if s.head == "dnn":
             return None, self.view(s.head_w_name, buf), self.view(s.head_b_name, buf)
-        w = self.view("wdl_weights", buf)     # quirk Q4: deep weights alias rows W..W+H-1 (models/wdl.py:224-225)
-        return None, w[s.wide_fields:s.wide_fields + H], self.view("wdl_bias", buf)
+        # quirk Q4: in models/wdl.py:224-225 the deep weights alias rows W..W+H-1; test_model/wdl.py:110 puts them behind
+        w = self.view("wdl_weights", buf)
+        off = s.wide_fields if s.deep_row_offset is None else s.deep_row_offset
+        return None, w[off:off + H], self.view("wdl_bias", buf)
 
     # ---- parameter injection / read-back (reference names and shapes) ------------------------------
     def set_weights(self, p: Dict[str, np.ndarray]) -> None:
@@ -634,7 +642,8 @@ class CtrEngine:
                ptr(extra), ptr(bias), ptr(lab), ptr(self.logit), ptr(self.score),
                ptr(self.dlogit) if with_loss else None,
                ptr(self.dz[0]) if (with_loss and self.train_mode) else None, s.hidden[-1], int(self.prec == 1),
-               ptr(self.loss) if with_loss else None, ptr(g_fm), ptr(g_deep), ptr(g_bias), ptr(self.ws), self.ws.numel())
+               ptr(self.loss) if with_loss else None, ptr(g_fm), ptr(g_deep), ptr(g_bias), ptr(self.ws), self.ws.numel(),
+               _lib.HEAD_SCE_ON_SCORE if s.loss == "sce_on_score" else 0)
         if self._sort_B is not None:        # CTR_SORT_AT=head: the sort runs under the backward GEMMs instead (A/B knob)
             self._launch_sort(self._sort_B)
             self._sort_B = None
@@ -661,6 +670,8 @@ class CtrEngine:
         """TF1 Adam step size (adam.py): lr from exponential_decay(staircase) on the PRE-increment
         global_step (models/deepfm.py:159-162), then lr_t = lr*sqrt(1-b2^t)/(1-b1^t)."""
         lr = self.lr0 * self.decay_rate ** math.floor(self.global_step / self.decay_steps)
+        if self.spec.optimizer == "ftrl":      # test_model/wdl.py:132-136: FtrlOptimizer(learning_rate=<decayed lr>)
+            return AdamHP(lr_t=lr, guard=self.status.data_ptr(), kind=AdamHP.FTRL)
         lr_t = lr * math.sqrt(1.0 - self.beta2_power) / (1.0 - self.beta1_power)
         return AdamHP(lr_t=lr_t, beta1=ADAM_BETA1, beta2=ADAM_BETA2, eps=ADAM_EPS, guard=self.status.data_ptr())
 
@@ -721,7 +732,7 @@ class CtrEngine:
             self._mark("sparse_update")
         self._reduce_dense_grads()
         self._mark("dense_reduce")
-        if self.adam_mode == "tf_dense":
+        if self.adam_mode == "tf_dense" and s.optimizer != "ftrl":
             # TF1 Adam moves EVERY row each step (m, v decay; theta -= lr_t*m/(sqrt(v)+eps)) -- exact mode
             h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
                    self.rows_local * s.table_stride, 0.0, 0.0, ptr(self.touched), s.table_stride, hp)
@@ -785,7 +796,7 @@ class CtrEngine:
                         ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.sw),
                         ptr(self.part))
             self._sparse_update(B, n, hp)
-            if self.adam_mode == "tf_dense":
+            if self.adam_mode == "tf_dense" and s.optimizer != "ftrl":
                 # TF1 Adam moves EVERY row each step (m, v decay; theta -= lr_t*m/(sqrt(v)+eps)) -- exact mode
                 h.call("ctr_adam_dense", sp.cuda_stream, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
                        self.rows_local * s.table_stride, 0.0, 0.0, ptr(self.touched), s.table_stride, hp)

@@ -42,6 +42,11 @@ class ModelSpec:
     frozen_name: Optional[str] = None     # reference constant appended to the table as never-updated rows ('tags_emb')
     frozen_rows: int = 0
     frozen_fields: Tuple[int, ...] = ()   # multi-valued fields that look up the frozen rows (feat_name == 'tag')
+    optimizer: str = "adam"     # 'adam': tf.train.AdamOptimizer (every models/*.py) | 'ftrl': FtrlOptimizer (test_model/wdl.py:136)
+    loss: str = "log_loss"      # 'log_loss' (models/deepfm.py:151) | 'sce_on_score' (test_model/wdl.py:119-121)
+    deep_row_offset: Optional[int] = None   # wdl head: first row of the deep-projection weights inside wdl_weights.  None:
+                                            # wide_fields, the aliasing of models/wdl.py:224-228 (quirk Q4);
+                                            # test_model/wdl.py:110 puts them behind the wide ids (cate_feats_size)
     split_fm: bool = False      # quirk Q2 (models/deepfm_pipeline.py:89,120): the FM part reads row id + C, the deep part row id
 
     @property
@@ -246,6 +251,17 @@ def spec_from_hparams(alg: str, hp) -> ModelSpec:
                          table_rows=int(hp.cate_index_size), emb_name="weight_mat", first_name=None, zero_row0=True,
                          head="wdl", head_w_name="wdl_weights", head_b_name="wdl_bias", l2_reg=l2, reg=reg,
                          wide_fields=int(hp.wide_field_size), wide_rows=int(hp.cate_index_size), gathered_l2=True)
+    if alg == "wdl_ftrl":
+        # test_model/wdl.py: ONE size for the table, the wide ids and the offset of the deep-projection
+        # rows (:61-64, :101-111); FTRL (:136); cross-entropy on the sigmoided value (:119-121); l2 on wdl_weights + deep_i
+        reg = {"deep_%d" % i: "l2" for i in range(len(H))}
+        reg["wdl_weights"] = "l2"
+        R = int(hp.cate_feats_size)
+        return ModelSpec(alg, C=int(hp.cont_field_size), V=0, Fc=int(hp.cate_field_size), k=k, hidden=H,
+                         table_rows=R, emb_name="weight_mat", first_name=None,
+                         head="wdl", head_w_name="wdl_weights", head_b_name="wdl_bias", l2_reg=l2, reg=reg,
+                         wide_fields=int(hp.wide_field_size), wide_rows=R, deep_row_offset=R,
+                         optimizer="ftrl", loss="sce_on_score")
     if alg == "wdl":
         reg = {"deep_%d" % i: "l2" for i in range(len(H))}
         reg["wdl_weights"] = "l2"

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define CTR_ABI_VERSION 2
+#define CTR_ABI_VERSION 3
 
 #define CTR_OK              0
 #define CTR_E_INVALID      -1   /* bad argument / unsupported shape */
@@ -181,6 +181,8 @@ int ctr_round_tf32_copy(ctr_handle* h, ctr_stream s, const float* in, float* out
  *   g_fm[j] = sum_b dlogit[b]*fm[b,j], g_deep[j] = sum_b dlogit[b]*deep[b,j], g_bias = sum_b dlogit[b]   (optional, with
  *             label: the head-weight gradients, accumulated while the rows are in registers; H <= 512, n_fm <= 128)
  * loss_out: one float, written by a second deterministic reduction pass. ws: ctr_head_ws_bytes() */
+#define CTR_HEAD_SCE_ON_SCORE 1
+#define CTR_HEAD_NO_RELU_GATE 2
 int64_t ctr_head_ws_bytes(ctr_handle* h, int B, int n_fm, int H);
 int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B,
                  int64_t B_global /* samples the loss is a mean over: B on one GPU, the sum of all ranks' batches when
@@ -191,7 +193,11 @@ int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B,
                  const float* extra, const float* bias,
                  const float* label, float* logit, float* score, float* dlogit, float* dz_last, int64_t lddz,
                  int round_tf32 /* round dz_last to tf32 */, float* loss_out,
-                 float* g_fm /*[n_fm]*/, float* g_deep /*[H]*/, float* g_bias /*[1]*/, void* ws, int64_t ws_bytes);
+                 float* g_fm /*[n_fm]*/, float* g_deep /*[H]*/, float* g_bias /*[1]*/, void* ws, int64_t ws_bytes,
+                 int flags /* 0: every models/*.py.  CTR_HEAD_SCE_ON_SCORE: the loss of test_model/wdl.py:119-121,
+                 tf.nn.sigmoid_cross_entropy_with_logits applied to the ALREADY-sigmoided score.  CTR_HEAD_NO_RELU_GATE:
+                 dz_last = dlogit * w_deep without the (deep > 0) gate -- the tower of test_model/DCN.py:66-70 has no
+                 activation */);
 /* dZ_last[b,j] = dlogit[b] * w_deep[j] * (deep[b,j] > 0)        (through the last ReLU) */
 int ctr_head_bwd_deep(ctr_handle* h, ctr_stream s, int B, int H, const float* dlogit, const float* w_deep,
                       const float* deep, int64_t deep_ld, float* dZ, int64_t lddz);
@@ -331,7 +337,15 @@ typedef struct ctr_adam_hp {
     float lr_t, beta1, beta2, eps, c1, c2;
     const uint32_t* guard;   /* device status words (CTR_STATUS_WORDS) or NULL: the update is skipped while one of the
                                 first three is non-zero */
+    int32_t kind;            /* CTR_OPT_ADAM (0): tf.train.AdamOptimizer, every models/*.py (models/deepfm.py:161).
+                                CTR_OPT_FTRL (1): tf.train.FtrlOptimizer with its defaults (test_model/wdl.py:136); slot m
+                                holds `accum` (initialise to 0.1), slot v holds `linear`, lr_t is the decayed learning
+                                rate; beta1 / beta2 / eps / c1 / c2 are not read.  The row kernels are the SPARSE apply
+                                (looked-up rows only), ctr_adam_dense / ctr_dense_update the dense one. */
+    int32_t reserved;
 } ctr_adam_hp;
+#define CTR_OPT_ADAM 0
+#define CTR_OPT_FTRL 1
 int64_t ctr_adam_rows_ws_bytes(ctr_handle* h, int64_t n_max);
 int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_ids, const uint32_t* n_rows, int64_t n_max,
                   int local_bits, const float* grads, const uint32_t* seg_start /* non-NULL: `grads` is the

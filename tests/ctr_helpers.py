@@ -76,7 +76,7 @@ def make_batch(alg, hp, seed, B=None, dist="zipf", id_dtype=None):
     if id_dtype is None:
         id_dtype = torch.int64 if reserve else torch.int32          # the tf.data generation parses int64 ids
     b = D.synthetic_batch(B, hp.cont_field_size, hp.cate_field_size, sizes, seed, V=hp.vector_feats_size,
-                          multi_top_n=tops, multi_sizes=multi_rows, wide=hp.wide_field_size if alg in ("wdl", "wdl_textline") else 0,
+                          multi_top_n=tops, multi_sizes=multi_rows, wide=hp.wide_field_size if alg in ("wdl", "wdl_textline", "wdl_ftrl") else 0,
                           dist=dist, reserve_zero=reserve, id_dtype=id_dtype)
     return b
 

@@ -199,7 +199,7 @@ def test_head_fwd_both_kernels_match_fp64(hd, B, H, n_fm, w_off, with_extra):
     ws = torch.zeros(wsn, dtype=torch.uint8, device="cuda")
     hd.call("ctr_head_fwd", _st(), B, 2 * B, ptr(fm) if n_fm else None, fm_ld, n_fm, ptr(w_fm) if n_fm else None, ptr(deep), deep_ld, H,
             ptr(w_deep), ptr(extra), ptr(bias), ptr(label), ptr(logit), ptr(score), ptr(dlogit), ptr(dz), lddz, 0, ptr(loss),
-            ptr(g_fm) if n_fm else None, ptr(g_deep), ptr(g_bias), ptr(ws), wsn)
+            ptr(g_fm) if n_fm else None, ptr(g_deep), ptr(g_bias), ptr(ws), wsn, 0)
     d64 = lambda t: t.double().cpu()
     z = d64(deep[:, :H]) @ d64(w_deep) + d64(bias)
     if n_fm:

@@ -30,7 +30,7 @@ def _run_parity(alg, hp, steps, precision="fp32", adam_mode="tf_dense", B=None, 
     tol = TOL[precision]
     B = B or hp.batch_size
     p = O.init_params(alg, hp, seed=2019, dtype=torch.float64)
-    st = O.adam_init(p)
+    st = O.optimizer_init(alg, p)            # Adam slots, or FTRL's (accum 0.1, linear 0) for test_model/wdl.py
     eng = _engine(alg, hp, p, hp.batch_size, precision, adam_mode)
     # weights survive the round trip through the device layouts bit-exactly
     back = eng.get_weights()
@@ -98,6 +98,14 @@ def test_deepfm_c1_three_steps_tf_exact_adam():
 
 def test_deepfm_c1_lazy_adam():
     _run_parity("deepfm", H.hp_c1(), steps=3, adam_mode="lazy")
+
+
+def test_wdl_ftrl_test_model_variant():
+    """SURVEY.md 8f N4, test_model/wdl.py: deep rows behind the wide ids (:110), FtrlOptimizer (:136: sparse apply on the
+    table, dense on everything else), sigmoid_cross_entropy_with_logits on the sigmoided value (:119-121)"""
+    hp = H.hp_c1(wide_field_size=20, l2_reg=1e-4)
+    _run_parity("wdl_ftrl", hp, steps=3, adam_mode="lazy")
+    _run_parity("wdl_ftrl", H.hp_criteo(B=512, rows=20000), steps=2, adam_mode="lazy")
 
 
 def test_deepfm_short_last_batch_and_uniform_ids():

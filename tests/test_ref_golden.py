@@ -26,6 +26,7 @@ ALGS = [os.path.basename(f)[4:-4] for f in FILES]
 # (wdl_ftrl, dcn) are pinned at the ORACLE level only so far -- their CUDA path is not built, so the
 # GPU replay (tests/test_ref_gpu.py) and the live surface checks (tests/test_ref_live.py) run over MODEL_ALGS
 MODEL_ALGS = [a for a in ALGS if a not in O.TEST_MODEL_FILES]
+CUDA_ALGS = MODEL_ALGS + [a for a in ALGS if a in ("wdl_ftrl",)]      # what tests/test_ref_gpu.py replays on the device
 
 TOL = 1e-12          # float64 on both sides, same operation order up to summation order inside torch reductions
 

@@ -18,7 +18,7 @@ import torch
 
 import ctr_helpers as H
 from golden.make_golden import tiny_hp
-from test_ref_golden import MODEL_ALGS as ALGS, HERE, LOGIT_EVAL          # the 13 files of models/ (test_model/ extras: oracle level only so far)
+from test_ref_golden import CUDA_ALGS as ALGS, HERE, LOGIT_EVAL          # the 13 files of models/ + test_model/wdl.py (DCN: oracle level only so far)
 
 pytestmark = pytest.mark.gpu
 
