@@ -62,6 +62,13 @@ class PeerRoute(C.Structure):
 ROUTE_WORDS, PLAN_VEC, PLAN_GRAD, PLAN_NREQ, PLAN_U, PLAN_WORDS = 48, 0, 48, 96, 97, 128     # include/ctr_b200.h CTR_PLAN_*
 
 
+class CrossCfg(C.Structure):
+    """mirror of `ctr_cross_cfg`"""
+    _fields_ = [("B", c_i32), ("D", c_i32), ("n_layers", c_i32), ("reserved", c_i32), ("ldx", c_i64),
+                ("w", c_vp * MAX_LAYERS), ("b", c_vp * MAX_LAYERS), ("gw", c_vp * MAX_LAYERS), ("gb", c_vp * MAX_LAYERS)]
+
+
+_P_CROSS = C.POINTER(CrossCfg)
 _P_CFG = C.POINTER(EmbedCfg)
 _P_RT = C.POINTER(PeerRoute)
 _P_HP = C.POINTER(AdamHP)
@@ -92,6 +99,9 @@ _PROTOS = {
                                    c_vp, c_i64, c_i32]),
     "ctr_transpose": (c_i32, [c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_i64, c_i32]),
     "ctr_round_tf32_copy": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64]),
+    "ctr_cross_fwd": (c_i32, [c_vp, c_vp, _P_CROSS, c_vp, c_vp, c_i64]),
+    "ctr_cross_bwd_ws_bytes": (c_i64, [c_vp, _P_CROSS]),
+    "ctr_cross_bwd": (c_i32, [c_vp, c_vp, _P_CROSS, c_vp, c_vp, c_vp, c_vp, c_i64]),
     "ctr_head_ws_bytes": (c_i64, [c_vp, c_i32, c_i32, c_i32]),
     "ctr_head_fwd": (c_i32, [c_vp, c_vp, c_i32, c_i64, c_vp, c_i64, c_i32, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp,
                              c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_i32]),

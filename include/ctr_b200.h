@@ -43,6 +43,7 @@ extern "C" {
 #define CTR_E_WORKSPACE    -3   /* workspace too small */
 #define CTR_E_UNSUPPORTED  -4   /* feature not built (e.g. wrong arch) */
 
+#define CTR_MAX_LAYERS 8
 typedef struct ctr_handle ctr_handle;
 typedef void* ctr_stream;        /* cudaStream_t */
 
@@ -168,6 +169,26 @@ int ctr_transpose(ctr_handle* h, ctr_stream s, const float* in, int K, int N, fl
                   int round_tf32);
 /* out[i] = rna_tf32(in[i]): the rounded weight copy the TF32 data-gradient GEMM reads */
 int ctr_round_tf32_copy(ctr_handle* h, ctr_stream s, const float* in, float* out, int64_t n);
+
+/* ---- cross network of DCN -------------------------------------------------------------
+ * replaces the loop of test_model/DCN.py:84-86:  xl = tensordot(matmul(x0, xl, transpose_b=True), w_l, axes=1) + b_l + xl,
+ * i.e.  x_{l+1} = x0 * (x_l . w_l) + b_l + x_l  (the [B, D, D] outer product is never formed).  One warp per sample;
+ * D <= 128, n_layers <= 4 (the reference uses 2).
+ *   ctr_cross_fwd   out[b, :D] = x_L
+ *   ctr_cross_bwd   gw[l][:] = d loss / d w_l, gb[l][:] = d loss / d b_l for d loss / d x_L [b, :] = dlogit[b] * w_proj[:]
+ *                   (written, not accumulated; deterministic two-pass sum over the batch).  ws: ctr_cross_bwd_ws_bytes(). */
+typedef struct ctr_cross_cfg {
+    int32_t B, D, n_layers, reserved;
+    int64_t ldx;                                /* floats per row of x0 */
+    const float* w[CTR_MAX_LAYERS];             /* cross_layer_l [D] */
+    const float* b[CTR_MAX_LAYERS];             /* cross_bias_l  [D] */
+    float* gw[CTR_MAX_LAYERS];                  /* gradients (ctr_cross_bwd only) */
+    float* gb[CTR_MAX_LAYERS];
+} ctr_cross_cfg;
+int ctr_cross_fwd(ctr_handle* h, ctr_stream s, const ctr_cross_cfg* cfg, const float* x0, float* out, int64_t ldo);
+int64_t ctr_cross_bwd_ws_bytes(ctr_handle* h, const ctr_cross_cfg* cfg);
+int ctr_cross_bwd(ctr_handle* h, ctr_stream s, const ctr_cross_cfg* cfg, const float* x0, const float* dlogit,
+                  const float* w_proj, void* ws, int64_t ws_bytes);
 
 /* ---- K5: head + sigmoid log-loss --------------------------------------------------------
  * replaces concat + matmul + sigmoid (models/deepfm.py:128-145; models/dnn.py:82-84; the deep half
@@ -376,7 +397,6 @@ int ctr_adam_dense(ctr_handle* h, ctr_stream s, float* theta, float* m, float* v
  * W_l [K,N] at w_off[l], the copies the tcgen05 GEMMs read next step: w_rounded[l][K,N] = rna_tf32(W) and
  * w_kmajor[l][N, ld_kmajor] = rna_tf32(W)^T (either may be NULL).  Same arithmetic as ctr_adam_dense + ctr_transpose +
  * ctr_round_tf32_copy. */
-#define CTR_MAX_LAYERS 8
 typedef struct ctr_dense_layout {
     int64_t group_end[3];
     float reg_scale;

@@ -37,6 +37,8 @@ def test_ctypes_prototypes_match_header(lib_built):
         if "*" in a:
             if "ctr_embed_cfg" in a:
                 return _lib._P_CFG
+            if "ctr_cross_cfg" in a:
+                return _lib._P_CROSS
             if "ctr_adam_hp" in a:
                 return _lib._P_HP
             if "ctr_peer_route" in a:
