@@ -309,7 +309,8 @@ def main():
     # it launches on.  Kept out of the timed region above (only the roofline kernel is timed there): ~60 extra event
     # records per step are host work, and the multi-GPU step is close to host-bound.
     timed = ("ctr_fm_gather_fwd", "ctr_embed_bwd_partials_weighted", "ctr_adam_rows", "ctr_adam_rows_gathered",
-             "ctr_sort_ids", "ctr_unique_segments", "ctr_mlp_fwd", "ctr_mlp_bwd_data", "ctr_mlp_bwd_weight", "ctr_head_fwd",
+             "ctr_sort_ids", "ctr_unique_segments", "ctr_mlp_fwd", "ctr_mlp_fwd_bits", "ctr_mlp_bwd_data", "ctr_mlp_bwd_data_bits",
+             "ctr_mlp_bwd_weight", "ctr_head_fwd",
              "ctr_fm_cont_bwd", "ctr_dense_update", "ctr_gather_rows_push", "ctr_embed_bwd_finalize_push", "ctr_peer_barrier")
     eng.h.timers = {n: [] for n in timed}
     for i in range(a.steps):
@@ -426,7 +427,8 @@ def main():
         per_step = avg * cnt / a.steps
         kernels[n] = {"ms_per_call": round(avg, 4), "calls_per_step": cnt / a.steps, "share_of_step": round(per_step / step_ms, 4)}
     mlp_flops = 3 * 2 * sum(k_ * h_ for k_, h_ in layer_dims) * B
-    mlp_ms = sum(kern[n][0] * kern[n][1] for n in ("ctr_mlp_fwd", "ctr_mlp_bwd_data", "ctr_mlp_bwd_weight")) / a.steps
+    mlp_ms = sum(kern[n][0] * kern[n][1] for n in ("ctr_mlp_fwd", "ctr_mlp_fwd_bits", "ctr_mlp_bwd_data", "ctr_mlp_bwd_data_bits",
+                                                     "ctr_mlp_bwd_weight")) / a.steps
     tf32_peak = extras.get("tf32_gemm_peak_tflops")
     mlp_tfl = mlp_flops / (mlp_ms * 1e-3) / 1e12 if mlp_ms > 0 else None
     line = {

@@ -94,6 +94,9 @@ _PROTOS = {
                             c_u64, c_vp, c_i64]),
     "ctr_mlp_bwd_data": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp, c_i64, c_f32,
                                  c_vp, c_i64]),
+    "ctr_mlp_relu_bits_bytes": (c_i64, [c_vp, c_i32, c_i32]),
+    "ctr_mlp_fwd_bits": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp, c_f32, c_u64, c_vp, c_i64, c_vp]),
+    "ctr_mlp_bwd_data_bits": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_vp, c_f32, c_vp, c_i64]),
     "ctr_mlp_bwd_weight_ws_bytes": (c_i64, [c_vp, c_i32, c_i32, c_i32, c_i32]),
     "ctr_mlp_bwd_weight": (c_i32, [c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp,
                                    c_vp, c_i64, c_i32]),

@@ -167,9 +167,11 @@ int wgrad_splits(ctr_handle* h, int B, int K, int N) {
 
 // TF32 tcgen05 path (mlp_tcgen05.cu)
 int ctr_tc_mlp_fwd(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* X, int64_t ldx, const float* Wt,
-                   const float* bias, int relu, float keep, uint64_t seed, float* Y, int64_t ldy);
+                   const float* bias, int relu, float keep, uint64_t seed, float* Y, int64_t ldy, uint32_t* relu_bits);
 int ctr_tc_mlp_bwd_data(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* dZ, int64_t lddz,
-                        const float* W, const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx);
+                        const float* W, const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx,
+                        const uint32_t* relu_bits);
+int64_t ctr_tc_relu_bits_bytes(int B, int N);
 int64_t ctr_tc_bwd_weight_ws_bytes(ctr_handle* h, int B, int K, int N);
 int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* X, int64_t ldx,
                           const float* dZ, int64_t lddz, float* dW, float* dbias, void* ws, int64_t ws_bytes);
@@ -182,7 +184,7 @@ extern "C" int ctr_mlp_fwd(ctr_handle* h, ctr_stream s, int precision, int B, in
     if (B == 0) return CTR_OK;
     if (precision == CTR_PREC_TF32) {
         CTR_REQUIRE(h, Wt != nullptr, "mlp_fwd: TF32 path needs the K-major copy Wt");
-        return ctr_tc_mlp_fwd(h, ctr_st(s), B, K, N, X, ldx, Wt, bias, relu, keep, seed, Y, ldy);
+        return ctr_tc_mlp_fwd(h, ctr_st(s), B, K, N, X, ldx, Wt, bias, relu, keep, seed, Y, ldy, nullptr);
     }
     CTR_REQUIRE(h, precision == CTR_PREC_FP32 && W, "mlp_fwd: bad precision / W null");
     Epilogue ep{bias, relu, keep, seed, nullptr, 0, 1.f};
@@ -195,11 +197,32 @@ extern "C" int ctr_mlp_bwd_data(ctr_handle* h, ctr_stream s, int precision, int 
     CTR_REQUIRE(h, dZ && W && dX && B >= 0 && K > 0 && N > 0 && lddz >= N && lddx >= K, "mlp_bwd_data: bad args");
     if (B == 0) return CTR_OK;
     if (precision == CTR_PREC_TF32)
-        return ctr_tc_mlp_bwd_data(h, ctr_st(s), B, K, N, dZ, lddz, W, mask, ldmask, mask_scale, dX, lddx);
+        return ctr_tc_mlp_bwd_data(h, ctr_st(s), B, K, N, dZ, lddz, W, mask, ldmask, mask_scale, dX, lddx, nullptr);
     CTR_REQUIRE(h, precision == CTR_PREC_FP32, "mlp_bwd_data: bad precision");
     // dX[B,K] = dZ[B,N] @ W[K,N]^T : "B" operand stored [K_out, N_red] = TB layout
     Epilogue ep{nullptr, 0, 1.f, 0, mask, ldmask, mask_scale};
     return launch_sgemm(h, ctr_st(s), false, true, B, K, N, dZ, lddz, W, N, dX, lddx, 1, ep);
+}
+
+// ---- TF32 only: ReLU sign bits instead of the fp32 activation as the data gradient's mask (include/ctr_b200.h)
+extern "C" int64_t ctr_mlp_relu_bits_bytes(ctr_handle* h, int B, int N) {
+    if (!h || B <= 0 || N <= 0) return 0;
+    return ctr_tc_relu_bits_bytes(B, N);
+}
+
+extern "C" int ctr_mlp_fwd_bits(ctr_handle* h, ctr_stream s, int B, int K, int N, const float* X, int64_t ldx, const float* Wt,
+                                const float* bias, float keep, uint64_t seed, float* Y, int64_t ldy, uint32_t* relu_bits) {
+    CTR_REQUIRE(h, X && Y && Wt && bias && relu_bits && B >= 0 && K > 0 && N > 0 && ldx >= K && ldy >= N, "mlp_fwd_bits: bad args");
+    CTR_REQUIRE(h, keep > 0.f && keep <= 1.f, "mlp_fwd_bits: keep must be in (0,1]");
+    if (B == 0) return CTR_OK;
+    return ctr_tc_mlp_fwd(h, ctr_st(s), B, K, N, X, ldx, Wt, bias, 1, keep, seed, Y, ldy, relu_bits);
+}
+
+extern "C" int ctr_mlp_bwd_data_bits(ctr_handle* h, ctr_stream s, int B, int K, int N, const float* dZ, int64_t lddz,
+                                     const float* W, const uint32_t* relu_bits, float mask_scale, float* dX, int64_t lddx) {
+    CTR_REQUIRE(h, dZ && W && dX && relu_bits && B >= 0 && K > 0 && N > 0 && lddz >= N && lddx >= K, "mlp_bwd_data_bits: bad args");
+    if (B == 0) return CTR_OK;
+    return ctr_tc_mlp_bwd_data(h, ctr_st(s), B, K, N, dZ, lddz, W, nullptr, 0, mask_scale, dX, lddx, relu_bits);
 }
 
 extern "C" int64_t ctr_mlp_bwd_weight_ws_bytes(ctr_handle* h, int precision, int B, int K, int N) {

@@ -158,10 +158,20 @@ struct EpiParams {
     int round_out;          // round outputs to tf32 (they feed the next tensor-core GEMM)
     int col0;               // first global output column of this CTA's slab (dropout hash index)
     int n_total;            // row pitch of the dropout hash index (the full N)
-    int dbg;                // experiments only (CTR_GEMM_DBG): 1 skip global stores, 2 skip MMAs, 4 skip TMA loads, 16 direct 256-bit epilogue
+    int dbg;                // experiments only (CTR_GEMM_DBG): 1 skip global stores, 2 skip MMAs, 4 skip TMA loads, 16 direct 256-bit epilogue,
+                            // 32 fast epilogue without its stores, 64 no epilogue at all (persistent kernel)
     unsigned long long* trace;   // CTR_GEMM_DBG & 8: per-CTA phase timestamps (8 slots per CTA)
     unsigned* sm_slots;     // split2 stagger: per-SM arrival counters (zeroed before the launch), or null
     unsigned stagger_ns;    // the second CTA to arrive on an SM starts this much later (first wave only)
+    int tma_lanes;          // lanes of the producer warp that issue TMA loads (see tma_lanes() on the host side)
+    // ReLU sign bits (ctr_mlp_fwd_bits / ctr_mlp_bwd_data_bits): one 32-bit word per (lane, 32 x 32 sub-tile) in the
+    // epilogue's own thread <-> element mapping: nibble j of lane l = columns 4*(l&7)..+3 of row (l>>3) + 4*j of the
+    // sub-tile.  Word index = ((row / 32) * bits_chunks + bits_c0 + c) * 32 + lane, c = the sub-tile's index inside the
+    // CTA's unit / slab.  The producing and the consuming GEMM have the same (M, N), hence the same kernel and geometry.
+    uint32_t* bits_out;     // forward: written when non-null (1 = stored activation > 0)
+    const uint32_t* bits_in;   // data gradient: the mask, instead of `mask`
+    int bits_chunks;        // sub-tile slots per 32-row block (host: launch_tn)
+    int bits_c0;            // first slot of this CTA's unit / slab (set by the kernel)
 };
 
 __device__ __forceinline__ unsigned long long gtimer() {
@@ -246,14 +256,17 @@ __device__ __forceinline__ float cvt_tf32_relu(float x) {
     return __uint_as_float(r);
 }
 
-template <bool BIAS, bool RELU, bool MASK, int EW>
+__device__ __forceinline__ int rbase_of(int m0, int ewarp) { return m0 + (ewarp & 3) * 32; }
+
+template <bool BIAS, bool RELU, int MASK, int EW>
 __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
                                               int64_t ldc, const EpiParams& ep, float* stage, uint32_t sbias) {
     const int q = ewarp & 3, half = ewarp >> 2;     // TMEM lane quarter; chunk phase (stride EW / 4)
     const uint32_t tile = smem_u32(stage) + (uint32_t) (ewarp * EPI_TILE_FLOATS * 4);
     const bool vec_ok = (ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(C) & 15) == 0);
-    const bool mvec_ok = MASK && (ep.ldmask % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.mask) & 15) == 0);
+    const bool mvec_ok = MASK == 1 && (ep.ldmask % 4 == 0) && ((reinterpret_cast<uintptr_t>(ep.mask) & 15) == 0);
     const bool dropout = ep.keep < 1.f;
+    const size_t bits_row = (size_t) (rbase_of(m0, ewarp) >> 5) * (size_t) ep.bits_chunks + (size_t) ep.bits_c0;
     const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
     const int nchunks = (N + 31) / 32;
     const int rsub = lane >> 3;            // row inside a group of 4 rows
@@ -270,7 +283,9 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
             bs = lds_f4(sbias + (uint32_t) (col * 4));
         }
         float4 mk[8];
-        if (MASK) {
+        uint32_t mbits = 0, obits = 0;
+        if (MASK == 2) mbits = __ldg(ep.bits_in + (bits_row + (size_t) c) * 32 + lane);
+        if (MASK == 1) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
                 const int row = rbase + rsub + 4 * j;
@@ -301,11 +316,18 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
             float4 v = tv[j];
             if (BIAS) { v.x += bs.x; v.y += bs.y; v.z += bs.z; v.w += bs.w; }
             if (RELU) { v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f); }
-            if (MASK) {
+            if (MASK == 1) {
                 v.x = mk[j].x > 0.f ? v.x * ep.mask_scale : 0.f;
                 v.y = mk[j].y > 0.f ? v.y * ep.mask_scale : 0.f;
                 v.z = mk[j].z > 0.f ? v.z * ep.mask_scale : 0.f;
                 v.w = mk[j].w > 0.f ? v.w * ep.mask_scale : 0.f;
+            }
+            if (MASK == 2) {
+                const uint32_t nib = mbits >> (4 * j);
+                v.x = (nib & 1u) ? v.x * ep.mask_scale : 0.f;
+                v.y = (nib & 2u) ? v.y * ep.mask_scale : 0.f;
+                v.z = (nib & 4u) ? v.z * ep.mask_scale : 0.f;
+                v.w = (nib & 8u) ? v.w * ep.mask_scale : 0.f;
             }
             if (ep.round_out) { v.x = cvt_tf32(v.x); v.y = cvt_tf32(v.y); v.z = cvt_tf32(v.z); v.w = cvt_tf32(v.w); }
             if (dropout) {
@@ -315,6 +337,9 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
                 v.z = dropout_u01(ep.seed, e0 + 2) < ep.keep ? v.z / ep.keep : 0.f;
                 v.w = dropout_u01(ep.seed, e0 + 3) < ep.keep ? v.w / ep.keep : 0.f;
             }
+            if (ep.bits_out)       // what the data gradient masks with: the STORED activation (after dropout) > 0
+                obits |= ((col + 0 < N && v.x > 0.f ? 1u : 0u) | (col + 1 < N && v.y > 0.f ? 2u : 0u) |
+                          (col + 2 < N && v.z > 0.f ? 4u : 0u) | (col + 3 < N && v.w > 0.f ? 8u : 0u)) << (4 * j);
             if (row < M && !(ep.dbg & 1)) {
                 float* dst = C + (int64_t) row * ldc + col;
                 if (vec_ok && col4) *reinterpret_cast<float4*>(dst) = v;
@@ -326,6 +351,7 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
                 }
             }
         }
+        if (ep.bits_out) ep.bits_out[(bits_row + (size_t) c) * 32 + lane] = obits;
         if (ewarp == 0 && lane == 0) TRACE_FINE(128 + 4 * c + 1);
         __syncwarp();      // the tile is rewritten by the next chunk
     }
@@ -339,7 +365,7 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
 // Tried and dropped: a transposition-free epilogue on tcgen05.ld.16x256b fragments (32-byte runs per thread quad, 64-bit
 // stores / mask loads) -- it frees the shared-memory port but the 8-sectors-per-instruction accesses made the
 // epilogue 1.5x (stores) to 2x (mask loads) slower.
-template <bool BIAS, bool RELU, bool MASK, int EW>
+template <bool BIAS, bool RELU, int MASK, bool BITS_OUT, int EW>
 __device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp, int lane, int m0, int N, float* C,
                                                    int64_t ldc, const EpiParams& ep, float* stage, uint32_t sbias) {
     const int q = ewarp & 3, half = ewarp >> 2;
@@ -351,7 +377,10 @@ __device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp
     const uint32_t st_addr = tile + (uint32_t) (lane * EPI_PITCH * 4);
     const uint32_t ld_addr = tile + (uint32_t) ((rsub * EPI_PITCH + cc) * 4);
     char* dst_row = reinterpret_cast<char*>(C + (int64_t) row0 * ldc + cc);
-    const char* msk_row = MASK ? reinterpret_cast<const char*>(ep.mask + (int64_t) row0 * ep.ldmask + cc) : nullptr;
+    const char* msk_row = MASK == 1 ? reinterpret_cast<const char*>(ep.mask + (int64_t) row0 * ep.ldmask + cc) : nullptr;
+    // sign-bit words of this warp's 32-row block (see EpiParams): one coalesced 128-byte access per sub-tile
+    const size_t bits_row = ((size_t) ((m0 >> 5) + q) * (size_t) ep.bits_chunks + (size_t) ep.bits_c0) * 32 + (size_t) lane;
+    uint32_t mbits = 0, mbits_next = 0;
     const int64_t dstep = 4 * ldc * 4, mstep = 4 * ep.ldmask * 4;         // 4 rows down, in bytes
     const float scale = ep.mask_scale;
     float4 mk[8], mkn[8];
@@ -364,7 +393,8 @@ __device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp
             mp += mstep;
         }
     };
-    if (MASK) load_mask(half, mkn);
+    if (MASK == 1) load_mask(half, mkn);
+    if (MASK == 2 && half < nchunks) mbits_next = __ldg(ep.bits_in + bits_row + (size_t) half * 32);
     for (int c = half; c < nchunks; c += EW / 4) {
         const int c0 = c * 32;
         uint32_t r[32];
@@ -372,11 +402,16 @@ __device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp
         const bool col_ok = c0 + cc < N;                  // N % 4 == 0: a lane's four columns are valid together
         float4 bs = make_float4(0.f, 0.f, 0.f, 0.f);
         if (BIAS) bs = lds_f4(sbias + (uint32_t) ((c0 + cc) * 4));
-        if (MASK) {
+        if (MASK == 1) {
 #pragma unroll
             for (int j = 0; j < 8; ++j) mk[j] = mkn[j];
             load_mask(c + EW / 4, mkn);                   // the next sub-tile's mask, in flight under this one
         }
+        if (MASK == 2) {
+            mbits = mbits_next;
+            if (c + EW / 4 < nchunks) mbits_next = __ldg(ep.bits_in + bits_row + (size_t) (c + EW / 4) * 32);
+        }
+        uint32_t obits = 0;
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 8; ++i)
@@ -391,15 +426,28 @@ __device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp
         for (int j = 0; j < 8; ++j) {
             float4 v = tv[j];
             if (BIAS) { v.x += bs.x; v.y += bs.y; v.z += bs.z; v.w += bs.w; }
-            if (MASK) {
+            if (MASK == 1) {
                 v.x = mk[j].x > 0.f ? v.x * scale : 0.f; v.y = mk[j].y > 0.f ? v.y * scale : 0.f;
                 v.z = mk[j].z > 0.f ? v.z * scale : 0.f; v.w = mk[j].w > 0.f ? v.w * scale : 0.f;
             }
+            if (MASK == 2) {
+                v.x = (mbits & (1u << (4 * j))) ? v.x * scale : 0.f; v.y = (mbits & (2u << (4 * j))) ? v.y * scale : 0.f;
+                v.z = (mbits & (4u << (4 * j))) ? v.z * scale : 0.f; v.w = (mbits & (8u << (4 * j))) ? v.w * scale : 0.f;
+            }
             if (RELU) { v.x = cvt_tf32_relu(v.x); v.y = cvt_tf32_relu(v.y); v.z = cvt_tf32_relu(v.z); v.w = cvt_tf32_relu(v.w); }
             else { v.x = cvt_tf32(v.x); v.y = cvt_tf32(v.y); v.z = cvt_tf32(v.z); v.w = cvt_tf32(v.w); }
-            if (col_ok) *reinterpret_cast<float4*>(dp) = v;
+            if (BITS_OUT && col_ok) {
+                // the stored value is >= +0 after the ReLU, so "> 0" is "bit pattern != 0": min(u, 1) is the bit
+                obits |= (min(__float_as_uint(v.x), 1u) | (min(__float_as_uint(v.y), 1u) << 1) |
+                          (min(__float_as_uint(v.z), 1u) << 2) | (min(__float_as_uint(v.w), 1u) << 3)) << (4 * j);
+            }
+            if (col_ok && !(ep.dbg & 32)) {
+                if (ep.dbg & 128) __stcs(reinterpret_cast<float4*>(dp), v);       // experiment: streaming (evict-first) stores
+                else *reinterpret_cast<float4*>(dp) = v;
+            }
             dp += dstep;
         }
+        if (BITS_OUT) ep.bits_out[bits_row + (size_t) c * 32] = obits;
         __syncwarp();      // the tile is rewritten by the next chunk
     }
 }
@@ -488,9 +536,10 @@ template <int EW, bool DIRECT = false>
 __device__ __forceinline__ void epilogue_dispatch(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
                                                   int64_t ldc, const EpiParams& ep, float* stage, uint32_t sbias) {
     const bool fast = m0 + BLOCK_M <= M && (N & 3) == 0 && (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0 &&
-                      ep.round_out && !(ep.keep < 1.f) && !(ep.dbg & 7) &&
+                      ep.round_out && !(ep.keep < 1.f) && !(ep.dbg & 1) &&
                       (!ep.mask || ((ep.ldmask & 3) == 0 && (reinterpret_cast<uintptr_t>(ep.mask) & 15) == 0));
-    if (DIRECT && fast && (N & 7) == 0 && (ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(C) & 31) == 0 &&
+    const bool bits = ep.bits_in != nullptr || ep.bits_out != nullptr;
+    if (DIRECT && fast && !bits && (N & 7) == 0 && (ldc & 7) == 0 && (reinterpret_cast<uintptr_t>(C) & 31) == 0 &&
         (!ep.mask || ((ep.ldmask & 7) == 0 && (reinterpret_cast<uintptr_t>(ep.mask) & 31) == 0))) {
         if (ep.mask) epilogue_rows_direct<false, false, true, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, sbias);
         else if (ep.bias && ep.relu) epilogue_rows_direct<true, true, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, sbias);
@@ -499,19 +548,24 @@ __device__ __forceinline__ void epilogue_dispatch(uint32_t tmem_base, int ewarp,
         else epilogue_rows_direct<false, false, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, sbias);
         return;
     }
-    if (fast) {
-        if (ep.mask) epilogue_rows_fast<false, false, true, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
-        else if (ep.bias && ep.relu) epilogue_rows_fast<true, true, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
-        else if (ep.bias) epilogue_rows_fast<true, false, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
-        else if (ep.relu) epilogue_rows_fast<false, true, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
-        else epilogue_rows_fast<false, false, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+    // sign bits are written only behind a ReLU (the fast path's "bit pattern != 0" test relies on stored values >= +0)
+    if (fast && !(ep.bits_out && !(ep.bias && ep.relu))) {
+        if (ep.bits_in) epilogue_rows_fast<false, false, 2, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        else if (ep.mask) epilogue_rows_fast<false, false, 1, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        else if (ep.bias && ep.relu && ep.bits_out)
+            epilogue_rows_fast<true, true, 0, true, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        else if (ep.bias && ep.relu) epilogue_rows_fast<true, true, 0, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        else if (ep.bias) epilogue_rows_fast<true, false, 0, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        else if (ep.relu) epilogue_rows_fast<false, true, 0, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        else epilogue_rows_fast<false, false, 0, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
         return;
     }
-    if (ep.mask) epilogue_rows<false, false, true, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
-    else if (ep.bias && ep.relu) epilogue_rows<true, true, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
-    else if (ep.bias) epilogue_rows<true, false, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
-    else if (ep.relu) epilogue_rows<false, true, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
-    else epilogue_rows<false, false, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+    if (ep.bits_in) epilogue_rows<false, false, 2, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+    else if (ep.mask) epilogue_rows<false, false, 1, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+    else if (ep.bias && ep.relu) epilogue_rows<true, true, 0, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+    else if (ep.bias) epilogue_rows<true, false, 0, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+    else if (ep.relu) epilogue_rows<false, true, 0, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+    else epilogue_rows<false, false, 0, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
 }
 
 __device__ __forceinline__ PipeBars* setup_cta(uint8_t* smem, size_t pipe_bytes, int nstages, uint32_t tmem_cols, int warp, int tma_warp) {
@@ -550,6 +604,7 @@ gemm_tn_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (ep.bias) ep.bias += n0;
     if (ep.mask) ep.mask += n0;
     ep.col0 = n0;
+    ep.bits_c0 = ((int) blockIdx.x % nslab) * ((NB + 31) / 32);
     const int a_bytes = BLOCK_M * BLOCK_R * 4;
     const int stage_bytes = a_bytes + NB * BLOCK_R * 4;
     const int m0 = ((int) blockIdx.x / nslab) * BLOCK_M;
@@ -798,23 +853,36 @@ gemm_tn_pair_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
     if (threadIdx.x == 0) TRACE(1);
 
     if (warp == TMA_WARP) {
-        if (elect_one()) {
-            prefetch_tmap(&tmA);
-            prefetch_tmap(&tmB);
-            uint32_t it = 0;
-            for (uint32_t u = 0; u < n_units; ++u) {
+        // One thread gets a TMA tile load through every ~0.3 us whatever its size (tools/probe_tma_fill.cu,
+        // profiles/r02j_probe_tma_fill.txt: 43 GB/s per SM from one issuing thread, 124 from four, lanes of one warp or
+        // separate warps alike), and the two loads of a k-block issued by one thread WERE this kernel's main loop
+        // (0.64 us per k-block against ~0.2 us of MMAs).  So the k-blocks are dealt round-robin to `nl` lanes, each
+        // running its own wait -> expect -> load loop; the stages still fill in ring order per lane, and the MMA issuer
+        // consumes them in order whichever lane filled them.
+        const int nl = ep.tma_lanes < 1 ? 1 : (ep.tma_lanes > nstages ? nstages : ep.tma_lanes);
+        if (lane < nl) {
+            if (lane == 0) {
+                prefetch_tmap(&tmA);
+                prefetch_tmap(&tmB);
+            }
+            const uint32_t total = n_units * (uint32_t) num_kb;
+            for (uint32_t it = (uint32_t) lane; it < total; it += (uint32_t) nl) {
+                const uint32_t u = it / (uint32_t) num_kb;
+                const int kb = (int) (it - u * (uint32_t) num_kb);
                 const int tile = cid + (int) (u / (uint32_t) nmma) * ncl, hh = (int) (u % (uint32_t) nmma);
                 const int m0 = (tile * 2 + (int) rank) * BLOCK_M;
-                for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                    const int s = (int) (it % (uint32_t) nstages);
-                    const uint32_t ph = (it / (uint32_t) nstages) & 1u;
-                    mbar_wait(&bars->empty[s], ph ^ 1u);       // my copy of the stage is free (multicast commit)
-                    uint8_t* sa = smem + (size_t) s * stage_bytes;
-                    if (rank == 0) mbar_expect_tx(&bars->full[s], (uint32_t) (2 * stage_bytes));   // both CTAs' bytes
-                    const uint32_t lbar = mapa_shared(smem_u32(&bars->full[s]), 0);
-                    tma_load_2d_pair(sa, &tmA, lbar, kb * BLOCK_R, m0);
-                    tma_load_2d_pair(sa + a_bytes, &tmB, lbar, kb * BLOCK_R, hh * n_each + (int) rank * n_half);
+                const int s = (int) (it % (uint32_t) nstages);
+                const uint32_t ph = (it / (uint32_t) nstages) & 1u;
+                mbar_wait(&bars->empty[s], ph ^ 1u);       // my copy of the stage is free (multicast commit)
+                uint8_t* sa = smem + (size_t) s * stage_bytes;
+                if (ep.dbg & 4) {                          // timing experiment: no loads, the MMAs read whatever is there
+                    if (rank == 0) mbar_expect_tx(&bars->full[s], 0u);
+                    continue;
                 }
+                if (rank == 0) mbar_expect_tx(&bars->full[s], (uint32_t) (2 * stage_bytes));   // both CTAs' bytes
+                const uint32_t lbar = mapa_shared(smem_u32(&bars->full[s]), 0);
+                tma_load_2d_pair(sa, &tmA, lbar, kb * BLOCK_R, m0);
+                tma_load_2d_pair(sa + a_bytes, &tmB, lbar, kb * BLOCK_R, hh * n_each + (int) rank * n_half);
             }
         }
     } else if (warp == MMA_WARP) {
@@ -838,7 +906,7 @@ gemm_tn_pair_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
                     for (int k = 0; k < BLOCK_R / UMMA_K; ++k) {
                         const uint64_t adesc = make_desc(a_base + k * UMMA_K * 4, 16, 8 * BLOCK_R * 4, LAYOUT_SW128);
                         const uint64_t bdesc = make_desc(b_base + k * UMMA_K * 4, 16, 8 * BLOCK_R * 4, LAYOUT_SW128);
-                        umma_tf32_pair(acc, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+                        if (!(ep.dbg & 2)) umma_tf32_pair(acc, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
                     umma_commit_pair(&bars->empty[s]);     // frees the stage in BOTH CTAs
                 }
@@ -860,10 +928,11 @@ gemm_tn_pair_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
             EpiParams epu = ep;
             if (epu.mask) epu.mask += n0;
             epu.col0 = n0;
+            epu.bits_c0 = hh * ((n_each + 31) / 32);
             mbar_wait(&bars->tmem_full[buf], use & 1u);
             tc_fence_after();
             if (threadIdx.x == 0) TRACE_FINE(256 + 4 * (int) u + 2);
-            if (Nu > 0)
+            if (Nu > 0 && !(ep.dbg & 64))
                 epilogue_dispatch<EW, DIRECT>(tmem_base + buf * BUF_COLS, warp, lane, m0, M, Nu, C + n0, ldc, epu, estage,
                                       smem_u32(sbias) + (uint32_t) (n0 * 4));
             tc_fence_before();
@@ -884,7 +953,7 @@ gemm_tn_pair_persistent_kernel(const __grid_constant__ CUtensorMap tmA, const __
 constexpr int NT_EW = 8;
 __global__ void __launch_bounds__(nthreads(NT_EW), 1)
 gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int R,
-               int r_per_split, int n1, int n2, int nstages, uint32_t tmem_cols, float* __restrict__ Cws) {
+               int r_per_split, int n1, int n2, int nstages, uint32_t tmem_cols, float* __restrict__ Cws, int tma_lanes, int dbg) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -902,7 +971,30 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const uint32_t tmem_base = bars->tmem_base;
 
     if (warp == TMA_WARP) {
-        if (elect_one()) {
+        // a k-block is BLOCK_M / 32 + nbx (up to 20) boxes of 32 x 32 floats: one box per lane, so the per-thread TMA issue
+        // time (see the tn kernel's producer) is paid once per k-block instead of once per box
+        const int nbox = BLOCK_M / 32 + nbx;
+        if (tma_lanes > 1) {
+            const unsigned active = nbox >= 32 ? 0xffffffffu : ((1u << nbox) - 1u);
+            if (lane < nbox) {
+                if (lane == 0) {
+                    prefetch_tmap(&tmA);
+                    prefetch_tmap(&tmB);
+                }
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    const int s = kb % nstages;
+                    const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
+                    mbar_wait(&bars->empty[s], ph ^ 1u);
+                    uint8_t* sa = smem + (size_t) s * stage_bytes;
+                    if (lane == 0) mbar_expect_tx(&bars->full[s], (dbg & 4) ? 0u : (uint32_t) stage_bytes);
+                    __syncwarp(active);
+                    if (dbg & 4) continue;                  // timing experiment: no loads
+                    const int r0 = r_lo + kb * BLOCK_R;
+                    if (lane < BLOCK_M / 32) tma_load_2d(sa + lane * BOX_BYTES, &tmA, &bars->full[s], m0 + lane * 32, r0);
+                    else tma_load_2d(sa + lane * BOX_BYTES, &tmB, &bars->full[s], (lane - BLOCK_M / 32) * 32, r0);
+                }
+            }
+        } else if (elect_one()) {
             prefetch_tmap(&tmA);
             prefetch_tmap(&tmB);
             for (int kb = 0; kb < num_kb; ++kb) {
@@ -933,6 +1025,7 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     const uint32_t koff = k * UMMA_K * 128;
                     const uint64_t adesc = make_desc(a_base + koff, BOX_BYTES, 512, LAYOUT_SW128_BASE32B);
                     const uint64_t bdesc1 = make_desc(b_base + koff, BOX_BYTES, 512, LAYOUT_SW128_BASE32B);
+                    if (dbg & 2) continue;                  // timing experiment: no MMAs
                     umma_tf32(tmem_base, adesc, bdesc1, idesc1, (kb | k) != 0 ? 1u : 0u);
                     if (n2 > 0) {
                         const uint64_t bdesc2 = make_desc(b_base + (n1 / 32) * BOX_BYTES + koff, BOX_BYTES, 512, LAYOUT_SW128_BASE32B);
@@ -948,8 +1041,8 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (num_kb > 0) {
             mbar_wait(&bars->tmem_full, 0);
             tc_fence_after();
-            EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f, 0, 0, 0, 0, nullptr, nullptr, 0};
-            epilogue_rows<false, false, false, EW>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem), 0u);
+            EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f, 0, 0, 0, 0, nullptr, nullptr, 0, 1, nullptr, nullptr, 0, 0};
+            epilogue_rows<false, false, 0, EW>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem), 0u);
         } else {                                   // empty slice: contribute zeros
             const int row = m0 + (warp & 3) * 32 + lane;
             if (row < M) for (int c = (warp >> 2); c < N; c += EW / 4) Cz[(size_t) row * N + c] = 0.f;
@@ -1031,6 +1124,20 @@ unsigned long long* gemm_trace_buf() {
     return g_trace_buf;
 }
 
+// CTR_GEMM_TMA_LANES = lanes of the producer warp that issue TMA loads in the persistent tn kernel (k-blocks dealt
+// round-robin) and in the nt kernel (> 1: one box per lane).  Default 4; 1 = one elected thread issues everything (the
+// round-1 kernels, kept for A/B).
+int tma_lanes() {
+    static int n = -1;
+    if (n < 0) {
+        const char* e = getenv("CTR_GEMM_TMA_LANES");
+        n = e ? atoi(e) : 4;
+        if (n < 1) n = 1;
+        if (n > 8) n = 8;
+    }
+    return n;
+}
+
 // CTR_GEMM_MODE = pp (default: persistent CTA pairs, double-buffered accumulator) | split2 (two co-resident half-N CTAs
 // per SM) | pair (one cta_group::2 tile per cluster) | single (one 128-row tile per CTA)
 int gemm_mode() {
@@ -1046,11 +1153,15 @@ int gemm_mode() {
 }
 
 int launch_tn(ctr_handle* h, cudaStream_t st, int M, int N, int R, const float* A, int64_t lda, const float* B,
-              int64_t ldb, float* C, int64_t ldc, const EpiParams& ep) {
+              int64_t ldb, float* C, int64_t ldc, EpiParams ep) {
     CTR_REQUIRE(h, N <= MAX_N, "TF32 path: N=%d > %d not supported", N, MAX_N);
     const int nmma = N > 256 ? 2 : 1;
     const int NB = nmma == 1 ? (int) ctr_align(N, 16) : (int) ctr_align(N, 32);
     const int n_each = NB / nmma;
+    // sign-bit slots per 32-row block: the units / slabs of every kernel below are n_each columns wide and start their
+    // sub-tile count at bits_c0 = index * ceil(n_each / 32); a CTA that covers all NB columns in one sweep (single, pair)
+    // counts ceil(NB / 32) <= nmma * ceil(n_each / 32) sub-tiles from 0
+    ep.bits_chunks = nmma * ((n_each + 31) / 32);
     // output columns [N, align4(N)) exist in C when ldc allows (pad columns of the activations / dX0): storing the zeros
     // the accumulator holds there keeps every store a full 128-bit one (fast epilogue).  Not with a bias / mask, whose
     // vectors end at N.
@@ -1199,16 +1310,27 @@ __global__ void __launch_bounds__(256) tc_splitk_reduce(const float* __restrict_
 }  // namespace
 
 int ctr_tc_mlp_fwd(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* X, int64_t ldx, const float* Wt,
-                   const float* bias, int relu, float keep, uint64_t seed, float* Y, int64_t ldy) {
+                   const float* bias, int relu, float keep, uint64_t seed, float* Y, int64_t ldy, uint32_t* relu_bits) {
     // Wt is the K-major copy [N, ldwt] with ldwt = K rounded up to 4 floats (TMA needs 16-byte row pitches)
-    EpiParams ep{bias, relu, keep, seed, nullptr, 0, 1.f, 1, 0, N, gemm_dbg(), gemm_trace_buf(), nullptr, 0};
+    EpiParams ep{bias, relu, keep, seed, nullptr, 0, 1.f, 1, 0, N, gemm_dbg(), gemm_trace_buf(), nullptr, 0, tma_lanes(),
+                 relu_bits, nullptr, 0, 0};
     return launch_tn(h, st, B, N, K, X, ldx, Wt, ctr_align(K, 4), Y, ldy, ep);
 }
 
+// bytes of the sign-bit buffer of a [B, N] activation: 4 blocks of 32 rows per 128-row tile, one word per lane and slot
+int64_t ctr_tc_relu_bits_bytes(int B, int N) {
+    const int nmma = N > 256 ? 2 : 1;
+    const int NB = nmma == 1 ? (int) ctr_align(N, 16) : (int) ctr_align(N, 32);
+    const int64_t slots = (int64_t) nmma * ((NB / nmma + 31) / 32);
+    return ctr_align(ctr_cdiv(B, BLOCK_M) * 4 * slots * 32 * 4, 256);
+}
+
 int ctr_tc_mlp_bwd_data(ctr_handle* h, cudaStream_t st, int B, int K, int N, const float* dZ, int64_t lddz,
-                        const float* W, const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx) {
+                        const float* W, const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx,
+                        const uint32_t* relu_bits) {
     // dX[B,K] = dZ[B,N] * W[K,N]^T : W is already reduction-major for this product
-    EpiParams ep{nullptr, 0, 1.f, 0, mask, ldmask, mask_scale, 1, 0, K, gemm_dbg(), gemm_trace_buf(), nullptr, 0};
+    EpiParams ep{nullptr, 0, 1.f, 0, relu_bits ? nullptr : mask, ldmask, mask_scale, 1, 0, K, gemm_dbg(), gemm_trace_buf(), nullptr, 0,
+                 tma_lanes(), nullptr, relu_bits, 0, 0};
     return launch_tn(h, st, B, K, N, dZ, lddz, W, N, dX, lddx, ep);
 }
 
@@ -1241,7 +1363,7 @@ int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K_w, int N,
     }
     dim3 grid((unsigned) p.mtiles, (unsigned) p.splits);
     gemm_nt_kernel<<<grid, nthreads(NT_EW), smem, st>>>(tmA, tmB, K, N, B, p.r_per_split, p.n1, p.n2, p.nstages,
-                                                    tmem_cols_for(p.n1 + p.n2), (float*) ws);
+                                                    tmem_cols_for(p.n1 + p.n2), (float*) ws, tma_lanes(), gemm_dbg());
     CTR_CHECK_LAUNCH(h, "gemm_nt_kernel");
     const int64_t n = (int64_t) K * N;
     tc_splitk_reduce<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>((const float*) ws, p.splits, n, (int64_t) K_w * N, dW, dbias);

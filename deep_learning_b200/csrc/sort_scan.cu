@@ -81,7 +81,7 @@ radix_scan_rows_kernel(uint32_t* __restrict__ hist, int nblk, uint32_t* __restri
 
 // ---- pass 3: stable scatter ------------------------------------------------------------------
 // Warp w owns keys [w*256, (w+1)*256) of the tile and walks them in 8 rounds of 32 consecutive keys;
-// __match_any_sync ranks equal digits inside a round in lane (= index) order, a per-warp counter
+// a ballot-built peer mask ranks equal digits inside a round in lane (= index) order, a per-warp counter
 // table carries ranks across rounds, a cross-warp exclusive sum and a scan over the digits finish the tile-local
 // rank.  The tile is then ordered in shared memory and written out from there: consecutive threads store consecutive
 // positions of a digit's run, so a warp store touches a few sectors instead of 32.
@@ -131,8 +131,16 @@ radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __res
         uint32_t d = (key[it] >> shift) & (RADIX - 1);
         // invalid lanes use a digit slot of their own (RADIX-1 of PAD keys still must not mix):
         // match on (valid, d) so padding lanes never rank against real keys
-        uint32_t mkey = valid ? d : (RADIX + (uint32_t) lane);
-        uint32_t peers = __match_any_sync(0xffffffffu, mkey);
+        // lanes with the same digit, from RADIX_BITS + 1 ballots.  (__match_any_sync does this in one instruction, but the
+        // hardware walks the distinct values of the warp one by one: with 9-bit digits nearly every lane is its own
+        // group, and MATCH.ANY was what this kernel's 29 us per pass were made of.)
+        uint32_t peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int b = 0; b < RADIX_BITS; ++b) {
+            const uint32_t m = __ballot_sync(0xffffffffu, (d >> b) & 1u);
+            peers &= ((d >> b) & 1u) ? m : ~m;
+        }
+        if (!valid) peers = 1u << lane;
         uint32_t rank = __popc(peers & ((1u << lane) - 1u));
         int leader = __ffs(peers) - 1;
         uint32_t old = 0;

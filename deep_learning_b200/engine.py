@@ -118,12 +118,21 @@ class CtrEngine:
         self._ids_external = False          # sharded engine: ids live in its id plans
         self._use_inputs(0)
         self.x0 = torch.zeros(B, s.x0_ld, **f32)
-        # hidden activations carry 4 pad columns; column H holds 1.0 for good, so the weight-gradient GEMM of the next
-        # layer yields the bias gradient as an extra row (no GEMM ever reads or writes past column H-1 otherwise)
-        self.act_ld = [h_ + 4 for h_ in s.hidden]
+        # hidden activations carry pad columns; column H holds 1.0 for good, so the weight-gradient GEMM of the next
+        # layer yields the bias gradient as an extra row (no GEMM ever reads or writes past column H-1 otherwise).  The row
+        # pitch is a multiple of 128 bytes: with H + 4 floats (1616 B at H = 400) every other row starts in the middle of a
+        # 32-byte sector and the epilogue's stores cost 6 % of the GEMM (62.3 vs 66.0 us, profiles/r02j_gemm_bound.txt)
+        self.act_ld = [_ru(h_ + 1, 32) for h_ in s.hidden]
         self.acts = [torch.zeros(B, ld, **f32) for ld in self.act_ld]
         for a, h_ in zip(self.acts, s.hidden):
             a[:, h_] = 1.0
+        # TF32 training: the forward pass of every hidden layer but the last also leaves its ReLU sign bits, and the data
+        # gradient of the next layer masks with those instead of re-reading the fp32 activation (ctr_mlp_fwd_bits);
+        # CTR_RELU_BITS=0 keeps the fp32 mask for A/B
+        self.relu_bits = None
+        if self.prec == 1 and train and os.environ.get("CTR_RELU_BITS", "1") != "0":
+            self.relu_bits = [torch.zeros(max(self.h.query("ctr_mlp_relu_bits_bytes", B, h_) // 4, 1), dtype=torch.int32, device=dev)
+                              for h_ in s.hidden[:-1]]
         self.fm = torch.zeros(B, s.fm_ld, **f32)
         self.sum_e = torch.zeros(B, s.k, **f32)
         self.logit, self.score, self.dlogit = (torch.zeros(B, **f32) for _ in range(3))
@@ -619,8 +628,12 @@ class CtrEngine:
         self._mark("embed")
         x, ldx = self.x0, s.x0_ld
         for i, (k_, h_) in enumerate(self._layer_dims()):
-            h.call("ctr_mlp_fwd", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self._w(i)),
-                   ptr(self.wt[i]) if self.wt is not None else None, ptr(self._b(i)), 1, 1.0, 0, ptr(self.acts[i]), self.act_ld[i])
+            if self.relu_bits is not None and self.train_mode and i < len(self.relu_bits):
+                h.call("ctr_mlp_fwd_bits", st, B, k_, h_, ptr(x), ldx, ptr(self.wt[i]), ptr(self._b(i)), 1.0, 0,
+                       ptr(self.acts[i]), self.act_ld[i], ptr(self.relu_bits[i]))
+            else:
+                h.call("ctr_mlp_fwd", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self._w(i)),
+                       ptr(self.wt[i]) if self.wt is not None else None, ptr(self._b(i)), 1, 1.0, 0, ptr(self.acts[i]), self.act_ld[i])
             x, ldx = self.acts[i], self.act_ld[i]
         w_fm, w_deep, bias = self._head_parts()
         self._mark("mlp_fwd")
@@ -706,8 +719,7 @@ class CtrEngine:
             h.call("ctr_mlp_bwd_weight", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self.dz[cur]), h_,
                    ptr(self._w(i, self.grad)), ptr(self._b(i, self.grad)), ws, wsn, 1)
             if i > 0:
-                h.call("ctr_mlp_bwd_data", st, self.prec, B, k_, h_, ptr(self.dz[cur]), h_, ptr(self._wd(i)), ptr(x),
-                       ldx, 1.0, ptr(self.dz[cur ^ 1]), k_)
+                self._dgrad_hidden(st, B, i, k_, h_, self.dz[cur], self.dz[cur ^ 1])
                 cur ^= 1
             elif s.E:
                 # only the embedding columns of X0 carry parameters: canonical order puts them first
@@ -743,6 +755,16 @@ class CtrEngine:
         self.global_step += 1
         self._steps_done += 1
 
+    def _dgrad_hidden(self, st: int, B: int, i: int, k_: int, h_: int, dz_in, dz_out) -> None:
+        """dZ of layer i-1 = (dZ of layer i @ W_i^T) masked by the ReLU of layer i-1's output (models/deepfm.py:121-126
+        differentiated): sign bits left by the forward pass when there are any, else the fp32 activation itself"""
+        if self.relu_bits is not None:
+            self.h.call("ctr_mlp_bwd_data_bits", st, B, k_, h_, ptr(dz_in), h_, ptr(self._wd(i)), ptr(self.relu_bits[i - 1]), 1.0,
+                        ptr(dz_out), k_)
+        else:
+            self.h.call("ctr_mlp_bwd_data", st, self.prec, B, k_, h_, ptr(dz_in), h_, ptr(self._wd(i)), ptr(self.acts[i - 1]),
+                        self.act_ld[i - 1], 1.0, ptr(dz_out), k_)
+
     class _OnStream:
         """while active, every helper of the engine enqueues on `stream` instead of the step's main stream"""
 
@@ -775,8 +797,7 @@ class CtrEngine:
         for i in range(L - 1, 0, -1):                      # dz[j] is dZ of layer L-1-j
             j = L - 1 - i
             k_, h_ = dims[i]
-            h.call("ctr_mlp_bwd_data", st, self.prec, B, k_, h_, ptr(self.dz[j]), h_, ptr(self._wd(i)), ptr(self.acts[i - 1]),
-                   self.act_ld[i - 1], 1.0, ptr(self.dz[j + 1]), k_)
+            self._dgrad_hidden(st, B, i, k_, h_, self.dz[j], self.dz[j + 1])
         if s.E:      # only the embedding columns of X0 carry parameters: canonical order puts them first
             h.call("ctr_mlp_bwd_data", st, self.prec, B, s.E, dims[0][1], ptr(self.dz[L - 1]), dims[0][1], ptr(self._wd(0)), None, 0,
                    1.0, ptr(self.dx0), self.dx0_ld)

@@ -156,6 +156,20 @@ int ctr_mlp_fwd(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
 int ctr_mlp_bwd_data(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
                      const float* dZ, int64_t lddz, const float* W,
                      const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx);
+/* TF32 path only: the forward pass of a hidden layer can leave ONE BIT per output element (1 = the stored activation
+ * is > 0) next to Y, and the data gradient of the NEXT layer can take those bits as its ReLU mask instead of re-reading
+ * the fp32 activation (105 MB per layer at config 4, and the latency of those loads was the data-gradient GEMM's
+ * epilogue).  Results are identical to the mask form.  The bit layout is private to the kernels (it follows the
+ * epilogue's thread <-> element mapping) and depends on (B, N) only, so a buffer written for a [B, N] activation is
+ * read back by the data gradient whose output is that [B, N] matrix; ctr_mlp_relu_bits_bytes(B, N) is its size.
+ * ctr_mlp_fwd_bits = ctr_mlp_fwd(precision TF32, relu = 1, bias required) + relu_bits;
+ * ctr_mlp_bwd_data_bits = ctr_mlp_bwd_data(precision TF32) with relu_bits (of the [B, K] activation) for the mask. */
+int64_t ctr_mlp_relu_bits_bytes(ctr_handle* h, int B, int N);
+int ctr_mlp_fwd_bits(ctr_handle* h, ctr_stream s, int B, int K, int N, const float* X, int64_t ldx,
+                     const float* Wt, const float* bias, float keep, uint64_t seed, float* Y, int64_t ldy,
+                     uint32_t* relu_bits);
+int ctr_mlp_bwd_data_bits(ctr_handle* h, ctr_stream s, int B, int K, int N, const float* dZ, int64_t lddz,
+                          const float* W, const uint32_t* relu_bits, float mask_scale, float* dX, int64_t lddx);
 /* dW[K,N] = X^T @ dZ ; dbias[N] = colsum(dZ).  ws: ctr_mlp_bwd_weight_ws_bytes().
  * x_ones_col != 0: the caller keeps X[:, K] == 1.0 (ldx > K); the TF32 path then gets dbias as row K of the same
  * GEMM instead of a separate pass over dZ (ignored by the FP32 path). */

@@ -54,6 +54,28 @@ def main():
         t = timeit(lambda i: hd.call("ctr_mlp_bwd_weight", st, 1, B, K, N, ptr(X[i]), ldx, ptr(dZ[i]), N, ptr(dW), ptr(db),
                                      ptr(ws), wsn, 0))
         print("wgrad K=%d N=%d: %7.1f us  %6.1f TFLOP/s  (HBM floor %.1f us)" % (K, N, t, flops / t / 1e6, (B * (K + N) * 4) / 6.5395e6))
+        nb = hd.query("ctr_mlp_relu_bits_bytes", B, N)
+        bits = [torch.zeros(nb // 4, dtype=torch.int32, device="cuda") for _ in range(NSET)]
+        t = timeit(lambda i: hd.call("ctr_mlp_fwd_bits", st, B, K, N, ptr(X[i]), ldx, ptr(Wt), ptr(bias), 1.0, 0, ptr(Y[i]), N + 4,
+                                     ptr(bits[i])))
+        print("fwd + sign bits      : %7.1f us" % t)
+        if K == N:      # the bits of a [B, N] activation mask the data gradient whose output is [B, K = N]
+            t = timeit(lambda i: hd.call("ctr_mlp_bwd_data_bits", st, B, K, N, ptr(dZ[i]), N, ptr(W), ptr(bits[i]), 1.0,
+                                         ptr(dX[i]), dX[i].shape[1]))
+            print("dgrad with sign bits : %7.1f us" % t)
+        # the library GEMM on the same operands (cuBLAS TF32 through torch.matmul: the bare product, no bias / ReLU / mask
+        # epilogue and no tf32 rounding of the output), as the yardstick for what this shape allows
+        torch.backends.cuda.matmul.allow_tf32 = True
+        Yc = [torch.zeros(B, N, device="cuda") for _ in range(NSET)]
+        dXc = [torch.zeros(B, K, device="cuda") for _ in range(NSET)]
+        dWc = torch.zeros(K, N, device="cuda")
+        t = timeit(lambda i: torch.mm(X[i][:, :K], W, out=Yc[i]))
+        print("  cuBLAS fwd  : %7.1f us  %6.1f TFLOP/s" % (t, flops / t / 1e6))
+        t = timeit(lambda i: torch.mm(dZ[i], W.t(), out=dXc[i]))
+        print("  cuBLAS dgrad: %7.1f us  %6.1f TFLOP/s" % (t, flops / t / 1e6))
+        t = timeit(lambda i: torch.mm(X[i][:, :K].t(), dZ[i], out=dWc))
+        print("  cuBLAS wgrad: %7.1f us  %6.1f TFLOP/s" % (t, flops / t / 1e6))
+        del Yc, dXc
 
 
 if __name__ == "__main__":

@@ -26,8 +26,14 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     B, R = int(os.environ.get("B", 65536)), int(os.environ.get("ROWS", 100_000_000))
-    hp = Bn.hparams(B, R)
-    spec = spec_from_hparams("deepfm", hp)
+    alg = os.environ.get("ALG", "deepfm")          # ALG=wdl ROWS=10000000: BASELINE.json configs[2]
+    if alg == "deepfm":
+        hp = Bn.hparams(B, R)
+    else:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import ctr_helpers as H
+        hp = H.hp_criteo(B=B, rows=R)
+    spec = spec_from_hparams(alg, hp)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
         from deep_learning_b200.sharded import ShardedCtrEngine
@@ -38,7 +44,10 @@ def main():
     eng.set_dense_weights(init_weights(spec, 2019, with_table=False))
     sizes = D.field_sizes(R, spec.Fc)
     NB = 4
-    batches = [D.synthetic_batch(B, spec.C, spec.Fc, sizes, seed=2020 + i * world + rank, device=dev) for i in range(NB)]
+    if alg == "deepfm":
+        batches = [D.synthetic_batch(B, spec.C, spec.Fc, sizes, seed=2020 + i * world + rank, device=dev) for i in range(NB)]
+    else:
+        batches = [{k: v.to(dev) for k, v in H.make_batch(alg, hp, seed=2020 + i * world + rank).items()} for i in range(NB)]
     pf = not os.environ.get("NOPREFETCH")
     for i in range(6):
         eng.train_step(batches[i % NB], next_batch=batches[(i + 1) % NB] if pf else None)

@@ -173,6 +173,47 @@ def test_mlp_tf32_tcgen05_gemms(hd, B, K, N):
     assert H.rel_err(db.cpu(), dZ.double().sum(0)) < 1e-5
 
 
+@pytest.mark.parametrize("B,K,N", [(100, 37, 72), (1000, 429, 400), (4096, 400, 400), (1300, 400, 256), (777, 64, 500)])
+def test_mlp_tf32_relu_sign_bits_equal_the_fp32_mask(hd, B, K, N):
+    """ctr_mlp_fwd_bits / ctr_mlp_bwd_data_bits (ReLU sign bits in the kernels' own layout) against ctr_mlp_fwd /
+    ctr_mlp_bwd_data with the fp32 activation as the mask: bit-for-bit the same Y and dX (tail tiles, both the
+    one-tile and the persistent kernel, one and two MMA units)."""
+    from deep_learning_b200._lib import ptr
+    if not hd.has_tcgen05:
+        pytest.skip("needs sm_100")
+    g = torch.Generator().manual_seed(11)
+    Kp = (K + 3) // 4 * 4
+    X = torch.zeros(B, Kp)
+    X[:, :K] = torch.randn(B, K, generator=g)
+    X = X.cuda()
+    W = (torch.randn(K, N, generator=g) * 0.1).cuda()
+    b = torch.randn(N, generator=g).cuda()
+    Wt = torch.zeros(N, Kp, device="cuda")
+    hd.call("ctr_transpose", _st(), ptr(W), K, N, ptr(Wt), Kp, 1)
+    ldy = (N + 1 + 31) // 32 * 32
+    Y0, Y1 = torch.zeros(B, ldy, device="cuda"), torch.zeros(B, ldy, device="cuda")
+    nb = hd.query("ctr_mlp_relu_bits_bytes", B, N)
+    assert nb >= B * N // 8
+    bits = torch.full((nb // 4,), -1, dtype=torch.int32, device="cuda")
+    hd.call("ctr_mlp_fwd", _st(), 1, B, K, N, ptr(X), Kp, ptr(W), ptr(Wt), ptr(b), 1, 1.0, 0, ptr(Y0), ldy)
+    hd.call("ctr_mlp_fwd_bits", _st(), B, K, N, ptr(X), Kp, ptr(Wt), ptr(b), 1.0, 0, ptr(Y1), ldy, ptr(bits))
+    torch.cuda.synchronize()
+    assert torch.equal(Y0, Y1)
+    frac = (Y0[:, :N] > 0).float().mean().item()
+    assert 0.2 < frac < 0.8                                   # both branches of the ReLU are exercised
+    # the next layer's data gradient: dX[B, N] = (dZ[B, N2] @ W2[N, N2]^T) masked by Y
+    N2 = 136
+    dZ = torch.randn(B, N2, generator=g).cuda()
+    W2 = (torch.randn(N, N2, generator=g) * 0.1).cuda()
+    ldd = (N + 3) // 4 * 4
+    d0, d1 = torch.zeros(B, ldd, device="cuda"), torch.zeros(B, ldd, device="cuda")
+    hd.call("ctr_mlp_bwd_data", _st(), 1, B, N, N2, ptr(dZ), N2, ptr(W2), ptr(Y0), ldy, 1.0, ptr(d0), ldd)
+    hd.call("ctr_mlp_bwd_data_bits", _st(), B, N, N2, ptr(dZ), N2, ptr(W2), ptr(bits), 1.0, ptr(d1), ldd)
+    torch.cuda.synchronize()
+    assert torch.equal(d0, d1)
+    assert (d0[:, :N] != 0).float().mean().item() > 0.15
+
+
 @pytest.mark.parametrize("B,H,n_fm,w_off,with_extra", [(1000, 400, 55, 55, False),     # config 4: w_deep slice 220 B into the head weight
                                                        (257, 128, 38, 38, False), (64, 512, 0, 0, True),
                                                        (77, 10, 7, 3, False),           # H % 4 != 0: scalar kernel

@@ -12,9 +12,10 @@ from deep_learning_b200 import _lib           # noqa: E402
 from deep_learning_b200._lib import ptr       # noqa: E402
 
 B, K, N, ldx = 65536, 400, 400, 404
+LDY = int(os.environ.get("LDY", N + 4))
 hd = _lib.Handle(0)
 st = torch.cuda.current_stream().cuda_stream
-X = torch.randn(B, ldx, device="cuda"); Y = torch.zeros(B, N + 4, device="cuda")
+X = torch.randn(B, ldx, device="cuda"); Y = torch.zeros(B, LDY, device="cuda")
 W = torch.randn(K, N, device="cuda") * 0.05; Wt = torch.zeros(N, K, device="cuda"); bias = torch.randn(N, device="cuda")
 hd.call("ctr_transpose", st, ptr(W), K, N, ptr(Wt), K, 1)
 dgrad = len(sys.argv) > 1 and sys.argv[1] == "dgrad"
@@ -23,7 +24,7 @@ for _ in range(3):
     if dgrad:
         hd.call("ctr_mlp_bwd_data", st, 1, B, K, N, ptr(dZ), N, ptr(W), ptr(X), ldx, 1.0, ptr(dX), ldx)
     else:
-        hd.call("ctr_mlp_fwd", st, 1, B, K, N, ptr(X), ldx, ptr(W), ptr(Wt), ptr(bias), 1, 1.0, 0, ptr(Y), N + 4)
+        hd.call("ctr_mlp_fwd", st, 1, B, K, N, ptr(X), ldx, ptr(W), ptr(Wt), ptr(bias), 1, 1.0, 0, ptr(Y), LDY)
 torch.cuda.synchronize()
 full = np.zeros((4096 + 64, 8), dtype=np.uint64)
 assert hd.lib.ctr_debug_gemm_trace(full.ctypes.data, 4096 + 64) == 0
