@@ -329,7 +329,8 @@ def main():
         eng.align_ranks()
     e0.record()
     for i in range(a.steps):
-        loss = float(eng.train_step(host_batches[i % NB], next_batch=host_batches[(i + 1) % NB]).item())
+        eng.train_step(host_batches[i % NB], next_batch=host_batches[(i + 1) % NB])
+        loss = eng.last_loss()       # this step's loss on the host, every step (waits for its D2H copy, see CtrEngine.last_loss)
     e1.record()
     sync()
     e2e_ms = max_over_ranks(e0.elapsed_time(e1))

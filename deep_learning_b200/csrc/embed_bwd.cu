@@ -576,7 +576,7 @@ scalar_segment_add_kernel(const uint32_t* __restrict__ uniq, const uint32_t* __r
                           const float* __restrict__ src, uint32_t ld, int64_t dst_rows, float* __restrict__ dst) {
     int64_t U = *n_unique;
     if (U > n_max) U = n_max;
-    const int sub = threadIdx.x & 7;
+    const int lane = threadIdx.x & 31, sub = lane & 7;
     const int64_t groups = ((int64_t) gridDim.x * blockDim.x) >> 3;
     // every lane of a warp runs the same number of iterations (the shuffles below are warp-wide)
     const int64_t g0 = ((int64_t) blockIdx.x * blockDim.x + threadIdx.x) >> 3;
@@ -584,17 +584,41 @@ scalar_segment_add_kernel(const uint32_t* __restrict__ uniq, const uint32_t* __r
     for (int64_t it = 0; it < iters; ++it) {
         const int64_t u = g0 + it * groups;
         float acc = 0.f;
-        uint32_t key = CTR_PAD_KEY;
+        uint32_t key = CTR_PAD_KEY, s = 0, e = 0;
         if (u < U) {
             key = uniq[u];
-            const uint32_t s = seg_start[u], e = seg_start[u + 1];
-            if (key != CTR_PAD_KEY)
-                for (uint32_t i = s + sub; i < e; i += 8) acc += src[perm[i] / ld];
+            s = seg_start[u];
+            e = seg_start[u + 1];
         }
+        const bool live = key != CTR_PAD_KEY;
+        // a hot id of a Zipf-distributed field is looked up by thousands of samples: walked by 8 lanes with two dependent
+        // loads per element that one run WAS the kernel (1 ms at config 3).  Runs longer than 64 elements are summed by the
+        // whole warp, eight independent loads per lane in flight; the order of the additions depends on the run's length
+        // only, so the result stays reproducible.
+        const bool is_long = live && (e - s) > 64u;
+        if (live && !is_long)
+            for (uint32_t i = s + sub; i < e; i += 8) acc += src[perm[i] / ld];
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
         acc += __shfl_xor_sync(0xffffffffu, acc, 4);
-        if (sub == 0 && key != CTR_PAD_KEY && (int64_t) key < dst_rows) dst[key] += acc;
+        unsigned todo = __ballot_sync(0xffffffffu, is_long && sub == 0);
+        while (todo) {
+            const int owner = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const uint32_t ls = __shfl_sync(0xffffffffu, s, owner), le = __shfl_sync(0xffffffffu, e, owner);
+            float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            uint32_t i = ls + lane;
+            for (; i + 7 * 32 < le; i += 8 * 32) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a[j] += src[perm[i + j * 32] / ld];
+            }
+            for (; i < le; i += 32) a[0] += src[perm[i] / ld];
+            float t = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+            if (lane == owner) acc = t;
+        }
+        if (sub == 0 && live && (int64_t) key < dst_rows) dst[key] += acc;
     }
 }
 

@@ -978,11 +978,54 @@ class CtrEngine:
         # it waits for ev_call and not for the forward
         self._prefetch_next(next_batch, ev_call)
         reg = self._reg_loss()
+        out = None
+        if self.loss_is_early:
+            # the value is final once the head kernel has run: hand it to the host copy now, so a caller that reads
+            # every step's loss (last_loss()) waits for the forward pass only and queues the next step under the backward
+            out = self._publish_loss(reg)
         self.backward_and_update(B)
-        loss = self._global_loss()
+        if out is None:
+            out = self._publish_loss(reg)
         self._end_step()
         self._mark("update")
-        return loss if reg is None else loss + reg
+        return out
+
+    @property
+    def loss_is_early(self) -> bool:
+        """sharded engines: the global loss comes back with the gradient all-reduce, after the backward; the gathered-l2
+        models (quirk Q6) add a loss term that the backward computes"""
+        return not (self.spec.gathered_l2 and self.spec.l2_reg > 0)
+
+    def _publish_loss(self, reg) -> torch.Tensor:
+        loss = self._global_loss()
+        if reg is not None:
+            loss = loss + reg
+        main = self._main_stream()
+        if self._loss_host is None:
+            self._loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+            self._loss_stream = torch.cuda.Stream(device=self.dev)
+            self._loss_events = [torch.cuda.Event(), torch.cuda.Event()]
+            self._loss_made = torch.cuda.Event()
+        self._loss_slot ^= 1
+        self._loss_made.record(main)
+        self._loss_stream.wait_event(self._loss_made)
+        with torch.cuda.stream(self._loss_stream):
+            self._loss_host[self._loss_slot:self._loss_slot + 1].copy_(loss, non_blocking=True)
+        loss.record_stream(self._loss_stream)
+        self._loss_events[self._loss_slot].record(self._loss_stream)
+        return loss
+
+    _loss_host = None
+    _loss_slot = 0
+
+    def last_loss(self) -> float:
+        """The loss of the latest train_step as a host float (what `sess.run([loss, optimizer])` hands back,
+        models/deepfm.py:181).  Waits for that value's device-to-host copy only -- on one GPU the loss is final after the
+        forward pass -- and not for the rest of the step, unlike `.item()` on the returned tensor."""
+        if self._loss_host is None:
+            raise _lib.CtrError("last_loss: no train_step has run")
+        self._loss_events[self._loss_slot].synchronize()
+        return float(self._loss_host[self._loss_slot])
 
     def _prefetch_next(self, next_batch: Optional[Dict], ev_call) -> None:
         """work for the next step that runs under this one: upload the next batch into the other input set"""

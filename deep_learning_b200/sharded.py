@@ -553,6 +553,8 @@ class ShardedCtrEngine(CtrEngine):
             self._dense_work.wait()          # stream-side wait: the main stream continues behind the collective
             self._dense_work = None
 
+    loss_is_early = False      # the global loss comes back with the gradient all-reduce
+
     def _global_loss(self) -> torch.Tensor:
         return self._dense_grad()[self.n_dense:self.n_dense + 1].clone()
 

@@ -250,6 +250,23 @@ def test_deepfm_free_running_trajectory_stays_close():
         assert np.percentile(d, 99.9) < 2e-3, (n, float(np.percentile(d, 99.9)), float(d.max()))
 
 
+def test_last_loss_is_the_returned_loss_every_step():
+    """CtrEngine.last_loss() (the host float a `sess.run([loss, optimizer])` caller gets each step; it waits for the
+    forward pass only) equals .item() of the tensor train_step returns, step after step, with and without a prefetched
+    next batch"""
+    hp = H.hp_c1(cate_feats_size=500, batch_size=1024)
+    p = O.init_params("deepfm", hp, dtype=torch.float64)
+    eng = _engine("deepfm", hp, p, hp.batch_size, adam_mode="lazy")
+    bs = [H.make_batch("deepfm", hp, seed=5 + i) for i in range(5)]
+    seen = []
+    for i in range(4):
+        t = eng.train_step(bs[i], next_batch=bs[i + 1] if i % 2 == 0 else None)
+        early = eng.last_loss()
+        assert early == float(t.item()), (i, early, float(t.item()))
+        seen.append(early)
+    assert len(set(seen)) == 4 and all(np.isfinite(seen))
+
+
 def test_training_is_deterministic_run_to_run():
     """bitwise-equal parameters from two identical runs (the sort/segment-reduce is order-fixed)"""
     hp = H.hp_c1(cate_feats_size=500, batch_size=1024)
