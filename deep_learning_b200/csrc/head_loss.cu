@@ -1,5 +1,7 @@
 // K5: output head (concat + [.,1] projection + sigmoid), tf.losses.log_loss and its gradient,
 // plus the deterministic column reductions that give head-weight / bias gradients.
+#include <stdlib.h>
+
 #include "ctr_common.cuh"
 
 namespace {
@@ -298,6 +300,167 @@ head_fwd_vec_kernel(int B, float inv_bg, const float* __restrict__ fm, int64_t f
     }
 }
 
+// ---- the training step's head, streamlined (ncu r02k: the general kernel above spent 99 us on 175 MB, issue-bound: ~50 M
+// warp instructions for 64K rows, half of them guards and address arithmetic for cases the training call never has).
+// Same lane <-> column mapping, same order of every sum (so the results are those of head_fwd_vec_kernel bit for bit),
+// but: every output is present, NT = ceil(H / 128) is a template parameter and only the last float4 group of a row can be
+// partial, the label / wide term of the next row travel with its prefetch, and two row buffers alternate instead of
+// being copied.
+template <int NT>
+struct HeadRow {
+    float4 d[NT];
+    float4 f;
+    float y, e;
+};
+
+template <int NT, bool GATE, bool ROUND>
+__global__ void __launch_bounds__(256, 2)
+head_train_kernel(int B, float inv_bg, const float* __restrict__ fm, int64_t fm_ld, int n_fm, const float* __restrict__ w_fm,
+                  const float* __restrict__ deep, int64_t deep_ld, int H, const float* __restrict__ w_deep,
+                  const float* __restrict__ extra, const float* __restrict__ bias, const float* __restrict__ label,
+                  float* __restrict__ logit, float* __restrict__ score, float* __restrict__ dlogit,
+                  float* __restrict__ dz_last, int64_t lddz, float* __restrict__ loss_part, float* __restrict__ colpart,
+                  int flags) {
+    extern __shared__ float sm[];                  // [HV_WARPS][H + n_fm + 1]
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int ncol = H + n_fm + 1;
+    const bool fm_lane = lane * 4 < n_fm;
+    const bool last_ok = 4 * lane + 128 * (NT - 1) < H;       // H % 4 == 0 and H > 128 * (NT - 1): earlier groups are whole
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 wd[NT], gd[NT];
+    float4 wf = zero4, gf = zero4;
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+        const int j = 4 * lane + 128 * t;
+        wd[t] = j < H ? make_float4(w_deep[j], w_deep[j + 1], w_deep[j + 2], w_deep[j + 3]) : zero4;
+        gd[t] = zero4;
+    }
+    const int jf = 4 * lane;
+    const bool f1 = jf + 1 < n_fm, f2 = jf + 2 < n_fm, f3 = jf + 3 < n_fm;
+    if (fm_lane) {
+        wf.x = w_fm[jf];
+        wf.y = f1 ? w_fm[jf + 1] : 0.f;
+        wf.z = f2 ? w_fm[jf + 2] : 0.f;
+        wf.w = f3 ? w_fm[jf + 3] : 0.f;
+    }
+    const float bs = bias ? bias[0] : 0.f;
+    float gb = 0.f, lsum = 0.f;
+
+    auto load_row = [&](int64_t b, HeadRow<NT>& r) {
+        const float4* p = reinterpret_cast<const float4*>(deep + b * deep_ld) + lane;
+#pragma unroll
+        for (int t = 0; t < NT - 1; ++t) r.d[t] = __ldcs(p + 32 * t);
+        r.d[NT - 1] = last_ok ? __ldcs(p + 32 * (NT - 1)) : zero4;
+        r.f = zero4;
+        if (fm_lane) {
+            r.f = __ldcs(reinterpret_cast<const float4*>(fm + b * fm_ld) + lane);
+            if (!f1) r.f.y = 0.f;                  // pad columns of the fm row are not part of the model
+            if (!f2) r.f.z = 0.f;
+            if (!f3) r.f.w = 0.f;
+        }
+        r.y = label[b];
+        r.e = extra ? extra[b] : 0.f;
+    };
+    auto process = [&](int64_t b, const HeadRow<NT>& r) {
+        float acc = 0.f;
+#pragma unroll
+        for (int t = 0; t < NT; ++t) acc = f4_dot(r.d[t], wd[t], acc);
+        acc = f4_dot(r.f, wf, acc);
+        acc = ctr_warp_sum(acc);
+        const float z = acc + r.e + bs;
+        const float p = 1.f / (1.f + expf(-z));
+        float l_, d_;
+        head_loss(p, r.y, flags, LOG_LOSS_EPS, l_, d_);
+        lsum += l_;
+        const float dl = d_ * inv_bg;
+        if (lane == 0) {
+            logit[b] = z;
+            score[b] = p;
+            dlogit[b] = dl;
+        }
+        float4* o = reinterpret_cast<float4*>(dz_last + b * lddz) + lane;
+#pragma unroll
+        for (int t = 0; t < NT; ++t) {
+            float4 g = make_float4(dl * wd[t].x, dl * wd[t].y, dl * wd[t].z, dl * wd[t].w);
+            // finite values: the same result as cvt.rna.tf32.f32 in two integer operations
+            if (ROUND) g = make_float4(ctr_round_tf32_fast(g.x), ctr_round_tf32_fast(g.y), ctr_round_tf32_fast(g.z), ctr_round_tf32_fast(g.w));
+            if (GATE) {
+                g.x = r.d[t].x > 0.f ? g.x : 0.f;
+                g.y = r.d[t].y > 0.f ? g.y : 0.f;
+                g.z = r.d[t].z > 0.f ? g.z : 0.f;
+                g.w = r.d[t].w > 0.f ? g.w : 0.f;
+            }
+            if (t < NT - 1 || last_ok) o[32 * t] = g;
+            gd[t].x = fmaf(dl, r.d[t].x, gd[t].x); gd[t].y = fmaf(dl, r.d[t].y, gd[t].y);
+            gd[t].z = fmaf(dl, r.d[t].z, gd[t].z); gd[t].w = fmaf(dl, r.d[t].w, gd[t].w);
+        }
+        gf.x = fmaf(dl, r.f.x, gf.x); gf.y = fmaf(dl, r.f.y, gf.y);
+        gf.z = fmaf(dl, r.f.z, gf.z); gf.w = fmaf(dl, r.f.w, gf.w);
+        gb += dl;
+    };
+
+    const int64_t GW = (int64_t) gridDim.x * HV_WARPS;
+    int64_t b = (int64_t) blockIdx.x * HV_WARPS + w;
+    HeadRow<NT> ra, rb;
+    if (b < B) load_row(b, ra);
+    while (b < B) {                                // uniform across the warp
+        const int64_t b1 = b + GW;
+        if (b1 < B) load_row(b1, rb);
+        process(b, ra);
+        if (b1 >= B) break;
+        const int64_t b2 = b1 + GW;
+        if (b2 < B) load_row(b2, ra);
+        process(b1, rb);
+        b = b2;
+    }
+    float* mine = sm + w * ncol;
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+        const int j = 4 * lane + 128 * t;
+        if (j < H) { mine[j] = gd[t].x; mine[j + 1] = gd[t].y; mine[j + 2] = gd[t].z; mine[j + 3] = gd[t].w; }
+    }
+    if (fm_lane) {
+        mine[H + jf] = gf.x;
+        if (f1) mine[H + jf + 1] = gf.y;
+        if (f2) mine[H + jf + 2] = gf.z;
+        if (f3) mine[H + jf + 3] = gf.w;
+    }
+    if (lane == 0) mine[H + n_fm] = gb;
+    __syncthreads();
+    for (int c = threadIdx.x; c < ncol; c += blockDim.x) {
+        float a = 0.f;
+#pragma unroll
+        for (int ww = 0; ww < HV_WARPS; ++ww) a += sm[ww * ncol + c];
+        colpart[(int64_t) blockIdx.x * ncol + c] = a;
+    }
+    __syncthreads();
+    if (lane == 0) sm[w] = lsum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float a = 0.f;
+#pragma unroll
+        for (int i = 0; i < HV_WARPS; ++i) a += sm[i];
+        loss_part[blockIdx.x] = a;
+    }
+}
+
+template <int NT>
+static void launch_head_train(int nblk, size_t smem, cudaStream_t st, bool gate, bool round, int B, float inv_bg, const float* fm,
+                              int64_t fm_ld, int n_fm, const float* w_fm, const float* deep, int64_t deep_ld, int H,
+                              const float* w_deep, const float* extra, const float* bias, const float* label, float* logit,
+                              float* score, float* dlogit, float* dz_last, int64_t lddz, float* loss_part, float* colpart,
+                              int flags) {
+#define CTR_HEAD_TRAIN(G, R)                                                                                              \
+    head_train_kernel<NT, G, R><<<nblk, 256, smem, st>>>(B, inv_bg, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra, \
+                                                         bias, label, logit, score, dlogit, dz_last, lddz, loss_part,      \
+                                                         colpart, flags)
+    if (gate && round) CTR_HEAD_TRAIN(true, true);
+    else if (gate) CTR_HEAD_TRAIN(true, false);
+    else if (round) CTR_HEAD_TRAIN(false, true);
+    else CTR_HEAD_TRAIN(false, false);
+#undef CTR_HEAD_TRAIN
+}
+
 static inline int head_vec_blocks(ctr_handle* h, int B) {
     const int64_t want = ctr_cdiv(B > 0 ? B : 1, HV_WARPS), cap = (int64_t) h->sm_count * 2;
     return (int) (want < cap ? want : cap);
@@ -414,7 +577,21 @@ extern "C" int ctr_head_fwd(ctr_handle* h, ctr_stream s, int B, int64_t B_global
         if (want_grads) colpart = (float*) ((char*) ws + ctr_align((int64_t) nblk * 4, 256));
     }
     const size_t smem = (colpart ? (size_t) HEAD_WARPS * (H + n_fm + 1) : (size_t) HEAD_WARPS) * sizeof(float);
-    if (vec)
+    // the training call of the step: every output wanted, whole float4 groups but possibly the last
+    const bool train_fast = vec && label && logit && score && dlogit && dz_last && loss_out && colpart &&
+                            getenv("CTR_HEAD_GENERAL") == nullptr;
+    if (train_fast) {
+        const int nt = (H + 127) / 128;
+        const bool gate = (flags & CTR_HEAD_NO_RELU_GATE) == 0, rnd = round_tf32 != 0;
+#define CTR_HEAD_NT(N)                                                                                                     \
+    launch_head_train<N>(nblk, smem, ctr_st(s), gate, rnd, B, inv_bg, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra, \
+                         bias, label, logit, score, dlogit, dz_last, lddz, part, colpart, flags)
+        if (nt == 1) CTR_HEAD_NT(1);
+        else if (nt == 2) CTR_HEAD_NT(2);
+        else if (nt == 3) CTR_HEAD_NT(3);
+        else CTR_HEAD_NT(4);
+#undef CTR_HEAD_NT
+    } else if (vec)
         head_fwd_vec_kernel<<<nblk, 256, smem, ctr_st(s)>>>(B, inv_bg, fm, fm_ld, n_fm, w_fm, deep, deep_ld, H, w_deep, extra,
                                                             bias, label, logit, score, dlogit, dz_last, lddz, round_tf32,
                                                             loss_out ? part : nullptr, colpart, flags);
