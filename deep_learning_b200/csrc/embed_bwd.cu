@@ -3,6 +3,8 @@
 // fly from dX0 (the MLP's input gradient), the saved FM sum and the head weights, accumulated in
 // registers per run of equal row ids and written once per (row, chunk).  The Adam update then
 // consumes those partials in chunk order, so the whole scatter-add is deterministic.
+#include <stdlib.h>
+
 #include "ctr_common.cuh"
 #include "peer_route.cuh"
 
@@ -17,8 +19,8 @@ constexpr int LONG_RUN = 8;   // runs with more partials than this take the warp
 // dl_b * w2 * s_b and D += dl_b; the update kernel, which reads e_r anyway, subtracts w2 * e_r * D.  That removes the
 // random re-read of the X0 tile (one of three 64-byte random reads per lookup).  Multi-valued slots enter the FM
 // through their pooled vector, not the row, so they keep the direct form and add nothing to D.
-template <int K>
-__global__ void __launch_bounds__(256)
+template <int K, int UN = 4, int MINB = 3>
+__global__ void __launch_bounds__(256, MINB)
 embed_bwd_partials_kernel(const ctr_embed_cfg cfg, const uint32_t* __restrict__ keys, const uint32_t* __restrict__ perm,
                           const uint32_t* __restrict__ uidx, const int64_t n, const int32_t* __restrict__ field_of_slot,
                           const float* __restrict__ x0, const float* __restrict__ dx0, const int64_t dx0_ld,
@@ -27,7 +29,7 @@ embed_bwd_partials_kernel(const ctr_embed_cfg cfg, const uint32_t* __restrict__ 
                           const float* __restrict__ inv_cnt_first, const float* __restrict__ cont_grad,
                           const float* __restrict__ slot_weight, float* __restrict__ part) {
     constexpr int G = K / 4;   // lanes per chunk walker: lane q owns coordinates 4q..4q+3
-    constexpr int UN = 4;      // lookups in flight per walker
+    // UN = lookups in flight per walker (template parameter)
     const int64_t t = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t c = t / G;   // chunk index
     const int q = (int) (t % G);
@@ -284,8 +286,8 @@ __device__ __forceinline__ void adam4(float4& th, float4& mm, float4& vv, const 
 
 // embedding tables (row = K coordinates [+ first-order weight]): K/4 lanes per row, 128-bit accesses, every load of a
 // row independent of the others.  The arithmetic per element is the generic kernel's, in the same order.
-template <int K>
-__global__ void __launch_bounds__(256)
+template <int K, int MINB = 4>
+__global__ void __launch_bounds__(256, MINB)
 adam_rows_vec_kernel(const uint32_t* __restrict__ row_ids, const uint32_t* __restrict__ n_rows, int64_t n_max, uint32_t mask,
                      const float* __restrict__ grads, const uint32_t* __restrict__ seg_start, int gs, int has_first,
                      float* __restrict__ table, float* __restrict__ m, float* __restrict__ v, int stride, int64_t table_rows,
@@ -746,14 +748,26 @@ extern "C" int ctr_embed_bwd_partials_weighted(ctr_handle* h, ctr_stream s, cons
     const int64_t chunks = ctr_cdiv(n, CH);
     const int64_t threads = chunks * (cfg->k / 4);
     const unsigned blocks = (unsigned) ctr_cdiv(threads, 256);
-#define LAUNCH_BP(KK)                                                                                                  \
-    embed_bwd_partials_kernel<KK><<<blocks, 256, 0, ctr_st(s)>>>(*cfg, sorted_keys, perm, uidx, n, field_of_slot, x0, dx0, \
+#define LAUNCH_BP(KK, ...)                                                                                             \
+    embed_bwd_partials_kernel<KK, ##__VA_ARGS__><<<blocks, 256, 0, ctr_st(s)>>>(*cfg, sorted_keys, perm, uidx, n, field_of_slot, x0, dx0, \
                                                                 dx0_ld, sum_e, dlogit, w_fm, inv_cnt_emb, inv_cnt_first,   \
                                                                 cont_grad, slot_weight, part)
+    // k = 16 (config 4): ONE lookup in flight per walker and 6 CTAs per SM (40 registers).  The 833 CTAs of a 64K batch then
+    // run as a single wave; with 4 lookups in flight (72 registers, 3 CTAs per SM) it was 1.9 waves of long serial walks:
+    // 85.7 -> 71.3 us in the step (profiles/r02l_partials_variants.txt).  CTR_BP_VARIANT=8 selects the old shape.
+    static int variant = -1;
+    if (variant < 0) {
+        const char* e = getenv("CTR_BP_VARIANT");
+        variant = e ? atoi(e) : 9;
+    }
     switch (cfg->k) {
         case 4: LAUNCH_BP(4); break;
         case 8: LAUNCH_BP(8); break;
-        case 16: LAUNCH_BP(16); break;
+        case 16:
+            if (variant == 8) LAUNCH_BP(16, 4, 3);
+            else if (variant == 4) LAUNCH_BP(16, 2, 4);
+            else LAUNCH_BP(16, 1, 6);
+            break;
         default: LAUNCH_BP(32); break;
     }
 #undef LAUNCH_BP
@@ -831,6 +845,8 @@ extern "C" int ctr_adam_rows(ctr_handle* h, ctr_stream s, const uint32_t* row_id
                      table_stride % 4 == 0 && grad_stride % 4 == 0 && aligned && (width == emb_k || grad_stride >= emb_k + 1);
     if (vec) {
         const int has_first = width == emb_k + 1;
+        // 64 registers, 4 CTAs per SM.  More CTAs per SM (48 / 40 / 32 registers: spills) and persistent grids were measured
+        // and are slower: 93.6 / 98.4 / 114.8 us against 83.7 (profiles/r02l_adam_rows_variants.txt)
         const unsigned grid = grid_for(h, n_max * (emb_k / 4));
 #define LAUNCH_AV(KK)                                                                                                         \
     adam_rows_vec_kernel<KK><<<grid, 256, 0, ctr_st(s)>>>(row_ids, n_rows, n_max, mask, grads, seg_start, grad_stride, has_first, \

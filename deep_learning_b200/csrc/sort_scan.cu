@@ -85,7 +85,12 @@ radix_scan_rows_kernel(uint32_t* __restrict__ hist, int nblk, uint32_t* __restri
 // table carries ranks across rounds, a cross-warp exclusive sum and a scan over the digits finish the tile-local
 // rank.  The tile is then ordered in shared memory and written out from there: consecutive threads store consecutive
 // positions of a digit's run, so a warp store touches a few sectors instead of 32.
-__global__ void __launch_bounds__(SORT_THREADS)
+// 6 CTAs per SM (40 registers, 36 KB of shared memory each): the 833 tiles of a 64K x 26 batch are then ONE wave; at the 62
+// registers the compiler takes unasked it was 4 per SM and a second, 40 %-full wave.  SORT_MINB is a build-time knob.
+#ifndef SORT_MINB
+#define SORT_MINB 6
+#endif
+__global__ void __launch_bounds__(SORT_THREADS, SORT_MINB)
 radix_scatter_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                      uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n, int shift,
                      const uint32_t* __restrict__ hist, const uint32_t* __restrict__ tot, int nblk) {
