@@ -365,8 +365,8 @@ __device__ __forceinline__ void epilogue_rows(uint32_t tmem_base, int ewarp, int
 // Tried and dropped: a transposition-free epilogue on tcgen05.ld.16x256b fragments (32-byte runs per thread quad, 64-bit
 // stores / mask loads) -- it frees the shared-memory port but the 8-sectors-per-instruction accesses made the
 // epilogue 1.5x (stores) to 2x (mask loads) slower.
-template <bool BIAS, bool RELU, int MASK, bool BITS_OUT, int EW>
-__device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp, int lane, int m0, int N, float* C,
+template <bool BIAS, bool RELU, int MASK, bool BITS_OUT, int EW, bool ROUND = true, bool MTAIL = false>
+__device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp, int lane, int m0, int M, int N, float* C,
                                                    int64_t ldc, const EpiParams& ep, float* stage, uint32_t sbias) {
     const int q = ewarp & 3, half = ewarp >> 2;
     const uint32_t tile = smem_u32(stage) + (uint32_t) (ewarp * EPI_TILE_FLOATS * 4);
@@ -374,6 +374,8 @@ __device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp
     const int nchunks = (N + 31) / 32;
     const int rsub = lane >> 3, cc = (lane & 7) * 4;
     const int row0 = m0 + q * 32 + rsub;
+    // MTAIL: rows row0 + 4 j, j < jmax, exist (the last tile of the matrix may be partial); else the tile is whole
+    const int jmax = !MTAIL ? 8 : (M - row0 >= 32 ? 8 : (M > row0 ? (M - row0 + 3) >> 2 : 0));
     const uint32_t st_addr = tile + (uint32_t) (lane * EPI_PITCH * 4);
     const uint32_t ld_addr = tile + (uint32_t) ((rsub * EPI_PITCH + cc) * 4);
     char* dst_row = reinterpret_cast<char*>(C + (int64_t) row0 * ldc + cc);
@@ -389,7 +391,7 @@ __device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp
         const char* mp = msk_row + (int64_t) c * 128;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            m[j] = ok ? ctr_ldg_f4_stream(reinterpret_cast<const float*>(mp)) : make_float4(0.f, 0.f, 0.f, 0.f);
+            m[j] = (ok && j < jmax) ? ctr_ldg_f4_stream(reinterpret_cast<const float*>(mp)) : make_float4(0.f, 0.f, 0.f, 0.f);
             mp += mstep;
         }
     };
@@ -435,13 +437,13 @@ __device__ __forceinline__ void epilogue_rows_fast(uint32_t tmem_base, int ewarp
                 v.z = (mbits & (4u << (4 * j))) ? v.z * scale : 0.f; v.w = (mbits & (8u << (4 * j))) ? v.w * scale : 0.f;
             }
             if (RELU) { v.x = cvt_tf32_relu(v.x); v.y = cvt_tf32_relu(v.y); v.z = cvt_tf32_relu(v.z); v.w = cvt_tf32_relu(v.w); }
-            else { v.x = cvt_tf32(v.x); v.y = cvt_tf32(v.y); v.z = cvt_tf32(v.z); v.w = cvt_tf32(v.w); }
+            else if (ROUND) { v.x = cvt_tf32(v.x); v.y = cvt_tf32(v.y); v.z = cvt_tf32(v.z); v.w = cvt_tf32(v.w); }
             if (BITS_OUT && col_ok) {
                 // the stored value is >= +0 after the ReLU, so "> 0" is "bit pattern != 0": min(u, 1) is the bit
                 obits |= (min(__float_as_uint(v.x), 1u) | (min(__float_as_uint(v.y), 1u) << 1) |
                           (min(__float_as_uint(v.z), 1u) << 2) | (min(__float_as_uint(v.w), 1u) << 3)) << (4 * j);
             }
-            if (col_ok && !(ep.dbg & 32)) {
+            if (col_ok && j < jmax && !(ep.dbg & 32)) {
                 if (ep.dbg & 128) __stcs(reinterpret_cast<float4*>(dp), v);       // experiment: streaming (evict-first) stores
                 else *reinterpret_cast<float4*>(dp) = v;
             }
@@ -550,14 +552,14 @@ __device__ __forceinline__ void epilogue_dispatch(uint32_t tmem_base, int ewarp,
     }
     // sign bits are written only behind a ReLU (the fast path's "bit pattern != 0" test relies on stored values >= +0)
     if (fast && !(ep.bits_out && !(ep.bias && ep.relu))) {
-        if (ep.bits_in) epilogue_rows_fast<false, false, 2, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
-        else if (ep.mask) epilogue_rows_fast<false, false, 1, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+        if (ep.bits_in) epilogue_rows_fast<false, false, 2, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+        else if (ep.mask) epilogue_rows_fast<false, false, 1, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
         else if (ep.bias && ep.relu && ep.bits_out)
-            epilogue_rows_fast<true, true, 0, true, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
-        else if (ep.bias && ep.relu) epilogue_rows_fast<true, true, 0, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
-        else if (ep.bias) epilogue_rows_fast<true, false, 0, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
-        else if (ep.relu) epilogue_rows_fast<false, true, 0, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
-        else epilogue_rows_fast<false, false, 0, false, EW>(tmem_base, ewarp, lane, m0, N, C, ldc, ep, stage, sbias);
+            epilogue_rows_fast<true, true, 0, true, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+        else if (ep.bias && ep.relu) epilogue_rows_fast<true, true, 0, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+        else if (ep.bias) epilogue_rows_fast<true, false, 0, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+        else if (ep.relu) epilogue_rows_fast<false, true, 0, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
+        else epilogue_rows_fast<false, false, 0, false, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
         return;
     }
     if (ep.bits_in) epilogue_rows<false, false, 2, EW>(tmem_base, ewarp, lane, m0, M, N, C, ldc, ep, stage, sbias);
@@ -1042,7 +1044,10 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_wait(&bars->tmem_full, 0);
             tc_fence_after();
             EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f, 0, 0, 0, 0, nullptr, nullptr, 0, 1, nullptr, nullptr, 0, 0};
-            epilogue_rows<false, false, 0, EW>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem), 0u);
+            if ((N & 3) == 0 && (reinterpret_cast<uintptr_t>(Cz) & 15) == 0)       // partial sums are NOT rounded to tf32
+                epilogue_rows_fast<false, false, 0, false, EW, false, true>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem), 0u);
+            else
+                epilogue_rows<false, false, 0, EW>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem), 0u);
         } else {                                   // empty slice: contribute zeros
             const int row = m0 + (warp & 3) * 32 + lane;
             if (row < M) for (int c = (warp >> 2); c < N; c += EW / 4) Cz[(size_t) row * N + c] = 0.f;
@@ -1051,6 +1056,126 @@ gemm_nt_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tc_fence_before();
     __syncthreads();
     if (warp == TMA_WARP) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+// ---- the same product on CTA pairs (cta_group::2): ONE M = 256 MMA spans the two CTAs of a cluster, CTA rank r stages
+// rows [(2p + r) * 128, +128) of A^T (its own 128 output rows) and HALF of every B tile.  Why: the one-CTA kernel above is
+// bound by what the SMs pull out of L2 (ncu r02k: 55.5 us, tensor pipe 52 %; every one of the 4 m-tiles streams all of dZ,
+// 525 MB of shared-memory fill per GEMM at the ~9.3 TB/s the L2 fabric delivers, profiles/r02j_probe_loads_vs_stores.txt).
+// Sharing B between the two SMs of a pair takes the fill to 315 MB.  N is covered by up to two MMAs per k-step (n1 + n2,
+// each a multiple of 64 so that a CTA's half is whole 32-column boxes); columns past N are zero-filled by TMA.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(nthreads(NT_EW), 1)
+gemm_nt_pair_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, int M, int N, int R,
+                    int r_per_split, int n1, int n2, int nstages, float* __restrict__ Cws, int dbg) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t) 1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    constexpr int BOX_BYTES = 32 * BLOCK_R * 4;             // 32 MN-elements x 32 reduction rows
+    const int nb1 = n1 / 64, nb2 = n2 / 64;                  // boxes of THIS CTA's half of each MMA's B tile
+    const int nbx = nb1 + nb2;
+    const int a_bytes = (BLOCK_M / 32) * BOX_BYTES;
+    const int stage_bytes = a_bytes + nbx * BOX_BYTES;
+    const int m0 = (int) blockIdx.x * BLOCK_M;               // blockIdx.x = 2 * pair + rank
+    const int r_lo = blockIdx.y * r_per_split;
+    const int r_hi = (r_lo + r_per_split < R) ? r_lo + r_per_split : R;
+    const int num_kb = r_hi > r_lo ? (r_hi - r_lo + BLOCK_R - 1) / BLOCK_R : 0;
+    constexpr int EW = NT_EW, TMA_WARP = EW, MMA_WARP = EW + 1;
+    constexpr uint32_t TMEM_COLS = 512;
+    const size_t pipe_bytes = pipe_region((size_t) nstages * stage_bytes, EW);
+    PipeBars* bars = reinterpret_cast<PipeBars*>(smem + pipe_bytes);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < nstages; ++s) {
+            mbar_init(&bars->full[s], 1);
+            mbar_init(&bars->empty[s], 1);
+        }
+        mbar_init(&bars->tmem_full, 1);
+        fence_barrier_init();
+    }
+    cluster_sync_all();                                      // both CTAs' barriers exist before anyone signals them
+    if (warp == TMA_WARP) tmem_alloc_pair(&bars->tmem_base, TMEM_COLS);
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = bars->tmem_base;
+
+    if (warp == TMA_WARP) {
+        // one box per lane (see the tn kernel's producer): 4 boxes of A, nbx of this CTA's B halves
+        const int nbox = BLOCK_M / 32 + nbx;
+        const unsigned active = (1u << nbox) - 1u;           // nbox <= 4 + 7
+        if (lane < nbox) {
+            if (lane == 0) {
+                prefetch_tmap(&tmA);
+                prefetch_tmap(&tmB);
+            }
+            // column of B this lane's box starts at: MMA 1 covers [0, n1), this CTA's half is [rank * n1 / 2, +n1 / 2);
+            // MMA 2 covers [n1, n1 + n2) likewise
+            int bcol = 0;
+            if (lane >= BLOCK_M / 32) {
+                const int j = lane - BLOCK_M / 32;
+                bcol = j < nb1 ? (int) rank * (n1 / 2) + j * 32 : n1 + (int) rank * (n2 / 2) + (j - nb1) * 32;
+            }
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % nstages;
+                const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
+                mbar_wait(&bars->empty[s], ph ^ 1u);           // my copy of the stage is free (multicast commit)
+                uint8_t* sa = smem + (size_t) s * stage_bytes;
+                if (rank == 0 && lane == 0) mbar_expect_tx(&bars->full[s], (dbg & 4) ? 0u : (uint32_t) (2 * stage_bytes));
+                __syncwarp(active);
+                if (dbg & 4) continue;
+                const uint32_t lbar = mapa_shared(smem_u32(&bars->full[s]), 0);
+                const int r0 = r_lo + kb * BLOCK_R;
+                if (lane < BLOCK_M / 32) tma_load_2d_pair(sa + lane * BOX_BYTES, &tmA, lbar, m0 + lane * 32, r0);
+                else tma_load_2d_pair(sa + lane * BOX_BYTES, &tmB, lbar, bcol, r0);
+            }
+        }
+    } else if (warp == MMA_WARP) {
+        if (rank == 0 && elect_one()) {
+            const uint32_t idesc1 = make_idesc(2 * BLOCK_M, n1, 1, 1);
+            const uint32_t idesc2 = make_idesc(2 * BLOCK_M, n2 > 0 ? n2 : 64, 1, 1);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % nstages;
+                const uint32_t ph = (uint32_t) (kb / nstages) & 1u;
+                mbar_wait(&bars->full[s], ph);
+                tc_fence_after();
+                const uint32_t a_base = smem_u32(smem + (size_t) s * stage_bytes);
+                const uint32_t b_base = a_base + a_bytes;
+#pragma unroll
+                for (int k = 0; k < BLOCK_R / UMMA_K; ++k) {
+                    if (dbg & 2) continue;
+                    const uint32_t koff = k * UMMA_K * 128;
+                    const uint64_t adesc = make_desc(a_base + koff, BOX_BYTES, 512, LAYOUT_SW128_BASE32B);
+                    const uint64_t bdesc1 = make_desc(b_base + koff, BOX_BYTES, 512, LAYOUT_SW128_BASE32B);
+                    umma_tf32_pair(tmem_base, adesc, bdesc1, idesc1, (kb | k) != 0 ? 1u : 0u);
+                    if (n2 > 0) {
+                        const uint64_t bdesc2 = make_desc(b_base + nb1 * BOX_BYTES + koff, BOX_BYTES, 512, LAYOUT_SW128_BASE32B);
+                        umma_tf32_pair(tmem_base + (uint32_t) n1, adesc, bdesc2, idesc2, (kb | k) != 0 ? 1u : 0u);
+                    }
+                }
+                umma_commit_pair(&bars->empty[s]);     // frees the stage in BOTH CTAs
+            }
+            umma_commit_pair(&bars->tmem_full);        // accumulators complete in both CTAs
+        }
+    } else {
+        float* Cz = Cws + (size_t) blockIdx.y * M * N;
+        if (num_kb > 0) {
+            mbar_wait(&bars->tmem_full, 0);
+            tc_fence_after();
+            EpiParams ep{nullptr, 0, 1.f, 0, nullptr, 0, 1.f, 0, 0, 0, 0, nullptr, nullptr, 0, 1, nullptr, nullptr, 0, 0};
+            if (m0 < M) {
+                if ((N & 3) == 0 && (reinterpret_cast<uintptr_t>(Cz) & 15) == 0)   // partial sums are NOT rounded to tf32
+                    epilogue_rows_fast<false, false, 0, false, EW, false, true>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem), 0u);
+                else
+                    epilogue_rows<false, false, 0, EW>(tmem_base, warp, lane, m0, M, N, Cz, N, ep, reinterpret_cast<float*>(smem), 0u);
+            }
+        } else {                                   // empty slice: contribute zeros
+            const int row = m0 + (warp & 3) * 32 + lane;
+            if (row < M) for (int c = (warp >> 2); c < N; c += EW / 4) Cz[(size_t) row * N + c] = 0.f;
+        }
+    }
+    tc_fence_before();
+    cluster_sync_all();                                   // neither CTA frees TMEM / exits while its peer still runs
+    if (warp == TMA_WARP) tmem_dealloc_pair(tmem_base, TMEM_COLS);
 }
 
 }  // namespace
@@ -1290,6 +1415,34 @@ NtPlan plan_nt(ctr_handle* h, int M, int N, int R) {
     return p;
 }
 
+// the CTA-pair form (gemm_nt_pair_kernel): pairs of m-tiles, B columns in MMAs of n1 + n2 (multiples of 64)
+NtPlan plan_nt_pair(ctr_handle* h, int M, int N, int R) {
+    NtPlan p;
+    const int NB = (int) ctr_align(N, 64);
+    p.n1 = NB > 256 ? 256 : NB;
+    p.n2 = NB - p.n1;
+    const int stage_bytes = (BLOCK_M / 32 + NB / 64) * 32 * BLOCK_R * 4;
+    p.nstages = pick_stages(stage_bytes);
+    p.mtiles = 2 * (int) ctr_cdiv(ctr_cdiv(M, BLOCK_M), 2);        // CTAs along x: whole pairs
+    int want = h->sm_count / p.mtiles;
+    if (want < 1) want = 1;
+    int64_t rps = ctr_align(ctr_cdiv(R, want), BLOCK_R);
+    if (rps < 4 * BLOCK_R) rps = 4 * BLOCK_R;
+    p.r_per_split = (int) rps;
+    p.splits = (int) ctr_cdiv(R, rps);
+    return p;
+}
+
+// CTR_WGRAD = pair (default) | single: which weight-gradient kernel runs (A/B)
+bool wgrad_pair() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("CTR_WGRAD");
+        v = (e && e[0] == 's') ? 0 : 1;
+    }
+    return v == 1;
+}
+
 // out[i] = sum over the splits; elements past n_main (the extra row produced by a ones column of X) go to `tail`
 __global__ void __launch_bounds__(256) tc_splitk_reduce(const float* __restrict__ ws, int splits, int64_t n, int64_t n_main,
                                                         float* __restrict__ out, float* __restrict__ tail) {
@@ -1336,7 +1489,9 @@ int ctr_tc_mlp_bwd_data(ctr_handle* h, cudaStream_t st, int B, int K, int N, con
 
 int64_t ctr_tc_bwd_weight_ws_bytes(ctr_handle* h, int B, int K, int N) {
     NtPlan p = plan_nt(h, K + 1, N, B);       // + 1: room for the dbias row of the ones-column form
-    return ctr_align((int64_t) p.splits * (K + 1) * N * 4, 256);
+    NtPlan q = plan_nt_pair(h, K + 1, N, B);
+    const int splits = p.splits > q.splits ? p.splits : q.splits;     // either kernel may run
+    return ctr_align((int64_t) splits * (K + 1) * N * 4, 256);
 }
 
 // dbias != nullptr: X carries a column of ones at index K_w (ldx > K_w), so the GEMM is run with K_w + 1 rows and
@@ -1346,7 +1501,8 @@ int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K_w, int N,
     CTR_REQUIRE(h, N <= MAX_N, "TF32 path: N=%d > %d not supported", N, MAX_N);
     const int K = K_w + (dbias ? 1 : 0);
     CTR_REQUIRE(h, ldx >= K, "TF32 wgrad: ones-column form needs ldx > K");
-    NtPlan p = plan_nt(h, K, N, B);
+    const bool pair = wgrad_pair() && B >= 4 * BLOCK_R;
+    NtPlan p = pair ? plan_nt_pair(h, K, N, B) : plan_nt(h, K, N, B);
     CTR_REQUIRE(h, p.nstages >= 2, "TF32 wgrad: tile does not fit shared memory");
     if (ws_bytes < (int64_t) p.splits * K * N * 4) return ctr_fail(h, CTR_E_WORKSPACE, "TF32 wgrad: ws too small");
     CUtensorMap tmA, tmB;
@@ -1354,17 +1510,26 @@ int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K_w, int N,
     if (rc) return rc;
     rc = make_map(h, &tmB, dZ, B, N, lddz, 32, BLOCK_R, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
     if (rc) return rc;
-    const int stage_bytes = (BLOCK_M / 32 + (p.n1 + p.n2) / 32) * 32 * BLOCK_R * 4;
-    const size_t smem = smem_total((size_t) p.nstages * stage_bytes, NT_EW);
     static bool attr_set = false;
     if (!attr_set) {
         CTR_CUDA(h, cudaFuncSetAttribute(gemm_nt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
+        CTR_CUDA(h, cudaFuncSetAttribute(gemm_nt_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT));
         attr_set = true;
     }
     dim3 grid((unsigned) p.mtiles, (unsigned) p.splits);
-    gemm_nt_kernel<<<grid, nthreads(NT_EW), smem, st>>>(tmA, tmB, K, N, B, p.r_per_split, p.n1, p.n2, p.nstages,
-                                                    tmem_cols_for(p.n1 + p.n2), (float*) ws, tma_lanes(), gemm_dbg());
-    CTR_CHECK_LAUNCH(h, "gemm_nt_kernel");
+    if (pair) {
+        const int stage_bytes = (BLOCK_M / 32 + (p.n1 + p.n2) / 64) * 32 * BLOCK_R * 4;
+        const size_t smem = smem_total((size_t) p.nstages * stage_bytes, NT_EW);
+        gemm_nt_pair_kernel<<<grid, nthreads(NT_EW), smem, st>>>(tmA, tmB, K, N, B, p.r_per_split, p.n1, p.n2, p.nstages, (float*) ws,
+                                                             gemm_dbg());
+        CTR_CHECK_LAUNCH(h, "gemm_nt_pair_kernel");
+    } else {
+        const int stage_bytes = (BLOCK_M / 32 + (p.n1 + p.n2) / 32) * 32 * BLOCK_R * 4;
+        const size_t smem = smem_total((size_t) p.nstages * stage_bytes, NT_EW);
+        gemm_nt_kernel<<<grid, nthreads(NT_EW), smem, st>>>(tmA, tmB, K, N, B, p.r_per_split, p.n1, p.n2, p.nstages,
+                                                        tmem_cols_for(p.n1 + p.n2), (float*) ws, tma_lanes(), gemm_dbg());
+        CTR_CHECK_LAUNCH(h, "gemm_nt_kernel");
+    }
     const int64_t n = (int64_t) K * N;
     tc_splitk_reduce<<<(unsigned) ctr_cdiv(n, 256), 256, 0, st>>>((const float*) ws, p.splits, n, (int64_t) K_w * N, dW, dbias);
     CTR_CHECK_LAUNCH(h, "tc_splitk_reduce");
