@@ -665,16 +665,19 @@ class CtrEngine:
         """samples the loss is a mean over (all ranks' batches when sharded)"""
         return B
 
-    def _reg_loss(self) -> torch.Tensor:
+    def _reg_loss(self, st: Optional[int] = None, ws: Optional[torch.Tensor] = None) -> torch.Tensor:
         """regulariser terms of the reported loss (models/deepfm.py:155-156, models/wdl.py:268-275,
-        models/dnn.py:88-90): one deterministic reduction per regulariser group of the flat buffer."""
-        s, st = self.spec, self._stream()
+        models/dnn.py:88-90): one deterministic reduction per regulariser group of the flat buffer.  `st` / `ws`: another
+        stream than the step's needs a workspace of its own (the torch arithmetic follows torch's current stream)."""
+        s = self.spec
+        st = self._stream() if st is None else st
+        ws = self.ws if ws is None else ws
         total = None
         for gi, mode, scale in ((1, 1, 0.5 * s.l2_reg), (2, 2, s.l2_reg)):
             a, b = self.groups[gi]
             if b > a:
                 out = self.reg_terms[gi:gi + 1]
-                self.h.call("ctr_reduce", st, ptr(self.theta[a:b]), b - a, mode, ptr(out), ptr(self.ws), self.ws.numel())
+                self.h.call("ctr_reduce", st, ptr(self.theta[a:b]), b - a, mode, ptr(out), ptr(ws), ws.numel())
                 total = out * scale if total is None else total + out * scale
         return total
 
@@ -749,6 +752,7 @@ class CtrEngine:
             h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
                    self.rows_local * s.table_stride, 0.0, 0.0, ptr(self.touched), s.table_stride, hp)
         # ---- dense side: Adam over the flat buffer + the GEMM-side weight copies, one launch ---------------------------
+        self._before_dense_update()
         h.call("ctr_dense_update", st, ptr(self.theta), ptr(self.m), ptr(self.v), ptr(self._dense_grad()), C.byref(self._dense_layout()), hp)
         self.beta1_power *= ADAM_BETA1
         self.beta2_power *= ADAM_BETA2
@@ -832,6 +836,7 @@ class CtrEngine:
         self._begin_dense_reduce()
         self._reduce_dense_grads()
         self._mark("dense_reduce")
+        self._before_dense_update()
         h.call("ctr_dense_update", st, ptr(self.theta), ptr(self.m), ptr(self.v), ptr(self._dense_grad()), C.byref(self._dense_layout()), hp)
         # the table is final (and, sharded, every peer past its gradient barrier) before anything that follows on the main
         # stream: the next step's gather, get_weights, a checkpoint
@@ -977,14 +982,17 @@ class CtrEngine:
         # prefetch would otherwise sit between this step's upload and its first kernel); it still STARTS early, since
         # it waits for ev_call and not for the forward
         self._prefetch_next(next_batch, ev_call)
-        reg = self._reg_loss()
         out = None
         if self.loss_is_early:
-            # the value is final once the head kernel has run: hand it to the host copy now, so a caller that reads
-            # every step's loss (last_loss()) waits for the forward pass only and queues the next step under the backward
-            out = self._publish_loss(reg)
-        self.backward_and_update(B)
-        if out is None:
+            # the value is final once the head kernel has run: the regulariser sums, the additions and the copy to the host
+            # go to the loss stream now, off the step's critical path (six small launches), and a caller that reads every
+            # step's loss (last_loss()) waits for the forward pass only and queues the next step under the backward
+            out = self._publish_loss(None, early=True)
+            self.backward_and_update(B)
+            self._main_stream().wait_event(self._loss_dev_done)     # the returned tensor is safe on the caller's stream
+        else:
+            reg = self._reg_loss()
+            self.backward_and_update(B)
             out = self._publish_loss(reg)
         self._end_step()
         self._mark("update")
@@ -996,27 +1004,51 @@ class CtrEngine:
         models (quirk Q6) add a loss term that the backward computes"""
         return not (self.spec.gathered_l2 and self.spec.l2_reg > 0)
 
-    def _publish_loss(self, reg) -> torch.Tensor:
-        loss = self._global_loss()
-        if reg is not None:
-            loss = loss + reg
+    def _publish_loss(self, reg, early: bool = False) -> torch.Tensor:
         main = self._main_stream()
         if self._loss_host is None:
             self._loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
             self._loss_stream = torch.cuda.Stream(device=self.dev)
             self._loss_events = [torch.cuda.Event(), torch.cuda.Event()]
-            self._loss_made = torch.cuda.Event()
+            self._loss_made, self._loss_dev_done = torch.cuda.Event(), torch.cuda.Event()
+            self._ws_reg = torch.zeros(1 << 16, dtype=torch.uint8, device=self.dev)
+        ls = self._loss_stream
         self._loss_slot ^= 1
-        self._loss_made.record(main)
-        self._loss_stream.wait_event(self._loss_made)
-        with torch.cuda.stream(self._loss_stream):
-            self._loss_host[self._loss_slot:self._loss_slot + 1].copy_(loss, non_blocking=True)
-        loss.record_stream(self._loss_stream)
-        self._loss_events[self._loss_slot].record(self._loss_stream)
+        if early:
+            # everything on the loss stream, behind the head kernel.  The regulariser reads the dense parameters: the dense
+            # update of this step waits for _loss_dev_done (backward_and_update)
+            self._loss_made.record(main)
+            ls.wait_event(self._loss_made)
+            with torch.cuda.stream(ls):
+                reg = self._reg_loss(ls.cuda_stream, self._ws_reg)
+                loss = self._global_loss()
+                if reg is not None:
+                    loss = loss + reg
+                self._loss_host[self._loss_slot:self._loss_slot + 1].copy_(loss, non_blocking=True)
+            self._loss_dev_done.record(ls)
+            self._loss_dev_pending = True
+            loss.record_stream(main)
+        else:
+            loss = self._global_loss()
+            if reg is not None:
+                loss = loss + reg
+            self._loss_made.record(main)
+            ls.wait_event(self._loss_made)
+            with torch.cuda.stream(ls):
+                self._loss_host[self._loss_slot:self._loss_slot + 1].copy_(loss, non_blocking=True)
+            loss.record_stream(ls)
+        self._loss_events[self._loss_slot].record(ls)
         return loss
 
     _loss_host = None
     _loss_slot = 0
+    _loss_dev_pending = False
+
+    def _before_dense_update(self) -> None:
+        """the loss stream's regulariser sums read the dense parameters the dense update rewrites"""
+        if self._loss_dev_pending:
+            self._main_stream().wait_event(self._loss_dev_done)
+            self._loss_dev_pending = False
 
     def last_loss(self) -> float:
         """The loss of the latest train_step as a host float (what `sess.run([loss, optimizer])` hands back,

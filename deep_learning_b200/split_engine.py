@@ -162,6 +162,7 @@ class SplitFmEngine(CtrEngine):
         if self.adam_mode == "tf_dense":
             h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
                    self.rows_local * s.table_stride, 0.0, 0.0, ptr(self.touched), s.table_stride, hp)
+        self._before_dense_update()
         h.call("ctr_dense_update", st, ptr(self.theta), ptr(self.m), ptr(self.v), ptr(self.grad), C.byref(self._dense_layout()), hp)
         self.beta1_power *= ADAM_BETA1
         self.beta2_power *= ADAM_BETA2
