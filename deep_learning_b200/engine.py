@@ -715,6 +715,9 @@ class CtrEngine:
         if self.bwd_overlap and s.ids_ld:
             self._backward_overlapped(B, cfg, dims, w_fm)
             return
+        if self.bwd_split and s.ids_ld:
+            self._backward_split(B, cfg, dims, w_fm)
+            return
         cur = 0
         for i in range(L - 1, -1, -1):
             k_, h_ = dims[i]
@@ -787,6 +790,65 @@ class CtrEngine:
 
     _on_sparse = False
     bwd_overlap = _BWD_OVERLAP      # (the sharded engine turns it off outside the peer-memory exchange)
+
+    bwd_split = False         # CTR_BWD_ORDER=split, sharded peer-memory engines only (opt-in: measured no faster)
+
+    def _backward_split(self, B: int, cfg, dims, w_fm) -> None:
+        """Backward of the sharded step, ONE stream, reordered:  dgrad L-1 .. dgrad 0 (-> dX0) | partials | gradient rows
+        stored into their owners' buffers | wgrad L-1 .. wgrad 0 | barrier | owner-side row update | dense update.
+        The idea: the stores over NVLink and the ranks' skew drain under the three weight-gradient GEMMs.  Measured at N = 2:
+        no gain (1.1007 vs 1.0968 ms), the barrier still costs 24 us behind the GEMMs -- kept as an opt-in A/B."""
+        s, st, h = self.spec, self._stream(), self.h
+        L = len(s.hidden)
+        ws, wsn = ptr(self.ws), self.ws.numel()
+        main = self._main_stream()
+        for i in range(L - 1, 0, -1):                      # dz[j] is dZ of layer L-1-j
+            j = L - 1 - i
+            k_, h_ = dims[i]
+            self._dgrad_hidden(st, B, i, k_, h_, self.dz[j], self.dz[j + 1])
+        if s.E:
+            h.call("ctr_mlp_bwd_data", st, self.prec, B, s.E, dims[0][1], ptr(self.dz[L - 1]), dims[0][1], ptr(self._wd(0)), None, 0,
+                   1.0, ptr(self.dx0), self.dx0_ld)
+        hp = self._adam_hp()
+        self._mark("mlp_bwd_data")
+        n = B * s.ids_ld + self.n_extra
+        main.wait_event(self.ev_sorted)
+        if self.n_extra:
+            main.wait_event(self.ev_cont)
+        h.call("ctr_embed_bwd_partials_weighted", st, cfg, ptr(self.keys), ptr(self.perm), ptr(self.uidx), n,
+               ptr(self.field_of_slot), ptr(self.x0), ptr(self.dx0), self.dx0_ld, ptr(self.sum_e), ptr(self.dlogit),
+               ptr(w_fm), ptr(self.inv_cnt_emb), ptr(self.inv_cnt_first), ptr(self.cont_grad), ptr(self.sw),
+               ptr(self.part))
+        self._mark("partials")
+        self._sparse_push(B, n)
+        self._mark("finalize")
+        for i in range(L - 1, -1, -1):
+            k_, h_ = dims[i]
+            x, ldx = (self.acts[i - 1], self.act_ld[i - 1]) if i > 0 else (self.x0, s.x0_ld)
+            h.call("ctr_mlp_bwd_weight", st, self.prec, B, k_, h_, ptr(x), ldx, ptr(self.dz[L - 1 - i]), h_,
+                   ptr(self._w(i, self.grad)), ptr(self._b(i, self.grad)), ws, wsn, 1)
+        self._mark("mlp_bwd_weight")
+        self._begin_dense_reduce()
+        self._sparse_apply(B, n, hp)
+        self._mark("sparse_update")
+        self._reduce_dense_grads()
+        self._mark("dense_reduce")
+        if self.adam_mode == "tf_dense" and s.optimizer != "ftrl":
+            h.call("ctr_adam_dense", st, ptr(self.table), ptr(self.m_table), ptr(self.v_table), None,
+                   self.rows_local * s.table_stride, 0.0, 0.0, ptr(self.touched), s.table_stride, hp)
+        self._before_dense_update()
+        h.call("ctr_dense_update", st, ptr(self.theta), ptr(self.m), ptr(self.v), ptr(self._dense_grad()), C.byref(self._dense_layout()), hp)
+        self.beta1_power *= ADAM_BETA1
+        self.beta2_power *= ADAM_BETA2
+        self.global_step += 1
+        self._steps_done += 1
+
+    def _sparse_push(self, B: int, n: int) -> None:
+        """first half of _sparse_update where it splits (sharded engines): gradient rows -> their owners"""
+
+    def _sparse_apply(self, B: int, n: int, hp: AdamHP) -> None:
+        """second half: the row update"""
+        self._sparse_update(B, n, hp)
 
     def _backward_overlapped(self, B: int, cfg, dims, w_fm) -> None:
         """Backward with the sparse side underneath the weight-gradient GEMMs.

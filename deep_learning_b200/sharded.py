@@ -121,6 +121,11 @@ class ShardedCtrEngine(CtrEngine):
             # torch.distributed collectives run on torch's CURRENT stream, not on the engine's sparse stream: the
             # overlapped backward order is only valid where the exchange is a kernel on the stream it is given
             self.bwd_overlap = False
+        # CTR_BWD_ORDER=split (peer-memory mode, opt-in): gradient rows are pushed BEFORE the weight-gradient GEMMs and applied
+        # behind them (CtrEngine._backward_split).  Parity-green on real peers, but no faster: 1.1007 against 1.0968 ms at
+        # N = 2 -- the barrier behind the GEMMs still costs 24 us, so it is not rank skew (profiles/r02m_bwd_split_n2.txt)
+        self.bwd_split = (self.exchange_mode == "peer" and self.train_mode and not self.bwd_overlap and
+                          os.environ.get("CTR_BWD_ORDER", "serial") == "split")
         self.peer_status = self.status[:2]      # [0] step barriers, [1] id-plan barriers: words of the engine's status array
         self._epoch, self._pepoch, self._sepoch, self._rows_dirty = 0, 0, 0, False
         if self.exchange_mode == "peer":
@@ -438,7 +443,11 @@ class ShardedCtrEngine(CtrEngine):
 
     # ---- backward: per-unique gradients -> all-to-all #3 -> owner sum in peer order -> Adam ------------------------
     def _sparse_update(self, B: int, n: int, hp: AdamHP) -> None:
-        s, st, h, sp, pl = self.spec, self._stream(), self.h, self.plan, self.cur
+        self._sparse_push(B, n)
+        self._sparse_apply(B, n, hp)
+
+    def _sparse_push(self, B: int, n: int) -> None:
+        s, st, h, pl = self.spec, self._stream(), self.h, self.cur
         # The second half of the next batch's id plan (key all-to-all, owner-side sort) needs its split sizes on the
         # host.  By now the whole forward + dense backward of THIS step is queued on the main stream, so the host wait
         # does not starve the GPU.  The position is fixed on purpose: the plan collectives run on their own
@@ -447,14 +456,19 @@ class ShardedCtrEngine(CtrEngine):
         if self._pending_exchange is not None:
             self._build_exchange(self._pending_exchange, self.side)
             self._pending_exchange = None
+        if self.exchange_mode == "peer":
+            # one gradient row per unique key, summed and stored straight into its owner's receive buffer (exchange #3)
+            h.call("ctr_embed_bwd_finalize_push", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
+                   ptr(self.part), C.byref(pl.route_g))
+            if not self.bwd_split:
+                self._mark("finalize")
+
+    def _sparse_apply(self, B: int, n: int, hp: AdamHP) -> None:
+        s, st, h, sp, pl = self.spec, self._stream(), self.h, self.plan, self.cur
         U, n_req = pl.U, pl.n_req
         if self.exchange_mode == "peer":
             if self.device_plan:
                 n_req = self._req_cap        # the device knows the real count (*o_nuniq); this only bounds the launch
-            # one gradient row per unique key, summed and stored straight into its owner's receive buffer (exchange #3)
-            h.call("ctr_embed_bwd_finalize_push", st, ptr(pl.seg_start), ptr(pl.n_unique), n, s.grad_width, self.wire,
-                   ptr(self.part), C.byref(pl.route_g))
-            self._mark("finalize")
             self._barrier(st)
             self._rows_dirty = False
             if not self._on_sparse:
