@@ -30,6 +30,7 @@ _BWD_OVERLAP = os.environ.get("CTR_BWD_ORDER", "serial") == "overlap"
 from .spec import ModelSpec
 
 ADAM_BETA1, ADAM_BETA2, ADAM_EPS = 0.9, 0.999, 1e-8   # tf.train.AdamOptimizer defaults (models/deepfm.py:161)
+_LOSS_STREAM_MIN_BATCH = 4096          # below it a step is launch-bound: the loss stream's events cost more than they hide
 FTRL_INIT_ACCUM = 0.1                                 # tf.train.FtrlOptimizer default (test_model/wdl.py:136)
 PREC = {"fp32": 0, "tf32": 1}
 _ALIGN = 64   # floats; keeps every dense parameter 256-byte aligned inside the flat buffer
@@ -1053,8 +1054,16 @@ class CtrEngine:
             self.backward_and_update(B)
             self._main_stream().wait_event(self._loss_dev_done)     # the returned tensor is safe on the caller's stream
         else:
-            reg = self._reg_loss()
-            self.backward_and_update(B)
+            # the loss itself arrives late (sharded: with the gradient all-reduce), but its regulariser terms depend on the
+            # parameters only: they are summed on the loss stream now, off the step's main stream (small batches: the step
+            # is launch-bound and the extra stream costs more host time than it hides)
+            if self.Bmax >= _LOSS_STREAM_MIN_BATCH:
+                reg = self._reg_loss_on_loss_stream()
+                self.backward_and_update(B)
+                self._main_stream().wait_event(self._loss_dev_done)
+            else:
+                reg = self._reg_loss()
+                self.backward_and_update(B)
             out = self._publish_loss(reg)
         self._end_step()
         self._mark("update")
@@ -1064,16 +1073,34 @@ class CtrEngine:
     def loss_is_early(self) -> bool:
         """sharded engines: the global loss comes back with the gradient all-reduce, after the backward; the gathered-l2
         models (quirk Q6) add a loss term that the backward computes"""
-        return not (self.spec.gathered_l2 and self.spec.l2_reg > 0)
+        return not (self.spec.gathered_l2 and self.spec.l2_reg > 0) and self.Bmax >= _LOSS_STREAM_MIN_BATCH
 
-    def _publish_loss(self, reg, early: bool = False) -> torch.Tensor:
-        main = self._main_stream()
+    def _loss_stream_init(self) -> None:
         if self._loss_host is None:
             self._loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
             self._loss_stream = torch.cuda.Stream(device=self.dev)
             self._loss_events = [torch.cuda.Event(), torch.cuda.Event()]
             self._loss_made, self._loss_dev_done = torch.cuda.Event(), torch.cuda.Event()
             self._ws_reg = torch.zeros(1 << 16, dtype=torch.uint8, device=self.dev)
+
+    def _reg_loss_on_loss_stream(self):
+        """regulariser sums on the loss stream, behind everything queued on the main stream so far; the dense update of this
+        step waits for them (_before_dense_update), and so must whoever reads the result on another stream"""
+        self._loss_stream_init()
+        main, ls = self._main_stream(), self._loss_stream
+        self._loss_made.record(main)
+        ls.wait_event(self._loss_made)
+        with torch.cuda.stream(ls):
+            reg = self._reg_loss(ls.cuda_stream, self._ws_reg)
+        self._loss_dev_done.record(ls)
+        self._loss_dev_pending = True
+        if reg is not None:
+            reg.record_stream(main)
+        return reg
+
+    def _publish_loss(self, reg, early: bool = False) -> torch.Tensor:
+        main = self._main_stream()
+        self._loss_stream_init()
         ls = self._loss_stream
         self._loss_slot ^= 1
         if early:
