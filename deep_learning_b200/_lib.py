@@ -78,6 +78,7 @@ _P_LAY = C.POINTER(DenseLayout)
 # except the handle-management ones.  Kept in header order.
 _PROTOS = {
     "ctr_abi_version": (c_i32, None),
+    "ctr_source_hash": (C.c_char_p, None),
     "ctr_sizeof_embed_cfg": (c_i32, None),
     "ctr_create": (c_i32, [c_i32, C.POINTER(c_vp)]),
     "ctr_destroy": (c_i32, [c_vp]),
@@ -188,6 +189,15 @@ def load(path: str = LIB_PATH) -> C.CDLL:
         raise CtrError("ABI version mismatch")
     if lib.ctr_sizeof_embed_cfg() != C.sizeof(EmbedCfg):
         raise CtrError("ctr_embed_cfg layout mismatch")
+    # the binary must be the one these sources build (a stale .so with fresh timestamps would otherwise go unnoticed);
+    # CTR_ALLOW_STALE_LIB=1 for a deployment that ships the library without csrc/
+    if path == LIB_PATH and os.environ.get("CTR_ALLOW_STALE_LIB") != "1":
+        from . import build as _build
+        if os.path.isdir(_build.CSRC):
+            want, have = _build.source_hash(), lib.ctr_source_hash().decode()
+            if want != have:
+                raise CtrError("libctr_b200.so was built from other sources (library %s..., sources %s...): rebuild with "
+                               "`python -m deep_learning_b200.build`" % (have[:12], want[:12]))
     _lib = lib
     return lib
 

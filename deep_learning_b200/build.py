@@ -4,6 +4,7 @@
 """
 from __future__ import annotations
 
+import hashlib
 import os
 import subprocess
 import sys
@@ -32,14 +33,41 @@ def sources():
     return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu"))
 
 
-def _deps_mtime() -> float:
-    paths = sources() + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
-    paths += [os.path.join(INCLUDE, "ctr_b200.h"), os.path.abspath(__file__)]
-    return max(os.path.getmtime(p) for p in paths)
+def _dep_paths():
+    paths = sources() + sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h")))
+    return paths + [os.path.join(INCLUDE, "ctr_b200.h")]
+
+
+def source_hash() -> str:
+    """SHA-256 over the names and contents of every source the library is built from, and the compiler flags"""
+    h = hashlib.sha256()
+    h.update(" ".join(NVCC_FLAGS).encode())
+    for p in _dep_paths():
+        h.update(os.path.basename(p).encode() + b"\0")
+        with open(p, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
+_MARK = b"CTR_SOURCE_HASH="
+
+
+def library_hash(path: str = LIB_PATH):
+    """the hash recorded in the built library (read out of the file, which is not loaded), or None"""
+    if not os.path.exists(path):
+        return None
+    with open(path, "rb") as f:
+        data = f.read()
+    i = data.find(_MARK)
+    if i < 0:
+        return None
+    j = data.find(b"\0", i)
+    return data[i + len(_MARK):j].decode("ascii", "replace")
 
 
 def needs_build() -> bool:
-    return not os.path.exists(LIB_PATH) or os.path.getmtime(LIB_PATH) < _deps_mtime()
+    """by content, not by timestamp: a checkout or a copied tree changes mtimes either way"""
+    return library_hash() != source_hash()
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
@@ -47,7 +75,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         return LIB_PATH
     os.makedirs(OBJ_DIR, exist_ok=True)
     nvcc = _nvcc()
-    flags = list(NVCC_FLAGS)
+    flags = list(NVCC_FLAGS) + ['-DCTR_SOURCE_HASH="%s"' % source_hash()]
 
     def compile_one(src: str) -> str:
         obj = os.path.join(OBJ_DIR, os.path.basename(src)[:-3] + ".o")

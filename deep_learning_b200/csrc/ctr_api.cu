@@ -2,6 +2,15 @@
 #include "ctr_common.cuh"
 
 extern "C" int ctr_abi_version(void) { return CTR_ABI_VERSION; }
+
+// SHA-256 of the sources this library was built from (deep_learning_b200/build.py passes it in; the marker in front lets
+// the build script read it out of the file without loading it).  The loader compares it with the sources next to it: a
+// stale binary with fresh timestamps does not go unnoticed.
+#ifndef CTR_SOURCE_HASH
+#define CTR_SOURCE_HASH "unknown"
+#endif
+static const char g_source_hash[] = "CTR_SOURCE_HASH=" CTR_SOURCE_HASH;
+extern "C" const char* ctr_source_hash(void) { return g_source_hash + 16; }
 extern "C" int ctr_sizeof_embed_cfg(void) { return (int) sizeof(ctr_embed_cfg); }
 
 // Scratch of ctr_reduce_static: the block partials of one reduction, in device memory that exists from the moment the

@@ -91,6 +91,10 @@ typedef struct ctr_embed_cfg {
 
 /* ---- handle ------------------------------------------------------------------------- */
 int  ctr_abi_version(void);
+/* hex SHA-256 of the sources (csrc, this header, compiler flags) the library was built from, "unknown" for a build that
+ * did not go through deep_learning_b200/build.py; the Python loader refuses a library whose hash differs from the sources
+ * beside it (no counterpart in the reference: a build-hygiene hook) */
+const char* ctr_source_hash(void);
 int  ctr_sizeof_embed_cfg(void);
 int  ctr_create(int device, ctr_handle** out);
 int  ctr_destroy(ctr_handle* h);

@@ -131,3 +131,24 @@ def test_no_undefined_names_in_files_that_only_run_on_the_gpu_box():
         if used - bound:
             bad[os.path.relpath(f, root)] = sorted(used - bound)
     assert not bad, bad
+
+
+def test_library_records_the_hash_of_its_sources():
+    """the built library carries the SHA-256 of csrc/ + the header + the compiler flags (build.py), readable both from
+    the file and through ctr_source_hash()"""
+    from deep_learning_b200 import build, _lib
+    assert build.library_hash() == build.source_hash()
+    assert _lib.load().ctr_source_hash().decode() == build.source_hash()
+    assert not build.needs_build()
+
+
+def test_stale_library_is_refused(monkeypatch):
+    """a library built from other sources than the ones beside it does not load (no silent stale binary)"""
+    import pytest
+    from deep_learning_b200 import build, _lib
+    monkeypatch.setattr(_lib, "_lib", None)
+    monkeypatch.setattr(build, "source_hash", lambda: "0" * 64)
+    with pytest.raises(_lib.CtrError, match="built from other sources"):
+        _lib.load()
+    monkeypatch.setenv("CTR_ALLOW_STALE_LIB", "1")
+    assert _lib.load() is not None
