@@ -56,6 +56,8 @@ def run(comm, alg="deepfm", adam_mode="lazy"):
     p = O.init_params(alg, hp, seed=2019, dtype=torch.float64)
     st = O.adam_init(p)
     eng = ShardedCtrEngine(spec, Bl, group=group, learning_rate=hp.learning_rate, precision="fp32", adam_mode=adam_mode)
+    if os.environ.get("CTR_BWD_ORDER") == "split" and eng.exchange_mode == "peer":
+        assert eng.bwd_split, "CTR_BWD_ORDER=split did not select the split backward order"
     eng.set_weights({k: v.numpy() for k, v in p.items()})
     back = eng.get_weights()
     for n in p:      # shards re-assemble to the injected tables bit-exactly

@@ -20,3 +20,14 @@ def test_sharded_step_world_n_on_one_gpu(world, alg, adam_mode, capsys):
     out = LoopbackWorld(world).run(lambda comm: mgpu_parity.run(comm, alg, adam_mode))
     assert out == [True] * world
     assert "MGPU PARITY OK" in capsys.readouterr().out
+
+
+@pytest.mark.parametrize("world,alg,adam_mode", [(2, "deepfm", "lazy"), (4, "deepfm", "tf_dense")])
+def test_sharded_step_split_backward_order(world, alg, adam_mode, capsys, monkeypatch):
+    """CTR_BWD_ORDER=split (opt-in): the gradient rows are pushed ahead of the weight-gradient GEMMs, barrier and owner-side
+    update run behind them (CtrEngine._backward_split) -- same results as the plain order"""
+    from deep_learning_b200.comm import LoopbackWorld
+    monkeypatch.setenv("CTR_BWD_ORDER", "split")
+    out = LoopbackWorld(world).run(lambda comm: mgpu_parity.run(comm, alg, adam_mode))
+    assert out == [True] * world
+    assert "MGPU PARITY OK" in capsys.readouterr().out
