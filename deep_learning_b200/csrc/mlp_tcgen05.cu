@@ -1501,7 +1501,9 @@ int ctr_tc_mlp_bwd_weight(ctr_handle* h, cudaStream_t st, int B, int K_w, int N,
     CTR_REQUIRE(h, N <= MAX_N, "TF32 path: N=%d > %d not supported", N, MAX_N);
     const int K = K_w + (dbias ? 1 : 0);
     CTR_REQUIRE(h, ldx >= K, "TF32 wgrad: ones-column form needs ldx > K");
-    const bool pair = wgrad_pair() && B >= 4 * BLOCK_R;
+    // CTA pairs only where there are at least two real m-tiles to pair (with one, the second CTA of the pair would idle and the
+    // one-CTA kernel has twice the batch splits)
+    const bool pair = wgrad_pair() && B >= 4 * BLOCK_R && K > BLOCK_M;
     NtPlan p = pair ? plan_nt_pair(h, K, N, B) : plan_nt(h, K, N, B);
     CTR_REQUIRE(h, p.nstages >= 2, "TF32 wgrad: tile does not fit shared memory");
     if (ws_bytes < (int64_t) p.splits * K * N * 4) return ctr_fail(h, CTR_E_WORKSPACE, "TF32 wgrad: ws too small");
