@@ -30,7 +30,12 @@ _BWD_OVERLAP = os.environ.get("CTR_BWD_ORDER", "serial") == "overlap"
 from .spec import ModelSpec
 
 ADAM_BETA1, ADAM_BETA2, ADAM_EPS = 0.9, 0.999, 1e-8   # tf.train.AdamOptimizer defaults (models/deepfm.py:161)
-_LOSS_STREAM_MIN_BATCH = 4096          # below it a step is launch-bound: the loss stream's events cost more than they hide
+def _loss_stream_min_batch() -> int:
+    """below it a step is launch-bound: the loss stream's events cost more than they hide (CTR_LOSS_STREAM_MIN_BATCH: tests
+    lower it to run the loss-stream paths on small batches)"""
+    return int(os.environ.get("CTR_LOSS_STREAM_MIN_BATCH", 4096))
+
+
 FTRL_INIT_ACCUM = 0.1                                 # tf.train.FtrlOptimizer default (test_model/wdl.py:136)
 PREC = {"fp32": 0, "tf32": 1}
 _ALIGN = 64   # floats; keeps every dense parameter 256-byte aligned inside the flat buffer
@@ -1057,7 +1062,7 @@ class CtrEngine:
             # the loss itself arrives late (sharded: with the gradient all-reduce), but its regulariser terms depend on the
             # parameters only: they are summed on the loss stream now, off the step's main stream (small batches: the step
             # is launch-bound and the extra stream costs more host time than it hides)
-            if self.Bmax >= _LOSS_STREAM_MIN_BATCH:
+            if self.Bmax >= _loss_stream_min_batch():
                 reg = self._reg_loss_on_loss_stream()
                 self.backward_and_update(B)
                 self._main_stream().wait_event(self._loss_dev_done)
@@ -1073,7 +1078,7 @@ class CtrEngine:
     def loss_is_early(self) -> bool:
         """sharded engines: the global loss comes back with the gradient all-reduce, after the backward; the gathered-l2
         models (quirk Q6) add a loss term that the backward computes"""
-        return not (self.spec.gathered_l2 and self.spec.l2_reg > 0) and self.Bmax >= _LOSS_STREAM_MIN_BATCH
+        return not (self.spec.gathered_l2 and self.spec.l2_reg > 0) and self.Bmax >= _loss_stream_min_batch()
 
     def _loss_stream_init(self) -> None:
         if self._loss_host is None:

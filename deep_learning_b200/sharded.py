@@ -143,7 +143,9 @@ class ShardedCtrEngine(CtrEngine):
             self._req_off = [r0, r0 + _ru(self._req_cap * 4, 256)]
             self._dense_off = self._req_off[1] + _ru(self._req_cap * 4, 256)
             n_dense = self.n_dense + _ALIGN
-            self.slab = PeerSlab(self.h, self._dense_off + _ru((n_dense if self.train_mode else 1) * 4, 256), self.comm, dev)
+            # last 256 bytes: this rank's share of the step's loss, two slots of 4 floats (read by every peer, early loss)
+            self._loss_off = self._dense_off + _ru((n_dense if self.train_mode else 1) * 4, 256)
+            self.slab = PeerSlab(self.h, self._loss_off + 256, self.comm, dev)
             self.rows_recv = self.slab.tensor(self._rows_off, (self.n_max + 1, self.wire))
             self.g_recv = self.slab.tensor(self._g_off, (max(self._g_cap, 1), self.wire)) if self.train_mode else None
             self._rt0 = self.slab.route([0] * W, [0] * W, 0)
@@ -156,6 +158,10 @@ class ShardedCtrEngine(CtrEngine):
                 self.grad_red = torch.zeros(n_dense, **f32)
                 self._rt_dense = self.slab.route([0] * W, [0] * W, self._dense_off)
                 self.ev_bar, self.ev_red = torch.cuda.Event(), torch.cuda.Event()
+                self._loss_slab = self.slab.tensor(self._loss_off, (8,))
+                self._rt_loss = [self.slab.route([0] * W, [0] * W, self._loss_off + 16 * sl) for sl in range(2)]
+                self._loss_red = torch.zeros(4, **f32)
+                self._loss_step = 0
         else:
             self.rows_recv = torch.zeros(self.n_max + 1, self.wire, **f32)
         self.plans = [_IdPlan(self, 0), _IdPlan(self, 1)]
@@ -496,9 +502,11 @@ class ShardedCtrEngine(CtrEngine):
                self.wire, s.row_width, ptr(self.table), ptr(self.m_table), ptr(self.v_table), s.table_stride,
                self.rows_local, ptr(self.touched), None, 0, self._fm_w2(), s.k, hp)
 
-    def _barrier(self, st: int) -> None:
-        """all ranks: everything stored into peer slabs so far is visible, and every peer is at the same point"""
-        if self._on_sparse:          # issued from the sparse stream (overlapped backward): its own words and epoch
+    def _barrier(self, st: int, third_set: bool = False) -> None:
+        """all ranks: everything stored into peer slabs so far is visible, and every peer is at the same point.
+        third_set: the barrier of the early loss on the loss stream (the words the overlapped backward's sparse stream uses;
+        the two are never active in the same engine)"""
+        if self._on_sparse or third_set:          # its own words and epoch: can be in flight beside a step barrier
             self._sepoch += 1
             flags, epoch = self._sflags_off, self._sepoch
         else:
@@ -567,10 +575,26 @@ class ShardedCtrEngine(CtrEngine):
             self._dense_work.wait()          # stream-side wait: the main stream continues behind the collective
             self._dense_work = None
 
-    loss_is_early = False      # the global loss comes back with the gradient all-reduce
+    @property
+    def loss_is_early(self) -> bool:
+        """Peer-memory mode: every rank leaves its share of the loss in its slab right behind the head kernel, and the
+        loss stream sums the shares out of peer memory in rank order (the dense-gradient mechanism on 16 bytes) -- so the
+        host gets the global loss after the forward pass, as on one GPU.  Otherwise the loss comes back with the gradient
+        all-reduce, after the backward.  CTR_EARLY_LOSS=0 switches it off."""
+        return (self.exchange_mode == "peer" and self.train_mode and self.world > 1 and not self.bwd_overlap and
+                CtrEngine.loss_is_early.fget(self) and os.environ.get("CTR_EARLY_LOSS", "1") != "0")
 
     def _global_loss(self) -> torch.Tensor:
-        return self._dense_grad()[self.n_dense:self.n_dense + 1].clone()
+        if not self.loss_is_early:
+            return self._dense_grad()[self.n_dense:self.n_dense + 1].clone()
+        # runs on torch's current stream = the loss stream (_publish_loss), behind the head kernel
+        ls = torch.cuda.current_stream(self.dev)
+        slot = self._loss_step & 1
+        self._loss_step += 1
+        self._loss_slab[4 * slot:4 * slot + 1].copy_(self.loss)
+        self._barrier(ls.cuda_stream, third_set=True)
+        self.h.call("ctr_peer_reduce_sum", ls.cuda_stream, C.byref(self._rt_loss[slot]), 4, ptr(self._loss_red))
+        return self._loss_red[0:1].clone()
 
     def predict(self, batch: Optional[Dict] = None) -> torch.Tensor:
         out = super().predict(batch)

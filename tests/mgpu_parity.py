@@ -134,7 +134,10 @@ def run(comm, alg="deepfm", adam_mode="lazy"):
     for i in range(steps):
         glob = {k: torch.cat([b[k] for b in seq[i]], dim=0) for k in seq[i][0]}
         loss_ref, p = O.train_step(alg, p, st, H.oracle_batch(glob, torch.float64), hp, adam_mode=adam_mode)
-        loss = float(eng.train_step(seq[i][rank], next_batch=seq[i + 1][rank]).item())
+        lt = eng.train_step(seq[i][rank], next_batch=seq[i + 1][rank])
+        early = eng.last_loss()                       # the host float of this step (early in peer mode, see last_loss)
+        loss = float(lt.item())
+        assert early == loss, ("last_loss != returned loss", early, loss)
         assert abs(loss - float(loss_ref)) < 1e-4 * max(1.0, abs(float(loss_ref))), ("prefetch step", i, loss, float(loss_ref))
     got = eng.get_weights()
     for n in p:

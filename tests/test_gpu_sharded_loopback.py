@@ -31,3 +31,15 @@ def test_sharded_step_split_backward_order(world, alg, adam_mode, capsys, monkey
     out = LoopbackWorld(world).run(lambda comm: mgpu_parity.run(comm, alg, adam_mode))
     assert out == [True] * world
     assert "MGPU PARITY OK" in capsys.readouterr().out
+
+
+@pytest.mark.parametrize("world,alg,adam_mode", [(2, "deepfm", "lazy"), (8, "deepfm", "lazy"), (3, "dnn", "lazy")])
+def test_sharded_step_early_global_loss(world, alg, adam_mode, capsys, monkeypatch):
+    """peer-memory mode hands the GLOBAL loss to the host right behind the forward pass (each rank's share summed out of the
+    peers' slabs in rank order on the loss stream).  The batches of the parity body are small, so the batch-size threshold
+    of the loss stream is lowered; the body checks last_loss() == the returned loss == the oracle's, step after step."""
+    from deep_learning_b200.comm import LoopbackWorld
+    monkeypatch.setenv("CTR_LOSS_STREAM_MIN_BATCH", "1")
+    out = LoopbackWorld(world).run(lambda comm: mgpu_parity.run(comm, alg, adam_mode))
+    assert out == [True] * world
+    assert "MGPU PARITY OK" in capsys.readouterr().out
