@@ -1105,38 +1105,38 @@ class CtrEngine:
 
     def _publish_loss(self, reg, early: bool = False) -> torch.Tensor:
         main = self._main_stream()
-        self._loss_stream_init()
-        ls = self._loss_stream
-        self._loss_slot ^= 1
-        if early:
-            # everything on the loss stream, behind the head kernel.  The regulariser reads the dense parameters: the dense
-            # update of this step waits for _loss_dev_done (backward_and_update)
-            self._loss_made.record(main)
-            ls.wait_event(self._loss_made)
-            with torch.cuda.stream(ls):
-                reg = self._reg_loss(ls.cuda_stream, self._ws_reg)
-                loss = self._global_loss()
-                if reg is not None:
-                    loss = loss + reg
-                self._loss_host[self._loss_slot:self._loss_slot + 1].copy_(loss, non_blocking=True)
-            self._loss_dev_done.record(ls)
-            self._loss_dev_pending = True
-            loss.record_stream(main)
-        else:
+        if not early:
+            # the value exists only after the backward: nothing to hide, so no extra stream work (a launch-bound small-batch
+            # step would pay ~30 us of host time for it); last_loss() reads the tensor
             loss = self._global_loss()
             if reg is not None:
                 loss = loss + reg
-            self._loss_made.record(main)
-            ls.wait_event(self._loss_made)
-            with torch.cuda.stream(ls):
-                self._loss_host[self._loss_slot:self._loss_slot + 1].copy_(loss, non_blocking=True)
-            loss.record_stream(ls)
+            self._loss_tensor = loss
+            return loss
+        self._loss_tensor = None
+        self._loss_stream_init()
+        ls = self._loss_stream
+        self._loss_slot ^= 1
+        # everything on the loss stream, behind the head kernel.  The regulariser reads the dense parameters: the dense
+        # update of this step waits for _loss_dev_done (backward_and_update)
+        self._loss_made.record(main)
+        ls.wait_event(self._loss_made)
+        with torch.cuda.stream(ls):
+            reg = self._reg_loss(ls.cuda_stream, self._ws_reg)
+            loss = self._global_loss()
+            if reg is not None:
+                loss = loss + reg
+            self._loss_host[self._loss_slot:self._loss_slot + 1].copy_(loss, non_blocking=True)
+        self._loss_dev_done.record(ls)
+        self._loss_dev_pending = True
+        loss.record_stream(main)
         self._loss_events[self._loss_slot].record(ls)
         return loss
 
     _loss_host = None
     _loss_slot = 0
     _loss_dev_pending = False
+    _loss_tensor = None        # late-loss steps: the returned tensor itself (last_loss() reads it)
 
     def _before_dense_update(self) -> None:
         """the loss stream's regulariser sums read the dense parameters the dense update rewrites"""
@@ -1148,6 +1148,8 @@ class CtrEngine:
         """The loss of the latest train_step as a host float (what `sess.run([loss, optimizer])` hands back,
         models/deepfm.py:181).  Waits for that value's device-to-host copy only -- on one GPU the loss is final after the
         forward pass -- and not for the rest of the step, unlike `.item()` on the returned tensor."""
+        if self._loss_tensor is not None:
+            return float(self._loss_tensor.item())
         if self._loss_host is None:
             raise _lib.CtrError("last_loss: no train_step has run")
         self._loss_events[self._loss_slot].synchronize()
@@ -1181,6 +1183,31 @@ class CtrEngine:
         """`sess.run("score:0")` (models/deepfm.py:250): scores [B] on the device."""
         B = self.load_batch(batch) if batch is not None else self.last_batch
         self.forward(B, with_loss=False)
+        return self.score[:B]
+
+    _pred_graphs = None
+
+    def predict_graphed(self, batch: Dict) -> torch.Tensor:
+        """`predict` with the forward pass replayed from a CUDA graph (one graph per batch size, captured on first use):
+        for small serving batches the ~10 launches of a predict are host time, not GPU time (config 5 at B = 1K: 95 us per
+        call launched one by one).  Same kernels, same results; single-GPU engines (the sharded forward plans ids on the
+        host side of the step).  The batch is copied into input set 0 outside the graph."""
+        if self.world > 1:
+            raise _lib.CtrError("predict_graphed is single-GPU")
+        self._use_inputs(0)
+        self._pf_id = self._pf_obj = None
+        B = self.load_batch(batch)
+        if self._pred_graphs is None:
+            self._pred_graphs = {}
+        g = self._pred_graphs.get(B)
+        if g is None:
+            self.forward(B, with_loss=False)               # warm-up: one-time attribute settings happen outside the capture
+            torch.cuda.current_stream(self.dev).synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.forward(B, with_loss=False)
+            self._pred_graphs[B] = g
+        g.replay()
         return self.score[:B]
 
     def auc(self, scores: torch.Tensor, labels: torch.Tensor) -> float:

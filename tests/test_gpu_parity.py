@@ -492,3 +492,26 @@ def _run_parity_split(hp, steps, adam_mode):
         p = O.to_dtype(O.to_dtype(p, torch.float32), torch.float64)
         st.m = O.to_dtype(O.to_dtype(st.m, torch.float32), torch.float64)
         st.v = O.to_dtype(O.to_dtype(st.v, torch.float32), torch.float64)
+
+
+@pytest.mark.parametrize("alg,prec", [("deepfm", "tf32"), ("deepfm_multi", "fp32"), ("wdl", "tf32")])
+def test_predict_graphed_equals_predict(alg, prec):
+    """CtrEngine.predict_graphed (forward pass replayed from a CUDA graph, one per batch size) returns predict()'s scores
+    bit for bit, for two batch sizes and again after the weights changed"""
+    from deep_learning_b200.engine import CtrEngine
+    from deep_learning_b200.spec import spec_from_hparams
+    hp = H.hp_multi(B=512) if alg == "deepfm_multi" else H.hp_criteo(B=512, rows=4000)
+    spec = spec_from_hparams(alg, hp)
+    p = O.init_params(alg, hp, dtype=torch.float64)
+    eng = CtrEngine(spec, 512, precision=prec, train=False)
+    eng.set_weights({n: v.float().numpy() for n, v in p.items()})
+    for seed, B in ((1, 512), (2, 200), (3, 512)):
+        b = H.make_batch(alg, hp, seed=seed, B=B)
+        a = eng.predict(b).clone()
+        g = eng.predict_graphed(b).clone()
+        assert torch.equal(a, g), (alg, B)
+        assert a.shape[0] == B and torch.isfinite(a).all()
+    p2 = {n: (v * 1.01).float().numpy() for n, v in p.items()}
+    eng.set_weights(p2)
+    b = H.make_batch(alg, hp, seed=4, B=512)
+    assert torch.equal(eng.predict(b).clone(), eng.predict_graphed(b).clone())
