@@ -128,7 +128,8 @@ _PROTOS = {
     "ctr_dense_update": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, _P_LAY, _P_HP]),
     "ctr_cont_bwd_ws_bytes": (c_i64, [c_vp, _P_CFG]),
     "ctr_fm_cont_bwd": (c_i32, [c_vp, c_vp, _P_CFG, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64]),
-    "ctr_scalar_segment_add": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i32, c_i64, c_vp]),
+    "ctr_scalar_segment_add": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i32, c_i64, c_vp, c_vp, c_i64]),
+    "ctr_scalar_segment_add_ws_bytes": (c_i64, [c_vp]),
     "ctr_scalar_gathered_l2": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_f32, c_i64, c_i64, c_i32, c_f32, c_vp,
                                        c_vp]),
     "ctr_segment_sum_rows": (c_i32, [c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_i32, c_i32, c_vp, c_i32]),
@@ -185,7 +186,7 @@ def load(path: str = LIB_PATH) -> C.CDLL:
         fn.restype = res
         if args is not None:
             fn.argtypes = args
-    if lib.ctr_abi_version() != 3:
+    if lib.ctr_abi_version() != 4:
         raise CtrError("ABI version mismatch")
     if lib.ctr_sizeof_embed_cfg() != C.sizeof(EmbedCfg):
         raise CtrError("ctr_embed_cfg layout mismatch")

@@ -570,12 +570,28 @@ __global__ void cont_bwd_pass2(const float* __restrict__ ws, int nblk, int C, in
 }
 
 // wide part of Wide&Deep (models/wdl.py:240-246): d wdl_weights[id] += sum over the lookups (b, j) of that id of
-// dlogit[b].  The lookups arrive sorted by id (ctr_sort_ids + ctr_unique_segments); 8 lanes walk one run with a
-// fixed stride and a fixed shuffle tree, so the sum order never changes from run to run.
+// dlogit[b].  The lookups arrive sorted by id (ctr_sort_ids + ctr_unique_segments).  Three shapes of run, each with a fixed
+// order of additions (the result never changes from call to call):
+//   <= 64 lookups     8 lanes walk the run with a fixed stride, then a fixed shuffle tree
+//   <= SSA_HUGE       the whole warp, eight independent loads per lane in flight
+//   longer (the hottest ids of a Zipf-distributed field: tens of thousands of lookups, and ONE warp walking them was
+//                     0.24 ms of config 3): cut into pieces of SSA_PIECE lookups that a second launch sums one block per
+//                     piece, and a third adds up in piece order.  Pieces and runs are listed in the caller's workspace;
+//                     a run that does not fit the lists is summed by its warp after all.
+constexpr uint32_t SSA_HUGE = 2048, SSA_PIECE = 4096;
+constexpr int SSA_MAX_RUNS = 1024, SSA_MAX_PIECES = 8192;
+struct SsaWs {
+    uint32_t n_pieces, n_runs, pad0, pad1;
+    uint32_t run_key[SSA_MAX_RUNS], run_first[SSA_MAX_RUNS], run_np[SSA_MAX_RUNS];
+    uint32_t piece_lo[SSA_MAX_PIECES], piece_hi[SSA_MAX_PIECES];
+    float piece_sum[SSA_MAX_PIECES];
+};
+
 __global__ void __launch_bounds__(256)
 scalar_segment_add_kernel(const uint32_t* __restrict__ uniq, const uint32_t* __restrict__ seg_start,
                           const uint32_t* __restrict__ n_unique, int64_t n_max, const uint32_t* __restrict__ perm,
-                          const float* __restrict__ src, uint32_t ld, int64_t dst_rows, float* __restrict__ dst) {
+                          const float* __restrict__ src, uint32_t ld, int64_t dst_rows, float* __restrict__ dst,
+                          SsaWs* __restrict__ ws) {
     int64_t U = *n_unique;
     if (U > n_max) U = n_max;
     const int lane = threadIdx.x & 31, sub = lane & 7;
@@ -593,17 +609,36 @@ scalar_segment_add_kernel(const uint32_t* __restrict__ uniq, const uint32_t* __r
             e = seg_start[u + 1];
         }
         const bool live = key != CTR_PAD_KEY;
-        // a hot id of a Zipf-distributed field is looked up by thousands of samples: walked by 8 lanes with two dependent
-        // loads per element that one run WAS the kernel (1 ms at config 3).  Runs longer than 64 elements are summed by the
-        // whole warp, eight independent loads per lane in flight; the order of the additions depends on the run's length
-        // only, so the result stays reproducible.
         const bool is_long = live && (e - s) > 64u;
+        int listed = 0;
+        if (ws && is_long && sub == 0 && (e - s) > SSA_HUGE && (int64_t) key < dst_rows) {
+            const uint32_t np = (e - s + SSA_PIECE - 1) / SSA_PIECE;
+            const uint32_t r = atomicAdd(&ws->n_runs, 1u);
+            if (r < (uint32_t) SSA_MAX_RUNS) {
+                const uint32_t first = atomicAdd(&ws->n_pieces, np);
+                if (first + np <= (uint32_t) SSA_MAX_PIECES) {
+                    ws->run_key[r] = key; ws->run_first[r] = first; ws->run_np[r] = np;
+                    for (uint32_t p = 0; p < np; ++p) {
+                        ws->piece_lo[first + p] = s + p * SSA_PIECE;
+                        ws->piece_hi[first + p] = (s + (p + 1) * SSA_PIECE < e) ? s + (p + 1) * SSA_PIECE : e;
+                    }
+                    listed = 1;
+                } else {
+                    // no room for its pieces: an empty run entry, and the slots it reserved below the cap become empty pieces
+                    // (every slot under min(n_pieces, cap) is then either a real piece or a defined empty one); the warp
+                    // sums the run below
+                    ws->run_np[r] = 0;
+                    for (uint32_t p = first; p < first + np && p < (uint32_t) SSA_MAX_PIECES; ++p) ws->piece_lo[p] = ws->piece_hi[p] = 0u;
+                }
+            }
+        }
+        listed = __shfl_sync(0xffffffffu, listed, lane & ~7);
         if (live && !is_long)
             for (uint32_t i = s + sub; i < e; i += 8) acc += src[perm[i] / ld];
         acc += __shfl_xor_sync(0xffffffffu, acc, 1);
         acc += __shfl_xor_sync(0xffffffffu, acc, 2);
         acc += __shfl_xor_sync(0xffffffffu, acc, 4);
-        unsigned todo = __ballot_sync(0xffffffffu, is_long && sub == 0);
+        unsigned todo = __ballot_sync(0xffffffffu, is_long && !listed && sub == 0);
         while (todo) {
             const int owner = __ffs(todo) - 1;
             todo &= todo - 1;
@@ -620,8 +655,54 @@ scalar_segment_add_kernel(const uint32_t* __restrict__ uniq, const uint32_t* __r
             for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
             if (lane == owner) acc = t;
         }
-        if (sub == 0 && live && (int64_t) key < dst_rows) dst[key] += acc;
+        if (sub == 0 && live && !listed && (int64_t) key < dst_rows) dst[key] += acc;
     }
+}
+
+// one block per listed piece: threads stride over its lookups, four loads in flight each, fixed reduction tree
+__global__ void __launch_bounds__(256)
+scalar_segment_pieces_kernel(SsaWs* __restrict__ ws, const uint32_t* __restrict__ perm, const float* __restrict__ src, uint32_t ld) {
+    __shared__ float part[8];
+    uint32_t np = ws->n_pieces;
+    if (np > (uint32_t) SSA_MAX_PIECES) np = SSA_MAX_PIECES;
+    for (uint32_t p = blockIdx.x; p < np; p += gridDim.x) {
+        const uint32_t lo = ws->piece_lo[p], hi = ws->piece_hi[p];
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        uint32_t i = lo + threadIdx.x;
+        for (; i + 3 * 256 < hi; i += 4 * 256) {
+            a0 += src[perm[i] / ld]; a1 += src[perm[i + 256] / ld];
+            a2 += src[perm[i + 512] / ld]; a3 += src[perm[i + 768] / ld];
+        }
+        for (; i < hi; i += 256) a0 += src[perm[i] / ld];
+        float t = (a0 + a1) + (a2 + a3);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = t;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float r = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) r += part[w];
+            ws->piece_sum[p] = r;
+        }
+        __syncthreads();
+    }
+}
+
+// one thread per listed run: its pieces in order; then the counters go back to zero for the next call
+__global__ void __launch_bounds__(256)
+scalar_segment_runs_kernel(SsaWs* __restrict__ ws, int64_t dst_rows, float* __restrict__ dst) {
+    uint32_t nr = ws->n_runs;
+    if (nr > (uint32_t) SSA_MAX_RUNS) nr = SSA_MAX_RUNS;
+    for (uint32_t r = threadIdx.x; r < nr; r += blockDim.x) {
+        const uint32_t np = ws->run_np[r], first = ws->run_first[r], key = ws->run_key[r];
+        if (np == 0) continue;                    // listed without room for its pieces: its warp summed it
+        float t = 0.f;
+        for (uint32_t p = 0; p < np; ++p) t += ws->piece_sum[first + p];
+        if ((int64_t) key < dst_rows) dst[key] += t;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { ws->n_pieces = 0; ws->n_runs = 0; }
 }
 
 // l2 term over GATHERED scalar weights (models/wdl_textline.py:264-269,284-286: the regulariser sees the [B, W+H] lookup
@@ -963,15 +1044,25 @@ extern "C" int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg*
     return CTR_OK;
 }
 
+extern "C" int64_t ctr_scalar_segment_add_ws_bytes(ctr_handle*) { return (int64_t) ((sizeof(SsaWs) + 255) / 256 * 256); }
+
 extern "C" int ctr_scalar_segment_add(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const uint32_t* seg_start,
                                       const uint32_t* n_unique, int64_t n_max, const uint32_t* perm, const float* src,
-                                      int ld, int64_t dst_rows, float* dst) {
+                                      int ld, int64_t dst_rows, float* dst, void* ws, int64_t ws_bytes) {
     CTR_REQUIRE(h, uniq && seg_start && n_unique && perm && src && dst && ld > 0 && dst_rows > 0 && n_max >= 0,
                 "scalar_segment_add: bad args");
     if (n_max == 0) return CTR_OK;
+    // ws (optional, ctr_scalar_segment_add_ws_bytes; its first 16 bytes zero on the first call, the call leaves them zero):
+    // with it, runs of more than 2048 lookups are summed by many blocks instead of one warp
+    SsaWs* w = (ws && ws_bytes >= (int64_t) sizeof(SsaWs)) ? (SsaWs*) ws : nullptr;
     scalar_segment_add_kernel<<<grid_for(h, n_max * 8), 256, 0, ctr_st(s)>>>(uniq, seg_start, n_unique, n_max, perm, src,
-                                                                             (uint32_t) ld, dst_rows, dst);
+                                                                             (uint32_t) ld, dst_rows, dst, w);
     CTR_CHECK_LAUNCH(h, "scalar_segment_add");
+    if (w) {
+        scalar_segment_pieces_kernel<<<h->sm_count * 2, 256, 0, ctr_st(s)>>>(w, perm, src, (uint32_t) ld);
+        scalar_segment_runs_kernel<<<1, 256, 0, ctr_st(s)>>>(w, dst_rows, dst);
+        CTR_CHECK_LAUNCH(h, "scalar_segment_add (long runs)");
+    }
     return CTR_OK;
 }
 

@@ -973,6 +973,8 @@ class CtrEngine:
                    ptr(self.w_uidx), ptr(self.w_n_unique), ws, wsn, None)
             self.ev_sorted_w.record(self.side if st == self.side.cuda_stream else self._main_stream())
 
+    _ws_wide = None
+
     def _wdl_wide_grad(self, B: int) -> None:
         """d wdl_weights[id] += sum of dlogit over the wide lookups of id (added on top of the deep-projection
         rows W..W+H-1 that the colsum already wrote: quirk Q4 makes the two alias, models/wdl.py:224-228)"""
@@ -980,9 +982,11 @@ class CtrEngine:
         if not s.wide_fields:
             return
         self._main_stream().wait_event(self.ev_sorted_w)
+        if self._ws_wide is None:       # piece / run lists of the long-run path (zeroed once; every call leaves the counters at zero)
+            self._ws_wide = torch.zeros(self.h.query("ctr_scalar_segment_add_ws_bytes"), dtype=torch.uint8, device=self.dev)
         self.h.call("ctr_scalar_segment_add", self._stream(), ptr(self.w_uniq), ptr(self.w_seg_start), ptr(self.w_n_unique),
                     B * s.wide_fields, ptr(self.w_perm), ptr(self.dlogit), s.wide_fields, s.wide_rows + s.hidden[-1],
-                    ptr(self.view("wdl_weights", self.grad)))
+                    ptr(self.view("wdl_weights", self.grad)), ptr(self._ws_wide), self._ws_wide.numel())
         self._gathered_l2_term(B)
 
     def _gathered_l2_term(self, B: int) -> None:

@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define CTR_ABI_VERSION 3
+#define CTR_ABI_VERSION 4
 
 #define CTR_OK              0
 #define CTR_E_INVALID      -1   /* bad argument / unsupported shape */
@@ -342,7 +342,11 @@ int ctr_fm_cont_bwd(ctr_handle* h, ctr_stream s, const ctr_embed_cfg* cfg, const
  * is fixed.  Keys 0xFFFFFFFF and keys >= dst_rows are skipped. */
 int ctr_scalar_segment_add(ctr_handle* h, ctr_stream s, const uint32_t* uniq, const uint32_t* seg_start,
                            const uint32_t* n_unique, int64_t n_max, const uint32_t* perm, const float* src,
-                           int ld, int64_t dst_rows, float* dst);
+                           int ld, int64_t dst_rows, float* dst, void* ws, int64_t ws_bytes);
+/* ws of ctr_scalar_segment_add (may be NULL): with it, runs of more than 2048 lookups (the hottest ids of a Zipf-distributed
+ * wide field) are cut into pieces summed by one block each.  The caller zeroes the buffer ONCE; every call leaves its
+ * counters at zero again.  One buffer per stream that calls the function. */
+int64_t ctr_scalar_segment_add_ws_bytes(ctr_handle* h);
 
 /* l2 regulariser over GATHERED scalar weights (models/wdl_textline.py:264-269 overwrites weights["wdl_weights"] with
  * the [B, W+H] lookup result before :284-286 regularises it):  for run u of the sorted wide ids with c = run length,

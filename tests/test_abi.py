@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol(lib_built):
     for n in names:
         assert hasattr(lib, n), n
     assert set(names) == set(_lib.EXPORTS)
-    assert lib.ctr_abi_version() == 3
+    assert lib.ctr_abi_version() == 4
     assert lib.ctr_sizeof_embed_cfg() == C.sizeof(_lib.EmbedCfg) == 104
 
 

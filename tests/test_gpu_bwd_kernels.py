@@ -184,12 +184,25 @@ def test_scalar_segment_add_matches_add_at(hd):
     dst0 = g.standard_normal(rows + 10).astype(np.float32)
     dst = torch.from_numpy(dst0.copy()).cuda()
     t_src = torch.from_numpy(src).cuda()
-    hd.call("ctr_scalar_segment_add", _st(), _ptr(uniq), _ptr(seg), _ptr(nun), n, _ptr(perm), _ptr(t_src), ld, rows + 10, _ptr(dst))
+    hd.call("ctr_scalar_segment_add", _st(), _ptr(uniq), _ptr(seg), _ptr(nun), n, _ptr(perm), _ptr(t_src), ld, rows + 10, _ptr(dst),
+            None, 0)
     ref = dst0.astype(np.float64)
     np.add.at(ref, ids, np.broadcast_to(src[:, None].astype(np.float64), ids.shape))
     got = dst.cpu().numpy()
     assert np.max(np.abs(got - ref)) < 1e-4 * max(1.0, np.abs(ref).max())
     assert np.array_equal(got[rows:], dst0[rows:])
+    # with a workspace the run of 3000 (> 2048) is cut into pieces summed by one block each; twice in a row on the same
+    # workspace (every call leaves its counters at zero), same result both times
+    ws = torch.zeros(hd.query("ctr_scalar_segment_add_ws_bytes"), dtype=torch.uint8, device="cuda")
+    outs = []
+    for _ in range(2):
+        d2 = torch.from_numpy(dst0.copy()).cuda()
+        hd.call("ctr_scalar_segment_add", _st(), _ptr(uniq), _ptr(seg), _ptr(nun), n, _ptr(perm), _ptr(t_src), ld, rows + 10,
+                _ptr(d2), _ptr(ws), ws.numel())
+        outs.append(d2.cpu().numpy())
+    assert np.array_equal(outs[0], outs[1])
+    assert np.max(np.abs(outs[0] - ref)) < 1e-4 * max(1.0, np.abs(ref).max())
+    assert int(ws[:8].view(torch.int32).abs().sum().item()) == 0
 
 
 @pytest.mark.parametrize("k,has_first,use_fm", [(16, 1, 1), (16, 0, 0), (8, 1, 0), (32, 1, 1), (4, 0, 0)])
