@@ -160,7 +160,8 @@ int ctr_mlp_fwd(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
 int ctr_mlp_bwd_data(ctr_handle* h, ctr_stream s, int precision, int B, int K, int N,
                      const float* dZ, int64_t lddz, const float* W,
                      const float* mask, int64_t ldmask, float mask_scale, float* dX, int64_t lddx);
-/* TF32 path only: the forward pass of a hidden layer can leave ONE BIT per output element (1 = the stored activation
+/* (same reference lines as ctr_mlp_fwd / ctr_mlp_bwd_data: models/deepfm.py:121-126 and what minimize() differentiates
+ * through them.)  TF32 path only: the forward pass of a hidden layer can leave ONE BIT per output element (1 = the stored activation
  * is > 0) next to Y, and the data gradient of the NEXT layer can take those bits as its ReLU mask instead of re-reading
  * the fp32 activation (105 MB per layer at config 4, and the latency of those loads was the data-gradient GEMM's
  * epilogue).  Results are identical to the mask form.  The bit layout is private to the kernels (it follows the
